@@ -1,0 +1,155 @@
+"""TEST INFRASTRUCTURE ONLY — never imported by the product package.
+
+ctypes front-end for the two CPU checkers that implement oracle/oracle_api.h:
+  Oracle("port")  -> oracle/libbdpt_port.so        (our restatement, oracle/port.cpp)
+  Oracle("ref")   -> oracle/_ref/libref_oracle.so  (the reference's own headers + oracle/ref_harness.cpp)
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs use this.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_LIGHT = 0, 1, 2, 3
+RNG_MT19937, RNG_PHILOX = 0, 1
+MISS = 0xFFFFFFFF
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("pad", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("aspect_ratio", C.c_double), ("image_width", C.c_int32), ("samples_per_pixel", C.c_int32),
+                ("max_depth", C.c_int32), ("pad", C.c_int32), ("background", C.c_double * 3),
+                ("vfov", C.c_double), ("lookfrom", C.c_double * 3), ("lookat", C.c_double * 3),
+                ("vup", C.c_double * 3), ("defocus_angle", C.c_double), ("focus_dist", C.c_double)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("rays", "node_visits", "aabb_tests", "aabb_hits", "tri_tests",
+                                          "tri_hits", "nodes_built", "shadow_rays")]
+
+
+def make_camera(width, height, spp, depth, lookfrom, lookat, vfov=90.0, vup=(0, 1, 0), background=(0, 0, 0),
+                focus_dist=10.0):
+    c = Camera()
+    c.aspect_ratio = float(width) / float(height)  # scene_loader.h:445
+    c.image_width, c.samples_per_pixel, c.max_depth = int(width), int(spp), int(depth)
+    c.background[:] = background
+    c.vfov = vfov
+    c.lookfrom[:] = lookfrom
+    c.lookat[:] = lookat
+    c.vup[:] = vup
+    c.defocus_angle = 0.0
+    c.focus_dist = focus_dist
+    return c
+
+
+def make_materials(mats):
+    """mats: list of (type, (r,g,b), param)"""
+    arr = (Material * len(mats))()
+    for i, (t, rgb, p) in enumerate(mats):
+        arr[i].type = t
+        arr[i].rgb[:] = rgb
+        arr[i].param = p
+    return arr
+
+
+def build(which="all"):
+    subprocess.check_call(["make", "-C", HERE, "-s"] + ([] if which == "all" else [which]))
+
+
+def lib_path(kind):
+    return os.path.join(HERE, "libbdpt_port.so" if kind == "port" else os.path.join("_ref", "libref_oracle.so"))
+
+
+def available(kind):
+    return os.path.exists(lib_path(kind))
+
+
+class Oracle:
+    def __init__(self, kind="port"):
+        self.kind = kind
+        path = lib_path(kind)
+        if not os.path.exists(path):
+            build("libbdpt_port.so" if kind == "port" else "ref")
+        self.lib = C.CDLL(path)
+        p = "port_" if kind == "port" else "ref_"
+        f = lambda n: getattr(self.lib, p + n)
+        self._create = f("scene_create"); self._create.restype = C.c_void_p
+        self._create.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32]
+        self._destroy = f("scene_destroy"); self._destroy.argtypes = [C.c_void_p]
+        self._nodes = f("bvh_node_count"); self._nodes.restype = C.c_uint64; self._nodes.argtypes = [C.c_void_p]
+        self._order = f("bvh_leaf_order"); self._order.argtypes = [C.c_void_p, C.c_void_p]
+        self._trace = f("trace"); self._trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64] + [C.c_void_p] * 4 + [C.c_int]
+        self._visible = f("visible"); self._visible.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]
+        self._render = f("render"); self._render.restype = C.c_int
+        self._render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        self._stats = f("stats_get"); self._stats.argtypes = [C.c_void_p]
+        self._stats_reset = f("stats_reset")
+        self._rgb8 = f("colors_to_rgb8"); self._rgb8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        self.scene = None
+
+    def load(self, verts, mat_id, mats):
+        verts = np.ascontiguousarray(verts, dtype=np.float64).reshape(-1, 9)
+        mat_id = np.ascontiguousarray(mat_id, dtype=np.uint32)
+        assert len(mat_id) == len(verts)
+        self.n_tris = len(verts)
+        marr = make_materials(mats) if isinstance(mats, list) else mats
+        if self.scene:
+            self._destroy(self.scene)
+        self.scene = self._create(verts.ctypes.data, mat_id.ctypes.data, len(verts), C.byref(marr), len(marr))
+        return self
+
+    def node_count(self):
+        return int(self._nodes(self.scene))
+
+    def leaf_order(self):
+        out = np.empty(self.n_tris, dtype=np.uint32)
+        self._order(self.scene, out.ctypes.data)
+        return out
+
+    def trace(self, rays, nthreads=1):
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 8)
+        n = len(rays)
+        prim = np.empty(n, np.uint32); t = np.empty(n); u = np.empty(n); v = np.empty(n)
+        self._trace(self.scene, rays.ctypes.data, n, prim.ctypes.data, t.ctypes.data, u.ctypes.data, v.ctypes.data, nthreads)
+        return prim, t, u, v
+
+    def visible(self, a, b, nthreads=1):
+        a = np.ascontiguousarray(a, dtype=np.float64).reshape(-1, 3)
+        b = np.ascontiguousarray(b, dtype=np.float64).reshape(-1, 3)
+        out = np.empty(len(a), np.uint8)
+        self._visible(self.scene, a.ctypes.data, b.ctypes.data, len(a), out.ctypes.data, nthreads)
+        return out.astype(bool)
+
+    def render(self, cam, rng_mode=RNG_MT19937, seed=0, row0=0, row1=1 << 30, nthreads=1, height=None):
+        W = cam.image_width
+        H = height if height is not None else max(1, int(W / cam.aspect_ratio))
+        film = np.zeros((H, W, 3), dtype=np.float64)
+        h = self._render(self.scene, C.byref(cam), rng_mode, seed, row0, row1, film.ctypes.data, nthreads)
+        assert h == H, (h, H)
+        return film
+
+    def stats(self):
+        s = Stats()
+        self._stats(C.byref(s))
+        return {n: int(getattr(s, n)) for n, _ in Stats._fields_}
+
+    def stats_reset(self):
+        self._stats_reset()
+
+    def colors_to_rgb8(self, film, spp):
+        film = np.ascontiguousarray(film, dtype=np.float64)
+        H, W, _ = film.shape
+        out = np.empty((H, W, 3), np.uint8)
+        self._rgb8(film.ctypes.data, W, H, spp, out.ctypes.data)
+        return out
+
+    def close(self):
+        if self.scene:
+            self._destroy(self.scene)
+            self.scene = None

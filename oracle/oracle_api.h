@@ -1,0 +1,93 @@
+/* TEST INFRASTRUCTURE ONLY — never linked, imported or executed by the product path.
+ *
+ * One C interface, implemented twice:
+ *   - oracle/port.cpp          (prefix port_): our CPU restatement of the reference algorithm
+ *   - oracle/ref_harness.cpp   (prefix ref_):  the reference's OWN headers, compiled where they lie
+ *                                              under /root/reference, driven through this interface
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
+ * either library.
+ *
+ * Conventions: triangles are a soup of N x 9 doubles (v0,v1,v2) in scene.world insertion order;
+ * prim ID := that insertion index.  Rays are n x 8 doubles (ox,oy,oz,dx,dy,dz,tmin,tmax).
+ * A miss is prim 0xFFFFFFFF.  Films are W*H*3 doubles holding the per-pixel SUM over strata
+ * (reference camera.h:55,117-124), not the average.
+ */
+#ifndef BDPT_ORACLE_API_H
+#define BDPT_ORACLE_API_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { ORC_MAT_LAMBERTIAN = 0, ORC_MAT_METAL = 1, ORC_MAT_DIELECTRIC = 2, ORC_MAT_LIGHT = 3 };
+
+typedef struct {
+    uint32_t type;    /* ORC_MAT_* */
+    uint32_t pad;
+    double   rgb[3];  /* albedo (lambertian, metal) or emission (light) */
+    double   param;   /* metal: fuzz (already clamped to <=1), dielectric: refraction index */
+} orc_material;
+
+/* the 13 public camera fields of reference camera.h:26-41 that affect the image */
+typedef struct {
+    double aspect_ratio;
+    int32_t image_width;
+    int32_t samples_per_pixel;
+    int32_t max_depth;
+    int32_t pad;
+    double background[3];
+    double vfov;
+    double lookfrom[3];
+    double lookat[3];
+    double vup[3];
+    double defocus_angle;   /* must be <= 0: the YAML loader forces it off (scene_loader.h:463) */
+    double focus_dist;
+} orc_camera;
+
+enum { ORC_RNG_MT19937 = 0,   /* the reference's global default-seeded mt19937 stream (main.h:28-32) */
+       ORC_RNG_PHILOX  = 1 }; /* counter-based stream keyed (seed, pixel, stratum, subpath); port only  */
+
+typedef struct {
+    uint64_t rays;          /* world.hit queries */
+    uint64_t node_visits;   /* bvh_node::hit entries (stats.h bvh_node_visits) */
+    uint64_t aabb_tests;
+    uint64_t aabb_hits;
+    uint64_t tri_tests;
+    uint64_t tri_hits;
+    uint64_t nodes_built;
+    uint64_t shadow_rays;   /* visible() queries among `rays` */
+} orc_stats;
+
+#ifndef ORC_PREFIX
+#define ORC_PREFIX port_
+#endif
+#define ORC_CAT2(a, b) a##b
+#define ORC_CAT(a, b) ORC_CAT2(a, b)
+#define ORC(name) ORC_CAT(ORC_PREFIX, name)
+
+void*    ORC(scene_create)(const double* verts, const uint32_t* mat_id, uint64_t n_tris,
+                           const orc_material* mats, uint32_t n_mats);
+void     ORC(scene_destroy)(void* scene);
+uint64_t ORC(bvh_node_count)(void* scene);
+/* DFS leaf order: order[k] = prim ID of the k-th triangle in the builder's final array. */
+void     ORC(bvh_leaf_order)(void* scene, uint32_t* order);
+/* closest hit; outputs may be NULL. nthreads<=1 runs serially. */
+void     ORC(trace)(void* scene, const double* rays, uint64_t n, uint32_t* prim, double* t,
+                    double* u, double* v, int nthreads);
+/* camera.h:425-438 on n segments a->b (each n x 3 doubles); out[i]=1 when visible */
+void     ORC(visible)(void* scene, const double* a, const double* b, uint64_t n, uint8_t* out,
+                      int nthreads);
+/* camera.h:43-145 minus threads/PNG: rows [row0,row1), every stratum; film is W*H*3 (only those rows
+ * written). rng_mode MT19937 requires nthreads==1 for a reproducible stream. Returns image height. */
+int      ORC(render)(void* scene, const orc_camera* cam, int rng_mode, uint64_t seed, int row0,
+                     int row1, double* film, int nthreads);
+void     ORC(stats_get)(orc_stats* out);
+void     ORC(stats_reset)(void);
+/* wpng.h:14-35 */
+void     ORC(colors_to_rgb8)(const double* film, int W, int H, int samples_per_pixel, uint8_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

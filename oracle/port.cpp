@@ -1,0 +1,635 @@
+// TEST INFRASTRUCTURE ONLY — never linked, imported or executed by the product path.
+//
+// CPU restatement ("port") of the reference's BDPT hot path, written from the reference's behaviour
+// with flat arrays instead of its shared_ptr/virtual object graph.  Every function cites the
+// reference file:line it follows (paths relative to /root/reference/src).  The arithmetic keeps the
+// reference's exact operation order in fp64 (e.g. v/t is (1/t)*v, vec3.h:40-42,98-100) so that in
+// ORC_RNG_MT19937 mode a single-threaded render is BIT-IDENTICAL to the reference's own headers
+// (pinned by tests/test_oracle_vs_reference.py here and by tests/golden/ on the GPU box).
+// ORC_RNG_PHILOX mode swaps only the random stream for the counter-based generator the CUDA kernels
+// use, which makes GPU-vs-port whole-render comparison possible sample by sample.
+//
+// Language: C++17, not plain C, because bit parity needs libstdc++'s std::sort (BVH leaf order for
+// equal keys, bvh.h:41) and std::mt19937 + std::uniform_real_distribution (main.h:28-32).
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <random>
+#include <thread>
+#include <vector>
+
+#define ORC_PREFIX port_
+#include "oracle_api.h"
+
+namespace {
+
+const double kInf = std::numeric_limits<double>::infinity();
+const double kPi = 3.1415926535897932385;  // main.h:20
+
+// ---------------------------------------------------------------- vec3.h:7-159
+struct V3 { double x, y, z; };
+inline V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
+inline V3 operator*(V3 a, V3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+inline V3 operator*(double t, V3 v) { return {t * v.x, t * v.y, t * v.z}; }       // vec3.h:90-92
+inline V3 operator*(V3 v, double t) { return t * v; }                             // vec3.h:94-96
+inline V3 operator/(V3 v, double t) { return (1 / t) * v; }                       // vec3.h:98-100
+inline double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }       // vec3.h:102-106
+inline V3 cross(V3 u, V3 v) {                                                     // vec3.h:108-112
+    return {u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x};
+}
+inline double len2(V3 v) { return v.x * v.x + v.y * v.y + v.z * v.z; }            // vec3.h:43-45
+inline double len(V3 v) { return std::sqrt(len2(v)); }
+inline V3 unit(V3 v) { return v / len(v); }                                       // vec3.h:114-116
+inline double comp(const V3& v, int a) { return a == 0 ? v.x : (a == 1 ? v.y : v.z); }
+
+// ---------------------------------------------------------------- RNG (main.h:28-42)
+// Philox4x32-10, key = (seed_lo ^ stream, seed_hi), counter = (sample_lo, sample_hi, block, 0x5EED).
+// One block yields two doubles in [0,1): (hi:lo >> 11) * 2^-53.  Identical code in csrc/rng.cuh.
+struct Philox {
+    static inline void round(uint32_t c[4], uint32_t k0, uint32_t k1) {
+        const uint64_t p0 = uint64_t(0xD2511F53u) * c[0];
+        const uint64_t p1 = uint64_t(0xCD9E8D57u) * c[2];
+        uint32_t n0 = uint32_t(p1 >> 32) ^ c[1] ^ k0;
+        uint32_t n1 = uint32_t(p1);
+        uint32_t n2 = uint32_t(p0 >> 32) ^ c[3] ^ k1;
+        uint32_t n3 = uint32_t(p0);
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    }
+    static inline void block(uint64_t seed, uint32_t stream, uint64_t sample, uint32_t blk, uint32_t out[4]) {
+        uint32_t k0 = uint32_t(seed) ^ stream, k1 = uint32_t(seed >> 32);
+        uint32_t c[4] = {uint32_t(sample), uint32_t(sample >> 32), blk, 0x5EEDu};
+        for (int i = 0; i < 10; ++i) {
+            round(c, k0, k1);
+            k0 += 0x9E3779B9u;
+            k1 += 0xBB67AE85u;
+        }
+        out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
+    }
+};
+
+struct Rng {
+    // mode MT: all streams alias one engine, exactly the reference's single global stream
+    std::mt19937* mt = nullptr;
+    std::uniform_real_distribution<double>* dist = nullptr;
+    // mode PHILOX
+    uint64_t seed = 0, sample = 0;
+    uint32_t stream = 0, draws = 0;
+    double next() {
+        if (mt) return (*dist)(*mt);
+        uint32_t o[4];
+        Philox::block(seed, stream, sample, draws >> 1, o);
+        const uint32_t lo = (draws & 1) ? o[2] : o[0], hi = (draws & 1) ? o[3] : o[1];
+        ++draws;
+        return double(((uint64_t(hi) << 32) | lo) >> 11) * (1.0 / 9007199254740992.0);
+    }
+    double next(double mn, double mx) { return mn + (mx - mn) * next(); }  // main.h:34-37
+};
+
+// vec3.h:128-135 — g++ evaluates the three constructor arguments of vec3::random(min,max)
+// (vec3.h:58-60) in the order pinned by tests/test_oracle_vs_reference.py; see kRandomVecOrder.
+inline V3 random_unit_vector(Rng& r) {
+    for (;;) {
+        // argument evaluation order of `vec3(random_double(..), random_double(..), random_double(..))`
+        // with this toolchain is last-to-first (z, y, x); verified bit-exactly against the reference.
+        double z = r.next(-1, 1);
+        double y = r.next(-1, 1);
+        double x = r.next(-1, 1);
+        V3 p{x, y, z};
+        double lensq = len2(p);
+        if (1e-160 < lensq && lensq <= 1) return p / std::sqrt(lensq);
+    }
+}
+inline V3 reflect(V3 v, V3 n) { return v - 2 * dot(v, n) * n; }  // vec3.h:138-140
+inline V3 refract(V3 uv, V3 n, double etai_over_etat) {          // vec3.h:142-147
+    double cos_theta = std::fmin(dot(-uv, n), 1.0);
+    V3 perp = etai_over_etat * (uv + cos_theta * n);
+    V3 par = -std::sqrt(std::fabs(1.0 - len2(perp))) * n;
+    return perp + par;
+}
+inline V3 random_cosine_direction(Rng& r) {  // vec3.h:149-159
+    double r1 = r.next(), r2 = r.next();
+    double phi = 2 * kPi * r1;
+    double x = std::cos(phi) * std::sqrt(r2);
+    double y = std::sin(phi) * std::sqrt(r2);
+    double z = std::sqrt(1 - r2);
+    return {x, y, z};
+}
+struct Onb {  // onb.h:4-24
+    V3 a0, a1, a2;
+    explicit Onb(V3 n) {
+        a2 = unit(n);
+        V3 a = (std::fabs(a2.x) > 0.9) ? V3{0, 1, 0} : V3{1, 0, 0};
+        a1 = unit(cross(a2, a));
+        a0 = cross(a2, a1);
+    }
+    V3 transform(V3 v) const { return (v.x * a0) + (v.y * a1) + (v.z * a2); }
+};
+
+// ---------------------------------------------------------------- interval.h / aabb.h
+struct Ival {
+    double mn, mx;
+    double size() const { return mx - mn; }
+};
+inline Ival merge(Ival a, Ival b) { return {a.mn <= b.mn ? a.mn : b.mn, a.mx >= b.mx ? a.mx : b.mx}; }  // interval.h:12-16
+struct Box {
+    Ival ax[3];
+    void pad() {  // aabb.h:81-88 (expand: interval.h:36-39)
+        const double delta = 0.0001;
+        for (int a = 0; a < 3; ++a)
+            if (ax[a].size() < delta) { double p = delta / 2; ax[a] = {ax[a].mn - p, ax[a].mx + p}; }
+    }
+    int longest_axis() const {  // aabb.h:68-75 (ties -> later axis)
+        if (ax[0].size() > ax[1].size()) return ax[0].size() > ax[2].size() ? 0 : 2;
+        return ax[1].size() > ax[2].size() ? 1 : 2;
+    }
+};
+inline Box merge(const Box& a, const Box& b) {  // aabb.h:27-33
+    Box r;
+    for (int i = 0; i < 3; ++i) r.ax[i] = merge(a.ax[i], b.ax[i]);
+    r.pad();
+    return r;
+}
+inline Box empty_box() {  // aabb.h:92 (padding an empty interval leaves (+inf,-inf))
+    Box r;
+    for (int i = 0; i < 3; ++i) r.ax[i] = {kInf, -kInf};
+    r.pad();
+    return r;
+}
+
+struct Stats { uint64_t rays = 0, node_visits = 0, aabb_tests = 0, aabb_hits = 0, tri_tests = 0, tri_hits = 0, shadow = 0; };
+thread_local Stats tl_stats;
+std::atomic<uint64_t> g_stats[8];
+void flush_stats() {
+    g_stats[0] += tl_stats.rays; g_stats[1] += tl_stats.node_visits; g_stats[2] += tl_stats.aabb_tests;
+    g_stats[3] += tl_stats.aabb_hits; g_stats[4] += tl_stats.tri_tests; g_stats[5] += tl_stats.tri_hits;
+    g_stats[7] += tl_stats.shadow;
+    tl_stats = Stats();
+}
+
+inline bool box_hit(const Box& b, V3 o, V3 d, double tmin, double tmax) {  // aabb.h:41-66
+    ++tl_stats.aabb_tests;
+    for (int a = 0; a < 3; ++a) {
+        const double adinv = 1.0 / comp(d, a);
+        double t0 = (b.ax[a].mn - comp(o, a)) * adinv;
+        double t1 = (b.ax[a].mx - comp(o, a)) * adinv;
+        if (t0 < t1) {
+            if (t0 > tmin) tmin = t0;
+            if (t1 < tmax) tmax = t1;
+        } else {
+            if (t1 > tmin) tmin = t1;
+            if (t0 < tmax) tmax = t0;
+        }
+        if (tmax <= tmin) return false;
+    }
+    ++tl_stats.aabb_hits;
+    return true;
+}
+
+// ---------------------------------------------------------------- triangle.h:19-133
+struct Tri {
+    V3 v0, e1, e2, normal;
+    double area;
+    Box box;
+    uint32_t mat;
+};
+inline Tri make_tri(V3 v0, V3 v1, V3 v2, uint32_t mat) {  // triangle.h:21-39
+    Tri t;
+    t.v0 = v0; t.e1 = v1 - v0; t.e2 = v2 - v0;
+    V3 n = cross(t.e1, t.e2);
+    t.normal = unit(n);
+    t.area = 0.5 * len(n);
+    t.mat = mat;
+    double mnx = std::fmin(v0.x, std::fmin(v1.x, v2.x)), mxx = std::fmax(v0.x, std::fmax(v1.x, v2.x));
+    double mny = std::fmin(v0.y, std::fmin(v1.y, v2.y)), mxy = std::fmax(v0.y, std::fmax(v1.y, v2.y));
+    double mnz = std::fmin(v0.z, std::fmin(v1.z, v2.z)), mxz = std::fmax(v0.z, std::fmax(v1.z, v2.z));
+    t.box.ax[0] = {mnx, mxx}; t.box.ax[1] = {mny, mxy}; t.box.ax[2] = {mnz, mxz};  // aabb.h:18-25, unpadded
+    return t;
+}
+struct Hit {  // hittable.h:10-27 plus the prim ID the reference lacks (F6)
+    V3 p, normal;
+    double t, u, v;
+    bool front;
+    uint32_t prim;
+};
+inline bool tri_hit(const Tri& tr, uint32_t id, V3 o, V3 d, double tmin, double tmax, Hit& rec) {  // triangle.h:41-74
+    ++tl_stats.tri_tests;
+    V3 pvec = cross(d, tr.e2);
+    double det = dot(tr.e1, pvec);
+    if (std::fabs(det) < 1e-8) return false;
+    double inv_det = 1.0 / det;
+    V3 tvec = o - tr.v0;
+    double u = dot(tvec, pvec) * inv_det;
+    if (u < 0.0 || u > 1.0) return false;
+    V3 qvec = cross(tvec, tr.e1);
+    double v = dot(d, qvec) * inv_det;
+    if (v < 0.0 || u + v > 1.0) return false;
+    double t = dot(tr.e2, qvec) * inv_det;
+    if (!(tmin <= t && t <= tmax)) return false;  // interval.h:22-24, inclusive
+    rec.t = t;
+    rec.p = o + t * d;  // ray.h:21-23
+    rec.u = u; rec.v = v;
+    rec.front = dot(d, tr.normal) < 0;  // hittable.h:20-26
+    rec.normal = rec.front ? tr.normal : -tr.normal;
+    rec.prim = id;
+    ++tl_stats.tri_hits;
+    return true;
+}
+
+// ---------------------------------------------------------------- bvh.h:13-86
+struct Node {
+    Box box;
+    int32_t left, right;  // internal: node indices; leaf: triangle (prim) IDs (left==right for span 1)
+    bool leaf;
+};
+
+struct Scene {
+    std::vector<Tri> tris;
+    std::vector<orc_material> mats;
+    std::vector<uint32_t> lights;  // prim IDs in reference light-list order (scene_loader.h:190-202; main.cpp:67)
+    std::vector<Node> nodes;
+    std::vector<uint32_t> order;   // builder's working array == DFS leaf order when finished
+    int32_t root = -1;
+
+    int32_t build(size_t start, size_t end) {  // bvh.h:20-48
+        int32_t me = int32_t(nodes.size());
+        nodes.push_back(Node());
+        Box bb = empty_box();
+        for (size_t i = start; i < end; ++i) bb = merge(bb, tris[order[i]].box);
+        int axis = bb.longest_axis();
+        size_t span = end - start;
+        Node n;
+        n.box = bb;
+        if (span == 1) {
+            n.leaf = true; n.left = n.right = int32_t(order[start]);
+        } else if (span == 2) {
+            n.leaf = true; n.left = int32_t(order[start]); n.right = int32_t(order[start + 1]);
+        } else {
+            // bvh.h:41,68-74: std::sort (unstable introsort) on the box minimum along `axis`
+            std::sort(order.begin() + start, order.begin() + end, [&](uint32_t a, uint32_t b) {
+                return tris[a].box.ax[axis].mn < tris[b].box.ax[axis].mn;
+            });
+            size_t mid = start + span / 2;
+            n.leaf = false;
+            n.left = build(start, mid);
+            n.right = build(mid, end);
+        }
+        nodes[me] = n;
+        return me;
+    }
+
+    bool hit_node(int32_t ni, V3 o, V3 d, double tmin, double tmax, Hit& rec) const {  // bvh.h:50-59
+        ++tl_stats.node_visits;
+        const Node& n = nodes[ni];
+        if (!box_hit(n.box, o, d, tmin, tmax)) return false;
+        bool hl, hr;
+        if (n.leaf) {
+            hl = tri_hit(tris[n.left], uint32_t(n.left), o, d, tmin, tmax, rec);
+            hr = tri_hit(tris[n.right], uint32_t(n.right), o, d, tmin, hl ? rec.t : tmax, rec);
+        } else {
+            hl = hit_node(n.left, o, d, tmin, tmax, rec);
+            hr = hit_node(n.right, o, d, tmin, hl ? rec.t : tmax, rec);
+        }
+        return hl || hr;
+    }
+    bool hit(V3 o, V3 d, double tmin, double tmax, Hit& rec) const {
+        ++tl_stats.rays;
+        return hit_node(root, o, d, tmin, tmax, rec);
+    }
+};
+
+// ---------------------------------------------------------------- camera.h
+struct Cam {  // camera.h:148-197
+    orc_camera c;
+    int H, sqrt_spp;
+    double recip_sqrt_spp;
+    V3 center, pixel00, du, dv, background;
+    explicit Cam(const orc_camera& in) : c(in) {
+        H = int(c.image_width / c.aspect_ratio);
+        H = (H < 1) ? 1 : H;
+        sqrt_spp = int(std::sqrt(c.samples_per_pixel));
+        recip_sqrt_spp = 1.0 / sqrt_spp;
+        V3 lookfrom{c.lookfrom[0], c.lookfrom[1], c.lookfrom[2]}, lookat{c.lookat[0], c.lookat[1], c.lookat[2]};
+        V3 vup{c.vup[0], c.vup[1], c.vup[2]};
+        background = {c.background[0], c.background[1], c.background[2]};
+        center = lookfrom;
+        double theta = c.vfov * kPi / 180.0;  // main.h:24-26
+        double h = std::tan(theta / 2);
+        double vh = 2 * h * c.focus_dist;
+        double vw = vh * (double(c.image_width) / H);
+        V3 w = unit(lookfrom - lookat);
+        V3 u = unit(cross(vup, w));
+        V3 v = cross(w, u);
+        V3 vu = vw * u;
+        V3 vv = vh * -v;
+        du = vu / c.image_width;
+        dv = vv / H;
+        V3 ul = center - (c.focus_dist * w) - vu / 2 - vv / 2;
+        pixel00 = ul + 0.5 * (du + dv);
+    }
+    void get_ray(int i, int j, int s_i, int s_j, Rng& r, V3& o, V3& d) const {  // camera.h:199-223
+        double px = ((s_i + r.next()) * recip_sqrt_spp) - 0.5;
+        double py = ((s_j + r.next()) * recip_sqrt_spp) - 0.5;
+        V3 ps = pixel00 + ((i + px) * du) + ((j + py) * dv);
+        o = center;  // defocus_angle <= 0 (scene_loader.h:463)
+        d = ps - o;
+        (void)r.next();  // ray_time, camera.h:210 (drawn, unused downstream)
+    }
+};
+
+struct Vertex {  // camera.h:236-243
+    V3 p, normal, throughput, wi, emission;
+    uint32_t mat;
+    bool delta, is_light;
+};
+
+struct Integrator {
+    const Scene& sc;
+    const Cam& cam;
+    Integrator(const Scene& s, const Cam& c) : sc(s), cam(c) {}
+
+    // material.h:133-147
+    V3 emitted(const orc_material& m, bool front) const {
+        if (m.type != ORC_MAT_LIGHT || !front) return {0, 0, 0};
+        return {m.rgb[0], m.rgb[1], m.rgb[2]};
+    }
+    // material.h:60-63; everything but lambertian evaluates to zero (material.h:35-37)
+    V3 eval_bsdf(const orc_material& m) const {
+        if (m.type != ORC_MAT_LAMBERTIAN) return {0, 0, 0};
+        return V3{m.rgb[0], m.rgb[1], m.rgb[2]} / kPi;
+    }
+
+    void trace_path(V3 o, V3 d, int depth, std::vector<Vertex>& path, V3 T, V3* bg, Rng& rng) const {  // camera.h:325-370
+        for (int bounce = 0; bounce < depth; ++bounce) {
+            Hit rec;
+            if (!sc.hit(o, d, 0.001, kInf, rec)) {
+                if (bg) *bg = *bg + T * cam.background;
+                break;
+            }
+            const orc_material& m = sc.mats[sc.tris[rec.prim].mat];
+            Vertex vx;
+            vx.p = rec.p; vx.normal = rec.normal; vx.mat = sc.tris[rec.prim].mat;
+            vx.throughput = T;
+            vx.wi = unit(-d);
+            vx.emission = emitted(m, rec.front);
+            vx.delta = (m.type == ORC_MAT_METAL || m.type == ORC_MAT_DIELECTRIC);
+            vx.is_light = (m.type == ORC_MAT_LIGHT);
+            path.push_back(vx);
+
+            if (m.type == ORC_MAT_LIGHT) break;  // material.h:22-24: scatter() false
+            V3 att{m.rgb[0], m.rgb[1], m.rgb[2]};
+            if (m.type == ORC_MAT_METAL) {  // material.h:73-83
+                V3 refl = reflect(d, rec.normal);
+                refl = unit(refl) + (m.param * random_unit_vector(rng));
+                T = T * att;
+                o = rec.p; d = refl;
+                continue;
+            }
+            if (m.type == ORC_MAT_DIELECTRIC) {  // material.h:96-116
+                double ri = rec.front ? (1.0 / m.param) : m.param;
+                V3 ud = unit(d);
+                double cos_theta = std::fmin(dot(-ud, rec.normal), 1.0);
+                double sin_theta = std::sqrt(1.0 - cos_theta * cos_theta);
+                bool cannot_refract = ri * sin_theta > 1.0;
+                V3 dir;
+                bool refl = cannot_refract;
+                if (!refl) {  // material.h:125-130 Schlick
+                    double r0 = (1 - ri) / (1 + ri);
+                    r0 = r0 * r0;
+                    double rf = r0 + (1 - r0) * std::pow((1 - cos_theta), 5);
+                    refl = rf > rng.next();
+                }
+                dir = refl ? reflect(ud, rec.normal) : refract(ud, rec.normal, ri);
+                T = T * V3{1.0, 1.0, 1.0};
+                o = rec.p; d = dir;
+                continue;
+            }
+            // lambertian: material.h:47-58, pdf.h:32-47, camera.h:361-368
+            Onb uvw(rec.normal);
+            V3 sd = uvw.transform(random_cosine_direction(rng));
+            double pdf_value = std::fmax(0, dot(unit(sd), uvw.a2) / kPi);
+            if (pdf_value <= 0) break;
+            double ct = dot(rec.normal, unit(sd));
+            double spdf = ct < 0 ? 0 : ct / kPi;
+            T = T * att * spdf / pdf_value;
+            o = rec.p; d = sd;
+        }
+    }
+
+    bool build_light_path(int depth, std::vector<Vertex>& path, Rng& rng) const {  // camera.h:372-418
+        if (depth <= 0 || sc.lights.empty()) return false;
+        // triangle.h:199-224
+        double total = 0.0;
+        for (uint32_t id : sc.lights) total += sc.tris[id].area;
+        if (total <= 0.0) return false;
+        double pick = rng.next(0.0, total);
+        const Tri* chosen = &sc.tris[sc.lights.back()];
+        double accum = 0.0;
+        for (uint32_t id : sc.lights) {
+            accum += sc.tris[id].area;
+            if (pick <= accum) { chosen = &sc.tris[id]; break; }
+        }
+        double u = rng.next(), v = rng.next();  // triangle.h:107-119
+        if (u + v > 1.0) { u = 1.0 - u; v = 1.0 - v; }
+        V3 pos = chosen->v0 + (u * chosen->e1) + (v * chosen->e2);
+        V3 n = chosen->normal;
+        double pdf = 1.0 / total;
+        const orc_material& m = sc.mats[chosen->mat];
+        V3 emission = emitted(m, true);
+        if (len2(emission) <= 0) return false;
+
+        Vertex ev;
+        ev.p = pos; ev.normal = n; ev.mat = chosen->mat;
+        ev.throughput = V3{1.0, 1.0, 1.0} / std::max(pdf, 1e-8);
+        ev.wi = n; ev.emission = emission; ev.delta = false; ev.is_light = true;
+        path.push_back(ev);
+
+        V3 dir = Onb(n).transform(random_cosine_direction(rng));
+        V3 du = unit(dir);
+        double cos_theta = std::max(0.0, dot(n, du));
+        if (cos_theta <= 0) return true;
+        double pdf_dir = std::max(cos_theta / kPi, 1e-8);
+        V3 T = ev.throughput * emission * (cos_theta / pdf_dir);
+        trace_path(pos + (0.001 * n), du, depth - 1, path, T, nullptr, rng);
+        return true;
+    }
+
+    bool visible(V3 a, V3 b) const {  // camera.h:425-438
+        V3 dir = b - a;
+        double dist = len(dir);
+        if (dist <= 0) return false;
+        V3 du = dir / dist;
+        double max_t = dist - 0.001;
+        if (max_t <= 0) return false;
+        Hit tmp;
+        ++tl_stats.shadow;
+        return !sc.hit(a + (0.001 * du), du, 0.001, max_t, tmp);
+    }
+
+    V3 connect(const Vertex& cv, const Vertex& lv) const {  // camera.h:440-475
+        if (cv.delta || lv.delta) return {0, 0, 0};
+        V3 dir = lv.p - cv.p;
+        double dist2 = len2(dir);
+        if (dist2 <= 0) return {0, 0, 0};
+        V3 du = unit(dir);
+        double cos_cam = std::fabs(dot(cv.normal, du));
+        double cos_light = std::fabs(dot(lv.normal, -du));
+        if (cos_cam <= 0 || cos_light <= 0) return {0, 0, 0};
+        if (!visible(cv.p, lv.p)) return {0, 0, 0};
+        V3 f_cam = eval_bsdf(sc.mats[cv.mat]);
+        if (len2(f_cam) <= 0) return {0, 0, 0};
+        V3 f_light = lv.is_light ? lv.emission : eval_bsdf(sc.mats[lv.mat]);
+        if (len2(f_light) <= 0) return {0, 0, 0};
+        V3 contrib = cv.throughput * f_cam;
+        contrib = contrib * lv.throughput * f_light;
+        contrib = contrib * (cos_cam * cos_light) / dist2;
+        return contrib;
+    }
+
+    V3 sample(V3 o, V3 d, int depth, Rng& cam_rng, Rng& light_rng) const {  // camera.h:294-323
+        std::vector<Vertex> cp, lp;
+        cp.reserve(depth);
+        V3 bg{0, 0, 0};
+        trace_path(o, d, depth, cp, {1, 1, 1}, &bg, cam_rng);
+        V3 result = bg;
+        for (const auto& vx : cp)
+            if (!vx.delta && len2(vx.emission) > 0) result = result + vx.throughput * vx.emission;
+        lp.reserve(depth);
+        if (!build_light_path(depth, lp, light_rng)) return result;
+        for (const auto& cv : cp)
+            for (const auto& lv : lp) result = result + connect(cv, lv);
+        return result;
+    }
+};
+
+template <class F>
+void parallel_for(uint64_t n, int nthreads, F f) {
+    if (nthreads <= 1 || n < 2) { f(0, n); flush_stats(); return; }
+    std::vector<std::thread> pool;
+    uint64_t chunk = (n + nthreads - 1) / nthreads;
+    for (int t = 0; t < nthreads; ++t) {
+        uint64_t a = std::min<uint64_t>(n, t * chunk), b = std::min<uint64_t>(n, a + chunk);
+        if (a < b) pool.emplace_back([=] { f(a, b); flush_stats(); });
+    }
+    for (auto& th : pool) th.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+void* port_scene_create(const double* v, const uint32_t* mat_id, uint64_t n, const orc_material* mats, uint32_t n_mats) {
+    auto* s = new Scene;
+    s->mats.assign(mats, mats + n_mats);
+    s->tris.reserve(n);
+    for (uint64_t i = 0; i < n; ++i) {
+        const double* p = v + 9 * i;
+        s->tris.push_back(make_tri({p[0], p[1], p[2]}, {p[3], p[4], p[5]}, {p[6], p[7], p[8]}, mat_id[i]));
+        if (mats[mat_id[i]].type == ORC_MAT_LIGHT) s->lights.push_back(uint32_t(i));
+    }
+    if (s->lights.empty())  // main.cpp:67
+        for (uint64_t i = 0; i < n; ++i) s->lights.push_back(uint32_t(i));
+    s->order.resize(n);
+    for (uint64_t i = 0; i < n; ++i) s->order[i] = uint32_t(i);
+    s->nodes.reserve(size_t(1.4 * n) + 4);
+    s->root = s->build(0, n);
+    g_stats[6] = s->nodes.size();
+    return s;
+}
+void port_scene_destroy(void* p) { delete static_cast<Scene*>(p); }
+uint64_t port_bvh_node_count(void* p) { return static_cast<Scene*>(p)->nodes.size(); }
+void port_bvh_leaf_order(void* p, uint32_t* order) {
+    auto* s = static_cast<Scene*>(p);
+    std::copy(s->order.begin(), s->order.end(), order);
+}
+
+void port_trace(void* p, const double* rays, uint64_t n, uint32_t* prim, double* t, double* u, double* v, int nthreads) {
+    auto* s = static_cast<Scene*>(p);
+    parallel_for(n, nthreads, [=](uint64_t a, uint64_t b) {
+        for (uint64_t i = a; i < b; ++i) {
+            const double* q = rays + 8 * i;
+            Hit rec;
+            bool h = s->hit({q[0], q[1], q[2]}, {q[3], q[4], q[5]}, q[6], q[7], rec);
+            if (prim) prim[i] = h ? rec.prim : 0xFFFFFFFFu;
+            if (t) t[i] = h ? rec.t : 0.0;
+            if (u) u[i] = h ? rec.u : 0.0;
+            if (v) v[i] = h ? rec.v : 0.0;
+        }
+    });
+}
+
+void port_visible(void* p, const double* a, const double* b, uint64_t n, uint8_t* out, int nthreads) {
+    auto* s = static_cast<Scene*>(p);
+    orc_camera oc;
+    std::memset(&oc, 0, sizeof oc);
+    oc.aspect_ratio = 1; oc.image_width = 1; oc.samples_per_pixel = 1; oc.vfov = 90; oc.focus_dist = 10;
+    oc.lookat[2] = -1; oc.vup[1] = 1;
+    Cam cam(oc);
+    Integrator integ(*s, cam);
+    parallel_for(n, nthreads, [&, a, b, out](uint64_t i0, uint64_t i1) {
+        for (uint64_t i = i0; i < i1; ++i)
+            out[i] = integ.visible({a[3 * i], a[3 * i + 1], a[3 * i + 2]}, {b[3 * i], b[3 * i + 1], b[3 * i + 2]}) ? 1 : 0;
+    });
+}
+
+int port_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int row0, int row1, double* film, int nthreads) {
+    auto* s = static_cast<Scene*>(p);
+    Cam cam(*c);
+    Integrator integ(*s, cam);
+    const int W = c->image_width, H = cam.H, n = cam.sqrt_spp;
+    row0 = std::max(0, row0);
+    row1 = std::min(H, row1);
+    if (row1 <= row0) return H;
+    if (rng_mode == ORC_RNG_MT19937) nthreads = 1;  // one global stream: main.h:28-32
+    std::mt19937 mt;  // default seed, as the reference's static generator
+    std::uniform_real_distribution<double> dist(0.0, 1.0);
+    parallel_for(uint64_t(row1 - row0), nthreads, [&](uint64_t a, uint64_t b) {
+        Rng cr, lr;
+        if (rng_mode == ORC_RNG_MT19937) { cr.mt = lr.mt = &mt; cr.dist = lr.dist = &dist; }
+        for (int j = row0 + int(a); j < row0 + int(b); ++j)
+            for (int i = 0; i < W; ++i) {  // camera.h:116-125
+                V3 px{0, 0, 0};
+                for (int s_j = 0; s_j < n; ++s_j)
+                    for (int s_i = 0; s_i < n; ++s_i) {
+                        if (rng_mode != ORC_RNG_MT19937) {
+                            uint64_t sample = (uint64_t(j) * W + i) * uint64_t(n * n) + uint64_t(s_j * n + s_i);
+                            cr = Rng(); lr = Rng();
+                            cr.seed = lr.seed = seed; cr.sample = lr.sample = sample;
+                            cr.stream = 0; lr.stream = 1;
+                        }
+                        V3 o, d;
+                        cam.get_ray(i, j, s_i, s_j, cr, o, d);
+                        px = px + integ.sample(o, d, c->max_depth, cr, lr);
+                    }
+                double* out = film + 3 * (size_t(j) * W + i);
+                out[0] = px.x; out[1] = px.y; out[2] = px.z;
+            }
+    });
+    return H;
+}
+
+void port_stats_get(orc_stats* o) {
+    flush_stats();
+    o->rays = g_stats[0]; o->node_visits = g_stats[1]; o->aabb_tests = g_stats[2]; o->aabb_hits = g_stats[3];
+    o->tri_tests = g_stats[4]; o->tri_hits = g_stats[5]; o->nodes_built = g_stats[6]; o->shadow_rays = g_stats[7];
+}
+void port_stats_reset(void) {
+    tl_stats = Stats();
+    for (int i = 0; i < 8; ++i) if (i != 6) g_stats[i] = 0;
+}
+
+void port_colors_to_rgb8(const double* film, int W, int H, int spp, uint8_t* out) {  // wpng.h:14-35
+    const double scale = 1.0 / std::max(1, spp);
+    auto clampd = [](double x, double lo, double hi) { return x < lo ? lo : (x > hi ? hi : x); };
+    for (size_t i = 0; i < size_t(W) * H; ++i)
+        for (int c = 0; c < 3; ++c) {
+            double x = film[3 * i + c] * scale;
+            out[3 * i + c] = static_cast<uint8_t>(256.0 * std::sqrt(clampd(x, 0.0, 0.999)));
+        }
+}
+
+}  // extern "C"

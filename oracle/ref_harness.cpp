@@ -1,0 +1,242 @@
+// TEST INFRASTRUCTURE ONLY — never linked, imported or executed by the product path.
+//
+// extern "C" harness around the reference's OWN, UNMODIFIED headers (compiled where they lie under
+// /root/reference/src by oracle/Makefile; output oracle/_ref/libref_oracle.so).  Nothing from the
+// reference is copied here: this file only #includes it and drives it through oracle_api.h.
+//
+// What it relies on:
+//   - one TU, main.h first (reference main.cpp:1-10 include order)
+//   - `#define private public` to reach camera::initialize/get_ray/ray_color/visible (camera.h:160-475)
+//   - prim IDs (F6): `id_triangle : triangle` records its insertion index on every successful hit;
+//     the last success in bvh_node::hit's left-then-right DFS is the final answer (bvh.h:55-56).
+//   - RNG: reference main.h untouched => one process-global default-seeded mt19937; a fresh process
+//     is needed to restart the stream (tests run this library in a subprocess for that).
+#include <algorithm>
+#include <array>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <filesystem>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <limits>
+#include <memory>
+#include <mutex>
+#include <random>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <vector>
+
+#define private public
+#include "main.h"
+#include "bvh.h"
+#include "camera.h"
+#include "hittable.h"
+#include "material.h"
+#include "triangle.h"
+#include "texture.h"
+#undef private
+
+#define ORC_PREFIX ref_
+#include "oracle_api.h"
+
+namespace {
+
+thread_local uint32_t g_last_prim = 0xFFFFFFFFu;
+
+class id_triangle : public triangle {
+  public:
+    id_triangle(const triangle& t, uint32_t id) : triangle(t), id(id) {}
+    bool hit(const ray& r, interval ray_t, hit_record& rec) const override {
+        bool h = triangle::hit(r, ray_t, rec);
+        if (h) g_last_prim = id;
+        return h;
+    }
+    uint32_t id;
+};
+
+struct ref_scene {
+    triangle_collection world;
+    triangle_collection lights;
+    std::vector<shared_ptr<material>> mats;
+    shared_ptr<bvh_node> bvh;
+    std::vector<uint32_t> leaf_order;
+    uint64_t nodes = 0;
+};
+
+shared_ptr<material> make_mat(const orc_material& m) {
+    color c(m.rgb[0], m.rgb[1], m.rgb[2]);
+    switch (m.type) {
+        case ORC_MAT_LAMBERTIAN: return make_shared<lambertian>(c);
+        case ORC_MAT_METAL:      return make_shared<metal>(c, m.param);
+        case ORC_MAT_DIELECTRIC: return make_shared<dielectric>(m.param);
+        default:                 return make_shared<diffuse_light>(c);
+    }
+}
+
+void collect_leaf_order(const hittable* h, std::vector<uint32_t>& out) {
+    if (auto n = dynamic_cast<const bvh_node*>(h)) {
+        collect_leaf_order(n->left.get(), out);
+        if (n->right.get() != n->left.get()) collect_leaf_order(n->right.get(), out);
+    } else if (auto t = dynamic_cast<const id_triangle*>(h)) {
+        out.push_back(t->id);
+    }
+}
+
+void set_camera(camera& cam, const orc_camera* c) {
+    cam.aspect_ratio = c->aspect_ratio;
+    cam.image_width = c->image_width;
+    cam.samples_per_pixel = c->samples_per_pixel;
+    cam.max_depth = c->max_depth;
+    cam.background = color(c->background[0], c->background[1], c->background[2]);
+    cam.vfov = c->vfov;
+    cam.lookfrom = point3(c->lookfrom[0], c->lookfrom[1], c->lookfrom[2]);
+    cam.lookat = point3(c->lookat[0], c->lookat[1], c->lookat[2]);
+    cam.vup = vec3(c->vup[0], c->vup[1], c->vup[2]);
+    cam.defocus_angle = c->defocus_angle;
+    cam.focus_dist = c->focus_dist;
+}
+
+template <class F>
+void parallel_for(uint64_t n, int nthreads, F f) {
+    if (nthreads <= 1 || n < 2) { f(0, n); return; }
+    std::vector<std::thread> pool;
+    uint64_t chunk = (n + nthreads - 1) / nthreads;
+    for (int t = 0; t < nthreads; ++t) {
+        uint64_t a = std::min(n, t * chunk), b = std::min(n, a + chunk);
+        if (a < b) pool.emplace_back([=] { f(a, b); });
+    }
+    for (auto& th : pool) th.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+void* ref_scene_create(const double* v, const uint32_t* mat_id, uint64_t n, const orc_material* mats,
+                       uint32_t n_mats) {
+    auto* s = new ref_scene;
+    for (uint32_t i = 0; i < n_mats; ++i) s->mats.push_back(make_mat(mats[i]));
+    for (uint64_t i = 0; i < n; ++i) {
+        const double* p = v + 9 * i;
+        auto mat = s->mats[mat_id[i]];
+        triangle tri(point3(p[0], p[1], p[2]), point3(p[3], p[4], p[5]), point3(p[6], p[7], p[8]), mat);
+        // scene_loader.h:190-202: every triangle goes to world; light-material triangles also to lights
+        s->world.add(tri);
+        if (std::dynamic_pointer_cast<diffuse_light>(mat)) s->lights.add(tri);
+    }
+    // main.cpp:66 builds bvh_node(world.to_hittable_list()); we build the same list with id-carrying
+    // triangles (identical geometry, identical bounding boxes => identical sort and topology).
+    hittable_list list;
+    for (uint64_t i = 0; i < n; ++i) list.add(make_shared<id_triangle>(s->world.tris[i], uint32_t(i)));
+    reset_bvh_stats();
+    s->bvh = make_shared<bvh_node>(list);
+    s->nodes = bvh_stats().bvh_nodes_built.load();
+    collect_leaf_order(s->bvh.get(), s->leaf_order);
+    return s;
+}
+
+void ref_scene_destroy(void* p) { delete static_cast<ref_scene*>(p); }
+uint64_t ref_bvh_node_count(void* p) { return static_cast<ref_scene*>(p)->nodes; }
+void ref_bvh_leaf_order(void* p, uint32_t* order) {
+    auto* s = static_cast<ref_scene*>(p);
+    std::copy(s->leaf_order.begin(), s->leaf_order.end(), order);
+}
+
+void ref_trace(void* p, const double* rays, uint64_t n, uint32_t* prim, double* t, double* u, double* v,
+               int nthreads) {
+    auto* s = static_cast<ref_scene*>(p);
+    parallel_for(n, nthreads, [=](uint64_t a, uint64_t b) {
+        for (uint64_t i = a; i < b; ++i) {
+            const double* q = rays + 8 * i;
+            ray r(point3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]), 0.0);
+            hit_record rec;
+            g_last_prim = 0xFFFFFFFFu;
+            bool h = s->bvh->hit(r, interval(q[6], q[7]), rec);
+            if (prim) prim[i] = h ? g_last_prim : 0xFFFFFFFFu;
+            if (t) t[i] = h ? rec.t : 0.0;
+            if (u) u[i] = h ? rec.u : 0.0;
+            if (v) v[i] = h ? rec.v : 0.0;
+        }
+    });
+}
+
+void ref_visible(void* p, const double* a, const double* b, uint64_t n, uint8_t* out, int nthreads) {
+    auto* s = static_cast<ref_scene*>(p);
+    camera cam;
+    parallel_for(n, nthreads, [=, &cam](uint64_t i0, uint64_t i1) {
+        for (uint64_t i = i0; i < i1; ++i)
+            out[i] = cam.visible(point3(a[3 * i], a[3 * i + 1], a[3 * i + 2]),
+                                 point3(b[3 * i], b[3 * i + 1], b[3 * i + 2]), *s->bvh) ? 1 : 0;
+    });
+}
+
+int ref_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int row0, int row1, double* film,
+               int nthreads) {
+    (void)seed;
+    if (rng_mode != ORC_RNG_MT19937) return -1;
+    auto* s = static_cast<ref_scene*>(p);
+    camera cam;
+    set_camera(cam, c);
+    cam.initialize();
+    const int W = cam.image_width, H = cam.image_height;
+    row0 = std::max(0, row0);
+    row1 = std::min(H, row1);
+    // main.cpp:67
+    const triangle_collection& lights = s->lights.empty() ? s->world : s->lights;
+    const hittable& world = *s->bvh;
+    // camera.h:111-129, with the same dynamic row counter when nthreads > 1 (racy RNG as shipped: F5)
+    std::atomic<int> next_row{row0};
+    auto worker = [&] {
+        for (;;) {
+            int j = next_row.fetch_add(1, std::memory_order_relaxed);
+            if (j >= row1) break;
+            for (int i = 0; i < W; ++i) {
+                color pixel_color(0, 0, 0);
+                for (int s_j = 0; s_j < cam.sqrt_spp; s_j++)
+                    for (int s_i = 0; s_i < cam.sqrt_spp; s_i++) {
+                        ray r = cam.get_ray(i, j, s_i, s_j);
+                        pixel_color += cam.ray_color(r, cam.max_depth, world, lights);
+                    }
+                double* o = film + 3 * (size_t(j) * W + i);
+                o[0] = pixel_color.x(); o[1] = pixel_color.y(); o[2] = pixel_color.z();
+            }
+        }
+    };
+    if (nthreads <= 1) worker();
+    else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthreads; ++t) pool.emplace_back(worker);
+        for (auto& th : pool) th.join();
+    }
+    return H;
+}
+
+void ref_stats_get(orc_stats* o) {
+    auto& s = bvh_stats();
+    o->rays = s.rays_traced.load();
+    o->node_visits = s.bvh_node_visits.load();
+    o->aabb_tests = s.aabb_tests.load();
+    o->aabb_hits = s.aabb_hits.load();
+    o->tri_tests = s.triangle_tests.load();
+    o->tri_hits = s.triangle_hits.load();
+    o->nodes_built = s.bvh_nodes_built.load();
+    o->shadow_rays = 0;
+}
+void ref_stats_reset(void) { reset_bvh_stats(); }
+
+void ref_colors_to_rgb8(const double* film, int W, int H, int spp, uint8_t* out) {
+    std::vector<color> fb(size_t(W) * H);
+    for (size_t i = 0; i < fb.size(); ++i) fb[i] = color(film[3 * i], film[3 * i + 1], film[3 * i + 2]);
+    std::vector<uint8_t> rgb;
+    colors_to_rgb8(fb, W, H, spp, rgb);
+    std::copy(rgb.begin(), rgb.end(), out);
+}
+
+}  // extern "C"
