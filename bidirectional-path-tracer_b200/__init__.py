@@ -1,0 +1,260 @@
+"""B200-native BDPT hot path — thin ctypes binding over the C-ABI of include/bdpt.h.
+
+The product is libbdpt.so (hand-written CUDA for sm_100a + host C++); this module only marshals numpy
+buffers across the C boundary for tests and bench.py.  There is no CPU fallback: creating a `Context`
+without a CUDA device raises.  The directory name carries a hyphen, so import it with
+`importlib.import_module("bidirectional-path-tracer_b200")` (see __graft_entry__.load_package()).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libbdpt.so")
+
+MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_LIGHT = 0, 1, 2, 3
+BVH_REFERENCE, BVH_FAST = 0, 1
+TRACE_CLOSEST, TRACE_ANY, TRACE_DEVICE_PTRS, TRACE_STATS = 0, 1, 16, 32
+MISS = 0xFFFFFFFF
+
+RAY_DTYPE = np.dtype([("o", "<f8", 3), ("d", "<f8", 3), ("tmin", "<f8"), ("tmax", "<f8")])
+HIT_DTYPE = np.dtype([("t", "<f8"), ("u", "<f8"), ("v", "<f8"), ("prim", "<u4"), ("pad", "<u4")])
+
+EXPORTS = [
+    "bdpt_ctx_create", "bdpt_ctx_destroy", "bdpt_last_error", "bdpt_scene_upload", "bdpt_bvh_info",
+    "bdpt_bvh_leaf_order", "bdpt_host_bvh_build", "bdpt_trace", "bdpt_visible", "bdpt_render",
+    "bdpt_film_clear", "bdpt_film_device_ptr", "bdpt_film_download", "bdpt_film_to_rgb8", "bdpt_stats",
+    "bdpt_stats_reset", "bdpt_last_device_ms", "bdpt_sync",
+]
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("pad", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("aspect_ratio", C.c_double), ("image_width", C.c_int32), ("samples_per_pixel", C.c_int32),
+                ("max_depth", C.c_int32), ("pad", C.c_int32), ("background", C.c_double * 3),
+                ("vfov", C.c_double), ("lookfrom", C.c_double * 3), ("lookat", C.c_double * 3),
+                ("vup", C.c_double * 3), ("defocus_angle", C.c_double), ("focus_dist", C.c_double)]
+
+
+class RenderOpts(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("stratum_begin", C.c_int32), ("stratum_end", C.c_int32),
+                ("stratum_step", C.c_int32), ("bvh", C.c_int32), ("row_begin", C.c_int32),
+                ("row_end", C.c_int32), ("batch_samples", C.c_int64)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("rays_closest", "rays_shadow", "node_visits", "tri_tests", "samples",
+                                          "kernel_launches", "camera_vertices", "light_vertices")]
+
+
+class BdptError(RuntimeError):
+    pass
+
+
+def build_library(force=False):
+    """Compile libbdpt.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    if force:
+        subprocess.check_call(["make", "-C", os.path.join(HERE, "csrc"), "-s", "clean"])
+    subprocess.check_call(["make", "-C", os.path.join(HERE, "csrc"), "-s", "-j4"])
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise BdptError("libbdpt.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'`); "
+                            "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.bdpt_last_error.restype = C.c_char_p
+        L.bdpt_last_error.argtypes = [C.c_void_p]
+        L.bdpt_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.bdpt_ctx_destroy.argtypes = [C.c_void_p]
+        L.bdpt_ctx_destroy.restype = None
+        L.bdpt_scene_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32]
+        L.bdpt_bvh_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
+        L.bdpt_bvh_leaf_order.argtypes = [C.c_void_p, C.c_void_p]
+        L.bdpt_host_bvh_build.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.bdpt_trace.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]
+        L.bdpt_visible.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]
+        L.bdpt_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.bdpt_film_clear.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.bdpt_film_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        L.bdpt_film_download.argtypes = [C.c_void_p, C.c_void_p]
+        L.bdpt_film_to_rgb8.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.bdpt_stats.argtypes = [C.c_void_p, C.c_void_p]
+        L.bdpt_stats_reset.argtypes = [C.c_void_p]
+        L.bdpt_last_device_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.bdpt_sync.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def make_materials(mats):
+    """mats: list of (type, (r,g,b), param)"""
+    arr = (Material * len(mats))()
+    for i, (t, rgb, p) in enumerate(mats):
+        arr[i].type = int(t)
+        arr[i].rgb[:] = [float(x) for x in rgb]
+        arr[i].param = float(p)
+    return arr
+
+
+def make_camera(width, height, spp, depth, lookfrom, lookat, vfov=90.0, vup=(0, 1, 0), background=(0, 0, 0),
+                focus_dist=10.0):
+    c = Camera()
+    c.aspect_ratio = float(width) / float(height)  # scene_loader.h:445
+    c.image_width, c.samples_per_pixel, c.max_depth = int(width), int(spp), int(depth)
+    c.background[:] = background
+    c.vfov = vfov
+    c.lookfrom[:] = lookfrom
+    c.lookat[:] = lookat
+    c.vup[:] = vup
+    c.defocus_angle = 0.0
+    c.focus_dist = focus_dist
+    return c
+
+
+def pack_rays(rays8):
+    """(n,8) float64 [ox,oy,oz,dx,dy,dz,tmin,tmax] -> bdpt_ray records (same memory layout)."""
+    r = np.ascontiguousarray(rays8, dtype=np.float64).reshape(-1, 8)
+    return r.view(RAY_DTYPE).reshape(-1)
+
+
+def host_bvh_build(verts, fast=False):
+    """Reference-topology BVH on the host only: returns (leaf_order, n_ref_nodes, n_fast_nodes|None)."""
+    v = np.ascontiguousarray(verts, dtype=np.float64).reshape(-1, 9)
+    order = np.empty(len(v), np.uint32)
+    nr, nf = C.c_uint64(0), C.c_uint64(0)
+    rc = lib().bdpt_host_bvh_build(v.ctypes.data, len(v), order.ctypes.data, C.byref(nr), C.byref(nf) if fast else None)
+    if rc:
+        raise BdptError("bdpt_host_bvh_build failed: %d %s" % (rc, lib().bdpt_last_error(None).decode()))
+    return order, nr.value, (nf.value if fast else None)
+
+
+class Context:
+    """One CUDA device. Mirrors the reference's call sequence (main.cpp:62-78):
+    upload scene (= load + bvh_node ctor), then trace()/visible() (= world.hit) or render() (= camera::render)."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        rc = lib().bdpt_ctx_create(int(device), C.byref(self._h))
+        if rc:
+            raise BdptError("bdpt_ctx_create failed (%d): %s — no CPU fallback exists"
+                            % (rc, lib().bdpt_last_error(None).decode()))
+        self.n_tris = 0
+        self.film_shape = None
+
+    def _chk(self, rc, what):
+        if rc:
+            raise BdptError("%s failed (%d): %s" % (what, rc, lib().bdpt_last_error(self._h).decode()))
+
+    def close(self):
+        if self._h:
+            lib().bdpt_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def upload(self, verts, mat_id, mats):
+        v = np.ascontiguousarray(verts, dtype=np.float64).reshape(-1, 9)
+        m = np.ascontiguousarray(mat_id, dtype=np.uint32)
+        if len(m) != len(v):
+            raise ValueError("mat_id length")
+        marr = make_materials(mats) if isinstance(mats, list) else mats
+        self._chk(lib().bdpt_scene_upload(self._h, v.ctypes.data, m.ctypes.data, len(v), C.byref(marr), len(marr)),
+                  "bdpt_scene_upload")
+        self.n_tris = len(v)
+        return self
+
+    def bvh_info(self, bvh=BVH_REFERENCE):
+        n, d = C.c_uint64(0), C.c_uint32(0)
+        self._chk(lib().bdpt_bvh_info(self._h, bvh, C.byref(n), C.byref(d)), "bdpt_bvh_info")
+        return n.value, d.value
+
+    def leaf_order(self):
+        out = np.empty(self.n_tris, np.uint32)
+        self._chk(lib().bdpt_bvh_leaf_order(self._h, out.ctypes.data), "bdpt_bvh_leaf_order")
+        return out
+
+    def trace(self, rays8, bvh=BVH_REFERENCE, any_hit=False, stats=False):
+        """Host buffers in, host buffers out (the e2e path). Returns structured HIT_DTYPE array."""
+        r = pack_rays(rays8)
+        out = np.empty(len(r), HIT_DTYPE)
+        flags = (TRACE_ANY if any_hit else 0) | (TRACE_STATS if stats else 0)
+        self._chk(lib().bdpt_trace(self._h, bvh, r.ctypes.data if len(r) else None, len(r),
+                                   out.ctypes.data if len(r) else None, flags), "bdpt_trace")
+        return out
+
+    def trace_device(self, d_rays, n, d_out, bvh=BVH_REFERENCE, any_hit=False, stats=False):
+        """Device pointers (ints) in and out; nothing is copied."""
+        flags = TRACE_DEVICE_PTRS | (TRACE_ANY if any_hit else 0) | (TRACE_STATS if stats else 0)
+        self._chk(lib().bdpt_trace(self._h, bvh, C.c_void_p(d_rays), n, C.c_void_p(d_out), flags), "bdpt_trace")
+
+    def visible(self, a, b, bvh=BVH_REFERENCE):
+        a = np.ascontiguousarray(a, dtype=np.float64).reshape(-1, 3)
+        b = np.ascontiguousarray(b, dtype=np.float64).reshape(-1, 3)
+        out = np.empty(len(a), np.uint8)
+        self._chk(lib().bdpt_visible(self._h, bvh, a.ctypes.data, b.ctypes.data, len(a), out.ctypes.data, 0), "bdpt_visible")
+        return out.astype(bool)
+
+    def film_clear(self, width, height):
+        self._chk(lib().bdpt_film_clear(self._h, int(width), int(height)), "bdpt_film_clear")
+        self.film_shape = (int(height), int(width), 3)
+
+    def render(self, cam, seed=0, bvh=BVH_REFERENCE, strata=(0, 0, 1), rows=(0, 0), batch_samples=0, clear=True,
+               height=None):
+        """camera::render's sample loop; returns nothing — read the film with film()."""
+        W = cam.image_width
+        H = height if height is not None else max(1, int(W / cam.aspect_ratio))
+        if clear or self.film_shape != (H, W, 3):
+            self.film_clear(W, H)
+        o = RenderOpts()
+        o.seed = seed
+        o.stratum_begin, o.stratum_end, o.stratum_step = strata
+        o.bvh = bvh
+        o.row_begin, o.row_end = rows
+        o.batch_samples = batch_samples
+        self._chk(lib().bdpt_render(self._h, C.byref(cam), C.byref(o)), "bdpt_render")
+
+    def film(self):
+        out = np.empty(self.film_shape, np.float64)
+        self._chk(lib().bdpt_film_download(self._h, out.ctypes.data), "bdpt_film_download")
+        return out
+
+    def film_device_ptr(self):
+        p, n = C.c_void_p(), C.c_uint64(0)
+        self._chk(lib().bdpt_film_device_ptr(self._h, C.byref(p), C.byref(n)), "bdpt_film_device_ptr")
+        return p.value, n.value
+
+    def film_rgb8(self, spp):
+        out = np.empty(self.film_shape, np.uint8)
+        self._chk(lib().bdpt_film_to_rgb8(self._h, int(spp), out.ctypes.data), "bdpt_film_to_rgb8")
+        return out
+
+    def stats(self):
+        s = Stats()
+        self._chk(lib().bdpt_stats(self._h, C.byref(s)), "bdpt_stats")
+        return {n: int(getattr(s, n)) for n, _ in Stats._fields_}
+
+    def stats_reset(self):
+        self._chk(lib().bdpt_stats_reset(self._h), "bdpt_stats_reset")
+
+    def last_device_ms(self):
+        ms = C.c_double(0)
+        self._chk(lib().bdpt_last_device_ms(self._h, C.byref(ms)), "bdpt_last_device_ms")
+        return ms.value
+
+    def sync(self):
+        self._chk(lib().bdpt_sync(self._h), "bdpt_sync")

@@ -1,0 +1,416 @@
+// C-ABI of libbdpt (include/bdpt.h): context, scene upload, batch trace / visible, film access.
+// Compiled with -fmad=false: the trace kernels instantiate the reference-exact traversal.
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+
+#include "ctx.h"
+#include "traverse_ref.cuh"
+#include "traverse_fast.cuh"
+
+using namespace bdpt;
+
+namespace {
+
+std::string g_create_err;
+
+constexpr int kTraceBlock = 128;
+
+template <class T>
+int upload(bdpt_ctx* ctx, const std::vector<T>& h, const T** d) {
+    void* p = nullptr;
+    size_t bytes = std::max<size_t>(h.size() * sizeof(T), 16);
+    BDPT_CUDA(ctx, cudaMalloc(&p, bytes));
+    ctx->scene_allocs.push_back(p);
+    if (!h.empty()) BDPT_CUDA(ctx, cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *d = static_cast<const T*>(p);
+    return BDPT_OK;
+}
+
+void free_scene(bdpt_ctx* ctx) {
+    for (void* p : ctx->scene_allocs) cudaFree(p);
+    ctx->scene_allocs.clear();
+    ctx->have_scene = false;
+}
+
+// ---------------------------------------------------------------- batch kernels
+// hittable::hit over a ray batch (hittable.h:33, bvh.h:50-59)
+template <int BVH, bool ANY, bool STATS>
+__global__ void __launch_bounds__(kTraceBlock) k_trace(SceneView sc, const bdpt_ray* __restrict__ rays, uint64_t n,
+                                                      bdpt_hit* __restrict__ out, unsigned long long* stats) {
+    __shared__ int32_t s_stack[kRefStackLevels * kTraceBlock];
+    const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
+    TravStats st{0, 0};
+    if (i < n) {
+        const double2* q = reinterpret_cast<const double2*>(rays + i);
+        double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
+        RayD r;
+        r.o = mk(a.x, a.y, b.x); r.d = mk(b.y, c.x, c.y); r.tmin = e.x; r.tmax = e.y;
+        HitD h;
+        h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS;
+        bool found;
+        if (BVH == BDPT_BVH_REFERENCE)
+            found = traverse_ref<ANY, STATS>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, &st);
+        else
+            found = traverse_fast<ANY, STATS>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, &st);
+        double2* o = reinterpret_cast<double2*>(out + i);
+        if (!found) { h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS; }
+        o[0] = make_double2(h.t, h.u);
+        double2 w;
+        w.x = h.v;
+        w.y = __longlong_as_double((long long)(unsigned long long)h.prim);
+        o[1] = w;
+    }
+    if (STATS) {
+        atomicAdd(&stats[ST_NODE], (unsigned long long)st.nodes);
+        atomicAdd(&stats[ST_TRI], (unsigned long long)st.tris);
+    }
+}
+
+// camera::visible (camera.h:425-438)
+template <int BVH>
+__global__ void __launch_bounds__(kTraceBlock) k_visible(SceneView sc, const double* __restrict__ a,
+                                                        const double* __restrict__ b, uint64_t n,
+                                                        uint8_t* __restrict__ out) {
+    __shared__ int32_t s_stack[kRefStackLevels * kTraceBlock];
+    const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
+    if (i >= n) return;
+    D3 pa = mk(a[3 * i], a[3 * i + 1], a[3 * i + 2]), pb = mk(b[3 * i], b[3 * i + 1], b[3 * i + 2]);
+    D3 dir = pb - pa;
+    double dist = len(dir);
+    uint8_t vis = 0;
+    if (dist > 0) {
+        D3 du = dir / dist;
+        double max_t = dist - 0.001;
+        if (max_t > 0) {
+            RayD r;
+            r.o = pa + (0.001 * du); r.d = du; r.tmin = 0.001; r.tmax = max_t;
+            HitD h;
+            bool found;
+            if (BVH == BDPT_BVH_REFERENCE)
+                found = traverse_ref<true, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, nullptr);
+            else
+                found = traverse_fast<true, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, nullptr);
+            vis = found ? 0 : 1;
+        }
+    }
+    out[i] = vis;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- C-ABI
+extern "C" {
+
+int bdpt_ctx_create(int device, bdpt_ctx** out) {
+    if (!out) return BDPT_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        // no CPU fallback: the product path needs a CUDA device
+        g_create_err = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+        return BDPT_ERR_CUDA;
+    }
+    if (device < 0 || device >= count) { g_create_err = "device index out of range"; return BDPT_ERR_ARG; }
+    bdpt_ctx* ctx = new bdpt_ctx;
+    ctx->device = device;
+    auto fail = [&](const char* what, cudaError_t err) {
+        g_create_err = std::string(what) + ": " + cudaGetErrorString(err);
+        delete ctx;
+        return BDPT_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaMalloc(&ctx->d_stats, 16 * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc", e);
+    cudaMemset(ctx->d_stats, 0, 16 * sizeof(unsigned long long));
+    *out = ctx;
+    return BDPT_OK;
+}
+
+void bdpt_ctx_destroy(bdpt_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    render_free(ctx);
+    free_scene(ctx);
+    if (ctx->film) cudaFree(ctx->film);
+    if (ctx->d_stats) cudaFree(ctx->d_stats);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* bdpt_last_error(bdpt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
+                      const bdpt_material* mats, uint32_t n_mats) {
+    if (!ctx) return BDPT_ERR_ARG;
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    try {
+        flatten_scene(verts, mat_id, n_tris, mats, n_mats, ctx->host);
+        build_ref_bvh(ctx->host);
+        build_fast_bvh(ctx->host);
+    } catch (const std::exception& ex) {
+        ctx->err = ex.what();
+        return BDPT_ERR_ARG;
+    }
+    HostScene& h = ctx->host;
+    if (h.ref_depth >= uint32_t(kRefStackLevels) || h.fast_depth >= uint32_t(kRefStackLevels)) {
+        ctx->err = "BVH deeper than the traversal stack";
+        return BDPT_ERR_ARG;
+    }
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    free_scene(ctx);
+    SceneView v{};
+    int rc;
+    if ((rc = upload(ctx, h.ref_nodes, &v.ref_nodes))) return rc;
+    if ((rc = upload(ctx, h.fast_nodes, &v.fast_nodes))) return rc;
+    if ((rc = upload(ctx, h.fast_prims, &v.fast_prims))) return rc;
+    if ((rc = upload(ctx, h.dfs_rank, &v.dfs_rank))) return rc;
+    if ((rc = upload(ctx, h.tris, &v.tris))) return rc;
+    if ((rc = upload(ctx, h.shade, &v.shade))) return rc;
+    if ((rc = upload(ctx, h.mats, &v.mats))) return rc;
+    if ((rc = upload(ctx, h.lights, &v.lights))) return rc;
+    if ((rc = upload(ctx, h.light_area, &v.light_area))) return rc;
+    v.n_lights = uint32_t(h.lights.size());
+    v.n_tris = uint32_t(h.tris.size());
+    v.n_ref_nodes = uint32_t(h.ref_nodes.size());
+    v.n_fast_nodes = uint32_t(h.fast_nodes.size());
+    v.light_total_area = h.light_total_area;
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->view = v;
+    ctx->have_scene = true;
+    return BDPT_OK;
+}
+
+int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth) {
+    if (!ctx) return BDPT_ERR_ARG;
+    if (!ctx->have_scene) { ctx->err = "no scene uploaded"; return BDPT_ERR_STATE; }
+    if (bvh == BDPT_BVH_REFERENCE) {
+        if (n_nodes) *n_nodes = ctx->host.ref_nodes.size();
+        if (max_depth) *max_depth = ctx->host.ref_depth;
+    } else if (bvh == BDPT_BVH_FAST) {
+        if (n_nodes) *n_nodes = ctx->host.fast_nodes.size();
+        if (max_depth) *max_depth = ctx->host.fast_depth;
+    } else { ctx->err = "unknown bvh flavour"; return BDPT_ERR_ARG; }
+    return BDPT_OK;
+}
+
+int bdpt_host_bvh_build(const double* verts, uint64_t n_tris, uint32_t* order, uint64_t* ref_nodes,
+                        uint64_t* fast_nodes) {
+    if (!verts || n_tris == 0) return BDPT_ERR_ARG;
+    try {
+        HostScene h;
+        std::vector<uint32_t> mat_id(n_tris, 0u);
+        bdpt_material m{};
+        m.type = BDPT_MAT_LAMBERTIAN;
+        flatten_scene(verts, mat_id.data(), n_tris, &m, 1, h);
+        build_ref_bvh(h);
+        if (order) std::memcpy(order, h.leaf_order.data(), n_tris * sizeof(uint32_t));
+        if (ref_nodes) *ref_nodes = h.ref_nodes.size();
+        if (fast_nodes) { build_fast_bvh(h); *fast_nodes = h.fast_nodes.size(); }
+    } catch (const std::exception& ex) {
+        g_create_err = ex.what();
+        return BDPT_ERR_ARG;
+    }
+    return BDPT_OK;
+}
+
+int bdpt_bvh_leaf_order(bdpt_ctx* ctx, uint32_t* order) {
+    if (!ctx || !order) return BDPT_ERR_ARG;
+    if (!ctx->have_scene) { ctx->err = "no scene uploaded"; return BDPT_ERR_STATE; }
+    std::memcpy(order, ctx->host.leaf_order.data(), ctx->host.leaf_order.size() * sizeof(uint32_t));
+    return BDPT_OK;
+}
+
+static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t n, bdpt_hit* d_out, int flags) {
+    const bool any = (flags & BDPT_TRACE_ANY) != 0, stats = (flags & BDPT_TRACE_STATS) != 0;
+    const unsigned grid = unsigned((n + kTraceBlock - 1) / kTraceBlock);
+    SceneView v = ctx->view;
+    unsigned long long* st = ctx->d_stats;
+#define BDPT_LAUNCH(B, A, S) k_trace<B, A, S><<<grid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out, st)
+    if (bvh == BDPT_BVH_REFERENCE) {
+        if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, false); }
+        else     { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, false); }
+    } else {
+        if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_FAST, true, true); else BDPT_LAUNCH(BDPT_BVH_FAST, true, false); }
+        else     { if (stats) BDPT_LAUNCH(BDPT_BVH_FAST, false, true); else BDPT_LAUNCH(BDPT_BVH_FAST, false, false); }
+    }
+#undef BDPT_LAUNCH
+    ctx->launches += 1;
+    BDPT_CUDA(ctx, cudaGetLastError());
+    return BDPT_OK;
+}
+
+int bdpt_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* rays, uint64_t n, bdpt_hit* out, int flags) {
+    if (!ctx) return BDPT_ERR_ARG;
+    if (!ctx->have_scene) { ctx->err = "no scene uploaded"; return BDPT_ERR_STATE; }
+    if (bvh != BDPT_BVH_REFERENCE && bvh != BDPT_BVH_FAST) { ctx->err = "unknown bvh flavour"; return BDPT_ERR_ARG; }
+    if (n == 0) { ctx->last_ms = 0.0; return BDPT_OK; }   // empty batch: nothing to do
+    if (!rays || !out) { ctx->err = "null ray/hit pointer"; return BDPT_ERR_ARG; }
+    if (n > (uint64_t(1) << 31) * kTraceBlock) { ctx->err = "batch too large"; return BDPT_ERR_ARG; }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const bool dev = (flags & BDPT_TRACE_DEVICE_PTRS) != 0;
+    const bdpt_ray* d_rays = rays;
+    bdpt_hit* d_out = out;
+    void *tmp_r = nullptr, *tmp_o = nullptr;
+    if (!dev) {
+        BDPT_CUDA(ctx, cudaMalloc(&tmp_r, n * sizeof(bdpt_ray)));
+        if (cudaMalloc(&tmp_o, n * sizeof(bdpt_hit)) != cudaSuccess) { cudaFree(tmp_r); ctx->err = "cudaMalloc hits"; return BDPT_ERR_NOMEM; }
+        BDPT_CUDA(ctx, cudaMemcpyAsync(tmp_r, rays, n * sizeof(bdpt_ray), cudaMemcpyHostToDevice, ctx->stream));
+        d_rays = static_cast<const bdpt_ray*>(tmp_r);
+        d_out = static_cast<bdpt_hit*>(tmp_o);
+    }
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    int rc = launch_trace(ctx, bvh, d_rays, n, d_out, flags);
+    if (rc) { cudaFree(tmp_r); cudaFree(tmp_o); return rc; }
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (!dev) BDPT_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * sizeof(bdpt_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (!dev) { cudaFree(tmp_r); cudaFree(tmp_o); }
+    if (e != cudaSuccess) { ctx->err = std::string("trace: ") + cudaGetErrorString(e); return BDPT_ERR_CUDA; }
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_ms = ms;
+    return BDPT_OK;
+}
+
+int bdpt_visible(bdpt_ctx* ctx, int bvh, const double* a, const double* b, uint64_t n, uint8_t* out, int flags) {
+    if (!ctx) return BDPT_ERR_ARG;
+    if (!ctx->have_scene) { ctx->err = "no scene uploaded"; return BDPT_ERR_STATE; }
+    if (bvh != BDPT_BVH_REFERENCE && bvh != BDPT_BVH_FAST) { ctx->err = "unknown bvh flavour"; return BDPT_ERR_ARG; }
+    if (n == 0) { ctx->last_ms = 0.0; return BDPT_OK; }
+    if (!a || !b || !out) { ctx->err = "null pointer"; return BDPT_ERR_ARG; }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const bool dev = (flags & BDPT_TRACE_DEVICE_PTRS) != 0;
+    const double *da = a, *db = b;
+    uint8_t* dout = out;
+    void *ta = nullptr, *tb = nullptr, *to = nullptr;
+    if (!dev) {
+        BDPT_CUDA(ctx, cudaMalloc(&ta, n * 24));
+        BDPT_CUDA(ctx, cudaMalloc(&tb, n * 24));
+        BDPT_CUDA(ctx, cudaMalloc(&to, n));
+        BDPT_CUDA(ctx, cudaMemcpyAsync(ta, a, n * 24, cudaMemcpyHostToDevice, ctx->stream));
+        BDPT_CUDA(ctx, cudaMemcpyAsync(tb, b, n * 24, cudaMemcpyHostToDevice, ctx->stream));
+        da = static_cast<const double*>(ta); db = static_cast<const double*>(tb); dout = static_cast<uint8_t*>(to);
+    }
+    const unsigned grid = unsigned((n + kTraceBlock - 1) / kTraceBlock);
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    if (bvh == BDPT_BVH_REFERENCE) k_visible<BDPT_BVH_REFERENCE><<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->view, da, db, n, dout);
+    else k_visible<BDPT_BVH_FAST><<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->view, da, db, n, dout);
+    ctx->launches += 1;
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    if (!dev) BDPT_CUDA(ctx, cudaMemcpyAsync(out, dout, n, cudaMemcpyDeviceToHost, ctx->stream));
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (!dev) { cudaFree(ta); cudaFree(tb); cudaFree(to); }
+    if (e != cudaSuccess) { ctx->err = std::string("visible: ") + cudaGetErrorString(e); return BDPT_ERR_CUDA; }
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_ms = ms;
+    return BDPT_OK;
+}
+
+// wpng.h:14-35: average, clamp to [0,0.999], gamma 2, 256x truncate
+__global__ void k_tonemap(const double* __restrict__ film, uint64_t n, double scale, uint8_t* __restrict__ out) {
+    uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double x = film[i] * scale;
+    x = x < 0.0 ? 0.0 : (x > 0.999 ? 0.999 : x);   // interval::clamp, interval.h:30-34 (NaN passes through)
+    out[i] = static_cast<uint8_t>(256.0 * sqrt(x));
+}
+
+int bdpt_film_clear(bdpt_ctx* ctx, int width, int height) {
+    if (!ctx || width <= 0 || height <= 0) return BDPT_ERR_ARG;
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!ctx->film || ctx->film_w != width || ctx->film_h != height) {
+        BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (ctx->film) cudaFree(ctx->film);
+        ctx->film = nullptr;
+        BDPT_CUDA(ctx, cudaMalloc(&ctx->film, size_t(width) * height * 3 * sizeof(double)));
+        ctx->film_w = width; ctx->film_h = height;
+    }
+    BDPT_CUDA(ctx, cudaMemsetAsync(ctx->film, 0, size_t(width) * height * 3 * sizeof(double), ctx->stream));
+    return BDPT_OK;
+}
+
+int bdpt_film_device_ptr(bdpt_ctx* ctx, void** ptr, uint64_t* n_doubles) {
+    if (!ctx || !ptr) return BDPT_ERR_ARG;
+    if (!ctx->film) { ctx->err = "no film"; return BDPT_ERR_STATE; }
+    *ptr = ctx->film;
+    if (n_doubles) *n_doubles = uint64_t(ctx->film_w) * ctx->film_h * 3;
+    return BDPT_OK;
+}
+
+int bdpt_film_download(bdpt_ctx* ctx, double* film_sum) {
+    if (!ctx || !film_sum) return BDPT_ERR_ARG;
+    if (!ctx->film) { ctx->err = "no film"; return BDPT_ERR_STATE; }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    BDPT_CUDA(ctx, cudaMemcpyAsync(film_sum, ctx->film, size_t(ctx->film_w) * ctx->film_h * 3 * sizeof(double),
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BDPT_OK;
+}
+
+int bdpt_film_to_rgb8(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out) {
+    if (!ctx || !out) return BDPT_ERR_ARG;
+    if (!ctx->film) { ctx->err = "no film"; return BDPT_ERR_STATE; }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const uint64_t n = uint64_t(ctx->film_w) * ctx->film_h * 3;
+    uint8_t* d = nullptr;
+    BDPT_CUDA(ctx, cudaMalloc(&d, n));
+    const double scale = 1.0 / double(samples_per_pixel > 1 ? samples_per_pixel : 1);  // wpng.h:18
+    k_tonemap<<<unsigned((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->film, n, scale, d);
+    ctx->launches += 1;
+    cudaError_t e = cudaMemcpyAsync(out, d, n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) { ctx->err = std::string("tonemap: ") + cudaGetErrorString(e); return BDPT_ERR_CUDA; }
+    return BDPT_OK;
+}
+
+int bdpt_render(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts) {
+    if (!ctx || !cam) return BDPT_ERR_ARG;
+    if (!ctx->have_scene) { ctx->err = "no scene uploaded"; return BDPT_ERR_STATE; }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    return render_impl(ctx, cam, opts);
+}
+
+int bdpt_stats(bdpt_ctx* ctx, bdpt_stats_t* out) {
+    if (!ctx || !out) return BDPT_ERR_ARG;
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned long long h[16];
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BDPT_CUDA(ctx, cudaMemcpy(h, ctx->d_stats, sizeof h, cudaMemcpyDeviceToHost));
+    out->node_visits = h[ST_NODE]; out->tri_tests = h[ST_TRI];
+    out->rays_closest = h[ST_RAYS_CLOSEST]; out->rays_shadow = h[ST_RAYS_SHADOW];
+    out->camera_vertices = h[ST_CAM_VERTS]; out->light_vertices = h[ST_LIGHT_VERTS];
+    out->samples = ctx->samples; out->kernel_launches = ctx->launches;
+    return BDPT_OK;
+}
+
+int bdpt_stats_reset(bdpt_ctx* ctx) {
+    if (!ctx) return BDPT_ERR_ARG;
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    BDPT_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, 16 * sizeof(unsigned long long), ctx->stream));
+    ctx->samples = 0; ctx->launches = 0;
+    return BDPT_OK;
+}
+
+int bdpt_last_device_ms(bdpt_ctx* ctx, double* ms) {
+    if (!ctx || !ms) return BDPT_ERR_ARG;
+    *ms = ctx->last_ms;
+    return BDPT_OK;
+}
+
+int bdpt_sync(bdpt_ctx* ctx) {
+    if (!ctx) return BDPT_ERR_ARG;
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return BDPT_OK;
+}
+
+}  // extern "C"

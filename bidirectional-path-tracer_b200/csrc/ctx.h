@@ -1,0 +1,52 @@
+// libbdpt context: one CUDA device, one stream, device-resident scene + film.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "host_scene.h"
+
+struct bdpt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    double last_ms = 0.0;
+
+    bdpt::HostScene host;
+    bool have_scene = false;
+    bdpt::SceneView view{};
+    std::vector<void*> scene_allocs;
+
+    // film (camera.h:55): fp64 RGB sum
+    double* film = nullptr;
+    int film_w = 0, film_h = 0;
+
+    // counters
+    unsigned long long* d_stats = nullptr;  // [16] device counters
+    uint64_t launches = 0;
+    uint64_t samples = 0;
+
+    // wavefront workspace (render.cu)
+    void* wf = nullptr;
+};
+
+namespace bdpt {
+
+#define BDPT_CUDA(ctx, call)                                                              \
+    do {                                                                                  \
+        cudaError_t e__ = (call);                                                         \
+        if (e__ != cudaSuccess) {                                                         \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);             \
+            return BDPT_ERR_CUDA;                                                         \
+        }                                                                                 \
+    } while (0)
+
+// device counter slots
+enum { ST_NODE = 0, ST_TRI = 1, ST_RAYS_CLOSEST = 2, ST_RAYS_SHADOW = 3, ST_CAM_VERTS = 4, ST_LIGHT_VERTS = 5 };
+
+int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts);
+void render_free(bdpt_ctx* ctx);
+
+}  // namespace bdpt

@@ -1,0 +1,191 @@
+// Binned-SAH builder for the fast BVH (host).  Not a reference behaviour: the reference only has the
+// median split of src/acceleration/bvh.h:20-48 (kept bit-exactly in host_scene.cu); this tree exists so
+// that traversal visits fewer nodes while returning the same hits (traverse_fast.cuh).
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <limits>
+
+#include "host_scene.h"
+
+namespace bdpt {
+
+namespace {
+
+constexpr int kBins = 16;
+constexpr uint32_t kMaxLeaf = 4;
+constexpr double kTravCost = 1.0, kTriCost = 1.5;
+
+struct B3 {
+    double lo[3], hi[3];
+    void reset() {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::numeric_limits<double>::infinity(); hi[k] = -lo[k]; }
+    }
+    void grow(const double* b) {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], b[k]); hi[k] = std::max(hi[k], b[3 + k]); }
+    }
+    void grow(const B3& o) {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], o.lo[k]); hi[k] = std::max(hi[k], o.hi[k]); }
+    }
+    double half_area() const {
+        double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        if (!(dx >= 0)) return 0.0;
+        return dx * dy + dy * dz + dz * dx;
+    }
+};
+
+inline float down32(double v) {
+    float f = float(v);
+    if (double(f) > v) f = std::nextafterf(f, -INFINITY);
+    return f;
+}
+inline float up32(double v) {
+    float f = float(v);
+    if (double(f) < v) f = std::nextafterf(f, INFINITY);
+    return f;
+}
+
+struct Task { uint32_t begin, end, depth; int32_t node; int side; };
+
+}  // namespace
+
+void build_fast_bvh(HostScene& s) {
+    const uint32_t n = uint32_t(s.tris.size());
+    const double* tb = s.tri_box.data();
+    s.fast_prims.resize(n);
+    for (uint32_t i = 0; i < n; ++i) s.fast_prims[i] = i;
+    s.fast_nodes.clear();
+    s.fast_nodes.reserve(n / 2 + 4);
+    B3 scene;
+    scene.reset();
+    for (uint32_t i = 0; i < n; ++i) scene.grow(tb + 6 * size_t(i));
+    double ext = 0.0;
+    for (int k = 0; k < 3; ++k) ext = std::max(ext, scene.hi[k] - scene.lo[k]);
+    // outward padding: far above fp64 slab/triangle rounding noise, far below feature size
+    const double eps = std::max(ext, 1e-30) * (1.0 / 1048576.0);
+
+    auto range_box = [&](uint32_t b, uint32_t e) {
+        B3 r; r.reset();
+        for (uint32_t i = b; i < e; ++i) r.grow(tb + 6 * size_t(s.fast_prims[i]));
+        return r;
+    };
+    auto store_box = [&](FastNode& nd, int side, const B3& b) {
+        float* lo = side ? nd.r_lo : nd.l_lo;
+        float* hi = side ? nd.r_hi : nd.l_hi;
+        for (int k = 0; k < 3; ++k) { lo[k] = down32(b.lo[k] - eps); hi[k] = up32(b.hi[k] + eps); }
+    };
+    auto leaf_code = [](uint32_t first, uint32_t cnt) { return int32_t(~((first << 3) | (cnt - 1))); };
+
+    uint32_t max_depth = 0;
+    std::vector<Task> todo;
+    // root: always an internal node so the kernel never special-cases
+    s.fast_nodes.push_back(FastNode());
+    todo.push_back(Task{0, n, 0, -1, 0});
+    bool root_done = false;
+    while (!todo.empty()) {
+        Task t = todo.back();
+        todo.pop_back();
+        const uint32_t cnt = t.end - t.begin;
+        max_depth = std::max(max_depth, t.depth);
+        B3 bb = range_box(t.begin, t.end);
+        // leaf?  (never for the root task: it must produce node 0)
+        if (t.node >= 0 && cnt <= kMaxLeaf) {
+            // decided by the parent (it stored the box); just encode
+            FastNode& p = s.fast_nodes[t.node];
+            (t.side ? p.right : p.left) = leaf_code(t.begin, cnt);
+            continue;
+        }
+        int32_t me;
+        if (t.node < 0) { me = 0; root_done = true; }
+        else {
+            me = int32_t(s.fast_nodes.size());
+            s.fast_nodes.push_back(FastNode());
+            FastNode& p = s.fast_nodes[t.node];
+            (t.side ? p.right : p.left) = me;
+        }
+        uint32_t mid = t.begin;
+        if (cnt == 1) {
+            // degenerate root: duplicate the single triangle as both children
+            FastNode nd{};
+            store_box(nd, 0, bb); store_box(nd, 1, bb);
+            nd.left = leaf_code(t.begin, 1); nd.right = leaf_code(t.begin, 1);
+            s.fast_nodes[me] = nd;
+            continue;
+        }
+        // centroid bounds
+        double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t i = t.begin; i < t.end; ++i) {
+            const double* b = tb + 6 * size_t(s.fast_prims[i]);
+            for (int k = 0; k < 3; ++k) {
+                double c = 0.5 * (b[k] + b[3 + k]);
+                clo[k] = std::min(clo[k], c); chi[k] = std::max(chi[k], c);
+            }
+        }
+        int axis = 0;
+        for (int k = 1; k < 3; ++k) if (chi[k] - clo[k] > chi[axis] - clo[axis]) axis = k;
+        const double cext = chi[axis] - clo[axis];
+        bool split_ok = false;
+        if (cext > 0 && t.depth < 22 && cnt > 2) {
+            // binned SAH over all three axes
+            double best_cost = std::numeric_limits<double>::infinity();
+            int best_axis = -1, best_bin = -1;
+            for (int ax = 0; ax < 3; ++ax) {
+                const double e = chi[ax] - clo[ax];
+                if (!(e > 0)) continue;
+                B3 bins[kBins]; uint32_t bc[kBins];
+                for (int b = 0; b < kBins; ++b) { bins[b].reset(); bc[b] = 0; }
+                const double sc = kBins / e;
+                for (uint32_t i = t.begin; i < t.end; ++i) {
+                    const double* b = tb + 6 * size_t(s.fast_prims[i]);
+                    int bi = int((0.5 * (b[ax] + b[3 + ax]) - clo[ax]) * sc);
+                    bi = std::min(std::max(bi, 0), kBins - 1);
+                    bins[bi].grow(b); ++bc[bi];
+                }
+                double ra[kBins]; uint32_t rc[kBins];
+                B3 acc; acc.reset(); uint32_t c = 0;
+                for (int b = kBins - 1; b > 0; --b) { acc.grow(bins[b]); c += bc[b]; ra[b] = acc.half_area(); rc[b] = c; }
+                acc.reset(); c = 0;
+                for (int b = 0; b < kBins - 1; ++b) {
+                    acc.grow(bins[b]); c += bc[b];
+                    if (c == 0 || rc[b + 1] == 0) continue;
+                    double cost = acc.half_area() * c + ra[b + 1] * rc[b + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = b; }
+                }
+            }
+            if (best_axis >= 0) {
+                const double e = chi[best_axis] - clo[best_axis];
+                const double sc = kBins / e;
+                const double lo = clo[best_axis];
+                auto it = std::partition(s.fast_prims.begin() + t.begin, s.fast_prims.begin() + t.end, [&](uint32_t p) {
+                    const double* b = tb + 6 * size_t(p);
+                    int bi = int((0.5 * (b[best_axis] + b[3 + best_axis]) - lo) * sc);
+                    bi = std::min(std::max(bi, 0), kBins - 1);
+                    return bi <= best_bin;
+                });
+                mid = uint32_t(it - s.fast_prims.begin());
+                split_ok = mid > t.begin && mid < t.end;
+            }
+        }
+        if (!split_ok) {
+            mid = t.begin + cnt / 2;
+            std::nth_element(s.fast_prims.begin() + t.begin, s.fast_prims.begin() + mid, s.fast_prims.begin() + t.end,
+                             [&](uint32_t a, uint32_t b) {
+                                 return tb[6 * size_t(a) + axis] + tb[6 * size_t(a) + 3 + axis] <
+                                        tb[6 * size_t(b) + axis] + tb[6 * size_t(b) + 3 + axis];
+                             });
+        }
+        FastNode nd{};
+        store_box(nd, 0, range_box(t.begin, mid));
+        store_box(nd, 1, range_box(mid, t.end));
+        nd.left = nd.right = 0;
+        s.fast_nodes[me] = nd;
+        // children: push right first so the left subtree is laid out next (preorder, near the parent)
+        todo.push_back(Task{mid, t.end, t.depth + 1, me, 1});
+        todo.push_back(Task{t.begin, mid, t.depth + 1, me, 0});
+    }
+    (void)root_done;
+    (void)kTravCost; (void)kTriCost;
+    s.fast_depth = max_depth + 1;
+}
+
+}  // namespace bdpt

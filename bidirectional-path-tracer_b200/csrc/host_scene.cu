@@ -1,0 +1,144 @@
+// Host-side scene flattening and the reference-topology BVH builder.
+// Replaces: triangle ctor (src/objects/primatives/triangle.h:21-39), triangle_collection light list
+// (triangle.h:135-230, scene_loader.h:190-202), bvh_node ctor (src/acceleration/bvh.h:20-48) and the
+// aabb merge / pad rules (src/acceleration/aabb.h:27-33,81-88, src/core/interval.h:12-16,36-39).
+#include <algorithm>
+#include <cmath>
+#include <limits>
+#include <stdexcept>
+
+#include "host_scene.h"
+
+namespace bdpt {
+
+namespace {
+
+struct Box6 { double lo[3], hi[3]; };
+
+inline void pad_axis(double& lo, double& hi) {  // aabb.h:81-88 via interval.h:36-39
+    const double delta = 0.0001;
+    if (hi - lo < delta) { const double p = delta / 2; lo = lo - p; hi = hi + p; }
+}
+
+inline Box6 merge_pad(const Box6& a, const double* b /* lo xyz hi xyz */) {  // aabb.h:27-33
+    Box6 r;
+    for (int k = 0; k < 3; ++k) {
+        r.lo[k] = a.lo[k] <= b[k] ? a.lo[k] : b[k];
+        r.hi[k] = a.hi[k] >= b[3 + k] ? a.hi[k] : b[3 + k];
+        pad_axis(r.lo[k], r.hi[k]);
+    }
+    return r;
+}
+
+inline int longest_axis(const Box6& b) {  // aabb.h:68-75 (ties go to the later axis)
+    const double sx = b.hi[0] - b.lo[0], sy = b.hi[1] - b.lo[1], sz = b.hi[2] - b.lo[2];
+    if (sx > sy) return sx > sz ? 0 : 2;
+    return sy > sz ? 1 : 2;
+}
+
+struct RefBuilder {
+    HostScene& s;
+    std::vector<uint32_t>& order;
+    uint32_t max_depth = 0;
+    explicit RefBuilder(HostScene& sc) : s(sc), order(sc.leaf_order) {}
+
+    int32_t build(size_t start, size_t end, uint32_t depth) {
+        const int32_t me = int32_t(s.ref_nodes.size());
+        s.ref_nodes.push_back(RefNode());
+        max_depth = std::max(max_depth, depth);
+        const double inf = std::numeric_limits<double>::infinity();
+        Box6 bb;  // aabb::empty (aabb.h:92): padding (+inf,-inf) leaves it unchanged (size = -inf < delta
+                  // gives (+inf - p, -inf + p) = (+inf, -inf))
+        for (int k = 0; k < 3; ++k) { bb.lo[k] = inf; bb.hi[k] = -inf; }
+        for (size_t i = start; i < end; ++i) bb = merge_pad(bb, &s.tri_box[6 * size_t(order[i])]);
+        const int axis = longest_axis(bb);
+        const size_t span = end - start;
+        RefNode n;
+        n.lo_x = bb.lo[0]; n.hi_x = bb.hi[0]; n.lo_y = bb.lo[1]; n.hi_y = bb.hi[1];
+        n.lo_z = bb.lo[2]; n.hi_z = bb.hi[2];
+        n.pad = 0;
+        if (span == 1) {
+            n.leaf = 1; n.left = n.right = int32_t(order[start]);
+        } else if (span == 2) {
+            n.leaf = 1; n.left = int32_t(order[start]); n.right = int32_t(order[start + 1]);
+        } else {
+            // bvh.h:41,68-74: libstdc++ std::sort (unstable) on the box minimum along `axis`; the same
+            // library, comparator results and initial order give the reference's permutation.
+            const double* tb = s.tri_box.data();
+            std::sort(order.begin() + start, order.begin() + end,
+                      [tb, axis](uint32_t a, uint32_t b) { return tb[6 * size_t(a) + axis] < tb[6 * size_t(b) + axis]; });
+            const size_t mid = start + span / 2;
+            n.leaf = 0;
+            n.left = build(start, mid, depth + 1);
+            n.right = build(mid, end, depth + 1);
+        }
+        s.ref_nodes[me] = n;
+        return me;
+    }
+};
+
+}  // namespace
+
+void flatten_scene(const double* verts, const uint32_t* mat_id, uint64_t n, const bdpt_material* mats,
+                   uint32_t n_mats, HostScene& out) {
+    if (!verts || !mat_id || !mats || n == 0 || n_mats == 0) throw std::runtime_error("empty scene");
+    if (n >= 0x7FFFFFFFull) throw std::runtime_error("too many triangles");
+    out = HostScene();
+    out.mats.resize(n_mats);
+    for (uint32_t i = 0; i < n_mats; ++i) {
+        if (mats[i].type > BDPT_MAT_LIGHT) throw std::runtime_error("unknown material type");
+        Mat m;
+        m.r = mats[i].rgb[0]; m.g = mats[i].rgb[1]; m.b = mats[i].rgb[2];
+        m.param = mats[i].param;
+        if (mats[i].type == BDPT_MAT_METAL && m.param > 1.0) m.param = 1.0;  // material.h:71
+        m.type = mats[i].type;
+        m.pad[0] = m.pad[1] = m.pad[2] = 0;
+        out.mats[i] = m;
+    }
+    out.tris.resize(n); out.shade.resize(n); out.area.resize(n); out.tri_box.resize(6 * n);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (mat_id[i] >= n_mats) throw std::runtime_error("material index out of range");
+        const double* p = verts + 9 * i;
+        const D3 v0 = mk(p[0], p[1], p[2]), v1 = mk(p[3], p[4], p[5]), v2 = mk(p[6], p[7], p[8]);
+        const D3 e1 = v1 - v0, e2 = v2 - v0;
+        const D3 nn = cross(e1, e2);
+        const D3 un = unit(nn);                      // triangle.h:27 (NaN for degenerate triangles, as there)
+        TriGeom g;
+        g.v0x = v0.x; g.v0y = v0.y; g.v0z = v0.z; g.e1x = e1.x; g.e1y = e1.y; g.e1z = e1.z;
+        g.e2x = e2.x; g.e2y = e2.y; g.e2z = e2.z; g.mat = mat_id[i]; g.pad = 0;
+        out.tris[i] = g;
+        TriShade sh;
+        sh.nx = un.x; sh.ny = un.y; sh.nz = un.z; sh.mat = mat_id[i]; sh.pad = 0;
+        out.shade[i] = sh;
+        out.area[i] = 0.5 * len(nn);
+        double* b = &out.tri_box[6 * i];
+        b[0] = std::fmin(v0.x, std::fmin(v1.x, v2.x)); b[3] = std::fmax(v0.x, std::fmax(v1.x, v2.x));
+        b[1] = std::fmin(v0.y, std::fmin(v1.y, v2.y)); b[4] = std::fmax(v0.y, std::fmax(v1.y, v2.y));
+        b[2] = std::fmin(v0.z, std::fmin(v1.z, v2.z)); b[5] = std::fmax(v0.z, std::fmax(v1.z, v2.z));
+        if (out.mats[mat_id[i]].type == BDPT_MAT_LIGHT) out.lights.push_back(uint32_t(i));
+    }
+    if (out.lights.empty())  // main.cpp:67: no lights -> the whole world is the light list
+        for (uint64_t i = 0; i < n; ++i) out.lights.push_back(uint32_t(i));
+    out.light_area.resize(out.lights.size());
+    double total = 0.0;  // triangle.h:200-203 sums in list order
+    for (size_t k = 0; k < out.lights.size(); ++k) {
+        out.light_area[k] = out.area[out.lights[k]];
+        total += out.light_area[k];
+    }
+    out.light_total_area = total;
+}
+
+void build_ref_bvh(HostScene& s) {
+    const size_t n = s.tris.size();
+    s.leaf_order.resize(n);
+    for (size_t i = 0; i < n; ++i) s.leaf_order[i] = uint32_t(i);
+    s.ref_nodes.clear();
+    s.ref_nodes.reserve(size_t(1.4 * double(n)) + 4);
+    RefBuilder b(s);
+    b.build(0, n, 0);
+    s.ref_depth = b.max_depth + 1;
+    s.dfs_rank.resize(n);
+    for (size_t k = 0; k < n; ++k) s.dfs_rank[s.leaf_order[k]] = uint32_t(k);
+}
+
+}  // namespace bdpt

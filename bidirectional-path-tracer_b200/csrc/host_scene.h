@@ -1,0 +1,42 @@
+// Host-side scene flattening and BVH builders (plain C++17, no CUDA calls).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/bdpt.h"
+#include "scene.cuh"
+
+namespace bdpt {
+
+struct HostScene {
+    std::vector<TriGeom> tris;
+    std::vector<TriShade> shade;
+    std::vector<double> area;          // triangle.h:28-29
+    std::vector<Mat> mats;
+    std::vector<uint32_t> lights;      // prim IDs (scene_loader.h:190-202; main.cpp:67 fallback)
+    std::vector<double> light_area;
+    double light_total_area = 0.0;
+
+    // reference topology
+    std::vector<RefNode> ref_nodes;    // preorder; root = 0
+    std::vector<uint32_t> leaf_order;  // builder's final array == DFS leaf order
+    std::vector<uint32_t> dfs_rank;    // prim -> position in leaf_order
+    uint32_t ref_depth = 0;
+
+    // fast topology
+    std::vector<FastNode> fast_nodes;
+    std::vector<uint32_t> fast_prims;
+    uint32_t fast_depth = 0;
+
+    // per-triangle fp64 bounds (triangle.h:31-38), unpadded: lo xyz, hi xyz
+    std::vector<double> tri_box;
+};
+
+// Throws std::runtime_error on bad input (caught at the C-ABI).
+void flatten_scene(const double* verts, const uint32_t* mat_id, uint64_t n_tris, const bdpt_material* mats,
+                   uint32_t n_mats, HostScene& out);
+void build_ref_bvh(HostScene& s);
+void build_fast_bvh(HostScene& s);
+
+}  // namespace bdpt

@@ -1,0 +1,74 @@
+// GPU-resident scene: flattened BVHs, triangle records, material table, light CDF.
+// Layout notes (DESIGN.md "Data layout in HBM"): every record is a multiple of 16 bytes and is read
+// with 16-byte vector loads.
+#pragma once
+#include "dmath.cuh"
+
+namespace bdpt {
+
+// ---- reference-topology BVH (replaces src/acceleration/bvh.h + aabb.h), fp64 boxes ------------
+// 64 B = 4 x 16-byte loads. Internal: left/right are node indices. Leaf (span 1 or 2, bvh.h:35-39):
+// left/right are triangle (prim) IDs; span 1 has left == right and the triangle is tested twice,
+// exactly as the reference does.
+struct __align__(16) RefNode {
+    double lo_x, hi_x, lo_y, hi_y, lo_z, hi_z;  // aabb.h:8 x,y,z intervals (padded per aabb.h:81-88)
+    int32_t left, right;
+    uint32_t leaf;                              // 1 = children are triangles
+    uint32_t pad;
+};
+static_assert(sizeof(RefNode) == 64, "RefNode must be 64 bytes");
+
+// fp64 triangle for intersection: triangle.h:21-31 (v0, edge1, edge2), 80 B = 5 x 16-byte loads.
+struct __align__(16) TriGeom {
+    double v0x, v0y, v0z, e1x, e1y, e1z, e2x, e2y, e2z;
+    uint32_t mat;
+    uint32_t pad;
+};
+static_assert(sizeof(TriGeom) == 80, "TriGeom must be 80 bytes");
+
+// shading side-table: unit geometric normal (triangle.h:32) + material, 32 B
+struct __align__(16) TriShade {
+    double nx, ny, nz;
+    uint32_t mat;
+    uint32_t pad;
+};
+static_assert(sizeof(TriShade) == 32, "TriShade must be 32 bytes");
+
+// material table entry (material.h:42-147), 48 B
+struct __align__(16) Mat {
+    double r, g, b;
+    double param;
+    uint32_t type;
+    uint32_t pad[3];
+};
+static_assert(sizeof(Mat) == 48, "Mat must be 48 bytes");
+
+// ---- fast BVH: binned-SAH binary tree, both child boxes in the parent, fp32 conservative ------
+// 64 B. child >= 0: node index. child < 0: leaf, ~child = (first << 3) | (count - 1), first = index into
+// the leaf-ordered prim list, 1..8 triangles.
+struct __align__(16) FastNode {
+    float l_lo[3], l_hi[3];
+    float r_lo[3], r_hi[3];
+    int32_t left, right;
+    uint32_t pad[2];
+};
+static_assert(sizeof(FastNode) == 64, "FastNode must be 64 bytes");
+
+struct SceneView {
+    const RefNode* ref_nodes;
+    const FastNode* fast_nodes;
+    const uint32_t* fast_prims;   // leaf-ordered prim IDs for the fast BVH
+    const uint32_t* dfs_rank;     // prim ID -> last position in the reference DFS leaf order (tie rule)
+    const TriGeom* tris;
+    const TriShade* shade;
+    const Mat* mats;
+    const uint32_t* lights;       // prim IDs, reference light-list order
+    const double* light_area;     // per light triangle area (triangle.h:33)
+    uint32_t n_lights;
+    uint32_t n_tris;
+    uint32_t n_ref_nodes;
+    uint32_t n_fast_nodes;
+    double light_total_area;      // summed in list order like triangle.h:200-203
+};
+
+}  // namespace bdpt

@@ -1,0 +1,149 @@
+/* libbdpt — C-ABI of the B200-native BDPT hot path.
+ *
+ * The reference (teehee567/Bidirectional-Path-Tracer) has no FFI layer; its de-facto operator
+ * boundary is three C++ calls in one TU (paths relative to /root/reference/src):
+ *   camera::render(world, lights)                 camera.h:43      -> bdpt_render_*
+ *   hittable::hit(ray, interval, hit_record&)     hittable.h:33    -> bdpt_trace / bdpt_visible
+ *   bvh_node(hittable_list)                       bvh.h:13-48      -> bdpt_scene_upload (+ BVH build)
+ * Everything here is plain pointers and sizes; no torch / C++ types cross the boundary.
+ * All calls return 0 on success, a negative bdpt_status otherwise; bdpt_last_error() gives the text.
+ * A context is bound to one CUDA device and is not thread-safe; contexts are independent.
+ * There is NO CPU fallback: without a CUDA device bdpt_ctx_create fails with BDPT_ERR_CUDA.
+ */
+#ifndef BDPT_H
+#define BDPT_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bdpt_ctx bdpt_ctx;
+
+typedef enum {
+    BDPT_OK = 0,
+    BDPT_ERR_ARG = -1,     /* bad argument (null pointer, size 0, unknown enum) */
+    BDPT_ERR_CUDA = -2,    /* CUDA runtime error, text in bdpt_last_error */
+    BDPT_ERR_STATE = -3,   /* call order (e.g. trace before scene upload) */
+    BDPT_ERR_NOMEM = -4
+} bdpt_status;
+
+/* material classes reachable from the reference's loader (scene_loader.h:101-170, material.h:42-147) */
+enum { BDPT_MAT_LAMBERTIAN = 0, BDPT_MAT_METAL = 1, BDPT_MAT_DIELECTRIC = 2, BDPT_MAT_LIGHT = 3 };
+
+typedef struct {
+    uint32_t type;    /* BDPT_MAT_* */
+    uint32_t pad;
+    double   rgb[3];  /* albedo (lambertian, metal) or emission (light); unused for dielectric */
+    double   param;   /* metal: fuzz, clamped to <=1 as material.h:71; dielectric: refraction index */
+} bdpt_material;
+
+/* The public camera fields of camera.h:26-41 that shape the image. */
+typedef struct {
+    double  aspect_ratio;
+    int32_t image_width;
+    int32_t samples_per_pixel;   /* sqrt_spp = int(sqrt(spp)) strata per axis, camera.h:164 */
+    int32_t max_depth;
+    int32_t pad;
+    double  background[3];
+    double  vfov;
+    double  lookfrom[3];
+    double  lookat[3];
+    double  vup[3];
+    double  defocus_angle;       /* must be <= 0 (scene_loader.h:463 forces it off) */
+    double  focus_dist;
+} bdpt_camera;
+
+/* BVH flavours */
+enum {
+    BDPT_BVH_REFERENCE = 0,  /* the reference's median-split topology (bvh.h:20-48), fp64 boxes:
+                                traversal results are bit-identical to bvh_node::hit */
+    BDPT_BVH_FAST      = 1   /* binned-SAH topology, fp32 conservative boxes, ordered traversal;
+                                triangles are still decided in fp64 with the reference's tie rule */
+};
+
+/* trace flags */
+enum {
+    BDPT_TRACE_CLOSEST = 0,
+    BDPT_TRACE_ANY     = 1,   /* shadow query: prim = any occluder or MISS, t undefined */
+    BDPT_TRACE_DEVICE_PTRS = 16, /* rays/out pointers are device memory of the ctx's device */
+    BDPT_TRACE_STATS = 32        /* count node visits / triangle tests into bdpt_stats (slower) */
+};
+
+#define BDPT_MISS 0xFFFFFFFFu
+
+/* n x 8 doubles: ox,oy,oz, dx,dy,dz, tmin,tmax (ray.h:6-29 + interval.h:4-24, inclusive ends) */
+typedef struct { double o[3], d[3], tmin, tmax; } bdpt_ray;
+/* hit_record (hittable.h:10-27) reduced to what cannot be recomputed, plus the prim ID it lacks */
+typedef struct { double t, u, v; uint32_t prim; uint32_t pad; } bdpt_hit;
+
+typedef struct {
+    uint64_t rays_closest;   /* world.hit queries from trace_path (camera.h:336) */
+    uint64_t rays_shadow;    /* world.hit queries from visible() (camera.h:437) */
+    uint64_t node_visits;    /* stats build only (BDPT_STATS), else 0 */
+    uint64_t tri_tests;      /* stats build only */
+    uint64_t samples;        /* (pixel, stratum) samples rendered */
+    uint64_t kernel_launches;/* our kernels launched since ctx creation / last reset */
+    uint64_t camera_vertices;
+    uint64_t light_vertices;
+} bdpt_stats_t;
+
+typedef struct {
+    uint64_t seed;
+    int32_t  stratum_begin;  /* strata [begin,end) of the sqrt_spp^2 per pixel, row-major s_j*n+s_i */
+    int32_t  stratum_end;    /* <=0 means all */
+    int32_t  stratum_step;   /* rank g of G renders begin=g, step=G; 0/1 = contiguous */
+    int32_t  bvh;            /* BDPT_BVH_* used for traversal */
+    int32_t  row_begin;      /* rows [row_begin,row_end) ; row_end<=0 means image height */
+    int32_t  row_end;
+    int64_t  batch_samples;  /* wavefront size; <=0 picks a default */
+} bdpt_render_opts;
+
+int  bdpt_ctx_create(int device, bdpt_ctx** out);
+void bdpt_ctx_destroy(bdpt_ctx* ctx);
+const char* bdpt_last_error(bdpt_ctx* ctx);   /* ctx may be NULL: last creation error */
+
+/* Triangle soup in scene.world insertion order (prim ID = index); verts is n_tris x 9
+ * doubles (v0,v1,v2: triangle.h:21). Lights are the triangles whose material is BDPT_MAT_LIGHT, in
+ * insertion order (scene_loader.h:190-202); if there are none every triangle is a light (main.cpp:67).
+ * Builds both BVH flavours on the host and uploads them. */
+int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
+                      const bdpt_material* mats, uint32_t n_mats);
+int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth);
+/* DFS leaf order of the BDPT_BVH_REFERENCE build: order[k] = prim ID (n_tris entries) */
+int bdpt_bvh_leaf_order(bdpt_ctx* ctx, uint32_t* order);
+
+/* Host-only (no CUDA device needed): build the BDPT_BVH_REFERENCE topology for a triangle soup and
+ * return its DFS leaf order, node count and, when fast_nodes != NULL, the fast BVH's node count.
+ * Lets the host builder be checked against the reference without a GPU. */
+int bdpt_host_bvh_build(const double* verts, uint64_t n_tris, uint32_t* order /* n_tris */,
+                        uint64_t* ref_nodes, uint64_t* fast_nodes);
+
+/* hittable::hit over a batch (hittable.h:33 / bvh.h:50-59). */
+int bdpt_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* rays, uint64_t n, bdpt_hit* out, int flags);
+/* camera::visible (camera.h:425-438) over n segments a->b (n x 3 doubles each); out[i] = 1 visible. */
+int bdpt_visible(bdpt_ctx* ctx, int bvh, const double* a, const double* b, uint64_t n, uint8_t* out,
+                 int flags);
+
+/* camera::render's sample loop (camera.h:111-129): adds every selected (pixel, stratum) sample of
+ * bidirectional_color (camera.h:294-323) into the context's device film (fp64 RGB SUM, camera.h:55).
+ * The film persists across calls until bdpt_film_clear. */
+int bdpt_render(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts);
+int bdpt_film_clear(bdpt_ctx* ctx, int width, int height);
+/* device pointer of the film (W*H*3 doubles) so a caller can reduce it across GPUs in place */
+int bdpt_film_device_ptr(bdpt_ctx* ctx, void** ptr, uint64_t* n_doubles);
+int bdpt_film_download(bdpt_ctx* ctx, double* film_sum /* W*H*3 */);
+/* wpng.h:14-35 on the device film: average, clamp [0,0.999], sqrt, 256x truncate. out: W*H*3 bytes (host) */
+int bdpt_film_to_rgb8(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out);
+
+int bdpt_stats(bdpt_ctx* ctx, bdpt_stats_t* out);
+int bdpt_stats_reset(bdpt_ctx* ctx);
+/* GPU time (ms, CUDA events on the ctx stream) of the last bdpt_trace / bdpt_visible / bdpt_render
+ * device work, excluding host<->device copies. */
+int bdpt_last_device_ms(bdpt_ctx* ctx, double* ms);
+int bdpt_sync(bdpt_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,69 @@
+"""CPU-side checks of the product library: it loads, exports every symbol include/bdpt.h declares,
+fails loudly without a GPU, and its host BVH builder reproduces the reference topology."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "bdpt.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(bdpt_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(bdpt):
+    L = ctypes.CDLL(bdpt.LIB_PATH)
+    syms = header_symbols()
+    assert len(syms) >= 18
+    for s in syms:
+        assert hasattr(L, s), s
+    assert sorted(bdpt.EXPORTS) == syms
+
+
+def test_struct_layouts_match_header(bdpt):
+    assert ctypes.sizeof(bdpt.Material) == 40
+    assert ctypes.sizeof(bdpt.Camera) == 144
+    assert ctypes.sizeof(bdpt.RenderOpts) == 40
+    assert bdpt.RAY_DTYPE.itemsize == 64 and bdpt.HIT_DTYPE.itemsize == 32
+
+
+def test_no_cpu_fallback(bdpt):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(bdpt.BdptError, match="no CPU fallback"):
+        bdpt.Context(0)
+
+
+@pytest.mark.parametrize("name", ["cornell_spheres", "cornell_box", "unit_room"])
+def test_host_bvh_matches_reference_topology(name, bdpt, scenes, golden):
+    g = golden(name)
+    v, m, mats, cam = scenes[name]()
+    order, n_ref, n_fast = bdpt.host_bvh_build(v, fast=True)
+    assert n_ref == int(g["nodes"])
+    assert np.array_equal(order, g["leaf_order"])
+    assert 1 <= n_fast <= len(v)
+
+
+def test_host_bvh_duplicate_keys_and_tiny_scenes(bdpt):
+    """std::sort's unstable order on equal keys must match the reference's (same libstdc++)."""
+    from oracle.oracle import Oracle
+    rng = np.random.default_rng(5)
+    base = rng.uniform(-1, 1, (1, 9))
+    for n in (1, 2, 3, 5, 64, 257):
+        v = np.repeat(base, n, axis=0)
+        v[:, 1::3] += np.arange(n)[:, None] % 3  # many equal x / z minima
+        o = Oracle("port").load(v, np.zeros(n, np.uint32), [(0, (0.5, 0.5, 0.5), 0.0)])
+        order, n_ref, _ = bdpt.host_bvh_build(v, fast=True)
+        assert n_ref == o.node_count()
+        assert np.array_equal(order, o.leaf_order())
+
+
+def test_host_bvh_rejects_empty(bdpt):
+    with pytest.raises(bdpt.BdptError):
+        bdpt.host_bvh_build(np.zeros((0, 9)))
