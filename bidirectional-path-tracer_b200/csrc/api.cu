@@ -171,6 +171,8 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     if ((rc = upload(ctx, h.fast_nodes, &v.fast_nodes))) return rc;
     if ((rc = upload(ctx, h.fast_prims, &v.fast_prims))) return rc;
     if ((rc = upload(ctx, h.dfs_rank, &v.dfs_rank))) return rc;
+    if ((rc = upload(ctx, h.ref_parent, &v.ref_parent))) return rc;
+    if ((rc = upload(ctx, h.prim_leaf, &v.prim_leaf))) return rc;
     if ((rc = upload(ctx, h.tris, &v.tris))) return rc;
     if ((rc = upload(ctx, h.shade, &v.shade))) return rc;
     if ((rc = upload(ctx, h.mats, &v.mats))) return rc;
@@ -181,6 +183,7 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     v.n_ref_nodes = uint32_t(h.ref_nodes.size());
     v.n_fast_nodes = uint32_t(h.fast_nodes.size());
     v.light_total_area = h.light_total_area;
+    v.extent = h.extent;
     BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->view = v;
     ctx->have_scene = true;

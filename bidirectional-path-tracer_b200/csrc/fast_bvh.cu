@@ -61,6 +61,7 @@ void build_fast_bvh(HostScene& s) {
     for (uint32_t i = 0; i < n; ++i) scene.grow(tb + 6 * size_t(i));
     double ext = 0.0;
     for (int k = 0; k < 3; ++k) ext = std::max(ext, scene.hi[k] - scene.lo[k]);
+    s.extent = ext;
     // outward padding: far above fp64 slab/triangle rounding noise, far below feature size
     const double eps = std::max(ext, 1e-30) * (1.0 / 1048576.0);
 

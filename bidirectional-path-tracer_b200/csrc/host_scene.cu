@@ -139,6 +139,13 @@ void build_ref_bvh(HostScene& s) {
     s.ref_depth = b.max_depth + 1;
     s.dfs_rank.resize(n);
     for (size_t k = 0; k < n; ++k) s.dfs_rank[s.leaf_order[k]] = uint32_t(k);
+    s.ref_parent.assign(s.ref_nodes.size(), -1);
+    s.prim_leaf.assign(n, -1);
+    for (size_t i = 0; i < s.ref_nodes.size(); ++i) {
+        const RefNode& nd = s.ref_nodes[i];
+        if (nd.leaf) { s.prim_leaf[nd.left] = int32_t(i); s.prim_leaf[nd.right] = int32_t(i); }
+        else { s.ref_parent[nd.left] = int32_t(i); s.ref_parent[nd.right] = int32_t(i); }
+    }
 }
 
 }  // namespace bdpt

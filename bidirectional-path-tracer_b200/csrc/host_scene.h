@@ -23,11 +23,14 @@ struct HostScene {
     std::vector<uint32_t> leaf_order;  // builder's final array == DFS leaf order
     std::vector<uint32_t> dfs_rank;    // prim -> position in leaf_order
     uint32_t ref_depth = 0;
+    std::vector<int32_t> ref_parent;   // node -> parent (-1 root)
+    std::vector<int32_t> prim_leaf;    // prim -> leaf node
 
     // fast topology
     std::vector<FastNode> fast_nodes;
     std::vector<uint32_t> fast_prims;
     uint32_t fast_depth = 0;
+    double extent = 0.0;               // largest side of the scene bounds
 
     // per-triangle fp64 bounds (triangle.h:31-38), unpadded: lo xyz, hi xyz
     std::vector<double> tri_box;

@@ -59,6 +59,8 @@ struct SceneView {
     const FastNode* fast_nodes;
     const uint32_t* fast_prims;   // leaf-ordered prim IDs for the fast BVH
     const uint32_t* dfs_rank;     // prim ID -> last position in the reference DFS leaf order (tie rule)
+    const int32_t* ref_parent;    // reference node -> parent node (-1 for the root)
+    const int32_t* prim_leaf;     // prim ID -> reference leaf node holding it
     const TriGeom* tris;
     const TriShade* shade;
     const Mat* mats;
@@ -69,6 +71,7 @@ struct SceneView {
     uint32_t n_ref_nodes;
     uint32_t n_fast_nodes;
     double light_total_area;      // summed in list order like triangle.h:200-203
+    double extent;                // largest side of the scene bounds (tie-band scale, traverse_fast.cuh)
 };
 
 }  // namespace bdpt

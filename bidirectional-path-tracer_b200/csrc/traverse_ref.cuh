@@ -58,9 +58,10 @@ __device__ __forceinline__ bool box_hit(const RefNode& n, const D3& o, const D3&
     return slab(n.lo_z, n.hi_z, o.z, adinv.z, tmin, tmax);
 }
 
-// triangle.h:41-74. Returns true and updates (t,u,v) when tmin <= t <= tmax.
-__device__ __forceinline__ bool tri_hit(const TriGeom* tp, const D3& o, const D3& d, double tmin, double tmax,
-                                        double& t_out, double& u_out, double& v_out) {
+// triangle.h:41-67: everything up to the interval check. True when the ray's line meets the triangle
+// (|det| >= 1e-8, u in [0,1], v >= 0, u+v <= 1); t is then the reference's t, bit for bit.
+__device__ __forceinline__ bool tri_candidate(const TriGeom* tp, const D3& o, const D3& d, double& t_out,
+                                              double& u_out, double& v_out) {
     const double2* q = reinterpret_cast<const double2*>(tp);
     double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
     double e2z = __ldg(reinterpret_cast<const double*>(q + 4));
@@ -75,7 +76,16 @@ __device__ __forceinline__ bool tri_hit(const TriGeom* tp, const D3& o, const D3
     D3 qvec = cross(tvec, e1);
     double v = dot(d, qvec) * inv_det;
     if (v < 0.0 || u + v > 1.0) return false;
-    double t = dot(e2, qvec) * inv_det;
+    t_out = dot(e2, qvec) * inv_det;
+    u_out = u; v_out = v;
+    return true;
+}
+
+// triangle.h:41-74. Returns true and updates (t,u,v) when tmin <= t <= tmax (interval.h:22-24).
+__device__ __forceinline__ bool tri_hit(const TriGeom* tp, const D3& o, const D3& d, double tmin, double tmax,
+                                        double& t_out, double& u_out, double& v_out) {
+    double t, u, v;
+    if (!tri_candidate(tp, o, d, t, u, v)) return false;
     if (!(tmin <= t && t <= tmax)) return false;
     t_out = t; u_out = u; v_out = v;
     return true;
