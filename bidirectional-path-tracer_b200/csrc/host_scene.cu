@@ -122,8 +122,8 @@ void flatten_scene(const double* verts, const uint32_t* mat_id, uint64_t n, cons
     out.light_area.resize(out.lights.size());
     double total = 0.0;  // triangle.h:200-203 sums in list order
     for (size_t k = 0; k < out.lights.size(); ++k) {
-        out.light_area[k] = out.area[out.lights[k]];
-        total += out.light_area[k];
+        total += out.area[out.lights[k]];
+        out.light_area[k] = total;   // running sum = the `accum` of the reference's linear scan
     }
     out.light_total_area = total;
 }

@@ -15,7 +15,7 @@ struct HostScene {
     std::vector<double> area;          // triangle.h:28-29
     std::vector<Mat> mats;
     std::vector<uint32_t> lights;      // prim IDs (scene_loader.h:190-202; main.cpp:67 fallback)
-    std::vector<double> light_area;
+    std::vector<double> light_area;    // running sums of the light triangles' areas, list order
     double light_total_area = 0.0;
 
     // reference topology

@@ -1,6 +1,704 @@
-// placeholder until the wavefront integrator lands
+// Wavefront bidirectional path tracer: camera::render's sample loop (src/camera.h:111-129) and
+// bidirectional_color (camera.h:294-323) restructured as queue-driven kernels.
+//
+//   K0 k_generate      get_ray (camera.h:199-223) + build_light_path's emitter (camera.h:372-414)
+//   K1 k_trace_paths   world.hit for every live subpath (camera.h:336) -> per-material queues
+//   K2 k_shade_*       one kernel per material class (material.h:42-147): vertex push, emission,
+//                      scatter, throughput update (camera.h:342-368); survivors -> next ray queue
+//   K3 k_connect       connect_vertices minus visibility (camera.h:440-475) -> shadow-ray queue
+//   K4 k_shadow        visible() (camera.h:425-438) + film accumulation (camera.h:121-124)
+//
+// All arithmetic is fp64 in the reference's operation order and this file is compiled with -fmad=false,
+// so a sample is computed exactly as the CPU oracle's counter-based mode computes it; only the order in
+// which contributions are summed into a pixel differs (fp64 atomics).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
 #include "ctx.h"
+#include "render_math.cuh"
+#include "traverse_fast.cuh"
+
 namespace bdpt {
-int render_impl(bdpt_ctx* ctx, const bdpt_camera*, const bdpt_render_opts*) { ctx->err = "render not built"; return BDPT_ERR_STATE; }
-void render_free(bdpt_ctx*) {}
+
+namespace {
+
+constexpr int kBlock = 128;
+constexpr uint32_t kLightFlag = 0x80000000u;
+
+// device counters (uint32 each)
+enum { C_ACTIVE0 = 0, C_ACTIVE1 = 1, C_MAT0 = 2 /* ..5 */, C_SHADOW = 6, C_MAXNC = 7, C_MAXNL = 8, C_SUMNC = 9,
+       C_SUMNL = 10, C_OVERFLOW = 11, C_COUNT = 16 };
+
+struct Frame {           // camera.h:148-197 derived values + this call's sample selection
+    D3 center, pixel00, du, dv, background;
+    double recip_sqrt_spp;
+    int W, H, n;         // n = sqrt_spp
+    int depth;
+    int row0, rows;      // selected rows
+    int s_begin, s_step; // selected strata: s_begin + k*s_step
+    uint64_t seed;
+    int64_t npix;        // rows * W
+};
+
+struct WF {              // wavefront workspace, all device pointers
+    int64_t B;           // batch capacity in samples
+    int depth;
+    int64_t scap;        // shadow queue capacity
+    // subpath state, index = path id (camera subpath of sample b: b; light subpath: B + b)
+    double *ox, *oy, *oz, *dx, *dy, *dz, *tx, *ty, *tz, *hit_t;
+    uint32_t *draws, *hit_prim;
+    int32_t* remaining;
+    uint32_t *q_active[2], *q_mat[4];
+    uint32_t* counters;
+    // vertex pools, index = slot * B + b
+    double *cv_px, *cv_py, *cv_pz, *cv_fx, *cv_fy, *cv_fz;   // camera vertex: p, throughput * f (camera.h:471)
+    uint32_t* cv_prim;
+    double *lv_px, *lv_py, *lv_pz, *lv_tx, *lv_ty, *lv_tz;   // light vertex: p, throughput
+    uint32_t* lv_prim;                                       // bit 31: is_light (camera.h:348)
+    uint32_t *ncam, *nlight;
+    // shadow queue
+    double *s_ox, *s_oy, *s_oz, *s_dx, *s_dy, *s_dz, *s_tmax, *s_cx, *s_cy, *s_cz;
+    uint32_t* s_pix;
+    void* base;
+    size_t bytes;
+};
+
+// one atomic per warp: every thread of the warp must call this (pred = whether it appends)
+__device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, pred);
+    const int lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (mask) {
+        const int leader = __ffs(mask) - 1;
+        if (lane == leader) base = atomicAdd(counter, uint32_t(__popc(mask)));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    }
+    return base + uint32_t(__popc(mask & ((1u << lane) - 1u)));
 }
+
+__device__ __forceinline__ void film_add(double* film, uint32_t pix, D3 c) {
+    atomicAdd(film + 3 * size_t(pix), c.x);
+    atomicAdd(film + 3 * size_t(pix) + 1, c.y);
+    atomicAdd(film + 3 * size_t(pix) + 2, c.z);
+}
+
+// linear sample index of this call -> pixel, stratum and the global sample id that keys the RNG
+struct SampleId { int i, j, s_i, s_j; uint32_t pix; uint64_t sid; };
+__device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
+    SampleId s;
+    const int64_t k = L / f.npix, p = L % f.npix;
+    s.j = f.row0 + int(p / f.W);
+    s.i = int(p % f.W);
+    const int stratum = f.s_begin + int(k) * f.s_step;
+    s.s_j = stratum / f.n;
+    s.s_i = stratum % f.n;
+    s.pix = uint32_t(s.j) * uint32_t(f.W) + uint32_t(s.i);
+    s.sid = uint64_t(s.pix) * uint64_t(f.n * f.n) + uint64_t(stratum);
+    return s;
+}
+
+// ------------------------------------------------------------------ K0
+__global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w, int64_t L0, int64_t nb) {
+    const int64_t b = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const bool valid = b < nb;
+    bool cam_live = false, light_live = false;
+    if (valid) {
+        const SampleId s = decode_sample(f, L0 + b);
+        // camera subpath: get_ray, camera.h:199-223 (defocus off: scene_loader.h:463)
+        Rng rc;
+        rc.init(f.seed, 0u, s.sid, 0u);
+        const double px = ((s.s_i + rc.next()) * f.recip_sqrt_spp) - 0.5;
+        const double py = ((s.s_j + rc.next()) * f.recip_sqrt_spp) - 0.5;
+        const D3 ps = f.pixel00 + ((s.i + px) * f.du) + ((s.j + py) * f.dv);
+        const D3 d = ps - f.center;
+        (void)rc.next();  // ray time (camera.h:210): drawn, never used
+        w.ox[b] = f.center.x; w.oy[b] = f.center.y; w.oz[b] = f.center.z;
+        w.dx[b] = d.x; w.dy[b] = d.y; w.dz[b] = d.z;
+        w.tx[b] = 1.0; w.ty[b] = 1.0; w.tz[b] = 1.0;
+        w.draws[b] = rc.draws;
+        w.remaining[b] = f.depth;
+        w.ncam[b] = 0;
+        cam_live = f.depth > 0;
+
+        // light subpath: build_light_path, camera.h:372-418
+        uint32_t nl = 0;
+        const int64_t lp = w.B + b;
+        if (f.depth > 0 && sc.n_lights > 0 && sc.light_total_area > 0.0) {
+            Rng rl;
+            rl.init(f.seed, 1u, s.sid, 0u);
+            // triangle_collection::sample_surface, triangle.h:199-224: linear scan `pick <= accum`
+            const double pick = rl.next(0.0, sc.light_total_area);
+            uint32_t lo = 0, hi = sc.n_lights - 1;   // light_area holds the running sums (same order of adds)
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (pick <= __ldg(sc.light_area + mid)) hi = mid; else lo = mid + 1;
+            }
+            const uint32_t prim = __ldg(sc.lights + lo);
+            double u = rl.next(), v = rl.next();      // triangle::sample, triangle.h:107-119
+            if (u + v > 1.0) { u = 1.0 - u; v = 1.0 - v; }
+            const TriGeom tg = sc.tris[prim];
+            const D3 pos = mk(tg.v0x, tg.v0y, tg.v0z) + (u * mk(tg.e1x, tg.e1y, tg.e1z)) + (v * mk(tg.e2x, tg.e2y, tg.e2z));
+            const TriShade sh = sc.shade[prim];
+            const D3 n = mk(sh.nx, sh.ny, sh.nz);
+            const double pdf = 1.0 / sc.light_total_area;
+            const Mat m = sc.mats[sh.mat];
+            const D3 emission = (m.type == BDPT_MAT_LIGHT) ? mk(m.r, m.g, m.b) : mk(0, 0, 0);  // emitted(front=true)
+            if (len2(emission) > 0) {
+                const D3 T0 = mk(1.0, 1.0, 1.0) / fmax(pdf, 1e-8);
+                w.lv_px[b] = pos.x; w.lv_py[b] = pos.y; w.lv_pz[b] = pos.z;
+                w.lv_tx[b] = T0.x; w.lv_ty[b] = T0.y; w.lv_tz[b] = T0.z;
+                w.lv_prim[b] = prim | kLightFlag;
+                nl = 1;
+                const D3 dir = Onb(n).transform(random_cosine_direction(rl));
+                const D3 du = unit(dir);
+                const double cos_theta = fmax(0.0, dot(n, du));
+                if (cos_theta > 0 && f.depth - 1 > 0) {
+                    const double pdf_dir = fmax(cos_theta / kPi, 1e-8);
+                    const D3 T = T0 * emission * (cos_theta / pdf_dir);
+                    const D3 o = pos + (0.001 * n);
+                    w.ox[lp] = o.x; w.oy[lp] = o.y; w.oz[lp] = o.z;
+                    w.dx[lp] = du.x; w.dy[lp] = du.y; w.dz[lp] = du.z;
+                    w.tx[lp] = T.x; w.ty[lp] = T.y; w.tz[lp] = T.z;
+                    w.draws[lp] = rl.draws;
+                    w.remaining[lp] = f.depth - 1;
+                    light_live = true;
+                }
+            }
+        }
+        w.nlight[b] = nl;
+    }
+    uint32_t slot = warp_append(w.counters + C_ACTIVE0, cam_live);
+    if (cam_live) w.q_active[0][slot] = uint32_t(b);
+    slot = warp_append(w.counters + C_ACTIVE0, light_live);
+    if (light_live) w.q_active[0][slot] = uint32_t(w.B + b);
+}
+
+// ------------------------------------------------------------------ K1
+// world.hit over the live subpaths (camera.h:336: interval [0.001, inf)); a miss ends the subpath and,
+// for a camera subpath, adds throughput * background (camera.h:337-340).  Hits are binned by material
+// class so each shading kernel runs divergence-free over its own queue.
+template <int BVH>
+__global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
+                                                       const uint32_t* __restrict__ n_ptr, int64_t L0, double* film) {
+    __shared__ int32_t s_stack[kRefStackLevels * kBlock];
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    const uint32_t n = *n_ptr;
+    int cls = -1;
+    uint32_t pid = 0;
+    if (idx < n) {
+        pid = queue[idx];
+        RayD r;
+        r.o = mk(w.ox[pid], w.oy[pid], w.oz[pid]);
+        r.d = mk(w.dx[pid], w.dy[pid], w.dz[pid]);
+        r.tmin = 0.001;
+        r.tmax = __longlong_as_double(0x7FF0000000000000LL);
+        HitD h;
+        bool found;
+        if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<false, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
+        else found = traverse_fast<false, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
+        if (found) {
+            w.hit_prim[pid] = h.prim;
+            w.hit_t[pid] = h.t;
+            cls = int(sc.mats[__ldg(&sc.shade[h.prim].mat)].type);
+        } else if (pid < uint32_t(w.B)) {
+            const D3 T = mk(w.tx[pid], w.ty[pid], w.tz[pid]);
+            const D3 c = T * f.background;
+            if (c.x != 0.0 || c.y != 0.0 || c.z != 0.0) film_add(film, decode_sample(f, L0 + pid).pix, c);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t slot = warp_append(w.counters + C_MAT0 + k, cls == k);
+        if (cls == k) w.q_mat[k][slot] = pid;
+    }
+}
+
+// hit point and face-forwarded geometric normal (ray.h:21-23, hittable.h:20-26)
+struct Surf { D3 o, d, T, p, n; bool front; uint32_t prim; };
+__device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint32_t pid) {
+    Surf s;
+    s.o = mk(w.ox[pid], w.oy[pid], w.oz[pid]);
+    s.d = mk(w.dx[pid], w.dy[pid], w.dz[pid]);
+    s.T = mk(w.tx[pid], w.ty[pid], w.tz[pid]);
+    s.prim = w.hit_prim[pid];
+    const double t = w.hit_t[pid];
+    s.p = s.o + t * s.d;
+    const TriShade sh = sc.shade[s.prim];
+    const D3 n = mk(sh.nx, sh.ny, sh.nz);
+    s.front = dot(s.d, n) < 0;
+    s.n = s.front ? n : -n;
+    return s;
+}
+
+__device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d, D3 T, uint32_t draws, int32_t remaining) {
+    w.ox[pid] = o.x; w.oy[pid] = o.y; w.oz[pid] = o.z;
+    w.dx[pid] = d.x; w.dy[pid] = d.y; w.dz[pid] = d.z;
+    w.tx[pid] = T.x; w.ty[pid] = T.y; w.tz[pid] = T.z;
+    w.draws[pid] = draws;
+    w.remaining[pid] = remaining;
+}
+
+// ------------------------------------------------------------------ K2: diffuse_light (material.h:133-147)
+// scatter() is false: the subpath ends here.  Camera subpath: bidirectional_color adds throughput *
+// emission for this non-delta vertex (camera.h:305-309); it never connects (evaluate_bsdf = 0).
+// Light subpath: the vertex is connectable with f_light = emission when hit from the front (camera.h:463).
+__global__ void __launch_bounds__(kBlock) k_shade_light(SceneView sc, Frame f, WF w, int64_t L0, double* film) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    if (idx >= w.counters[C_MAT0 + BDPT_MAT_LIGHT]) return;
+    const uint32_t pid = w.q_mat[BDPT_MAT_LIGHT][idx];
+    const Surf s = load_surf(sc, w, pid);
+    if (!s.front) return;  // emitted() is one-sided (material.h:140)
+    const Mat m = sc.mats[sc.shade[s.prim].mat];
+    const D3 Le = mk(m.r, m.g, m.b);
+    if (!(len2(Le) > 0)) return;
+    if (pid < uint32_t(w.B)) {
+        film_add(film, decode_sample(f, L0 + pid).pix, s.T * Le);
+    } else {
+        const uint32_t b = pid - uint32_t(w.B);
+        const uint32_t slot = w.nlight[b];
+        const size_t v = size_t(slot) * size_t(w.B) + b;
+        w.lv_px[v] = s.p.x; w.lv_py[v] = s.p.y; w.lv_pz[v] = s.p.z;
+        w.lv_tx[v] = s.T.x; w.lv_ty[v] = s.T.y; w.lv_tz[v] = s.T.z;
+        w.lv_prim[v] = s.prim | kLightFlag;
+        w.nlight[b] = slot + 1;
+    }
+}
+
+// ------------------------------------------------------------------ K2: lambertian (material.h:42-67)
+__global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f, WF w, int64_t L0, int nxt) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    bool live = false;
+    uint32_t pid = 0;
+    if (idx < w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN]) {
+        pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx];
+        const Surf s = load_surf(sc, w, pid);
+        const Mat m = sc.mats[sc.shade[s.prim].mat];
+        const D3 albedo = mk(m.r, m.g, m.b);
+        const bool is_cam = pid < uint32_t(w.B);
+        const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
+        // vertex push (camera.h:342-349) — only vertices that can contribute: evaluate_bsdf = albedo/pi
+        // (material.h:60-63); an all-zero BSDF makes connect_vertices return 0 (camera.h:460,468)
+        const D3 fr = albedo / kPi;
+        if (len2(fr) > 0) {
+            if (is_cam) {
+                const uint32_t slot = w.ncam[b];
+                const size_t v = size_t(slot) * size_t(w.B) + b;
+                const D3 tf = s.T * fr;   // camera.h:471: cam_v.throughput * f_cam
+                w.cv_px[v] = s.p.x; w.cv_py[v] = s.p.y; w.cv_pz[v] = s.p.z;
+                w.cv_fx[v] = tf.x; w.cv_fy[v] = tf.y; w.cv_fz[v] = tf.z;
+                w.cv_prim[v] = s.prim;
+                w.ncam[b] = slot + 1;
+            } else {
+                const uint32_t slot = w.nlight[b];
+                const size_t v = size_t(slot) * size_t(w.B) + b;
+                w.lv_px[v] = s.p.x; w.lv_py[v] = s.p.y; w.lv_pz[v] = s.p.z;
+                w.lv_tx[v] = s.T.x; w.lv_ty[v] = s.T.y; w.lv_tz[v] = s.T.z;
+                w.lv_prim[v] = s.prim;
+                w.nlight[b] = slot + 1;
+            }
+        }
+        const int32_t remaining = w.remaining[pid] - 1;
+        if (remaining > 0) {
+            // scatter: cosine_pdf about the face-forwarded normal (material.h:47-52, pdf.h:32-47, onb.h:6-11)
+            Rng rng;
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, L0 + b).sid, w.draws[pid]);
+            const Onb uvw(s.n);
+            const D3 sd = uvw.transform(random_cosine_direction(rng));
+            const double pdf_value = fmax(0.0, dot(unit(sd), uvw.a2) / kPi);   // pdf.h:37-40
+            if (pdf_value > 0) {                                               // camera.h:362-363
+                const double ct = dot(s.n, unit(sd));                          // material.h:55-58
+                const double spdf = ct < 0 ? 0 : ct / kPi;
+                const D3 T = s.T * albedo * spdf / pdf_value;                  // camera.h:366
+                store_ray(w, pid, s.p, sd, T, rng.draws, remaining);           // camera.h:367: ray(rec.p, dir)
+                live = true;
+            }
+        }
+    }
+    const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
+    if (live) w.q_active[nxt][slot] = pid;
+}
+
+// ------------------------------------------------------------------ K2: metal (material.h:69-90)
+// Always a delta vertex, even when fuzzy (material.h:85): never stored, never connected.  The fuzzed
+// direction is not rejected when it points below the surface (material.h:74-82).
+__global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, WF w, int64_t L0, int nxt) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    bool live = false;
+    uint32_t pid = 0;
+    if (idx < w.counters[C_MAT0 + BDPT_MAT_METAL]) {
+        pid = w.q_mat[BDPT_MAT_METAL][idx];
+        const int32_t remaining = w.remaining[pid] - 1;
+        if (remaining > 0) {
+            const Surf s = load_surf(sc, w, pid);
+            const Mat m = sc.mats[sc.shade[s.prim].mat];
+            const bool is_cam = pid < uint32_t(w.B);
+            const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
+            Rng rng;
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, L0 + b).sid, w.draws[pid]);
+            D3 refl = reflect(s.d, s.n);
+            refl = unit(refl) + (m.param * random_unit_vector(rng));
+            const D3 T = s.T * mk(m.r, m.g, m.b);                              // camera.h:355
+            store_ray(w, pid, s.p, refl, T, rng.draws, remaining);
+            live = true;
+        }
+    }
+    const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
+    if (live) w.q_active[nxt][slot] = pid;
+}
+
+// ------------------------------------------------------------------ K2: dielectric (material.h:92-131)
+__global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame f, WF w, int64_t L0, int nxt) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    bool live = false;
+    uint32_t pid = 0;
+    if (idx < w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC]) {
+        pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx];
+        const int32_t remaining = w.remaining[pid] - 1;
+        if (remaining > 0) {
+            const Surf s = load_surf(sc, w, pid);
+            const Mat m = sc.mats[sc.shade[s.prim].mat];
+            const bool is_cam = pid < uint32_t(w.B);
+            const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
+            Rng rng;
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, L0 + b).sid, w.draws[pid]);
+            const double ri = s.front ? (1.0 / m.param) : m.param;
+            const D3 ud = unit(s.d);
+            const double cos_theta = fmin(dot(-ud, s.n), 1.0);
+            const double sin_theta = sqrt(1.0 - cos_theta * cos_theta);
+            bool refl = ri * sin_theta > 1.0;                                   // total internal reflection
+            if (!refl) {                                                        // Schlick, material.h:125-130
+                double r0 = (1 - ri) / (1 + ri);
+                r0 = r0 * r0;
+                const double rf = r0 + (1 - r0) * det_pow5(1 - cos_theta);
+                refl = rf > rng.next();
+            }
+            const D3 dir = refl ? reflect(ud, s.n) : refract(ud, s.n, ri);
+            const D3 T = s.T * mk(1.0, 1.0, 1.0);
+            store_ray(w, pid, s.p, dir, T, rng.draws, remaining);
+            live = true;
+        }
+    }
+    const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
+    if (live) w.q_active[nxt][slot] = pid;
+}
+
+// ------------------------------------------------------------------ vertex-count reduction
+__global__ void __launch_bounds__(256) k_counts(WF w, int64_t nb) {
+    const int64_t b = int64_t(blockIdx.x) * 256 + threadIdx.x;
+    uint32_t nc = 0, nl = 0;
+    if (b < nb) { nc = w.ncam[b]; nl = w.nlight[b]; }
+    const uint32_t mc = __reduce_max_sync(0xFFFFFFFFu, nc), ml = __reduce_max_sync(0xFFFFFFFFu, nl);
+    const uint32_t sc_ = __reduce_add_sync(0xFFFFFFFFu, nc), sl = __reduce_add_sync(0xFFFFFFFFu, nl);
+    if ((threadIdx.x & 31) == 0) {
+        if (mc) atomicMax(w.counters + C_MAXNC, mc);
+        if (ml) atomicMax(w.counters + C_MAXNL, ml);
+        if (sc_) atomicAdd(w.counters + C_SUMNC, sc_);
+        if (sl) atomicAdd(w.counters + C_SUMNL, sl);
+    }
+}
+
+// ------------------------------------------------------------------ K3
+// connect_vertices (camera.h:440-475) for camera-vertex slots [k0, k1) of every sample against all of
+// the sample's light vertices.  Everything except visible() is evaluated here; pairs that survive the
+// early-outs become shadow rays carrying their finished contribution.
+__global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w, int64_t L0, int64_t nb, int k0, int k1) {
+    const int64_t idx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int64_t total = int64_t(k1 - k0) * nb;
+    const bool valid = idx < total;
+    const int k = valid ? k0 + int(idx / nb) : 0;
+    const int64_t b = valid ? idx % nb : 0;
+    uint32_t nl = 0;
+    D3 cp = mk(0, 0, 0), ctf = mk(0, 0, 0), cn = mk(0, 0, 0);
+    uint32_t pix = 0;
+    if (valid && uint32_t(k) < w.ncam[b]) {
+        nl = w.nlight[b];
+        const size_t v = size_t(k) * size_t(w.B) + size_t(b);
+        cp = mk(w.cv_px[v], w.cv_py[v], w.cv_pz[v]);
+        ctf = mk(w.cv_fx[v], w.cv_fy[v], w.cv_fz[v]);
+        const TriShade sh = sc.shade[w.cv_prim[v]];
+        cn = mk(sh.nx, sh.ny, sh.nz);   // |dot| below makes the face flip irrelevant (camera.h:451-452)
+        pix = decode_sample(f, L0 + b).pix;
+    }
+    const uint32_t nl_max = __reduce_max_sync(0xFFFFFFFFu, nl);
+    for (uint32_t m = 0; m < nl_max; ++m) {
+        bool emit = false;
+        D3 so = mk(0, 0, 0), sd = mk(0, 0, 0), contrib = mk(0, 0, 0);
+        double max_t = 0;
+        if (m < nl) {
+            const size_t v = size_t(m) * size_t(w.B) + size_t(b);
+            const D3 lp = mk(w.lv_px[v], w.lv_py[v], w.lv_pz[v]);
+            const D3 dir = lp - cp;
+            const double dist2 = len2(dir);
+            if (dist2 > 0) {
+                const D3 du = unit(dir);
+                const uint32_t lprim = w.lv_prim[v];
+                const TriShade lsh = sc.shade[lprim & ~kLightFlag];
+                const D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
+                const double cos_cam = fabs(dot(cn, du));
+                const double cos_light = fabs(dot(ln, -du));
+                if (cos_cam > 0 && cos_light > 0) {
+                    // visible() prologue, camera.h:425-436 (its own dist, from sqrt of the same length_squared)
+                    const double dist = len(dir);
+                    const D3 vdu = dir / dist;
+                    max_t = dist - 0.001;
+                    if (dist > 0 && max_t > 0) {
+                        const Mat lm = sc.mats[lsh.mat];
+                        const D3 lrgb = mk(lm.r, lm.g, lm.b);
+                        const D3 f_light = (lprim & kLightFlag) ? lrgb : lrgb / kPi;   // camera.h:463-466
+                        if (len2(f_light) > 0) {
+                            const D3 lT = mk(w.lv_tx[v], w.lv_ty[v], w.lv_tz[v]);
+                            contrib = ctf * lT * f_light;                               // camera.h:471-472
+                            contrib = contrib * (cos_cam * cos_light) / dist2;          // camera.h:473
+                            so = cp + (0.001 * vdu);
+                            sd = vdu;
+                            emit = true;
+                        }
+                    }
+                }
+            }
+        }
+        const uint32_t slot = warp_append(w.counters + C_SHADOW, emit);
+        if (emit) {
+            if (slot < uint32_t(w.scap)) {
+                w.s_ox[slot] = so.x; w.s_oy[slot] = so.y; w.s_oz[slot] = so.z;
+                w.s_dx[slot] = sd.x; w.s_dy[slot] = sd.y; w.s_dz[slot] = sd.z;
+                w.s_tmax[slot] = max_t;
+                w.s_cx[slot] = contrib.x; w.s_cy[slot] = contrib.y; w.s_cz[slot] = contrib.z;
+                w.s_pix[slot] = pix;
+            } else {
+                w.counters[C_OVERFLOW] = 1;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ K4
+// visible() (camera.h:437: world.hit over [0.001, dist-0.001], inclusive ends — SURVEY F4) and the
+// film accumulation of every unoccluded connection.
+template <int BVH>
+__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* film) {
+    __shared__ int32_t s_stack[kRefStackLevels * kBlock];
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    if (idx >= w.counters[C_SHADOW]) return;
+    RayD r;
+    r.o = mk(w.s_ox[idx], w.s_oy[idx], w.s_oz[idx]);
+    r.d = mk(w.s_dx[idx], w.s_dy[idx], w.s_dz[idx]);
+    r.tmin = 0.001;
+    r.tmax = w.s_tmax[idx];
+    HitD h;
+    bool found;
+    if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<true, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
+    else found = traverse_fast<true, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
+    if (!found) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host side
+namespace {
+
+struct Carver {
+    char* p; size_t off = 0;
+    template <class T> T* take(size_t n) {
+        off = (off + 255) & ~size_t(255);
+        T* r = p ? reinterpret_cast<T*>(p + off) : nullptr;
+        off += n * sizeof(T);
+        return r;
+    }
+};
+
+void carve(WF& w, char* base) {
+    Carver c{base};
+    const size_t P = size_t(2 * w.B), V = size_t(w.depth) * size_t(w.B), B = size_t(w.B), S = size_t(w.scap);
+    double** pd[] = {&w.ox, &w.oy, &w.oz, &w.dx, &w.dy, &w.dz, &w.tx, &w.ty, &w.tz, &w.hit_t};
+    for (double** q : pd) *q = c.take<double>(P);
+    w.draws = c.take<uint32_t>(P); w.hit_prim = c.take<uint32_t>(P); w.remaining = c.take<int32_t>(P);
+    for (int k = 0; k < 2; ++k) w.q_active[k] = c.take<uint32_t>(P);
+    for (int k = 0; k < 4; ++k) w.q_mat[k] = c.take<uint32_t>(P);
+    w.counters = c.take<uint32_t>(C_COUNT);
+    double** cv[] = {&w.cv_px, &w.cv_py, &w.cv_pz, &w.cv_fx, &w.cv_fy, &w.cv_fz, &w.lv_px, &w.lv_py, &w.lv_pz, &w.lv_tx, &w.lv_ty, &w.lv_tz};
+    for (double** q : cv) *q = c.take<double>(V);
+    w.cv_prim = c.take<uint32_t>(V); w.lv_prim = c.take<uint32_t>(V);
+    w.ncam = c.take<uint32_t>(B); w.nlight = c.take<uint32_t>(B);
+    double** sq[] = {&w.s_ox, &w.s_oy, &w.s_oz, &w.s_dx, &w.s_dy, &w.s_dz, &w.s_tmax, &w.s_cx, &w.s_cy, &w.s_cz};
+    for (double** q : sq) *q = c.take<double>(S);
+    w.s_pix = c.take<uint32_t>(S);
+    w.bytes = c.off + 256;
+}
+
+// camera::initialize, camera.h:160-197 (host fp64, no FMA contraction: -ffp-contract=off)
+Frame make_frame(const bdpt_camera& c, int H) {
+    Frame f{};
+    f.W = c.image_width; f.H = H;
+    f.n = int(std::sqrt(double(c.samples_per_pixel)));
+    f.recip_sqrt_spp = 1.0 / f.n;
+    f.depth = c.max_depth;
+    const D3 lookfrom = mk(c.lookfrom[0], c.lookfrom[1], c.lookfrom[2]), lookat = mk(c.lookat[0], c.lookat[1], c.lookat[2]);
+    const D3 vup = mk(c.vup[0], c.vup[1], c.vup[2]);
+    f.background = mk(c.background[0], c.background[1], c.background[2]);
+    f.center = lookfrom;
+    const double theta = c.vfov * 3.1415926535897932385 / 180.0;   // main.h:24-26
+    const double h = std::tan(theta / 2);
+    const double vh = 2 * h * c.focus_dist;
+    const double vw = vh * (double(c.image_width) / H);
+    const D3 w = unit(lookfrom - lookat);
+    const D3 u = unit(cross(vup, w));
+    const D3 v = cross(w, u);
+    const D3 vu = vw * u;
+    const D3 vv = vh * -v;
+    f.du = vu / c.image_width;
+    f.dv = vv / H;
+    const D3 ul = f.center - (c.focus_dist * w) - vu / 2 - vv / 2;
+    f.pixel00 = ul + 0.5 * (f.du + f.dv);
+    return f;
+}
+
+inline unsigned grid_for(int64_t n, int block) { return unsigned(std::max<int64_t>(1, (n + block - 1) / block)); }
+
+}  // namespace
+
+void render_free(bdpt_ctx* ctx) {
+    if (!ctx->wf) return;
+    WF* w = static_cast<WF*>(ctx->wf);
+    if (w->base) cudaFree(w->base);
+    delete w;
+    ctx->wf = nullptr;
+}
+
+int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts_in) {
+    bdpt_render_opts o{};
+    if (opts_in) o = *opts_in;
+    if (cam->image_width <= 0 || cam->samples_per_pixel <= 0 || cam->aspect_ratio <= 0 || cam->max_depth < 0) {
+        ctx->err = "bad camera"; return BDPT_ERR_ARG;
+    }
+    if (cam->defocus_angle > 0) { ctx->err = "defocus blur is off in the reference's loader (scene_loader.h:463)"; return BDPT_ERR_ARG; }
+    if (o.bvh != BDPT_BVH_REFERENCE && o.bvh != BDPT_BVH_FAST) { ctx->err = "unknown bvh flavour"; return BDPT_ERR_ARG; }
+    int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
+    H = H < 1 ? 1 : H;
+    if (!ctx->film || ctx->film_w != cam->image_width || ctx->film_h != H) {
+        int rc = bdpt_film_clear(ctx, cam->image_width, H);
+        if (rc) return rc;
+    }
+    Frame f = make_frame(*cam, H);
+    if (f.n < 1) { ctx->err = "samples_per_pixel < 1"; return BDPT_ERR_ARG; }
+    f.seed = o.seed;
+    const int n2 = f.n * f.n;
+    int s_begin = std::max(0, o.stratum_begin), s_end = o.stratum_end <= 0 ? n2 : std::min(n2, o.stratum_end);
+    const int s_step = o.stratum_step <= 0 ? 1 : o.stratum_step;
+    const int row0 = std::max(0, o.row_begin), row1 = o.row_end <= 0 ? H : std::min(H, o.row_end);
+    const int64_t n_strata = s_end > s_begin ? (s_end - s_begin + s_step - 1) / s_step : 0;
+    f.row0 = row0; f.rows = std::max(0, row1 - row0);
+    f.s_begin = s_begin; f.s_step = s_step;
+    f.npix = int64_t(f.rows) * f.W;
+    const int64_t total = n_strata * f.npix;
+    ctx->last_ms = 0.0;
+    if (total <= 0 || f.depth <= 0) {
+        // depth 0: trace_path pushes nothing and adds no background (camera.h:333) -> black
+        ctx->samples += uint64_t(std::max<int64_t>(0, total));
+        return BDPT_OK;
+    }
+
+    // workspace
+    int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 20);
+    B = std::min<int64_t>(B, total);
+    B = std::min<int64_t>(B, int64_t(1) << 30);
+    WF* w = static_cast<WF*>(ctx->wf);
+    if (!w || w->B < B || w->depth < f.depth) {
+        render_free(ctx);
+        w = new WF();
+        std::memset(w, 0, sizeof(WF));
+        w->B = B; w->depth = f.depth;
+        w->scap = std::max<int64_t>(B * 32, int64_t(f.depth) * B);   // >= one camera slot against every light vertex
+        w->scap = std::min<int64_t>(w->scap, int64_t(0xFFFFFFF0u));
+        carve(*w, nullptr);
+        void* base = nullptr;
+        cudaError_t e = cudaMalloc(&base, w->bytes);
+        if (e != cudaSuccess) { ctx->err = std::string("wavefront workspace: ") + cudaGetErrorString(e); delete w; return BDPT_ERR_NOMEM; }
+        w->base = base;
+        carve(*w, static_cast<char*>(base));
+        ctx->wf = w;
+    }
+    WF wf = *w;
+    const int64_t Bcap = wf.B;   // indices use the allocated stride
+    SceneView sc = ctx->view;
+    cudaStream_t st = ctx->stream;
+    uint32_t hc[C_COUNT];
+    uint64_t rays_closest = 0, rays_shadow = 0, cam_verts = 0, light_verts = 0;
+
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+    for (int64_t L0 = 0; L0 < total; L0 += Bcap) {
+        const int64_t nb = std::min<int64_t>(Bcap, total - L0);
+        BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters, 0, C_COUNT * sizeof(uint32_t), st));
+        k_generate<<<grid_for(nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb);
+        ctx->launches += 1;
+        BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        BDPT_CUDA(ctx, cudaStreamSynchronize(st));
+        int cur = 0;
+        uint32_t n_active = hc[C_ACTIVE0];
+        while (n_active > 0) {
+            const int nxt = cur ^ 1;
+            // zero the next-ray counter and the material counters
+            BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_ACTIVE0 + nxt, 0, sizeof(uint32_t), st));
+            BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_MAT0, 0, 4 * sizeof(uint32_t), st));
+            const unsigned g = grid_for(n_active, kBlock);
+            if (o.bvh == BDPT_BVH_REFERENCE)
+                k_trace_paths<BDPT_BVH_REFERENCE><<<g, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, ctx->film);
+            else
+                k_trace_paths<BDPT_BVH_FAST><<<g, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, ctx->film);
+            k_shade_light<<<g, kBlock, 0, st>>>(sc, f, wf, L0, ctx->film);
+            k_shade_lambert<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
+            k_shade_metal<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
+            k_shade_dielectric<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
+            ctx->launches += 5;
+            rays_closest += n_active;
+            BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            BDPT_CUDA(ctx, cudaStreamSynchronize(st));
+            n_active = hc[C_ACTIVE0 + nxt];
+            cur = nxt;
+        }
+        // connections
+        k_counts<<<grid_for(nb, 256), 256, 0, st>>>(wf, nb);
+        ctx->launches += 1;
+        BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        BDPT_CUDA(ctx, cudaStreamSynchronize(st));
+        const int max_nc = int(hc[C_MAXNC]), max_nl = int(hc[C_MAXNL]);
+        cam_verts += hc[C_SUMNC]; light_verts += hc[C_SUMNL];
+        if (max_nc > 0 && max_nl > 0) {
+            int slots_per_round = int(std::max<int64_t>(1, wf.scap / (nb * int64_t(max_nl))));
+            for (int k0 = 0; k0 < max_nc; k0 += slots_per_round) {
+                const int k1 = std::min(max_nc, k0 + slots_per_round);
+                BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_SHADOW, 0, sizeof(uint32_t), st));
+                k_connect<<<grid_for(int64_t(k1 - k0) * nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb, k0, k1);
+                BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                BDPT_CUDA(ctx, cudaStreamSynchronize(st));
+                ctx->launches += 1;
+                if (hc[C_OVERFLOW]) { ctx->err = "shadow queue overflow"; return BDPT_ERR_STATE; }
+                const uint32_t ns = hc[C_SHADOW];
+                if (ns) {
+                    if (o.bvh == BDPT_BVH_REFERENCE) k_shadow<BDPT_BVH_REFERENCE><<<grid_for(ns, kBlock), kBlock, 0, st>>>(sc, wf, ctx->film);
+                    else k_shadow<BDPT_BVH_FAST><<<grid_for(ns, kBlock), kBlock, 0, st>>>(sc, wf, ctx->film);
+                    ctx->launches += 1;
+                    rays_shadow += ns;
+                }
+            }
+        }
+        ctx->samples += uint64_t(nb);
+    }
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+    BDPT_CUDA(ctx, cudaStreamSynchronize(st));
+    BDPT_CUDA(ctx, cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_ms = ms;
+    // host-side tallies go into the device counter block so bdpt_stats reads one place
+    unsigned long long add[4] = {rays_closest, rays_shadow, cam_verts, light_verts};
+    unsigned long long cur_stats[16];
+    BDPT_CUDA(ctx, cudaMemcpy(cur_stats, ctx->d_stats, sizeof cur_stats, cudaMemcpyDeviceToHost));
+    cur_stats[ST_RAYS_CLOSEST] += add[0]; cur_stats[ST_RAYS_SHADOW] += add[1];
+    cur_stats[ST_CAM_VERTS] += add[2]; cur_stats[ST_LIGHT_VERTS] += add[3];
+    BDPT_CUDA(ctx, cudaMemcpy(ctx->d_stats, cur_stats, sizeof cur_stats, cudaMemcpyHostToDevice));
+    return BDPT_OK;
+}
+
+}  // namespace bdpt

@@ -65,7 +65,7 @@ struct SceneView {
     const TriShade* shade;
     const Mat* mats;
     const uint32_t* lights;       // prim IDs, reference light-list order
-    const double* light_area;     // per light triangle area (triangle.h:33)
+    const double* light_area;     // running sums of light triangle areas in list order (triangle.h:206-212)
     uint32_t n_lights;
     uint32_t n_tris;
     uint32_t n_ref_nodes;

@@ -72,7 +72,31 @@ struct Philox {
     }
 };
 
+// Deterministic sin/cos and x^5 used ONLY in ORC_RNG_PHILOX mode (never in the reference-pinned
+// MT19937 mode, which keeps libm's std::sin/std::cos/std::pow for bit parity with the reference).
+// libm and CUDA's math library differ in the last ulp, and camera::visible()'s far-endpoint test is a
+// rounding knife edge, so a per-sample GPU-vs-port comparison needs transcendental
+// functions that are plain IEEE add/mul sequences: Cody-Waite reduction by pi/2 + the classic degree-13/12
+// minimax kernels on [-pi/4, pi/4] (error < 1 ulp).  csrc/render_math.cuh states the same algorithm.
+inline void det_sincos(double phi, double& s_out, double& c_out) {
+    const int k = int(phi * 0.63661977236758134308 + 0.5);               // nearest multiple of pi/2
+    const double y = (phi - k * 1.57079632673412561417e+00) - k * 6.07710050650619224932e-11;
+    const double z = y * y;
+    const double s = y + y * z * (-1.66666666666666324348e-01 + z * (8.33333333332248946124e-03 + z * (-1.98412698298579493134e-04 +
+                     z * (2.75573137070700676789e-06 + z * (-2.50507602534068634195e-08 + z * 1.58969099521155010221e-10)))));
+    const double c = 1.0 - 0.5 * z + z * z * (4.16666666666666019037e-02 + z * (-1.38888888888741095749e-03 + z * (2.48015872894767294178e-05 +
+                     z * (-2.75573143513906633035e-07 + z * (2.08757232129817482790e-09 + z * -1.13596475577881948265e-11)))));
+    switch (k & 3) {
+        case 0: s_out = s; c_out = c; break;
+        case 1: s_out = c; c_out = -s; break;
+        case 2: s_out = -s; c_out = -c; break;
+        default: s_out = -c; c_out = s; break;
+    }
+}
+inline double det_pow5(double x) { const double x2 = x * x; const double x4 = x2 * x2; return x4 * x; }
+
 struct Rng {
+    bool det = false;  // PHILOX mode: deterministic sin/cos/pow5 (see above)
     // mode MT: all streams alias one engine, exactly the reference's single global stream
     std::mt19937* mt = nullptr;
     std::uniform_real_distribution<double>* dist = nullptr;
@@ -114,8 +138,10 @@ inline V3 refract(V3 uv, V3 n, double etai_over_etat) {          // vec3.h:142-1
 inline V3 random_cosine_direction(Rng& r) {  // vec3.h:149-159
     double r1 = r.next(), r2 = r.next();
     double phi = 2 * kPi * r1;
-    double x = std::cos(phi) * std::sqrt(r2);
-    double y = std::sin(phi) * std::sqrt(r2);
+    double cs = 0, sn = 0;
+    if (r.det) det_sincos(phi, sn, cs); else { cs = std::cos(phi); sn = std::sin(phi); }
+    double x = cs * std::sqrt(r2);
+    double y = sn * std::sqrt(r2);
     double z = std::sqrt(1 - r2);
     return {x, y, z};
 }
@@ -400,7 +426,7 @@ struct Integrator {
                 if (!refl) {  // material.h:125-130 Schlick
                     double r0 = (1 - ri) / (1 + ri);
                     r0 = r0 * r0;
-                    double rf = r0 + (1 - r0) * std::pow((1 - cos_theta), 5);
+                    double rf = r0 + (1 - r0) * (rng.det ? det_pow5(1 - cos_theta) : std::pow((1 - cos_theta), 5));
                     refl = rf > rng.next();
                 }
                 dir = refl ? reflect(ud, rec.normal) : refract(ud, rec.normal, ri);
@@ -600,6 +626,7 @@ int port_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int r
                             cr = Rng(); lr = Rng();
                             cr.seed = lr.seed = seed; cr.sample = lr.sample = sample;
                             cr.stream = 0; lr.stream = 1;
+                            cr.det = lr.det = true;
                         }
                         V3 o, d;
                         cam.get_ray(i, j, s_i, s_j, cr, o, d);
@@ -621,6 +648,9 @@ void port_stats_reset(void) {
     tl_stats = Stats();
     for (int i = 0; i < 8; ++i) if (i != 6) g_stats[i] = 0;
 }
+
+// test hook: the PHILOX-mode deterministic sin/cos (accuracy is pinned in tests/test_oracle.py)
+void port_det_sincos(double phi, double* s, double* c) { det_sincos(phi, *s, *c); }
 
 void port_colors_to_rgb8(const double* film, int W, int H, int spp, uint8_t* out) {  // wpng.h:14-35
     const double scale = 1.0 / std::max(1, spp);
