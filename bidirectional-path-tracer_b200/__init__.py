@@ -27,6 +27,8 @@ EXPORTS = [
     "bdpt_bvh_leaf_order", "bdpt_host_bvh_build", "bdpt_trace", "bdpt_visible", "bdpt_render",
     "bdpt_film_clear", "bdpt_film_device_ptr", "bdpt_film_download", "bdpt_film_to_rgb8", "bdpt_stats",
     "bdpt_stats_reset", "bdpt_last_device_ms", "bdpt_sync",
+    "bdpt_scene_file_load", "bdpt_scene_file_free", "bdpt_scene_file_info", "bdpt_scene_file_copy",
+    "bdpt_write_png", "bdpt_host_last_error",
 ]
 
 
@@ -93,6 +95,14 @@ def lib():
         L.bdpt_stats_reset.argtypes = [C.c_void_p]
         L.bdpt_last_device_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.bdpt_sync.argtypes = [C.c_void_p]
+        L.bdpt_scene_file_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        L.bdpt_scene_file_free.argtypes = [C.c_void_p]
+        L.bdpt_scene_file_free.restype = None
+        L.bdpt_scene_file_info.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64),
+                                           C.c_void_p, C.c_char_p, C.c_uint64]
+        L.bdpt_scene_file_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.bdpt_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+        L.bdpt_host_last_error.restype = C.c_char_p
         _lib = L
     return _lib
 
@@ -137,6 +147,52 @@ def host_bvh_build(verts, fast=False):
     if rc:
         raise BdptError("bdpt_host_bvh_build failed: %d %s" % (rc, lib().bdpt_last_error(None).decode()))
     return order, nr.value, (nf.value if fast else None)
+
+
+class SceneFile:
+    """load_scene_from_yaml (scene_loader.h:480-523) through the C-ABI: camera fields + flattened triangle soup."""
+
+    def __init__(self, yaml_path):
+        h = C.c_void_p()
+        rc = lib().bdpt_scene_file_load(os.fsencode(yaml_path), C.byref(h))
+        if rc:
+            raise BdptError("Failed to load scene: " + lib().bdpt_host_last_error().decode())
+        try:
+            nt, nm, nl = C.c_uint64(0), C.c_uint32(0), C.c_uint64(0)
+            self.camera = Camera()
+            name = C.create_string_buffer(512)
+            lib().bdpt_scene_file_info(h, C.byref(nt), C.byref(nm), C.byref(nl), C.byref(self.camera), name, 512)
+            self.n_lights = nl.value
+            self.output = name.value.decode()
+            self.verts = np.empty((nt.value, 9), np.float64)
+            self.mat_id = np.empty(nt.value, np.uint32)
+            self.materials = (Material * max(1, nm.value))()
+            lib().bdpt_scene_file_copy(h, self.verts.ctypes.data, self.mat_id.ctypes.data, C.byref(self.materials))
+            self.n_mats = nm.value
+        finally:
+            lib().bdpt_scene_file_free(h)
+
+    def material_list(self):
+        return [(int(m.type), tuple(m.rgb), float(m.param)) for m in list(self.materials)[:self.n_mats]]
+
+    def camera_with(self, width=None, height=None, spp=None, depth=None):
+        """The CLI's --res/--spp/--depth overrides (BASELINE.json configs differ from the YAML values)."""
+        c = Camera.from_buffer_copy(self.camera)
+        if width and height:
+            c.image_width = int(width)
+            c.aspect_ratio = float(width) / float(height)
+        if spp:
+            c.samples_per_pixel = int(spp)
+        if depth is not None:
+            c.max_depth = int(depth)
+        return c
+
+
+def write_png(path, rgb):
+    rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
+    h, w, _ = rgb.shape
+    if lib().bdpt_write_png(os.fsencode(path), rgb.ctypes.data, w, h):
+        raise BdptError(lib().bdpt_host_last_error().decode())
 
 
 class Context:

@@ -1,0 +1,170 @@
+// Host-side object model of the drop-in surface: the names a user of the reference touches in
+// main.cpp (src/main.cpp:62-78) — vec3/point3/color, material classes, triangle, triangle_collection,
+// hittable_list, bvh_node, camera, scene_load_result — kept source-compatible, but as plain descriptors:
+// shading, intersection and the BVH live on the GPU behind include/bdpt.h.
+//   reference                                   here
+//   material + 4 subclasses (material.h:16-147)  `material` with a kind tag; same constructors
+//   triangle (triangle.h:19-133)                 3 points + material handle
+//   triangle_collection (triangle.h:135-230)     std::vector<triangle>, add/size/to_hittable_list
+//   bvh_node(hittable_list) (bvh.h:13)           records the primitive list; the trees are built at upload
+//   camera (camera.h:23-477)                     same public fields; render() drives libbdpt
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/bdpt.h"
+
+using std::make_shared;
+using std::shared_ptr;
+
+class vec3 {
+  public:
+    double e[3];
+    vec3() : e{0, 0, 0} {}
+    vec3(double x, double y, double z) : e{x, y, z} {}
+    double x() const { return e[0]; }
+    double y() const { return e[1]; }
+    double z() const { return e[2]; }
+    double operator[](int i) const { return e[i]; }
+    double& operator[](int i) { return e[i]; }
+    double length_squared() const { return e[0] * e[0] + e[1] * e[1] + e[2] * e[2]; }
+    double length() const { return std::sqrt(length_squared()); }
+};
+using point3 = vec3;
+using color = vec3;
+
+class material {
+  public:
+    enum kind_t { Lambertian = BDPT_MAT_LAMBERTIAN, Metal = BDPT_MAT_METAL, Dielectric = BDPT_MAT_DIELECTRIC,
+                  DiffuseLight = BDPT_MAT_LIGHT };
+    virtual ~material() = default;
+    kind_t kind;
+    color rgb;       // albedo or emission
+    double param;    // fuzz or refraction index
+    virtual bool is_delta() const { return kind == Metal || kind == Dielectric; }   // material.h:38,85,118
+  protected:
+    material(kind_t k, const color& c, double p) : kind(k), rgb(c), param(p) {}
+};
+class lambertian : public material {   // material.h:42-67
+  public:
+    explicit lambertian(const color& albedo) : material(Lambertian, albedo, 0.0) {}
+};
+class metal : public material {        // material.h:69-90 (fuzz clamped to <= 1, :71)
+  public:
+    metal(const color& albedo, double fuzz) : material(Metal, albedo, fuzz < 1 ? fuzz : 1) {}
+};
+class dielectric : public material {   // material.h:92-131
+  public:
+    explicit dielectric(double refraction_index) : material(Dielectric, color(1, 1, 1), refraction_index) {}
+};
+class diffuse_light : public material {  // material.h:133-147
+  public:
+    explicit diffuse_light(const color& emit) : material(DiffuseLight, emit, 0.0) {}
+};
+
+class hittable {
+  public:
+    virtual ~hittable() = default;
+};
+
+class triangle : public hittable {
+  public:
+    triangle(const point3& a, const point3& b, const point3& c, shared_ptr<material> m) : v0(a), v1(b), v2(c), mat(std::move(m)) {}
+    point3 v0, v1, v2;
+    shared_ptr<material> mat;
+};
+
+class hittable_list : public hittable {
+  public:
+    std::vector<shared_ptr<hittable>> objects;
+    void add(shared_ptr<hittable> o) { objects.push_back(std::move(o)); }
+    void clear() { objects.clear(); }
+};
+
+class triangle_collection : public hittable {
+  public:
+    std::vector<triangle> tris;
+    void add(const triangle& t) { tris.push_back(t); }
+    void clear() { tris.clear(); }
+    size_t size() const { return tris.size(); }
+    bool empty() const { return tris.empty(); }
+    hittable_list to_hittable_list() const {   // triangle.h:191
+        hittable_list l;
+        l.objects.reserve(tris.size());
+        for (const auto& t : tris) l.add(make_shared<triangle>(t));
+        return l;
+    }
+};
+
+// bvh_node(hittable_list) (bvh.h:13-18): here it only records the primitives, in list order (= prim ID);
+// both trees (reference topology and SAH) are built inside bdpt_scene_upload.
+class bvh_node : public hittable {
+  public:
+    explicit bvh_node(hittable_list list) {
+        prims.reserve(list.objects.size());
+        for (auto& o : list.objects)
+            if (auto t = std::dynamic_pointer_cast<triangle>(o)) prims.push_back(*t);
+    }
+    std::vector<triangle> prims;
+};
+
+struct render_options {         // overrides the CLI adds on top of the YAML
+    int gpus = 1;               // strata are sharded over this many devices
+    int bvh = BDPT_BVH_FAST;    // both give the reference's hits; REFERENCE also walks its topology
+    uint64_t seed = 0;
+    bool quiet = false;
+    bool write_file = true;     // write ./output/<file_name> like camera.h:139-142
+};
+
+struct render_report {
+    double device_ms = 0, wall_s = 0;
+    uint64_t samples = 0, rays_closest = 0, rays_shadow = 0, launches = 0;
+    int width = 0, height = 0;
+    std::vector<double> film;   // W*H*3 fp64 SUM over strata (camera.h:55)
+};
+
+class camera {
+  public:
+    // camera.h:26-41
+    double aspect_ratio = 1.0;
+    int image_width = 100;
+    int samples_per_pixel = 50;
+    int max_depth = 10;
+    color background = color(0, 0, 0);
+    double vfov = 90;
+    point3 lookfrom = point3(0, 0, 0);
+    point3 lookat = point3(0, 0, -1);
+    vec3 vup = vec3(0, 1, 0);
+    double defocus_angle = 0;
+    double focus_dist = 10;
+    std::string file_name = "image.png";
+
+    render_options options;     // not in the reference: device-side knobs
+    render_report last_report;
+
+    // camera.h:43. `world` may be a bvh_node (as main.cpp:66 builds) or a triangle_collection; `lights`
+    // is accepted for signature compatibility — the device derives the light list from the materials, in
+    // world order, which is what scene_loader.h:190-202 / main.cpp:67 produce.
+    void render(const hittable& world, const hittable& lights);
+};
+
+struct scene_load_result {      // scene_loader.h:22-26
+    camera cam;
+    triangle_collection world;
+    triangle_collection lights;
+};
+
+scene_load_result load_scene_from_yaml(const std::string& path);   // scene_loader.h:480-523
+
+// image output, wpng.h:14-89
+void colors_to_rgb8(const std::vector<color>& framebuffer, int image_width, int image_height, int samples_per_pixel,
+                    std::vector<uint8_t>& out_rgb);
+void write_png(const std::string& file_name, const std::vector<uint8_t>& rgb, int image_width, int image_height);
+void write_png_path(const std::string& path, const uint8_t* rgb, int image_width, int image_height);
+
+// flatten a primitive list to the C-ABI's soup (prim ID = list order); material table dedups by pointer
+void flatten_triangles(const std::vector<triangle>& tris, std::vector<double>& verts, std::vector<uint32_t>& mat_id,
+                       std::vector<bdpt_material>& mats);

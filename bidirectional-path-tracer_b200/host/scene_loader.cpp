@@ -1,0 +1,287 @@
+// YAML + OBJ scene front-end: behaviour of the reference's src/scene/scene_loader.h (schema in SURVEY
+// Appendix B), written against yaml_lite instead of yaml-cpp.  Not on the timed path.
+#include <algorithm>
+#include <cstring>
+#include <filesystem>
+#include <fstream>
+#include <iostream>
+#include <sstream>
+#include <stdexcept>
+#include <unordered_map>
+
+#include "scene.h"
+#include "yaml_lite.h"
+
+namespace {
+
+using yaml_lite::node;
+using material_map = std::unordered_map<std::string, shared_ptr<material>>;
+
+// scalar helpers with the reference's "default on anything odd" behaviour (scene_loader.h:32-72)
+std::string to_string(const node& n, const std::string& def = {}) { return n.is_scalar() ? n.scalar : def; }
+double to_double(const node& n, double def = 0.0) { double v; return n.as_double(v) ? v : def; }
+int to_int(const node& n, int def = 0) { int v; return n.as_int(v) ? v : def; }
+std::vector<double> to_double_list(const node& n) {
+    std::vector<double> out;
+    if (!n.is_sequence()) return out;
+    out.reserve(n.seq.size());
+    for (const auto& e : n.seq) out.push_back(to_double(e, 0.0));
+    return out;
+}
+color read_color(const node& n, const color& fallback) {            // scene_loader.h:74-79
+    const auto v = to_double_list(n);
+    return v.size() < 3 ? fallback : color(v[0], v[1], v[2]);
+}
+color read_color_scaled(const node& n, const color& fallback) {     // scene_loader.h:81-92: 0-255 -> 0-1
+    const auto v = to_double_list(n);
+    if (v.size() < 3) return fallback;
+    double r = v[0], g = v[1], b = v[2];
+    const double maxc = std::max({std::fabs(r), std::fabs(g), std::fabs(b)});
+    if (maxc > 1.0 && maxc <= 255.0) { const double s = 1.0 / 255.0; r *= s; g *= s; b *= s; }
+    return color(r, g, b);
+}
+
+shared_ptr<material> build_material(const node& n) {                 // scene_loader.h:101-170
+    if (!n.is_map()) throw std::runtime_error("Material must be a mapping");
+    const color black(0, 0, 0);
+    const std::string type = to_string(n["type"], "");
+    if (!type.empty()) {
+        const color c = read_color_scaled(n["color"], read_color_scaled(n["albedo"],
+                        read_color_scaled(n["base_color"], read_color_scaled(n["base_colour"], black))));
+        if (type == "light" || type == "diffuse_light")
+            return make_shared<diffuse_light>(read_color(n["emission"], black));   // linear HDR, never /255
+        if (type == "lambertian") return make_shared<lambertian>(c);
+        if (type == "metal") return make_shared<metal>(c, std::clamp(to_double(n["roughness"], 0.0), 0.0, 1.0));
+        if (type == "dielectric" || type == "glass") {
+            const double ior = to_double(n["ior"], 1.5);
+            return make_shared<dielectric>(ior > 0.0 ? ior : 1.5);
+        }
+    }
+    // legacy PBR-ish keys (scene_loader.h:138-169)
+    color base = read_color_scaled(n["base_color"], black);
+    if (n["base_colour"].defined()) base = read_color_scaled(n["base_colour"], base);
+    color emission = read_color_scaled(n["emission"], black);
+    if (emission.length_squared() > 0.0) {
+        const double maxc = std::max({std::fabs(emission.x()), std::fabs(emission.y()), std::fabs(emission.z())});
+        if (maxc > 50.0) { const double s = 50.0 / maxc; emission = color(emission.x() * s, emission.y() * s, emission.z() * s); }
+        return make_shared<diffuse_light>(emission);
+    }
+    double transmission = to_double(n["transmission"], 0.0);
+    if (transmission == 0.0) transmission = to_double(n["spec_trans"], 0.0);
+    const double ior = to_double(n["ior"], 1.5);
+    if (transmission > 0.0) return make_shared<dielectric>(ior > 0.0 ? ior : 1.5);
+    const double metallic = to_double(n["metallic"], 0.0);
+    const double roughness = std::clamp(to_double(n["roughness"], 0.0), 0.0, 1.0);
+    if (metallic > 0.5) return make_shared<metal>(base, roughness);
+    return make_shared<lambertian>(base);
+}
+
+material_map load_materials(const node& n) {                         // scene_loader.h:173-188
+    material_map out;
+    if (!n.is_map()) return out;
+    for (const auto& kv : n.map) {
+        try { out[kv.first] = build_material(kv.second); } catch (...) { /* bad entries are skipped */ }
+    }
+    return out;
+}
+
+struct sink {                                                        // scene_loader.h:190-202
+    triangle_collection& world;
+    triangle_collection& lights;
+    void add(const point3& a, const point3& b, const point3& c, const shared_ptr<material>& m) {
+        triangle t(a, b, c, m);
+        world.add(t);
+        if (m->kind == material::DiffuseLight) lights.add(t);
+    }
+};
+
+shared_ptr<material> resolve_material(const node& m, const material_map& mats) {   // scene_loader.h:318-329,411-422
+    shared_ptr<material> mat;
+    if (m.is_scalar()) { auto it = mats.find(m.scalar); if (it != mats.end()) mat = it->second; }
+    else if (m.is_map()) mat = build_material(m);
+    if (!mat) mat = make_shared<lambertian>(color(0.8, 0.8, 0.8));
+    return mat;
+}
+
+void load_tri_mesh(const node& mesh, sink& out) {                    // scene_loader.h:244-272
+    const node& data = mesh["data"];
+    if (!data.is_map()) throw std::runtime_error("Mesh missing data field");
+    if (!data["vertices"].is_sequence()) throw std::runtime_error("Missing vertices");
+    const auto v = to_double_list(data["vertices"]);
+    if (v.size() % 9 != 0) throw std::runtime_error("Vertices length not a multiple of 9");
+    if (!mesh["material"].defined()) throw std::runtime_error("Missing material field");
+    const auto mat = build_material(mesh["material"]);
+    for (size_t i = 0; i < v.size(); i += 9)
+        out.add(point3(v[i], v[i + 1], v[i + 2]), point3(v[i + 3], v[i + 4], v[i + 5]), point3(v[i + 6], v[i + 7], v[i + 8]), mat);
+}
+
+point3 sphere_point(double theta, double phi, const point3& c, double r) {   // scene_loader.h:204-210
+    const double st = std::sin(theta);
+    const double x = r * st * std::cos(phi), y = r * std::cos(theta), z = r * st * std::sin(phi);
+    return point3(c.x() + x, c.y() + y, c.z() + z);
+}
+
+void load_sphere(const node& mesh, sink& out) {                      // scene_loader.h:212-242,274-294
+    if (!mesh["material"].defined()) throw std::runtime_error("Missing material field");
+    const auto mat = build_material(mesh["material"]);
+    const node& data = mesh["data"];
+    if (!data.is_map()) throw std::runtime_error("Missing data field");
+    const auto cv = to_double_list(data["center"]);
+    const point3 center = cv.size() < 3 ? point3(0, 0, 0) : point3(cv[0], cv[1], cv[2]);
+    const double radius = to_double(data["radius"], 0.0);
+    if (radius <= 0.0) throw std::runtime_error("Missing or invalid radius field");
+    const int lat_steps = 16, lon_steps = 32;   // 960 triangles
+    const double pi = 3.14159265358979323846;
+    for (int lat = 0; lat < lat_steps; ++lat) {
+        const double t0 = pi * (double(lat) / lat_steps), t1 = pi * (double(lat + 1) / lat_steps);
+        for (int lon = 0; lon < lon_steps; ++lon) {
+            const double p0 = 2.0 * pi * (double(lon) / lon_steps), p1 = 2.0 * pi * (double(lon + 1) / lon_steps);
+            const point3 p00 = sphere_point(t0, p0, center, radius), p01 = sphere_point(t0, p1, center, radius);
+            const point3 p10 = sphere_point(t1, p0, center, radius), p11 = sphere_point(t1, p1, center, radius);
+            if (lat > 0) out.add(p00, p10, p11, mat);
+            if (lat < lat_steps - 1) out.add(p00, p11, p01, mat);
+        }
+    }
+}
+
+void load_indexed_mesh(const node& mesh, sink& out, const material_map& mats) {   // scene_loader.h:297-343
+    const node &vn = mesh["vertices"], &tn = mesh["triangles"];
+    if (!vn.is_sequence()) throw std::runtime_error("Indexed mesh missing vertices");
+    if (!tn.is_sequence()) throw std::runtime_error("Indexed mesh missing triangles");
+    std::vector<point3> verts;
+    verts.reserve(vn.seq.size());
+    for (const auto& v : vn.seq) {
+        const auto vals = to_double_list(v);
+        if (vals.size() < 3) continue;
+        verts.emplace_back(vals[0], vals[1], vals[2]);
+    }
+    const auto mat = resolve_material(mesh["material"], mats);
+    for (const auto& tri : tn.seq) {
+        std::vector<int> idx;
+        if (tri.is_sequence()) for (const auto& t : tri.seq) idx.push_back(to_int(t, 0));
+        if (idx.size() < 3) continue;
+        out.add(verts.at(size_t(idx[0])), verts.at(size_t(idx[1])), verts.at(size_t(idx[2])), mat);   // 0-based; .at throws
+    }
+}
+
+// OBJ: 'v' and 'f' lines only, 1-based and negative indices, fan triangulation (scene_loader.h:346-397).
+// Tokenised by hand (the reference's istringstream-per-line parse is the slow part at 10^7 faces).
+void load_obj_file(const std::filesystem::path& path, const shared_ptr<material>& mat, sink& out) {
+    std::ifstream in(path, std::ios::binary);
+    if (!in) throw std::runtime_error("Failed to open OBJ file: " + path.string());
+    std::string buf((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+    std::vector<point3> verts;
+    verts.reserve(1024);
+    std::vector<int> fidx;
+    const char* p = buf.c_str();
+    const char* end = p + buf.size();
+    while (p < end) {
+        const char* eol = static_cast<const char*>(std::memchr(p, '\n', size_t(end - p)));
+        if (!eol) eol = end;
+        const char* q = p;
+        while (q < eol && (*q == ' ' || *q == '\t')) ++q;
+        const bool sep = q + 1 < eol && (q[1] == ' ' || q[1] == '\t');
+        if (q < eol && *q == 'v' && sep) {
+            char* e1; char* e2; char* e3;
+            const double x = std::strtod(q + 1, &e1);
+            const double y = (e1 != q + 1 && e1 < eol) ? std::strtod(e1, &e2) : (e2 = e1, 0.0);
+            const double z = (e2 != e1 && e2 < eol) ? std::strtod(e2, &e3) : (e3 = e2, 0.0);
+            if (e1 != q + 1 && e2 != e1 && e3 != e2 && e3 <= eol) verts.emplace_back(x, y, z);
+        } else if (q < eol && *q == 'f' && sep) {
+            fidx.clear();
+            const char* t = q + 1;
+            while (t < eol) {
+                while (t < eol && (*t == ' ' || *t == '\t' || *t == '\r')) ++t;
+                if (t >= eol) break;
+                char* e;
+                const long vi = std::strtol(t, &e, 10);     // "vi", "vi/vt", "vi/vt/vn", "vi//vn": leading int
+                if (e != t) fidx.push_back(vi > 0 ? int(vi - 1) : int(verts.size()) + int(vi));
+                t = e != t ? e : t + 1;
+                while (t < eol && *t != ' ' && *t != '\t') ++t;   // skip the /vt/vn tail
+            }
+            for (size_t k = 2; k < fidx.size(); ++k)
+                out.add(verts.at(size_t(fidx[0])), verts.at(size_t(fidx[k - 1])), verts.at(size_t(fidx[k])), mat);
+        }
+        p = eol + 1;
+    }
+}
+
+void load_object(const node& n, const std::filesystem::path& dir, sink& out, const material_map& mats) {   // :399-425
+    const std::string rel = to_string(n["file"]);
+    if (rel.empty()) throw std::runtime_error("Object missing file field");
+    load_obj_file(dir / rel, resolve_material(n["material"], mats), out);
+}
+
+void load_camera(const node& n, camera& cam) {                       // scene_loader.h:427-476
+    if (!n.is_map()) throw std::runtime_error("Camera section must be a mapping");
+    const node& res = n["resolution"];
+    if (!res.is_sequence() || res.size() < 2) throw std::runtime_error("Camera missing resolution");
+    const auto rv = to_double_list(res);
+    const int width = int(rv[0]), height = int(rv[1]);
+    if (width <= 0 || height <= 0) throw std::runtime_error("Resolution values must be positive");
+    cam.image_width = width;
+    cam.aspect_ratio = double(width) / double(height);
+    double vfov = cam.vfov;
+    if (n["vfov"].defined() || n["fov"].defined()) vfov = to_double(n["vfov"], to_double(n["fov"], vfov));
+    cam.vfov = std::clamp(vfov, 1.0, 179.0);
+    cam.focus_dist = to_double(n["focus_distance"], cam.focus_dist);
+    cam.defocus_angle = 0.0;                                          // aperture settings are ignored (:463)
+    cam.lookfrom = read_color(n["location"], cam.lookfrom);
+    cam.lookat = read_color(n["look_at"], cam.lookat);
+    cam.vup = read_color(n["up"], cam.vup);
+    cam.background = read_color(n["background"], cam.background);
+    cam.samples_per_pixel = to_int(n["samples_per_pixel"], cam.samples_per_pixel);
+    cam.max_depth = to_int(n["max_depth"], cam.max_depth);
+    const std::string output = to_string(n["output"]);
+    if (!output.empty()) cam.file_name = output;
+}
+
+}  // namespace
+
+scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_loader.h:480-523
+    const node root = yaml_lite::load_file(path);
+    if (!root.is_map()) throw std::runtime_error("Scene root must be a mapping");
+    scene_load_result result;
+    load_camera(root["camera"], result.cam);
+    const material_map mats = load_materials(root["materials"]);
+    const node* surfaces = &root["surfaces"];
+    if (!surfaces->defined()) surfaces = &root["scene"];
+    if (!surfaces->is_sequence()) throw std::runtime_error("Scene/surfaces field missing or not a sequence");
+    const std::filesystem::path dir = std::filesystem::path(path).parent_path();
+    sink out{result.world, result.lights};
+    for (const auto& mesh : surfaces->seq) {
+        if (!mesh.is_map()) throw std::runtime_error("Scene entries must be mappings");
+        const std::string type = to_string(mesh["type"]);
+        if (type.empty()) throw std::runtime_error("Mesh missing type field");
+        if (type == "TriMesh") load_tri_mesh(mesh, out);
+        else if (type == "Sphere") load_sphere(mesh, out);
+        else if (type == "mesh") load_indexed_mesh(mesh, out, mats);
+        else if (type == "object") load_object(mesh, dir, out, mats);
+        else std::cerr << "Unknown mesh type: " << type << "\n";
+    }
+    std::cout << "Triangles: " << result.world.size() << "\n";
+    return result;
+}
+
+void flatten_triangles(const std::vector<triangle>& tris, std::vector<double>& verts, std::vector<uint32_t>& mat_id,
+                       std::vector<bdpt_material>& mats) {
+    verts.resize(tris.size() * 9);
+    mat_id.resize(tris.size());
+    mats.clear();
+    std::unordered_map<const material*, uint32_t> index;
+    for (size_t i = 0; i < tris.size(); ++i) {
+        const triangle& t = tris[i];
+        const point3* p[3] = {&t.v0, &t.v1, &t.v2};
+        for (int k = 0; k < 3; ++k) for (int c = 0; c < 3; ++c) verts[9 * i + 3 * k + c] = (*p[k])[c];
+        auto it = index.find(t.mat.get());
+        if (it == index.end()) {
+            bdpt_material m{};
+            m.type = uint32_t(t.mat->kind);
+            m.rgb[0] = t.mat->rgb.x(); m.rgb[1] = t.mat->rgb.y(); m.rgb[2] = t.mat->rgb.z();
+            m.param = t.mat->param;
+            it = index.emplace(t.mat.get(), uint32_t(mats.size())).first;
+            mats.push_back(m);
+        }
+        mat_id[i] = it->second;
+    }
+}

@@ -143,6 +143,18 @@ int bdpt_stats_reset(bdpt_ctx* ctx);
 int bdpt_last_device_ms(bdpt_ctx* ctx, double* ms);
 int bdpt_sync(bdpt_ctx* ctx);
 
+/* ---- scene files: the host front-end behind load_scene_from_yaml (scene_loader.h:480-523) and
+ * write_png (wpng.h:38-89), for callers that are not C++. Host only; errors via bdpt_host_last_error. */
+typedef struct bdpt_scene_file bdpt_scene_file;
+int  bdpt_scene_file_load(const char* yaml_path, bdpt_scene_file** out);
+void bdpt_scene_file_free(bdpt_scene_file* f);
+int  bdpt_scene_file_info(const bdpt_scene_file* f, uint64_t* n_tris, uint32_t* n_mats, uint64_t* n_lights,
+                          bdpt_camera* cam, char* output_name, uint64_t output_cap);
+/* copies the flattened soup: verts n_tris*9, mat_id n_tris, mats n_mats (any may be NULL) */
+int  bdpt_scene_file_copy(const bdpt_scene_file* f, double* verts, uint32_t* mat_id, bdpt_material* mats);
+int  bdpt_write_png(const char* path, const uint8_t* rgb, int width, int height);
+const char* bdpt_host_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif
