@@ -1,0 +1,372 @@
+#!/usr/bin/env python
+"""bench.py — the hot path's headline benchmark (BASELINE.json: "BDPT Msamples/s and BVH Mrays/s").
+
+Workload (config.workload): scenes/coffee_machine.yaml at 1920x1080, 256 spp (16x16 strata), max depth 16,
+stand-in geometry (the reference ships no OBJ assets).  One STEP = one pass of the whole
+wavefront pipeline (generate -> trace -> shade -> connect -> shadow -> film) over STRATA_PER_STEP strata of
+every pixel of the frame; consecutive steps render consecutive strata of the 256-spp frame, so no step
+repeats another's samples.  With N GPUs each rank renders its own strata (rank g takes stratum s*N+g:
+stratum sharding), per-GPU work fixed -> weak scaling; the rank films are summed with ONE NCCL
+reduce at the end of the timed region (one reduce per frame).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our CUDA path (libbdpt.so)
+  python bench.py --impl reference ...                          the reference's own CPU code (oracle/_ref)
+
+value  = samples of all ranks / device time of the K steps (inputs resident in HBM).
+e2e    = same metric through the host-facing call sequence: scene upload from host buffers (BVH build +
+         H2D), K steps, film read-back (D2H) — everything a camera::render call pays.
+"""
+import argparse
+import ctypes
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WIDTH, HEIGHT, SPP, DEPTH = 1920, 1080, 256, 16
+STRATA_PER_STEP = 4
+SCENE = os.path.join(ROOT, "scenes", "coffee_machine.yaml")
+MICRO_SCENE = os.path.join(ROOT, "scenes", "glass-of-water.yaml")
+MICRO_RAYS = 1 << 24
+
+
+def ensure_scenes():
+    from tools import make_standin_scenes as ms
+    ms.generate(detail=2, quiet=True)
+
+
+def measured_peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [x.strip() for x in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": int(self.rows[0][1]) if self.rows and self.rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_reference(spp, steps, warmup, procs=None):
+    """The reference CPU renderer on this box's host cores: `procs` independent single-thread processes,
+    each rendering one full-width row of the workload per step at `spp` samples per pixel."""
+    ensure_scenes()
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-s"], stdout=subprocess.DEVNULL)
+    procs = procs or host_cores()
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "cpu_ref_worker.py"), SCENE, str(WIDTH), str(HEIGHT), str(spp), str(DEPTH)]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    ps = [subprocess.Popen(cmd + [str(int((p + 0.5) * HEIGHT / procs)), str(steps), str(warmup)], stdout=subprocess.PIPE,
+                           stderr=subprocess.DEVNULL, text=True, env=env) for p in range(procs)]
+    outs = []
+    for p in ps:
+        out, _ = p.communicate()
+        lines = [l for l in out.splitlines() if l.startswith("{")]
+        if p.returncode == 0 and lines:
+            outs.append(json.loads(lines[-1]))
+    if not outs:
+        raise RuntimeError("CPU reference workers failed")
+    samples = sum(o["samples_per_step"] * len(o["step_s"]) for o in outs)
+    wall = max(sum(o["step_s"]) for o in outs)
+    rays = sum(o["rays"] for o in outs)
+    all_samples = sum(o["samples_per_step"] * o["all_steps"] for o in outs)
+    return {"value": samples / wall / 1e6, "unit": "Msamples/s", "cores": len(outs), "kind": outs[0]["kind"],
+            "sample": "%d independent single-thread processes x %d step(s) x 1 row of %dx%d at %d spp, depth %d "
+                      "(%d samples timed); reference headers compiled -O2, BVH build excluded"
+                      % (len(outs), steps, WIDTH, HEIGHT, spp, DEPTH, samples),
+            "ms_per_step": 1e3 * wall / max(1, steps), "closest_rays_per_sample": rays / max(1, all_samples),
+            "node_visits_per_ray": sum(o["node_visits"] for o in outs) / max(1, rays),
+            "tri_tests_per_ray": sum(o["tri_tests"] for o in outs) / max(1, rays)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    # one row at 256 spp costs ~10-20 s per process; shrink the per-step sample when many steps are asked for
+    spp = 256 if (args.steps + args.warmup) <= 4 else (64 if (args.steps + args.warmup) <= 16 else 16)
+    r = cpu_reference(spp, args.steps, args.warmup)
+    line = {"impl": "reference", "metric": "BDPT Msamples/s", "value": r["value"], "unit": "Msamples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(),
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "reference_counters": {k: r[k] for k in ("closest_rays_per_sample", "node_visits_per_ray", "tri_tests_per_ray")}}
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config():
+    return {"workload": "scenes/coffee_machine.yaml %dx%d, %d spp (16x16 strata), max depth %d, stand-in geometry "
+                        "(reference ships no OBJ assets); step = %d strata of every pixel"
+                        % (WIDTH, HEIGHT, SPP, DEPTH, STRATA_PER_STEP),
+            "samples_per_step_per_gpu": WIDTH * HEIGHT * STRATA_PER_STEP,
+            "l2": "working set per step (wavefront state ~4.7 GB) exceeds the 126 MB L2; no flush needed",
+            "parallelism": "stratum sharding, one NCCL film reduce per frame"}
+
+
+class CudaArray:
+    """__cuda_array_interface__ view of a device pointer owned by libbdpt (the film), so torch.distributed
+    can reduce it in place over NCCL."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 3}
+
+
+def run_ours(args):
+    import torch
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        ensure_scenes()
+    if dist:
+        dist.barrier()
+    pkg = importlib.import_module("bidirectional-path-tracer_b200")
+    sf = pkg.SceneFile(SCENE)
+    cam = sf.camera_with(WIDTH, HEIGHT, SPP, DEPTH)
+    bvh = pkg.BVH_REFERENCE if args.bvh == "ref" else pkg.BVH_FAST
+    ctx = pkg.Context(local)
+    K, Wm = args.steps, args.warmup
+    n2 = 256
+
+    def strata_of(step):          # this rank's strata for a step; wraps after the 256-spp frame is complete
+        base = ((step * world + rank) * STRATA_PER_STEP) % n2
+        return (base, base + STRATA_PER_STEP, 1)
+
+    def sync_all():
+        ctx.sync()
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---------------- device-resident measurement
+    ctx.upload(sf.verts, sf.mat_id, sf.materials)
+    ctx.film_clear(WIDTH, HEIGHT)
+    fptr, fn = ctx.film_device_ptr()
+    film_t = torch.as_tensor(CudaArray(fptr, fn), device=torch.device("cuda", local))
+    for s in range(Wm):
+        ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(s), clear=False, height=HEIGHT)
+    if dist:
+        dist.reduce(film_t, dst=0)   # warm NCCL up too
+    ctx.film_clear(WIDTH, HEIGHT)
+    ctx.stats_reset()
+    sampler = ClockSampler(local)
+    sync_all()
+    sampler.start()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for s in range(K):
+        ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT)
+        dev_ms += ctx.last_device_ms()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    red_ms = 0.0
+    if dist:
+        ev0.record()
+        dist.reduce(film_t, dst=0)   # the one film reduce per frame
+        ev1.record()
+        torch.cuda.synchronize()
+        red_ms = ev0.elapsed_time(ev1)
+    sync_all()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+    st = ctx.stats()
+    kt = ctx.kernel_times()
+    step_ms = torch.tensor([dev_ms + red_ms, wall_ms], dtype=torch.float64, device="cuda")
+    if dist:
+        dist.all_reduce(step_ms, op=dist.ReduceOp.MAX)
+    total_ms, wall_ms = float(step_ms[0]), float(step_ms[1])
+    samples = WIDTH * HEIGHT * STRATA_PER_STEP * K * world
+    value = samples / (total_ms * 1e3)
+
+    # ---------------- end-to-end through host buffers: upload (BVH build + H2D) + K steps + film D2H
+    ctx2 = pkg.Context(local)
+    sync_all()
+    t0 = time.perf_counter()
+    ctx2.upload(sf.verts, sf.mat_id, sf.materials)
+    ctx2.film_clear(WIDTH, HEIGHT)
+    for s in range(K):
+        ctx2.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT)
+    if dist:
+        p2, n2_ = ctx2.film_device_ptr()
+        dist.reduce(torch.as_tensor(CudaArray(p2, n2_), device=torch.device("cuda", local)), dst=0)
+    film_host = ctx2.film()
+    sync_all()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = samples / float(e2e_s[0]) / 1e6
+    h2d = sf.verts.nbytes + sf.mat_id.nbytes
+    d2h = film_host.nbytes
+    ctx2.close()
+
+    extra = {}
+    if rank == 0:
+        extra = rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K)
+    ctx.close()
+    if rank == 0:
+        line = {"metric": "BDPT Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": Wm,
+                "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic", "config": dict(workload_config(), bvh=args.bvh),
+                "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
+                        "note": "scene upload from host buffers (host BVH build + H2D) + K steps + film read-back"},
+                "gpu_launches": st["kernel_launches"], "clocks": clocks, "wall_ms_per_step": wall_ms / K,
+                "film_reduce_ms": red_ms,
+                "mrays_per_s": (st["rays_closest"] + st["rays_shadow"]) * world / (total_ms * 1e3),
+                "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow": st["rays_shadow"] / st["samples"]},
+                "film_checksum": float(np.nan_to_num(film_host).sum())}
+        line.update(extra)
+        print(json.dumps(line))
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
+    """roofline of the dominant kernel class, the 16M-ray BVH microbench (config 2) and the CPU baseline."""
+    out = {}
+    peak, peak_src = measured_peaks()
+    # algorithmic bytes per ray: SURVEY 8(d)  A_ray = 32 (ray in) + 16 (hit out) + 32 x nodes + 48 x triangles,
+    # nodes / triangles counted by the SAME kernels in a stats pass over one step's strata (untimed)
+    ctx.stats_reset()
+    ctx.render(cam, seed=args.seed, bvh=bvh, strata=(0, STRATA_PER_STEP, 1), clear=True, height=HEIGHT, stats=True)
+    s2 = ctx.stats()
+    per = {}
+    for kind, rays, nodes, tris in (("trace", "rays_closest", "nodes_closest", "tris_closest"),
+                                    ("shadow", "rays_shadow", "nodes_shadow", "tris_shadow")):
+        r = max(1, s2[rays])
+        per[kind] = {"nodes_per_ray": s2[nodes] / r, "tris_per_ray": s2[tris] / r,
+                     "bytes_per_ray": 48.0 + 32.0 * s2[nodes] / r + 48.0 * s2[tris] / r}
+    dom = "trace" if kt["trace"][0] >= kt["shadow"][0] else "shadow"
+    rays_dom = st["rays_closest"] if dom == "trace" else st["rays_shadow"]
+    ms_dom, launches_dom = kt[dom]
+    achieved = rays_dom * per[dom]["bytes_per_ray"] / (ms_dom * 1e-3) / 1e9 if ms_dom > 0 else 0.0
+    total_kernel_ms = sum(v[0] for v in kt.values())
+    out["roofline"] = {"bound": "hbm", "kernel": "k_trace_paths" if dom == "trace" else "k_shadow", "achieved": achieved,
+                       "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                       "avg_launch_ms": ms_dom / max(1, launches_dom), "launches": launches_dom,
+                       "algorithmic_bytes_per_ray": per[dom]["bytes_per_ray"],
+                       "algorithmic_bytes_per_launch": rays_dom * per[dom]["bytes_per_ray"] / max(1, launches_dom),
+                       "mrays_per_s_in_kernel": rays_dom / (ms_dom * 1e3) if ms_dom > 0 else 0.0,
+                       "share_of_step": ms_dom / total_kernel_ms if total_kernel_ms else None}
+    out["kernel_ms"] = {k: {"ms": v[0], "launches": v[1]} for k, v in kt.items()}
+    out["traversal_work"] = per
+    if not args.skip_micro:
+        out["bvh_microbench"] = bvh_microbench(args, pkg, bvh)
+    if not args.skip_cpu:
+        try:
+            r = cpu_reference(64, 1, 0)
+            out["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as e:  # the GPU numbers stand on their own
+            out["cpu_baseline"] = {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "failed: %s" % e}
+    return out
+
+
+def bvh_microbench(args, pkg, bvh):
+    """BASELINE.json config 2: 16,777,216 fixed-seed rays (camera / incoherent / shadow-segment thirds, fp32-
+    representable) against the glass-of-water BVH. Device-resident Mrays/s and host-buffer (e2e) Mrays/s."""
+    from tools import testscenes as ts
+    sf = pkg.SceneFile(MICRO_SCENE)
+    cam = {"lookfrom": tuple(sf.camera.lookfrom), "lookat": tuple(sf.camera.lookat), "vfov": sf.camera.vfov}
+    rays = ts.ray_batch(sf.verts, MICRO_RAYS, seed=0x5EED0001, cam=cam, width=512, height=512)
+    n = len(rays)
+    with pkg.Context(int(os.environ.get("LOCAL_RANK", "0"))) as c:
+        c.upload(sf.verts, sf.mat_id, sf.materials)
+        res = {"rays": n, "triangles": len(sf.verts), "scene": "glass-of-water (stand-in geometry)"}
+        for name, flavour in (("fast", pkg.BVH_FAST), ("reference_topology", pkg.BVH_REFERENCE)):
+            best_ms, best_wall = 1e30, 1e30
+            for rep in range(3):
+                t0 = time.perf_counter()
+                h = c.trace(rays, bvh=flavour)
+                best_wall = min(best_wall, time.perf_counter() - t0)
+                best_ms = min(best_ms, c.last_device_ms())
+            c.stats_reset()
+            c.trace(rays[: 1 << 20], bvh=flavour, stats=True)
+            s = c.stats()
+            res[name] = {"mrays_per_s": n / best_ms / 1e3, "e2e_mrays_per_s": n / best_wall / 1e6, "device_ms": best_ms,
+                         "nodes_per_ray": s["node_visits"] / (1 << 20), "tris_per_ray": s["tri_tests"] / (1 << 20),
+                         "hit_fraction": float((h["prim"] != 0xFFFFFFFF).mean()),
+                         "prim_checksum": int(h["prim"].astype(np.uint64).sum())}
+        res["prim_ids_equal_between_flavours"] = res["fast"]["prim_checksum"] == res["reference_topology"]["prim_checksum"]
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bvh", default="fast", choices=["fast", "ref"],
+                    help="traversal flavour; both return the reference's hits (tests/test_trace_gpu.py)")
+    ap.add_argument("--seed", type=int, default=20261104)
+    ap.add_argument("--skip-micro", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    args.steps = max(1, args.steps)
+    args.warmup = max(3, args.warmup) if args.impl == "ours" else max(0, args.warmup)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args)
+    if args.gpus != world:
+        if world == 1 and args.gpus > 1:   # launched without torchrun: re-exec under it
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+                   "--master-addr", "127.0.0.1", "--master-port", "29531", os.path.abspath(__file__)] + sys.argv[1:]
+            return subprocess.call(cmd)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

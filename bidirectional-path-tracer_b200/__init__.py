@@ -26,7 +26,7 @@ EXPORTS = [
     "bdpt_ctx_create", "bdpt_ctx_destroy", "bdpt_last_error", "bdpt_scene_upload", "bdpt_bvh_info",
     "bdpt_bvh_leaf_order", "bdpt_host_bvh_build", "bdpt_trace", "bdpt_visible", "bdpt_render",
     "bdpt_film_clear", "bdpt_film_device_ptr", "bdpt_film_download", "bdpt_film_to_rgb8", "bdpt_stats",
-    "bdpt_stats_reset", "bdpt_last_device_ms", "bdpt_sync",
+    "bdpt_stats_reset", "bdpt_last_device_ms", "bdpt_sync", "bdpt_kernel_times",
     "bdpt_scene_file_load", "bdpt_scene_file_free", "bdpt_scene_file_info", "bdpt_scene_file_copy",
     "bdpt_write_png", "bdpt_host_last_error",
 ]
@@ -46,12 +46,17 @@ class Camera(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("stratum_begin", C.c_int32), ("stratum_end", C.c_int32),
                 ("stratum_step", C.c_int32), ("bvh", C.c_int32), ("row_begin", C.c_int32),
-                ("row_end", C.c_int32), ("batch_samples", C.c_int64)]
+                ("row_end", C.c_int32), ("batch_samples", C.c_int64), ("flags", C.c_int32), ("pad", C.c_int32)]
 
 
 class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_closest", "rays_shadow", "node_visits", "tri_tests", "samples",
-                                          "kernel_launches", "camera_vertices", "light_vertices")]
+                                          "kernel_launches", "camera_vertices", "light_vertices", "nodes_closest",
+                                          "tris_closest", "nodes_shadow", "tris_shadow")]
+
+
+RENDER_STATS = 1
+KERNEL_CLASSES = ("generate", "trace", "shade", "connect", "shadow")
 
 
 class BdptError(RuntimeError):
@@ -95,6 +100,7 @@ def lib():
         L.bdpt_stats_reset.argtypes = [C.c_void_p]
         L.bdpt_last_device_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.bdpt_sync.argtypes = [C.c_void_p]
+        L.bdpt_kernel_times.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.bdpt_scene_file_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
         L.bdpt_scene_file_free.argtypes = [C.c_void_p]
         L.bdpt_scene_file_free.restype = None
@@ -270,7 +276,7 @@ class Context:
         self.film_shape = (int(height), int(width), 3)
 
     def render(self, cam, seed=0, bvh=BVH_REFERENCE, strata=(0, 0, 1), rows=(0, 0), batch_samples=0, clear=True,
-               height=None):
+               height=None, stats=False):
         """camera::render's sample loop; returns nothing — read the film with film()."""
         W = cam.image_width
         H = height if height is not None else max(1, int(W / cam.aspect_ratio))
@@ -282,6 +288,7 @@ class Context:
         o.bvh = bvh
         o.row_begin, o.row_end = rows
         o.batch_samples = batch_samples
+        o.flags = RENDER_STATS if stats else 0
         self._chk(lib().bdpt_render(self._h, C.byref(cam), C.byref(o)), "bdpt_render")
 
     def film(self):
@@ -306,6 +313,13 @@ class Context:
 
     def stats_reset(self):
         self._chk(lib().bdpt_stats_reset(self._h), "bdpt_stats_reset")
+
+    def kernel_times(self):
+        """{class: (ms, launches)} of bdpt_render's kernels since the last stats_reset (CUDA events on the ctx stream)."""
+        ms = (C.c_double * 5)()
+        n = (C.c_uint64 * 5)()
+        self._chk(lib().bdpt_kernel_times(self._h, ms, n), "bdpt_kernel_times")
+        return {k: (ms[i], int(n[i])) for i, k in enumerate(KERNEL_CLASSES)}
 
     def last_device_ms(self):
         ms = C.c_double(0)

@@ -392,6 +392,8 @@ int bdpt_stats(bdpt_ctx* ctx, bdpt_stats_t* out) {
     out->rays_closest = h[ST_RAYS_CLOSEST]; out->rays_shadow = h[ST_RAYS_SHADOW];
     out->camera_vertices = h[ST_CAM_VERTS]; out->light_vertices = h[ST_LIGHT_VERTS];
     out->samples = ctx->samples; out->kernel_launches = ctx->launches;
+    out->nodes_closest = h[ST_NODE_CLOSEST]; out->tris_closest = h[ST_TRI_CLOSEST];
+    out->nodes_shadow = h[ST_NODE_SHADOW]; out->tris_shadow = h[ST_TRI_SHADOW];
     return BDPT_OK;
 }
 
@@ -400,12 +402,19 @@ int bdpt_stats_reset(bdpt_ctx* ctx) {
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
     BDPT_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, 16 * sizeof(unsigned long long), ctx->stream));
     ctx->samples = 0; ctx->launches = 0;
+    for (int i = 0; i < 8; ++i) { ctx->kernel_ms[i] = 0.0; ctx->kernel_launches[i] = 0; }
     return BDPT_OK;
 }
 
 int bdpt_last_device_ms(bdpt_ctx* ctx, double* ms) {
     if (!ctx || !ms) return BDPT_ERR_ARG;
     *ms = ctx->last_ms;
+    return BDPT_OK;
+}
+
+int bdpt_kernel_times(bdpt_ctx* ctx, double* ms, uint64_t* launches) {
+    if (!ctx || !ms) return BDPT_ERR_ARG;
+    for (int i = 0; i < KT_COUNT; ++i) { ms[i] = ctx->kernel_ms[i]; if (launches) launches[i] = ctx->kernel_launches[i]; }
     return BDPT_OK;
 }
 

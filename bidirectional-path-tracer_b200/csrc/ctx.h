@@ -30,6 +30,9 @@ struct bdpt_ctx {
 
     // wavefront workspace (render.cu)
     void* wf = nullptr;
+    void* timers = nullptr;
+    double kernel_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};       // per kernel class, KT_*
+    uint64_t kernel_launches[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 namespace bdpt {
@@ -44,7 +47,10 @@ namespace bdpt {
     } while (0)
 
 // device counter slots
-enum { ST_NODE = 0, ST_TRI = 1, ST_RAYS_CLOSEST = 2, ST_RAYS_SHADOW = 3, ST_CAM_VERTS = 4, ST_LIGHT_VERTS = 5 };
+enum { ST_NODE = 0, ST_TRI = 1, ST_RAYS_CLOSEST = 2, ST_RAYS_SHADOW = 3, ST_CAM_VERTS = 4, ST_LIGHT_VERTS = 5,
+       ST_NODE_CLOSEST = 6, ST_TRI_CLOSEST = 7, ST_NODE_SHADOW = 8, ST_TRI_SHADOW = 9 };
+// kernel classes of the wavefront (bdpt_kernel_times)
+enum { KT_GENERATE = 0, KT_TRACE = 1, KT_SHADE = 2, KT_CONNECT = 3, KT_SHADOW = 4, KT_COUNT = 5 };
 
 int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts);
 void render_free(bdpt_ctx* ctx);

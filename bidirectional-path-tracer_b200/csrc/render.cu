@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 #include "ctx.h"
 #include "render_math.cuh"
@@ -178,9 +179,10 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
 // world.hit over the live subpaths (camera.h:336: interval [0.001, inf)); a miss ends the subpath and,
 // for a camera subpath, adds throughput * background (camera.h:337-340).  Hits are binned by material
 // class so each shading kernel runs divergence-free over its own queue.
-template <int BVH>
+template <int BVH, bool STATS>
 __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
-                                                       const uint32_t* __restrict__ n_ptr, int64_t L0, double* film) {
+                                                       const uint32_t* __restrict__ n_ptr, int64_t L0, double* film,
+                                                       unsigned long long* stats) {
     __shared__ int32_t s_stack[kRefStackLevels * kBlock];
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
     const uint32_t n = *n_ptr;
@@ -195,8 +197,10 @@ __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, W
         r.tmax = __longlong_as_double(0x7FF0000000000000LL);
         HitD h;
         bool found;
-        if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<false, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
-        else found = traverse_fast<false, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
+        TravStats ts{0, 0};
+        if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<false, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
+        else found = traverse_fast<false, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
+        if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); }
         if (found) {
             w.hit_prim[pid] = h.prim;
             w.hit_t[pid] = h.t;
@@ -476,8 +480,8 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
 // ------------------------------------------------------------------ K4
 // visible() (camera.h:437: world.hit over [0.001, dist-0.001], inclusive ends — SURVEY F4) and the
 // film accumulation of every unoccluded connection.
-template <int BVH>
-__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* film) {
+template <int BVH, bool STATS>
+__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* film, unsigned long long* stats) {
     __shared__ int32_t s_stack[kRefStackLevels * kBlock];
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
     if (idx >= w.counters[C_SHADOW]) return;
@@ -488,8 +492,10 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* f
     r.tmax = w.s_tmax[idx];
     HitD h;
     bool found;
-    if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<true, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
-    else found = traverse_fast<true, false>(sc, r, h, s_stack + threadIdx.x, kBlock, nullptr);
+    TravStats ts{0, 0};
+    if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<true, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
+    else found = traverse_fast<true, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
+    if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
     if (!found) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
 }
 
@@ -554,11 +560,46 @@ Frame make_frame(const bdpt_camera& c, int H) {
     return f;
 }
 
+// Per-kernel-class device time: a CUDA event pair around every launch group on the launching stream,
+// read back whenever the stream is known to be idle.  (bench.py's roofline uses the trace/shadow classes.)
+struct KernelTimers {
+    struct Pair { cudaEvent_t a, b; int cls; };
+    std::vector<Pair> pool;
+    size_t used = 0;
+    int open = -1;
+    void begin(int cls, cudaStream_t st) {
+        if (used == pool.size()) {
+            Pair p{};
+            cudaEventCreate(&p.a); cudaEventCreate(&p.b);
+            pool.push_back(p);
+        }
+        pool[used].cls = cls;
+        cudaEventRecord(pool[used].a, st);
+        open = int(used);
+    }
+    void end(int, cudaStream_t st) { cudaEventRecord(pool[size_t(open)].b, st); ++used; }
+    void collect(double* ms, uint64_t* launches) {
+        for (size_t i = 0; i < used; ++i) {
+            float t = 0.f;
+            if (cudaEventSynchronize(pool[i].b) == cudaSuccess && cudaEventElapsedTime(&t, pool[i].a, pool[i].b) == cudaSuccess) {
+                ms[pool[i].cls] += t; launches[pool[i].cls] += 1;
+            }
+        }
+        used = 0;
+    }
+    ~KernelTimers() { for (auto& p : pool) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); } }
+};
+KernelTimers* ctx_timers(bdpt_ctx* ctx) {
+    if (!ctx->timers) ctx->timers = new KernelTimers();
+    return static_cast<KernelTimers*>(ctx->timers);
+}
+
 inline unsigned grid_for(int64_t n, int block) { return unsigned(std::max<int64_t>(1, (n + block - 1) / block)); }
 
 }  // namespace
 
 void render_free(bdpt_ctx* ctx) {
+    if (ctx->timers) { delete static_cast<KernelTimers*>(ctx->timers); ctx->timers = nullptr; }
     if (!ctx->wf) return;
     WF* w = static_cast<WF*>(ctx->wf);
     if (w->base) cudaFree(w->base);
@@ -624,13 +665,17 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     SceneView sc = ctx->view;
     cudaStream_t st = ctx->stream;
     uint32_t hc[C_COUNT];
+    const bool want_stats = (o.flags & BDPT_RENDER_STATS) != 0;
+    KernelTimers& tm = *ctx_timers(ctx);
     uint64_t rays_closest = 0, rays_shadow = 0, cam_verts = 0, light_verts = 0;
 
     BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
     for (int64_t L0 = 0; L0 < total; L0 += Bcap) {
         const int64_t nb = std::min<int64_t>(Bcap, total - L0);
         BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters, 0, C_COUNT * sizeof(uint32_t), st));
+        tm.begin(KT_GENERATE, st);
         k_generate<<<grid_for(nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb);
+        tm.end(KT_GENERATE, st);
         ctx->launches += 1;
         BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
         BDPT_CUDA(ctx, cudaStreamSynchronize(st));
@@ -642,14 +687,18 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_ACTIVE0 + nxt, 0, sizeof(uint32_t), st));
             BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_MAT0, 0, 4 * sizeof(uint32_t), st));
             const unsigned g = grid_for(n_active, kBlock);
-            if (o.bvh == BDPT_BVH_REFERENCE)
-                k_trace_paths<BDPT_BVH_REFERENCE><<<g, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, ctx->film);
-            else
-                k_trace_paths<BDPT_BVH_FAST><<<g, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, ctx->film);
+            tm.begin(KT_TRACE, st);
+#define BDPT_TP(B, S) k_trace_paths<B, S><<<g, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, ctx->film, ctx->d_stats)
+            if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
+            else { if (want_stats) BDPT_TP(BDPT_BVH_FAST, true); else BDPT_TP(BDPT_BVH_FAST, false); }
+#undef BDPT_TP
+            tm.end(KT_TRACE, st);
+            tm.begin(KT_SHADE, st);
             k_shade_light<<<g, kBlock, 0, st>>>(sc, f, wf, L0, ctx->film);
             k_shade_lambert<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
             k_shade_metal<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
             k_shade_dielectric<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
+            tm.end(KT_SHADE, st);
             ctx->launches += 5;
             rays_closest += n_active;
             BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -669,21 +718,28 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             for (int k0 = 0; k0 < max_nc; k0 += slots_per_round) {
                 const int k1 = std::min(max_nc, k0 + slots_per_round);
                 BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_SHADOW, 0, sizeof(uint32_t), st));
+                tm.begin(KT_CONNECT, st);
                 k_connect<<<grid_for(int64_t(k1 - k0) * nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb, k0, k1);
+                tm.end(KT_CONNECT, st);
                 BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
                 BDPT_CUDA(ctx, cudaStreamSynchronize(st));
                 ctx->launches += 1;
                 if (hc[C_OVERFLOW]) { ctx->err = "shadow queue overflow"; return BDPT_ERR_STATE; }
                 const uint32_t ns = hc[C_SHADOW];
                 if (ns) {
-                    if (o.bvh == BDPT_BVH_REFERENCE) k_shadow<BDPT_BVH_REFERENCE><<<grid_for(ns, kBlock), kBlock, 0, st>>>(sc, wf, ctx->film);
-                    else k_shadow<BDPT_BVH_FAST><<<grid_for(ns, kBlock), kBlock, 0, st>>>(sc, wf, ctx->film);
+                    tm.begin(KT_SHADOW, st);
+#define BDPT_SH(B, S) k_shadow<B, S><<<grid_for(ns, kBlock), kBlock, 0, st>>>(sc, wf, ctx->film, ctx->d_stats)
+                    if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_SH(BDPT_BVH_REFERENCE, true); else BDPT_SH(BDPT_BVH_REFERENCE, false); }
+                    else { if (want_stats) BDPT_SH(BDPT_BVH_FAST, true); else BDPT_SH(BDPT_BVH_FAST, false); }
+#undef BDPT_SH
+                    tm.end(KT_SHADOW, st);
                     ctx->launches += 1;
                     rays_shadow += ns;
                 }
             }
         }
         ctx->samples += uint64_t(nb);
+        tm.collect(ctx->kernel_ms, ctx->kernel_launches);   // the stream is idle here (last sync above or below)
     }
     BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
     BDPT_CUDA(ctx, cudaStreamSynchronize(st));
@@ -691,6 +747,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_ms = ms;
+    tm.collect(ctx->kernel_ms, ctx->kernel_launches);
     // host-side tallies go into the device counter block so bdpt_stats reads one place
     unsigned long long add[4] = {rays_closest, rays_shadow, cam_verts, light_verts};
     unsigned long long cur_stats[16];

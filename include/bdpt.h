@@ -86,7 +86,13 @@ typedef struct {
     uint64_t kernel_launches;/* our kernels launched since ctx creation / last reset */
     uint64_t camera_vertices;
     uint64_t light_vertices;
+    /* bdpt_render with BDPT_RENDER_STATS: traversal work split by ray kind */
+    uint64_t nodes_closest, tris_closest, nodes_shadow, tris_shadow;
 } bdpt_stats_t;
+
+/* Device time per kernel class of bdpt_render since the last bdpt_stats_reset, from CUDA event pairs on
+ * the context's stream around each launch (ms[i], launches[i]; i = BDPT_KT_*). */
+enum { BDPT_KT_GENERATE = 0, BDPT_KT_TRACE = 1, BDPT_KT_SHADE = 2, BDPT_KT_CONNECT = 3, BDPT_KT_SHADOW = 4, BDPT_KT_COUNT = 5 };
 
 typedef struct {
     uint64_t seed;
@@ -97,7 +103,10 @@ typedef struct {
     int32_t  row_begin;      /* rows [row_begin,row_end) ; row_end<=0 means image height */
     int32_t  row_end;
     int64_t  batch_samples;  /* wavefront size; <=0 picks a default */
+    int32_t  flags;          /* BDPT_RENDER_* */
+    int32_t  pad;
 } bdpt_render_opts;
+enum { BDPT_RENDER_STATS = 1 /* count node visits / triangle tests of the traversal kernels (slower) */ };
 
 int  bdpt_ctx_create(int device, bdpt_ctx** out);
 void bdpt_ctx_destroy(bdpt_ctx* ctx);
@@ -142,6 +151,7 @@ int bdpt_stats_reset(bdpt_ctx* ctx);
  * device work, excluding host<->device copies. */
 int bdpt_last_device_ms(bdpt_ctx* ctx, double* ms);
 int bdpt_sync(bdpt_ctx* ctx);
+int bdpt_kernel_times(bdpt_ctx* ctx, double* ms /* BDPT_KT_COUNT */, uint64_t* launches /* BDPT_KT_COUNT */);
 
 /* ---- scene files: the host front-end behind load_scene_from_yaml (scene_loader.h:480-523) and
  * write_png (wpng.h:38-89), for callers that are not C++. Host only; errors via bdpt_host_last_error. */

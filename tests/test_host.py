@@ -28,7 +28,8 @@ def test_library_exports_every_declared_symbol(bdpt):
 def test_struct_layouts_match_header(bdpt):
     assert ctypes.sizeof(bdpt.Material) == 40
     assert ctypes.sizeof(bdpt.Camera) == 144
-    assert ctypes.sizeof(bdpt.RenderOpts) == 40
+    assert ctypes.sizeof(bdpt.RenderOpts) == 48
+    assert ctypes.sizeof(bdpt.Stats) == 96
     assert bdpt.RAY_DTYPE.itemsize == 64 and bdpt.HIT_DTYPE.itemsize == 32
 
 
