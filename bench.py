@@ -127,7 +127,8 @@ def run_reference(args):
     if rank != 0:
         return 0
     # one row at 256 spp costs ~10-20 s per process; shrink the per-step sample when many steps are asked for
-    spp = 256 if (args.steps + args.warmup) <= 4 else (64 if (args.steps + args.warmup) <= 16 else 16)
+    n_steps = args.steps + args.warmup
+    spp = 256 if n_steps <= 2 else (64 if n_steps <= 6 else 16)   # ~75 s / ~19 s / ~5 s per step on 8 cores
     r = cpu_reference(spp, args.steps, args.warmup)
     line = {"impl": "reference", "metric": "BDPT Msamples/s", "value": r["value"], "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
