@@ -290,6 +290,15 @@ def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
         r = max(1, s2[rays])
         per[kind] = {"nodes_per_ray": s2[nodes] / r, "tris_per_ray": s2[tris] / r,
                      "bytes_per_ray": 48.0 + 32.0 * s2[nodes] / r + 48.0 * s2[tris] / r}
+    # per-kernel durations: CUDA-event pairs around every launch, in a pass with ONE wavefront in flight
+    # (streams=1) so that a launch's duration is its own and not its share of a GPU it co-runs on; the
+    # timed region above keeps several wavefronts in flight and is faster than the sum of these
+    ctx.stats_reset()
+    for s_ in range(2):
+        ctx.render(cam, seed=args.seed, bvh=bvh, strata=((s_ + 1) * STRATA_PER_STEP, (s_ + 2) * STRATA_PER_STEP, 1),
+                   clear=False, height=HEIGHT, streams=1)
+    st, kt = ctx.stats(), ctx.kernel_times()
+    out["serialized_pass"] = {"streams": 1, "steps": 2, "ms_per_step": sum(v[0] for v in kt.values()) / 2}
     dom = "trace" if kt["trace"][0] >= kt["shadow"][0] else "shadow"
     rays_dom = st["rays_closest"] if dom == "trace" else st["rays_shadow"]
     ms_dom, launches_dom = kt[dom]
@@ -301,7 +310,8 @@ def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
                        "algorithmic_bytes_per_ray": per[dom]["bytes_per_ray"],
                        "algorithmic_bytes_per_launch": rays_dom * per[dom]["bytes_per_ray"] / max(1, launches_dom),
                        "mrays_per_s_in_kernel": rays_dom / (ms_dom * 1e3) if ms_dom > 0 else 0.0,
-                       "share_of_step": ms_dom / total_kernel_ms if total_kernel_ms else None}
+                       "share_of_step": ms_dom / total_kernel_ms if total_kernel_ms else None,
+                       "timing": "CUDA events per launch on the launching stream, streams=1 pass"}
     out["kernel_ms"] = {k: {"ms": v[0], "launches": v[1]} for k, v in kt.items()}
     out["traversal_work"] = per
     if not args.skip_micro:

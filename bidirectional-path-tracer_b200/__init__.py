@@ -46,7 +46,7 @@ class Camera(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("stratum_begin", C.c_int32), ("stratum_end", C.c_int32),
                 ("stratum_step", C.c_int32), ("bvh", C.c_int32), ("row_begin", C.c_int32),
-                ("row_end", C.c_int32), ("batch_samples", C.c_int64), ("flags", C.c_int32), ("pad", C.c_int32)]
+                ("row_end", C.c_int32), ("batch_samples", C.c_int64), ("flags", C.c_int32), ("streams", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -276,7 +276,7 @@ class Context:
         self.film_shape = (int(height), int(width), 3)
 
     def render(self, cam, seed=0, bvh=BVH_REFERENCE, strata=(0, 0, 1), rows=(0, 0), batch_samples=0, clear=True,
-               height=None, stats=False):
+               height=None, stats=False, streams=0):
         """camera::render's sample loop; returns nothing — read the film with film()."""
         W = cam.image_width
         H = height if height is not None else max(1, int(W / cam.aspect_ratio))
@@ -289,6 +289,7 @@ class Context:
         o.row_begin, o.row_end = rows
         o.batch_samples = batch_samples
         o.flags = RENDER_STATS if stats else 0
+        o.streams = streams
         self._chk(lib().bdpt_render(self._h, C.byref(cam), C.byref(o)), "bdpt_render")
 
     def film(self):

@@ -38,7 +38,7 @@ void free_scene(bdpt_ctx* ctx) {
 template <int BVH, bool ANY, bool STATS>
 __global__ void __launch_bounds__(kTraceBlock) k_trace(SceneView sc, const bdpt_ray* __restrict__ rays, uint64_t n,
                                                       bdpt_hit* __restrict__ out, unsigned long long* stats) {
-    __shared__ int32_t s_stack[kRefStackLevels * kTraceBlock];
+    __shared__ StackEntry s_stack[kRefStackLevels * kTraceBlock];
     const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
     TravStats st{0, 0};
     if (i < n) {
@@ -50,9 +50,9 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(SceneView sc, const bdpt_
         h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS;
         bool found;
         if (BVH == BDPT_BVH_REFERENCE)
-            found = traverse_ref<ANY, STATS>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, &st);
+            found = traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_stack + threadIdx.x), 2 * kTraceBlock, &st);
         else
-            found = traverse_fast<ANY, STATS>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, &st);
+            found = traverse_fast<ANY, STATS, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, &st) == TR_HIT;
         double2* o = reinterpret_cast<double2*>(out + i);
         if (!found) { h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS; }
         o[0] = make_double2(h.t, h.u);
@@ -72,7 +72,7 @@ template <int BVH>
 __global__ void __launch_bounds__(kTraceBlock) k_visible(SceneView sc, const double* __restrict__ a,
                                                         const double* __restrict__ b, uint64_t n,
                                                         uint8_t* __restrict__ out) {
-    __shared__ int32_t s_stack[kRefStackLevels * kTraceBlock];
+    __shared__ StackEntry s_stack[kRefStackLevels * kTraceBlock];
     const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
     if (i >= n) return;
     D3 pa = mk(a[3 * i], a[3 * i + 1], a[3 * i + 2]), pb = mk(b[3 * i], b[3 * i + 1], b[3 * i + 2]);
@@ -88,9 +88,9 @@ __global__ void __launch_bounds__(kTraceBlock) k_visible(SceneView sc, const dou
             HitD h;
             bool found;
             if (BVH == BDPT_BVH_REFERENCE)
-                found = traverse_ref<true, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, nullptr);
+                found = traverse_ref<true, false>(sc, r, h, reinterpret_cast<int32_t*>(s_stack + threadIdx.x), 2 * kTraceBlock, nullptr);
             else
-                found = traverse_fast<true, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, nullptr);
+                found = traverse_fast<true, false, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, nullptr) == TR_HIT;
             vis = found ? 0 : 1;
         }
     }
@@ -184,6 +184,7 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     v.n_fast_nodes = uint32_t(h.fast_nodes.size());
     v.light_total_area = h.light_total_area;
     v.extent = h.extent;
+    v.center = mk(h.center[0], h.center[1], h.center[2]);
     BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->view = v;
     ctx->have_scene = true;

@@ -62,8 +62,9 @@ void build_fast_bvh(HostScene& s) {
     double ext = 0.0;
     for (int k = 0; k < 3; ++k) ext = std::max(ext, scene.hi[k] - scene.lo[k]);
     s.extent = ext;
+    for (int k = 0; k < 3; ++k) s.center[k] = 0.5 * (scene.lo[k] + scene.hi[k]);
     // outward padding: far above fp64 slab/triangle rounding noise, far below feature size
-    const double eps = std::max(ext, 1e-30) * (1.0 / 1048576.0);
+    const double eps = std::max(ext, 1e-30) * (1.0 / 65536.0);
 
     auto range_box = [&](uint32_t b, uint32_t e) {
         B3 r; r.reset();

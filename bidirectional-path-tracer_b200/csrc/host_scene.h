@@ -31,6 +31,7 @@ struct HostScene {
     std::vector<uint32_t> fast_prims;
     uint32_t fast_depth = 0;
     double extent = 0.0;               // largest side of the scene bounds
+    double center[3] = {0, 0, 0};
 
     // per-triangle fp64 bounds (triangle.h:31-38), unpadded: lo xyz, hi xyz
     std::vector<double> tri_box;

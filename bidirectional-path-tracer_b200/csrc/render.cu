@@ -14,6 +14,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "ctx.h"
@@ -29,7 +31,7 @@ constexpr uint32_t kLightFlag = 0x80000000u;
 
 // device counters (uint32 each)
 enum { C_ACTIVE0 = 0, C_ACTIVE1 = 1, C_MAT0 = 2 /* ..5 */, C_SHADOW = 6, C_MAXNC = 7, C_MAXNL = 8, C_SUMNC = 9,
-       C_SUMNL = 10, C_OVERFLOW = 11, C_COUNT = 16 };
+       C_SUMNL = 10, C_OVERFLOW = 11, C_PAIRS_LO = 12, C_PAIRS_HI = 13 /* 64-bit, 8-byte aligned */, C_EXACT = 14, C_EXACT_SHADOW = 15, C_COUNT = 16 };
 
 struct Frame {           // camera.h:148-197 derived values + this call's sample selection
     D3 center, pixel00, du, dv, background;
@@ -51,6 +53,7 @@ struct WF {              // wavefront workspace, all device pointers
     uint32_t *draws, *hit_prim;
     int32_t* remaining;
     uint32_t *q_active[2], *q_mat[4];
+    uint32_t *q_exact, *q_exact_s;   // rays deferred to the reference-exact kernels (path ids / shadow slots)
     uint32_t* counters;
     // vertex pools, index = slot * B + b
     double *cv_px, *cv_py, *cv_pz, *cv_fx, *cv_fy, *cv_fz;   // camera vertex: p, throughput * f (camera.h:471)
@@ -179,42 +182,91 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
 // world.hit over the live subpaths (camera.h:336: interval [0.001, inf)); a miss ends the subpath and,
 // for a camera subpath, adds throughput * background (camera.h:337-340).  Hits are binned by material
 // class so each shading kernel runs divergence-free over its own queue.
-template <int BVH, bool STATS>
-__global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
-                                                       const uint32_t* __restrict__ n_ptr, int64_t L0, double* film,
-                                                       unsigned long long* stats) {
-    __shared__ int32_t s_stack[kRefStackLevels * kBlock];
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
-    const uint32_t n = *n_ptr;
-    int cls = -1;
-    uint32_t pid = 0;
-    if (idx < n) {
-        pid = queue[idx];
-        RayD r;
-        r.o = mk(w.ox[pid], w.oy[pid], w.oz[pid]);
-        r.d = mk(w.dx[pid], w.dy[pid], w.dz[pid]);
-        r.tmin = 0.001;
-        r.tmax = __longlong_as_double(0x7FF0000000000000LL);
-        HitD h;
-        bool found;
-        TravStats ts{0, 0};
-        if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<false, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
-        else found = traverse_fast<false, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
-        if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); }
-        if (found) {
-            w.hit_prim[pid] = h.prim;
-            w.hit_t[pid] = h.t;
-            cls = int(sc.mats[__ldg(&sc.shade[h.prim].mat)].type);
-        } else if (pid < uint32_t(w.B)) {
-            const D3 T = mk(w.tx[pid], w.ty[pid], w.tz[pid]);
-            const D3 c = T * f.background;
-            if (c.x != 0.0 || c.y != 0.0 || c.z != 0.0) film_add(film, decode_sample(f, L0 + pid).pix, c);
-        }
+// result of one closest-hit query: record the hit and pick the material queue, or finish the subpath
+__device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, bool found,
+                                            const HitD& h, int64_t L0, double* film) {
+    if (found) {
+        w.hit_prim[pid] = h.prim;
+        w.hit_t[pid] = h.t;
+        return int(sc.mats[__ldg(&sc.shade[h.prim].mat)].type);
     }
+    if (pid < uint32_t(w.B)) {
+        const D3 T = mk(w.tx[pid], w.ty[pid], w.tz[pid]);
+        const D3 c = T * f.background;
+        if (c.x != 0.0 || c.y != 0.0 || c.z != 0.0) film_add(film, decode_sample(f, L0 + pid).pix, c);
+    }
+    return -1;
+}
+__device__ __forceinline__ RayD load_path_ray(const WF& w, uint32_t pid) {
+    RayD r;
+    r.o = mk(w.ox[pid], w.oy[pid], w.oz[pid]);
+    r.d = mk(w.dx[pid], w.dy[pid], w.dz[pid]);
+    r.tmin = 0.001;
+    r.tmax = __longlong_as_double(0x7FF0000000000000LL);
+    return r;
+}
+__device__ __forceinline__ void bin_by_material(const WF& w, int cls, uint32_t pid) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const uint32_t slot = warp_append(w.counters + C_MAT0 + k, cls == k);
         if (cls == k) w.q_mat[k][slot] = pid;
+    }
+}
+
+extern __shared__ StackEntry s_dyn_stack[];   // [levels][kBlock], sized at launch from the tree depths
+
+template <int BVH, bool STATS>
+__global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
+                                                       const uint32_t* __restrict__ n_ptr, int64_t L0, double* film,
+                                                       unsigned long long* stats) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    const uint32_t n = *n_ptr;
+    int cls = -1;
+    uint32_t pid = 0;
+    bool defer = false;
+    if (idx < n) {
+        pid = queue[idx];
+        const RayD r = load_path_ray(w, pid);
+        HitD h;
+        bool found;
+        TravStats ts{0, 0};
+        if (BVH == BDPT_BVH_REFERENCE) {
+            found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+        } else {
+            const int rc = traverse_fast<false, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts);
+            found = rc == TR_HIT;
+            defer = rc == TR_DEFER;
+        }
+        if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); }
+        if (!defer) cls = finish_trace(sc, f, w, pid, found, h, L0, film);
+    }
+    if (BVH != BDPT_BVH_REFERENCE) {   // rays that need the reference tree go to the exact kernel, compacted
+        const uint32_t slot = warp_append(w.counters + C_EXACT, defer);
+        if (defer) w.q_exact[slot] = pid;
+    }
+    bin_by_material(w, cls, pid);
+}
+
+// the deferred rays of k_trace_paths (ties, knife edges, zero direction components: traverse_fast.cuh),
+// through the reference-exact traversal; grid-stride over a device-side count
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock) k_trace_exact(SceneView sc, Frame f, WF w, int64_t L0, double* film,
+                                                       unsigned long long* stats) {
+    const uint32_t n = w.counters[C_EXACT];
+    for (uint32_t base = blockIdx.x * kBlock; base < n; base += gridDim.x * kBlock) {
+        const uint32_t idx = base + threadIdx.x;
+        int cls = -1;
+        uint32_t pid = 0;
+        if (idx < n) {
+            pid = w.q_exact[idx];
+            const RayD r = load_path_ray(w, pid);
+            HitD h;
+            TravStats ts{0, 0};
+            const bool found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); }
+            cls = finish_trace(sc, f, w, pid, found, h, L0, film);
+        }
+        bin_by_material(w, cls, pid);
     }
 }
 
@@ -394,7 +446,9 @@ __global__ void __launch_bounds__(256) k_counts(WF w, int64_t nb) {
     if (b < nb) { nc = w.ncam[b]; nl = w.nlight[b]; }
     const uint32_t mc = __reduce_max_sync(0xFFFFFFFFu, nc), ml = __reduce_max_sync(0xFFFFFFFFu, nl);
     const uint32_t sc_ = __reduce_add_sync(0xFFFFFFFFu, nc), sl = __reduce_add_sync(0xFFFFFFFFu, nl);
+    const uint32_t pairs = __reduce_add_sync(0xFFFFFFFFu, nc * nl);   // <= 32 * depth^2
     if ((threadIdx.x & 31) == 0) {
+        if (pairs) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_PAIRS_LO), (unsigned long long)pairs);
         if (mc) atomicMax(w.counters + C_MAXNC, mc);
         if (ml) atomicMax(w.counters + C_MAXNL, ml);
         if (sc_) atomicAdd(w.counters + C_SUMNC, sc_);
@@ -480,23 +534,52 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
 // ------------------------------------------------------------------ K4
 // visible() (camera.h:437: world.hit over [0.001, dist-0.001], inclusive ends — SURVEY F4) and the
 // film accumulation of every unoccluded connection.
-template <int BVH, bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* film, unsigned long long* stats) {
-    __shared__ int32_t s_stack[kRefStackLevels * kBlock];
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
-    if (idx >= w.counters[C_SHADOW]) return;
+__device__ __forceinline__ RayD load_shadow_ray(const WF& w, uint32_t idx) {
     RayD r;
     r.o = mk(w.s_ox[idx], w.s_oy[idx], w.s_oz[idx]);
     r.d = mk(w.s_dx[idx], w.s_dy[idx], w.s_dz[idx]);
     r.tmin = 0.001;
     r.tmax = w.s_tmax[idx];
-    HitD h;
-    bool found;
-    TravStats ts{0, 0};
-    if (BVH == BDPT_BVH_REFERENCE) found = traverse_ref<true, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
-    else found = traverse_fast<true, STATS>(sc, r, h, s_stack + threadIdx.x, kBlock, &ts);
-    if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
-    if (!found) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
+    return r;
+}
+
+template <int BVH, bool STATS>
+__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* film, unsigned long long* stats) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    bool defer = false;
+    if (idx < w.counters[C_SHADOW]) {
+        const RayD r = load_shadow_ray(w, idx);
+        HitD h;
+        bool found;
+        TravStats ts{0, 0};
+        if (BVH == BDPT_BVH_REFERENCE) {
+            found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+        } else {
+            const int rc = traverse_fast<true, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts);
+            found = rc == TR_HIT;
+            defer = rc == TR_DEFER;
+        }
+        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
+        if (!found && !defer) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
+    }
+    if (BVH != BDPT_BVH_REFERENCE) {
+        const uint32_t slot = warp_append(w.counters + C_EXACT_SHADOW, defer);
+        if (defer) w.q_exact_s[slot] = idx;
+    }
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock) k_shadow_exact(SceneView sc, WF w, double* film, unsigned long long* stats) {
+    const uint32_t n = w.counters[C_EXACT_SHADOW];
+    for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
+        const uint32_t idx = w.q_exact_s[i];
+        const RayD r = load_shadow_ray(w, idx);
+        HitD h;
+        TravStats ts{0, 0};
+        const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
+        if (!found) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
+    }
 }
 
 }  // namespace
@@ -522,6 +605,8 @@ void carve(WF& w, char* base) {
     w.draws = c.take<uint32_t>(P); w.hit_prim = c.take<uint32_t>(P); w.remaining = c.take<int32_t>(P);
     for (int k = 0; k < 2; ++k) w.q_active[k] = c.take<uint32_t>(P);
     for (int k = 0; k < 4; ++k) w.q_mat[k] = c.take<uint32_t>(P);
+    w.q_exact = c.take<uint32_t>(P);
+    w.q_exact_s = c.take<uint32_t>(S);
     w.counters = c.take<uint32_t>(C_COUNT);
     double** cv[] = {&w.cv_px, &w.cv_py, &w.cv_pz, &w.cv_fx, &w.cv_fy, &w.cv_fz, &w.lv_px, &w.lv_py, &w.lv_pz, &w.lv_tx, &w.lv_ty, &w.lv_tz};
     for (double** q : cv) *q = c.take<double>(V);
@@ -598,13 +683,147 @@ inline unsigned grid_for(int64_t n, int block) { return unsigned(std::max<int64_
 
 }  // namespace
 
+namespace {
+
+// One wavefront in flight: its own stream, workspace, timers and tallies.  bdpt_render keeps several
+// (opts.streams) so that the long tail of one wavefront — late bounces with few live rays, whose launch
+// time is the latency of the slowest ray — overlaps the bulk of another.
+struct Worker {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    WF wf{};
+    KernelTimers tm;
+    uint32_t* hc = nullptr;              // pinned read-back of the device counters
+    uint64_t rays_closest = 0, rays_shadow = 0, cam_verts = 0, light_verts = 0, launches = 0, samples = 0;
+    double kernel_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint64_t kernel_launches[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::string err;
+    int rc = BDPT_OK;
+    ~Worker() {
+        if (wf.base) cudaFree(wf.base);
+        if (hc) cudaFreeHost(hc);
+        if (done) cudaEventDestroy(done);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+struct Workers { std::vector<Worker*> w; ~Workers() { for (auto* x : w) delete x; } };
+
+#define WK_CUDA(call)                                                                   \
+    do {                                                                                \
+        cudaError_t e__ = (call);                                                       \
+        if (e__ != cudaSuccess) { wk.err = std::string(#call) + ": " + cudaGetErrorString(e__); wk.rc = BDPT_ERR_CUDA; return; } \
+    } while (0)
+
+struct Job {
+    SceneView sc; Frame f; bdpt_render_opts o;
+    int64_t total; double* film; unsigned long long* d_stats;
+    size_t smem; unsigned exact_grid; int device; int n_workers;
+    int64_t B;   // samples per wavefront (every worker's workspace holds at least this many)
+};
+
+// all wavefronts of one worker: batches id, id + n_workers, ...
+void run_worker(const Job& J, Worker& wk, int id) {
+    cudaSetDevice(J.device);
+    const SceneView& sc = J.sc; const Frame& f = J.f; const bdpt_render_opts& o = J.o;
+    WF& wf = wk.wf;
+    cudaStream_t st = wk.stream;
+    KernelTimers& tm = wk.tm;
+    uint32_t* hc = wk.hc;
+    const bool want_stats = (o.flags & BDPT_RENDER_STATS) != 0;
+    const size_t smem = J.smem;
+    for (int64_t L0 = int64_t(id) * J.B; L0 < J.total; L0 += J.B * J.n_workers) {
+        const int64_t nb = std::min<int64_t>(J.B, J.total - L0);
+        WK_CUDA(cudaMemsetAsync(wf.counters, 0, C_COUNT * sizeof(uint32_t), st));
+        tm.begin(KT_GENERATE, st);
+        k_generate<<<grid_for(nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb);
+        tm.end(KT_GENERATE, st);
+        wk.launches += 1;
+        WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        WK_CUDA(cudaStreamSynchronize(st));
+        int cur = 0;
+        uint32_t n_active = hc[C_ACTIVE0];
+        while (n_active > 0) {
+            const int nxt = cur ^ 1;
+            WK_CUDA(cudaMemsetAsync(wf.counters + C_ACTIVE0 + nxt, 0, sizeof(uint32_t), st));
+            WK_CUDA(cudaMemsetAsync(wf.counters + C_MAT0, 0, 4 * sizeof(uint32_t), st));
+            WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT, 0, sizeof(uint32_t), st));
+            const unsigned g = grid_for(n_active, kBlock);
+            tm.begin(KT_TRACE, st);
+#define BDPT_TP(B, S) k_trace_paths<B, S><<<g, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, J.film, J.d_stats)
+            if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
+            else {
+                if (want_stats) BDPT_TP(BDPT_BVH_FAST, true); else BDPT_TP(BDPT_BVH_FAST, false);
+                if (want_stats) k_trace_exact<true><<<J.exact_grid, kBlock, smem, st>>>(sc, f, wf, L0, J.film, J.d_stats);
+                else k_trace_exact<false><<<J.exact_grid, kBlock, smem, st>>>(sc, f, wf, L0, J.film, J.d_stats);
+                wk.launches += 1;
+            }
+#undef BDPT_TP
+            tm.end(KT_TRACE, st);
+            tm.begin(KT_SHADE, st);
+            k_shade_light<<<g, kBlock, 0, st>>>(sc, f, wf, L0, J.film);
+            k_shade_lambert<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
+            k_shade_metal<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
+            k_shade_dielectric<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
+            tm.end(KT_SHADE, st);
+            wk.launches += 5;
+            wk.rays_closest += n_active;
+            WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            WK_CUDA(cudaStreamSynchronize(st));
+            n_active = hc[C_ACTIVE0 + nxt];
+            cur = nxt;
+        }
+        // connections
+        k_counts<<<grid_for(nb, 256), 256, 0, st>>>(wf, nb);
+        wk.launches += 1;
+        WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        WK_CUDA(cudaStreamSynchronize(st));
+        const int max_nc = int(hc[C_MAXNC]), max_nl = int(hc[C_MAXNL]);
+        wk.cam_verts += hc[C_SUMNC]; wk.light_verts += hc[C_SUMNL];
+        if (max_nc > 0 && max_nl > 0) {
+            // every (camera vertex, light vertex) pair is at most one shadow ray: if they all fit, one round
+            const uint64_t pairs = uint64_t(hc[C_PAIRS_LO]) | (uint64_t(hc[C_PAIRS_HI]) << 32);
+            const int slots_per_round = pairs <= uint64_t(wf.scap) ? max_nc : int(std::max<int64_t>(1, wf.scap / (nb * int64_t(max_nl))));
+            for (int k0 = 0; k0 < max_nc; k0 += slots_per_round) {
+                const int k1 = std::min(max_nc, k0 + slots_per_round);
+                WK_CUDA(cudaMemsetAsync(wf.counters + C_SHADOW, 0, sizeof(uint32_t), st));
+                WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT_SHADOW, 0, sizeof(uint32_t), st));
+                tm.begin(KT_CONNECT, st);
+                k_connect<<<grid_for(int64_t(k1 - k0) * nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb, k0, k1);
+                tm.end(KT_CONNECT, st);
+                WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                WK_CUDA(cudaStreamSynchronize(st));
+                wk.launches += 1;
+                if (hc[C_OVERFLOW]) { wk.err = "shadow queue overflow"; wk.rc = BDPT_ERR_STATE; return; }
+                const uint32_t ns = hc[C_SHADOW];
+                if (ns) {
+                    tm.begin(KT_SHADOW, st);
+#define BDPT_SH(B, S) k_shadow<B, S><<<grid_for(ns, kBlock), kBlock, smem, st>>>(sc, wf, J.film, J.d_stats)
+                    if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_SH(BDPT_BVH_REFERENCE, true); else BDPT_SH(BDPT_BVH_REFERENCE, false); }
+                    else {
+                        if (want_stats) BDPT_SH(BDPT_BVH_FAST, true); else BDPT_SH(BDPT_BVH_FAST, false);
+                        if (want_stats) k_shadow_exact<true><<<J.exact_grid, kBlock, smem, st>>>(sc, wf, J.film, J.d_stats);
+                        else k_shadow_exact<false><<<J.exact_grid, kBlock, smem, st>>>(sc, wf, J.film, J.d_stats);
+                        wk.launches += 1;
+                    }
+#undef BDPT_SH
+                    tm.end(KT_SHADOW, st);
+                    wk.launches += 1;
+                    wk.rays_shadow += ns;
+                }
+            }
+        }
+        wk.samples += uint64_t(nb);
+        WK_CUDA(cudaStreamSynchronize(st));
+        tm.collect(wk.kernel_ms, wk.kernel_launches);
+    }
+    WK_CUDA(cudaEventRecord(wk.done, st));
+}
+
+}  // namespace
+
 void render_free(bdpt_ctx* ctx) {
     if (ctx->timers) { delete static_cast<KernelTimers*>(ctx->timers); ctx->timers = nullptr; }
-    if (!ctx->wf) return;
-    WF* w = static_cast<WF*>(ctx->wf);
-    if (w->base) cudaFree(w->base);
-    delete w;
-    ctx->wf = nullptr;
+    if (ctx->wf) { delete static_cast<Workers*>(ctx->wf); ctx->wf = nullptr; }
 }
 
 int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts_in) {
@@ -640,120 +859,77 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
         return BDPT_OK;
     }
 
-    // workspace
-    int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 20);
+    // wavefront size and how many wavefronts are kept in flight
+    int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 19);
     B = std::min<int64_t>(B, total);
     B = std::min<int64_t>(B, int64_t(1) << 30);
-    WF* w = static_cast<WF*>(ctx->wf);
-    if (!w || w->B < B || w->depth < f.depth) {
-        render_free(ctx);
-        w = new WF();
-        std::memset(w, 0, sizeof(WF));
-        w->B = B; w->depth = f.depth;
-        w->scap = std::max<int64_t>(B * 32, int64_t(f.depth) * B);   // >= one camera slot against every light vertex
-        w->scap = std::min<int64_t>(w->scap, int64_t(0xFFFFFFF0u));
-        carve(*w, nullptr);
-        void* base = nullptr;
-        cudaError_t e = cudaMalloc(&base, w->bytes);
-        if (e != cudaSuccess) { ctx->err = std::string("wavefront workspace: ") + cudaGetErrorString(e); delete w; return BDPT_ERR_NOMEM; }
-        w->base = base;
-        carve(*w, static_cast<char*>(base));
-        ctx->wf = w;
+    const int64_t n_batches = (total + B - 1) / B;
+    int S = o.streams > 0 ? o.streams : 4;
+    S = int(std::min<int64_t>(std::min(S, 16), n_batches));
+    Workers* ws = static_cast<Workers*>(ctx->wf);
+    if (!ws) { ws = new Workers(); ctx->wf = ws; }
+    while (int(ws->w.size()) < S) ws->w.push_back(new Worker());
+    for (int i = 0; i < S; ++i) {
+        Worker& wk = *ws->w[i];
+        if (!wk.stream) {
+            BDPT_CUDA(ctx, cudaStreamCreateWithFlags(&wk.stream, cudaStreamNonBlocking));
+            BDPT_CUDA(ctx, cudaEventCreateWithFlags(&wk.done, cudaEventDisableTiming));
+            BDPT_CUDA(ctx, cudaMallocHost(&wk.hc, C_COUNT * sizeof(uint32_t)));
+        }
+        if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth) {
+            if (wk.wf.base) { BDPT_CUDA(ctx, cudaStreamSynchronize(wk.stream)); cudaFree(wk.wf.base); }
+            std::memset(&wk.wf, 0, sizeof(WF));
+            wk.wf.B = B; wk.wf.depth = f.depth;
+            wk.wf.scap = std::max<int64_t>(B * 32, int64_t(f.depth) * B);   // >= one camera slot against every light vertex
+            wk.wf.scap = std::min<int64_t>(wk.wf.scap, int64_t(0xFFFFFFF0u));
+            carve(wk.wf, nullptr);
+            void* base = nullptr;
+            cudaError_t e = cudaMalloc(&base, wk.wf.bytes);
+            if (e != cudaSuccess) { ctx->err = std::string("wavefront workspace: ") + cudaGetErrorString(e); wk.wf.base = nullptr; return BDPT_ERR_NOMEM; }
+            wk.wf.base = base;
+            carve(wk.wf, static_cast<char*>(base));
+        }
+        wk.rays_closest = wk.rays_shadow = wk.cam_verts = wk.light_verts = wk.launches = wk.samples = 0;
+        for (int k = 0; k < 8; ++k) { wk.kernel_ms[k] = 0.0; wk.kernel_launches[k] = 0; }
+        wk.err.clear(); wk.rc = BDPT_OK;
     }
-    WF wf = *w;
-    const int64_t Bcap = wf.B;   // indices use the allocated stride
-    SceneView sc = ctx->view;
-    cudaStream_t st = ctx->stream;
-    uint32_t hc[C_COUNT];
-    const bool want_stats = (o.flags & BDPT_RENDER_STATS) != 0;
-    KernelTimers& tm = *ctx_timers(ctx);
-    uint64_t rays_closest = 0, rays_shadow = 0, cam_verts = 0, light_verts = 0;
 
-    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
-    for (int64_t L0 = 0; L0 < total; L0 += Bcap) {
-        const int64_t nb = std::min<int64_t>(Bcap, total - L0);
-        BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters, 0, C_COUNT * sizeof(uint32_t), st));
-        tm.begin(KT_GENERATE, st);
-        k_generate<<<grid_for(nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb);
-        tm.end(KT_GENERATE, st);
-        ctx->launches += 1;
-        BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-        BDPT_CUDA(ctx, cudaStreamSynchronize(st));
-        int cur = 0;
-        uint32_t n_active = hc[C_ACTIVE0];
-        while (n_active > 0) {
-            const int nxt = cur ^ 1;
-            // zero the next-ray counter and the material counters
-            BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_ACTIVE0 + nxt, 0, sizeof(uint32_t), st));
-            BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_MAT0, 0, 4 * sizeof(uint32_t), st));
-            const unsigned g = grid_for(n_active, kBlock);
-            tm.begin(KT_TRACE, st);
-#define BDPT_TP(B, S) k_trace_paths<B, S><<<g, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, ctx->film, ctx->d_stats)
-            if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
-            else { if (want_stats) BDPT_TP(BDPT_BVH_FAST, true); else BDPT_TP(BDPT_BVH_FAST, false); }
-#undef BDPT_TP
-            tm.end(KT_TRACE, st);
-            tm.begin(KT_SHADE, st);
-            k_shade_light<<<g, kBlock, 0, st>>>(sc, f, wf, L0, ctx->film);
-            k_shade_lambert<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
-            k_shade_metal<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
-            k_shade_dielectric<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
-            tm.end(KT_SHADE, st);
-            ctx->launches += 5;
-            rays_closest += n_active;
-            BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-            BDPT_CUDA(ctx, cudaStreamSynchronize(st));
-            n_active = hc[C_ACTIVE0 + nxt];
-            cur = nxt;
-        }
-        // connections
-        k_counts<<<grid_for(nb, 256), 256, 0, st>>>(wf, nb);
-        ctx->launches += 1;
-        BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-        BDPT_CUDA(ctx, cudaStreamSynchronize(st));
-        const int max_nc = int(hc[C_MAXNC]), max_nl = int(hc[C_MAXNL]);
-        cam_verts += hc[C_SUMNC]; light_verts += hc[C_SUMNL];
-        if (max_nc > 0 && max_nl > 0) {
-            int slots_per_round = int(std::max<int64_t>(1, wf.scap / (nb * int64_t(max_nl))));
-            for (int k0 = 0; k0 < max_nc; k0 += slots_per_round) {
-                const int k1 = std::min(max_nc, k0 + slots_per_round);
-                BDPT_CUDA(ctx, cudaMemsetAsync(wf.counters + C_SHADOW, 0, sizeof(uint32_t), st));
-                tm.begin(KT_CONNECT, st);
-                k_connect<<<grid_for(int64_t(k1 - k0) * nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb, k0, k1);
-                tm.end(KT_CONNECT, st);
-                BDPT_CUDA(ctx, cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-                BDPT_CUDA(ctx, cudaStreamSynchronize(st));
-                ctx->launches += 1;
-                if (hc[C_OVERFLOW]) { ctx->err = "shadow queue overflow"; return BDPT_ERR_STATE; }
-                const uint32_t ns = hc[C_SHADOW];
-                if (ns) {
-                    tm.begin(KT_SHADOW, st);
-#define BDPT_SH(B, S) k_shadow<B, S><<<grid_for(ns, kBlock), kBlock, 0, st>>>(sc, wf, ctx->film, ctx->d_stats)
-                    if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_SH(BDPT_BVH_REFERENCE, true); else BDPT_SH(BDPT_BVH_REFERENCE, false); }
-                    else { if (want_stats) BDPT_SH(BDPT_BVH_FAST, true); else BDPT_SH(BDPT_BVH_FAST, false); }
-#undef BDPT_SH
-                    tm.end(KT_SHADOW, st);
-                    ctx->launches += 1;
-                    rays_shadow += ns;
-                }
-            }
-        }
-        ctx->samples += uint64_t(nb);
-        tm.collect(ctx->kernel_ms, ctx->kernel_launches);   // the stream is idle here (last sync above or below)
+    Job J;
+    J.sc = ctx->view; J.f = f; J.o = o; J.total = total; J.film = ctx->film; J.d_stats = ctx->d_stats;
+    // traversal stack: one StackEntry per tree level per thread (deferred children only)
+    const size_t levels = size_t(std::max(ctx->host.fast_depth, ctx->host.ref_depth)) + 2;
+    J.smem = levels * kBlock * sizeof(StackEntry);
+    J.exact_grid = 148 * 2;
+    J.device = ctx->device; J.n_workers = S; J.B = B;
+
+    // the film clear (and anything else queued on the context stream) happens-before the workers
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    for (int i = 0; i < S; ++i) BDPT_CUDA(ctx, cudaStreamWaitEvent(ws->w[i]->stream, ctx->ev0, 0));
+    std::vector<std::thread> pool;
+    for (int i = 1; i < S; ++i) pool.emplace_back([&, i] { run_worker(J, *ws->w[i], i); });
+    run_worker(J, *ws->w[0], 0);
+    for (auto& th : pool) th.join();
+    for (int i = 0; i < S; ++i) {
+        Worker& wk = *ws->w[i];
+        if (wk.rc != BDPT_OK) { ctx->err = wk.err; cudaDeviceSynchronize(); return wk.rc; }
+        BDPT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, wk.done, 0));
     }
-    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
-    BDPT_CUDA(ctx, cudaStreamSynchronize(st));
+    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     BDPT_CUDA(ctx, cudaGetLastError());
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_ms = ms;
-    tm.collect(ctx->kernel_ms, ctx->kernel_launches);
-    // host-side tallies go into the device counter block so bdpt_stats reads one place
-    unsigned long long add[4] = {rays_closest, rays_shadow, cam_verts, light_verts};
+    // tallies go into the device counter block so bdpt_stats reads one place
     unsigned long long cur_stats[16];
     BDPT_CUDA(ctx, cudaMemcpy(cur_stats, ctx->d_stats, sizeof cur_stats, cudaMemcpyDeviceToHost));
-    cur_stats[ST_RAYS_CLOSEST] += add[0]; cur_stats[ST_RAYS_SHADOW] += add[1];
-    cur_stats[ST_CAM_VERTS] += add[2]; cur_stats[ST_LIGHT_VERTS] += add[3];
+    for (int i = 0; i < S; ++i) {
+        const Worker& wk = *ws->w[i];
+        cur_stats[ST_RAYS_CLOSEST] += wk.rays_closest; cur_stats[ST_RAYS_SHADOW] += wk.rays_shadow;
+        cur_stats[ST_CAM_VERTS] += wk.cam_verts; cur_stats[ST_LIGHT_VERTS] += wk.light_verts;
+        ctx->launches += wk.launches; ctx->samples += wk.samples;
+        for (int k = 0; k < 8; ++k) { ctx->kernel_ms[k] += wk.kernel_ms[k]; ctx->kernel_launches[k] += wk.kernel_launches[k]; }
+    }
     BDPT_CUDA(ctx, cudaMemcpy(ctx->d_stats, cur_stats, sizeof cur_stats, cudaMemcpyHostToDevice));
     return BDPT_OK;
 }

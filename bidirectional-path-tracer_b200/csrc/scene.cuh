@@ -71,6 +71,7 @@ struct SceneView {
     uint32_t n_ref_nodes;
     uint32_t n_fast_nodes;
     double light_total_area;      // summed in list order like triangle.h:200-203
+    D3 center;                    // centre of the scene bounds
     double extent;                // largest side of the scene bounds (tie-band scale, traverse_fast.cuh)
 };
 

@@ -14,15 +14,23 @@
 
 namespace bdpt {
 
-__device__ __forceinline__ bool slab_fast(double lo, double hi, double o, double adinv, double& tmin, double& tmax) {
-    double t0 = (lo - o) * adinv;
-    double t1 = (hi - o) * adinv;
-    // NaN (0 * inf) only when the origin lies exactly on a slab plane of a zero-direction axis:
-    // fmin/fmax drop the NaN, which keeps the slab (conservative).
-    double tn = fmin(t0, t1), tf = fmax(t0, t1);
-    tmin = fmax(tmin, tn);
-    tmax = fmin(tmax, tf);
-    return tmin <= tmax;
+// One slab of a child box in scalar type T (float on the normal path, double for rays whose origin is so
+// far outside the scene that fp32 would eat the outward padding).  NaN (0 * inf, origin exactly on a slab
+// plane of a zero-direction axis) is dropped by fmin/fmax, which keeps the slab: conservative.
+template <class T>
+__device__ __forceinline__ void slab_fast(T lo, T hi, T o, T inv, T& tn, T& tf) {
+    const T t0 = (lo - o) * inv, t1 = (hi - o) * inv;
+    tn = fmax(tn, fmin(t0, t1));
+    tf = fmin(tf, fmax(t0, t1));
+}
+
+enum { TR_MISS = 0, TR_HIT = 1, TR_DEFER = 2 };
+
+// traversal stack entry: deferred child + its box-entry distance (fp32, a lower bound), so that a
+// child made unreachable by a closer hit found in the meantime is dropped at pop time without a fetch
+typedef unsigned long long StackEntry;
+__device__ __forceinline__ StackEntry pack_entry(int32_t node, float t) {
+    return (StackEntry(uint32_t(node)) << 32) | StackEntry(__float_as_uint(t));
 }
 
 // Where the reference's answer is NOT simply "closest triangle" — and how this kernel reproduces it:
@@ -37,15 +45,22 @@ __device__ __forceinline__ bool slab_fast(double lo, double hi, double o, double
 //  Both depend on the reference tree, so such rays are re-run through the reference-exact traversal.
 //  Detection: every triangle the ray's line meets reports its exact t; if it lies within a band of
 //  tmin, of tmax, or of another candidate's t, the ray is flagged.  The band (1e-10 of the scene extent
-//  in t units) is far above fp64 rounding (~1e-13) and far below the outward box padding (2^-20 of the
+//  in t units) is far above fp64 rounding (~1e-13) and far below the outward box padding (2^-16 of the
 //  extent), so a flagged-band triangle can never have been culled by THIS tree's boxes.
-template <bool ANY, bool STATS>
-__device__ __forceinline__ bool traverse_fast(const SceneView& sc, const RayD& r, HitD& hit, int32_t* stack,
-                                              int stride, TravStats* st) {
-    if (r.d.x == 0.0 || r.d.y == 0.0 || r.d.z == 0.0) return traverse_ref<ANY, STATS>(sc, r, hit, stack, stride, st);
-    const D3 adinv = mk(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
-    const double band_abs = 1e-10 * sc.extent * fmin(fabs(adinv.x), fmin(fabs(adinv.y), fabs(adinv.z)));
+// Returns TR_HIT / TR_MISS, or TR_DEFER when DEFER is set and the ray needs the reference-exact traversal
+// (the caller queues it for the exact kernel); with DEFER unset that traversal runs inline.
+// `stack` is this thread's column of a [levels][stride] shared array of StackEntry.
+template <bool ANY, bool STATS, bool DEFER, class T>
+__device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& r, HitD& hit, StackEntry* stack,
+                                               int stride, TravStats* st) {
+    const T ox = T(r.o.x), oy = T(r.o.y), oz = T(r.o.z);
+    const T ix = T(1.0 / r.d.x), iy = T(1.0 / r.d.y), iz = T(1.0 / r.d.z);
+    const double inv_max = fmin(fabs(1.0 / r.d.x), fmin(fabs(1.0 / r.d.y), fabs(1.0 / r.d.z)));
+    const double band_abs = 1e-10 * sc.extent * inv_max;
+    // bounds in T, rounded outward
+    const T tmin_t = sizeof(T) == 4 ? T(__double2float_rd(r.tmin)) : T(r.tmin);
     double best = r.tmax;
+    T best_t = sizeof(T) == 4 ? T(__double2float_ru(best)) : T(best);
     uint32_t best_rank = 0;
     bool found = false, flagged = false;
     int sp = 0;
@@ -54,32 +69,48 @@ __device__ __forceinline__ bool traverse_fast(const SceneView& sc, const RayD& r
     constexpr int kMaxEdge = 4;
     uint32_t edge_prim[kMaxEdge];
     int n_edge = 0;
-    for (;;) {
-        if (cur >= 0) {
+    bool done = false;
+    while (!done) {
+        // ---- inner nodes: descend until a leaf (or the stack runs dry)
+        while (cur >= 0) {
             const float4* q = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
-            float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
-            int4 w = __ldg(reinterpret_cast<const int4*>(q + 3));
+            const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+            const int4 w = __ldg(reinterpret_cast<const int4*>(q + 3));
             if (STATS) ++nn;
             // a = l_lo.xyz l_hi.x | b = l_hi.yz r_lo.xy | c = r_lo.z r_hi.xyz
-            double ln = r.tmin, lf = best, rn = r.tmin, rf = best;
-            bool hl = slab_fast(a.x, a.w, r.o.x, adinv.x, ln, lf) && slab_fast(a.y, b.x, r.o.y, adinv.y, ln, lf) &&
-                      slab_fast(a.z, b.y, r.o.z, adinv.z, ln, lf);
-            bool hr = slab_fast(b.z, c.y, r.o.x, adinv.x, rn, rf) && slab_fast(b.w, c.z, r.o.y, adinv.y, rn, rf) &&
-                      slab_fast(c.x, c.w, r.o.z, adinv.z, rn, rf);
+            T ln = tmin_t, lf = best_t, rn = tmin_t, rf = best_t;
+            slab_fast<T>(T(a.x), T(a.w), ox, ix, ln, lf);
+            slab_fast<T>(T(a.y), T(b.x), oy, iy, ln, lf);
+            slab_fast<T>(T(a.z), T(b.y), oz, iz, ln, lf);
+            slab_fast<T>(T(b.z), T(c.y), ox, ix, rn, rf);
+            slab_fast<T>(T(b.w), T(c.z), oy, iy, rn, rf);
+            slab_fast<T>(T(c.x), T(c.w), oz, iz, rn, rf);
+            const bool hl = ln <= lf, hr = rn <= rf;
             int32_t lc = w.x, rc = w.y;
             if (hl && hr) {
-                if (rn < ln) { int32_t t = lc; lc = rc; rc = t; }
-                stack[sp * stride] = rc;
+                float far_t = float(rn);
+                if (rn < ln) { const int32_t t = lc; lc = rc; rc = t; far_t = float(ln); }
+                stack[sp * stride] = pack_entry(rc, far_t);
                 ++sp;
                 cur = lc;
-                continue;
-            } else if (hl) { cur = lc; continue; }
-            else if (hr) { cur = rc; continue; }
-        } else {
-            // leaf: cur = ~(first << 3 | count-1)
+            } else if (hl) cur = lc;
+            else if (hr) cur = rc;
+            else {
+                // pop, dropping children that a closer hit has put out of reach
+                for (;;) {
+                    if (sp == 0) { done = true; break; }
+                    --sp;
+                    const StackEntry e = stack[sp * stride];
+                    if (T(__uint_as_float(uint32_t(e))) <= best_t) { cur = int32_t(uint32_t(e >> 32)); break; }
+                }
+                if (done) break;
+            }
+        }
+        if (done) break;
+        // ---- leaf: cur = ~(first << 3 | count-1)
+        {
             const uint32_t code = uint32_t(~cur);
             const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
-            bool done = false;
             for (uint32_t k = 0; k < cnt; ++k) {
                 const uint32_t prim = __ldg(sc.fast_prims + first + k);
                 if (STATS) ++nt;
@@ -104,42 +135,69 @@ __device__ __forceinline__ bool traverse_fast(const SceneView& sc, const RayD& r
                         const uint32_t rank = __ldg(sc.dfs_rank + prim);
                         if (!found || t < best || rank > best_rank) {
                             best = t; best_rank = rank; found = true;
+                            best_t = sizeof(T) == 4 ? T(__double2float_ru(best)) : T(best);
                             hit.t = t; hit.u = u; hit.v = v; hit.prim = prim;
                         }
                     }
                 }
             }
             if (done) break;
+            for (;;) {
+                if (sp == 0) { done = true; break; }
+                --sp;
+                const StackEntry e = stack[sp * stride];
+                if (T(__uint_as_float(uint32_t(e))) <= best_t) { cur = int32_t(uint32_t(e >> 32)); break; }
+            }
         }
-        if (sp == 0) break;
-        --sp;
-        cur = stack[sp * stride];
     }
     if (STATS && st) { st->nodes += nn; st->tris += nt; }
-    const uint32_t nn_walk = nn;
     if (ANY) {
-        if (found) return true;
-        if (flagged) return traverse_ref<ANY, STATS>(sc, r, hit, stack, stride, st);
-        // No certain occluder.  The reference reports a hit iff some knife-edge triangle that passes its
-        // (bit-identical) interval test is actually REACHED, i.e. every box on its root-to-leaf chain in
-        // the reference tree passes aabb::hit with the untouched bound [tmin, tmax] (the bound only
-        // shrinks after a hit, and then the answer is already "occluded").
-        for (int k = 0; k < n_edge; ++k) {
-            int32_t node = __ldg(sc.prim_leaf + edge_prim[k]);
-            bool reached = true;
-            while (node >= 0) {
-                RefNode nd = load_ref_node(sc.ref_nodes + node);
-                if (STATS) ++nn;
-                if (!box_hit(nd, r.o, adinv, r.tmin, r.tmax)) { reached = false; break; }
-                node = __ldg(sc.ref_parent + node);
+        if (found) return TR_HIT;
+        if (!flagged) {
+            // No certain occluder.  The reference reports a hit iff some knife-edge triangle that passes its
+            // (bit-identical) interval test is actually REACHED, i.e. every box on its root-to-leaf chain in
+            // the reference tree passes aabb::hit with the untouched bound [tmin, tmax] (the bound only
+            // shrinks after a hit, and then the answer is already "occluded").
+            if (n_edge == 0) return TR_MISS;
+            const D3 adinv = mk(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
+            uint32_t walk = 0;
+            for (int k = 0; k < n_edge && !found; ++k) {
+                int32_t node = __ldg(sc.prim_leaf + edge_prim[k]);
+                bool reached = true;
+                while (node >= 0) {
+                    const RefNode nd = load_ref_node(sc.ref_nodes + node);
+                    ++walk;
+                    if (!box_hit(nd, r.o, adinv, r.tmin, r.tmax)) { reached = false; break; }
+                    node = __ldg(sc.ref_parent + node);
+                }
+                if (reached) { hit.prim = edge_prim[k]; hit.t = r.tmax; hit.u = 0.0; hit.v = 0.0; found = true; }
             }
-            if (reached) { hit.prim = edge_prim[k]; hit.t = r.tmax; hit.u = 0.0; hit.v = 0.0; found = true; break; }
+            if (STATS && st) st->nodes += walk;
+            return found ? TR_HIT : TR_MISS;
         }
-        if (STATS && st) st->nodes += nn - nn_walk;
-        return found;
+    } else if (!flagged) {
+        return found ? TR_HIT : TR_MISS;
     }
-    if (flagged) return traverse_ref<ANY, STATS>(sc, r, hit, stack, stride, st);
-    return found;
+    if (DEFER) return TR_DEFER;
+    return traverse_ref<ANY, STATS>(sc, r, hit, reinterpret_cast<int32_t*>(stack), 2 * stride, st) ? TR_HIT : TR_MISS;
+}
+
+// Entry point: picks the arithmetic of the box tests.
+//  - a zero direction component -> reference-exact traversal (case 1 above)
+//  - origin (or the scene itself) farther than 8 scene extents from the scene centre / the world origin -> fp64 slabs (fp32 would eat the padding)
+//  - otherwise fp32 slabs: outward padding of 2^-16 extent covers the <= 5e-6 extent fp32 error
+template <bool ANY, bool STATS, bool DEFER>
+__device__ __forceinline__ int traverse_fast(const SceneView& sc, const RayD& r, HitD& hit, StackEntry* stack,
+                                             int stride, TravStats* st) {
+    if (r.d.x == 0.0 || r.d.y == 0.0 || r.d.z == 0.0) {
+        if (DEFER) return TR_DEFER;
+        return traverse_ref<ANY, STATS>(sc, r, hit, reinterpret_cast<int32_t*>(stack), 2 * stride, st) ? TR_HIT : TR_MISS;
+    }
+    const double far = 8.0 * sc.extent;
+    const bool near_scene = fabs(r.o.x - sc.center.x) <= far && fabs(r.o.y - sc.center.y) <= far && fabs(r.o.z - sc.center.z) <= far &&
+                            fabs(sc.center.x) <= far && fabs(sc.center.y) <= far && fabs(sc.center.z) <= far;
+    if (near_scene) return traverse_fast_t<ANY, STATS, DEFER, float>(sc, r, hit, stack, stride, st);
+    return traverse_fast_t<ANY, STATS, DEFER, double>(sc, r, hit, stack, stride, st);
 }
 
 }  // namespace bdpt

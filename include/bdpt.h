@@ -104,7 +104,7 @@ typedef struct {
     int32_t  row_end;
     int64_t  batch_samples;  /* wavefront size; <=0 picks a default */
     int32_t  flags;          /* BDPT_RENDER_* */
-    int32_t  pad;
+    int32_t  streams;        /* wavefronts kept in flight on separate CUDA streams; <=0 picks a default (4) */
 } bdpt_render_opts;
 enum { BDPT_RENDER_STATS = 1 /* count node visits / triangle tests of the traversal kernels (slower) */ };
 
