@@ -28,6 +28,8 @@ import time
 
 import numpy as np
 
+_JSON_OUT = None
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -84,6 +86,12 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -137,7 +145,7 @@ def run_reference(args):
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "reference_counters": {k: r[k] for k in ("closest_rays_per_sample", "node_visits_per_ray", "tri_tests_per_ray")}}
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -268,7 +276,7 @@ def run_ours(args):
                 "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow": st["rays_shadow"] / st["samples"]},
                 "film_checksum": float(np.nan_to_num(film_host).sum())}
         line.update(extra)
-        print(json.dumps(line))
+        emit(line)
     if dist:
         dist.barrier()
         dist.destroy_process_group()
@@ -369,13 +377,18 @@ def main():
     args.steps = max(1, args.steps)
     args.warmup = max(3, args.warmup) if args.impl == "ours" else max(0, args.warmup)
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if args.impl == "reference":
-        return run_reference(args)
     if args.gpus != world:
         if world == 1 and args.gpus > 1:   # launched without torchrun: re-exec under it
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
                    "--master-addr", "127.0.0.1", "--master-port", "29531", os.path.abspath(__file__)] + sys.argv[1:]
             return subprocess.call(cmd)
+    # the scene loader prints "Triangles: N" on stdout like scene_loader.h:521; keep stdout for the ONE JSON line
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    if args.impl == "reference":
+        return run_reference(args)
     return run_ours(args)
 
 
