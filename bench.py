@@ -206,7 +206,7 @@ def run_ours(args):
     fptr, fn = ctx.film_device_ptr()
     film_t = torch.as_tensor(CudaArray(fptr, fn), device=torch.device("cuda", local))
     for s in range(Wm):
-        ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(s), clear=False, height=HEIGHT)
+        ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
     if dist:
         dist.reduce(film_t, dst=0)   # warm NCCL up too
     ctx.film_clear(WIDTH, HEIGHT)
@@ -217,7 +217,7 @@ def run_ours(args):
     t0 = time.perf_counter()
     dev_ms = 0.0
     for s in range(K):
-        ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT)
+        ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
         dev_ms += ctx.last_device_ms()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     red_ms = 0.0
@@ -246,7 +246,7 @@ def run_ours(args):
     ctx2.upload(sf.verts, sf.mat_id, sf.materials)
     ctx2.film_clear(WIDTH, HEIGHT)
     for s in range(K):
-        ctx2.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT)
+        ctx2.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
     if dist:
         p2, n2_ = ctx2.film_device_ptr()
         dist.reduce(torch.as_tensor(CudaArray(p2, n2_), device=torch.device("cuda", local)), dst=0)
@@ -321,6 +321,8 @@ def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
                        "share_of_step": ms_dom / total_kernel_ms if total_kernel_ms else None,
                        "timing": "CUDA events per launch on the launching stream, streams=1 pass"}
     out["kernel_ms"] = {k: {"ms": v[0], "launches": v[1]} for k, v in kt.items()}
+    per["max_work_single_ray"] = {"closest": s2["max_work_closest"], "shadow": s2["max_work_shadow"],
+                                  "note": "nodes + triangles touched by the most expensive ray of the stats pass"}
     out["traversal_work"] = per
     if not args.skip_micro:
         out["bvh_microbench"] = bvh_microbench(args, pkg, bvh)
@@ -371,6 +373,8 @@ def main():
     ap.add_argument("--bvh", default="fast", choices=["fast", "ref"],
                     help="traversal flavour; both return the reference's hits (tests/test_trace_gpu.py)")
     ap.add_argument("--seed", type=int, default=20261104)
+    ap.add_argument("--batch", type=int, default=0, help="sample slots per wavefront (0 = library default)")
+    ap.add_argument("--streams", type=int, default=0, help="wavefronts in flight (0 = library default)")
     ap.add_argument("--skip-micro", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     args = ap.parse_args()

@@ -52,11 +52,12 @@ class RenderOpts(C.Structure):
 class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_closest", "rays_shadow", "node_visits", "tri_tests", "samples",
                                           "kernel_launches", "camera_vertices", "light_vertices", "nodes_closest",
-                                          "tris_closest", "nodes_shadow", "tris_shadow")]
+                                          "tris_closest", "nodes_shadow", "tris_shadow", "max_work_closest",
+                                          "max_work_shadow", "deferred_closest", "deferred_shadow")]
 
 
 RENDER_STATS = 1
-KERNEL_CLASSES = ("generate", "trace", "shade", "connect", "shadow")
+KERNEL_CLASSES = ("generate", "trace", "shade", "connect", "shadow", "trace_exact", "shadow_exact")
 
 
 class BdptError(RuntimeError):
@@ -317,8 +318,8 @@ class Context:
 
     def kernel_times(self):
         """{class: (ms, launches)} of bdpt_render's kernels since the last stats_reset (CUDA events on the ctx stream)."""
-        ms = (C.c_double * 5)()
-        n = (C.c_uint64 * 5)()
+        ms = (C.c_double * len(KERNEL_CLASSES))()
+        n = (C.c_uint64 * len(KERNEL_CLASSES))()
         self._chk(lib().bdpt_kernel_times(self._h, ms, n), "bdpt_kernel_times")
         return {k: (ms[i], int(n[i])) for i, k in enumerate(KERNEL_CLASSES)}
 

@@ -173,6 +173,7 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     if ((rc = upload(ctx, h.dfs_rank, &v.dfs_rank))) return rc;
     if ((rc = upload(ctx, h.ref_parent, &v.ref_parent))) return rc;
     if ((rc = upload(ctx, h.prim_leaf, &v.prim_leaf))) return rc;
+    if ((rc = upload(ctx, h.chain_box, &v.chain_box))) return rc;
     if ((rc = upload(ctx, h.tris, &v.tris))) return rc;
     if ((rc = upload(ctx, h.shade, &v.shade))) return rc;
     if ((rc = upload(ctx, h.mats, &v.mats))) return rc;
@@ -395,6 +396,8 @@ int bdpt_stats(bdpt_ctx* ctx, bdpt_stats_t* out) {
     out->samples = ctx->samples; out->kernel_launches = ctx->launches;
     out->nodes_closest = h[ST_NODE_CLOSEST]; out->tris_closest = h[ST_TRI_CLOSEST];
     out->nodes_shadow = h[ST_NODE_SHADOW]; out->tris_shadow = h[ST_TRI_SHADOW];
+    out->max_work_closest = h[ST_MAX_CLOSEST]; out->max_work_shadow = h[ST_MAX_SHADOW];
+    out->deferred_closest = h[ST_DEFER_CLOSEST]; out->deferred_shadow = h[ST_DEFER_SHADOW];
     return BDPT_OK;
 }
 

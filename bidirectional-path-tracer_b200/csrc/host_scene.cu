@@ -146,6 +146,27 @@ void build_ref_bvh(HostScene& s) {
         if (nd.leaf) { s.prim_leaf[nd.left] = int32_t(i); s.prim_leaf[nd.right] = int32_t(i); }
         else { s.ref_parent[nd.left] = int32_t(i); s.ref_parent[nd.right] = int32_t(i); }
     }
+    // Intersection of the chain's boxes, top-down (preorder: a parent precedes its children).  A ray that
+    // passes aabb::hit on this box passes it on every box of the chain (each slab bound of the intersection
+    // is the tightest of the chain's, and IEEE rounding is monotone), so traversal can accept "the reference
+    // reaches this triangle" with one box test; a failure proves nothing (child boxes are not nested in
+    // their parents where pad_to_minimums, aabb.h:81-88, widened a thin child) and falls back to the chain.
+    std::vector<double> acc(6 * s.ref_nodes.size());
+    s.chain_box.assign(6 * n, 0.0);
+    for (size_t i = 0; i < s.ref_nodes.size(); ++i) {
+        const RefNode& nd = s.ref_nodes[i];
+        double* a = &acc[6 * i];
+        a[0] = nd.lo_x; a[1] = nd.hi_x; a[2] = nd.lo_y; a[3] = nd.hi_y; a[4] = nd.lo_z; a[5] = nd.hi_z;
+        const int32_t p = s.ref_parent[i];
+        if (p >= 0) {
+            const double* q = &acc[6 * size_t(p)];
+            for (int k = 0; k < 6; k += 2) { a[k] = std::fmax(a[k], q[k]); a[k + 1] = std::fmin(a[k + 1], q[k + 1]); }
+        }
+        if (nd.leaf) {
+            std::copy(a, a + 6, &s.chain_box[6 * size_t(nd.left)]);
+            std::copy(a, a + 6, &s.chain_box[6 * size_t(nd.right)]);
+        }
+    }
 }
 
 }  // namespace bdpt

@@ -25,6 +25,7 @@ struct HostScene {
     uint32_t ref_depth = 0;
     std::vector<int32_t> ref_parent;   // node -> parent (-1 root)
     std::vector<int32_t> prim_leaf;    // prim -> leaf node
+    std::vector<double> chain_box;     // prim -> intersection of the boxes on its root-to-leaf chain: lo_x,hi_x,lo_y,hi_y,lo_z,hi_z
 
     // fast topology
     std::vector<FastNode> fast_nodes;

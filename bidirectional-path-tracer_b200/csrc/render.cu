@@ -8,10 +8,15 @@
 //   K3 k_connect       connect_vertices minus visibility (camera.h:440-475) -> shadow-ray queue
 //   K4 k_shadow        visible() (camera.h:425-438) + film accumulation (camera.h:121-124)
 //
+// Path regeneration: a wavefront has B sample SLOTS.  A slot whose two subpaths have both ended is
+// connected (K3/K4), freed, and refilled with the next sample by K0 in the following iteration, so every
+// iteration traces a full queue instead of the thinning tail of one fixed batch.
+//
 // All arithmetic is fp64 in the reference's operation order and this file is compiled with -fmad=false,
 // so a sample is computed exactly as the CPU oracle's counter-based mode computes it; only the order in
 // which contributions are summed into a pixel differs (fp64 atomics).
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <string>
@@ -31,7 +36,8 @@ constexpr uint32_t kLightFlag = 0x80000000u;
 
 // device counters (uint32 each)
 enum { C_ACTIVE0 = 0, C_ACTIVE1 = 1, C_MAT0 = 2 /* ..5 */, C_SHADOW = 6, C_MAXNC = 7, C_MAXNL = 8, C_SUMNC = 9,
-       C_SUMNL = 10, C_OVERFLOW = 11, C_PAIRS_LO = 12, C_PAIRS_HI = 13 /* 64-bit, 8-byte aligned */, C_EXACT = 14, C_EXACT_SHADOW = 15, C_COUNT = 16 };
+       C_SUMNL = 10, C_OVERFLOW = 11, C_PAIRS_LO = 12, C_PAIRS_HI = 13 /* 64-bit, 8-byte aligned */, C_UNUSED14 = 14, C_EXACT_SHADOW = 15,
+       C_DONE0 = 16, C_DONE1 = 17, C_SHADOW_TOTAL = 18 /* ..19: 64-bit, shadow rays of the whole worker run */, C_SHADOW_LIVE = 20, C_EXACT0 = 21, C_EXACT1 = 22, C_COUNT = 24 };
 
 struct Frame {           // camera.h:148-197 derived values + this call's sample selection
     D3 center, pixel00, du, dv, background;
@@ -52,8 +58,13 @@ struct WF {              // wavefront workspace, all device pointers
     double *ox, *oy, *oz, *dx, *dy, *dz, *tx, *ty, *tz, *hit_t;
     uint32_t *draws, *hit_prim;
     int32_t* remaining;
+    // per slot: the sample it holds (index into this call's sample list) and how many of its subpaths run
+    int64_t* sample;
+    uint32_t* live;
+    uint32_t* q_slots[2];            // slots whose subpaths have both ended (ping-pong: done list -> free list)
     uint32_t *q_active[2], *q_mat[4];
-    uint32_t *q_exact, *q_exact_s;   // rays deferred to the reference-exact kernels (path ids / shadow slots)
+    uint32_t* q_shadow_live;         // shadow rays the far-endpoint test did not settle (indices into the shadow queue)
+    uint32_t *q_exact[2], *q_exact_s;   // rays deferred to the reference-exact traversal (path ids, ping-pong / shadow slots)
     uint32_t* counters;
     // vertex pools, index = slot * B + b
     double *cv_px, *cv_py, *cv_pz, *cv_fx, *cv_fy, *cv_fz;   // camera vertex: p, throughput * f (camera.h:471)
@@ -63,7 +74,7 @@ struct WF {              // wavefront workspace, all device pointers
     uint32_t *ncam, *nlight;
     // shadow queue
     double *s_ox, *s_oy, *s_oz, *s_dx, *s_dy, *s_dz, *s_tmax, *s_cx, *s_cy, *s_cz;
-    uint32_t* s_pix;
+    uint32_t *s_pix, *s_far;         // pixel; prim of the far (light-side) vertex
     void* base;
     size_t bytes;
 };
@@ -87,6 +98,16 @@ __device__ __forceinline__ void film_add(double* film, uint32_t pix, D3 c) {
     atomicAdd(film + 3 * size_t(pix) + 2, c.z);
 }
 
+// A subpath of slot b has ended.  The thread that ends the slot's LAST live subpath appends the slot to the
+// done list; connection and refill happen in later launches, so the vertices written by either subpath
+// are visible by then.  Must be called by every thread of the warp (ended = false for bystanders).
+__device__ __forceinline__ void retire(const WF& w, bool ended, uint32_t b, int dn) {
+    bool last = false;
+    if (ended) last = atomicSub(&w.live[b], 1u) == 1u;
+    const uint32_t slot = warp_append(w.counters + C_DONE0 + dn, last);
+    if (last) w.q_slots[dn][slot] = b;
+}
+
 // linear sample index of this call -> pixel, stratum and the global sample id that keys the RNG
 struct SampleId { int i, j, s_i, s_j; uint32_t pix; uint64_t sid; };
 __device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
@@ -103,12 +124,19 @@ __device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
 }
 
 // ------------------------------------------------------------------ K0
-__global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w, int64_t L0, int64_t nb) {
-    const int64_t b = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    const bool valid = b < nb;
+// Fills `ngen` free slots (free_list, or slots 0..ngen-1 on a worker's first iteration) with samples
+// gen_base .. gen_base+ngen-1 of this call; consecutive threads take consecutive samples = neighbouring
+// pixels, so the primary rays of a refill are coherent.
+__global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ free_list,
+                                                    int64_t gen_base, int64_t ngen, int cur, int dn) {
+    const int64_t gi = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const bool valid = gi < ngen;
     bool cam_live = false, light_live = false;
+    int64_t b = 0;
     if (valid) {
-        const SampleId s = decode_sample(f, L0 + b);
+        b = free_list ? int64_t(free_list[gi]) : gi;
+        const SampleId s = decode_sample(f, gen_base + gi);
+        w.sample[b] = gen_base + gi;
         // camera subpath: get_ray, camera.h:199-223 (defocus off: scene_loader.h:463)
         Rng rc;
         rc.init(f.seed, 0u, s.sid, 0u);
@@ -171,11 +199,15 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
             }
         }
         w.nlight[b] = nl;
+        w.live[b] = uint32_t(cam_live) + uint32_t(light_live);
     }
-    uint32_t slot = warp_append(w.counters + C_ACTIVE0, cam_live);
-    if (cam_live) w.q_active[0][slot] = uint32_t(b);
-    slot = warp_append(w.counters + C_ACTIVE0, light_live);
-    if (light_live) w.q_active[0][slot] = uint32_t(w.B + b);
+    uint32_t slot = warp_append(w.counters + C_ACTIVE0 + cur, cam_live);
+    if (cam_live) w.q_active[cur][slot] = uint32_t(b);
+    slot = warp_append(w.counters + C_ACTIVE0 + cur, light_live);
+    if (light_live) w.q_active[cur][slot] = uint32_t(w.B + b);
+    const bool dead = valid && !cam_live && !light_live;   // nothing to trace: straight to the done list
+    slot = warp_append(w.counters + C_DONE0 + dn, dead);
+    if (dead) w.q_slots[dn][slot] = uint32_t(b);
 }
 
 // ------------------------------------------------------------------ K1
@@ -184,7 +216,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
 // class so each shading kernel runs divergence-free over its own queue.
 // result of one closest-hit query: record the hit and pick the material queue, or finish the subpath
 __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, bool found,
-                                            const HitD& h, int64_t L0, double* film) {
+                                            const HitD& h, double* film) {
     if (found) {
         w.hit_prim[pid] = h.prim;
         w.hit_t[pid] = h.t;
@@ -193,7 +225,7 @@ __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f,
     if (pid < uint32_t(w.B)) {
         const D3 T = mk(w.tx[pid], w.ty[pid], w.tz[pid]);
         const D3 c = T * f.background;
-        if (c.x != 0.0 || c.y != 0.0 || c.z != 0.0) film_add(film, decode_sample(f, L0 + pid).pix, c);
+        if (c.x != 0.0 || c.y != 0.0 || c.z != 0.0) film_add(film, decode_sample(f, w.sample[pid]).pix, c);
     }
     return -1;
 }
@@ -215,59 +247,55 @@ __device__ __forceinline__ void bin_by_material(const WF& w, int cls, uint32_t p
 
 extern __shared__ StackEntry s_dyn_stack[];   // [levels][kBlock], sized at launch from the tree depths
 
+// Blocks [0, n_def_blocks) re-trace the rays the PREVIOUS iteration's launch deferred (ties, knife edges,
+// zero direction components: traverse_fast.cuh) through the reference-exact traversal; there are a handful
+// per launch but each walks ~1000 nodes of the reference tree, so instead of a launch of their own (whose
+// duration would be one thread's latency chain) they ride at the front of the next bulk launch and their
+// paths simply lag one iteration behind — path regeneration makes that free.
 template <int BVH, bool STATS>
 __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
-                                                       const uint32_t* __restrict__ n_ptr, int64_t L0, double* film,
-                                                       unsigned long long* stats) {
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
-    const uint32_t n = *n_ptr;
+                                                       const uint32_t* __restrict__ n_ptr, int dn, int ex, uint32_t n_def_blocks,
+                                                       double* film, unsigned long long* stats) {
     int cls = -1;
     uint32_t pid = 0;
-    bool defer = false;
-    if (idx < n) {
-        pid = queue[idx];
-        const RayD r = load_path_ray(w, pid);
-        HitD h;
-        bool found;
-        TravStats ts{0, 0};
-        if (BVH == BDPT_BVH_REFERENCE) {
-            found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
-        } else {
-            const int rc = traverse_fast<false, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts);
-            found = rc == TR_HIT;
-            defer = rc == TR_DEFER;
-        }
-        if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); }
-        if (!defer) cls = finish_trace(sc, f, w, pid, found, h, L0, film);
-    }
-    if (BVH != BDPT_BVH_REFERENCE) {   // rays that need the reference tree go to the exact kernel, compacted
-        const uint32_t slot = warp_append(w.counters + C_EXACT, defer);
-        if (defer) w.q_exact[slot] = pid;
-    }
-    bin_by_material(w, cls, pid);
-}
-
-// the deferred rays of k_trace_paths (ties, knife edges, zero direction components: traverse_fast.cuh),
-// through the reference-exact traversal; grid-stride over a device-side count
-template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_trace_exact(SceneView sc, Frame f, WF w, int64_t L0, double* film,
-                                                       unsigned long long* stats) {
-    const uint32_t n = w.counters[C_EXACT];
-    for (uint32_t base = blockIdx.x * kBlock; base < n; base += gridDim.x * kBlock) {
-        const uint32_t idx = base + threadIdx.x;
-        int cls = -1;
-        uint32_t pid = 0;
-        if (idx < n) {
-            pid = w.q_exact[idx];
+    bool defer = false, ended = false;
+    if (blockIdx.x < n_def_blocks) {
+        const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+        if (idx < w.counters[C_EXACT0 + (ex ^ 1)]) {
+            pid = w.q_exact[ex ^ 1][idx];
             const RayD r = load_path_ray(w, pid);
             HitD h;
             TravStats ts{0, 0};
             const bool found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
-            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); }
-            cls = finish_trace(sc, f, w, pid, found, h, L0, film);
+            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            cls = finish_trace(sc, f, w, pid, found, h, film);
+            ended = cls < 0;
         }
-        bin_by_material(w, cls, pid);
+    } else {
+        const uint32_t idx = (blockIdx.x - n_def_blocks) * kBlock + threadIdx.x;
+        if (idx < *n_ptr) {
+            pid = queue[idx];
+            const RayD r = load_path_ray(w, pid);
+            HitD h;
+            bool found;
+            TravStats ts{0, 0};
+            if (BVH == BDPT_BVH_REFERENCE) {
+                found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+            } else {
+                const int rc = traverse_fast<false, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts);
+                found = rc == TR_HIT;
+                defer = rc == TR_DEFER;
+            }
+            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (!defer) { cls = finish_trace(sc, f, w, pid, found, h, film); ended = cls < 0; }
+        }
     }
+    if (BVH != BDPT_BVH_REFERENCE) {   // rays that need the reference tree: compacted for the next launch's front blocks
+        const uint32_t slot = warp_append(w.counters + C_EXACT0 + ex, defer);
+        if (defer) w.q_exact[ex][slot] = pid;
+    }
+    bin_by_material(w, cls, pid);
+    retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
 }
 
 // hit point and face-forwarded geometric normal (ray.h:21-23, hittable.h:20-26)
@@ -299,34 +327,40 @@ __device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d,
 // scatter() is false: the subpath ends here.  Camera subpath: bidirectional_color adds throughput *
 // emission for this non-delta vertex (camera.h:305-309); it never connects (evaluate_bsdf = 0).
 // Light subpath: the vertex is connectable with f_light = emission when hit from the front (camera.h:463).
-__global__ void __launch_bounds__(kBlock) k_shade_light(SceneView sc, Frame f, WF w, int64_t L0, double* film) {
+__global__ void __launch_bounds__(kBlock) k_shade_light(SceneView sc, Frame f, WF w, int dn, double* film) {
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
-    if (idx >= w.counters[C_MAT0 + BDPT_MAT_LIGHT]) return;
-    const uint32_t pid = w.q_mat[BDPT_MAT_LIGHT][idx];
-    const Surf s = load_surf(sc, w, pid);
-    if (!s.front) return;  // emitted() is one-sided (material.h:140)
-    const Mat m = sc.mats[sc.shade[s.prim].mat];
-    const D3 Le = mk(m.r, m.g, m.b);
-    if (!(len2(Le) > 0)) return;
-    if (pid < uint32_t(w.B)) {
-        film_add(film, decode_sample(f, L0 + pid).pix, s.T * Le);
-    } else {
-        const uint32_t b = pid - uint32_t(w.B);
-        const uint32_t slot = w.nlight[b];
-        const size_t v = size_t(slot) * size_t(w.B) + b;
-        w.lv_px[v] = s.p.x; w.lv_py[v] = s.p.y; w.lv_pz[v] = s.p.z;
-        w.lv_tx[v] = s.T.x; w.lv_ty[v] = s.T.y; w.lv_tz[v] = s.T.z;
-        w.lv_prim[v] = s.prim | kLightFlag;
-        w.nlight[b] = slot + 1;
+    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_LIGHT];
+    uint32_t b = 0;
+    if (valid) {
+        const uint32_t pid = w.q_mat[BDPT_MAT_LIGHT][idx];
+        const bool is_cam = pid < uint32_t(w.B);
+        b = is_cam ? pid : pid - uint32_t(w.B);
+        const Surf s = load_surf(sc, w, pid);
+        const Mat m = sc.mats[sc.shade[s.prim].mat];
+        const D3 Le = mk(m.r, m.g, m.b);
+        if (s.front && len2(Le) > 0) {   // emitted() is one-sided (material.h:140)
+            if (is_cam) {
+                film_add(film, decode_sample(f, w.sample[b]).pix, s.T * Le);
+            } else {
+                const uint32_t slot = w.nlight[b];
+                const size_t v = size_t(slot) * size_t(w.B) + b;
+                w.lv_px[v] = s.p.x; w.lv_py[v] = s.p.y; w.lv_pz[v] = s.p.z;
+                w.lv_tx[v] = s.T.x; w.lv_ty[v] = s.T.y; w.lv_tz[v] = s.T.z;
+                w.lv_prim[v] = s.prim | kLightFlag;
+                w.nlight[b] = slot + 1;
+            }
+        }
     }
+    retire(w, valid, b, dn);   // scatter() is false: the subpath always ends on a light
 }
 
 // ------------------------------------------------------------------ K2: lambertian (material.h:42-67)
-__global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f, WF w, int64_t L0, int nxt) {
+__global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f, WF w, int nxt, int dn) {
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
     bool live = false;
     uint32_t pid = 0;
-    if (idx < w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN]) {
+    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN];
+    if (valid) {
         pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx];
         const Surf s = load_surf(sc, w, pid);
         const Mat m = sc.mats[sc.shade[s.prim].mat];
@@ -358,7 +392,7 @@ __global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f,
         if (remaining > 0) {
             // scatter: cosine_pdf about the face-forwarded normal (material.h:47-52, pdf.h:32-47, onb.h:6-11)
             Rng rng;
-            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, L0 + b).sid, w.draws[pid]);
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, w.draws[pid]);
             const Onb uvw(s.n);
             const D3 sd = uvw.transform(random_cosine_direction(rng));
             const double pdf_value = fmax(0.0, dot(unit(sd), uvw.a2) / kPi);   // pdf.h:37-40
@@ -373,16 +407,18 @@ __global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f,
     }
     const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
+    retire(w, valid && !live, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
 }
 
 // ------------------------------------------------------------------ K2: metal (material.h:69-90)
 // Always a delta vertex, even when fuzzy (material.h:85): never stored, never connected.  The fuzzed
 // direction is not rejected when it points below the surface (material.h:74-82).
-__global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, WF w, int64_t L0, int nxt) {
+__global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, WF w, int nxt, int dn) {
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
     bool live = false;
     uint32_t pid = 0;
-    if (idx < w.counters[C_MAT0 + BDPT_MAT_METAL]) {
+    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_METAL];
+    if (valid) {
         pid = w.q_mat[BDPT_MAT_METAL][idx];
         const int32_t remaining = w.remaining[pid] - 1;
         if (remaining > 0) {
@@ -391,7 +427,7 @@ __global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, W
             const bool is_cam = pid < uint32_t(w.B);
             const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
             Rng rng;
-            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, L0 + b).sid, w.draws[pid]);
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, w.draws[pid]);
             D3 refl = reflect(s.d, s.n);
             refl = unit(refl) + (m.param * random_unit_vector(rng));
             const D3 T = s.T * mk(m.r, m.g, m.b);                              // camera.h:355
@@ -401,14 +437,16 @@ __global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, W
     }
     const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
+    retire(w, valid && !live, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
 }
 
 // ------------------------------------------------------------------ K2: dielectric (material.h:92-131)
-__global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame f, WF w, int64_t L0, int nxt) {
+__global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame f, WF w, int nxt, int dn) {
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
     bool live = false;
     uint32_t pid = 0;
-    if (idx < w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC]) {
+    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
+    if (valid) {
         pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx];
         const int32_t remaining = w.remaining[pid] - 1;
         if (remaining > 0) {
@@ -417,7 +455,7 @@ __global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame
             const bool is_cam = pid < uint32_t(w.B);
             const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
             Rng rng;
-            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, L0 + b).sid, w.draws[pid]);
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, w.draws[pid]);
             const double ri = s.front ? (1.0 / m.param) : m.param;
             const D3 ud = unit(s.d);
             const double cos_theta = fmin(dot(-ud, s.n), 1.0);
@@ -437,13 +475,14 @@ __global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame
     }
     const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
+    retire(w, valid && !live, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
 }
 
-// ------------------------------------------------------------------ vertex-count reduction
-__global__ void __launch_bounds__(256) k_counts(WF w, int64_t nb) {
-    const int64_t b = int64_t(blockIdx.x) * 256 + threadIdx.x;
+// ------------------------------------------------------------------ vertex-count reduction over the done list
+__global__ void __launch_bounds__(256) k_counts(WF w, int dn) {
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
     uint32_t nc = 0, nl = 0;
-    if (b < nb) { nc = w.ncam[b]; nl = w.nlight[b]; }
+    if (i < w.counters[C_DONE0 + dn]) { const uint32_t b = w.q_slots[dn][i]; nc = w.ncam[b]; nl = w.nlight[b]; }
     const uint32_t mc = __reduce_max_sync(0xFFFFFFFFu, nc), ml = __reduce_max_sync(0xFFFFFFFFu, nl);
     const uint32_t sc_ = __reduce_add_sync(0xFFFFFFFFu, nc), sl = __reduce_add_sync(0xFFFFFFFFu, nl);
     const uint32_t pairs = __reduce_add_sync(0xFFFFFFFFu, nc * nl);   // <= 32 * depth^2
@@ -457,15 +496,16 @@ __global__ void __launch_bounds__(256) k_counts(WF w, int64_t nb) {
 }
 
 // ------------------------------------------------------------------ K3
-// connect_vertices (camera.h:440-475) for camera-vertex slots [k0, k1) of every sample against all of
-// the sample's light vertices.  Everything except visible() is evaluated here; pairs that survive the
+// connect_vertices (camera.h:440-475) for camera-vertex slots [k0, k1) of every finished sample (the done
+// list) against all of the sample's light vertices.  Everything except visible() is evaluated here; pairs that survive the
 // early-outs become shadow rays carrying their finished contribution.
-__global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w, int64_t L0, int64_t nb, int k0, int k1) {
+__global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ done, int64_t nb,
+                                                   int k0, int k1) {
     const int64_t idx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int64_t total = int64_t(k1 - k0) * nb;
     const bool valid = idx < total;
     const int k = valid ? k0 + int(idx / nb) : 0;
-    const int64_t b = valid ? idx % nb : 0;
+    const int64_t b = valid ? int64_t(done[idx % nb]) : 0;
     uint32_t nl = 0;
     D3 cp = mk(0, 0, 0), ctf = mk(0, 0, 0), cn = mk(0, 0, 0);
     uint32_t pix = 0;
@@ -476,13 +516,14 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
         ctf = mk(w.cv_fx[v], w.cv_fy[v], w.cv_fz[v]);
         const TriShade sh = sc.shade[w.cv_prim[v]];
         cn = mk(sh.nx, sh.ny, sh.nz);   // |dot| below makes the face flip irrelevant (camera.h:451-452)
-        pix = decode_sample(f, L0 + b).pix;
+        pix = decode_sample(f, w.sample[b]).pix;
     }
     const uint32_t nl_max = __reduce_max_sync(0xFFFFFFFFu, nl);
     for (uint32_t m = 0; m < nl_max; ++m) {
         bool emit = false;
         D3 so = mk(0, 0, 0), sd = mk(0, 0, 0), contrib = mk(0, 0, 0);
         double max_t = 0;
+        uint32_t far_prim = 0;
         if (m < nl) {
             const size_t v = size_t(m) * size_t(w.B) + size_t(b);
             const D3 lp = mk(w.lv_px[v], w.lv_py[v], w.lv_pz[v]);
@@ -491,7 +532,8 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
             if (dist2 > 0) {
                 const D3 du = unit(dir);
                 const uint32_t lprim = w.lv_prim[v];
-                const TriShade lsh = sc.shade[lprim & ~kLightFlag];
+                far_prim = lprim & ~kLightFlag;
+                const TriShade lsh = sc.shade[far_prim];
                 const D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
                 const double cos_cam = fabs(dot(cn, du));
                 const double cos_light = fabs(dot(ln, -du));
@@ -524,6 +566,7 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                 w.s_tmax[slot] = max_t;
                 w.s_cx[slot] = contrib.x; w.s_cy[slot] = contrib.y; w.s_cz[slot] = contrib.z;
                 w.s_pix[slot] = pix;
+                w.s_far[slot] = far_prim;
             } else {
                 w.counters[C_OVERFLOW] = 1;
             }
@@ -543,11 +586,33 @@ __device__ __forceinline__ RayD load_shadow_ray(const WF& w, uint32_t idx) {
     return r;
 }
 
+// Stage 1 (fast flavour): the far-endpoint test settles ~80 % of the segments with one triangle
+// and one box; the rest are compacted into q_shadow_live so that stage 2's warps are full of rays that
+// really walk the tree.
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock) k_shadow_pre(SceneView sc, WF w, unsigned long long* stats) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    if (idx == 0) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)w.counters[C_SHADOW]);
+    bool live = false;
+    if (idx < w.counters[C_SHADOW]) {
+        const RayD r = load_shadow_ray(w, idx);
+        TravStats ts{0, 0};
+        live = !far_endpoint_occludes(sc, r, w.s_far[idx], STATS ? &ts : nullptr);
+        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+    }
+    const uint32_t slot = warp_append(w.counters + C_SHADOW_LIVE, live);
+    if (live) w.q_shadow_live[slot] = idx;
+}
+
 template <int BVH, bool STATS>
 __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* film, unsigned long long* stats) {
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
     bool defer = false;
-    if (idx < w.counters[C_SHADOW]) {
+    uint32_t idx = i;
+    if (BVH == BDPT_BVH_REFERENCE && i == 0)
+        atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)w.counters[C_SHADOW]);
+    if (i < w.counters[BVH == BDPT_BVH_REFERENCE ? C_SHADOW : C_SHADOW_LIVE]) {
+        if (BVH != BDPT_BVH_REFERENCE) idx = w.q_shadow_live[i];
         const RayD r = load_shadow_ray(w, idx);
         HitD h;
         bool found;
@@ -559,7 +624,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* f
             found = rc == TR_HIT;
             defer = rc == TR_DEFER;
         }
-        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
+        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
         if (!found && !defer) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
     }
     if (BVH != BDPT_BVH_REFERENCE) {
@@ -571,13 +636,14 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* f
 template <bool STATS>
 __global__ void __launch_bounds__(kBlock) k_shadow_exact(SceneView sc, WF w, double* film, unsigned long long* stats) {
     const uint32_t n = w.counters[C_EXACT_SHADOW];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(&stats[ST_DEFER_SHADOW], (unsigned long long)n);
     for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
         const uint32_t idx = w.q_exact_s[i];
         const RayD r = load_shadow_ray(w, idx);
         HitD h;
         TravStats ts{0, 0};
         const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
-        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
+        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
         if (!found) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
     }
 }
@@ -603,10 +669,13 @@ void carve(WF& w, char* base) {
     double** pd[] = {&w.ox, &w.oy, &w.oz, &w.dx, &w.dy, &w.dz, &w.tx, &w.ty, &w.tz, &w.hit_t};
     for (double** q : pd) *q = c.take<double>(P);
     w.draws = c.take<uint32_t>(P); w.hit_prim = c.take<uint32_t>(P); w.remaining = c.take<int32_t>(P);
+    w.sample = c.take<int64_t>(B); w.live = c.take<uint32_t>(B);
+    for (int k = 0; k < 2; ++k) w.q_slots[k] = c.take<uint32_t>(B);
     for (int k = 0; k < 2; ++k) w.q_active[k] = c.take<uint32_t>(P);
     for (int k = 0; k < 4; ++k) w.q_mat[k] = c.take<uint32_t>(P);
-    w.q_exact = c.take<uint32_t>(P);
+    for (int k = 0; k < 2; ++k) w.q_exact[k] = c.take<uint32_t>(P);
     w.q_exact_s = c.take<uint32_t>(S);
+    w.q_shadow_live = c.take<uint32_t>(S);
     w.counters = c.take<uint32_t>(C_COUNT);
     double** cv[] = {&w.cv_px, &w.cv_py, &w.cv_pz, &w.cv_fx, &w.cv_fy, &w.cv_fz, &w.lv_px, &w.lv_py, &w.lv_pz, &w.lv_tx, &w.lv_ty, &w.lv_tz};
     for (double** q : cv) *q = c.take<double>(V);
@@ -614,7 +683,7 @@ void carve(WF& w, char* base) {
     w.ncam = c.take<uint32_t>(B); w.nlight = c.take<uint32_t>(B);
     double** sq[] = {&w.s_ox, &w.s_oy, &w.s_oz, &w.s_dx, &w.s_dy, &w.s_dz, &w.s_tmax, &w.s_cx, &w.s_cy, &w.s_cz};
     for (double** q : sq) *q = c.take<double>(S);
-    w.s_pix = c.take<uint32_t>(S);
+    w.s_pix = c.take<uint32_t>(S); w.s_far = c.take<uint32_t>(S);
     w.bytes = c.off + 256;
 }
 
@@ -695,6 +764,7 @@ struct Worker {
     KernelTimers tm;
     uint32_t* hc = nullptr;              // pinned read-back of the device counters
     uint64_t rays_closest = 0, rays_shadow = 0, cam_verts = 0, light_verts = 0, launches = 0, samples = 0;
+    uint64_t deferred_closest = 0, deferred_shadow = 0;
     double kernel_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     uint64_t kernel_launches[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     std::string err;
@@ -718,11 +788,14 @@ struct Job {
     SceneView sc; Frame f; bdpt_render_opts o;
     int64_t total; double* film; unsigned long long* d_stats;
     size_t smem; unsigned exact_grid; int device; int n_workers;
-    int64_t B;   // samples per wavefront (every worker's workspace holds at least this many)
+    int64_t B;                       // sample slots per wavefront (every worker's workspace holds at least this many)
+    std::atomic<int64_t>* next;      // next sample of this call not yet handed to a worker
 };
 
-// all wavefronts of one worker: batches id, id + n_workers, ...
-void run_worker(const Job& J, Worker& wk, int id) {
+// One worker: a wavefront of B slots, refilled from the call's shared sample counter until it runs dry.
+// Iteration = refill free slots -> trace every live subpath one bounce -> shade -> (host reads the counter
+// block: the only sync) -> connect + shadow the samples that finished -> their slots become the free list.
+void run_worker(const Job& J, Worker& wk, int /*id*/) {
     cudaSetDevice(J.device);
     const SceneView& sc = J.sc; const Frame& f = J.f; const bdpt_render_opts& o = J.o;
     WF& wf = wk.wf;
@@ -731,76 +804,92 @@ void run_worker(const Job& J, Worker& wk, int id) {
     uint32_t* hc = wk.hc;
     const bool want_stats = (o.flags & BDPT_RENDER_STATS) != 0;
     const size_t smem = J.smem;
-    for (int64_t L0 = int64_t(id) * J.B; L0 < J.total; L0 += J.B * J.n_workers) {
-        const int64_t nb = std::min<int64_t>(J.B, J.total - L0);
-        WK_CUDA(cudaMemsetAsync(wf.counters, 0, C_COUNT * sizeof(uint32_t), st));
-        tm.begin(KT_GENERATE, st);
-        k_generate<<<grid_for(nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb);
-        tm.end(KT_GENERATE, st);
-        wk.launches += 1;
-        WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-        WK_CUDA(cudaStreamSynchronize(st));
-        int cur = 0;
-        uint32_t n_active = hc[C_ACTIVE0];
-        while (n_active > 0) {
-            const int nxt = cur ^ 1;
-            WK_CUDA(cudaMemsetAsync(wf.counters + C_ACTIVE0 + nxt, 0, sizeof(uint32_t), st));
-            WK_CUDA(cudaMemsetAsync(wf.counters + C_MAT0, 0, 4 * sizeof(uint32_t), st));
-            WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT, 0, sizeof(uint32_t), st));
-            const unsigned g = grid_for(n_active, kBlock);
-            tm.begin(KT_TRACE, st);
-#define BDPT_TP(B, S) k_trace_paths<B, S><<<g, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, L0, J.film, J.d_stats)
-            if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
-            else {
-                if (want_stats) BDPT_TP(BDPT_BVH_FAST, true); else BDPT_TP(BDPT_BVH_FAST, false);
-                if (want_stats) k_trace_exact<true><<<J.exact_grid, kBlock, smem, st>>>(sc, f, wf, L0, J.film, J.d_stats);
-                else k_trace_exact<false><<<J.exact_grid, kBlock, smem, st>>>(sc, f, wf, L0, J.film, J.d_stats);
-                wk.launches += 1;
-            }
-#undef BDPT_TP
-            tm.end(KT_TRACE, st);
-            tm.begin(KT_SHADE, st);
-            k_shade_light<<<g, kBlock, 0, st>>>(sc, f, wf, L0, J.film);
-            k_shade_lambert<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
-            k_shade_metal<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
-            k_shade_dielectric<<<g, kBlock, 0, st>>>(sc, f, wf, L0, nxt);
-            tm.end(KT_SHADE, st);
-            wk.launches += 5;
-            wk.rays_closest += n_active;
-            WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-            WK_CUDA(cudaStreamSynchronize(st));
-            n_active = hc[C_ACTIVE0 + nxt];
-            cur = nxt;
+    WK_CUDA(cudaMemsetAsync(wf.counters, 0, C_COUNT * sizeof(uint32_t), st));
+    int cur = 0, dn = 0, ex = 0;
+    int64_t n_active = 0, n_free = J.B;
+    uint32_t n_def = 0;              // rays deferred by the previous iteration's trace launch
+    bool first = true;
+    for (;;) {
+        int64_t ngen = 0, gen_base = 0;
+        if (n_free > 0) {
+            gen_base = J.next->fetch_add(n_free);
+            ngen = std::max<int64_t>(0, std::min<int64_t>(n_free, J.total - gen_base));
         }
-        // connections
-        k_counts<<<grid_for(nb, 256), 256, 0, st>>>(wf, nb);
-        wk.launches += 1;
+        if (ngen == 0 && n_active == 0 && n_def == 0) break;
+        const int nxt = cur ^ 1;
+        // counters of this iteration's outputs (ACTIVE[cur] keeps the survivors of the last one)
+        WK_CUDA(cudaMemsetAsync(wf.counters + C_ACTIVE0 + nxt, 0, sizeof(uint32_t), st));
+        WK_CUDA(cudaMemsetAsync(wf.counters + C_MAT0, 0, (C_EXACT_SHADOW + 1 - C_MAT0) * sizeof(uint32_t), st));
+        WK_CUDA(cudaMemsetAsync(wf.counters + C_DONE0 + dn, 0, sizeof(uint32_t), st));
+        WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT0 + ex, 0, sizeof(uint32_t), st));
+        if (ngen > 0) {
+            tm.begin(KT_GENERATE, st);
+            k_generate<<<grid_for(ngen, kBlock), kBlock, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
+            tm.end(KT_GENERATE, st);
+            wk.launches += 1;
+            wk.samples += uint64_t(ngen);
+        }
+        first = false;
+        const unsigned g = grid_for(n_active + 2 * ngen, kBlock);   // upper bound; the kernels read the device count
+        const unsigned gd = n_def ? grid_for(n_def, kBlock) : 0u;
+        tm.begin(KT_TRACE, st);
+#define BDPT_TP(B, S) k_trace_paths<B, S><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.film, J.d_stats)
+        if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
+        else { if (want_stats) BDPT_TP(BDPT_BVH_FAST, true); else BDPT_TP(BDPT_BVH_FAST, false); }
+#undef BDPT_TP
+        tm.end(KT_TRACE, st);
+        tm.begin(KT_SHADE, st);
+        k_shade_light<<<g, kBlock, 0, st>>>(sc, f, wf, dn, J.film);
+        k_shade_lambert<<<g, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
+        k_shade_metal<<<g, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
+        k_shade_dielectric<<<g, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
+        k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
+        tm.end(KT_SHADE, st);
+        wk.launches += 6;
         WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
         WK_CUDA(cudaStreamSynchronize(st));
+        wk.rays_closest += hc[C_ACTIVE0 + cur];
+        n_def = hc[C_EXACT0 + ex];
+        wk.deferred_closest += n_def;
+        ex ^= 1;
+        n_active = hc[C_ACTIVE0 + nxt];
+        const int64_t n_done = hc[C_DONE0 + dn];
         const int max_nc = int(hc[C_MAXNC]), max_nl = int(hc[C_MAXNL]);
         wk.cam_verts += hc[C_SUMNC]; wk.light_verts += hc[C_SUMNL];
-        if (max_nc > 0 && max_nl > 0) {
+        // connections of the samples that finished in this iteration
+        if (n_done > 0 && max_nc > 0 && max_nl > 0) {
             // every (camera vertex, light vertex) pair is at most one shadow ray: if they all fit, one round
             const uint64_t pairs = uint64_t(hc[C_PAIRS_LO]) | (uint64_t(hc[C_PAIRS_HI]) << 32);
-            const int slots_per_round = pairs <= uint64_t(wf.scap) ? max_nc : int(std::max<int64_t>(1, wf.scap / (nb * int64_t(max_nl))));
+            const int slots_per_round = pairs <= uint64_t(wf.scap) ? max_nc : int(std::max<int64_t>(1, wf.scap / (n_done * int64_t(max_nl))));
             for (int k0 = 0; k0 < max_nc; k0 += slots_per_round) {
                 const int k1 = std::min(max_nc, k0 + slots_per_round);
                 WK_CUDA(cudaMemsetAsync(wf.counters + C_SHADOW, 0, sizeof(uint32_t), st));
                 WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT_SHADOW, 0, sizeof(uint32_t), st));
+                WK_CUDA(cudaMemsetAsync(wf.counters + C_SHADOW_LIVE, 0, sizeof(uint32_t), st));
                 tm.begin(KT_CONNECT, st);
-                k_connect<<<grid_for(int64_t(k1 - k0) * nb, kBlock), kBlock, 0, st>>>(sc, f, wf, L0, nb, k0, k1);
+                k_connect<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, wf.q_slots[dn], n_done, k0, k1);
                 tm.end(KT_CONNECT, st);
-                WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-                WK_CUDA(cudaStreamSynchronize(st));
                 wk.launches += 1;
-                if (hc[C_OVERFLOW]) { wk.err = "shadow queue overflow"; wk.rc = BDPT_ERR_STATE; return; }
-                const uint32_t ns = hc[C_SHADOW];
-                if (ns) {
+                // one round: size the shadow launch by the pair count (an upper bound) and skip the read-back
+                uint32_t ns_bound = uint32_t(std::min<uint64_t>(pairs, uint64_t(wf.scap)));
+                const bool single = slots_per_round >= max_nc;
+                if (!single) {
+                    WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                    WK_CUDA(cudaStreamSynchronize(st));
+                    if (hc[C_OVERFLOW]) { wk.err = "shadow queue overflow"; wk.rc = BDPT_ERR_STATE; return; }
+                    ns_bound = hc[C_SHADOW];
+                }
+                if (ns_bound) {
                     tm.begin(KT_SHADOW, st);
-#define BDPT_SH(B, S) k_shadow<B, S><<<grid_for(ns, kBlock), kBlock, smem, st>>>(sc, wf, J.film, J.d_stats)
+#define BDPT_SH(B, S) k_shadow<B, S><<<grid_for(ns_bound, kBlock), kBlock, smem, st>>>(sc, wf, J.film, J.d_stats)
                     if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_SH(BDPT_BVH_REFERENCE, true); else BDPT_SH(BDPT_BVH_REFERENCE, false); }
                     else {
+                        if (want_stats) k_shadow_pre<true><<<grid_for(ns_bound, kBlock), kBlock, 0, st>>>(sc, wf, J.d_stats);
+                        else k_shadow_pre<false><<<grid_for(ns_bound, kBlock), kBlock, 0, st>>>(sc, wf, J.d_stats);
+                        wk.launches += 1;
                         if (want_stats) BDPT_SH(BDPT_BVH_FAST, true); else BDPT_SH(BDPT_BVH_FAST, false);
+                        tm.end(KT_SHADOW, st);
+                        tm.begin(KT_SHADOW_EXACT, st);
                         if (want_stats) k_shadow_exact<true><<<J.exact_grid, kBlock, smem, st>>>(sc, wf, J.film, J.d_stats);
                         else k_shadow_exact<false><<<J.exact_grid, kBlock, smem, st>>>(sc, wf, J.film, J.d_stats);
                         wk.launches += 1;
@@ -808,14 +897,17 @@ void run_worker(const Job& J, Worker& wk, int id) {
 #undef BDPT_SH
                     tm.end(KT_SHADOW, st);
                     wk.launches += 1;
-                    wk.rays_shadow += ns;
                 }
             }
         }
-        wk.samples += uint64_t(nb);
-        WK_CUDA(cudaStreamSynchronize(st));
-        tm.collect(wk.kernel_ms, wk.kernel_launches);
+        n_free = n_done;
+        dn ^= 1;
+        cur = nxt;
     }
+    WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    WK_CUDA(cudaStreamSynchronize(st));
+    wk.rays_shadow += uint64_t(hc[C_SHADOW_TOTAL]) | (uint64_t(hc[C_SHADOW_TOTAL + 1]) << 32);
+    tm.collect(wk.kernel_ms, wk.kernel_launches);
     WK_CUDA(cudaEventRecord(wk.done, st));
 }
 
@@ -861,11 +953,10 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 
     // wavefront size and how many wavefronts are kept in flight
     int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 19);
-    B = std::min<int64_t>(B, total);
     B = std::min<int64_t>(B, int64_t(1) << 30);
-    const int64_t n_batches = (total + B - 1) / B;
     int S = o.streams > 0 ? o.streams : 4;
-    S = int(std::min<int64_t>(std::min(S, 16), n_batches));
+    S = int(std::min<int64_t>(std::min(S, 16), std::max<int64_t>(1, total / 8192)));
+    B = std::min<int64_t>(B, (total + S - 1) / S);   // every worker gets slots to fill
     Workers* ws = static_cast<Workers*>(ctx->wf);
     if (!ws) { ws = new Workers(); ctx->wf = ws; }
     while (int(ws->w.size()) < S) ws->w.push_back(new Worker());
@@ -880,7 +971,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             if (wk.wf.base) { BDPT_CUDA(ctx, cudaStreamSynchronize(wk.stream)); cudaFree(wk.wf.base); }
             std::memset(&wk.wf, 0, sizeof(WF));
             wk.wf.B = B; wk.wf.depth = f.depth;
-            wk.wf.scap = std::max<int64_t>(B * 32, int64_t(f.depth) * B);   // >= one camera slot against every light vertex
+            wk.wf.scap = std::max<int64_t>(B * 8, int64_t(f.depth) * B);   // >= one camera slot against every light vertex
             wk.wf.scap = std::min<int64_t>(wk.wf.scap, int64_t(0xFFFFFFF0u));
             carve(wk.wf, nullptr);
             void* base = nullptr;
@@ -890,6 +981,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             carve(wk.wf, static_cast<char*>(base));
         }
         wk.rays_closest = wk.rays_shadow = wk.cam_verts = wk.light_verts = wk.launches = wk.samples = 0;
+        wk.deferred_closest = wk.deferred_shadow = 0;
         for (int k = 0; k < 8; ++k) { wk.kernel_ms[k] = 0.0; wk.kernel_launches[k] = 0; }
         wk.err.clear(); wk.rc = BDPT_OK;
     }
@@ -901,6 +993,8 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     J.smem = levels * kBlock * sizeof(StackEntry);
     J.exact_grid = 148 * 2;
     J.device = ctx->device; J.n_workers = S; J.B = B;
+    std::atomic<int64_t> next_sample{0};
+    J.next = &next_sample;
 
     // the film clear (and anything else queued on the context stream) happens-before the workers
     BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
@@ -927,6 +1021,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
         const Worker& wk = *ws->w[i];
         cur_stats[ST_RAYS_CLOSEST] += wk.rays_closest; cur_stats[ST_RAYS_SHADOW] += wk.rays_shadow;
         cur_stats[ST_CAM_VERTS] += wk.cam_verts; cur_stats[ST_LIGHT_VERTS] += wk.light_verts;
+        cur_stats[ST_DEFER_CLOSEST] += wk.deferred_closest; cur_stats[ST_DEFER_SHADOW] += wk.deferred_shadow;
         ctx->launches += wk.launches; ctx->samples += wk.samples;
         for (int k = 0; k < 8; ++k) { ctx->kernel_ms[k] += wk.kernel_ms[k]; ctx->kernel_launches[k] += wk.kernel_launches[k]; }
     }

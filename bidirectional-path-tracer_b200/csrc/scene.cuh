@@ -61,6 +61,7 @@ struct SceneView {
     const uint32_t* dfs_rank;     // prim ID -> last position in the reference DFS leaf order (tie rule)
     const int32_t* ref_parent;    // reference node -> parent node (-1 for the root)
     const int32_t* prim_leaf;     // prim ID -> reference leaf node holding it
+    const double* chain_box;      // prim ID -> 6 doubles, intersection of its reference chain's boxes
     const TriGeom* tris;
     const TriShade* shade;
     const Mat* mats;

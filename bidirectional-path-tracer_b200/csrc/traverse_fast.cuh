@@ -26,6 +26,44 @@ __device__ __forceinline__ void slab_fast(T lo, T hi, T o, T inv, T& tn, T& tf) 
 
 enum { TR_MISS = 0, TR_HIT = 1, TR_DEFER = 2 };
 
+// Does the reference's traversal REACH triangle `prim` with the untouched bound [tmin, tmax], i.e. does
+// every box on its root-to-leaf chain pass aabb::hit?  One test of the chain's intersection box accepts;
+// only when that fails is the chain walked (host_scene.cu: build_ref_bvh).
+__device__ __forceinline__ bool reference_reaches(const SceneView& sc, uint32_t prim, const RayD& r, const D3& adinv,
+                                                  uint32_t& walk) {
+    const double2* q = reinterpret_cast<const double2*>(sc.chain_box + 6 * size_t(prim));
+    const double2 bx = __ldg(q), by = __ldg(q + 1), bz = __ldg(q + 2);
+    RefNode cb;
+    cb.lo_x = bx.x; cb.hi_x = bx.y; cb.lo_y = by.x; cb.hi_y = by.y; cb.lo_z = bz.x; cb.hi_z = bz.y;
+    ++walk;
+    if (box_hit(cb, r.o, adinv, r.tmin, r.tmax)) return true;
+    int32_t node = __ldg(sc.prim_leaf + prim);
+    while (node >= 0) {
+        const RefNode nd = load_ref_node(sc.ref_nodes + node);
+        ++walk;
+        if (!box_hit(nd, r.o, adinv, r.tmin, r.tmax)) return false;
+        node = __ldg(sc.ref_parent + node);
+    }
+    return true;
+}
+
+// Shadow rays of connect_vertices end ON a surface: max_t = dist - 0.001 lands on the far vertex's own
+// triangle, which therefore occludes most segments.  Test that triangle before walking
+// anything: if its t is inside [tmin, tmax] and the reference reaches it, the answer is "occluded".
+// Anything else (outside the interval, not reached, zero direction component) decides nothing.
+__device__ __forceinline__ bool far_endpoint_occludes(const SceneView& sc, const RayD& r, uint32_t prim, TravStats* st) {
+    if (r.d.x == 0.0 || r.d.y == 0.0 || r.d.z == 0.0) return false;
+    double t, u, v;
+    if (st) ++st->tris;
+    if (!tri_candidate(sc.tris + prim, r.o, r.d, t, u, v)) return false;
+    if (!(r.tmin <= t && t <= r.tmax)) return false;
+    const D3 adinv = mk(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
+    uint32_t walk = 0;
+    const bool reached = reference_reaches(sc, prim, r, adinv, walk);
+    if (st) st->nodes += walk;
+    return reached;
+}
+
 // traversal stack entry: deferred child + its box-entry distance (fp32, a lower bound), so that a
 // child made unreachable by a closer hit found in the meantime is dropped at pop time without a fetch
 typedef unsigned long long StackEntry;
@@ -162,15 +200,7 @@ __device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& 
             const D3 adinv = mk(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
             uint32_t walk = 0;
             for (int k = 0; k < n_edge && !found; ++k) {
-                int32_t node = __ldg(sc.prim_leaf + edge_prim[k]);
-                bool reached = true;
-                while (node >= 0) {
-                    const RefNode nd = load_ref_node(sc.ref_nodes + node);
-                    ++walk;
-                    if (!box_hit(nd, r.o, adinv, r.tmin, r.tmax)) { reached = false; break; }
-                    node = __ldg(sc.ref_parent + node);
-                }
-                if (reached) { hit.prim = edge_prim[k]; hit.t = r.tmax; hit.u = 0.0; hit.v = 0.0; found = true; }
+                if (reference_reaches(sc, edge_prim[k], r, adinv, walk)) { hit.prim = edge_prim[k]; hit.t = r.tmax; hit.u = 0.0; hit.v = 0.0; found = true; }
             }
             if (STATS && st) st->nodes += walk;
             return found ? TR_HIT : TR_MISS;

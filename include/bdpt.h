@@ -88,11 +88,16 @@ typedef struct {
     uint64_t light_vertices;
     /* bdpt_render with BDPT_RENDER_STATS: traversal work split by ray kind */
     uint64_t nodes_closest, tris_closest, nodes_shadow, tris_shadow;
+    /* ... and the most expensive single ray of each kind (nodes + triangles it touched): the latency floor of a launch */
+    uint64_t max_work_closest, max_work_shadow;
+    /* rays the fast traversal handed to the reference-exact kernels (ties, knife edges, zero direction components) */
+    uint64_t deferred_closest, deferred_shadow;
 } bdpt_stats_t;
 
 /* Device time per kernel class of bdpt_render since the last bdpt_stats_reset, from CUDA event pairs on
  * the context's stream around each launch (ms[i], launches[i]; i = BDPT_KT_*). */
-enum { BDPT_KT_GENERATE = 0, BDPT_KT_TRACE = 1, BDPT_KT_SHADE = 2, BDPT_KT_CONNECT = 3, BDPT_KT_SHADOW = 4, BDPT_KT_COUNT = 5 };
+enum { BDPT_KT_GENERATE = 0, BDPT_KT_TRACE = 1, BDPT_KT_SHADE = 2, BDPT_KT_CONNECT = 3, BDPT_KT_SHADOW = 4,
+       BDPT_KT_TRACE_EXACT = 5, BDPT_KT_SHADOW_EXACT = 6 /* the deferred rays' reference-topology kernels */, BDPT_KT_COUNT = 7 };
 
 typedef struct {
     uint64_t seed;
