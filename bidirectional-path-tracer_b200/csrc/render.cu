@@ -50,14 +50,32 @@ struct Frame {           // camera.h:148-197 derived values + this call's sample
     int64_t npix;        // rows * W
 };
 
+// Subpath state and path vertices are gathered through queues of arbitrary ids, so they are stored as
+// records (AoS): one thread touches whole 32-byte sectors of its own record instead of one 8-byte word in
+// each of a dozen arrays.
+struct __align__(32) PathRec {   // 96 B = 3 sectors
+    double ox, oy, oz, dx, dy, dz;   // ray of the next world.hit (sectors 0-1: all the trace kernel reads)
+    double tx, ty, tz;               // throughput
+    double hit_t;
+    uint32_t draws, hit_prim;
+    int32_t remaining;
+    uint32_t pad;
+};
+static_assert(sizeof(PathRec) == 96, "PathRec must be 96 bytes");
+struct __align__(32) VertRec {   // 64 B = 2 sectors
+    double px, py, pz;
+    double ax, ay, az;               // camera vertex: throughput * f (camera.h:471); light vertex: throughput
+    uint32_t prim;                   // light vertex: bit 31 = is_light (camera.h:348)
+    uint32_t pad[3];
+};
+static_assert(sizeof(VertRec) == 64, "VertRec must be 64 bytes");
+
 struct WF {              // wavefront workspace, all device pointers
     int64_t B;           // batch capacity in samples
     int depth;
     int64_t scap;        // shadow queue capacity
     // subpath state, index = path id (camera subpath of sample b: b; light subpath: B + b)
-    double *ox, *oy, *oz, *dx, *dy, *dz, *tx, *ty, *tz, *hit_t;
-    uint32_t *draws, *hit_prim;
-    int32_t* remaining;
+    PathRec* path;
     // per slot: the sample it holds (index into this call's sample list) and how many of its subpaths run
     int64_t* sample;
     uint32_t* live;
@@ -66,11 +84,8 @@ struct WF {              // wavefront workspace, all device pointers
     uint32_t* q_shadow_live;         // shadow rays the far-endpoint test did not settle (indices into the shadow queue)
     uint32_t *q_exact[2], *q_exact_s;   // rays deferred to the reference-exact traversal (path ids, ping-pong / shadow slots)
     uint32_t* counters;
-    // vertex pools, index = slot * B + b
-    double *cv_px, *cv_py, *cv_pz, *cv_fx, *cv_fy, *cv_fz;   // camera vertex: p, throughput * f (camera.h:471)
-    uint32_t* cv_prim;
-    double *lv_px, *lv_py, *lv_pz, *lv_tx, *lv_ty, *lv_tz;   // light vertex: p, throughput
-    uint32_t* lv_prim;                                       // bit 31: is_light (camera.h:348)
+    // vertex pools, index = b * depth + slot (a sample's vertices are contiguous)
+    VertRec *cv, *lv;
     uint32_t *ncam, *nlight;
     // shadow queue
     double *s_ox, *s_oy, *s_oz, *s_dx, *s_dy, *s_dz, *s_tmax, *s_cx, *s_cy, *s_cz;
@@ -96,6 +111,25 @@ __device__ __forceinline__ void film_add(double* film, uint32_t pix, D3 c) {
     atomicAdd(film + 3 * size_t(pix), c.x);
     atomicAdd(film + 3 * size_t(pix) + 1, c.y);
     atomicAdd(film + 3 * size_t(pix) + 2, c.z);
+}
+
+// 16-byte vector accessors of the records
+__device__ __forceinline__ void store_path(PathRec* r, D3 o, D3 d, D3 T, uint32_t draws, int32_t remaining) {
+    double2* q = reinterpret_cast<double2*>(r);
+    q[0] = make_double2(o.x, o.y); q[1] = make_double2(o.z, d.x); q[2] = make_double2(d.y, d.z);
+    q[3] = make_double2(T.x, T.y); q[4] = make_double2(T.z, 0.0);
+    reinterpret_cast<int4*>(r)[5] = make_int4(int(draws), -1, remaining, 0);
+}
+__device__ __forceinline__ void store_vertex(VertRec* r, D3 p, D3 a, uint32_t prim) {
+    double2* q = reinterpret_cast<double2*>(r);
+    q[0] = make_double2(p.x, p.y); q[1] = make_double2(p.z, a.x); q[2] = make_double2(a.y, a.z);
+    reinterpret_cast<int4*>(r)[3] = make_int4(int(prim), 0, 0, 0);
+}
+__device__ __forceinline__ void load_vertex(const VertRec* r, D3& p, D3& a, uint32_t& prim) {
+    const double2* q = reinterpret_cast<const double2*>(r);
+    const double2 q0 = q[0], q1 = q[1], q2 = q[2];
+    prim = uint32_t(reinterpret_cast<const int4*>(r)[3].x);
+    p = mk(q0.x, q0.y, q1.x); a = mk(q1.y, q2.x, q2.y);
 }
 
 // A subpath of slot b has ended.  The thread that ends the slot's LAST live subpath appends the slot to the
@@ -145,11 +179,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
         const D3 ps = f.pixel00 + ((s.i + px) * f.du) + ((s.j + py) * f.dv);
         const D3 d = ps - f.center;
         (void)rc.next();  // ray time (camera.h:210): drawn, never used
-        w.ox[b] = f.center.x; w.oy[b] = f.center.y; w.oz[b] = f.center.z;
-        w.dx[b] = d.x; w.dy[b] = d.y; w.dz[b] = d.z;
-        w.tx[b] = 1.0; w.ty[b] = 1.0; w.tz[b] = 1.0;
-        w.draws[b] = rc.draws;
-        w.remaining[b] = f.depth;
+        store_path(w.path + b, f.center, d, mk(1.0, 1.0, 1.0), rc.draws, f.depth);
         w.ncam[b] = 0;
         cam_live = f.depth > 0;
 
@@ -178,9 +208,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
             const D3 emission = (m.type == BDPT_MAT_LIGHT) ? mk(m.r, m.g, m.b) : mk(0, 0, 0);  // emitted(front=true)
             if (len2(emission) > 0) {
                 const D3 T0 = mk(1.0, 1.0, 1.0) / fmax(pdf, 1e-8);
-                w.lv_px[b] = pos.x; w.lv_py[b] = pos.y; w.lv_pz[b] = pos.z;
-                w.lv_tx[b] = T0.x; w.lv_ty[b] = T0.y; w.lv_tz[b] = T0.z;
-                w.lv_prim[b] = prim | kLightFlag;
+                store_vertex(w.lv + size_t(b) * size_t(w.depth), pos, T0, prim | kLightFlag);
                 nl = 1;
                 const D3 dir = Onb(n).transform(random_cosine_direction(rl));
                 const D3 du = unit(dir);
@@ -189,11 +217,7 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
                     const double pdf_dir = fmax(cos_theta / kPi, 1e-8);
                     const D3 T = T0 * emission * (cos_theta / pdf_dir);
                     const D3 o = pos + (0.001 * n);
-                    w.ox[lp] = o.x; w.oy[lp] = o.y; w.oz[lp] = o.z;
-                    w.dx[lp] = du.x; w.dy[lp] = du.y; w.dz[lp] = du.z;
-                    w.tx[lp] = T.x; w.ty[lp] = T.y; w.tz[lp] = T.z;
-                    w.draws[lp] = rl.draws;
-                    w.remaining[lp] = f.depth - 1;
+                    store_path(w.path + lp, o, du, T, rl.draws, f.depth - 1);
                     light_live = true;
                 }
             }
@@ -218,12 +242,13 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
 __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, bool found,
                                             const HitD& h, double* film) {
     if (found) {
-        w.hit_prim[pid] = h.prim;
-        w.hit_t[pid] = h.t;
+        w.path[pid].hit_prim = h.prim;
+        w.path[pid].hit_t = h.t;
         return int(sc.mats[__ldg(&sc.shade[h.prim].mat)].type);
     }
     if (pid < uint32_t(w.B)) {
-        const D3 T = mk(w.tx[pid], w.ty[pid], w.tz[pid]);
+        const PathRec& pr = w.path[pid];
+        const D3 T = mk(pr.tx, pr.ty, pr.tz);
         const D3 c = T * f.background;
         if (c.x != 0.0 || c.y != 0.0 || c.z != 0.0) film_add(film, decode_sample(f, w.sample[pid]).pix, c);
     }
@@ -231,8 +256,10 @@ __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f,
 }
 __device__ __forceinline__ RayD load_path_ray(const WF& w, uint32_t pid) {
     RayD r;
-    r.o = mk(w.ox[pid], w.oy[pid], w.oz[pid]);
-    r.d = mk(w.dx[pid], w.dy[pid], w.dz[pid]);
+    const double2* q = reinterpret_cast<const double2*>(w.path + pid);
+    const double2 q0 = q[0], q1 = q[1], q2 = q[2];
+    r.o = mk(q0.x, q0.y, q1.x);
+    r.d = mk(q1.y, q2.x, q2.y);
     r.tmin = 0.001;
     r.tmax = __longlong_as_double(0x7FF0000000000000LL);
     return r;
@@ -299,14 +326,19 @@ __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, W
 }
 
 // hit point and face-forwarded geometric normal (ray.h:21-23, hittable.h:20-26)
-struct Surf { D3 o, d, T, p, n; bool front; uint32_t prim; };
+struct Surf { D3 o, d, T, p, n; bool front; uint32_t prim, draws; int32_t remaining; };
 __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint32_t pid) {
     Surf s;
-    s.o = mk(w.ox[pid], w.oy[pid], w.oz[pid]);
-    s.d = mk(w.dx[pid], w.dy[pid], w.dz[pid]);
-    s.T = mk(w.tx[pid], w.ty[pid], w.tz[pid]);
-    s.prim = w.hit_prim[pid];
-    const double t = w.hit_t[pid];
+    const double2* q = reinterpret_cast<const double2*>(w.path + pid);
+    const double2 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3], q4 = q[4];
+    const int4 q5 = reinterpret_cast<const int4*>(w.path + pid)[5];
+    s.o = mk(q0.x, q0.y, q1.x);
+    s.d = mk(q1.y, q2.x, q2.y);
+    s.T = mk(q3.x, q3.y, q4.x);
+    s.prim = uint32_t(q5.y);
+    s.draws = uint32_t(q5.x);
+    s.remaining = q5.z;
+    const double t = q4.y;
     s.p = s.o + t * s.d;
     const TriShade sh = sc.shade[s.prim];
     const D3 n = mk(sh.nx, sh.ny, sh.nz);
@@ -316,11 +348,7 @@ __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint
 }
 
 __device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d, D3 T, uint32_t draws, int32_t remaining) {
-    w.ox[pid] = o.x; w.oy[pid] = o.y; w.oz[pid] = o.z;
-    w.dx[pid] = d.x; w.dy[pid] = d.y; w.dz[pid] = d.z;
-    w.tx[pid] = T.x; w.ty[pid] = T.y; w.tz[pid] = T.z;
-    w.draws[pid] = draws;
-    w.remaining[pid] = remaining;
+    store_path(w.path + pid, o, d, T, draws, remaining);
 }
 
 // ------------------------------------------------------------------ K2: diffuse_light (material.h:133-147)
@@ -343,10 +371,7 @@ __global__ void __launch_bounds__(kBlock) k_shade_light(SceneView sc, Frame f, W
                 film_add(film, decode_sample(f, w.sample[b]).pix, s.T * Le);
             } else {
                 const uint32_t slot = w.nlight[b];
-                const size_t v = size_t(slot) * size_t(w.B) + b;
-                w.lv_px[v] = s.p.x; w.lv_py[v] = s.p.y; w.lv_pz[v] = s.p.z;
-                w.lv_tx[v] = s.T.x; w.lv_ty[v] = s.T.y; w.lv_tz[v] = s.T.z;
-                w.lv_prim[v] = s.prim | kLightFlag;
+                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | kLightFlag);
                 w.nlight[b] = slot + 1;
             }
         }
@@ -373,26 +398,20 @@ __global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f,
         if (len2(fr) > 0) {
             if (is_cam) {
                 const uint32_t slot = w.ncam[b];
-                const size_t v = size_t(slot) * size_t(w.B) + b;
                 const D3 tf = s.T * fr;   // camera.h:471: cam_v.throughput * f_cam
-                w.cv_px[v] = s.p.x; w.cv_py[v] = s.p.y; w.cv_pz[v] = s.p.z;
-                w.cv_fx[v] = tf.x; w.cv_fy[v] = tf.y; w.cv_fz[v] = tf.z;
-                w.cv_prim[v] = s.prim;
+                store_vertex(w.cv + size_t(b) * size_t(w.depth) + slot, s.p, tf, s.prim);
                 w.ncam[b] = slot + 1;
             } else {
                 const uint32_t slot = w.nlight[b];
-                const size_t v = size_t(slot) * size_t(w.B) + b;
-                w.lv_px[v] = s.p.x; w.lv_py[v] = s.p.y; w.lv_pz[v] = s.p.z;
-                w.lv_tx[v] = s.T.x; w.lv_ty[v] = s.T.y; w.lv_tz[v] = s.T.z;
-                w.lv_prim[v] = s.prim;
+                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim);
                 w.nlight[b] = slot + 1;
             }
         }
-        const int32_t remaining = w.remaining[pid] - 1;
+        const int32_t remaining = s.remaining - 1;
         if (remaining > 0) {
             // scatter: cosine_pdf about the face-forwarded normal (material.h:47-52, pdf.h:32-47, onb.h:6-11)
             Rng rng;
-            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, w.draws[pid]);
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, s.draws);
             const Onb uvw(s.n);
             const D3 sd = uvw.transform(random_cosine_direction(rng));
             const double pdf_value = fmax(0.0, dot(unit(sd), uvw.a2) / kPi);   // pdf.h:37-40
@@ -420,14 +439,14 @@ __global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, W
     const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_METAL];
     if (valid) {
         pid = w.q_mat[BDPT_MAT_METAL][idx];
-        const int32_t remaining = w.remaining[pid] - 1;
+        const int32_t remaining = w.path[pid].remaining - 1;
         if (remaining > 0) {
             const Surf s = load_surf(sc, w, pid);
             const Mat m = sc.mats[sc.shade[s.prim].mat];
             const bool is_cam = pid < uint32_t(w.B);
             const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
             Rng rng;
-            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, w.draws[pid]);
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, s.draws);
             D3 refl = reflect(s.d, s.n);
             refl = unit(refl) + (m.param * random_unit_vector(rng));
             const D3 T = s.T * mk(m.r, m.g, m.b);                              // camera.h:355
@@ -448,14 +467,14 @@ __global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame
     const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
     if (valid) {
         pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx];
-        const int32_t remaining = w.remaining[pid] - 1;
+        const int32_t remaining = w.path[pid].remaining - 1;
         if (remaining > 0) {
             const Surf s = load_surf(sc, w, pid);
             const Mat m = sc.mats[sc.shade[s.prim].mat];
             const bool is_cam = pid < uint32_t(w.B);
             const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
             Rng rng;
-            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, w.draws[pid]);
+            rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, s.draws);
             const double ri = s.front ? (1.0 / m.param) : m.param;
             const D3 ud = unit(s.d);
             const double cos_theta = fmin(dot(-ud, s.n), 1.0);
@@ -511,10 +530,9 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
     uint32_t pix = 0;
     if (valid && uint32_t(k) < w.ncam[b]) {
         nl = w.nlight[b];
-        const size_t v = size_t(k) * size_t(w.B) + size_t(b);
-        cp = mk(w.cv_px[v], w.cv_py[v], w.cv_pz[v]);
-        ctf = mk(w.cv_fx[v], w.cv_fy[v], w.cv_fz[v]);
-        const TriShade sh = sc.shade[w.cv_prim[v]];
+        uint32_t cprim;
+        load_vertex(w.cv + size_t(b) * size_t(w.depth) + size_t(k), cp, ctf, cprim);
+        const TriShade sh = sc.shade[cprim];
         cn = mk(sh.nx, sh.ny, sh.nz);   // |dot| below makes the face flip irrelevant (camera.h:451-452)
         pix = decode_sample(f, w.sample[b]).pix;
     }
@@ -525,13 +543,13 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
         double max_t = 0;
         uint32_t far_prim = 0;
         if (m < nl) {
-            const size_t v = size_t(m) * size_t(w.B) + size_t(b);
-            const D3 lp = mk(w.lv_px[v], w.lv_py[v], w.lv_pz[v]);
+            D3 lp, lT;
+            uint32_t lprim;
+            load_vertex(w.lv + size_t(b) * size_t(w.depth) + size_t(m), lp, lT, lprim);
             const D3 dir = lp - cp;
             const double dist2 = len2(dir);
             if (dist2 > 0) {
                 const D3 du = unit(dir);
-                const uint32_t lprim = w.lv_prim[v];
                 far_prim = lprim & ~kLightFlag;
                 const TriShade lsh = sc.shade[far_prim];
                 const D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
@@ -547,7 +565,6 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                         const D3 lrgb = mk(lm.r, lm.g, lm.b);
                         const D3 f_light = (lprim & kLightFlag) ? lrgb : lrgb / kPi;   // camera.h:463-466
                         if (len2(f_light) > 0) {
-                            const D3 lT = mk(w.lv_tx[v], w.lv_ty[v], w.lv_tz[v]);
                             contrib = ctf * lT * f_light;                               // camera.h:471-472
                             contrib = contrib * (cos_cam * cos_light) / dist2;          // camera.h:473
                             so = cp + (0.001 * vdu);
@@ -666,9 +683,7 @@ struct Carver {
 void carve(WF& w, char* base) {
     Carver c{base};
     const size_t P = size_t(2 * w.B), V = size_t(w.depth) * size_t(w.B), B = size_t(w.B), S = size_t(w.scap);
-    double** pd[] = {&w.ox, &w.oy, &w.oz, &w.dx, &w.dy, &w.dz, &w.tx, &w.ty, &w.tz, &w.hit_t};
-    for (double** q : pd) *q = c.take<double>(P);
-    w.draws = c.take<uint32_t>(P); w.hit_prim = c.take<uint32_t>(P); w.remaining = c.take<int32_t>(P);
+    w.path = c.take<PathRec>(P);
     w.sample = c.take<int64_t>(B); w.live = c.take<uint32_t>(B);
     for (int k = 0; k < 2; ++k) w.q_slots[k] = c.take<uint32_t>(B);
     for (int k = 0; k < 2; ++k) w.q_active[k] = c.take<uint32_t>(P);
@@ -677,9 +692,7 @@ void carve(WF& w, char* base) {
     w.q_exact_s = c.take<uint32_t>(S);
     w.q_shadow_live = c.take<uint32_t>(S);
     w.counters = c.take<uint32_t>(C_COUNT);
-    double** cv[] = {&w.cv_px, &w.cv_py, &w.cv_pz, &w.cv_fx, &w.cv_fy, &w.cv_fz, &w.lv_px, &w.lv_py, &w.lv_pz, &w.lv_tx, &w.lv_ty, &w.lv_tz};
-    for (double** q : cv) *q = c.take<double>(V);
-    w.cv_prim = c.take<uint32_t>(V); w.lv_prim = c.take<uint32_t>(V);
+    w.cv = c.take<VertRec>(V); w.lv = c.take<VertRec>(V);
     w.ncam = c.take<uint32_t>(B); w.nlight = c.take<uint32_t>(B);
     double** sq[] = {&w.s_ox, &w.s_oy, &w.s_oz, &w.s_dx, &w.s_dy, &w.s_dz, &w.s_tmax, &w.s_cx, &w.s_cy, &w.s_cz};
     for (double** q : sq) *q = c.take<double>(S);
