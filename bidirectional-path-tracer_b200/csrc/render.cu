@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -33,11 +34,17 @@ namespace {
 
 constexpr int kBlock = 128;
 constexpr uint32_t kLightFlag = 0x80000000u;
+// Front blocks give every parked ray a warp of its own (lane 0): these rays are latency chains of ~1000
+// dependent steps, and 32 of them in one warp would serialise on each other's loop phases (measured: 7x
+// slower than alone).  Issue slots are not the constraint — a few hundred such rays per launch.
+constexpr int kFrontPerBlock = kBlock / 32;
+constexpr uint32_t kSlowFlag = 0x80000000u;   // q_exact entry: re-run the FAST traversal without a work limit (else: reference traversal)
 
 // device counters (uint32 each)
 enum { C_ACTIVE0 = 0, C_ACTIVE1 = 1, C_MAT0 = 2 /* ..5 */, C_SHADOW = 6, C_MAXNC = 7, C_MAXNL = 8, C_SUMNC = 9,
        C_SUMNL = 10, C_OVERFLOW = 11, C_PAIRS_LO = 12, C_PAIRS_HI = 13 /* 64-bit, 8-byte aligned */, C_UNUSED14 = 14, C_EXACT_SHADOW = 15,
-       C_DONE0 = 16, C_DONE1 = 17, C_SHADOW_TOTAL = 18 /* ..19: 64-bit, shadow rays of the whole worker run */, C_SHADOW_LIVE = 20, C_EXACT0 = 21, C_EXACT1 = 22, C_COUNT = 24 };
+       C_DONE0 = 16, C_DONE1 = 17, C_SHADOW_TOTAL = 18 /* ..19: 64-bit, shadow rays of the whole worker run */, C_SHADOW_LIVE = 20, C_EXACT0 = 21, C_EXACT1 = 22,
+       C_SLOW_S0 = 24, C_SLOW_S1 = 25 /* parked shadow segments, ping-pong */, C_COUNT = 28 };
 
 struct Frame {           // camera.h:148-197 derived values + this call's sample selection
     D3 center, pixel00, du, dv, background;
@@ -70,6 +77,22 @@ struct __align__(32) VertRec {   // 64 B = 2 sectors
 };
 static_assert(sizeof(VertRec) == 64, "VertRec must be 64 bytes");
 
+struct __align__(32) SlowShadow {   // a parked shadow segment: ray, finished contribution, pixel; 96 B
+    double ox, oy, oz, dx, dy, dz, tmax, cx, cy, cz;
+    uint32_t pix, kind;              // kind 1: needs the reference traversal
+    uint32_t pad[2];
+};
+static_assert(sizeof(SlowShadow) == 96, "SlowShadow must be 96 bytes");
+
+// Shadow queue: SoA, written at consecutive slots (warp-aggregated append) and read by index.
+struct SQ {
+    double *ox, *oy, *oz, *dx, *dy, *dz, *tmax, *cx, *cy, *cz;   // segment and its finished contribution
+    uint32_t *pix, *far;             // pixel; prim of the far (light-side) vertex
+    uint32_t* live;                  // segments the far-endpoint test did not settle (indices into this queue)
+    uint32_t* cnt;                   // SQ_*
+};
+enum { SQ_N = 0, SQ_LIVE = 1, SQ_OVERFLOW = 2, SQ_COUNT = 8 };
+
 struct WF {              // wavefront workspace, all device pointers
     int64_t B;           // batch capacity in samples
     int depth;
@@ -81,15 +104,15 @@ struct WF {              // wavefront workspace, all device pointers
     uint32_t* live;
     uint32_t* q_slots[2];            // slots whose subpaths have both ended (ping-pong: done list -> free list)
     uint32_t *q_active[2], *q_mat[4];
-    uint32_t* q_shadow_live;         // shadow rays the far-endpoint test did not settle (indices into the shadow queue)
-    uint32_t *q_exact[2], *q_exact_s;   // rays deferred to the reference-exact traversal (path ids, ping-pong / shadow slots)
+    uint32_t* q_exact[2];            // path rays for the next launch's front blocks (reference traversal or unbounded re-run), ping-pong
+    SlowShadow* ss[2];               // parked shadow segments, ping-pong
+    int64_t sscap;
     uint32_t* counters;
     // vertex pools, index = b * depth + slot (a sample's vertices are contiguous)
     VertRec *cv, *lv;
     uint32_t *ncam, *nlight;
-    // shadow queue
-    double *s_ox, *s_oy, *s_oz, *s_dx, *s_dy, *s_dz, *s_tmax, *s_cx, *s_cy, *s_cz;
-    uint32_t *s_pix, *s_far;         // pixel; prim of the far (light-side) vertex
+    SQ sq[2];                        // shadow queues, ping-pong: the shadow stage of one iteration runs on its own
+                                     // stream while the main stream already traces the next
     void* base;
     size_t bytes;
 };
@@ -282,18 +305,23 @@ extern __shared__ StackEntry s_dyn_stack[];   // [levels][kBlock], sized at laun
 template <int BVH, bool STATS>
 __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
                                                        const uint32_t* __restrict__ n_ptr, int dn, int ex, uint32_t n_def_blocks,
-                                                       double* film, unsigned long long* stats) {
+                                                       uint32_t limit, double* film, unsigned long long* stats) {
     int cls = -1;
-    uint32_t pid = 0;
+    uint32_t pid = 0, defer_tag = 0;
     bool defer = false, ended = false;
     if (blockIdx.x < n_def_blocks) {
-        const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
-        if (idx < w.counters[C_EXACT0 + (ex ^ 1)]) {
-            pid = w.q_exact[ex ^ 1][idx];
+        const uint32_t idx = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5);
+        if ((threadIdx.x & 31) == 0 && idx < w.counters[C_EXACT0 + (ex ^ 1)]) {
+            const uint32_t e = w.q_exact[ex ^ 1][idx];
+            pid = e & ~kSlowFlag;
             const RayD r = load_path_ray(w, pid);
             HitD h;
             TravStats ts{0, 0};
-            const bool found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+            bool found;
+            if (BVH != BDPT_BVH_REFERENCE && (e & kSlowFlag))
+                found = traverse_fast<false, STATS, false>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts) == TR_HIT;
+            else
+                found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
             if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
             cls = finish_trace(sc, f, w, pid, found, h, film);
             ended = cls < 0;
@@ -309,9 +337,10 @@ __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, W
             if (BVH == BDPT_BVH_REFERENCE) {
                 found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
             } else {
-                const int rc = traverse_fast<false, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts);
+                const int rc = traverse_fast<false, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts, limit);
                 found = rc == TR_HIT;
-                defer = rc == TR_DEFER;
+                defer = rc == TR_DEFER || rc == TR_SLOW;
+                defer_tag = rc == TR_SLOW ? kSlowFlag : 0u;
             }
             if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
             if (!defer) { cls = finish_trace(sc, f, w, pid, found, h, film); ended = cls < 0; }
@@ -319,7 +348,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, W
     }
     if (BVH != BDPT_BVH_REFERENCE) {   // rays that need the reference tree: compacted for the next launch's front blocks
         const uint32_t slot = warp_append(w.counters + C_EXACT0 + ex, defer);
-        if (defer) w.q_exact[ex][slot] = pid;
+        if (defer) w.q_exact[ex][slot] = pid | defer_tag;
     }
     bin_by_material(w, cls, pid);
     retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
@@ -518,7 +547,7 @@ __global__ void __launch_bounds__(256) k_counts(WF w, int dn) {
 // connect_vertices (camera.h:440-475) for camera-vertex slots [k0, k1) of every finished sample (the done
 // list) against all of the sample's light vertices.  Everything except visible() is evaluated here; pairs that survive the
 // early-outs become shadow rays carrying their finished contribution.
-__global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ done, int64_t nb,
+__global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w, SQ q, const uint32_t* __restrict__ done, int64_t nb,
                                                    int k0, int k1) {
     const int64_t idx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int64_t total = int64_t(k1 - k0) * nb;
@@ -575,17 +604,17 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                 }
             }
         }
-        const uint32_t slot = warp_append(w.counters + C_SHADOW, emit);
+        const uint32_t slot = warp_append(q.cnt + SQ_N, emit);
         if (emit) {
             if (slot < uint32_t(w.scap)) {
-                w.s_ox[slot] = so.x; w.s_oy[slot] = so.y; w.s_oz[slot] = so.z;
-                w.s_dx[slot] = sd.x; w.s_dy[slot] = sd.y; w.s_dz[slot] = sd.z;
-                w.s_tmax[slot] = max_t;
-                w.s_cx[slot] = contrib.x; w.s_cy[slot] = contrib.y; w.s_cz[slot] = contrib.z;
-                w.s_pix[slot] = pix;
-                w.s_far[slot] = far_prim;
+                q.ox[slot] = so.x; q.oy[slot] = so.y; q.oz[slot] = so.z;
+                q.dx[slot] = sd.x; q.dy[slot] = sd.y; q.dz[slot] = sd.z;
+                q.tmax[slot] = max_t;
+                q.cx[slot] = contrib.x; q.cy[slot] = contrib.y; q.cz[slot] = contrib.z;
+                q.pix[slot] = pix;
+                q.far[slot] = far_prim;
             } else {
-                w.counters[C_OVERFLOW] = 1;
+                q.cnt[SQ_OVERFLOW] = 1;
             }
         }
     }
@@ -594,12 +623,12 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
 // ------------------------------------------------------------------ K4
 // visible() (camera.h:437: world.hit over [0.001, dist-0.001], inclusive ends — SURVEY F4) and the
 // film accumulation of every unoccluded connection.
-__device__ __forceinline__ RayD load_shadow_ray(const WF& w, uint32_t idx) {
+__device__ __forceinline__ RayD load_shadow_ray(const SQ& q, uint32_t idx) {
     RayD r;
-    r.o = mk(w.s_ox[idx], w.s_oy[idx], w.s_oz[idx]);
-    r.d = mk(w.s_dx[idx], w.s_dy[idx], w.s_dz[idx]);
+    r.o = mk(q.ox[idx], q.oy[idx], q.oz[idx]);
+    r.d = mk(q.dx[idx], q.dy[idx], q.dz[idx]);
     r.tmin = 0.001;
-    r.tmax = w.s_tmax[idx];
+    r.tmax = q.tmax[idx];
     return r;
 }
 
@@ -607,61 +636,94 @@ __device__ __forceinline__ RayD load_shadow_ray(const WF& w, uint32_t idx) {
 // and one box; the rest are compacted into q_shadow_live so that stage 2's warps are full of rays that
 // really walk the tree.
 template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow_pre(SceneView sc, WF w, unsigned long long* stats) {
+__global__ void __launch_bounds__(kBlock) k_shadow_pre(SceneView sc, WF w, SQ q, unsigned long long* stats) {
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
-    if (idx == 0) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)w.counters[C_SHADOW]);
+    if (idx == 0) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)q.cnt[SQ_N]);
     bool live = false;
-    if (idx < w.counters[C_SHADOW]) {
-        const RayD r = load_shadow_ray(w, idx);
+    if (idx < q.cnt[SQ_N]) {
+        const RayD r = load_shadow_ray(q, idx);
         TravStats ts{0, 0};
-        live = !far_endpoint_occludes(sc, r, w.s_far[idx], STATS ? &ts : nullptr);
+        live = !far_endpoint_occludes(sc, r, q.far[idx], STATS ? &ts : nullptr);
         if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
     }
-    const uint32_t slot = warp_append(w.counters + C_SHADOW_LIVE, live);
-    if (live) w.q_shadow_live[slot] = idx;
+    const uint32_t slot = warp_append(q.cnt + SQ_LIVE, live);
+    if (live) q.live[slot] = idx;
 }
 
+// Stage 2.  Blocks [0, n_slow_blocks) finish the segments that an EARLIER launch gave up on — over the work
+// limit (re-run unbounded) or in need of the reference tree (ties, knife edges) — from their own copies of
+// the payload; the other blocks walk this round's live segments under the work limit and park what they
+// cannot settle in ss[sx] for the next launch.
 template <int BVH, bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, double* film, unsigned long long* stats) {
-    const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-    bool defer = false;
-    uint32_t idx = i;
-    if (BVH == BDPT_BVH_REFERENCE && i == 0)
-        atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)w.counters[C_SHADOW]);
-    if (i < w.counters[BVH == BDPT_BVH_REFERENCE ? C_SHADOW : C_SHADOW_LIVE]) {
-        if (BVH != BDPT_BVH_REFERENCE) idx = w.q_shadow_live[i];
-        const RayD r = load_shadow_ray(w, idx);
-        HitD h;
-        bool found;
-        TravStats ts{0, 0};
-        if (BVH == BDPT_BVH_REFERENCE) {
-            found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
-        } else {
-            const int rc = traverse_fast<true, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts);
-            found = rc == TR_HIT;
-            defer = rc == TR_DEFER;
+__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, SQ q, int sx, uint32_t n_slow_blocks, uint32_t limit, double* film,
+                                                  unsigned long long* stats) {
+    if (BVH == BDPT_BVH_REFERENCE) {
+        const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+        if (i == 0) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)q.cnt[SQ_N]);
+        if (i < q.cnt[SQ_N]) {
+            const RayD r = load_shadow_ray(q, i);
+            HitD h;
+            TravStats ts{0, 0};
+            const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (!found) film_add(film, q.pix[i], mk(q.cx[i], q.cy[i], q.cz[i]));
         }
-        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
-        if (!found && !defer) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
+        return;
     }
-    if (BVH != BDPT_BVH_REFERENCE) {
-        const uint32_t slot = warp_append(w.counters + C_EXACT_SHADOW, defer);
-        if (defer) w.q_exact_s[slot] = idx;
+    if (blockIdx.x < n_slow_blocks) {   // one parked segment per warp at a time, warp-stride over the device-side count
+        const uint32_t n = min(w.counters[C_SLOW_S0 + (sx ^ 1)], uint32_t(w.sscap));
+        if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(&stats[ST_DEFER_SHADOW], (unsigned long long)n);
+        if ((threadIdx.x & 31) != 0) return;
+        for (uint32_t i = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5); i < n; i += n_slow_blocks * kFrontPerBlock) {
+            const SlowShadow* e = w.ss[sx ^ 1] + i;
+            const double2* pq = reinterpret_cast<const double2*>(e);
+            const double2 q0 = pq[0], q1 = pq[1], q2 = pq[2], q3 = pq[3], q4 = pq[4];
+            const int4 q5 = reinterpret_cast<const int4*>(e)[5];
+            RayD r;
+            r.o = mk(q0.x, q0.y, q1.x); r.d = mk(q1.y, q2.x, q2.y); r.tmin = 0.001; r.tmax = q3.x;
+            HitD h;
+            TravStats ts{0, 0};
+            bool found;
+            if (q5.y) found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+            else found = traverse_fast<true, STATS, false>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts) == TR_HIT;
+            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
+        }
+        return;
     }
-}
-
-template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow_exact(SceneView sc, WF w, double* film, unsigned long long* stats) {
-    const uint32_t n = w.counters[C_EXACT_SHADOW];
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(&stats[ST_DEFER_SHADOW], (unsigned long long)n);
-    for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
-        const uint32_t idx = w.q_exact_s[i];
-        const RayD r = load_shadow_ray(w, idx);
+    const uint32_t i = (blockIdx.x - n_slow_blocks) * kBlock + threadIdx.x;
+    bool park = false;
+    int kind = 0;
+    uint32_t idx = 0;
+    RayD r;
+    if (i < q.cnt[SQ_LIVE]) {
+        idx = q.live[i];
+        r = load_shadow_ray(q, idx);
         HitD h;
         TravStats ts{0, 0};
-        const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+        const int rc = traverse_fast<true, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts, limit);
+        park = rc == TR_DEFER || rc == TR_SLOW;
+        kind = rc == TR_DEFER ? 1 : 0;
         if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
-        if (!found) film_add(film, w.s_pix[idx], mk(w.s_cx[idx], w.s_cy[idx], w.s_cz[idx]));
+        if (rc == TR_MISS) film_add(film, q.pix[idx], mk(q.cx[idx], q.cy[idx], q.cz[idx]));
+    }
+    const uint32_t slot = warp_append(w.counters + C_SLOW_S0 + sx, park);
+    if (park) {
+        const D3 c = mk(q.cx[idx], q.cy[idx], q.cz[idx]);
+        const uint32_t pix = q.pix[idx];
+        if (slot < uint32_t(w.sscap)) {
+            SlowShadow* e = w.ss[sx] + slot;
+            double2* pq = reinterpret_cast<double2*>(e);
+            pq[0] = make_double2(r.o.x, r.o.y); pq[1] = make_double2(r.o.z, r.d.x); pq[2] = make_double2(r.d.y, r.d.z);
+            pq[3] = make_double2(r.tmax, c.x); pq[4] = make_double2(c.y, c.z);
+            reinterpret_cast<int4*>(e)[5] = make_int4(int(pix), kind, 0, 0);
+        } else {   // parking lot full: settle it here, unbounded
+            HitD h;
+            TravStats ts{0, 0};
+            const bool found = traverse_fast<true, STATS, false>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts) == TR_HIT;
+            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
+            if (!found) film_add(film, pix, c);
+        }
     }
 }
 
@@ -689,14 +751,17 @@ void carve(WF& w, char* base) {
     for (int k = 0; k < 2; ++k) w.q_active[k] = c.take<uint32_t>(P);
     for (int k = 0; k < 4; ++k) w.q_mat[k] = c.take<uint32_t>(P);
     for (int k = 0; k < 2; ++k) w.q_exact[k] = c.take<uint32_t>(P);
-    w.q_exact_s = c.take<uint32_t>(S);
-    w.q_shadow_live = c.take<uint32_t>(S);
+    for (int k = 0; k < 2; ++k) w.ss[k] = c.take<SlowShadow>(size_t(w.sscap));
     w.counters = c.take<uint32_t>(C_COUNT);
     w.cv = c.take<VertRec>(V); w.lv = c.take<VertRec>(V);
     w.ncam = c.take<uint32_t>(B); w.nlight = c.take<uint32_t>(B);
-    double** sq[] = {&w.s_ox, &w.s_oy, &w.s_oz, &w.s_dx, &w.s_dy, &w.s_dz, &w.s_tmax, &w.s_cx, &w.s_cy, &w.s_cz};
-    for (double** q : sq) *q = c.take<double>(S);
-    w.s_pix = c.take<uint32_t>(S); w.s_far = c.take<uint32_t>(S);
+    for (int k = 0; k < 2; ++k) {
+        SQ& q = w.sq[k];
+        double** sq[] = {&q.ox, &q.oy, &q.oz, &q.dx, &q.dy, &q.dz, &q.tmax, &q.cx, &q.cy, &q.cz};
+        for (double** d : sq) *d = c.take<double>(S);
+        q.pix = c.take<uint32_t>(S); q.far = c.take<uint32_t>(S); q.live = c.take<uint32_t>(S);
+        q.cnt = c.take<uint32_t>(SQ_COUNT);
+    }
     w.bytes = c.off + 256;
 }
 
@@ -772,7 +837,9 @@ namespace {
 // time is the latency of the slowest ray — overlaps the bulk of another.
 struct Worker {
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;      // the shadow stage (k_shadow_pre, k_shadow) of each iteration
     cudaEvent_t done = nullptr;
+    cudaEvent_t ev_connect = nullptr, ev_shadow[2] = {nullptr, nullptr};
     WF wf{};
     KernelTimers tm;
     uint32_t* hc = nullptr;              // pinned read-back of the device counters
@@ -786,6 +853,9 @@ struct Worker {
         if (wf.base) cudaFree(wf.base);
         if (hc) cudaFreeHost(hc);
         if (done) cudaEventDestroy(done);
+        if (ev_connect) cudaEventDestroy(ev_connect);
+        for (auto& e : ev_shadow) if (e) cudaEventDestroy(e);
+        if (stream2) cudaStreamDestroy(stream2);
         if (stream) cudaStreamDestroy(stream);
     }
 };
@@ -803,6 +873,7 @@ struct Job {
     size_t smem; unsigned exact_grid; int device; int n_workers;
     int64_t B;                       // sample slots per wavefront (every worker's workspace holds at least this many)
     std::atomic<int64_t>* next;      // next sample of this call not yet handed to a worker
+    uint32_t limit;                  // work limit of the bulk traversal launches (traverse_fast.cuh); 0 = none
 };
 
 // One worker: a wavefront of B slots, refilled from the call's shared sample counter until it runs dry.
@@ -818,10 +889,38 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
     const bool want_stats = (o.flags & BDPT_RENDER_STATS) != 0;
     const size_t smem = J.smem;
     WK_CUDA(cudaMemsetAsync(wf.counters, 0, C_COUNT * sizeof(uint32_t), st));
+    WK_CUDA(cudaEventRecord(wk.ev_connect, st));              // the side stream starts after the counter reset
+    WK_CUDA(cudaStreamWaitEvent(wk.stream2, wk.ev_connect, 0));
     int cur = 0, dn = 0, ex = 0;
     int64_t n_active = 0, n_free = J.B;
     uint32_t n_def = 0;              // rays deferred by the previous iteration's trace launch
+    int sx = 0;                      // parking lot the next shadow launch fills; it drains ss[sx ^ 1]
+    int sb = 0;                      // shadow queue the next connect round writes
     bool first = true;
+    cudaStream_t st2 = wk.stream2;
+    constexpr unsigned kFrontBlocks = 64;   // 256 warps drain the parked segments, one segment per warp at a time
+    // the shadow stage of one connect round, on the side stream: front blocks drain what earlier launches
+    // parked, the rest walk this round's live segments
+    auto launch_shadow = [&](const SQ& q, uint32_t ns_bound) {
+        tm.begin(KT_SHADOW, st2);
+        if (o.bvh == BDPT_BVH_REFERENCE) {
+            if (want_stats) k_shadow<BDPT_BVH_REFERENCE, true><<<grid_for(ns_bound, kBlock), kBlock, smem, st2>>>(sc, wf, q, sx, 0u, 0u, J.film, J.d_stats);
+            else k_shadow<BDPT_BVH_REFERENCE, false><<<grid_for(ns_bound, kBlock), kBlock, smem, st2>>>(sc, wf, q, sx, 0u, 0u, J.film, J.d_stats);
+        } else {
+            cudaMemsetAsync(wf.counters + C_SLOW_S0 + sx, 0, sizeof(uint32_t), st2);
+            if (ns_bound) {
+                if (want_stats) k_shadow_pre<true><<<grid_for(ns_bound, kBlock), kBlock, 0, st2>>>(sc, wf, q, J.d_stats);
+                else k_shadow_pre<false><<<grid_for(ns_bound, kBlock), kBlock, 0, st2>>>(sc, wf, q, J.d_stats);
+                wk.launches += 1;
+            }
+            const unsigned gm = ns_bound ? grid_for(ns_bound, kBlock) : 0u;
+            if (want_stats) k_shadow<BDPT_BVH_FAST, true><<<kFrontBlocks + gm, kBlock, smem, st2>>>(sc, wf, q, sx, kFrontBlocks, J.limit, J.film, J.d_stats);
+            else k_shadow<BDPT_BVH_FAST, false><<<kFrontBlocks + gm, kBlock, smem, st2>>>(sc, wf, q, sx, kFrontBlocks, J.limit, J.film, J.d_stats);
+            sx ^= 1;
+        }
+        tm.end(KT_SHADOW, st2);
+        wk.launches += 1;
+    };
     for (;;) {
         int64_t ngen = 0, gen_base = 0;
         if (n_free > 0) {
@@ -844,9 +943,9 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         }
         first = false;
         const unsigned g = grid_for(n_active + 2 * ngen, kBlock);   // upper bound; the kernels read the device count
-        const unsigned gd = n_def ? grid_for(n_def, kBlock) : 0u;
+        const unsigned gd = n_def ? grid_for(n_def, kFrontPerBlock) : 0u;
         tm.begin(KT_TRACE, st);
-#define BDPT_TP(B, S) k_trace_paths<B, S><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.film, J.d_stats)
+#define BDPT_TP(B, S) k_trace_paths<B, S><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.limit, J.film, J.d_stats)
         if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
         else { if (want_stats) BDPT_TP(BDPT_BVH_FAST, true); else BDPT_TP(BDPT_BVH_FAST, false); }
 #undef BDPT_TP
@@ -876,40 +975,28 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
             const int slots_per_round = pairs <= uint64_t(wf.scap) ? max_nc : int(std::max<int64_t>(1, wf.scap / (n_done * int64_t(max_nl))));
             for (int k0 = 0; k0 < max_nc; k0 += slots_per_round) {
                 const int k1 = std::min(max_nc, k0 + slots_per_round);
-                WK_CUDA(cudaMemsetAsync(wf.counters + C_SHADOW, 0, sizeof(uint32_t), st));
-                WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT_SHADOW, 0, sizeof(uint32_t), st));
-                WK_CUDA(cudaMemsetAsync(wf.counters + C_SHADOW_LIVE, 0, sizeof(uint32_t), st));
+                const SQ& q = wf.sq[sb];
+                WK_CUDA(cudaStreamWaitEvent(st, wk.ev_shadow[sb], 0));   // the shadow stage that last read this queue
+                WK_CUDA(cudaMemsetAsync(q.cnt, 0, SQ_COUNT * sizeof(uint32_t), st));
                 tm.begin(KT_CONNECT, st);
-                k_connect<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, wf.q_slots[dn], n_done, k0, k1);
+                k_connect<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
                 tm.end(KT_CONNECT, st);
                 wk.launches += 1;
                 // one round: size the shadow launch by the pair count (an upper bound) and skip the read-back
                 uint32_t ns_bound = uint32_t(std::min<uint64_t>(pairs, uint64_t(wf.scap)));
-                const bool single = slots_per_round >= max_nc;
-                if (!single) {
-                    WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                if (slots_per_round < max_nc) {
+                    uint32_t* hq = hc + C_COUNT;
+                    WK_CUDA(cudaMemcpyAsync(hq, q.cnt, SQ_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
                     WK_CUDA(cudaStreamSynchronize(st));
-                    if (hc[C_OVERFLOW]) { wk.err = "shadow queue overflow"; wk.rc = BDPT_ERR_STATE; return; }
-                    ns_bound = hc[C_SHADOW];
+                    if (hq[SQ_OVERFLOW]) { wk.err = "shadow queue overflow"; wk.rc = BDPT_ERR_STATE; return; }
+                    ns_bound = hq[SQ_N];
                 }
                 if (ns_bound) {
-                    tm.begin(KT_SHADOW, st);
-#define BDPT_SH(B, S) k_shadow<B, S><<<grid_for(ns_bound, kBlock), kBlock, smem, st>>>(sc, wf, J.film, J.d_stats)
-                    if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_SH(BDPT_BVH_REFERENCE, true); else BDPT_SH(BDPT_BVH_REFERENCE, false); }
-                    else {
-                        if (want_stats) k_shadow_pre<true><<<grid_for(ns_bound, kBlock), kBlock, 0, st>>>(sc, wf, J.d_stats);
-                        else k_shadow_pre<false><<<grid_for(ns_bound, kBlock), kBlock, 0, st>>>(sc, wf, J.d_stats);
-                        wk.launches += 1;
-                        if (want_stats) BDPT_SH(BDPT_BVH_FAST, true); else BDPT_SH(BDPT_BVH_FAST, false);
-                        tm.end(KT_SHADOW, st);
-                        tm.begin(KT_SHADOW_EXACT, st);
-                        if (want_stats) k_shadow_exact<true><<<J.exact_grid, kBlock, smem, st>>>(sc, wf, J.film, J.d_stats);
-                        else k_shadow_exact<false><<<J.exact_grid, kBlock, smem, st>>>(sc, wf, J.film, J.d_stats);
-                        wk.launches += 1;
-                    }
-#undef BDPT_SH
-                    tm.end(KT_SHADOW, st);
-                    wk.launches += 1;
+                    WK_CUDA(cudaEventRecord(wk.ev_connect, st));
+                    WK_CUDA(cudaStreamWaitEvent(st2, wk.ev_connect, 0));
+                    launch_shadow(q, ns_bound);
+                    WK_CUDA(cudaEventRecord(wk.ev_shadow[sb], st2));
+                    sb ^= 1;
                 }
             }
         }
@@ -917,6 +1004,9 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         dn ^= 1;
         cur = nxt;
     }
+    // segments still parked by the last shadow launch: one more launch of front blocks only (they never park)
+    if (o.bvh != BDPT_BVH_REFERENCE) launch_shadow(wf.sq[0], 0);
+    WK_CUDA(cudaStreamSynchronize(st2));
     WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     WK_CUDA(cudaStreamSynchronize(st));
     wk.rays_shadow += uint64_t(hc[C_SHADOW_TOTAL]) | (uint64_t(hc[C_SHADOW_TOTAL + 1]) << 32);
@@ -978,7 +1068,10 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
         if (!wk.stream) {
             BDPT_CUDA(ctx, cudaStreamCreateWithFlags(&wk.stream, cudaStreamNonBlocking));
             BDPT_CUDA(ctx, cudaEventCreateWithFlags(&wk.done, cudaEventDisableTiming));
-            BDPT_CUDA(ctx, cudaMallocHost(&wk.hc, C_COUNT * sizeof(uint32_t)));
+            BDPT_CUDA(ctx, cudaStreamCreateWithFlags(&wk.stream2, cudaStreamNonBlocking));
+            BDPT_CUDA(ctx, cudaEventCreateWithFlags(&wk.ev_connect, cudaEventDisableTiming));
+            for (auto& e : wk.ev_shadow) BDPT_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            BDPT_CUDA(ctx, cudaMallocHost(&wk.hc, (C_COUNT + SQ_COUNT) * sizeof(uint32_t)));
         }
         if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth) {
             if (wk.wf.base) { BDPT_CUDA(ctx, cudaStreamSynchronize(wk.stream)); cudaFree(wk.wf.base); }
@@ -986,6 +1079,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             wk.wf.B = B; wk.wf.depth = f.depth;
             wk.wf.scap = std::max<int64_t>(B * 8, int64_t(f.depth) * B);   // >= one camera slot against every light vertex
             wk.wf.scap = std::min<int64_t>(wk.wf.scap, int64_t(0xFFFFFFF0u));
+            wk.wf.sscap = std::max<int64_t>(4096, wk.wf.scap / 8);
             carve(wk.wf, nullptr);
             void* base = nullptr;
             cudaError_t e = cudaMalloc(&base, wk.wf.bytes);
@@ -1006,6 +1100,8 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     J.smem = levels * kBlock * sizeof(StackEntry);
     J.exact_grid = 148 * 2;
     J.device = ctx->device; J.n_workers = S; J.B = B;
+    J.limit = 0;   // parking over-limit rays was measured slower than letting them finish in place
+    if (const char* e = std::getenv("BDPT_WORK_LIMIT")) J.limit = uint32_t(std::strtoul(e, nullptr, 10));
     std::atomic<int64_t> next_sample{0};
     J.next = &next_sample;
 

@@ -24,7 +24,7 @@ __device__ __forceinline__ void slab_fast(T lo, T hi, T o, T inv, T& tn, T& tf) 
     tf = fmin(tf, fmax(t0, t1));
 }
 
-enum { TR_MISS = 0, TR_HIT = 1, TR_DEFER = 2 };
+enum { TR_MISS = 0, TR_HIT = 1, TR_DEFER = 2, TR_SLOW = 3 };
 
 // Does the reference's traversal REACH triangle `prim` with the untouched bound [tmin, tmax], i.e. does
 // every box on its root-to-leaf chain pass aabb::hit?  One test of the chain's intersection box accepts;
@@ -88,9 +88,13 @@ __device__ __forceinline__ StackEntry pack_entry(int32_t node, float t) {
 // Returns TR_HIT / TR_MISS, or TR_DEFER when DEFER is set and the ray needs the reference-exact traversal
 // (the caller queues it for the exact kernel); with DEFER unset that traversal runs inline.
 // `stack` is this thread's column of a [levels][stride] shared array of StackEntry.
+// `limit` > 0 bounds the walk: a ray that has touched more than `limit` nodes + triangles gives up with
+// TR_SLOW (nothing decided) so that the caller can re-run it, unbounded, among its own kind — a launch's
+// duration is then no longer the latency chain of its single worst ray (a segment running inside a
+// tessellated plane touches ~1000 nodes against a mean of ~25).
 template <bool ANY, bool STATS, bool DEFER, class T>
 __device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& r, HitD& hit, StackEntry* stack,
-                                               int stride, TravStats* st) {
+                                               int stride, TravStats* st, uint32_t limit) {
     const T ox = T(r.o.x), oy = T(r.o.y), oz = T(r.o.z);
     const T ix = T(1.0 / r.d.x), iy = T(1.0 / r.d.y), iz = T(1.0 / r.d.z);
     const double inv_max = fmin(fabs(1.0 / r.d.x), fmin(fabs(1.0 / r.d.y), fabs(1.0 / r.d.z)));
@@ -104,6 +108,7 @@ __device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& 
     int sp = 0;
     int32_t cur = 0;
     uint32_t nn = 0, nt = 0;
+    uint32_t work = 0;
     constexpr int kMaxEdge = 4;
     uint32_t edge_prim[kMaxEdge];
     int n_edge = 0;
@@ -115,6 +120,7 @@ __device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& 
             const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
             const int4 w = __ldg(reinterpret_cast<const int4*>(q + 3));
             if (STATS) ++nn;
+            ++work;
             // a = l_lo.xyz l_hi.x | b = l_hi.yz r_lo.xy | c = r_lo.z r_hi.xyz
             T ln = tmin_t, lf = best_t, rn = tmin_t, rf = best_t;
             slab_fast<T>(T(a.x), T(a.w), ox, ix, ln, lf);
@@ -149,6 +155,11 @@ __device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& 
         {
             const uint32_t code = uint32_t(~cur);
             const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+            work += cnt;
+            if (limit && work > limit) {
+                if (STATS && st) { st->nodes += nn; st->tris += nt; }
+                return TR_SLOW;
+            }
             for (uint32_t k = 0; k < cnt; ++k) {
                 const uint32_t prim = __ldg(sc.fast_prims + first + k);
                 if (STATS) ++nt;
@@ -218,7 +229,7 @@ __device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& 
 //  - otherwise fp32 slabs: outward padding of 2^-16 extent covers the <= 5e-6 extent fp32 error
 template <bool ANY, bool STATS, bool DEFER>
 __device__ __forceinline__ int traverse_fast(const SceneView& sc, const RayD& r, HitD& hit, StackEntry* stack,
-                                             int stride, TravStats* st) {
+                                             int stride, TravStats* st, uint32_t limit = 0) {
     if (r.d.x == 0.0 || r.d.y == 0.0 || r.d.z == 0.0) {
         if (DEFER) return TR_DEFER;
         return traverse_ref<ANY, STATS>(sc, r, hit, reinterpret_cast<int32_t*>(stack), 2 * stride, st) ? TR_HIT : TR_MISS;
@@ -226,8 +237,8 @@ __device__ __forceinline__ int traverse_fast(const SceneView& sc, const RayD& r,
     const double far = 8.0 * sc.extent;
     const bool near_scene = fabs(r.o.x - sc.center.x) <= far && fabs(r.o.y - sc.center.y) <= far && fabs(r.o.z - sc.center.z) <= far &&
                             fabs(sc.center.x) <= far && fabs(sc.center.y) <= far && fabs(sc.center.z) <= far;
-    if (near_scene) return traverse_fast_t<ANY, STATS, DEFER, float>(sc, r, hit, stack, stride, st);
-    return traverse_fast_t<ANY, STATS, DEFER, double>(sc, r, hit, stack, stride, st);
+    if (near_scene) return traverse_fast_t<ANY, STATS, DEFER, float>(sc, r, hit, stack, stride, st, limit);
+    return traverse_fast_t<ANY, STATS, DEFER, double>(sc, r, hit, stack, stride, st, limit);
 }
 
 }  // namespace bdpt
