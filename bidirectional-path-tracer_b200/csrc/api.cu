@@ -2,7 +2,9 @@
 // Compiled with -fmad=false: the trace kernels instantiate the reference-exact traversal.
 #include <cstdio>
 #include <cstring>
+#include <exception>
 #include <stdexcept>
+#include <thread>
 
 #include "ctx.h"
 #include "traverse_ref.cuh"
@@ -152,8 +154,12 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
     try {
         flatten_scene(verts, mat_id, n_tris, mats, n_mats, ctx->host);
-        build_ref_bvh(ctx->host);
-        build_fast_bvh(ctx->host);
+        // the two trees share only read-only inputs (tri_box): build them side by side
+        std::exception_ptr fast_err;
+        std::thread fast_thread([&] { try { build_fast_bvh(ctx->host); } catch (...) { fast_err = std::current_exception(); } });
+        try { build_ref_bvh(ctx->host); } catch (...) { fast_thread.join(); throw; }
+        fast_thread.join();
+        if (fast_err) std::rethrow_exception(fast_err);
     } catch (const std::exception& ex) {
         ctx->err = ex.what();
         return BDPT_ERR_ARG;

@@ -2,7 +2,11 @@
 // median split of src/acceleration/bvh.h:20-48 (kept bit-exactly in host_scene.cu); this tree exists so
 // that traversal visits fewer nodes while returning the same hits (traverse_fast.cuh).
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
+#include <deque>
+#include <thread>
+#include <vector>
 #include <cmath>
 #include <limits>
 
@@ -78,31 +82,29 @@ void build_fast_bvh(HostScene& s) {
     };
     auto leaf_code = [](uint32_t first, uint32_t cnt) { return int32_t(~((first << 3) | (cnt - 1))); };
 
-    uint32_t max_depth = 0;
-    std::vector<Task> todo;
-    // root: always an internal node so the kernel never special-cases
-    s.fast_nodes.push_back(FastNode());
-    todo.push_back(Task{0, n, 0, -1, 0});
-    bool root_done = false;
-    while (!todo.empty()) {
-        Task t = todo.back();
-        todo.pop_back();
+    // One (sub)tree: tasks are expanded depth-first into `nodes` (node 0 = the task seeded with node -1).
+    // `stop_at` > 0 makes it breadth-first instead and stops as soon as that many tasks are pending, which is
+    // how the top of the tree is split into independent subtrees for the worker threads.
+    auto grow = [&](std::vector<FastNode>& nodes, std::deque<Task>& todo, uint32_t& max_depth, size_t stop_at) {
+    while (!todo.empty() && (stop_at == 0 || todo.size() < stop_at)) {
+        Task t;
+        if (stop_at) { t = todo.front(); todo.pop_front(); } else { t = todo.back(); todo.pop_back(); }
         const uint32_t cnt = t.end - t.begin;
         max_depth = std::max(max_depth, t.depth);
         B3 bb = range_box(t.begin, t.end);
         // leaf?  (never for the root task: it must produce node 0)
         if (t.node >= 0 && cnt <= kMaxLeaf) {
             // decided by the parent (it stored the box); just encode
-            FastNode& p = s.fast_nodes[t.node];
+            FastNode& p = nodes[t.node];
             (t.side ? p.right : p.left) = leaf_code(t.begin, cnt);
             continue;
         }
         int32_t me;
-        if (t.node < 0) { me = 0; root_done = true; }
+        if (t.node < 0) me = 0;
         else {
-            me = int32_t(s.fast_nodes.size());
-            s.fast_nodes.push_back(FastNode());
-            FastNode& p = s.fast_nodes[t.node];
+            me = int32_t(nodes.size());
+            nodes.push_back(FastNode());
+            FastNode& p = nodes[t.node];
             (t.side ? p.right : p.left) = me;
         }
         uint32_t mid = t.begin;
@@ -111,7 +113,7 @@ void build_fast_bvh(HostScene& s) {
             FastNode nd{};
             store_box(nd, 0, bb); store_box(nd, 1, bb);
             nd.left = leaf_code(t.begin, 1); nd.right = leaf_code(t.begin, 1);
-            s.fast_nodes[me] = nd;
+            nodes[me] = nd;
             continue;
         }
         // centroid bounds
@@ -180,12 +182,54 @@ void build_fast_bvh(HostScene& s) {
         store_box(nd, 0, range_box(t.begin, mid));
         store_box(nd, 1, range_box(mid, t.end));
         nd.left = nd.right = 0;
-        s.fast_nodes[me] = nd;
+        nodes[me] = nd;
         // children: push right first so the left subtree is laid out next (preorder, near the parent)
         todo.push_back(Task{mid, t.end, t.depth + 1, me, 1});
         todo.push_back(Task{t.begin, mid, t.depth + 1, me, 0});
     }
-    (void)root_done;
+    };
+
+    // top of the tree on this thread until there are enough independent subtrees ...
+    uint32_t max_depth = 0;
+    std::deque<Task> top;
+    s.fast_nodes.push_back(FastNode());   // root: always an internal node so the kernel never special-cases
+    top.push_back(Task{0, n, 0, -1, 0});
+    grow(s.fast_nodes, top, max_depth, 64);
+    // ... then one subtree per task, on worker threads, each into its own node array (prim ranges are disjoint)
+    std::vector<Task> subs(top.begin(), top.end());
+    std::sort(subs.begin(), subs.end(), [](const Task& a, const Task& b) { return a.end - a.begin > b.end - b.begin; });
+    std::vector<std::vector<FastNode>> local(subs.size());
+    std::vector<uint32_t> local_depth(subs.size(), 0);
+    std::atomic<size_t> next{0};
+    auto worker = [&] {
+        for (size_t i = next.fetch_add(1); i < subs.size(); i = next.fetch_add(1)) {
+            const Task& t = subs[i];
+            if (t.end - t.begin <= kMaxLeaf) continue;   // a leaf of the top part: encoded below
+            std::deque<Task> todo;
+            local[i].push_back(FastNode());
+            todo.push_back(Task{t.begin, t.end, t.depth, -1, 0});
+            grow(local[i], todo, local_depth[i], 0);
+        }
+    };
+    const unsigned n_threads = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    std::vector<std::thread> pool;
+    for (unsigned k = 1; k < n_threads && k < subs.size(); ++k) pool.emplace_back(worker);
+    worker();
+    for (auto& th : pool) th.join();
+    // splice: a subtree's internal links move by its base index; leaf codes (negative) are global already
+    for (size_t i = 0; i < subs.size(); ++i) {
+        const Task& t = subs[i];
+        FastNode& p = s.fast_nodes[t.node];
+        max_depth = std::max(max_depth, std::max(t.depth, local_depth[i]));
+        if (local[i].empty()) { (t.side ? p.right : p.left) = leaf_code(t.begin, t.end - t.begin); continue; }
+        const int32_t base = int32_t(s.fast_nodes.size());
+        (t.side ? p.right : p.left) = base;
+        for (FastNode nd : local[i]) {
+            if (nd.left >= 0) nd.left += base;
+            if (nd.right >= 0) nd.right += base;
+            s.fast_nodes.push_back(nd);
+        }
+    }
     (void)kTravCost; (void)kTriCost;
     s.fast_depth = max_depth + 1;
 }

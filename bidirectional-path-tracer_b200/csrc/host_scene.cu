@@ -3,9 +3,12 @@
 // (triangle.h:135-230, scene_loader.h:190-202), bvh_node ctor (src/acceleration/bvh.h:20-48) and the
 // aabb merge / pad rules (src/acceleration/aabb.h:27-33,81-88, src/core/interval.h:12-16,36-39).
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <limits>
+#include <map>
 #include <stdexcept>
+#include <thread>
 
 #include "host_scene.h"
 
@@ -36,16 +39,33 @@ inline int longest_axis(const Box6& b) {  // aabb.h:68-75 (ties go to the later 
     return sy > sz ? 1 : 2;
 }
 
+// Node count of the reference tree over a span: f(1) = f(2) = 1, f(n) = 1 + f(n/2) + f(n - n/2) (bvh.h:35-46).
+// It depends on the span's size only, so every node's preorder index is known before anything is built and
+// subtrees can be built by different threads straight into their final places.
+struct NodeCount {
+    std::map<size_t, size_t> memo;
+    size_t operator()(size_t n) {
+        if (n <= 2) return 1;
+        auto it = memo.find(n);
+        if (it != memo.end()) return it->second;
+        const size_t v = 1 + (*this)(n / 2) + (*this)(n - n / 2);
+        memo[n] = v;
+        return v;
+    }
+};
+
 struct RefBuilder {
     HostScene& s;
     std::vector<uint32_t>& order;
-    uint32_t max_depth = 0;
+    std::atomic<uint32_t> max_depth{0};
+    std::map<size_t, size_t> counts;   // filled before the build, read-only during it
     explicit RefBuilder(HostScene& sc) : s(sc), order(sc.leaf_order) {}
 
-    int32_t build(size_t start, size_t end, uint32_t depth) {
-        const int32_t me = int32_t(s.ref_nodes.size());
-        s.ref_nodes.push_back(RefNode());
-        max_depth = std::max(max_depth, depth);
+    size_t count(size_t n) const { return n <= 2 ? 1 : counts.at(n); }
+
+    void build(size_t start, size_t end, uint32_t depth, size_t me, int fork_levels) {
+        uint32_t seen = max_depth.load(std::memory_order_relaxed);
+        while (depth > seen && !max_depth.compare_exchange_weak(seen, depth, std::memory_order_relaxed)) {}
         const double inf = std::numeric_limits<double>::infinity();
         Box6 bb;  // aabb::empty (aabb.h:92): padding (+inf,-inf) leaves it unchanged (size = -inf < delta
                   // gives (+inf - p, -inf + p) = (+inf, -inf))
@@ -64,16 +84,29 @@ struct RefBuilder {
         } else {
             // bvh.h:41,68-74: libstdc++ std::sort (unstable) on the box minimum along `axis`; the same
             // library, comparator results and initial order give the reference's permutation.
+            // Sorted as (key, prim) pairs: std::sort's moves depend only on the comparison outcomes, so the
+            // permutation equals that of sorting the pointers, without a cache miss per comparison.
             const double* tb = s.tri_box.data();
-            std::sort(order.begin() + start, order.begin() + end,
-                      [tb, axis](uint32_t a, uint32_t b) { return tb[6 * size_t(a) + axis] < tb[6 * size_t(b) + axis]; });
+            struct KeyId { double key; uint32_t id; };
+            std::vector<KeyId> tmp(span);
+            for (size_t i = 0; i < span; ++i) { const uint32_t p = order[start + i]; tmp[i] = KeyId{tb[6 * size_t(p) + axis], p}; }
+            std::sort(tmp.begin(), tmp.end(), [](const KeyId& a, const KeyId& b) { return a.key < b.key; });
+            for (size_t i = 0; i < span; ++i) order[start + i] = tmp[i].id;
             const size_t mid = start + span / 2;
+            const size_t left = me + 1, right = me + 1 + count(mid - start);   // preorder
             n.leaf = 0;
-            n.left = build(start, mid, depth + 1);
-            n.right = build(mid, end, depth + 1);
+            n.left = int32_t(left);
+            n.right = int32_t(right);
+            if (fork_levels > 0 && span > 4096) {
+                std::thread th([=] { build(start, mid, depth + 1, left, fork_levels - 1); });
+                build(mid, end, depth + 1, right, fork_levels - 1);
+                th.join();
+            } else {
+                build(start, mid, depth + 1, left, 0);
+                build(mid, end, depth + 1, right, 0);
+            }
         }
         s.ref_nodes[me] = n;
-        return me;
     }
 };
 
@@ -132,11 +165,12 @@ void build_ref_bvh(HostScene& s) {
     const size_t n = s.tris.size();
     s.leaf_order.resize(n);
     for (size_t i = 0; i < n; ++i) s.leaf_order[i] = uint32_t(i);
-    s.ref_nodes.clear();
-    s.ref_nodes.reserve(size_t(1.4 * double(n)) + 4);
     RefBuilder b(s);
-    b.build(0, n, 0);
-    s.ref_depth = b.max_depth + 1;
+    NodeCount nc;
+    s.ref_nodes.assign(nc(n), RefNode());
+    b.counts = nc.memo;
+    b.build(0, n, 0, 0, 4);   // up to 16 subtrees in flight
+    s.ref_depth = b.max_depth.load() + 1;
     s.dfs_rank.resize(n);
     for (size_t k = 0; k < n; ++k) s.dfs_rank[s.leaf_order[k]] = uint32_t(k);
     s.ref_parent.assign(s.ref_nodes.size(), -1);
