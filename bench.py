@@ -304,7 +304,7 @@ def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
     ctx.stats_reset()
     for s_ in range(2):
         ctx.render(cam, seed=args.seed, bvh=bvh, strata=((s_ + 1) * STRATA_PER_STEP, (s_ + 2) * STRATA_PER_STEP, 1),
-                   clear=False, height=HEIGHT, streams=1)
+                   clear=False, height=HEIGHT, streams=1, serial=True)
     st, kt = ctx.stats(), ctx.kernel_times()
     out["serialized_pass"] = {"streams": 1, "steps": 2, "ms_per_step": sum(v[0] for v in kt.values()) / 2}
     dom = "trace" if kt["trace"][0] >= kt["shadow"][0] else "shadow"

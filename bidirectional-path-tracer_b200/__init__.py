@@ -57,6 +57,7 @@ class Stats(C.Structure):
 
 
 RENDER_STATS = 1
+RENDER_SERIAL = 2
 KERNEL_CLASSES = ("generate", "trace", "shade", "connect", "shadow", "trace_exact", "shadow_exact")
 
 
@@ -277,7 +278,7 @@ class Context:
         self.film_shape = (int(height), int(width), 3)
 
     def render(self, cam, seed=0, bvh=BVH_REFERENCE, strata=(0, 0, 1), rows=(0, 0), batch_samples=0, clear=True,
-               height=None, stats=False, streams=0):
+               height=None, stats=False, streams=0, serial=False):
         """camera::render's sample loop; returns nothing — read the film with film()."""
         W = cam.image_width
         H = height if height is not None else max(1, int(W / cam.aspect_ratio))
@@ -289,7 +290,7 @@ class Context:
         o.bvh = bvh
         o.row_begin, o.row_end = rows
         o.batch_samples = batch_samples
-        o.flags = RENDER_STATS if stats else 0
+        o.flags = (RENDER_STATS if stats else 0) | (RENDER_SERIAL if serial else 0)
         o.streams = streams
         self._chk(lib().bdpt_render(self._h, C.byref(cam), C.byref(o)), "bdpt_render")
 
@@ -330,3 +331,45 @@ class Context:
 
     def sync(self):
         self._chk(lib().bdpt_sync(self._h), "bdpt_sync")
+
+
+# ---------------------------------------------------------------- multi-GPU: stratum sharding
+def shard_strata(rank, world, samples_per_pixel):
+    """The strata rank `rank` of `world` renders: (begin, end, step) for bdpt_render_opts — stratum s belongs to
+    rank s mod world, which keeps the reference's stratification (camera.h:164,213-223) and gives every rank the
+    same share of every pixel."""
+    n = int(np.sqrt(float(samples_per_pixel)))
+    if not 0 <= rank < world:
+        raise ValueError("rank %d outside world %d" % (rank, world))
+    return (int(rank), n * n, int(world))
+
+
+class CudaArray:
+    """__cuda_array_interface__ view of a device pointer owned by libbdpt (the film), so that torch.distributed
+    can reduce it in place over NCCL."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 3}
+
+
+def reduce_film(film, dist, dst=0):
+    """The one exchange step of a frame: SUM of the ranks' film sums onto `dst` (NCCL on device tensors, gloo on
+    CPU tensors). `film` is a torch tensor and is reduced in place."""
+    dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
+    return film
+
+
+def render_sharded(ctx, cam, dist=None, seed=0, bvh=BVH_FAST, height=None, device=None):
+    """camera::render across the ranks of an initialised torch.distributed group: every rank renders its strata
+    into its own film, then one reduce. Returns the summed film (numpy, H x W x 3) on rank 0, None elsewhere.
+    With dist=None it is a plain single-GPU render."""
+    rank, world = (dist.get_rank(), dist.get_world_size()) if dist is not None else (0, 1)
+    ctx.render(cam, seed=seed, bvh=bvh, strata=shard_strata(rank, world, cam.samples_per_pixel), clear=True, height=height)
+    if dist is not None and world > 1:
+        import torch
+        ptr, n = ctx.film_device_ptr()
+        ctx.sync()
+        t = torch.as_tensor(CudaArray(ptr, n), device=device if device is not None else torch.device("cuda", torch.cuda.current_device()))
+        reduce_film(t, dist, dst=0)
+        torch.cuda.synchronize()
+    return ctx.film() if rank == 0 else None

@@ -897,7 +897,7 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
     int sx = 0;                      // parking lot the next shadow launch fills; it drains ss[sx ^ 1]
     int sb = 0;                      // shadow queue the next connect round writes
     bool first = true;
-    cudaStream_t st2 = wk.stream2;
+    cudaStream_t st2 = (o.flags & BDPT_RENDER_SERIAL) ? wk.stream : wk.stream2;
     constexpr unsigned kFrontBlocks = 64;   // 256 warps drain the parked segments, one segment per warp at a time
     // the shadow stage of one connect round, on the side stream: front blocks drain what earlier launches
     // parked, the rest walk this round's live segments

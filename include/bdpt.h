@@ -111,7 +111,9 @@ typedef struct {
     int32_t  flags;          /* BDPT_RENDER_* */
     int32_t  streams;        /* wavefronts kept in flight on separate CUDA streams; <=0 picks a default (4) */
 } bdpt_render_opts;
-enum { BDPT_RENDER_STATS = 1 /* count node visits / triangle tests of the traversal kernels (slower) */ };
+enum { BDPT_RENDER_STATS = 1,  /* count node visits / triangle tests of the traversal kernels (slower) */
+       BDPT_RENDER_SERIAL = 2  /* keep every kernel of a wavefront on ONE stream (the shadow stage normally overlaps the
+                                  next iteration on a side stream): per-kernel event times are then each kernel's own */ };
 
 int  bdpt_ctx_create(int device, bdpt_ctx** out);
 void bdpt_ctx_destroy(bdpt_ctx* ctx);

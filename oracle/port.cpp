@@ -611,7 +611,8 @@ int port_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int r
     row1 = std::min(H, row1);
     if (row1 <= row0) return H;
     if (rng_mode == ORC_RNG_MT19937) nthreads = 1;  // one global stream: main.h:28-32
-    std::mt19937 mt;  // default seed, as the reference's static generator
+    std::mt19937 mt;  // default seed, as the reference's static generator (main.h:28-32) ...
+    if (seed) mt.seed(uint32_t(seed));  // ... unless the caller asks for an independent stream (convergence tests)
     std::uniform_real_distribution<double> dist(0.0, 1.0);
     parallel_for(uint64_t(row1 - row0), nthreads, [&](uint64_t a, uint64_t b) {
         Rng cr, lr;

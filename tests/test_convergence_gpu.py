@@ -1,0 +1,63 @@
+"""Whole renders are Monte Carlo and cannot be bit-exact against the reference's mt19937 stream:
+the gate is that the relative MSE against a high-spp render falls at the same RATE as the reference's own
+output and is the same SIZE at equal spp.
+
+  relMSE(x) = mean over pixels and channels of (x - ref)^2 / (ref^2 + 1e-2), on the linear averaged film,
+              without the largest 2 % of the terms (fireflies of the unweighted estimator)
+  ref       = 4096 spp (64 x 64 strata); the estimator is the same function in both arms and the GPU arm equals
+              the oracle port sample for sample (tests/test_render_gpu.py), so the GPU renders it
+  CPU arm   = the reference's own headers (oracle/_ref) when built, else the bit-identical port, mt19937 stream
+  gate      = |slope_gpu - slope_cpu| <= 0.1 (log-log slope over spp 1, 4, 16, 64) and relMSE ratio at every spp
+              within [0.8, 1.25] — SURVEY 8(d)'s numbers; each relMSE is the mean over SEEDS independent renders
+"""
+import numpy as np
+import pytest
+
+from oracle.oracle import Oracle, available, make_camera as ocam, RNG_MT19937
+
+pytestmark = pytest.mark.gpu
+
+W = H = 32
+DEPTH = 6
+SPPS = (1, 4, 16, 64)
+SEEDS = 16
+
+
+TRIM = 0.02
+
+
+def rel_mse(film_sum, spp, ref):
+    """The reference's estimator has the unweighted 1/dist^2 connection term (camera.h:473): its variance is
+    unbounded, and a plain mean is ruled by one firefly.  As usual for relMSE the largest TRIM of the per-value
+    errors are dropped — in both arms alike."""
+    x = np.nan_to_num(film_sum / float(spp))
+    e = np.sort(((x - ref) ** 2 / (ref ** 2 + 1e-2)).ravel())
+    return float(np.mean(e[: int(len(e) * (1.0 - TRIM))]))
+
+
+def test_relmse_converges_like_the_reference(bdpt, gpu_ctx, scenes):
+    v, m, mats, cam = scenes["cornell_box"]()
+    gpu_ctx.upload(v, m, mats)
+    gpu_ctx.render(bdpt.make_camera(W, H, 4096, DEPTH, **cam), seed=987654321, bvh=bdpt.BVH_FAST, height=H)
+    ref = np.nan_to_num(gpu_ctx.film() / 4096.0)
+    assert ref.max() > 0
+    cpu = Oracle("ref" if available("ref") else "port").load(v, m, mats)
+    g, c = [], []
+    for spp in SPPS:
+        eg, ec = [], []
+        for k in range(SEEDS):
+            gpu_ctx.render(bdpt.make_camera(W, H, spp, DEPTH, **cam), seed=1000 + 17 * k + spp, bvh=bdpt.BVH_FAST, height=H)
+            eg.append(rel_mse(gpu_ctx.film(), spp, ref))
+            f = cpu.render(ocam(W, H, spp, DEPTH, **cam), rng_mode=RNG_MT19937, seed=5000 + 31 * k + spp, height=H)
+            ec.append(rel_mse(f, spp, ref))
+        g.append(np.mean(eg))
+        c.append(np.mean(ec))
+    lx = np.log(np.array(SPPS, dtype=np.float64))
+    slope_g = np.polyfit(lx, np.log(g), 1)[0]
+    slope_c = np.polyfit(lx, np.log(c), 1)[0]
+    print("relMSE gpu", g, "cpu", c, "slopes", slope_g, slope_c)
+    # both converge at all (not a clean power law at 1-4 spp: most one-sample pixels see no connection)
+    assert g[-1] < 0.5 * g[1] and c[-1] < 0.5 * c[1]
+    assert abs(slope_g - slope_c) <= 0.1
+    for a, b in zip(g, c):
+        assert 0.8 <= a / b <= 1.25, (g, c)
