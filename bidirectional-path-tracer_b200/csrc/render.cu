@@ -295,7 +295,14 @@ __device__ __forceinline__ void bin_by_material(const WF& w, int cls, uint32_t p
     }
 }
 
-extern __shared__ StackEntry s_dyn_stack[];   // [levels][kBlock], sized at launch from the tree depths
+// Traversal stacks live in local memory (L1-cached, lane-interleaved by the hardware): a shared-memory stack
+// of tree-depth levels cost 24.5 KB per block, capped residency at 6 blocks per SM and shrank L1.
+#ifndef BDPT_TRAV_BLOCKS
+#define BDPT_TRAV_BLOCKS 10
+#endif
+constexpr int kTravBlocksPerSM = BDPT_TRAV_BLOCKS;   // residency target of the traversal kernels (register cap = 65536 / (128 * this))
+constexpr int kStackLevels = 32;              // StackEntry slots (fast tree, depth <= 23) = 64 int32 slots (reference tree)
+#define BDPT_DECLARE_STACK StackEntry l_stack[kStackLevels]
 
 // Blocks [0, n_def_blocks) re-trace the rays the PREVIOUS iteration's launch deferred (ties, knife edges,
 // zero direction components: traverse_fast.cuh) through the reference-exact traversal; there are a handful
@@ -303,9 +310,10 @@ extern __shared__ StackEntry s_dyn_stack[];   // [levels][kBlock], sized at laun
 // duration would be one thread's latency chain) they ride at the front of the next bulk launch and their
 // paths simply lag one iteration behind — path regeneration makes that free.
 template <int BVH, bool STATS>
-__global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
+__global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
                                                        const uint32_t* __restrict__ n_ptr, int dn, int ex, uint32_t n_def_blocks,
                                                        uint32_t limit, double* film, unsigned long long* stats) {
+    BDPT_DECLARE_STACK;
     int cls = -1;
     uint32_t pid = 0, defer_tag = 0;
     bool defer = false, ended = false;
@@ -319,9 +327,9 @@ __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, W
             TravStats ts{0, 0};
             bool found;
             if (BVH != BDPT_BVH_REFERENCE && (e & kSlowFlag))
-                found = traverse_fast<false, STATS, false>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts) == TR_HIT;
+                found = traverse_fast<false, STATS, false>(sc, r, h, l_stack, 1, &ts) == TR_HIT;
             else
-                found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+                found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
             if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
             cls = finish_trace(sc, f, w, pid, found, h, film);
             ended = cls < 0;
@@ -335,9 +343,9 @@ __global__ void __launch_bounds__(kBlock) k_trace_paths(SceneView sc, Frame f, W
             bool found;
             TravStats ts{0, 0};
             if (BVH == BDPT_BVH_REFERENCE) {
-                found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+                found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
             } else {
-                const int rc = traverse_fast<false, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts, limit);
+                const int rc = traverse_fast<false, STATS, true>(sc, r, h, l_stack, 1, &ts, limit);
                 found = rc == TR_HIT;
                 defer = rc == TR_DEFER || rc == TR_SLOW;
                 defer_tag = rc == TR_SLOW ? kSlowFlag : 0u;
@@ -655,8 +663,9 @@ __global__ void __launch_bounds__(kBlock) k_shadow_pre(SceneView sc, WF w, SQ q,
 // the payload; the other blocks walk this round's live segments under the work limit and park what they
 // cannot settle in ss[sx] for the next launch.
 template <int BVH, bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, SQ q, int sx, uint32_t n_slow_blocks, uint32_t limit, double* film,
+__global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView sc, WF w, SQ q, int sx, uint32_t n_slow_blocks, uint32_t limit, double* film,
                                                   unsigned long long* stats) {
+    BDPT_DECLARE_STACK;
     if (BVH == BDPT_BVH_REFERENCE) {
         const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
         if (i == 0) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)q.cnt[SQ_N]);
@@ -664,7 +673,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, SQ q, int
             const RayD r = load_shadow_ray(q, i);
             HitD h;
             TravStats ts{0, 0};
-            const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
+            const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
             if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
             if (!found) film_add(film, q.pix[i], mk(q.cx[i], q.cy[i], q.cz[i]));
         }
@@ -684,8 +693,8 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, SQ q, int
             HitD h;
             TravStats ts{0, 0};
             bool found;
-            if (q5.y) found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_dyn_stack + threadIdx.x), 2 * kBlock, &ts);
-            else found = traverse_fast<true, STATS, false>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts) == TR_HIT;
+            if (q5.y) found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
+            else found = traverse_fast<true, STATS, false>(sc, r, h, l_stack, 1, &ts) == TR_HIT;
             if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
             if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
         }
@@ -701,7 +710,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, SQ q, int
         r = load_shadow_ray(q, idx);
         HitD h;
         TravStats ts{0, 0};
-        const int rc = traverse_fast<true, STATS, true>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts, limit);
+        const int rc = traverse_fast<true, STATS, true>(sc, r, h, l_stack, 1, &ts, limit);
         park = rc == TR_DEFER || rc == TR_SLOW;
         kind = rc == TR_DEFER ? 1 : 0;
         if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
@@ -720,7 +729,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneView sc, WF w, SQ q, int
         } else {   // parking lot full: settle it here, unbounded
             HitD h;
             TravStats ts{0, 0};
-            const bool found = traverse_fast<true, STATS, false>(sc, r, h, s_dyn_stack + threadIdx.x, kBlock, &ts) == TR_HIT;
+            const bool found = traverse_fast<true, STATS, false>(sc, r, h, l_stack, 1, &ts) == TR_HIT;
             if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
             if (!found) film_add(film, pix, c);
         }
@@ -1097,7 +1106,11 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     J.sc = ctx->view; J.f = f; J.o = o; J.total = total; J.film = ctx->film; J.d_stats = ctx->d_stats;
     // traversal stack: one StackEntry per tree level per thread (deferred children only)
     const size_t levels = size_t(std::max(ctx->host.fast_depth, ctx->host.ref_depth)) + 2;
-    J.smem = levels * kBlock * sizeof(StackEntry);
+    if (ctx->host.fast_depth + 2 > uint32_t(kStackLevels) || ctx->host.ref_depth + 2 > uint32_t(2 * kStackLevels)) {
+        ctx->err = "BVH deeper than the traversal stack"; return BDPT_ERR_ARG;
+    }
+    (void)levels;
+    J.smem = 0;
     J.exact_grid = 148 * 2;
     J.device = ctx->device; J.n_workers = S; J.B = B;
     J.limit = 0;   // parking over-limit rays was measured slower than letting them finish in place
