@@ -27,12 +27,13 @@
 #include "ctx.h"
 #include "render_math.cuh"
 #include "traverse_fast.cuh"
+#include "traverse_walk.cuh"
 
 namespace bdpt {
 
 namespace {
 
-constexpr int kBlock = 128;
+constexpr int kBlock = 64;
 constexpr uint32_t kLightFlag = 0x80000000u;
 // Front blocks give every parked ray a warp of its own (lane 0): these rays are latency chains of ~1000
 // dependent steps, and 32 of them in one warp would serialise on each other's loop phases (measured: 7x
@@ -42,7 +43,7 @@ constexpr uint32_t kSlowFlag = 0x80000000u;   // q_exact entry: re-run the FAST 
 
 // device counters (uint32 each)
 enum { C_ACTIVE0 = 0, C_ACTIVE1 = 1, C_MAT0 = 2 /* ..5 */, C_SHADOW = 6, C_MAXNC = 7, C_MAXNL = 8, C_SUMNC = 9,
-       C_SUMNL = 10, C_OVERFLOW = 11, C_PAIRS_LO = 12, C_PAIRS_HI = 13 /* 64-bit, 8-byte aligned */, C_UNUSED14 = 14, C_EXACT_SHADOW = 15,
+       C_SUMNL = 10, C_OVERFLOW = 11, C_PAIRS_LO = 12, C_PAIRS_HI = 13 /* 64-bit, 8-byte aligned */, C_CURSOR = 14 /* dynamic-fetch cursor of the trace launch */, C_EXACT_SHADOW = 15,
        C_DONE0 = 16, C_DONE1 = 17, C_SHADOW_TOTAL = 18 /* ..19: 64-bit, shadow rays of the whole worker run */, C_SHADOW_LIVE = 20, C_EXACT0 = 21, C_EXACT1 = 22,
        C_SLOW_S0 = 24, C_SLOW_S1 = 25 /* parked shadow segments, ping-pong */, C_COUNT = 28 };
 
@@ -91,7 +92,7 @@ struct SQ {
     uint32_t* live;                  // segments the far-endpoint test did not settle (indices into this queue)
     uint32_t* cnt;                   // SQ_*
 };
-enum { SQ_N = 0, SQ_LIVE = 1, SQ_OVERFLOW = 2, SQ_COUNT = 8 };
+enum { SQ_N = 0, SQ_LIVE = 1, SQ_OVERFLOW = 2, SQ_CURSOR = 3 /* dynamic-fetch cursor of stage 2 */, SQ_COUNT = 8 };
 
 struct WF {              // wavefront workspace, all device pointers
     int64_t B;           // batch capacity in samples
@@ -298,9 +299,9 @@ __device__ __forceinline__ void bin_by_material(const WF& w, int cls, uint32_t p
 // Traversal stacks live in local memory (L1-cached, lane-interleaved by the hardware): a shared-memory stack
 // of tree-depth levels cost 24.5 KB per block, capped residency at 6 blocks per SM and shrank L1.
 #ifndef BDPT_TRAV_BLOCKS
-#define BDPT_TRAV_BLOCKS 10
+#define BDPT_TRAV_BLOCKS 8
 #endif
-constexpr int kTravBlocksPerSM = BDPT_TRAV_BLOCKS;   // residency target of the traversal kernels (register cap = 65536 / (128 * this))
+constexpr int kTravBlocksPerSM = BDPT_TRAV_BLOCKS * 128 / kBlock;   // residency target of the traversal kernels (register cap = 65536 / (128 * this))
 constexpr int kStackLevels = 32;              // StackEntry slots (fast tree, depth <= 23) = 64 int32 slots (reference tree)
 #define BDPT_DECLARE_STACK StackEntry l_stack[kStackLevels]
 
@@ -360,6 +361,92 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_paths(SceneV
     }
     bin_by_material(w, cls, pid);
     retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+}
+
+// ------------------------------------------------------------------ K1, fast flavour: persistent warps with dynamic fetch
+// Every warp keeps pulling rays from the queue (one atomic per refill) into the lanes whose ray is decided,
+// and its walk (traverse_walk.cuh) hands control back as soon as fewer than `threshold` lanes are still
+// walking.  All queue appends happen at the top of the loop, where the warp is converged.
+// Blocks [0, n_def_blocks) are the front blocks described above k_trace_paths.
+// a refill is worth its atomic and its ray set-up only when at least `min_idle` lanes are idle (or all are)
+__device__ __forceinline__ uint32_t warp_fetch(uint32_t* cursor, bool need, uint32_t n, bool& exhausted, int min_idle) {
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, need);
+    if (!mask || exhausted) return 0xFFFFFFFFu;
+    if (mask != 0xFFFFFFFFu && __popc(mask) < min_idle) return 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(cursor, uint32_t(__popc(mask)));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (base + uint32_t(__popc(mask)) >= n) exhausted = true;   // nothing left after this batch
+    const uint32_t my = base + uint32_t(__popc(mask & ((1u << lane) - 1u)));
+    return (need && my < n) ? my : 0xFFFFFFFFu;
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
+                                                                        const uint32_t* __restrict__ n_ptr, int dn, int ex,
+                                                                        uint32_t n_def_blocks, int threshold, double* film,
+                                                                        unsigned long long* stats) {
+    BDPT_DECLARE_STACK;
+    if (blockIdx.x < n_def_blocks) {
+        int cls = -1;
+        uint32_t pid = 0;
+        bool ended = false;
+        const uint32_t idx = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5);
+        if ((threadIdx.x & 31) == 0 && idx < w.counters[C_EXACT0 + (ex ^ 1)]) {
+            const uint32_t e = w.q_exact[ex ^ 1][idx];
+            pid = e & ~kSlowFlag;
+            const RayD r = load_path_ray(w, pid);
+            HitD h;
+            TravStats ts{0, 0};
+            const bool found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
+            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            cls = finish_trace(sc, f, w, pid, found, h, film);
+            ended = cls < 0;
+        }
+        bin_by_material(w, cls, pid);
+        retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+        return;
+    }
+    const uint32_t n = *n_ptr;
+    Walk<false, STATS> W;
+    bool have = false, exhausted = false;
+    int result = WALK_YIELD;   // != WALK_YIELD: this lane's ray `pid` is decided and waits for the epilogue
+    uint32_t pid = 0;
+    for (;;) {
+        __syncwarp();
+        // ---- epilogue of the lanes whose ray was decided in the last round
+        const bool fin = result != WALK_YIELD;
+        if (__any_sync(0xFFFFFFFFu, fin)) {
+            int cls = -1;
+            bool ended = false, defer = false;
+            if (fin) {
+                if (STATS && result != TR_DEFER) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+                if (result == TR_DEFER) defer = true;
+                else { cls = finish_trace(sc, f, w, pid, result == TR_HIT, W.hit, film); ended = cls < 0; }
+            }
+            const uint32_t slot = warp_append(w.counters + C_EXACT0 + ex, defer);
+            if (defer) w.q_exact[ex][slot] = pid;
+            bin_by_material(w, cls, pid);
+            retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+            result = WALK_YIELD;
+        }
+        // ---- refill the idle lanes
+        const uint32_t my = warp_fetch(w.counters + C_CURSOR, !have, n, exhausted, threshold >> 8);
+        if (my != 0xFFFFFFFFu) {
+            pid = queue[my];
+            const RayD r = load_path_ray(w, pid);
+            if (walk_eligible(sc, r)) { W.init(sc, r); have = true; }
+            else result = TR_DEFER;   // fp64 slabs or the reference tree: the next launch's front blocks
+        }
+        if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
+        // ---- walk
+        if (have) {
+            const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF));
+            if (rc != WALK_YIELD) { result = rc; have = false; }
+        }
+    }
 }
 
 // hit point and face-forwarded geometric normal (ray.h:21-23, hittable.h:20-26)
@@ -736,6 +823,79 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView s
     }
 }
 
+// ------------------------------------------------------------------ K4 stage 2, fast flavour: persistent warps with dynamic fetch
+// Same structure as k_trace_fast over this round's live segments (q.live).  A segment the fp32 walk cannot
+// settle (tie / knife edge / fp64 slabs needed) is parked in ss[sx] with its payload and finished by the
+// front blocks of a later launch through the reference traversal.
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneView sc, WF w, SQ q, int sx, uint32_t n_slow_blocks,
+                                                                         int threshold, double* film, unsigned long long* stats) {
+    BDPT_DECLARE_STACK;
+    if (blockIdx.x < n_slow_blocks) {   // one parked segment per warp at a time, warp-stride over the device-side count
+        const uint32_t n = min(w.counters[C_SLOW_S0 + (sx ^ 1)], uint32_t(w.sscap));
+        if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(&stats[ST_DEFER_SHADOW], (unsigned long long)n);
+        if ((threadIdx.x & 31) != 0) return;
+        for (uint32_t i = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5); i < n; i += n_slow_blocks * kFrontPerBlock) {
+            const SlowShadow* e = w.ss[sx ^ 1] + i;
+            const double2* pq = reinterpret_cast<const double2*>(e);
+            const double2 q0 = pq[0], q1 = pq[1], q2 = pq[2], q3 = pq[3], q4 = pq[4];
+            const int4 q5 = reinterpret_cast<const int4*>(e)[5];
+            RayD r;
+            r.o = mk(q0.x, q0.y, q1.x); r.d = mk(q1.y, q2.x, q2.y); r.tmin = 0.001; r.tmax = q3.x;
+            HitD h;
+            TravStats ts{0, 0};
+            const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
+            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
+        }
+        return;
+    }
+    const uint32_t n = q.cnt[SQ_LIVE];
+    Walk<true, STATS> W;
+    bool have = false, exhausted = false;
+    int result = WALK_YIELD;
+    uint32_t idx = 0;
+    for (;;) {
+        __syncwarp();
+        const bool fin = result != WALK_YIELD;
+        if (__any_sync(0xFFFFFFFFu, fin)) {
+            const bool park = fin && result == TR_DEFER;
+            if (fin && STATS && !park) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+            if (fin && result == TR_MISS) film_add(film, q.pix[idx], mk(q.cx[idx], q.cy[idx], q.cz[idx]));
+            const uint32_t slot = warp_append(w.counters + C_SLOW_S0 + sx, park);
+            if (park) {
+                const RayD r = load_shadow_ray(q, idx);
+                const D3 c = mk(q.cx[idx], q.cy[idx], q.cz[idx]);
+                const uint32_t pix = q.pix[idx];
+                if (slot < uint32_t(w.sscap)) {
+                    SlowShadow* e = w.ss[sx] + slot;
+                    double2* pq = reinterpret_cast<double2*>(e);
+                    pq[0] = make_double2(r.o.x, r.o.y); pq[1] = make_double2(r.o.z, r.d.x); pq[2] = make_double2(r.d.y, r.d.z);
+                    pq[3] = make_double2(r.tmax, c.x); pq[4] = make_double2(c.y, c.z);
+                    reinterpret_cast<int4*>(e)[5] = make_int4(int(pix), 1, 0, 0);
+                } else {   // parking lot full: settle it here
+                    HitD h;
+                    const bool found = traverse_ref<true, false>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, nullptr);
+                    if (!found) film_add(film, pix, c);
+                }
+            }
+            result = WALK_YIELD;
+        }
+        const uint32_t my = warp_fetch(q.cnt + SQ_CURSOR, !have, n, exhausted, threshold >> 8);
+        if (my != 0xFFFFFFFFu) {
+            idx = q.live[my];
+            const RayD r = load_shadow_ray(q, idx);
+            if (walk_eligible(sc, r)) { W.init(sc, r); have = true; }
+            else result = TR_DEFER;
+        }
+        if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
+        if (have) {
+            const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF));
+            if (rc != WALK_YIELD) { result = rc; have = false; }
+        }
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------ host side
@@ -883,6 +1043,8 @@ struct Job {
     int64_t B;                       // sample slots per wavefront (every worker's workspace holds at least this many)
     std::atomic<int64_t>* next;      // next sample of this call not yet handed to a worker
     uint32_t limit;                  // work limit of the bulk traversal launches (traverse_fast.cuh); 0 = none
+    unsigned resident_blocks;        // blocks of a traversal kernel the device keeps resident (persistent grids)
+    int threshold;                   // dynamic fetch: a walk yields when fewer lanes than this are still walking
 };
 
 // One worker: a wavefront of B slots, refilled from the call's shared sample counter until it runs dry.
@@ -922,9 +1084,10 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
                 else k_shadow_pre<false><<<grid_for(ns_bound, kBlock), kBlock, 0, st2>>>(sc, wf, q, J.d_stats);
                 wk.launches += 1;
             }
-            const unsigned gm = ns_bound ? grid_for(ns_bound, kBlock) : 0u;
-            if (want_stats) k_shadow<BDPT_BVH_FAST, true><<<kFrontBlocks + gm, kBlock, smem, st2>>>(sc, wf, q, sx, kFrontBlocks, J.limit, J.film, J.d_stats);
-            else k_shadow<BDPT_BVH_FAST, false><<<kFrontBlocks + gm, kBlock, smem, st2>>>(sc, wf, q, sx, kFrontBlocks, J.limit, J.film, J.d_stats);
+            // persistent: no more blocks than stay resident; the warps pull their segments from q.live
+            const unsigned gm = ns_bound ? std::min(grid_for(ns_bound, kBlock), J.resident_blocks) : 0u;
+            if (want_stats) k_shadow_fast<true><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.film, J.d_stats);
+            else k_shadow_fast<false><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.film, J.d_stats);
             sx ^= 1;
         }
         tm.end(KT_SHADOW, st2);
@@ -956,7 +1119,11 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         tm.begin(KT_TRACE, st);
 #define BDPT_TP(B, S) k_trace_paths<B, S><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.limit, J.film, J.d_stats)
         if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
-        else { if (want_stats) BDPT_TP(BDPT_BVH_FAST, true); else BDPT_TP(BDPT_BVH_FAST, false); }
+        else {
+            const unsigned gp = std::min(g, J.resident_blocks);
+            if (want_stats) k_trace_fast<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.film, J.d_stats);
+            else k_trace_fast<false><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.film, J.d_stats);
+        }
 #undef BDPT_TP
         tm.end(KT_TRACE, st);
         tm.begin(KT_SHADE, st);
@@ -1115,6 +1282,13 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     J.device = ctx->device; J.n_workers = S; J.B = B;
     J.limit = 0;   // parking over-limit rays was measured slower than letting them finish in place
     if (const char* e = std::getenv("BDPT_WORK_LIMIT")) J.limit = uint32_t(std::strtoul(e, nullptr, 10));
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    J.resident_blocks = unsigned(sms * kTravBlocksPerSM);
+    int slice = 4, min_idle = 8;   // walk time slice (leaf visits) and idle lanes that trigger a refill
+    if (const char* e = std::getenv("BDPT_WALK_SLICE")) slice = std::atoi(e);
+    if (const char* e = std::getenv("BDPT_MIN_IDLE")) min_idle = std::atoi(e);
+    J.threshold = (slice & 0xFF) | (min_idle << 8);
     std::atomic<int64_t> next_sample{0};
     J.next = &next_sample;
 
