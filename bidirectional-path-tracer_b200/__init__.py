@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(HERE, "libbdpt.so")
 
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_LIGHT = 0, 1, 2, 3
 BVH_REFERENCE, BVH_FAST = 0, 1
-TRACE_CLOSEST, TRACE_ANY, TRACE_DEVICE_PTRS, TRACE_STATS = 0, 1, 16, 32
+TRACE_CLOSEST, TRACE_ANY, TRACE_DEVICE_PTRS, TRACE_STATS, TRACE_SPLIT = 0, 1, 16, 32, 64
 MISS = 0xFFFFFFFF
 
 RAY_DTYPE = np.dtype([("o", "<f8", 3), ("d", "<f8", 3), ("tmin", "<f8"), ("tmax", "<f8")])
@@ -252,11 +252,11 @@ class Context:
         self._chk(lib().bdpt_bvh_leaf_order(self._h, out.ctypes.data), "bdpt_bvh_leaf_order")
         return out
 
-    def trace(self, rays8, bvh=BVH_REFERENCE, any_hit=False, stats=False):
+    def trace(self, rays8, bvh=BVH_REFERENCE, any_hit=False, stats=False, split=False):
         """Host buffers in, host buffers out (the e2e path). Returns structured HIT_DTYPE array."""
         r = pack_rays(rays8)
         out = np.empty(len(r), HIT_DTYPE)
-        flags = (TRACE_ANY if any_hit else 0) | (TRACE_STATS if stats else 0)
+        flags = (TRACE_ANY if any_hit else 0) | (TRACE_STATS if stats else 0) | (TRACE_SPLIT if split else 0)
         self._chk(lib().bdpt_trace(self._h, bvh, r.ctypes.data if len(r) else None, len(r),
                                    out.ctypes.data if len(r) else None, flags), "bdpt_trace")
         return out

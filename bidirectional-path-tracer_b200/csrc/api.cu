@@ -9,6 +9,7 @@
 #include "ctx.h"
 #include "traverse_ref.cuh"
 #include "traverse_fast.cuh"
+#include "traverse_walk.cuh"
 
 using namespace bdpt;
 
@@ -67,6 +68,34 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(SceneView sc, const bdpt_
         atomicAdd(&stats[ST_NODE], (unsigned long long)st.nodes);
         atomicAdd(&stats[ST_TRI], (unsigned long long)st.tris);
     }
+}
+
+// the same, one ray per WARP through split_walk (traverse_walk.cuh); ties found on the way fall back to the
+// reference traversal on lane 0, as in the render kernels' front blocks
+template <bool ANY>
+__global__ void __launch_bounds__(kTraceBlock) k_trace_split(SceneView sc, const bdpt_ray* __restrict__ rays, uint64_t n,
+                                                            bdpt_hit* __restrict__ out) {
+    StackEntry l_stack[32];
+    const uint64_t i = (uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x) >> 5;
+    if (i >= n) return;   // warp-uniform
+    const double2* q = reinterpret_cast<const double2*>(rays + i);
+    double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
+    RayD r;
+    r.o = mk(a.x, a.y, b.x); r.d = mk(b.y, c.x, c.y); r.tmin = e.x; r.tmax = e.y;
+    HitD h;
+    h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS;
+    TravStats ts{0, 0};
+    int rc = TR_DEFER;
+    if (walk_eligible(sc, r)) rc = split_walk<ANY, false>(sc, r, h, l_stack, ts);
+    if ((threadIdx.x & 31) != 0) return;
+    const bool found = rc == TR_DEFER ? traverse_ref<ANY, false>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, nullptr) : rc == TR_HIT;
+    if (!found) { h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS; }
+    double2* o = reinterpret_cast<double2*>(out + i);
+    o[0] = make_double2(h.t, h.u);
+    double2 w;
+    w.x = h.v;
+    w.y = __longlong_as_double((long long)(unsigned long long)h.prim);
+    o[1] = w;
 }
 
 // camera::visible (camera.h:425-438)
@@ -243,6 +272,14 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
     const unsigned grid = unsigned((n + kTraceBlock - 1) / kTraceBlock);
     SceneView v = ctx->view;
     unsigned long long* st = ctx->d_stats;
+    if ((flags & BDPT_TRACE_SPLIT) && bvh == BDPT_BVH_FAST) {
+        const unsigned wgrid = unsigned((n * 32 + kTraceBlock - 1) / kTraceBlock);
+        if (any) k_trace_split<true><<<wgrid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out);
+        else k_trace_split<false><<<wgrid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out);
+        ctx->launches += 1;
+        BDPT_CUDA(ctx, cudaGetLastError());
+        return BDPT_OK;
+    }
 #define BDPT_LAUNCH(B, A, S) k_trace<B, A, S><<<grid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out, st)
     if (bvh == BDPT_BVH_REFERENCE) {
         if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, false); }

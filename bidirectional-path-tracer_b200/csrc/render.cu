@@ -386,7 +386,7 @@ __device__ __forceinline__ uint32_t warp_fetch(uint32_t* cursor, bool need, uint
 template <bool STATS>
 __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
                                                                         const uint32_t* __restrict__ n_ptr, int dn, int ex,
-                                                                        uint32_t n_def_blocks, int threshold, double* film,
+                                                                        uint32_t n_def_blocks, int threshold, uint32_t limit, double* film,
                                                                         unsigned long long* stats) {
     BDPT_DECLARE_STACK;
     if (blockIdx.x < n_def_blocks) {
@@ -394,16 +394,23 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
         uint32_t pid = 0;
         bool ended = false;
         const uint32_t idx = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5);
-        if ((threadIdx.x & 31) == 0 && idx < w.counters[C_EXACT0 + (ex ^ 1)]) {
+        const bool lane0 = (threadIdx.x & 31) == 0;
+        if (idx < w.counters[C_EXACT0 + (ex ^ 1)]) {   // warp-uniform
             const uint32_t e = w.q_exact[ex ^ 1][idx];
             pid = e & ~kSlowFlag;
             const RayD r = load_path_ray(w, pid);
             HitD h;
             TravStats ts{0, 0};
-            const bool found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
+            // over the work limit: the whole warp walks it, split 32 ways; anything else (or a tie found on the
+            // way): the reference traversal on lane 0
+            int rc = TR_DEFER;
+            if (e & kSlowFlag) rc = split_walk<false, STATS>(sc, r, h, l_stack, ts);
+            if (lane0) {
+            const bool found = rc == TR_DEFER ? traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts) : rc == TR_HIT;
             if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
             cls = finish_trace(sc, f, w, pid, found, h, film);
             ended = cls < 0;
+            }
         }
         bin_by_material(w, cls, pid);
         retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
@@ -422,12 +429,12 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
             int cls = -1;
             bool ended = false, defer = false;
             if (fin) {
-                if (STATS && result != TR_DEFER) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
-                if (result == TR_DEFER) defer = true;
+                if (STATS && result != TR_DEFER && result != TR_SLOW) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+                if (result == TR_DEFER || result == TR_SLOW) defer = true;
                 else { cls = finish_trace(sc, f, w, pid, result == TR_HIT, W.hit, film); ended = cls < 0; }
             }
             const uint32_t slot = warp_append(w.counters + C_EXACT0 + ex, defer);
-            if (defer) w.q_exact[ex][slot] = pid;
+            if (defer) w.q_exact[ex][slot] = pid | (result == TR_SLOW ? kSlowFlag : 0u);
             bin_by_material(w, cls, pid);
             retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
             result = WALK_YIELD;
@@ -443,7 +450,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
         if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
         // ---- walk
         if (have) {
-            const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF));
+            const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF), limit);
             if (rc != WALK_YIELD) { result = rc; have = false; }
         }
     }
@@ -829,12 +836,13 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView s
 // front blocks of a later launch through the reference traversal.
 template <bool STATS>
 __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneView sc, WF w, SQ q, int sx, uint32_t n_slow_blocks,
-                                                                         int threshold, double* film, unsigned long long* stats) {
+                                                                         int threshold, uint32_t limit, double* film,
+                                                                         unsigned long long* stats) {
     BDPT_DECLARE_STACK;
     if (blockIdx.x < n_slow_blocks) {   // one parked segment per warp at a time, warp-stride over the device-side count
         const uint32_t n = min(w.counters[C_SLOW_S0 + (sx ^ 1)], uint32_t(w.sscap));
         if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(&stats[ST_DEFER_SHADOW], (unsigned long long)n);
-        if ((threadIdx.x & 31) != 0) return;
+        const bool lane0 = (threadIdx.x & 31) == 0;
         for (uint32_t i = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5); i < n; i += n_slow_blocks * kFrontPerBlock) {
             const SlowShadow* e = w.ss[sx ^ 1] + i;
             const double2* pq = reinterpret_cast<const double2*>(e);
@@ -844,7 +852,10 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
             r.o = mk(q0.x, q0.y, q1.x); r.d = mk(q1.y, q2.x, q2.y); r.tmin = 0.001; r.tmax = q3.x;
             HitD h;
             TravStats ts{0, 0};
-            const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
+            int rc = TR_DEFER;   // kind 1: the reference traversal; kind 0 (over the work limit): split over the warp
+            if (q5.y == 0) rc = split_walk<true, STATS>(sc, r, h, l_stack, ts);
+            if (!lane0) continue;
+            const bool found = rc == TR_DEFER ? traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts) : rc == TR_HIT;
             if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
             if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
         }
@@ -859,7 +870,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
         __syncwarp();
         const bool fin = result != WALK_YIELD;
         if (__any_sync(0xFFFFFFFFu, fin)) {
-            const bool park = fin && result == TR_DEFER;
+            const bool park = fin && (result == TR_DEFER || result == TR_SLOW);
             if (fin && STATS && !park) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
             if (fin && result == TR_MISS) film_add(film, q.pix[idx], mk(q.cx[idx], q.cy[idx], q.cz[idx]));
             const uint32_t slot = warp_append(w.counters + C_SLOW_S0 + sx, park);
@@ -872,7 +883,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
                     double2* pq = reinterpret_cast<double2*>(e);
                     pq[0] = make_double2(r.o.x, r.o.y); pq[1] = make_double2(r.o.z, r.d.x); pq[2] = make_double2(r.d.y, r.d.z);
                     pq[3] = make_double2(r.tmax, c.x); pq[4] = make_double2(c.y, c.z);
-                    reinterpret_cast<int4*>(e)[5] = make_int4(int(pix), 1, 0, 0);
+                    reinterpret_cast<int4*>(e)[5] = make_int4(int(pix), result == TR_DEFER ? 1 : 0, 0, 0);
                 } else {   // parking lot full: settle it here
                     HitD h;
                     const bool found = traverse_ref<true, false>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, nullptr);
@@ -890,7 +901,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
         }
         if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
         if (have) {
-            const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF));
+            const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF), limit);
             if (rc != WALK_YIELD) { result = rc; have = false; }
         }
     }
@@ -1042,7 +1053,7 @@ struct Job {
     size_t smem; unsigned exact_grid; int device; int n_workers;
     int64_t B;                       // sample slots per wavefront (every worker's workspace holds at least this many)
     std::atomic<int64_t>* next;      // next sample of this call not yet handed to a worker
-    uint32_t limit;                  // work limit of the bulk traversal launches (traverse_fast.cuh); 0 = none
+    uint32_t limit, limit_shadow;    // work limits of the bulk traversal launches (traverse_walk.cuh); 0 = none
     unsigned resident_blocks;        // blocks of a traversal kernel the device keeps resident (persistent grids)
     int threshold;                   // dynamic fetch: a walk yields when fewer lanes than this are still walking
 };
@@ -1086,8 +1097,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
             }
             // persistent: no more blocks than stay resident; the warps pull their segments from q.live
             const unsigned gm = ns_bound ? std::min(grid_for(ns_bound, kBlock), J.resident_blocks) : 0u;
-            if (want_stats) k_shadow_fast<true><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.film, J.d_stats);
-            else k_shadow_fast<false><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.film, J.d_stats);
+            if (want_stats) k_shadow_fast<true><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.limit_shadow, J.film, J.d_stats);
+            else k_shadow_fast<false><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.limit_shadow, J.film, J.d_stats);
             sx ^= 1;
         }
         tm.end(KT_SHADOW, st2);
@@ -1121,16 +1132,17 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
         else {
             const unsigned gp = std::min(g, J.resident_blocks);
-            if (want_stats) k_trace_fast<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.film, J.d_stats);
-            else k_trace_fast<false><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.film, J.d_stats);
+            if (want_stats) k_trace_fast<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
+            else k_trace_fast<false><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
         }
 #undef BDPT_TP
         tm.end(KT_TRACE, st);
         tm.begin(KT_SHADE, st);
-        k_shade_light<<<g, kBlock, 0, st>>>(sc, f, wf, dn, J.film);
-        k_shade_lambert<<<g, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
-        k_shade_metal<<<g, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
-        k_shade_dielectric<<<g, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
+        const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kBlock);   // the lagged rays of the front blocks are shaded too
+        k_shade_light<<<gsh, kBlock, 0, st>>>(sc, f, wf, dn, J.film);
+        k_shade_lambert<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
+        k_shade_metal<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
+        k_shade_dielectric<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
         k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
         tm.end(KT_SHADE, st);
         wk.launches += 6;
@@ -1231,7 +1243,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     }
 
     // wavefront size and how many wavefronts are kept in flight
-    int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 19);
+    int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 20);
     B = std::min<int64_t>(B, int64_t(1) << 30);
     int S = o.streams > 0 ? o.streams : 4;
     S = int(std::min<int64_t>(std::min(S, 16), std::max<int64_t>(1, total / 8192)));
@@ -1280,8 +1292,13 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     J.smem = 0;
     J.exact_grid = 148 * 2;
     J.device = ctx->device; J.n_workers = S; J.B = B;
-    J.limit = 0;   // parking over-limit rays was measured slower than letting them finish in place
+    // Work limit: rays over this many nodes + triangles are parked and re-run split over a warp (traverse_walk.cuh:
+    // split_walk).  Off by default: on the named scenes ~16 % of the unoccluded shadow segments exceed 160 steps
+    // (mean 115), so parking them was measured slower; BDPT_WORK_LIMIT=n turns it on.
+    J.limit = 0;
     if (const char* e = std::getenv("BDPT_WORK_LIMIT")) J.limit = uint32_t(std::strtoul(e, nullptr, 10));
+    J.limit_shadow = J.limit;
+    if (const char* e = std::getenv("BDPT_WORK_LIMIT_SHADOW")) J.limit_shadow = uint32_t(std::strtoul(e, nullptr, 10));
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
     J.resident_blocks = unsigned(sms * kTravBlocksPerSM);

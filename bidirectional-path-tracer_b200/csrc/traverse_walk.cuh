@@ -29,6 +29,8 @@ struct Walk {
     // ray (fp64 for the triangle tests, fp32 for the slabs)
     RayD r;
     float ox, oy, oz, ix, iy, iz, tmin_t, best_t;
+    float cull_hi;     // upper end of the part of the ray this walk is responsible for (split walks), else FLT_MAX
+    uint32_t work;     // nodes + triangles touched so far
     double best, band_abs;
     // answer so far
     HitD hit;
@@ -42,15 +44,21 @@ struct Walk {
     int n_edge;
     TravStats ts;
 
-    __device__ __forceinline__ void init(const SceneView& sc, const RayD& ray) {
+    // [cull_lo, cull_hi] (fp32, conservative): only boxes overlapping this part of the ray are opened.  Hits are
+    // still accepted over the ray's whole interval, so a split walk returns a valid hit of the full ray and the
+    // closest one whenever it lies in its part.
+    __device__ __forceinline__ void init(const SceneView& sc, const RayD& ray, float cull_lo = 0.f,
+                                         float cull_hi_ = 3.402823466e+38f) {
         r = ray;
         ox = float(r.o.x); oy = float(r.o.y); oz = float(r.o.z);
         ix = float(1.0 / r.d.x); iy = float(1.0 / r.d.y); iz = float(1.0 / r.d.z);
         const double inv_max = fmin(fabs(1.0 / r.d.x), fmin(fabs(1.0 / r.d.y), fabs(1.0 / r.d.z)));
         band_abs = 1e-10 * sc.extent * inv_max;
-        tmin_t = __double2float_rd(r.tmin);
+        tmin_t = fmaxf(__double2float_rd(r.tmin), cull_lo);
+        cull_hi = cull_hi_;
         best = r.tmax;
-        best_t = __double2float_ru(best);
+        best_t = fminf(__double2float_ru(best), cull_hi);
+        work = 0;
         best_rank = 0;
         found = false; flagged = false;
         sp = 0; cur = 0;
@@ -69,16 +77,17 @@ struct Walk {
     }
 
     // Walks until the ray is decided (returns TR_HIT / TR_MISS / TR_DEFER) or until it has visited `rounds`
-    // leaves (returns WALK_YIELD; call again to continue; rounds <= 0: no limit).  The time slice is what
+    // leaves (returns WALK_YIELD; call again to continue; rounds <= 0: no limit), or TR_SLOW once it has touched
+    // more than `limit` nodes + triangles (limit 0: never).  The time slice is what
     // brings the warp back together: __activemask() inside the walk only sees the lanes that happen to be
     // scheduled together, not the lanes that still have work.
-    __device__ __forceinline__ int run(const SceneView& sc, StackEntry* stack, int rounds);
+    __device__ __forceinline__ int run(const SceneView& sc, StackEntry* stack, int rounds, uint32_t limit = 0);
     // the decision once the walk has ended (the tail of traverse_fast_t)
     __device__ __forceinline__ int finish(const SceneView& sc);
 };
 
 template <bool ANY, bool STATS>
-__device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackEntry* stack, int rounds) {
+__device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackEntry* stack, int rounds, uint32_t limit) {
     for (;;) {
         // ---- inner nodes: descend until a leaf (or the stack runs dry)
         while (cur >= 0) {
@@ -86,6 +95,7 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
             const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
             const int4 w = __ldg(reinterpret_cast<const int4*>(q + 3));
             if (STATS) ++ts.nodes;
+            ++work;
             // a = l_lo.xyz l_hi.x | b = l_hi.yz r_lo.xy | c = r_lo.z r_hi.xyz
             float ln = tmin_t, lf = best_t, rn = tmin_t, rf = best_t;
             slab_fast<float>(a.x, a.w, ox, ix, ln, lf);
@@ -109,6 +119,8 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
         // ---- leaf: cur = ~(first << 3 | count-1)
         const uint32_t code = uint32_t(~cur);
         const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+        work += cnt;
+        if (limit && work > limit) return TR_SLOW;   // nothing decided: the caller parks the ray for a split walk
         for (uint32_t k = 0; k < cnt; ++k) {
             const uint32_t prim = __ldg(sc.fast_prims + first + k);
             if (STATS) ++ts.tris;
@@ -134,7 +146,7 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
                     const uint32_t rank = __ldg(sc.dfs_rank + prim);
                     if (!found || t < best || rank > best_rank) {
                         best = t; best_rank = rank; found = true;
-                        best_t = __double2float_ru(best);
+                        best_t = fminf(__double2float_ru(best), cull_hi);
                         hit.t = t; hit.u = u; hit.v = v; hit.prim = prim;
                     }
                 }
@@ -167,6 +179,73 @@ __device__ __forceinline__ int Walk<ANY, STATS>::finish(const SceneView& sc) {
         return found ? TR_HIT : TR_MISS;
     }
     return TR_DEFER;
+}
+
+// One ray walked by a whole warp: lane j opens only the boxes that overlap the j-th of 32 equal parts of the
+// ray's passage through the scene, so a ray that would touch ~1000 nodes on its own (a segment running
+// inside a tessellated plane) costs each lane ~1/32 of that plus the top of the tree.  Every lane still
+// accepts hits over the whole interval, so the answer is: ANY — occluded if any lane found an occluder;
+// closest — the smallest t over the lanes, deferred to the reference tree when two different triangles tie
+// within the band, exactly as within one walk.  Must be called by all 32 lanes with the same ray (which must
+// be walk_eligible).  The result is valid in every lane.
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+    return v;
+}
+
+template <bool ANY, bool STATS>
+__device__ __forceinline__ int split_walk(const SceneView& sc, const RayD& r, HitD& hit, StackEntry* stack, TravStats& ts) {
+    const int lane = threadIdx.x & 31;
+    // the ray's passage through a cube around the scene (wider than every padded box of the fast tree)
+    const double h = 0.5005 * sc.extent + 1e-300;
+    double t0 = r.tmin, t1 = r.tmax;
+    {
+        const double cx[3] = {sc.center.x, sc.center.y, sc.center.z}, o[3] = {r.o.x, r.o.y, r.o.z}, d[3] = {r.d.x, r.d.y, r.d.z};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double inv = 1.0 / d[k];
+            const double a = (cx[k] - h - o[k]) * inv, b = (cx[k] + h - o[k]) * inv;
+            t0 = fmax(t0, fmin(a, b));
+            t1 = fmin(t1, fmax(a, b));
+        }
+    }
+    if (!(t0 <= t1)) return TR_MISS;   // never enters the scene: no box can be opened, no candidate exists
+    const double step = (t1 - t0) * (1.0 / 32.0);
+    const float lo = __double2float_rd(t0 + step * lane), hi = lane == 31 ? __double2float_ru(t1) : __double2float_ru(t0 + step * (lane + 1));
+    Walk<ANY, STATS> W;
+    W.init(sc, r, lo, hi);
+    const int rc = W.run(sc, stack, 0, 0);
+    if (STATS) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { W.ts.nodes += __shfl_xor_sync(0xFFFFFFFFu, W.ts.nodes, o); W.ts.tris += __shfl_xor_sync(0xFFFFFFFFu, W.ts.tris, o); }
+        ts.nodes += W.ts.nodes; ts.tris += W.ts.tris;
+    }
+    if (ANY) {
+        const uint32_t hits = __ballot_sync(0xFFFFFFFFu, rc == TR_HIT);
+        if (hits) {
+            const int src = __ffs(hits) - 1;
+            hit.prim = __shfl_sync(0xFFFFFFFFu, W.hit.prim, src);
+            hit.t = __shfl_sync(0xFFFFFFFFu, W.hit.t, src); hit.u = 0.0; hit.v = 0.0;
+            return TR_HIT;
+        }
+        return __any_sync(0xFFFFFFFFu, rc == TR_DEFER) ? TR_DEFER : TR_MISS;
+    }
+    if (__any_sync(0xFFFFFFFFu, rc == TR_DEFER)) return TR_DEFER;
+    const double inf = __longlong_as_double(0x7FF0000000000000LL);
+    const double mine = W.found ? W.best : inf;
+    const double tmin_all = warp_min(mine);
+    if (!(tmin_all < inf)) return TR_MISS;
+    const uint32_t winners = __ballot_sync(0xFFFFFFFFu, W.found && mine == tmin_all);
+    const int src = __ffs(winners) - 1;
+    const uint32_t prim = __shfl_sync(0xFFFFFFFFu, W.hit.prim, src);
+    const double band = W.band_abs + 1e-10 * fabs(tmin_all);
+    if (__any_sync(0xFFFFFFFFu, W.found && W.hit.prim != prim && fabs(mine - tmin_all) <= band)) return TR_DEFER;
+    hit.prim = prim;
+    hit.t = tmin_all;
+    hit.u = __shfl_sync(0xFFFFFFFFu, W.hit.u, src);
+    hit.v = __shfl_sync(0xFFFFFFFFu, W.hit.v, src);
+    return TR_HIT;
 }
 
 }  // namespace bdpt

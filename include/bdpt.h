@@ -67,7 +67,9 @@ enum {
     BDPT_TRACE_CLOSEST = 0,
     BDPT_TRACE_ANY     = 1,   /* shadow query: prim = any occluder or MISS, t undefined */
     BDPT_TRACE_DEVICE_PTRS = 16, /* rays/out pointers are device memory of the ctx's device */
-    BDPT_TRACE_STATS = 32        /* count node visits / triangle tests into bdpt_stats (slower) */
+    BDPT_TRACE_STATS = 32,       /* count node visits / triangle tests into bdpt_stats (slower) */
+    BDPT_TRACE_SPLIT = 64        /* BDPT_BVH_FAST only: every ray is walked by a whole warp, split 32 ways along its length
+                                    (the kernel path bdpt_render uses for rays over its work limit); same answers */
 };
 
 #define BDPT_MISS 0xFFFFFFFFu

@@ -96,3 +96,21 @@ def test_render_edge_cases(bdpt, gpu_ctx, scenes):
         ocam(8, 8, 1, 4, lookfrom=cam["lookfrom"], lookat=cam["lookat"], vfov=cam["vfov"], background=(0.5, 0.25, 1.0)),
         rng_mode=RNG_PHILOX, seed=0, height=8)
     assert rel_err(gpu_ctx.film(), ref) < 1e-9 or not ref.any()
+
+
+def test_split_walk_and_parking_keep_the_film(bdpt, gpu_ctx, scenes, monkeypatch):
+    """BDPT_WORK_LIMIT parks every ray that touches more than n nodes + triangles and re-runs it split 32 ways over
+    a warp (traverse_walk.cuh: split_walk); the film must not move."""
+    v, m, mats, cam = scenes["cornell_spheres"]()
+    gpu_ctx.upload(v, m, mats)
+    c = bdpt.make_camera(24, 24, 9, 10, **cam)
+    monkeypatch.delenv("BDPT_WORK_LIMIT", raising=False)
+    gpu_ctx.render(c, seed=11, bvh=bdpt.BVH_FAST, height=24)
+    whole = gpu_ctx.film()
+    for limit in ("8", "40"):
+        monkeypatch.setenv("BDPT_WORK_LIMIT", limit)
+        gpu_ctx.stats_reset()
+        gpu_ctx.render(c, seed=11, bvh=bdpt.BVH_FAST, height=24, batch_samples=1500)
+        assert rel_err(gpu_ctx.film(), whole) < 1e-12
+        st = gpu_ctx.stats()
+        assert st["deferred_closest"] > 0 and st["deferred_shadow"] > 0   # the parked paths really ran

@@ -106,3 +106,16 @@ def test_state_errors(bdpt):
     with pytest.raises(bdpt.BdptError, match="no scene"):
         ctx.trace(np.zeros((1, 8)))
     ctx.close()
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_split_walk_matches_reference_golden(name, bdpt, gpu_ctx, scenes, golden):
+    """The warp-cooperative walk (one ray split 32 ways along its length, traverse_walk.cuh) returns the reference's
+    hits bit for bit: it is the path bdpt_render sends rays over its work limit through."""
+    g = golden(name)
+    v, m, mats, cam = scenes[name]()
+    gpu_ctx.upload(v, m, mats)
+    h = gpu_ctx.trace(g["rays"], bvh=1, split=True)
+    check_hits(h, g["prim"], g["t"], g["u"], g["v"], exact=True)
+    ha = gpu_ctx.trace(g["rays"], bvh=1, any_hit=True, split=True)
+    assert np.array_equal(ha["prim"] != 0xFFFFFFFF, g["prim"] != 0xFFFFFFFF)
