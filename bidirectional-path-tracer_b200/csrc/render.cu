@@ -1080,7 +1080,7 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
     int sb = 0;                      // shadow queue the next connect round writes
     bool first = true;
     cudaStream_t st2 = (o.flags & BDPT_RENDER_SERIAL) ? wk.stream : wk.stream2;
-    constexpr unsigned kFrontBlocks = 64;   // 256 warps drain the parked segments, one segment per warp at a time
+    constexpr unsigned kFrontBlocks = 148;    // 296 warps drain the parked segments, one segment per warp at a time
     // the shadow stage of one connect round, on the side stream: front blocks drain what earlier launches
     // parked, the rest walk this round's live segments
     auto launch_shadow = [&](const SQ& q, uint32_t ns_bound) {

@@ -24,11 +24,21 @@ __device__ __forceinline__ bool walk_eligible(const SceneView& sc, const RayD& r
            fabs(sc.center.x) <= far && fabs(sc.center.y) <= far && fabs(sc.center.z) <= far;
 }
 
+// One slab in fp32 with explicit FMAs (this file is compiled with -fmad=false for the fp64 parity code):
+// t = plane * inv - o * inv.  Against (plane - o) * inv this moves the result by a few ulps of |o * inv|,
+// which stays far inside the outward padding of the boxes (2^-16 of the scene extent, fast_bvh.cu) for the
+// rays that are walk_eligible (origin within 8 extents).
+__device__ __forceinline__ void slab_fma(float lo, float hi, float noi, float inv, float& tn, float& tf) {
+    const float t0 = __fmaf_rn(lo, inv, noi), t1 = __fmaf_rn(hi, inv, noi);
+    tn = fmaxf(tn, fminf(t0, t1));
+    tf = fminf(tf, fmaxf(t0, t1));
+}
+
 template <bool ANY, bool STATS>
 struct Walk {
     // ray (fp64 for the triangle tests, fp32 for the slabs)
     RayD r;
-    float ox, oy, oz, ix, iy, iz, tmin_t, best_t;
+    float ox, oy, oz, ix, iy, iz, tmin_t, best_t;   // ox.. hold -o * inv: one FMA per slab plane
     float cull_hi;     // upper end of the part of the ray this walk is responsible for (split walks), else FLT_MAX
     uint32_t work;     // nodes + triangles touched so far
     double best, band_abs;
@@ -50,8 +60,8 @@ struct Walk {
     __device__ __forceinline__ void init(const SceneView& sc, const RayD& ray, float cull_lo = 0.f,
                                          float cull_hi_ = 3.402823466e+38f) {
         r = ray;
-        ox = float(r.o.x); oy = float(r.o.y); oz = float(r.o.z);
         ix = float(1.0 / r.d.x); iy = float(1.0 / r.d.y); iz = float(1.0 / r.d.z);
+        ox = -float(r.o.x) * ix; oy = -float(r.o.y) * iy; oz = -float(r.o.z) * iz;
         const double inv_max = fmin(fabs(1.0 / r.d.x), fmin(fabs(1.0 / r.d.y), fabs(1.0 / r.d.z)));
         band_abs = 1e-10 * sc.extent * inv_max;
         tmin_t = fmaxf(__double2float_rd(r.tmin), cull_lo);
@@ -98,12 +108,12 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
             ++work;
             // a = l_lo.xyz l_hi.x | b = l_hi.yz r_lo.xy | c = r_lo.z r_hi.xyz
             float ln = tmin_t, lf = best_t, rn = tmin_t, rf = best_t;
-            slab_fast<float>(a.x, a.w, ox, ix, ln, lf);
-            slab_fast<float>(a.y, b.x, oy, iy, ln, lf);
-            slab_fast<float>(a.z, b.y, oz, iz, ln, lf);
-            slab_fast<float>(b.z, c.y, ox, ix, rn, rf);
-            slab_fast<float>(b.w, c.z, oy, iy, rn, rf);
-            slab_fast<float>(c.x, c.w, oz, iz, rn, rf);
+            slab_fma(a.x, a.w, ox, ix, ln, lf);
+            slab_fma(a.y, b.x, oy, iy, ln, lf);
+            slab_fma(a.z, b.y, oz, iz, ln, lf);
+            slab_fma(b.z, c.y, ox, ix, rn, rf);
+            slab_fma(b.w, c.z, oy, iy, rn, rf);
+            slab_fma(c.x, c.w, oz, iz, rn, rf);
             const bool hl = ln <= lf, hr = rn <= rf;
             int32_t lc = w.x, rc = w.y;
             if (hl && hr) {
