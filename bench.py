@@ -154,7 +154,8 @@ def workload_config():
                         "(reference ships no OBJ assets); step = %d strata of every pixel"
                         % (WIDTH, HEIGHT, SPP, DEPTH, STRATA_PER_STEP),
             "samples_per_step_per_gpu": WIDTH * HEIGHT * STRATA_PER_STEP,
-            "l2": "working set per step (wavefront state ~4.7 GB) exceeds the 126 MB L2; no flush needed",
+            "l2": "working set per step (wavefront state of 4 workers, ~20 GB, streamed every iteration) exceeds the 126 MB L2; "
+                  "no flush needed; the 50 MB scene itself is L2-resident by design",
             "parallelism": "stratum sharding, one NCCL film reduce per frame"}
 
 
@@ -283,6 +284,23 @@ def run_ours(args):
     return 0
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel`, from the committed ncu --set full
+    summary of this round (profiles/): a number measured under the profiler, quoted, not re-measured here."""
+    path = os.path.join(ROOT, "profiles", "r1_ncu_full_%s.csv" % kernel)
+    try:
+        vals = {}
+        for line in open(path):
+            p = line.strip().split(",")
+            if len(p) >= 3 and p[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                vals[p[0]] = float(p[1]) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[p[2]]
+        if len(vals) == 2:
+            return sum(vals.values()), "bytes of the captured launch in profiles/%s (the first, largest launch of a step)" % os.path.basename(path)
+    except Exception:
+        pass
+    return None, "no ncu capture committed for this kernel"
+
+
 def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
     """roofline of the dominant kernel class, the 16M-ray BVH microbench (config 2) and the CPU baseline."""
     out = {}
@@ -312,8 +330,12 @@ def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
     ms_dom, launches_dom = kt[dom]
     achieved = rays_dom * per[dom]["bytes_per_ray"] / (ms_dom * 1e-3) / 1e9 if ms_dom > 0 else 0.0
     total_kernel_ms = sum(v[0] for v in kt.values())
-    out["roofline"] = {"bound": "hbm", "kernel": "k_trace_paths" if dom == "trace" else "k_shadow", "achieved": achieved,
-                       "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+    fast = bvh == pkg.BVH_FAST
+    kname = ("k_trace_fast" if fast else "k_trace_paths") if dom == "trace" else ("k_shadow_fast" if fast else "k_shadow")
+    traffic, traffic_note = ncu_traffic(kname)
+    out["roofline"] = {"bound": "hbm", "kernel": kname, "achieved": achieved,
+                       "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
+                       "peak_source": peak_src,
                        "avg_launch_ms": ms_dom / max(1, launches_dom), "launches": launches_dom,
                        "algorithmic_bytes_per_ray": per[dom]["bytes_per_ray"],
                        "algorithmic_bytes_per_launch": rays_dom * per[dom]["bytes_per_ray"] / max(1, launches_dom),

@@ -17,7 +17,7 @@ namespace {
 
 std::string g_create_err;
 
-constexpr int kTraceBlock = 128;
+constexpr int kTraceBlock = 64;
 
 template <class T>
 int upload(bdpt_ctx* ctx, const std::vector<T>& h, const T** d) {
@@ -39,9 +39,11 @@ void free_scene(bdpt_ctx* ctx) {
 // ---------------------------------------------------------------- batch kernels
 // hittable::hit over a ray batch (hittable.h:33, bvh.h:50-59)
 template <int BVH, bool ANY, bool STATS>
-__global__ void __launch_bounds__(kTraceBlock) k_trace(SceneView sc, const bdpt_ray* __restrict__ rays, uint64_t n,
+__global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_trace(SceneView sc, const bdpt_ray* __restrict__ rays, uint64_t n,
                                                       bdpt_hit* __restrict__ out, unsigned long long* stats) {
-    __shared__ StackEntry s_stack[kRefStackLevels * kTraceBlock];
+    // stack in local memory (as in the render kernels): 48 int32 levels for the reference tree = 24 StackEntry;
+    // 32 StackEntry cover the fast tree (depth <= 23)
+    StackEntry l_stack[32];
     const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
     TravStats st{0, 0};
     if (i < n) {
@@ -53,9 +55,16 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(SceneView sc, const bdpt_
         h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS;
         bool found;
         if (BVH == BDPT_BVH_REFERENCE)
-            found = traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(s_stack + threadIdx.x), 2 * kTraceBlock, &st);
-        else
-            found = traverse_fast<ANY, STATS, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, &st) == TR_HIT;
+            found = traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st);
+        else if (walk_eligible(sc, r)) {   // the render kernels' walk (fp32 FMA slabs); a tie goes to the reference tree
+            Walk<ANY, STATS> W;
+            W.init(sc, r);
+            const int rc = W.run(sc, l_stack, 0);
+            if (STATS) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; }
+            h = W.hit;
+            found = rc == TR_DEFER ? traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st) : rc == TR_HIT;
+        } else
+            found = traverse_fast<ANY, STATS, false>(sc, r, h, l_stack, 1, &st) == TR_HIT;
         double2* o = reinterpret_cast<double2*>(out + i);
         if (!found) { h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS; }
         o[0] = make_double2(h.t, h.u);
@@ -100,10 +109,10 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_split(SceneView sc, const
 
 // camera::visible (camera.h:425-438)
 template <int BVH>
-__global__ void __launch_bounds__(kTraceBlock) k_visible(SceneView sc, const double* __restrict__ a,
+__global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_visible(SceneView sc, const double* __restrict__ a,
                                                         const double* __restrict__ b, uint64_t n,
                                                         uint8_t* __restrict__ out) {
-    __shared__ StackEntry s_stack[kRefStackLevels * kTraceBlock];
+    StackEntry l_stack[32];
     const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
     if (i >= n) return;
     D3 pa = mk(a[3 * i], a[3 * i + 1], a[3 * i + 2]), pb = mk(b[3 * i], b[3 * i + 1], b[3 * i + 2]);
@@ -119,9 +128,9 @@ __global__ void __launch_bounds__(kTraceBlock) k_visible(SceneView sc, const dou
             HitD h;
             bool found;
             if (BVH == BDPT_BVH_REFERENCE)
-                found = traverse_ref<true, false>(sc, r, h, reinterpret_cast<int32_t*>(s_stack + threadIdx.x), 2 * kTraceBlock, nullptr);
+                found = traverse_ref<true, false>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, nullptr);
             else
-                found = traverse_fast<true, false, false>(sc, r, h, s_stack + threadIdx.x, kTraceBlock, nullptr) == TR_HIT;
+                found = traverse_fast<true, false, false>(sc, r, h, l_stack, 1, nullptr) == TR_HIT;
             vis = found ? 0 : 1;
         }
     }
@@ -194,7 +203,7 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
         return BDPT_ERR_ARG;
     }
     HostScene& h = ctx->host;
-    if (h.ref_depth >= uint32_t(kRefStackLevels) || h.fast_depth >= uint32_t(kRefStackLevels)) {
+    if (h.ref_depth >= uint32_t(kRefStackLevels) || h.fast_depth + 2 > 32u) {   // 64 int32 / 32 StackEntry slots of local stack
         ctx->err = "BVH deeper than the traversal stack";
         return BDPT_ERR_ARG;
     }
