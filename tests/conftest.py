@@ -37,6 +37,7 @@ def scenes():
         "cornell_spheres": lambda: ts.cornell(True, (8, 12)),
         "cornell_box": lambda: ts.cornell(False),
         "unit_room": lambda: ts.unit_room(seed=1, n_blobs=6),
+        "sphere_grid": lambda: ts.sphere_grid(6, 9, 10),   # BASELINE.json config 5 in miniature
     }
 
 

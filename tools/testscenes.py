@@ -174,3 +174,30 @@ def ray_batch(verts, n, seed=0x5EED0001, cam=None, width=64, height=64):
     fin = np.isfinite(t)
     t[fin] = t[fin].astype(np.float32).astype(np.float64)
     return np.ascontiguousarray(rays)
+
+
+def sphere_grid(g=50, lat_steps=41, lon_steps=50, spacing=2.5, radius=1.0):
+    """BASELINE.json config 5: floor + 3 light quads + a g x g grid of UV spheres; sphere i is
+    lambertian when i % 10 == 0, else dielectric(1.5) for odd i and metal(0.7, fuzz 0.1) for even i.
+    g=50, 41 x 50 steps -> 2,500 spheres x 4,000 triangles = 10,000,008 triangles with floor and lights.
+    Camera above the grid looking at its centre."""
+    unit = uv_sphere((0, 0, 0), 1.0, lat_steps, lon_steps).reshape(-1, 3, 3)          # T x 3 x 3
+    ext = g * spacing
+    ij = np.stack(np.meshgrid(np.arange(g), np.arange(g), indexing="ij"), -1).reshape(-1, 2)
+    centers = np.stack([(ij[:, 0] + 0.5) * spacing - ext / 2, np.full(len(ij), radius), (ij[:, 1] + 0.5) * spacing - ext / 2], -1)
+    sb = SceneBuilder()
+    floor = sb.material(LAMB, (.6, .6, .6)); light = sb.material(LIGHT, (40, 40, 40))
+    diffuse = sb.material(LAMB, (.7, .3, .2)); glass = sb.material(GLASS, param=1.5); metal = sb.material(METAL, (.7, .7, .7), 0.1)
+    m = 0.55 * ext
+    sb.add(quad((-m, 0, -m), (0, 0, 2 * m), (2 * m, 0, 0)), floor)                         # normal +y
+    h = 0.35 * ext + 4 * radius
+    for cx in (-0.3 * ext, 0.0, 0.3 * ext):                                                # three lights, normals -y
+        sb.add(quad((cx - 0.08 * ext, h, -0.08 * ext), (0.16 * ext, 0, 0), (0, 0, 0.16 * ext)), light)
+    idx = np.arange(len(centers))
+    mat_of = np.where(idx % 10 == 0, diffuse, np.where(idx % 2 == 1, glass, metal)).astype(np.uint32)
+    verts = (unit[None] * radius + centers[:, None, None, :]).reshape(-1, 9)
+    sb.verts.append(verts)
+    sb.mat_id.append(np.repeat(mat_of, len(unit)))
+    v, mid, mats = sb.done()
+    cam = dict(lookfrom=(0.0, 0.55 * ext, -0.75 * ext), lookat=(0.0, 0.0, 0.0), vfov=40.0)
+    return v, mid, mats, cam
