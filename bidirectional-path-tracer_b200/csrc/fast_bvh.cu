@@ -17,7 +17,7 @@ namespace bdpt {
 namespace {
 
 constexpr int kBins = 16;
-constexpr uint32_t kMaxLeaf = 4;
+constexpr uint32_t kMaxLeaf = 2;
 constexpr double kTravCost = 1.0, kTriCost = 1.5;
 
 struct B3 {

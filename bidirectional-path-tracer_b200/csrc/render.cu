@@ -3,7 +3,7 @@
 //
 //   K0 k_generate      get_ray (camera.h:199-223) + build_light_path's emitter (camera.h:372-414)
 //   K1 k_trace_paths   world.hit for every live subpath (camera.h:336) -> per-material queues
-//   K2 k_shade_*       one kernel per material class (material.h:42-147): vertex push, emission,
+//   K2 k_shade         one launch over the per-material queues (material.h:42-147): vertex push, emission,
 //                      scatter, throughput update (camera.h:342-368); survivors -> next ray queue
 //   K3 k_connect       connect_vertices minus visibility (camera.h:440-475) -> shadow-ray queue
 //   K4 k_shadow        visible() (camera.h:425-438) + film accumulation (camera.h:121-124)
@@ -486,14 +486,10 @@ __device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d,
 // scatter() is false: the subpath ends here.  Camera subpath: bidirectional_color adds throughput *
 // emission for this non-delta vertex (camera.h:305-309); it never connects (evaluate_bsdf = 0).
 // Light subpath: the vertex is connectable with f_light = emission when hit from the front (camera.h:463).
-__global__ void __launch_bounds__(kBlock) k_shade_light(SceneView sc, Frame f, WF w, int dn, double* film) {
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
-    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_LIGHT];
-    uint32_t b = 0;
-    if (valid) {
-        const uint32_t pid = w.q_mat[BDPT_MAT_LIGHT][idx];
+__device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, double* film) {
+    {
         const bool is_cam = pid < uint32_t(w.B);
-        b = is_cam ? pid : pid - uint32_t(w.B);
+        const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
         const Surf s = load_surf(sc, w, pid);
         const Mat m = sc.mats[sc.shade[s.prim].mat];
         const D3 Le = mk(m.r, m.g, m.b);
@@ -507,17 +503,13 @@ __global__ void __launch_bounds__(kBlock) k_shade_light(SceneView sc, Frame f, W
             }
         }
     }
-    retire(w, valid, b, dn);   // scatter() is false: the subpath always ends on a light
+    return false;   // scatter() is false: the subpath always ends on a light
 }
 
 // ------------------------------------------------------------------ K2: lambertian (material.h:42-67)
-__global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f, WF w, int nxt, int dn) {
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+__device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
-    uint32_t pid = 0;
-    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN];
-    if (valid) {
-        pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx];
+    {
         const Surf s = load_surf(sc, w, pid);
         const Mat m = sc.mats[sc.shade[s.prim].mat];
         const D3 albedo = mk(m.r, m.g, m.b);
@@ -555,21 +547,15 @@ __global__ void __launch_bounds__(kBlock) k_shade_lambert(SceneView sc, Frame f,
             }
         }
     }
-    const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
-    if (live) w.q_active[nxt][slot] = pid;
-    retire(w, valid && !live, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+    return live;
 }
 
 // ------------------------------------------------------------------ K2: metal (material.h:69-90)
 // Always a delta vertex, even when fuzzy (material.h:85): never stored, never connected.  The fuzzed
 // direction is not rejected when it points below the surface (material.h:74-82).
-__global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, WF w, int nxt, int dn) {
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+__device__ __forceinline__ bool shade_metal(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
-    uint32_t pid = 0;
-    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_METAL];
-    if (valid) {
-        pid = w.q_mat[BDPT_MAT_METAL][idx];
+    {
         const int32_t remaining = w.path[pid].remaining - 1;
         if (remaining > 0) {
             const Surf s = load_surf(sc, w, pid);
@@ -585,19 +571,13 @@ __global__ void __launch_bounds__(kBlock) k_shade_metal(SceneView sc, Frame f, W
             live = true;
         }
     }
-    const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
-    if (live) w.q_active[nxt][slot] = pid;
-    retire(w, valid && !live, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+    return live;
 }
 
 // ------------------------------------------------------------------ K2: dielectric (material.h:92-131)
-__global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame f, WF w, int nxt, int dn) {
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+__device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
-    uint32_t pid = 0;
-    const bool valid = idx < w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
-    if (valid) {
-        pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx];
+    {
         const int32_t remaining = w.path[pid].remaining - 1;
         if (remaining > 0) {
             const Surf s = load_surf(sc, w, pid);
@@ -622,6 +602,26 @@ __global__ void __launch_bounds__(kBlock) k_shade_dielectric(SceneView sc, Frame
             store_ray(w, pid, s.p, dir, T, rng.draws, remaining);
             live = true;
         }
+    }
+    return live;
+}
+
+// ------------------------------------------------------------------ K2: one launch over the four material queues
+// Thread idx walks the concatenation light | lambertian | metal | dielectric of the queues k_trace_* filled, so
+// a warp straddles at most one class boundary; the survivors' queue append and the retirement of ended
+// subpaths are shared.
+__global__ void __launch_bounds__(kBlock) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    const uint32_t n_li = w.counters[C_MAT0 + BDPT_MAT_LIGHT], n_la = w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN],
+                   n_me = w.counters[C_MAT0 + BDPT_MAT_METAL], n_di = w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
+    const bool valid = idx < n_li + n_la + n_me + n_di;
+    bool live = false;
+    uint32_t pid = 0;
+    if (valid) {
+        if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light(sc, f, w, pid, film); }
+        else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert(sc, f, w, pid); }
+        else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal(sc, f, w, pid); }
+        else { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric(sc, f, w, pid); }
     }
     const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
@@ -1139,13 +1139,10 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         tm.end(KT_TRACE, st);
         tm.begin(KT_SHADE, st);
         const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kBlock);   // the lagged rays of the front blocks are shaded too
-        k_shade_light<<<gsh, kBlock, 0, st>>>(sc, f, wf, dn, J.film);
-        k_shade_lambert<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
-        k_shade_metal<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
-        k_shade_dielectric<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn);
+        k_shade<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn, J.film);
         k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
         tm.end(KT_SHADE, st);
-        wk.launches += 6;
+        wk.launches += 3;
         WK_CUDA(cudaMemcpyAsync(hc, wf.counters, C_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
         WK_CUDA(cudaStreamSynchronize(st));
         wk.rays_closest += hc[C_ACTIVE0 + cur];
@@ -1243,11 +1240,28 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     }
 
     // wavefront size and how many wavefronts are kept in flight
-    int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 20);
+    int64_t B = o.batch_samples > 0 ? o.batch_samples : (int64_t(1) << 21);
     B = std::min<int64_t>(B, int64_t(1) << 30);
     int S = o.streams > 0 ? o.streams : 4;
     S = int(std::min<int64_t>(std::min(S, 16), std::max<int64_t>(1, total / 8192)));
     B = std::min<int64_t>(B, (total + S - 1) / S);   // every worker gets slots to fill
+    if (o.batch_samples <= 0) {
+        // the default takes at most half of the free device memory: a slot costs ~5 KB at depth 16 and ~25 KB at
+        // depth 80 (vertex pools and shadow queues grow with the depth)
+        WF probe{};
+        probe.B = 65536; probe.depth = f.depth;
+        probe.scap = std::max<int64_t>(probe.B * 8, int64_t(f.depth) * probe.B);
+        probe.sscap = std::max<int64_t>(4096, probe.scap / 8);
+        carve(probe, nullptr);
+        const double per_slot = double(probe.bytes) / double(probe.B);
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+            size_t held = 0;   // workspaces this context already holds can be reused or are freed before growing
+            if (ctx->wf) for (auto* wk : static_cast<Workers*>(ctx->wf)->w) held += wk->wf.base ? wk->wf.bytes : 0;
+            const int64_t cap = int64_t(0.5 * double(free_b + held) / (per_slot * S));
+            B = std::max<int64_t>(4096, std::min<int64_t>(B, cap));
+        }
+    }
     Workers* ws = static_cast<Workers*>(ctx->wf);
     if (!ws) { ws = new Workers(); ctx->wf = ws; }
     while (int(ws->w.size()) < S) ws->w.push_back(new Worker());
