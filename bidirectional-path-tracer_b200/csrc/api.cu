@@ -214,6 +214,7 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     if ((rc = upload(ctx, h.ref_nodes, &v.ref_nodes))) return rc;
     if ((rc = upload(ctx, h.fast_nodes, &v.fast_nodes))) return rc;
     if ((rc = upload(ctx, h.fast_prims, &v.fast_prims))) return rc;
+    if ((rc = upload(ctx, h.fast_tris, &v.fast_tris))) return rc;
     if ((rc = upload(ctx, h.dfs_rank, &v.dfs_rank))) return rc;
     if ((rc = upload(ctx, h.ref_parent, &v.ref_parent))) return rc;
     if ((rc = upload(ctx, h.prim_leaf, &v.prim_leaf))) return rc;

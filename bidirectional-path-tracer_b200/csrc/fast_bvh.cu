@@ -232,6 +232,8 @@ void build_fast_bvh(HostScene& s) {
     }
     (void)kTravCost; (void)kTriCost;
     s.fast_depth = max_depth + 1;
+    s.fast_tris.resize(n);
+    for (uint32_t k = 0; k < n; ++k) s.fast_tris[k] = s.tris[s.fast_prims[k]];
 }
 
 }  // namespace bdpt

@@ -30,6 +30,7 @@ struct HostScene {
     // fast topology
     std::vector<FastNode> fast_nodes;
     std::vector<uint32_t> fast_prims;
+    std::vector<TriGeom> fast_tris;    // tris[fast_prims[k]]: a leaf's triangles are contiguous, no id indirection on the walk
     uint32_t fast_depth = 0;
     double extent = 0.0;               // largest side of the scene bounds
     double center[3] = {0, 0, 0};

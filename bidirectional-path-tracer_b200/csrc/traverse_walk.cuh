@@ -122,6 +122,13 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
                 stack[sp] = pack_entry(rc, far_t);
                 ++sp;
                 cur = lc;
+#ifdef BDPT_PREFETCH_FAR
+                if (rc >= 0) {   // the deferred child is popped later: start its 64 bytes on their way to L1
+                    const char* pf = reinterpret_cast<const char*>(sc.fast_nodes + rc);
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + 32));
+                }
+#endif
             } else if (hl) cur = lc;
             else if (hr) cur = rc;
             else if (!pop(stack)) return finish(sc);
@@ -132,10 +139,10 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
         work += cnt;
         if (limit && work > limit) return TR_SLOW;   // nothing decided: the caller parks the ray for a split walk
         for (uint32_t k = 0; k < cnt; ++k) {
-            const uint32_t prim = __ldg(sc.fast_prims + first + k);
             if (STATS) ++ts.tris;
             double t, u, v;
-            if (!tri_candidate(sc.tris + prim, r.o, r.d, t, u, v)) continue;
+            if (!tri_candidate(sc.fast_tris + first + k, r.o, r.d, t, u, v)) continue;
+            const uint32_t prim = __ldg(sc.fast_prims + first + k);   // only candidates need their id
             const double band = band_abs + 1e-10 * fabs(t);
             const bool edge = fabs(t - r.tmin) <= band || fabs(t - r.tmax) <= band;
             if (ANY) {
