@@ -132,3 +132,33 @@ def test_named_scenes_match_oracle_per_sample(name, W, H, spp, depth, bdpt, gpu_
     for bvh in (bdpt.BVH_FAST, bdpt.BVH_REFERENCE):
         gpu_ctx.render(cam, seed=5, bvh=bvh, height=H)
         assert rel_err(gpu_ctx.film(), ref) < 1e-9
+
+
+def test_cli_renders_the_same_png_as_the_api(bdpt, gpu_ctx, tmp_path):
+    """`bdpt scene.yaml` (host/main.cpp = the reference's main.cpp:62-78 on libbdpt): load_scene_from_yaml ->
+    bvh_node -> camera::render -> ./output/<name>.  Its PNG must be the C-ABI path's film through wpng.h's
+    colors_to_rgb8, byte for byte."""
+    import os, subprocess
+    from test_loader import decode_png
+    from tools import make_standin_scenes as ms
+    ms.generate(detail=2, quiet=True)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "bidirectional-path-tracer_b200", "bdpt")
+    scene = os.path.join(root, "scenes", "coffee_machine.yaml")
+    r = subprocess.run([exe, scene, "--res", "64x36", "--spp", "4", "--depth", "6", "--seed", "3", "--out", "cli.png"],
+                       cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-1000:]
+    assert "Triangles:" in r.stdout                                    # scene_loader.h:521
+    png = decode_png(tmp_path / "output" / "cli.png")                  # wpng.h:45-49: ./output/<file_name>
+    sf = bdpt.SceneFile(scene)
+    cam = sf.camera_with(64, 36, 4, 6)
+    gpu_ctx.upload(sf.verts, sf.mat_id, sf.materials)
+    gpu_ctx.render(cam, seed=3, bvh=bdpt.BVH_FAST, height=36)
+    rgb = gpu_ctx.film_rgb8(4)
+    assert png.shape == rgb.shape == (36, 64, 3)
+    # fp64 atomics sum a pixel's samples in a different order in the two runs: allow one 8-bit step on rare pixels
+    d = np.abs(png.astype(int) - rgb.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 0.01
+    # a bad argument fails like main.cpp:72-75
+    r = subprocess.run([exe, str(tmp_path / "missing.yaml")], cwd=tmp_path, capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "Failed to load scene" in r.stderr
