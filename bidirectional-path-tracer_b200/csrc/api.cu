@@ -1,6 +1,8 @@
 // C-ABI of libbdpt (include/bdpt.h): context, scene upload, batch trace / visible, film access.
 // Compiled with -fmad=false: the trace kernels instantiate the reference-exact traversal.
+#include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <stdexcept>
@@ -190,12 +192,19 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
                       const bdpt_material* mats, uint32_t n_mats) {
     if (!ctx) return BDPT_ERR_ARG;
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const bool timing = std::getenv("BDPT_TIMING") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [&](std::chrono::steady_clock::time_point t) { return std::chrono::duration<double, std::milli>(now() - t).count(); };
+    const auto t_start = now();
+    double t_flat = 0, t_ref = 0, t_fast = 0;
     try {
         flatten_scene(verts, mat_id, n_tris, mats, n_mats, ctx->host);
+        t_flat = ms_since(t_start);
         // the two trees share only read-only inputs (tri_box): build them side by side
         std::exception_ptr fast_err;
-        std::thread fast_thread([&] { try { build_fast_bvh(ctx->host); } catch (...) { fast_err = std::current_exception(); } });
-        try { build_ref_bvh(ctx->host); } catch (...) { fast_thread.join(); throw; }
+        const auto t_b = now();
+        std::thread fast_thread([&] { try { build_fast_bvh(ctx->host); t_fast = ms_since(t_b); } catch (...) { fast_err = std::current_exception(); } });
+        try { build_ref_bvh(ctx->host); t_ref = ms_since(t_b); } catch (...) { fast_thread.join(); throw; }
         fast_thread.join();
         if (fast_err) std::rethrow_exception(fast_err);
     } catch (const std::exception& ex) {
@@ -234,6 +243,9 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->view = v;
     ctx->have_scene = true;
+    if (timing)
+        std::fprintf(stderr, "bdpt_scene_upload: %llu triangles: flatten %.1f ms, reference tree %.1f ms || fast tree %.1f ms, total %.1f ms\n",
+                     (unsigned long long)n_tris, t_flat, t_ref, t_fast, ms_since(t_start));
     return BDPT_OK;
 }
 

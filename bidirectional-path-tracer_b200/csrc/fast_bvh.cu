@@ -4,6 +4,9 @@
 #include <algorithm>
 #include <atomic>
 #include <cfloat>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <deque>
 #include <thread>
 #include <vector>
@@ -51,6 +54,23 @@ inline float up32(double v) {
 
 struct Task { uint32_t begin, end, depth; int32_t node; int side; };
 
+// fn(chunk_begin, chunk_end, chunk_index) over [b, e) on up to `threads` threads (the big nodes at the top of the
+// tree are built by one task: their linear passes are what is worth splitting)
+template <class F>
+void par_chunks(uint32_t b, uint32_t e, unsigned threads, F fn) {
+    const uint32_t n = e - b;
+    if (threads <= 1 || n < 32768) { fn(b, e, 0u); return; }
+    std::vector<std::thread> pool;
+    const uint32_t per = (n + threads - 1) / threads;
+    for (unsigned k = 1; k < threads; ++k) {
+        const uint32_t cb = b + std::min(n, k * per), ce = b + std::min(n, (k + 1) * per);
+        if (cb < ce) pool.emplace_back([=] { fn(cb, ce, k); });
+    }
+    fn(b, b + std::min(n, per), 0u);
+    for (auto& th : pool) th.join();
+}
+constexpr unsigned kTopThreads = 8;
+
 }  // namespace
 
 void build_fast_bvh(HostScene& s) {
@@ -91,7 +111,6 @@ void build_fast_bvh(HostScene& s) {
         if (stop_at) { t = todo.front(); todo.pop_front(); } else { t = todo.back(); todo.pop_back(); }
         const uint32_t cnt = t.end - t.begin;
         max_depth = std::max(max_depth, t.depth);
-        B3 bb = range_box(t.begin, t.end);
         // leaf?  (never for the root task: it must produce node 0)
         if (t.node >= 0 && cnt <= kMaxLeaf) {
             // decided by the parent (it stored the box); just encode
@@ -111,6 +130,7 @@ void build_fast_bvh(HostScene& s) {
         if (cnt == 1) {
             // degenerate root: duplicate the single triangle as both children
             FastNode nd{};
+            const B3 bb = range_box(t.begin, t.end);
             store_box(nd, 0, bb); store_box(nd, 1, bb);
             nd.left = leaf_code(t.begin, 1); nd.right = leaf_code(t.begin, 1);
             nodes[me] = nd;
@@ -118,32 +138,70 @@ void build_fast_bvh(HostScene& s) {
         }
         // centroid bounds
         double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
-        for (uint32_t i = t.begin; i < t.end; ++i) {
-            const double* b = tb + 6 * size_t(s.fast_prims[i]);
-            for (int k = 0; k < 3; ++k) {
-                double c = 0.5 * (b[k] + b[3 + k]);
-                clo[k] = std::min(clo[k], c); chi[k] = std::max(chi[k], c);
+        const bool fork = stop_at && cnt >= 32768;   // only the single-threaded top phase may fork
+        if (!fork) {
+            for (uint32_t i = t.begin; i < t.end; ++i) {
+                const double* b = tb + 6 * size_t(s.fast_prims[i]);
+                for (int k = 0; k < 3; ++k) {
+                    double c = 0.5 * (b[k] + b[3 + k]);
+                    clo[k] = std::min(clo[k], c); chi[k] = std::max(chi[k], c);
+                }
             }
+        } else {
+            struct alignas(64) CB { double lo[3], hi[3]; } part[kTopThreads];
+            for (auto& x : part) for (int k = 0; k < 3; ++k) { x.lo[k] = INFINITY; x.hi[k] = -INFINITY; }
+            par_chunks(t.begin, t.end, kTopThreads, [&](uint32_t cb, uint32_t ce, unsigned q) {
+                double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+                for (uint32_t i = cb; i < ce; ++i) {
+                    const double* b = tb + 6 * size_t(s.fast_prims[i]);
+                    for (int k = 0; k < 3; ++k) {
+                        double c = 0.5 * (b[k] + b[3 + k]);
+                        lo[k] = std::min(lo[k], c); hi[k] = std::max(hi[k], c);
+                    }
+                }
+                for (int k = 0; k < 3; ++k) { part[q].lo[k] = lo[k]; part[q].hi[k] = hi[k]; }
+            });
+            for (auto& x : part) for (int k = 0; k < 3; ++k) { clo[k] = std::min(clo[k], x.lo[k]); chi[k] = std::max(chi[k], x.hi[k]); }
         }
         int axis = 0;
         for (int k = 1; k < 3; ++k) if (chi[k] - clo[k] > chi[axis] - clo[axis]) axis = k;
         const double cext = chi[axis] - clo[axis];
         bool split_ok = false;
+        B3 lbox, rbox;   // child boxes of a SAH split: unions of its bins (what range_box would recompute)
         if (cext > 0 && t.depth < 22 && cnt > 2) {
             // binned SAH over all three axes
             double best_cost = std::numeric_limits<double>::infinity();
             int best_axis = -1, best_bin = -1;
+            B3 best_bins[kBins];
             for (int ax = 0; ax < 3; ++ax) {
                 const double e = chi[ax] - clo[ax];
                 if (!(e > 0)) continue;
                 B3 bins[kBins]; uint32_t bc[kBins];
                 for (int b = 0; b < kBins; ++b) { bins[b].reset(); bc[b] = 0; }
                 const double sc = kBins / e;
-                for (uint32_t i = t.begin; i < t.end; ++i) {
-                    const double* b = tb + 6 * size_t(s.fast_prims[i]);
-                    int bi = int((0.5 * (b[ax] + b[3 + ax]) - clo[ax]) * sc);
-                    bi = std::min(std::max(bi, 0), kBins - 1);
-                    bins[bi].grow(b); ++bc[bi];
+                if (!fork) {
+                    for (uint32_t i = t.begin; i < t.end; ++i) {
+                        const double* b = tb + 6 * size_t(s.fast_prims[i]);
+                        int bi = int((0.5 * (b[ax] + b[3 + ax]) - clo[ax]) * sc);
+                        bi = std::min(std::max(bi, 0), kBins - 1);
+                        bins[bi].grow(b); ++bc[bi];
+                    }
+                } else {
+                    struct alignas(64) PB { B3 b[kBins]; uint32_t c[kBins]; };
+                    std::vector<PB> part(kTopThreads);
+                    for (auto& x : part) for (int b = 0; b < kBins; ++b) { x.b[b].reset(); x.c[b] = 0; }
+                    par_chunks(t.begin, t.end, kTopThreads, [&](uint32_t cb, uint32_t ce, unsigned q) {
+                        PB mine = part[q];
+                        for (uint32_t i = cb; i < ce; ++i) {
+                            const double* b = tb + 6 * size_t(s.fast_prims[i]);
+                            int bi = int((0.5 * (b[ax] + b[3 + ax]) - clo[ax]) * sc);
+                            bi = std::min(std::max(bi, 0), kBins - 1);
+                            mine.b[bi].grow(b); ++mine.c[bi];
+                        }
+                        part[q] = mine;
+                    });
+                    for (auto& x : part)
+                        for (int b = 0; b < kBins; ++b) { bins[b].grow(x.b[b]); bc[b] += x.c[b]; }
                 }
                 double ra[kBins]; uint32_t rc[kBins];
                 B3 acc; acc.reset(); uint32_t c = 0;
@@ -153,7 +211,10 @@ void build_fast_bvh(HostScene& s) {
                     acc.grow(bins[b]); c += bc[b];
                     if (c == 0 || rc[b + 1] == 0) continue;
                     double cost = acc.half_area() * c + ra[b + 1] * rc[b + 1];
-                    if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = b; }
+                    if (cost < best_cost) {
+                        best_cost = cost; best_axis = ax; best_bin = b;
+                        for (int k = 0; k < kBins; ++k) best_bins[k] = bins[k];
+                    }
                 }
             }
             if (best_axis >= 0) {
@@ -168,6 +229,8 @@ void build_fast_bvh(HostScene& s) {
                 });
                 mid = uint32_t(it - s.fast_prims.begin());
                 split_ok = mid > t.begin && mid < t.end;
+                lbox.reset(); rbox.reset();
+                for (int k = 0; k < kBins; ++k) (k <= best_bin ? lbox : rbox).grow(best_bins[k]);
             }
         }
         if (!split_ok) {
@@ -179,8 +242,9 @@ void build_fast_bvh(HostScene& s) {
                              });
         }
         FastNode nd{};
-        store_box(nd, 0, range_box(t.begin, mid));
-        store_box(nd, 1, range_box(mid, t.end));
+        if (!split_ok) { lbox = range_box(t.begin, mid); rbox = range_box(mid, t.end); }
+        store_box(nd, 0, lbox);
+        store_box(nd, 1, rbox);
         nd.left = nd.right = 0;
         nodes[me] = nd;
         // children: push right first so the left subtree is laid out next (preorder, near the parent)
@@ -189,12 +253,18 @@ void build_fast_bvh(HostScene& s) {
     }
     };
 
+    const bool timing = std::getenv("BDPT_TIMING") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (timing) std::fprintf(stderr, "  fast tree: %s at %.1f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    };
     // top of the tree on this thread until there are enough independent subtrees ...
     uint32_t max_depth = 0;
     std::deque<Task> top;
     s.fast_nodes.push_back(FastNode());   // root: always an internal node so the kernel never special-cases
     top.push_back(Task{0, n, 0, -1, 0});
-    grow(s.fast_nodes, top, max_depth, 64);
+    grow(s.fast_nodes, top, max_depth, 32);
+    lap("top levels done");
     // ... then one subtree per task, on worker threads, each into its own node array (prim ranges are disjoint)
     std::vector<Task> subs(top.begin(), top.end());
     std::sort(subs.begin(), subs.end(), [](const Task& a, const Task& b) { return a.end - a.begin > b.end - b.begin; });
@@ -216,24 +286,42 @@ void build_fast_bvh(HostScene& s) {
     for (unsigned k = 1; k < n_threads && k < subs.size(); ++k) pool.emplace_back(worker);
     worker();
     for (auto& th : pool) th.join();
+    lap("subtrees done");
     // splice: a subtree's internal links move by its base index; leaf codes (negative) are global already
+    std::vector<int32_t> base(subs.size(), 0);
+    {
+        size_t total_nodes = s.fast_nodes.size();
+        for (size_t i = 0; i < subs.size(); ++i) { base[i] = int32_t(total_nodes); total_nodes += local[i].size(); }
+        s.fast_nodes.resize(total_nodes);
+    }
     for (size_t i = 0; i < subs.size(); ++i) {
         const Task& t = subs[i];
         FastNode& p = s.fast_nodes[t.node];
         max_depth = std::max(max_depth, std::max(t.depth, local_depth[i]));
-        if (local[i].empty()) { (t.side ? p.right : p.left) = leaf_code(t.begin, t.end - t.begin); continue; }
-        const int32_t base = int32_t(s.fast_nodes.size());
-        (t.side ? p.right : p.left) = base;
-        for (FastNode nd : local[i]) {
-            if (nd.left >= 0) nd.left += base;
-            if (nd.right >= 0) nd.right += base;
-            s.fast_nodes.push_back(nd);
-        }
+        (t.side ? p.right : p.left) = local[i].empty() ? leaf_code(t.begin, t.end - t.begin) : base[i];
     }
+    std::atomic<size_t> next_copy{0};
+    auto copier = [&] {
+        for (size_t i = next_copy.fetch_add(1); i < subs.size(); i = next_copy.fetch_add(1)) {
+            FastNode* dst = s.fast_nodes.data() + base[i];
+            for (FastNode nd : local[i]) {
+                if (nd.left >= 0) nd.left += base[i];
+                if (nd.right >= 0) nd.right += base[i];
+                *dst++ = nd;
+            }
+        }
+    };
+    pool.clear();
+    for (unsigned k = 1; k < n_threads && k < subs.size(); ++k) pool.emplace_back(copier);
+    copier();
+    for (auto& th : pool) th.join();
     (void)kTravCost; (void)kTriCost;
     s.fast_depth = max_depth + 1;
+    lap("spliced");
     s.fast_tris.resize(n);
-    for (uint32_t k = 0; k < n; ++k) s.fast_tris[k] = s.tris[s.fast_prims[k]];
+    par_chunks(0, n, n_threads, [&](uint32_t cb, uint32_t ce, unsigned) {
+        for (uint32_t k = cb; k < ce; ++k) s.fast_tris[k] = s.tris[s.fast_prims[k]];
+    });
 }
 
 }  // namespace bdpt
