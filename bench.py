@@ -73,7 +73,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append(parts)
             except Exception:
                 pass
-            self._stop_evt.wait(0.2)
+            self._stop_evt.wait(0.05)
 
     def stop(self):
         self._stop_evt.set()
@@ -154,7 +154,7 @@ def workload_config():
                         "(reference ships no OBJ assets); step = %d strata of every pixel"
                         % (WIDTH, HEIGHT, SPP, DEPTH, STRATA_PER_STEP),
             "samples_per_step_per_gpu": WIDTH * HEIGHT * STRATA_PER_STEP,
-            "l2": "working set per step (wavefront state of 4 workers, ~20 GB, streamed every iteration) exceeds the 126 MB L2; "
+            "l2": "working set per step (wavefront state of 4 workers x 2^21 sample slots, ~46 GB of path/vertex records and queues, streamed every iteration) exceeds the 126 MB L2; "
                   "no flush needed; the 50 MB scene itself is L2-resident by design",
             "parallelism": "stratum sharding, one NCCL film reduce per frame"}
 

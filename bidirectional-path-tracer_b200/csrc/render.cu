@@ -610,7 +610,10 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
 // Thread idx walks the concatenation light | lambertian | metal | dielectric of the queues k_trace_* filled, so
 // a warp straddles at most one class boundary; the survivors' queue append and the retirement of ended
 // subpaths are shared.
-__global__ void __launch_bounds__(kBlock) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
+#ifndef SHADE_BLOCKS
+#define SHADE_BLOCKS 12
+#endif
+__global__ void __launch_bounds__(kBlock, SHADE_BLOCKS) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
     const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
     const uint32_t n_li = w.counters[C_MAT0 + BDPT_MAT_LIGHT], n_la = w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN],
                    n_me = w.counters[C_MAT0 + BDPT_MAT_METAL], n_di = w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
