@@ -298,6 +298,9 @@ __device__ __forceinline__ void bin_by_material(const WF& w, int cls, uint32_t p
 
 // Traversal stacks live in local memory (L1-cached, lane-interleaved by the hardware): a shared-memory stack
 // of tree-depth levels cost 24.5 KB per block, capped residency at 6 blocks per SM and shrank L1.
+#ifndef BDPT_WIDE_WALK
+#define BDPT_WIDE_WALK 0   // 1: bulk rays take the warp-wide lock-step walk with postponed leaves (Walk::run_wide): parity-green, measured 25 % slower
+#endif
 #ifndef BDPT_TRAV_BLOCKS
 #define BDPT_TRAV_BLOCKS 8
 #endif
@@ -440,7 +443,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
             result = WALK_YIELD;
         }
         // ---- refill the idle lanes
-        const uint32_t my = warp_fetch(w.counters + C_CURSOR, !have, n, exhausted, threshold >> 8);
+        const uint32_t my = warp_fetch(w.counters + C_CURSOR, !have, n, exhausted, (threshold >> 8) & 0xFF);
         if (my != 0xFFFFFFFFu) {
             pid = queue[my];
             const RayD r = load_path_ray(w, pid);
@@ -449,10 +452,18 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
         }
         if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
         // ---- walk
+#if BDPT_WIDE_WALK
+        {
+            const int rc = W.run_wide(sc, l_stack, have, threshold & 0xFF, (threshold >> 16) & 0xFF, (threshold >> 24) & 0xFF,
+                                      exhausted ? 0 : ((threshold >> 8) & 0xFF), limit);
+            if (have && rc != WALK_YIELD) { result = rc; have = false; }
+        }
+#else
         if (have) {
             const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF), limit);
             if (rc != WALK_YIELD) { result = rc; have = false; }
         }
+#endif
     }
 }
 
@@ -895,7 +906,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
             }
             result = WALK_YIELD;
         }
-        const uint32_t my = warp_fetch(q.cnt + SQ_CURSOR, !have, n, exhausted, threshold >> 8);
+        const uint32_t my = warp_fetch(q.cnt + SQ_CURSOR, !have, n, exhausted, (threshold >> 8) & 0xFF);
         if (my != 0xFFFFFFFFu) {
             idx = q.live[my];
             const RayD r = load_shadow_ray(q, idx);
@@ -903,10 +914,18 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
             else result = TR_DEFER;
         }
         if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
+#if BDPT_WIDE_WALK
+        {
+            const int rc = W.run_wide(sc, l_stack, have, threshold & 0xFF, (threshold >> 16) & 0xFF, (threshold >> 24) & 0xFF,
+                                      exhausted ? 0 : ((threshold >> 8) & 0xFF), limit);
+            if (have && rc != WALK_YIELD) { result = rc; have = false; }
+        }
+#else
         if (have) {
             const int rc = W.run(sc, l_stack, exhausted ? 0 : (threshold & 0xFF), limit);
             if (rc != WALK_YIELD) { result = rc; have = false; }
         }
+#endif
     }
 }
 
@@ -1319,10 +1338,17 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
     J.resident_blocks = unsigned(sms * kTravBlocksPerSM);
-    int slice = 4, min_idle = 8;   // walk time slice (leaf visits) and idle lanes that trigger a refill
+#if BDPT_WIDE_WALK
+    int slice = 16, min_idle = 8;   // trips per call of the lock-step walk and idle lanes that trigger a refill
+#else
+    int slice = 4, min_idle = 8;    // walk time slice (leaf visits) and idle lanes that trigger a refill
+#endif
+    int t_leaf = 16, t_walk = 8;    // lock-step walk: postponed leaves that start the triangle tests / walkers below which they start anyway
     if (const char* e = std::getenv("BDPT_WALK_SLICE")) slice = std::atoi(e);
     if (const char* e = std::getenv("BDPT_MIN_IDLE")) min_idle = std::atoi(e);
-    J.threshold = (slice & 0xFF) | (min_idle << 8);
+    if (const char* e = std::getenv("BDPT_T_LEAF")) t_leaf = std::atoi(e);
+    if (const char* e = std::getenv("BDPT_T_WALK")) t_walk = std::atoi(e);
+    J.threshold = int(uint32_t(slice & 0xFF) | (uint32_t(min_idle & 0xFF) << 8) | (uint32_t(t_leaf & 0xFF) << 16) | (uint32_t(t_walk & 0xFF) << 24));
     std::atomic<int64_t> next_sample{0};
     J.next = &next_sample;
 

@@ -49,6 +49,7 @@ struct Walk {
     // walk position
     int sp;
     int32_t cur;
+    int32_t pend;      // run_wide: a leaf whose triangle tests are postponed (0: none; leaf codes are negative)
     // ANY: knife-edge candidates decided after the walk
     uint32_t edge_prim[4];
     int n_edge;
@@ -71,7 +72,7 @@ struct Walk {
         work = 0;
         best_rank = 0;
         found = false; flagged = false;
-        sp = 0; cur = 0;
+        sp = 0; cur = 0; pend = 0;
         n_edge = 0;
         ts.nodes = 0; ts.tris = 0;
     }
@@ -92,6 +93,15 @@ struct Walk {
     // brings the warp back together: __activemask() inside the walk only sees the lanes that happen to be
     // scheduled together, not the lanes that still have work.
     __device__ __forceinline__ int run(const SceneView& sc, StackEntry* stack, int rounds, uint32_t limit = 0);
+    // The same walk for a whole warp in lock step (all 32 lanes must call it; `busy` = this lane has a ray):
+    // every trip each walking lane opens ONE node, a lane that reaches a leaf postpones its triangle tests and
+    // keeps walking, and the tests run for all postponed leaves at once when at least `t_leaf` lanes have one
+    // or at most `t_walk` lanes can still walk.  Returns after `trips` trips, or earlier when no lane is busy
+    // or (min_idle > 0) at least `min_idle` lanes are idle.  Per lane: WALK_YIELD (call again) or TR_*.
+    __device__ __forceinline__ int run_wide(const SceneView& sc, StackEntry* stack, bool busy, int trips, int t_leaf,
+                                            int t_walk, int min_idle, uint32_t limit = 0);
+    // triangle tests of one leaf; true: ANY walk found a certain occluder (hit is set)
+    __device__ __forceinline__ bool leaf_tests(const SceneView& sc, uint32_t first, uint32_t cnt);
     // the decision once the walk has ended (the tail of traverse_fast_t)
     __device__ __forceinline__ int finish(const SceneView& sc);
 };
@@ -138,40 +148,105 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
         const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
         work += cnt;
         if (limit && work > limit) return TR_SLOW;   // nothing decided: the caller parks the ray for a split walk
-        for (uint32_t k = 0; k < cnt; ++k) {
-            if (STATS) ++ts.tris;
-            double t, u, v;
-            if (!tri_candidate(sc.fast_tris + first + k, r.o, r.d, t, u, v)) continue;
-            const uint32_t prim = __ldg(sc.fast_prims + first + k);   // only candidates need their id
-            const double band = band_abs + 1e-10 * fabs(t);
-            const bool edge = fabs(t - r.tmin) <= band || fabs(t - r.tmax) <= band;
-            if (ANY) {
-                if (edge) {   // knife edge: decided after the walk, by the reference's own box chain
-                    if (r.tmin <= t && t <= r.tmax) {
-                        if (n_edge < 4) edge_prim[n_edge++] = prim; else flagged = true;
-                    }
-                    continue;
-                }
-                if (r.tmin <= t && t <= r.tmax) {                  // certain occluder
-                    hit.t = t; hit.u = u; hit.v = v; hit.prim = prim; found = true;
-                    return TR_HIT;
-                }
-            } else {
-                if (found && fabs(t - best) <= band) flagged = true;   // tie with the current best
-                if (edge) flagged = true;
-                if (r.tmin <= t && t <= best) {
-                    const uint32_t rank = __ldg(sc.dfs_rank + prim);
-                    if (!found || t < best || rank > best_rank) {
-                        best = t; best_rank = rank; found = true;
-                        best_t = fminf(__double2float_ru(best), cull_hi);
-                        hit.t = t; hit.u = u; hit.v = v; hit.prim = prim;
-                    }
-                }
-            }
-        }
+        if (leaf_tests(sc, first, cnt)) return TR_HIT;
         if (!pop(stack)) return finish(sc);
         if (--rounds == 0) return WALK_YIELD;
     }
+}
+
+template <bool ANY, bool STATS>
+__device__ __forceinline__ bool Walk<ANY, STATS>::leaf_tests(const SceneView& sc, uint32_t first, uint32_t cnt) {
+    for (uint32_t k = 0; k < cnt; ++k) {
+        if (STATS) ++ts.tris;
+        double t, u, v;
+        if (!tri_candidate(sc.fast_tris + first + k, r.o, r.d, t, u, v)) continue;
+        const uint32_t prim = __ldg(sc.fast_prims + first + k);   // only candidates need their id
+        const double band = band_abs + 1e-10 * fabs(t);
+        const bool edge = fabs(t - r.tmin) <= band || fabs(t - r.tmax) <= band;
+        if (ANY) {
+            if (edge) {   // knife edge: decided after the walk, by the reference's own box chain
+                if (r.tmin <= t && t <= r.tmax) {
+                    if (n_edge < 4) edge_prim[n_edge++] = prim; else flagged = true;
+                }
+                continue;
+            }
+            if (r.tmin <= t && t <= r.tmax) {                  // certain occluder
+                hit.t = t; hit.u = u; hit.v = v; hit.prim = prim; found = true;
+                return true;
+            }
+        } else {
+            if (found && fabs(t - best) <= band) flagged = true;   // tie with the current best
+            if (edge) flagged = true;
+            if (r.tmin <= t && t <= best) {
+                const uint32_t rank = __ldg(sc.dfs_rank + prim);
+                if (!found || t < best || rank > best_rank) {
+                    best = t; best_rank = rank; found = true;
+                    best_t = fminf(__double2float_ru(best), cull_hi);
+                    hit.t = t; hit.u = u; hit.v = v; hit.prim = prim;
+                }
+            }
+        }
+    }
+    return false;
+}
+
+constexpr int32_t kWalkDry = INT32_MIN;   // cur: the stack has run dry (never a leaf code: first < 2^28)
+
+template <bool ANY, bool STATS>
+__device__ __forceinline__ int Walk<ANY, STATS>::run_wide(const SceneView& sc, StackEntry* stack, bool busy, int trips,
+                                                          int t_leaf, int t_walk, int min_idle, uint32_t limit) {
+    int result = WALK_YIELD;
+    for (int trip = 0; trip < trips; ++trip) {
+        // ---- one node per walking lane
+        if (busy && cur >= 0) {
+            const float4* q = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
+            const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+            const int4 w = __ldg(reinterpret_cast<const int4*>(q + 3));
+            if (STATS) ++ts.nodes;
+            ++work;
+            float ln = tmin_t, lf = best_t, rn = tmin_t, rf = best_t;
+            slab_fma(a.x, a.w, ox, ix, ln, lf);
+            slab_fma(a.y, b.x, oy, iy, ln, lf);
+            slab_fma(a.z, b.y, oz, iz, ln, lf);
+            slab_fma(b.z, c.y, ox, ix, rn, rf);
+            slab_fma(b.w, c.z, oy, iy, rn, rf);
+            slab_fma(c.x, c.w, oz, iz, rn, rf);
+            const bool hl = ln <= lf, hr = rn <= rf;
+            int32_t lc = w.x, rc = w.y;
+            if (hl && hr) {
+                float far_t = rn;
+                if (rn < ln) { const int32_t t = lc; lc = rc; rc = t; far_t = ln; }
+                stack[sp] = pack_entry(rc, far_t);
+                ++sp;
+                cur = lc;
+            } else if (hl) cur = lc;
+            else if (hr) cur = rc;
+            else if (!pop(stack)) cur = kWalkDry;
+        }
+        // ---- a leaf moves into the postponed slot when that is free, and the lane walks on
+        if (busy && cur < 0 && cur != kWalkDry && pend == 0) {
+            pend = cur;
+            if (!pop(stack)) cur = kWalkDry;
+        }
+        // ---- triangle tests for every postponed leaf at once
+        const uint32_t m_pend = __ballot_sync(0xFFFFFFFFu, busy && pend != 0);
+        const uint32_t m_walk = __ballot_sync(0xFFFFFFFFu, busy && cur >= 0);
+        if (m_pend && (__popc(m_pend) >= t_leaf || __popc(m_walk) <= t_walk)) {
+            if (busy && pend != 0) {
+                const uint32_t code = uint32_t(~pend);
+                const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+                pend = 0;
+                work += cnt;
+                if (limit && work > limit) { result = TR_SLOW; busy = false; }
+                else if (leaf_tests(sc, first, cnt)) { result = TR_HIT; busy = false; }
+                // a closer hit lowers best_t: pop() and the slab test drop what no longer matters as it comes up
+            }
+        }
+        if (busy && cur == kWalkDry && pend == 0) { result = finish(sc); busy = false; }
+        const uint32_t m_busy = __ballot_sync(0xFFFFFFFFu, busy);
+        if (!m_busy || (min_idle > 0 && 32 - __popc(m_busy) >= min_idle)) break;
+    }
+    return result;
 }
 
 template <bool ANY, bool STATS>
