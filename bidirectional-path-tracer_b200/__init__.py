@@ -294,8 +294,13 @@ class Context:
         o.streams = streams
         self._chk(lib().bdpt_render(self._h, C.byref(cam), C.byref(o)), "bdpt_render")
 
-    def film(self):
-        out = np.empty(self.film_shape, np.float64)
+    def film(self, out=None):
+        """The fp64 RGB sum film (camera.h:55) copied to the host; `out`: a C-contiguous float64 array of
+        film_shape to fill (e.g. a view of pinned memory, reused from frame to frame)."""
+        if out is None:
+            out = np.empty(self.film_shape, np.float64)
+        elif out.dtype != np.float64 or tuple(out.shape) != tuple(self.film_shape) or not out.flags.c_contiguous:
+            raise ValueError("film(out=...): need a C-contiguous float64 array of shape %r" % (tuple(self.film_shape),))
         self._chk(lib().bdpt_film_download(self._h, out.ctypes.data), "bdpt_film_download")
         return out
 

@@ -197,42 +197,50 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     auto ms_since = [&](std::chrono::steady_clock::time_point t) { return std::chrono::duration<double, std::milli>(now() - t).count(); };
     const auto t_start = now();
     double t_flat = 0, t_ref = 0, t_fast = 0;
+    HostScene& h = ctx->host;
+    SceneView v{};
+    int rc = BDPT_OK;
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    free_scene(ctx);
+    ctx->have_scene = false;
     try {
-        flatten_scene(verts, mat_id, n_tris, mats, n_mats, ctx->host);
+        flatten_scene(verts, mat_id, n_tris, mats, n_mats, h);
         t_flat = ms_since(t_start);
-        // the two trees share only read-only inputs (tri_box): build them side by side
-        std::exception_ptr fast_err;
+        // The two trees share only read-only inputs (tri_box): they are built side by side on their own threads
+        // while this one copies what is already final, then each tree's arrays as soon as that tree is done.
+        std::exception_ptr fast_err, ref_err;
         const auto t_b = now();
-        std::thread fast_thread([&] { try { build_fast_bvh(ctx->host); t_fast = ms_since(t_b); } catch (...) { fast_err = std::current_exception(); } });
-        try { build_ref_bvh(ctx->host); t_ref = ms_since(t_b); } catch (...) { fast_thread.join(); throw; }
+        std::thread fast_thread([&] { try { build_fast_bvh(h); t_fast = ms_since(t_b); } catch (...) { fast_err = std::current_exception(); } });
+        std::thread ref_thread([&] { try { build_ref_bvh(h); t_ref = ms_since(t_b); } catch (...) { ref_err = std::current_exception(); } });
+        if (!rc) rc = upload(ctx, h.tris, &v.tris);
+        if (!rc) rc = upload(ctx, h.shade, &v.shade);
+        if (!rc) rc = upload(ctx, h.mats, &v.mats);
+        if (!rc) rc = upload(ctx, h.lights, &v.lights);
+        if (!rc) rc = upload(ctx, h.light_area, &v.light_area);
         fast_thread.join();
+        if (!rc && !fast_err) {
+            rc = upload(ctx, h.fast_nodes, &v.fast_nodes);
+            if (!rc) rc = upload(ctx, h.fast_prims, &v.fast_prims);
+            if (!rc) rc = upload(ctx, h.fast_tris, &v.fast_tris);
+        }
+        ref_thread.join();
         if (fast_err) std::rethrow_exception(fast_err);
+        if (ref_err) std::rethrow_exception(ref_err);
     } catch (const std::exception& ex) {
+        free_scene(ctx);
         ctx->err = ex.what();
         return BDPT_ERR_ARG;
     }
-    HostScene& h = ctx->host;
-    if (h.ref_depth >= uint32_t(kRefStackLevels) || h.fast_depth + 2 > 32u) {   // 64 int32 / 32 StackEntry slots of local stack
+    if (!rc) rc = upload(ctx, h.ref_nodes, &v.ref_nodes);
+    if (!rc) rc = upload(ctx, h.dfs_rank, &v.dfs_rank);
+    if (!rc) rc = upload(ctx, h.ref_parent, &v.ref_parent);
+    if (!rc) rc = upload(ctx, h.prim_leaf, &v.prim_leaf);
+    if (!rc) rc = upload(ctx, h.chain_box, &v.chain_box);
+    if (!rc && (h.ref_depth >= uint32_t(kRefStackLevels) || h.fast_depth + 2 > 32u)) {   // 64 int32 / 32 StackEntry slots of local stack
         ctx->err = "BVH deeper than the traversal stack";
-        return BDPT_ERR_ARG;
+        rc = BDPT_ERR_ARG;
     }
-    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    free_scene(ctx);
-    SceneView v{};
-    int rc;
-    if ((rc = upload(ctx, h.ref_nodes, &v.ref_nodes))) return rc;
-    if ((rc = upload(ctx, h.fast_nodes, &v.fast_nodes))) return rc;
-    if ((rc = upload(ctx, h.fast_prims, &v.fast_prims))) return rc;
-    if ((rc = upload(ctx, h.fast_tris, &v.fast_tris))) return rc;
-    if ((rc = upload(ctx, h.dfs_rank, &v.dfs_rank))) return rc;
-    if ((rc = upload(ctx, h.ref_parent, &v.ref_parent))) return rc;
-    if ((rc = upload(ctx, h.prim_leaf, &v.prim_leaf))) return rc;
-    if ((rc = upload(ctx, h.chain_box, &v.chain_box))) return rc;
-    if ((rc = upload(ctx, h.tris, &v.tris))) return rc;
-    if ((rc = upload(ctx, h.shade, &v.shade))) return rc;
-    if ((rc = upload(ctx, h.mats, &v.mats))) return rc;
-    if ((rc = upload(ctx, h.lights, &v.lights))) return rc;
-    if ((rc = upload(ctx, h.light_area, &v.light_area))) return rc;
+    if (rc) { free_scene(ctx); return rc; }
     v.n_lights = uint32_t(h.lights.size());
     v.n_tris = uint32_t(h.tris.size());
     v.n_ref_nodes = uint32_t(h.ref_nodes.size());

@@ -171,66 +171,65 @@ void build_fast_bvh(HostScene& s) {
         if (cext > 0 && t.depth < 22 && cnt > 2) {
             // binned SAH over all three axes
             double best_cost = std::numeric_limits<double>::infinity();
-            int best_axis = -1, best_bin = -1;
+            int best_axis = -1, best_bin = -1, best_nb = kBins;
             B3 best_bins[kBins];
-            for (int ax = 0; ax < 3; ++ax) {
-                const double e = chi[ax] - clo[ax];
-                if (!(e > 0)) continue;
-                B3 bins[kBins]; uint32_t bc[kBins];
-                for (int b = 0; b < kBins; ++b) { bins[b].reset(); bc[b] = 0; }
-                const double sc = kBins / e;
-                if (!fork) {
-                    for (uint32_t i = t.begin; i < t.end; ++i) {
-                        const double* b = tb + 6 * size_t(s.fast_prims[i]);
-                        int bi = int((0.5 * (b[ax] + b[3 + ax]) - clo[ax]) * sc);
-                        bi = std::min(std::max(bi, 0), kBins - 1);
-                        bins[bi].grow(b); ++bc[bi];
+            // few triangles need few bins: the sweeps below cost per bin, and most nodes of a tree are small
+            const int nb = int(std::min<uint32_t>(kBins, std::max<uint32_t>(4u, 2u * cnt)));
+            best_nb = nb;
+            // one pass over the triangles fills the bins of all three axes
+            struct alignas(64) PB { B3 b[3][kBins]; uint32_t c[3][kBins]; };
+            double sc3[3];
+            for (int ax = 0; ax < 3; ++ax) { const double e = chi[ax] - clo[ax]; sc3[ax] = e > 0 ? nb / e : 0.0; }
+            auto fill = [&](PB& pb, uint32_t cb, uint32_t ce) {
+                for (int ax = 0; ax < 3; ++ax) for (int k = 0; k < nb; ++k) { pb.b[ax][k].reset(); pb.c[ax][k] = 0; }
+                for (uint32_t i = cb; i < ce; ++i) {
+                    const double* bx = tb + 6 * size_t(s.fast_prims[i]);
+                    for (int ax = 0; ax < 3; ++ax) {
+                        int bi = int((0.5 * (bx[ax] + bx[3 + ax]) - clo[ax]) * sc3[ax]);
+                        bi = std::min(std::max(bi, 0), nb - 1);
+                        pb.b[ax][bi].grow(bx); ++pb.c[ax][bi];
                     }
-                } else {
-                    struct alignas(64) PB { B3 b[kBins]; uint32_t c[kBins]; };
-                    std::vector<PB> part(kTopThreads);
-                    for (auto& x : part) for (int b = 0; b < kBins; ++b) { x.b[b].reset(); x.c[b] = 0; }
-                    par_chunks(t.begin, t.end, kTopThreads, [&](uint32_t cb, uint32_t ce, unsigned q) {
-                        PB mine = part[q];
-                        for (uint32_t i = cb; i < ce; ++i) {
-                            const double* b = tb + 6 * size_t(s.fast_prims[i]);
-                            int bi = int((0.5 * (b[ax] + b[3 + ax]) - clo[ax]) * sc);
-                            bi = std::min(std::max(bi, 0), kBins - 1);
-                            mine.b[bi].grow(b); ++mine.c[bi];
-                        }
-                        part[q] = mine;
-                    });
-                    for (auto& x : part)
-                        for (int b = 0; b < kBins; ++b) { bins[b].grow(x.b[b]); bc[b] += x.c[b]; }
                 }
+            };
+            PB all;
+            if (!fork) fill(all, t.begin, t.end);
+            else {
+                std::vector<PB> part(kTopThreads);
+                for (auto& x : part) fill(x, 0, 0);
+                par_chunks(t.begin, t.end, kTopThreads, [&](uint32_t cb, uint32_t ce, unsigned q) { fill(part[q], cb, ce); });
+                fill(all, 0, 0);
+                for (auto& x : part)
+                    for (int ax = 0; ax < 3; ++ax)
+                        for (int k = 0; k < nb; ++k) { all.b[ax][k].grow(x.b[ax][k]); all.c[ax][k] += x.c[ax][k]; }
+            }
+            for (int ax = 0; ax < 3; ++ax) {
+                if (!(chi[ax] - clo[ax] > 0)) continue;
+                const B3* bins = all.b[ax]; const uint32_t* bc = all.c[ax];
                 double ra[kBins]; uint32_t rc[kBins];
                 B3 acc; acc.reset(); uint32_t c = 0;
-                for (int b = kBins - 1; b > 0; --b) { acc.grow(bins[b]); c += bc[b]; ra[b] = acc.half_area(); rc[b] = c; }
+                for (int k = nb - 1; k > 0; --k) { acc.grow(bins[k]); c += bc[k]; ra[k] = acc.half_area(); rc[k] = c; }
                 acc.reset(); c = 0;
-                for (int b = 0; b < kBins - 1; ++b) {
-                    acc.grow(bins[b]); c += bc[b];
-                    if (c == 0 || rc[b + 1] == 0) continue;
-                    double cost = acc.half_area() * c + ra[b + 1] * rc[b + 1];
-                    if (cost < best_cost) {
-                        best_cost = cost; best_axis = ax; best_bin = b;
-                        for (int k = 0; k < kBins; ++k) best_bins[k] = bins[k];
-                    }
+                for (int k = 0; k < nb - 1; ++k) {
+                    acc.grow(bins[k]); c += bc[k];
+                    if (c == 0 || rc[k + 1] == 0) continue;
+                    double cost = acc.half_area() * c + ra[k + 1] * rc[k + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = k; }
                 }
             }
+            if (best_axis >= 0) for (int k = 0; k < nb; ++k) best_bins[k] = all.b[best_axis][k];
             if (best_axis >= 0) {
-                const double e = chi[best_axis] - clo[best_axis];
-                const double sc = kBins / e;
+                const double sc = sc3[best_axis];
                 const double lo = clo[best_axis];
                 auto it = std::partition(s.fast_prims.begin() + t.begin, s.fast_prims.begin() + t.end, [&](uint32_t p) {
                     const double* b = tb + 6 * size_t(p);
                     int bi = int((0.5 * (b[best_axis] + b[3 + best_axis]) - lo) * sc);
-                    bi = std::min(std::max(bi, 0), kBins - 1);
+                    bi = std::min(std::max(bi, 0), best_nb - 1);
                     return bi <= best_bin;
                 });
                 mid = uint32_t(it - s.fast_prims.begin());
                 split_ok = mid > t.begin && mid < t.end;
                 lbox.reset(); rbox.reset();
-                for (int k = 0; k < kBins; ++k) (k <= best_bin ? lbox : rbox).grow(best_bins[k]);
+                for (int k = 0; k < best_nb; ++k) (k <= best_bin ? lbox : rbox).grow(best_bins[k]);
             }
         }
         if (!split_ok) {
