@@ -202,7 +202,7 @@ def run_ours(args):
             torch.cuda.synchronize()
 
     # ---------------- device-resident measurement
-    ctx.upload(sf.verts, sf.mat_id, sf.materials)
+    ctx.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
     ctx.film_clear(WIDTH, HEIGHT)
     fptr, fn = ctx.film_device_ptr()
     film_t = torch.as_tensor(CudaArray(fptr, fn), device=torch.device("cuda", local))
@@ -245,7 +245,7 @@ def run_ours(args):
     film_buf = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64, pin_memory=True).numpy()   # the caller's frame buffer, pinned
     sync_all()
     t0 = time.perf_counter()
-    ctx2.upload(sf.verts, sf.mat_id, sf.materials)
+    ctx2.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
     ctx2.film_clear(WIDTH, HEIGHT)
     for s in range(K):
         ctx2.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
@@ -269,7 +269,7 @@ def run_ours(args):
     if rank == 0:
         line = {"metric": "BDPT Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": Wm,
                 "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic", "config": dict(workload_config(), bvh=args.bvh),
+                "dtype": "f64", "data": "synthetic", "config": dict(workload_config(), bvh=args.bvh, fast_tree="device, Morton order" if args.gpu_tree else "host, binned SAH"),
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
                         "note": "scene upload from host buffers (host BVH build + H2D) + K steps + film read-back into a pinned host frame buffer"},
                 "gpu_launches": st["kernel_launches"], "clocks": clocks, "wall_ms_per_step": wall_ms / K,
@@ -367,7 +367,7 @@ def bvh_microbench(args, pkg, bvh):
     rays = ts.ray_batch(sf.verts, MICRO_RAYS, seed=0x5EED0001, cam=cam, width=512, height=512)
     n = len(rays)
     with pkg.Context(int(os.environ.get("LOCAL_RANK", "0"))) as c:
-        c.upload(sf.verts, sf.mat_id, sf.materials)
+        c.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
         res = {"rays": n, "triangles": len(sf.verts), "scene": "glass-of-water (stand-in geometry)"}
         for name, flavour in (("fast", pkg.BVH_FAST), ("reference_topology", pkg.BVH_REFERENCE)):
             best_ms, best_wall = 1e30, 1e30
@@ -398,6 +398,7 @@ def main():
     ap.add_argument("--seed", type=int, default=20261104)
     ap.add_argument("--batch", type=int, default=0, help="sample slots per wavefront (0 = library default)")
     ap.add_argument("--streams", type=int, default=0, help="wavefronts in flight (0 = library default)")
+    ap.add_argument("--gpu-tree", action="store_true", help="build the fast tree on the device (Morton order) instead of the host binned-SAH build")
     ap.add_argument("--skip-micro", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     args = ap.parse_args()

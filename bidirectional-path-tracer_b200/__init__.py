@@ -23,7 +23,7 @@ RAY_DTYPE = np.dtype([("o", "<f8", 3), ("d", "<f8", 3), ("tmin", "<f8"), ("tmax"
 HIT_DTYPE = np.dtype([("t", "<f8"), ("u", "<f8"), ("v", "<f8"), ("prim", "<u4"), ("pad", "<u4")])
 
 EXPORTS = [
-    "bdpt_ctx_create", "bdpt_ctx_destroy", "bdpt_last_error", "bdpt_scene_upload", "bdpt_bvh_info",
+    "bdpt_ctx_create", "bdpt_ctx_destroy", "bdpt_last_error", "bdpt_scene_upload", "bdpt_scene_upload_ex", "bdpt_bvh_info",
     "bdpt_bvh_leaf_order", "bdpt_host_bvh_build", "bdpt_trace", "bdpt_visible", "bdpt_render",
     "bdpt_film_clear", "bdpt_film_device_ptr", "bdpt_film_download", "bdpt_film_to_rgb8", "bdpt_stats",
     "bdpt_stats_reset", "bdpt_last_device_ms", "bdpt_sync", "bdpt_kernel_times",
@@ -58,6 +58,7 @@ class Stats(C.Structure):
 
 RENDER_STATS = 1
 RENDER_SERIAL = 2
+UPLOAD_FAST_TREE_GPU = 1
 KERNEL_CLASSES = ("generate", "trace", "shade", "connect", "shadow", "trace_exact", "shadow_exact")
 
 
@@ -88,6 +89,7 @@ def lib():
         L.bdpt_ctx_destroy.argtypes = [C.c_void_p]
         L.bdpt_ctx_destroy.restype = None
         L.bdpt_scene_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32]
+        L.bdpt_scene_upload_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32]
         L.bdpt_bvh_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
         L.bdpt_bvh_leaf_order.argtypes = [C.c_void_p, C.c_void_p]
         L.bdpt_host_bvh_build.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -231,14 +233,15 @@ class Context:
     def __exit__(self, *a):
         self.close()
 
-    def upload(self, verts, mat_id, mats):
+    def upload(self, verts, mat_id, mats, gpu_tree=False):
+        """bdpt_scene_upload; gpu_tree: build the BVH_FAST tree on the device (UPLOAD_FAST_TREE_GPU)."""
         v = np.ascontiguousarray(verts, dtype=np.float64).reshape(-1, 9)
         m = np.ascontiguousarray(mat_id, dtype=np.uint32)
         if len(m) != len(v):
             raise ValueError("mat_id length")
         marr = make_materials(mats) if isinstance(mats, list) else mats
-        self._chk(lib().bdpt_scene_upload(self._h, v.ctypes.data, m.ctypes.data, len(v), C.byref(marr), len(marr)),
-                  "bdpt_scene_upload")
+        self._chk(lib().bdpt_scene_upload_ex(self._h, v.ctypes.data, m.ctypes.data, len(v), C.byref(marr), len(marr),
+                                             UPLOAD_FAST_TREE_GPU if gpu_tree else 0), "bdpt_scene_upload")
         self.n_tris = len(v)
         return self
 

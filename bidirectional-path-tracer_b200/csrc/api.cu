@@ -190,7 +190,14 @@ const char* bdpt_last_error(bdpt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_c
 
 int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                       const bdpt_material* mats, uint32_t n_mats) {
+    return bdpt_scene_upload_ex(ctx, verts, mat_id, n_tris, mats, n_mats, 0u);
+}
+
+int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
+                         const bdpt_material* mats, uint32_t n_mats, uint32_t flags) {
     if (!ctx) return BDPT_ERR_ARG;
+    if (flags & ~BDPT_UPLOAD_FAST_TREE_GPU) { ctx->err = "unknown upload flags"; return BDPT_ERR_ARG; }
+    const bool gpu_tree = (flags & BDPT_UPLOAD_FAST_TREE_GPU) != 0;
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
     const bool timing = std::getenv("BDPT_TIMING") != nullptr;
     auto now = [] { return std::chrono::steady_clock::now(); };
@@ -210,7 +217,10 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
         // while this one copies what is already final, then each tree's arrays as soon as that tree is done.
         std::exception_ptr fast_err, ref_err;
         const auto t_b = now();
-        std::thread fast_thread([&] { try { build_fast_bvh(h); t_fast = ms_since(t_b); } catch (...) { fast_err = std::current_exception(); } });
+        std::thread fast_thread([&] {
+            if (gpu_tree) return;
+            try { build_fast_bvh(h); t_fast = ms_since(t_b); } catch (...) { fast_err = std::current_exception(); }
+        });
         std::thread ref_thread([&] { try { build_ref_bvh(h); t_ref = ms_since(t_b); } catch (...) { ref_err = std::current_exception(); } });
         if (!rc) rc = upload(ctx, h.tris, &v.tris);
         if (!rc) rc = upload(ctx, h.shade, &v.shade);
@@ -218,10 +228,18 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
         if (!rc) rc = upload(ctx, h.lights, &v.lights);
         if (!rc) rc = upload(ctx, h.light_area, &v.light_area);
         fast_thread.join();
-        if (!rc && !fast_err) {
+        if (!rc && gpu_tree) {
+            double lo[3], hi[3];
+            scene_bounds(h, lo, hi);
+            h.fast_nodes.clear(); h.fast_prims.clear(); h.fast_tris.clear();
+            rc = build_fast_bvh_gpu(ctx, v.tris, uint32_t(h.tris.size()), lo, hi, h.extent, &v.fast_nodes, &v.fast_prims, &v.fast_tris,
+                                    &v.n_fast_nodes, &h.fast_depth);
+            t_fast = ms_since(t_b);
+        } else if (!rc && !fast_err) {
             rc = upload(ctx, h.fast_nodes, &v.fast_nodes);
             if (!rc) rc = upload(ctx, h.fast_prims, &v.fast_prims);
             if (!rc) rc = upload(ctx, h.fast_tris, &v.fast_tris);
+            v.n_fast_nodes = uint32_t(h.fast_nodes.size());
         }
         ref_thread.join();
         if (fast_err) std::rethrow_exception(fast_err);
@@ -244,7 +262,6 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
     v.n_lights = uint32_t(h.lights.size());
     v.n_tris = uint32_t(h.tris.size());
     v.n_ref_nodes = uint32_t(h.ref_nodes.size());
-    v.n_fast_nodes = uint32_t(h.fast_nodes.size());
     v.light_total_area = h.light_total_area;
     v.extent = h.extent;
     v.center = mk(h.center[0], h.center[1], h.center[2]);
@@ -264,7 +281,7 @@ int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth
         if (n_nodes) *n_nodes = ctx->host.ref_nodes.size();
         if (max_depth) *max_depth = ctx->host.ref_depth;
     } else if (bvh == BDPT_BVH_FAST) {
-        if (n_nodes) *n_nodes = ctx->host.fast_nodes.size();
+        if (n_nodes) *n_nodes = ctx->view.n_fast_nodes;
         if (max_depth) *max_depth = ctx->host.fast_depth;
     } else { ctx->err = "unknown bvh flavour"; return BDPT_ERR_ARG; }
     return BDPT_OK;

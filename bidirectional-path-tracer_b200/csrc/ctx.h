@@ -54,5 +54,9 @@ enum { KT_GENERATE = 0, KT_TRACE = 1, KT_SHADE = 2, KT_CONNECT = 3, KT_SHADOW = 
 
 int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts);
 void render_free(bdpt_ctx* ctx);
+// gpu_bvh.cu: the fast tree built on the device from triangles already uploaded (queued on ctx->stream)
+int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const double lo[3], const double hi[3], double extent,
+                       const FastNode** out_nodes, const uint32_t** out_prims, const TriGeom** out_tris, uint32_t* out_n_nodes,
+                       uint32_t* out_depth);
 
 }  // namespace bdpt

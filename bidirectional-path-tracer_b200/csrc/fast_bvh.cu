@@ -73,6 +73,19 @@ constexpr unsigned kTopThreads = 8;
 
 }  // namespace
 
+// bounds of all triangles; sets s.extent (largest side) and s.center
+void scene_bounds(HostScene& s, double lo[3], double hi[3]) {
+    const uint32_t n = uint32_t(s.tris.size());
+    const double* tb = s.tri_box.data();
+    B3 scene;
+    scene.reset();
+    for (uint32_t i = 0; i < n; ++i) scene.grow(tb + 6 * size_t(i));
+    double ext = 0.0;
+    for (int k = 0; k < 3; ++k) ext = std::max(ext, scene.hi[k] - scene.lo[k]);
+    s.extent = ext;
+    for (int k = 0; k < 3; ++k) { s.center[k] = 0.5 * (scene.lo[k] + scene.hi[k]); lo[k] = scene.lo[k]; hi[k] = scene.hi[k]; }
+}
+
 void build_fast_bvh(HostScene& s) {
     const uint32_t n = uint32_t(s.tris.size());
     const double* tb = s.tri_box.data();
@@ -80,13 +93,9 @@ void build_fast_bvh(HostScene& s) {
     for (uint32_t i = 0; i < n; ++i) s.fast_prims[i] = i;
     s.fast_nodes.clear();
     s.fast_nodes.reserve(n / 2 + 4);
-    B3 scene;
-    scene.reset();
-    for (uint32_t i = 0; i < n; ++i) scene.grow(tb + 6 * size_t(i));
-    double ext = 0.0;
-    for (int k = 0; k < 3; ++k) ext = std::max(ext, scene.hi[k] - scene.lo[k]);
-    s.extent = ext;
-    for (int k = 0; k < 3; ++k) s.center[k] = 0.5 * (scene.lo[k] + scene.hi[k]);
+    double slo[3], shi[3];
+    scene_bounds(s, slo, shi);
+    const double ext = s.extent;
     // outward padding: far above fp64 slab/triangle rounding noise, far below feature size
     const double eps = std::max(ext, 1e-30) * (1.0 / 65536.0);
 

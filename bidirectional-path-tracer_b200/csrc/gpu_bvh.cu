@@ -1,0 +1,256 @@
+// Fast-tree builder on the GPU (replaces the host build of the acceleration tree, bvh.h:13-48, for
+// big scenes).  It produces the same structure the walk reads (FastNode: both child boxes in the parent, fp32
+// rounded outward; leaves of <= 2 triangles in a leaf-ordered triangle copy), so every kernel and every parity
+// property is unchanged: the tree only decides which triangles the exact fp64 test sees.
+//
+//   1. k_morton      63-bit Morton code of each triangle's box centre within the scene bounds
+//   2. cub radix sort (code, prim id)
+//   3. k_gather      triangles copied into sorted order (fast_tris)
+//   4. k_split       top-down, one launch per level: a range splits where the highest differing code bit
+//                    flips (spatial median, LBVH), clamped so that no child holds more than 2^(kMaxLevel - level)
+//                    triangles: the depth is bounded by construction (the walk's stack has 32 slots), whatever
+//                    the distribution.  Ranges of <= 2 triangles are leaves.
+//   5. k_boxes       bottom-up, one launch per level: child boxes from leaves' triangles or from the children's
+//                    own boxes (fp64), padded and rounded outward like the host builder (fast_bvh.cu).
+// Node ids are handed out per level by an atomic counter, so levels are contiguous in memory (the top of the
+// tree shares cache lines); ids within a level vary from run to run, results do not.
+#include "ctx.h"
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+namespace bdpt {
+namespace {
+
+constexpr int kMaxLevel = 27;   // internal nodes live on levels 0..kMaxLevel: at most 28 stack entries per ray
+constexpr int kBuildBlock = 256;
+
+__device__ __forceinline__ void grow_tri(const TriGeom& t, double lo[3], double hi[3]) {
+    const double p[3][3] = {{t.v0x, t.v0y, t.v0z}, {t.v0x + t.e1x, t.v0y + t.e1y, t.v0z + t.e1z}, {t.v0x + t.e2x, t.v0y + t.e2y, t.v0z + t.e2z}};
+#pragma unroll
+    for (int v = 0; v < 3; ++v)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { lo[k] = fmin(lo[k], p[v][k]); hi[k] = fmax(hi[k], p[v][k]); }
+}
+
+__device__ __forceinline__ unsigned long long spread21(unsigned long long x) {   // 21 bits -> every third bit
+    x &= 0x1FFFFFull;
+    x = (x | x << 32) & 0x1F00000000FFFFull;
+    x = (x | x << 16) & 0x1F0000FF0000FFull;
+    x = (x | x << 8) & 0x100F00F00F00F00Full;
+    x = (x | x << 4) & 0x10C30C30C30C30C3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void __launch_bounds__(kBuildBlock) k_morton(const TriGeom* __restrict__ tris, uint32_t n, double lx, double ly, double lz,
+                                                        double sx, double sy, double sz, unsigned long long* __restrict__ keys,
+                                                        uint32_t* __restrict__ ids) {
+    const uint32_t i = blockIdx.x * kBuildBlock + threadIdx.x;
+    if (i >= n) return;
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    grow_tri(tris[i], lo, hi);
+    const double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
+    const double q[3] = {(c[0] - lx) * sx, (c[1] - ly) * sy, (c[2] - lz) * sz};   // [0, 2^21)
+    unsigned long long code = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double v = fmin(fmax(q[k], 0.0), 2097151.0);
+        code |= spread21((unsigned long long)v) << (2 - k);
+    }
+    keys[i] = code;
+    ids[i] = i;
+}
+
+__global__ void __launch_bounds__(kBuildBlock) k_gather(const TriGeom* __restrict__ tris, const uint32_t* __restrict__ prims, uint32_t n,
+                                                        TriGeom* __restrict__ out) {
+    const uint32_t i = blockIdx.x * kBuildBlock + threadIdx.x;
+    if (i >= n) return;
+    const int4* src = reinterpret_cast<const int4*>(tris + prims[i]);
+    int4* dst = reinterpret_cast<int4*>(out + i);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) dst[k] = src[k];
+}
+
+__device__ __forceinline__ int32_t leaf_code(uint32_t first, uint32_t cnt) { return int32_t(~((first << 3) | (cnt - 1u))); }
+
+// nodes [first_node, first_node + n_level) of one level split their ranges; children that stay internal get ids
+// from `counter` (all of them on the next level)
+__global__ void __launch_bounds__(kBuildBlock) k_split(const unsigned long long* __restrict__ keys, uint32_t* __restrict__ nb,
+                                                       uint32_t* __restrict__ ne, FastNode* __restrict__ nodes, uint32_t* counter,
+                                                       uint32_t first_node, uint32_t n_level, int level) {
+    const uint32_t j = blockIdx.x * kBuildBlock + threadIdx.x;
+    if (j >= n_level) return;
+    const uint32_t i = first_node + j;
+    const uint32_t b = nb[i], e = ne[i], cnt = e - b;
+    int32_t link[2];
+    if (cnt == 1) {   // a one-triangle scene: the root needs two children
+        link[0] = link[1] = leaf_code(b, 1);
+    } else {
+        const unsigned long long kf = keys[b], kl = keys[e - 1];
+        uint32_t mid;
+        if (kf == kl) mid = b + cnt / 2;
+        else {
+            const int p = __clzll((long long)(kf ^ kl));
+            uint32_t lo = b, hi = e - 1;   // keys[lo] shares more than p leading bits with kf, keys[hi] exactly p
+            while (hi - lo > 1) {
+                const uint32_t m = lo + (hi - lo) / 2;
+                if (__clzll((long long)(kf ^ keys[m])) > p) lo = m; else hi = m;
+            }
+            mid = hi;
+        }
+        const uint32_t cap = 1u << (kMaxLevel - level);   // cnt <= 2 * cap by induction (host checks the root)
+        if (e - mid > cap) mid = e - cap;
+        if (mid - b > cap) mid = b + cap;
+        const uint32_t cb[2] = {b, mid}, ce[2] = {mid, e};
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            const uint32_t c = ce[s] - cb[s];
+            if (c <= 2) link[s] = leaf_code(cb[s], c);
+            else {
+                const uint32_t id = atomicAdd(counter, 1u);
+                nb[id] = cb[s]; ne[id] = ce[s];
+                link[s] = int32_t(id);
+            }
+        }
+    }
+    nodes[i].left = link[0];
+    nodes[i].right = link[1];
+    nodes[i].pad[0] = 0; nodes[i].pad[1] = 0;
+}
+
+__global__ void __launch_bounds__(kBuildBlock) k_boxes(const TriGeom* __restrict__ ftris, FastNode* __restrict__ nodes, double* __restrict__ own,
+                                                       uint32_t first_node, uint32_t n_level, double eps) {
+    const uint32_t j = blockIdx.x * kBuildBlock + threadIdx.x;
+    if (j >= n_level) return;
+    const uint32_t i = first_node + j;
+    const int32_t link[2] = {nodes[i].left, nodes[i].right};
+    double lo[2][3], hi[2][3];
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+        for (int k = 0; k < 3; ++k) { lo[s][k] = INFINITY; hi[s][k] = -INFINITY; }
+        if (link[s] < 0) {
+            const uint32_t code = uint32_t(~link[s]);
+            const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+            for (uint32_t k = 0; k < cnt; ++k) grow_tri(ftris[first + k], lo[s], hi[s]);
+        } else {
+            const double* o = own + 6 * size_t(link[s]);
+            for (int k = 0; k < 3; ++k) { lo[s][k] = o[k]; hi[s][k] = o[3 + k]; }
+        }
+    }
+    FastNode& nd = nodes[i];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        nd.l_lo[k] = __double2float_rd(lo[0][k] - eps); nd.l_hi[k] = __double2float_ru(hi[0][k] + eps);
+        nd.r_lo[k] = __double2float_rd(lo[1][k] - eps); nd.r_hi[k] = __double2float_ru(hi[1][k] + eps);
+    }
+    double* o = own + 6 * size_t(i);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { o[k] = fmin(lo[0][k], lo[1][k]); o[3 + k] = fmax(hi[0][k], hi[1][k]); }
+}
+
+struct Scratch {
+    std::vector<void*> ptrs;
+    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
+    template <class T> cudaError_t take(T** p, size_t n) {
+        void* q = nullptr;
+        const cudaError_t e = cudaMalloc(&q, std::max<size_t>(n * sizeof(T), 16));
+        if (e == cudaSuccess) { ptrs.push_back(q); *p = static_cast<T*>(q); }
+        return e;
+    }
+};
+
+}  // namespace
+
+#define GB_CUDA(call)                                                                             \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess) {                                                                  \
+            ctx->err = std::string("gpu bvh build: " #call ": ") + cudaGetErrorString(e_);       \
+            return e_ == cudaErrorMemoryAllocation ? BDPT_ERR_NOMEM : BDPT_ERR_CUDA;              \
+        }                                                                                         \
+    } while (0)
+
+// d_tris: the scene's triangles in prim order, already on the device (queued on ctx->stream).  lo/hi: scene
+// bounds, extent: their largest side.  On success the three arrays are owned by ctx->scene_allocs.
+int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const double lo[3], const double hi[3], double extent,
+                       const FastNode** out_nodes, const uint32_t** out_prims, const TriGeom** out_tris, uint32_t* out_n_nodes,
+                       uint32_t* out_depth) {
+    if (n == 0 || n >= (1u << 28)) { ctx->err = "gpu bvh build: triangle count out of range"; return BDPT_ERR_ARG; }
+    const bool timing = std::getenv("BDPT_TIMING") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    cudaStream_t st = ctx->stream;
+    Scratch tmp;
+    unsigned long long *keys = nullptr, *keys_sorted = nullptr;
+    uint32_t *ids = nullptr, *nb = nullptr, *ne = nullptr, *counter = nullptr;
+    double* own = nullptr;
+    void* sort_tmp = nullptr;
+    GB_CUDA(tmp.take(&keys, n));
+    GB_CUDA(tmp.take(&keys_sorted, n));
+    GB_CUDA(tmp.take(&ids, n));
+    GB_CUDA(tmp.take(&nb, n));
+    GB_CUDA(tmp.take(&ne, n));
+    GB_CUDA(tmp.take(&counter, 1));
+    GB_CUDA(tmp.take(&own, 6 * size_t(n)));
+    // results (kept): at most n - 1 internal nodes
+    FastNode* nodes = nullptr;
+    uint32_t* prims = nullptr;
+    TriGeom* ftris = nullptr;
+    {
+        void* p = nullptr;
+        GB_CUDA(cudaMalloc(&p, size_t(n) * sizeof(FastNode)));  ctx->scene_allocs.push_back(p); nodes = static_cast<FastNode*>(p);
+        GB_CUDA(cudaMalloc(&p, size_t(n) * sizeof(uint32_t)));  ctx->scene_allocs.push_back(p); prims = static_cast<uint32_t*>(p);
+        GB_CUDA(cudaMalloc(&p, size_t(n) * sizeof(TriGeom)));   ctx->scene_allocs.push_back(p); ftris = static_cast<TriGeom*>(p);
+    }
+    const unsigned grid_n = (n + kBuildBlock - 1) / kBuildBlock;
+    double sc[3];
+    for (int k = 0; k < 3; ++k) sc[k] = hi[k] > lo[k] ? 2097152.0 / (hi[k] - lo[k]) : 0.0;
+    k_morton<<<grid_n, kBuildBlock, 0, st>>>(d_tris, n, lo[0], lo[1], lo[2], sc[0], sc[1], sc[2], keys, ids);
+    size_t sort_bytes = 0;
+    GB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys, keys_sorted, ids, prims, int(n), 0, 63, st));
+    GB_CUDA(tmp.take(reinterpret_cast<char**>(&sort_tmp), sort_bytes));
+    GB_CUDA(cub::DeviceRadixSort::SortPairs(sort_tmp, sort_bytes, keys, keys_sorted, ids, prims, int(n), 0, 63, st));
+    k_gather<<<grid_n, kBuildBlock, 0, st>>>(d_tris, prims, n, ftris);
+    // ---- top-down
+    const uint32_t root_range[2] = {0u, n};
+    const uint32_t one = 1u;
+    GB_CUDA(cudaMemcpyAsync(nb, &root_range[0], 4, cudaMemcpyHostToDevice, st));
+    GB_CUDA(cudaMemcpyAsync(ne, &root_range[1], 4, cudaMemcpyHostToDevice, st));
+    GB_CUDA(cudaMemcpyAsync(counter, &one, 4, cudaMemcpyHostToDevice, st));
+    if ((uint64_t(n) + 1) / 2 > (1ull << kMaxLevel)) { ctx->err = "gpu bvh build: too many triangles for the depth bound"; return BDPT_ERR_ARG; }
+    std::vector<uint32_t> level_first{0u};
+    uint32_t total = 1;
+    for (int level = 0;; ++level) {
+        const uint32_t first = level_first.back(), cnt = total - first;
+        if (cnt == 0) { level_first.pop_back(); break; }
+        if (level > kMaxLevel) { ctx->err = "gpu bvh build: depth bound violated"; return BDPT_ERR_CUDA; }
+        k_split<<<(cnt + kBuildBlock - 1) / kBuildBlock, kBuildBlock, 0, st>>>(keys_sorted, nb, ne, nodes, counter, first, cnt, level);
+        uint32_t now = 0;
+        GB_CUDA(cudaMemcpyAsync(&now, counter, 4, cudaMemcpyDeviceToHost, st));
+        GB_CUDA(cudaStreamSynchronize(st));
+        level_first.push_back(total);
+        total = now;
+    }
+    // ---- bottom-up
+    const double eps = std::max(extent, 1e-30) * (1.0 / 65536.0);   // the host builder's outward padding
+    for (size_t l = level_first.size(); l-- > 0;) {
+        const uint32_t first = level_first[l];
+        const uint32_t cnt = (l + 1 < level_first.size() ? level_first[l + 1] : total) - first;
+        k_boxes<<<(cnt + kBuildBlock - 1) / kBuildBlock, kBuildBlock, 0, st>>>(ftris, nodes, own, first, cnt, eps);
+    }
+    GB_CUDA(cudaGetLastError());
+    GB_CUDA(cudaStreamSynchronize(st));
+    *out_nodes = nodes; *out_prims = prims; *out_tris = ftris;
+    *out_n_nodes = total;
+    *out_depth = uint32_t(level_first.size()) + 1;   // internal levels + the leaves below them
+    if (timing)
+        std::fprintf(stderr, "  fast tree on the GPU: %u nodes, %zu levels, %.1f ms\n", total, level_first.size(),
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    return BDPT_OK;
+}
+
+}  // namespace bdpt

@@ -44,5 +44,6 @@ void flatten_scene(const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                    uint32_t n_mats, HostScene& out);
 void build_ref_bvh(HostScene& s);
 void build_fast_bvh(HostScene& s);
+void scene_bounds(HostScene& s, double lo[3], double hi[3]);
 
 }  // namespace bdpt

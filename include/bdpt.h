@@ -127,6 +127,13 @@ const char* bdpt_last_error(bdpt_ctx* ctx);   /* ctx may be NULL: last creation 
  * Builds both BVH flavours on the host and uploads them. */
 int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                       const bdpt_material* mats, uint32_t n_mats);
+/* The same with options.  BDPT_UPLOAD_FAST_TREE_GPU: the BDPT_BVH_FAST tree is built on the device (Morton
+ * sort + top-down splits with a depth bound, csrc/gpu_bvh.cu) instead of the host's binned-SAH build: a few
+ * ms for 10^7 triangles against seconds, for a tree that costs the walk more node visits per ray.  Results
+ * are identical either way (the tree only selects candidates for the exact test).  SURVEY 8f-1. */
+#define BDPT_UPLOAD_FAST_TREE_GPU 1u
+int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
+                         const bdpt_material* mats, uint32_t n_mats, uint32_t flags);
 int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth);
 /* DFS leaf order of the BDPT_BVH_REFERENCE build: order[k] = prim ID (n_tris entries) */
 int bdpt_bvh_leaf_order(bdpt_ctx* ctx, uint32_t* order);
