@@ -246,15 +246,19 @@ def run_ours(args):
     sync_all()
     t0 = time.perf_counter()
     ctx2.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
+    t_up = time.perf_counter()
     ctx2.film_clear(WIDTH, HEIGHT)
     for s in range(K):
         ctx2.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
+    t_rd = time.perf_counter()
     if dist:
         p2, n2_ = ctx2.film_device_ptr()
         dist.reduce(torch.as_tensor(CudaArray(p2, n2_), device=torch.device("cuda", local)), dst=0)
     film_host = ctx2.film(out=film_buf)
     sync_all()
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    t_end = time.perf_counter()
+    e2e_parts = {"scene_upload_ms": (t_up - t0) * 1e3, "render_ms": (t_rd - t_up) * 1e3, "film_reduce_and_readback_ms": (t_end - t_rd) * 1e3}
+    e2e_s = torch.tensor([t_end - t0], dtype=torch.float64, device="cuda")
     if dist:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = samples / float(e2e_s[0]) / 1e6
@@ -271,6 +275,7 @@ def run_ours(args):
                 "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic", "config": dict(workload_config(), bvh=args.bvh, fast_tree="device, Morton order" if args.gpu_tree else "host, binned SAH"),
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
+                        "rank0_ms": e2e_parts,
                         "note": "scene upload from host buffers (host BVH build + H2D) + K steps + film read-back into a pinned host frame buffer"},
                 "gpu_launches": st["kernel_launches"], "clocks": clocks, "wall_ms_per_step": wall_ms / K,
                 "film_reduce_ms": red_ms,

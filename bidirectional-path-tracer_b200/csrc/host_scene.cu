@@ -4,6 +4,9 @@
 // aabb merge / pad rules (src/acceleration/aabb.h:27-33,81-88, src/core/interval.h:12-16,36-39).
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cmath>
 #include <limits>
 #include <map>
@@ -129,27 +132,41 @@ void flatten_scene(const double* verts, const uint32_t* mat_id, uint64_t n, cons
         out.mats[i] = m;
     }
     out.tris.resize(n); out.shade.resize(n); out.area.resize(n); out.tri_box.resize(6 * n);
-    for (uint64_t i = 0; i < n; ++i) {
-        if (mat_id[i] >= n_mats) throw std::runtime_error("material index out of range");
-        const double* p = verts + 9 * i;
-        const D3 v0 = mk(p[0], p[1], p[2]), v1 = mk(p[3], p[4], p[5]), v2 = mk(p[6], p[7], p[8]);
-        const D3 e1 = v1 - v0, e2 = v2 - v0;
-        const D3 nn = cross(e1, e2);
-        const D3 un = unit(nn);                      // triangle.h:27 (NaN for degenerate triangles, as there)
-        TriGeom g;
-        g.v0x = v0.x; g.v0y = v0.y; g.v0z = v0.z; g.e1x = e1.x; g.e1y = e1.y; g.e1z = e1.z;
-        g.e2x = e2.x; g.e2y = e2.y; g.e2z = e2.z; g.mat = mat_id[i]; g.pad = 0;
-        out.tris[i] = g;
-        TriShade sh;
-        sh.nx = un.x; sh.ny = un.y; sh.nz = un.z; sh.mat = mat_id[i]; sh.pad = 0;
-        out.shade[i] = sh;
-        out.area[i] = 0.5 * len(nn);
-        double* b = &out.tri_box[6 * i];
-        b[0] = std::fmin(v0.x, std::fmin(v1.x, v2.x)); b[3] = std::fmax(v0.x, std::fmax(v1.x, v2.x));
-        b[1] = std::fmin(v0.y, std::fmin(v1.y, v2.y)); b[4] = std::fmax(v0.y, std::fmax(v1.y, v2.y));
-        b[2] = std::fmin(v0.z, std::fmin(v1.z, v2.z)); b[5] = std::fmax(v0.z, std::fmax(v1.z, v2.z));
-        if (out.mats[mat_id[i]].type == BDPT_MAT_LIGHT) out.lights.push_back(uint32_t(i));
+    // triangles are independent: flattened on a few threads (the light list, which is ordered, afterwards)
+    std::atomic<bool> bad_mat{false};
+    auto flatten_range = [&](uint64_t i0, uint64_t i1) {
+        for (uint64_t i = i0; i < i1; ++i) {
+            if (mat_id[i] >= n_mats) { bad_mat = true; return; }
+            const double* p = verts + 9 * i;
+            const D3 v0 = mk(p[0], p[1], p[2]), v1 = mk(p[3], p[4], p[5]), v2 = mk(p[6], p[7], p[8]);
+            const D3 e1 = v1 - v0, e2 = v2 - v0;
+            const D3 nn = cross(e1, e2);
+            const D3 un = unit(nn);                      // triangle.h:27 (NaN for degenerate triangles, as there)
+            TriGeom g;
+            g.v0x = v0.x; g.v0y = v0.y; g.v0z = v0.z; g.e1x = e1.x; g.e1y = e1.y; g.e1z = e1.z;
+            g.e2x = e2.x; g.e2y = e2.y; g.e2z = e2.z; g.mat = mat_id[i]; g.pad = 0;
+            out.tris[i] = g;
+            TriShade sh;
+            sh.nx = un.x; sh.ny = un.y; sh.nz = un.z; sh.mat = mat_id[i]; sh.pad = 0;
+            out.shade[i] = sh;
+            out.area[i] = 0.5 * len(nn);
+            double* b = &out.tri_box[6 * i];
+            b[0] = std::fmin(v0.x, std::fmin(v1.x, v2.x)); b[3] = std::fmax(v0.x, std::fmax(v1.x, v2.x));
+            b[1] = std::fmin(v0.y, std::fmin(v1.y, v2.y)); b[4] = std::fmax(v0.y, std::fmax(v1.y, v2.y));
+            b[2] = std::fmin(v0.z, std::fmin(v1.z, v2.z)); b[5] = std::fmax(v0.z, std::fmax(v1.z, v2.z));
+        }
+    };
+    {
+        const unsigned nt = n < 65536 ? 1u : std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+        const uint64_t per = (n + nt - 1) / nt;
+        std::vector<std::thread> pool;
+        for (unsigned k = 1; k < nt; ++k) pool.emplace_back(flatten_range, std::min(n, k * per), std::min(n, (k + 1) * per));
+        flatten_range(0, std::min(n, per));
+        for (auto& th : pool) th.join();
     }
+    if (bad_mat) throw std::runtime_error("material index out of range");
+    for (uint64_t i = 0; i < n; ++i)
+        if (out.mats[mat_id[i]].type == BDPT_MAT_LIGHT) out.lights.push_back(uint32_t(i));
     if (out.lights.empty())  // main.cpp:67: no lights -> the whole world is the light list
         for (uint64_t i = 0; i < n; ++i) out.lights.push_back(uint32_t(i));
     out.light_area.resize(out.lights.size());
@@ -169,7 +186,13 @@ void build_ref_bvh(HostScene& s) {
     NodeCount nc;
     s.ref_nodes.assign(nc(n), RefNode());
     b.counts = nc.memo;
+    const bool timing = std::getenv("BDPT_TIMING") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (timing) std::fprintf(stderr, "  reference tree: %s at %.1f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    };
     b.build(0, n, 0, 0, 4);   // up to 16 subtrees in flight
+    lap("nodes built");
     s.ref_depth = b.max_depth.load() + 1;
     s.dfs_rank.resize(n);
     for (size_t k = 0; k < n; ++k) s.dfs_rank[s.leaf_order[k]] = uint32_t(k);
@@ -185,22 +208,35 @@ void build_ref_bvh(HostScene& s) {
     // is the tightest of the chain's, and IEEE rounding is monotone), so traversal can accept "the reference
     // reaches this triangle" with one box test; a failure proves nothing (child boxes are not nested in
     // their parents where pad_to_minimums, aabb.h:81-88, widened a thin child) and falls back to the chain.
-    std::vector<double> acc(6 * s.ref_nodes.size());
+    lap("rank and parent tables");
     s.chain_box.assign(6 * n, 0.0);
-    for (size_t i = 0; i < s.ref_nodes.size(); ++i) {
-        const RefNode& nd = s.ref_nodes[i];
-        double* a = &acc[6 * i];
-        a[0] = nd.lo_x; a[1] = nd.hi_x; a[2] = nd.lo_y; a[3] = nd.hi_y; a[4] = nd.lo_z; a[5] = nd.hi_z;
-        const int32_t p = s.ref_parent[i];
-        if (p >= 0) {
-            const double* q = &acc[6 * size_t(p)];
-            for (int k = 0; k < 6; k += 2) { a[k] = std::fmax(a[k], q[k]); a[k + 1] = std::fmin(a[k + 1], q[k + 1]); }
+    struct Chain {
+        HostScene& s;
+        bool fork;
+        // node i under the running intersection `up` of its ancestors' boxes; the right subtrees of the first
+        // four levels go to their own threads
+        void go(int32_t i, const double* up, int depth) {
+            const RefNode& nd = s.ref_nodes[size_t(i)];
+            double a[6] = {nd.lo_x, nd.hi_x, nd.lo_y, nd.hi_y, nd.lo_z, nd.hi_z};
+            if (up)
+                for (int k = 0; k < 6; k += 2) { a[k] = std::fmax(a[k], up[k]); a[k + 1] = std::fmin(a[k + 1], up[k + 1]); }
+            if (nd.leaf) {
+                std::copy(a, a + 6, &s.chain_box[6 * size_t(nd.left)]);
+                std::copy(a, a + 6, &s.chain_box[6 * size_t(nd.right)]);
+                return;
+            }
+            if (fork && depth < 4) {
+                std::thread right([&] { go(nd.right, a, depth + 1); });
+                go(nd.left, a, depth + 1);
+                right.join();
+            } else {
+                go(nd.left, a, depth + 1);
+                go(nd.right, a, depth + 1);
+            }
         }
-        if (nd.leaf) {
-            std::copy(a, a + 6, &s.chain_box[6 * size_t(nd.left)]);
-            std::copy(a, a + 6, &s.chain_box[6 * size_t(nd.right)]);
-        }
-    }
+    };
+    Chain{s, n >= 65536}.go(0, nullptr, 0);
+    lap("chain boxes");
 }
 
 }  // namespace bdpt
