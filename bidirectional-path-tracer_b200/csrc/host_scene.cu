@@ -57,6 +57,37 @@ struct NodeCount {
     }
 };
 
+// std::sort with its top quicksort levels spread over threads.  It calls libstdc++'s own building blocks in the
+// order std::__sort does (bits/stl_algo.h: __introsort_loop = partition around the median-of-three pivot, recurse
+// into the right part, loop on the left; then one __final_insertion_sort over everything).  The two parts of a
+// partition are disjoint and sorted independently of each other, so handing the right part to another thread
+// changes nothing about the moves made: the permutation is exactly std::sort's, ties included.
+template <class It, class Cmp>
+void introsort_loop_forked(It first, It last, long depth_limit, Cmp comp, int forks) {
+    std::vector<std::thread> pool;
+    while (last - first > 16) {   // _S_threshold
+        if (depth_limit == 0) { std::__partial_sort(first, last, last, comp); break; }
+        --depth_limit;
+        It cut = std::__unguarded_partition_pivot(first, last, comp);
+        if (forks > 0 && last - cut > 4096) {
+            --forks;
+            pool.emplace_back([=] { introsort_loop_forked(cut, last, depth_limit, comp, forks); });
+        } else {
+            std::__introsort_loop(cut, last, depth_limit, comp);
+        }
+        last = cut;
+    }
+    for (auto& th : pool) th.join();
+}
+
+template <class It, class Less>
+void sort_like_std(It first, It last, Less less, int forks) {
+    if (first == last) return;
+    auto comp = __gnu_cxx::__ops::__iter_comp_iter(less);
+    introsort_loop_forked(first, last, long(std::__lg(last - first)) * 2, comp, forks);
+    std::__final_insertion_sort(first, last, comp);
+}
+
 struct RefBuilder {
     HostScene& s;
     std::vector<uint32_t>& order;
@@ -93,7 +124,9 @@ struct RefBuilder {
             struct KeyId { double key; uint32_t id; };
             std::vector<KeyId> tmp(span);
             for (size_t i = 0; i < span; ++i) { const uint32_t p = order[start + i]; tmp[i] = KeyId{tb[6 * size_t(p) + axis], p}; }
-            std::sort(tmp.begin(), tmp.end(), [](const KeyId& a, const KeyId& b) { return a.key < b.key; });
+            auto by_key = [](const KeyId& a, const KeyId& b) { return a.key < b.key; };
+            if (fork_levels > 0 && span > 32768) sort_like_std(tmp.begin(), tmp.end(), by_key, fork_levels);
+            else std::sort(tmp.begin(), tmp.end(), by_key);
             for (size_t i = 0; i < span; ++i) order[start + i] = tmp[i].id;
             const size_t mid = start + span / 2;
             const size_t left = me + 1, right = me + 1 + count(mid - start);   // preorder

@@ -68,3 +68,25 @@ def test_host_bvh_duplicate_keys_and_tiny_scenes(bdpt):
 def test_host_bvh_rejects_empty(bdpt):
     with pytest.raises(bdpt.BdptError):
         bdpt.host_bvh_build(np.zeros((0, 9)))
+
+
+def test_host_bvh_large_tied_scene_matches_the_reference_build(bdpt):
+    """Spans above 32768 triangles take the threaded sort (host_scene.cu, sort_like_std): its permutation must
+    be std::sort's, ties included.  Quantised coordinates give thousands of equal keys per axis; checked against
+    the reference's own bvh_node (oracle/_ref) and the single-threaded port."""
+    from oracle.oracle import Oracle
+    rng = np.random.default_rng(77)
+    n = 100000
+    c = np.round(rng.uniform(-8, 8, (n, 1, 3)) * 4) / 4                    # centres on a 0.25 grid: massive ties
+    v = (c + np.round(rng.uniform(-0.5, 0.5, (n, 3, 3)) * 8) / 8).reshape(n, 9)
+    mats = [(0, (0.5, 0.5, 0.5), 0.0)]
+    order, n_ref, _ = bdpt.host_bvh_build(v, fast=False)
+    for kind in ("ref", "port"):
+        try:
+            o = Oracle(kind).load(v, np.zeros(n, np.uint32), mats)
+        except Exception:
+            if kind == "ref":
+                continue   # the reference build is absent on this box
+            raise
+        assert n_ref == o.node_count()
+        assert np.array_equal(order, o.leaf_order()), kind
