@@ -44,7 +44,6 @@ struct Walk {
     double best, band_abs;
     // answer so far
     HitD hit;
-    uint32_t best_rank;
     bool found, flagged;
     // walk position
     int sp;
@@ -70,7 +69,6 @@ struct Walk {
         best = r.tmax;
         best_t = fminf(__double2float_ru(best), cull_hi);
         work = 0;
-        best_rank = 0;
         found = false; flagged = false;
         sp = 0; cur = 0; pend = 0;
         n_edge = 0;
@@ -177,12 +175,13 @@ __device__ __forceinline__ bool Walk<ANY, STATS>::leaf_tests(const SceneView& sc
         } else {
             if (found && fabs(t - best) <= band) flagged = true;   // tie with the current best
             if (edge) flagged = true;
+            // t == best (the reference's DFS order decides) cannot be settled here and need not be: an exact
+            // tie is inside the band above, so the ray is flagged and re-traced through the reference tree
             if (r.tmin <= t && t <= best) {
-                const uint32_t rank = __ldg(sc.dfs_rank + prim);
-                if (!found || t < best || rank > best_rank) {
-                    best = t; best_rank = rank; found = true;
+                if (!found || t < best) {
+                    best = t; found = true;
                     best_t = fminf(__double2float_ru(best), cull_hi);
-                    hit.t = t; hit.u = u; hit.v = v; hit.prim = prim;
+                    hit.u = u; hit.v = v; hit.prim = prim;   // hit.t: `best`, copied by finish()
                 }
             }
         }
@@ -268,6 +267,7 @@ __device__ __forceinline__ int Walk<ANY, STATS>::finish(const SceneView& sc) {
             return found ? TR_HIT : TR_MISS;
         }
     } else if (!flagged) {
+        hit.t = best;
         return found ? TR_HIT : TR_MISS;
     }
     return TR_DEFER;
