@@ -1,6 +1,9 @@
 // YAML + OBJ scene front-end: behaviour of the reference's src/scene/scene_loader.h (schema in SURVEY
 // Appendix B), written against yaml_lite instead of yaml-cpp.  Not on the timed path.
 #include <algorithm>
+#include <array>
+#include <charconv>
+#include <future>
 #include <cstring>
 #include <filesystem>
 #include <fstream>
@@ -165,13 +168,35 @@ void load_indexed_mesh(const node& mesh, sink& out, const material_map& mats) { 
 }
 
 // OBJ: 'v' and 'f' lines only, 1-based and negative indices, fan triangulation (scene_loader.h:346-397).
-// Tokenised by hand (the reference's istringstream-per-line parse is the slow part at 10^7 faces).
-void load_obj_file(const std::filesystem::path& path, const shared_ptr<material>& mat, sink& out) {
+// Tokenised by hand with std::from_chars (correctly rounded like the reference's stream extraction, a third of
+// strtod's cost): the reference's istringstream-per-line parse is the slow part at 10^7 faces.
+// A file is parsed into a plain vertex-triple list so that the files of a scene can be read side by side.
+using tri_points = std::array<point3, 3>;
+
+// strtod's contract on [p, eol): skips blanks, returns false when no number starts there
+inline bool parse_double(const char*& p, const char* eol, double& out) {
+    while (p < eol && (*p == ' ' || *p == '\t')) ++p;
+    const char* q = p;
+    if (q < eol && *q == '+') ++q;
+    const auto r = std::from_chars(q, eol, out);
+    if (r.ec == std::errc()) { p = r.ptr; return true; }
+    if (r.ec == std::errc::result_out_of_range || (q < eol && (*q == 'i' || *q == 'I' || *q == 'n' || *q == 'N'))) {
+        // overflow / underflow / inf / nan spellings: leave those to strtod (the line is NUL- or newline-terminated)
+        char* e;
+        out = std::strtod(p, &e);
+        if (e != p && e <= eol) { p = e; return true; }
+    }
+    return false;
+}
+
+std::vector<tri_points> parse_obj_file(const std::filesystem::path& path) {
     std::ifstream in(path, std::ios::binary);
     if (!in) throw std::runtime_error("Failed to open OBJ file: " + path.string());
     std::string buf((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
     std::vector<point3> verts;
-    verts.reserve(1024);
+    verts.reserve(buf.size() / 64);
+    std::vector<tri_points> tris;
+    tris.reserve(buf.size() / 48);
     std::vector<int> fidx;
     const char* p = buf.c_str();
     const char* end = p + buf.size();
@@ -182,34 +207,44 @@ void load_obj_file(const std::filesystem::path& path, const shared_ptr<material>
         while (q < eol && (*q == ' ' || *q == '\t')) ++q;
         const bool sep = q + 1 < eol && (q[1] == ' ' || q[1] == '\t');
         if (q < eol && *q == 'v' && sep) {
-            char* e1; char* e2; char* e3;
-            const double x = std::strtod(q + 1, &e1);
-            const double y = (e1 != q + 1 && e1 < eol) ? std::strtod(e1, &e2) : (e2 = e1, 0.0);
-            const double z = (e2 != e1 && e2 < eol) ? std::strtod(e2, &e3) : (e3 = e2, 0.0);
-            if (e1 != q + 1 && e2 != e1 && e3 != e2 && e3 <= eol) verts.emplace_back(x, y, z);
+            const char* t = q + 1;
+            double x, y, z;
+            if (parse_double(t, eol, x) && parse_double(t, eol, y) && parse_double(t, eol, z)) verts.emplace_back(x, y, z);
         } else if (q < eol && *q == 'f' && sep) {
             fidx.clear();
             const char* t = q + 1;
             while (t < eol) {
                 while (t < eol && (*t == ' ' || *t == '\t' || *t == '\r')) ++t;
                 if (t >= eol) break;
-                char* e;
-                const long vi = std::strtol(t, &e, 10);     // "vi", "vi/vt", "vi/vt/vn", "vi//vn": leading int
-                if (e != t) fidx.push_back(vi > 0 ? int(vi - 1) : int(verts.size()) + int(vi));
-                t = e != t ? e : t + 1;
+                long vi = 0;                                  // "vi", "vi/vt", "vi/vt/vn", "vi//vn": leading int
+                const char* d = (*t == '+') ? t + 1 : t;
+                const auto r = std::from_chars(d, eol, vi);
+                if (r.ec == std::errc()) { fidx.push_back(vi > 0 ? int(vi - 1) : int(verts.size()) + int(vi)); t = r.ptr; }
+                else ++t;
                 while (t < eol && *t != ' ' && *t != '\t') ++t;   // skip the /vt/vn tail
             }
             for (size_t k = 2; k < fidx.size(); ++k)
-                out.add(verts.at(size_t(fidx[0])), verts.at(size_t(fidx[k - 1])), verts.at(size_t(fidx[k])), mat);
+                tris.push_back(tri_points{verts.at(size_t(fidx[0])), verts.at(size_t(fidx[k - 1])), verts.at(size_t(fidx[k]))});
         }
         p = eol + 1;
     }
+    return tris;
 }
 
-void load_object(const node& n, const std::filesystem::path& dir, sink& out, const material_map& mats) {   // :399-425
+using obj_jobs = std::unordered_map<const node*, std::future<std::vector<tri_points>>>;
+
+std::filesystem::path object_path(const node& n, const std::filesystem::path& dir) {
     const std::string rel = to_string(n["file"]);
     if (rel.empty()) throw std::runtime_error("Object missing file field");
-    load_obj_file(dir / rel, resolve_material(n["material"], mats), out);
+    return dir / rel;
+}
+
+void load_object(const node& n, const std::filesystem::path& dir, sink& out, const material_map& mats, obj_jobs& jobs) {   // :399-425
+    const std::filesystem::path path = object_path(n, dir);
+    auto it = jobs.find(&n);
+    const std::vector<tri_points> tris = it != jobs.end() ? it->second.get() : parse_obj_file(path);   // get() rethrows the parse error here, in scene order
+    const auto mat = resolve_material(n["material"], mats);
+    for (const tri_points& t : tris) out.add(t[0], t[1], t[2], mat);
 }
 
 void load_camera(const node& n, camera& cam) {                       // scene_loader.h:427-476
@@ -249,6 +284,11 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
     if (!surfaces->is_sequence()) throw std::runtime_error("Scene/surfaces field missing or not a sequence");
     const std::filesystem::path dir = std::filesystem::path(path).parent_path();
     sink out{result.world, result.lights};
+    // OBJ files are read and tokenised concurrently; their triangles still enter the world in scene order
+    obj_jobs jobs;
+    for (const auto& mesh : surfaces->seq)
+        if (mesh.is_map() && to_string(mesh["type"]) == "object" && !to_string(mesh["file"]).empty())
+            jobs.emplace(&mesh, std::async(std::launch::async, parse_obj_file, object_path(mesh, dir)));
     for (const auto& mesh : surfaces->seq) {
         if (!mesh.is_map()) throw std::runtime_error("Scene entries must be mappings");
         const std::string type = to_string(mesh["type"]);
@@ -256,7 +296,7 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
         if (type == "TriMesh") load_tri_mesh(mesh, out);
         else if (type == "Sphere") load_sphere(mesh, out);
         else if (type == "mesh") load_indexed_mesh(mesh, out, mats);
-        else if (type == "object") load_object(mesh, dir, out, mats);
+        else if (type == "object") load_object(mesh, dir, out, mats, jobs);
         else std::cerr << "Unknown mesh type: " << type << "\n";
     }
     std::cout << "Triangles: " << result.world.size() << "\n";
