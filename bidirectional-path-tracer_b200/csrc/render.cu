@@ -876,6 +876,14 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
         return;
     }
     const uint32_t n = q.cnt[SQ_LIVE];
+    {
+        // Few segments survive k_shadow_pre, and their walks differ by two orders of magnitude in length: if every
+        // resident warp took 32 of them at once, nothing would be left to refill the lanes that finish early and
+        // each warp would idle behind its longest ray.  Only as many warps stay as leave `over` rounds of refills.
+        const uint32_t over = (uint32_t(threshold) >> 16) & 0xFFu;
+        const uint32_t warp_id = ((blockIdx.x - n_slow_blocks) * kBlock + threadIdx.x) >> 5;
+        if (over > 1u && uint64_t(warp_id) * 32u * over >= n) return;
+    }
     Walk<true, STATS> W;
     bool have = false, exhausted = false;
     int result = WALK_YIELD;
@@ -1344,6 +1352,10 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     int slice = 4, min_idle = 8;    // walk time slice (leaf visits) and idle lanes that trigger a refill
 #endif
     int t_leaf = 16, t_walk = 8;    // lock-step walk: postponed leaves that start the triangle tests / walkers below which they start anyway
+#if !BDPT_WIDE_WALK
+    t_leaf = 1;                     // per-lane walk: these bits hold the shadow kernel's refill rounds instead (k_shadow_fast; 1 = off: 2 and 4 measured within noise, 8 slower)
+    if (const char* e = std::getenv("BDPT_SHADOW_OVER")) t_leaf = std::atoi(e);
+#endif
     if (const char* e = std::getenv("BDPT_WALK_SLICE")) slice = std::atoi(e);
     if (const char* e = std::getenv("BDPT_MIN_IDLE")) min_idle = std::atoi(e);
     if (const char* e = std::getenv("BDPT_T_LEAF")) t_leaf = std::atoi(e);
