@@ -131,6 +131,37 @@ __device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
     return base + uint32_t(__popc(mask & ((1u << lane) - 1u)));
 }
 
+// one atomic per block of NT threads: every thread of the block must call this.  The streaming kernels
+// (generate, shade) append from every warp to the same counter; ncu showed them waiting on that one address
+// (29 % of k_generate's stall samples on the warp leaders' atomicAdd), so their warps pool their counts first.
+constexpr int kWide = 256;
+template <int NT>
+__device__ __forceinline__ uint32_t block_append(uint32_t* counter, bool pred) {
+    __shared__ uint32_t s_off[NT / 32];
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, pred);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) s_off[wid] = uint32_t(__popc(mask));
+    __syncthreads();
+    if (wid == 0) {
+        const uint32_t c = lane < NT / 32 ? s_off[lane] : 0u;
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < NT / 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, NT / 32 - 1);
+        uint32_t base = 0;
+        if (lane == 0 && total) base = atomicAdd(counter, total);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (lane < NT / 32) s_off[lane] = base + incl - c;
+    }
+    __syncthreads();
+    const uint32_t r = s_off[wid] + uint32_t(__popc(mask & ((1u << lane) - 1u)));
+    __syncthreads();   // s_off is free again for the next call
+    return r;
+}
+
 __device__ __forceinline__ void film_add(double* film, uint32_t pix, D3 c) {
     atomicAdd(film + 3 * size_t(pix), c.x);
     atomicAdd(film + 3 * size_t(pix) + 1, c.y);
@@ -166,6 +197,15 @@ __device__ __forceinline__ void retire(const WF& w, bool ended, uint32_t b, int 
     if (last) w.q_slots[dn][slot] = b;
 }
 
+// the same for kernels that append per block (every thread of the block must call it)
+template <int NT>
+__device__ __forceinline__ void retire_block(const WF& w, bool ended, uint32_t b, int dn) {
+    bool last = false;
+    if (ended) last = atomicSub(&w.live[b], 1u) == 1u;
+    const uint32_t slot = block_append<NT>(w.counters + C_DONE0 + dn, last);
+    if (last) w.q_slots[dn][slot] = b;
+}
+
 // linear sample index of this call -> pixel, stratum and the global sample id that keys the RNG
 struct SampleId { int i, j, s_i, s_j; uint32_t pix; uint64_t sid; };
 __device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
@@ -185,9 +225,9 @@ __device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
 // Fills `ngen` free slots (free_list, or slots 0..ngen-1 on a worker's first iteration) with samples
 // gen_base .. gen_base+ngen-1 of this call; consecutive threads take consecutive samples = neighbouring
 // pixels, so the primary rays of a refill are coherent.
-__global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ free_list,
-                                                    int64_t gen_base, int64_t ngen, int cur, int dn) {
-    const int64_t gi = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+__global__ void __launch_bounds__(kWide) k_generate(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ free_list,
+                                                   int64_t gen_base, int64_t ngen, int cur, int dn) {
+    const int64_t gi = int64_t(blockIdx.x) * kWide + threadIdx.x;
     const bool valid = gi < ngen;
     bool cam_live = false, light_live = false;
     int64_t b = 0;
@@ -249,12 +289,12 @@ __global__ void __launch_bounds__(kBlock) k_generate(SceneView sc, Frame f, WF w
         w.nlight[b] = nl;
         w.live[b] = uint32_t(cam_live) + uint32_t(light_live);
     }
-    uint32_t slot = warp_append(w.counters + C_ACTIVE0 + cur, cam_live);
+    uint32_t slot = block_append<kWide>(w.counters + C_ACTIVE0 + cur, cam_live);
     if (cam_live) w.q_active[cur][slot] = uint32_t(b);
-    slot = warp_append(w.counters + C_ACTIVE0 + cur, light_live);
+    slot = block_append<kWide>(w.counters + C_ACTIVE0 + cur, light_live);
     if (light_live) w.q_active[cur][slot] = uint32_t(w.B + b);
     const bool dead = valid && !cam_live && !light_live;   // nothing to trace: straight to the done list
-    slot = warp_append(w.counters + C_DONE0 + dn, dead);
+    slot = block_append<kWide>(w.counters + C_DONE0 + dn, dead);
     if (dead) w.q_slots[dn][slot] = uint32_t(b);
 }
 
@@ -621,11 +661,8 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
 // Thread idx walks the concatenation light | lambertian | metal | dielectric of the queues k_trace_* filled, so
 // a warp straddles at most one class boundary; the survivors' queue append and the retirement of ended
 // subpaths are shared.
-#ifndef SHADE_BLOCKS
-#define SHADE_BLOCKS 12
-#endif
-__global__ void __launch_bounds__(kBlock, SHADE_BLOCKS) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
-    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+__global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
+    const uint32_t idx = blockIdx.x * kWide + threadIdx.x;
     const uint32_t n_li = w.counters[C_MAT0 + BDPT_MAT_LIGHT], n_la = w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN],
                    n_me = w.counters[C_MAT0 + BDPT_MAT_METAL], n_di = w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
     const bool valid = idx < n_li + n_la + n_me + n_di;
@@ -637,9 +674,9 @@ __global__ void __launch_bounds__(kBlock, SHADE_BLOCKS) k_shade(SceneView sc, Fr
         else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal(sc, f, w, pid); }
         else { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric(sc, f, w, pid); }
     }
-    const uint32_t slot = warp_append(w.counters + C_ACTIVE0 + nxt, live);
+    const uint32_t slot = block_append<kWide>(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
-    retire(w, valid && !live, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+    retire_block<kWide>(w, valid && !live, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
 }
 
 // ------------------------------------------------------------------ vertex-count reduction over the done list
@@ -1149,7 +1186,7 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT0 + ex, 0, sizeof(uint32_t), st));
         if (ngen > 0) {
             tm.begin(KT_GENERATE, st);
-            k_generate<<<grid_for(ngen, kBlock), kBlock, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
+            k_generate<<<grid_for(ngen, kWide), kWide, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
             tm.end(KT_GENERATE, st);
             wk.launches += 1;
             wk.samples += uint64_t(ngen);
@@ -1168,8 +1205,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
 #undef BDPT_TP
         tm.end(KT_TRACE, st);
         tm.begin(KT_SHADE, st);
-        const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kBlock);   // the lagged rays of the front blocks are shaded too
-        k_shade<<<gsh, kBlock, 0, st>>>(sc, f, wf, nxt, dn, J.film);
+        const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kWide);   // the lagged rays of the front blocks are shaded too
+        k_shade<<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film);
         k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
         tm.end(KT_SHADE, st);
         wk.launches += 3;
