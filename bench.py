@@ -241,30 +241,40 @@ def run_ours(args):
     value = samples / (total_ms * 1e3)
 
     # ---------------- end-to-end through host buffers: upload (BVH build + H2D) + K steps + film D2H
-    ctx2 = pkg.Context(local)
+    # Three passes, each with a fresh context; the MEDIAN pass is reported (all three are kept in the line): a
+    # sporadic 20-80 ms stall inside a driver call (cudaMalloc of the 46 GB workspace, the first H2D of a new
+    # context) otherwise decides a 250 ms measurement.
     film_buf = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64, pin_memory=True).numpy()   # the caller's frame buffer, pinned
-    sync_all()
-    t0 = time.perf_counter()
-    ctx2.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
-    t_up = time.perf_counter()
-    ctx2.film_clear(WIDTH, HEIGHT)
-    for s in range(K):
-        ctx2.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
-    t_rd = time.perf_counter()
-    if dist:
-        p2, n2_ = ctx2.film_device_ptr()
-        dist.reduce(torch.as_tensor(CudaArray(p2, n2_), device=torch.device("cuda", local)), dst=0)
-    film_host = ctx2.film(out=film_buf)
-    sync_all()
-    t_end = time.perf_counter()
-    e2e_parts = {"scene_upload_ms": (t_up - t0) * 1e3, "render_ms": (t_rd - t_up) * 1e3, "film_reduce_and_readback_ms": (t_end - t_rd) * 1e3}
-    e2e_s = torch.tensor([t_end - t0], dtype=torch.float64, device="cuda")
-    if dist:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = samples / float(e2e_s[0]) / 1e6
+    passes = []
+    for _ in range(3):
+        ctx2 = pkg.Context(local)
+        sync_all()
+        t0 = time.perf_counter()
+        ctx2.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
+        t_up = time.perf_counter()
+        ctx2.film_clear(WIDTH, HEIGHT)
+        per_call = []
+        for s in range(K):
+            tc = time.perf_counter()
+            ctx2.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
+            per_call.append(round((time.perf_counter() - tc) * 1e3, 2))
+        t_rd = time.perf_counter()
+        if dist:
+            p2, n2_ = ctx2.film_device_ptr()
+            dist.reduce(torch.as_tensor(CudaArray(p2, n2_), device=torch.device("cuda", local)), dst=0)
+        film_host = ctx2.film(out=film_buf)
+        sync_all()
+        t_end = time.perf_counter()
+        e2e_s = torch.tensor([t_end - t0], dtype=torch.float64, device="cuda")
+        if dist:
+            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        passes.append({"seconds_max_over_ranks": float(e2e_s[0]), "scene_upload_ms": (t_up - t0) * 1e3, "render_ms": (t_rd - t_up) * 1e3,
+                       "film_reduce_and_readback_ms": (t_end - t_rd) * 1e3, "render_calls_ms": per_call})
+        ctx2.close()
+    e2e_parts = sorted(passes, key=lambda p: p["seconds_max_over_ranks"])[1]
+    e2e_value = samples / e2e_parts["seconds_max_over_ranks"] / 1e6
     h2d = sf.verts.nbytes + sf.mat_id.nbytes
     d2h = film_host.nbytes
-    ctx2.close()
 
     extra = {}
     if rank == 0:
@@ -275,8 +285,9 @@ def run_ours(args):
                 "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic", "config": dict(workload_config(), bvh=args.bvh, fast_tree="device, Morton order" if args.gpu_tree else "host, binned SAH"),
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
-                        "rank0_ms": e2e_parts,
-                        "note": "scene upload from host buffers (host BVH build + H2D) + K steps + film read-back into a pinned host frame buffer"},
+                        "rank0_ms": e2e_parts, "all_passes_msamples_per_s": [samples / p["seconds_max_over_ranks"] / 1e6 for p in passes],
+                        "note": "scene upload from host buffers (host BVH build + H2D) + K steps + film read-back into a pinned host frame buffer; "
+                                "median of three passes, each on a fresh context"},
                 "gpu_launches": st["kernel_launches"], "clocks": clocks, "wall_ms_per_step": wall_ms / K,
                 "film_reduce_ms": red_ms,
                 "mrays_per_s": (st["rays_closest"] + st["rays_shadow"]) * world / (total_ms * 1e3),

@@ -135,6 +135,7 @@ __device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
 // (generate, shade) append from every warp to the same counter; ncu showed them waiting on that one address
 // (29 % of k_generate's stall samples on the warp leaders' atomicAdd), so their warps pool their counts first.
 constexpr int kWide = 256;
+constexpr int kGen = 128;    // k_generate: 84 registers, 5 blocks of 128 stay resident where 2 of 256 would
 template <int NT>
 __device__ __forceinline__ uint32_t block_append(uint32_t* counter, bool pred) {
     __shared__ uint32_t s_off[NT / 32];
@@ -225,9 +226,9 @@ __device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
 // Fills `ngen` free slots (free_list, or slots 0..ngen-1 on a worker's first iteration) with samples
 // gen_base .. gen_base+ngen-1 of this call; consecutive threads take consecutive samples = neighbouring
 // pixels, so the primary rays of a refill are coherent.
-__global__ void __launch_bounds__(kWide) k_generate(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ free_list,
+__global__ void __launch_bounds__(kGen) k_generate(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ free_list,
                                                    int64_t gen_base, int64_t ngen, int cur, int dn) {
-    const int64_t gi = int64_t(blockIdx.x) * kWide + threadIdx.x;
+    const int64_t gi = int64_t(blockIdx.x) * kGen + threadIdx.x;
     const bool valid = gi < ngen;
     bool cam_live = false, light_live = false;
     int64_t b = 0;
@@ -289,12 +290,12 @@ __global__ void __launch_bounds__(kWide) k_generate(SceneView sc, Frame f, WF w,
         w.nlight[b] = nl;
         w.live[b] = uint32_t(cam_live) + uint32_t(light_live);
     }
-    uint32_t slot = block_append<kWide>(w.counters + C_ACTIVE0 + cur, cam_live);
+    uint32_t slot = block_append<kGen>(w.counters + C_ACTIVE0 + cur, cam_live);
     if (cam_live) w.q_active[cur][slot] = uint32_t(b);
-    slot = block_append<kWide>(w.counters + C_ACTIVE0 + cur, light_live);
+    slot = block_append<kGen>(w.counters + C_ACTIVE0 + cur, light_live);
     if (light_live) w.q_active[cur][slot] = uint32_t(w.B + b);
     const bool dead = valid && !cam_live && !light_live;   // nothing to trace: straight to the done list
-    slot = block_append<kWide>(w.counters + C_DONE0 + dn, dead);
+    slot = block_append<kGen>(w.counters + C_DONE0 + dn, dead);
     if (dead) w.q_slots[dn][slot] = uint32_t(b);
 }
 
@@ -1186,7 +1187,7 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT0 + ex, 0, sizeof(uint32_t), st));
         if (ngen > 0) {
             tm.begin(KT_GENERATE, st);
-            k_generate<<<grid_for(ngen, kWide), kWide, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
+            k_generate<<<grid_for(ngen, kGen), kGen, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
             tm.end(KT_GENERATE, st);
             wk.launches += 1;
             wk.samples += uint64_t(ngen);
