@@ -29,6 +29,9 @@ EXPORTS = [
     "bdpt_stats_reset", "bdpt_last_device_ms", "bdpt_sync", "bdpt_kernel_times",
     "bdpt_scene_file_load", "bdpt_scene_file_free", "bdpt_scene_file_info", "bdpt_scene_file_copy",
     "bdpt_write_png", "bdpt_host_last_error",
+    "bdpt_scene_image_build", "bdpt_scene_image_free", "bdpt_scene_image_info", "bdpt_scene_image_last_error",
+    "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
+    "bdpt_scene_source_key", "bdpt_scene_file_open_cached",
 ]
 
 
@@ -56,6 +59,13 @@ class Stats(C.Structure):
                                           "max_work_shadow", "deferred_closest", "deferred_shadow")]
 
 
+class SceneImageInfo(C.Structure):
+    _fields_ = [("n_tris", C.c_uint64), ("n_ref_nodes", C.c_uint64), ("n_fast_nodes", C.c_uint64), ("n_mats", C.c_uint32),
+                ("n_lights", C.c_uint32), ("ref_depth", C.c_uint32), ("fast_depth", C.c_uint32), ("source_key", C.c_uint64),
+                ("payload_hash", C.c_uint64), ("device_bytes", C.c_uint64)]
+
+
+IMAGE_VERIFY = 1
 RENDER_STATS = 1
 RENDER_SERIAL = 2
 UPLOAD_FAST_TREE_GPU = 1
@@ -113,6 +123,20 @@ def lib():
         L.bdpt_scene_file_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.bdpt_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
         L.bdpt_host_last_error.restype = C.c_char_p
+        L.bdpt_scene_image_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint64,
+                                             C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        L.bdpt_scene_image_free.argtypes = [C.c_void_p]
+        L.bdpt_scene_image_free.restype = None
+        L.bdpt_scene_image_info.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+        L.bdpt_scene_image_last_error.restype = C.c_char_p
+        L.bdpt_scene_upload_image.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]
+        L.bdpt_scene_image_save.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64]
+        L.bdpt_scene_image_map.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        L.bdpt_scene_image_unmap.argtypes = [C.c_void_p, C.c_uint64]
+        L.bdpt_scene_image_unmap.restype = None
+        L.bdpt_scene_source_key.argtypes = [C.c_char_p, C.POINTER(C.c_uint64)]
+        L.bdpt_scene_file_open_cached.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                                  C.POINTER(C.c_uint64), C.POINTER(C.c_int)]
         _lib = L
     return _lib
 
@@ -157,6 +181,106 @@ def host_bvh_build(verts, fast=False):
     if rc:
         raise BdptError("bdpt_host_bvh_build failed: %d %s" % (rc, lib().bdpt_last_error(None).decode()))
     return order, nr.value, (nf.value if fast else None)
+
+
+class SceneImage:
+    """A scene image (include/bdpt.h): flattened soup + both BVHs as one block in the kernels' layout.
+    Built on the host (`SceneImage.build`), read from a file (`SceneImage.map`) or wrapped around caller bytes
+    (`SceneImage.from_bytes`, e.g. a pinned buffer); uploaded with Context.upload_image."""
+
+    def __init__(self, ptr, nbytes, kind, keep=None):
+        self.ptr, self.nbytes, self._kind, self._keep = ptr, int(nbytes), kind, keep
+
+    @classmethod
+    def build(cls, verts, mat_id, mats, source_key=0):
+        v = np.ascontiguousarray(verts, dtype=np.float64).reshape(-1, 9)
+        m = np.ascontiguousarray(mat_id, dtype=np.uint32)
+        if len(m) != len(v):
+            raise ValueError("mat_id length")
+        marr = make_materials(mats) if isinstance(mats, list) else mats
+        p, n = C.c_void_p(), C.c_uint64(0)
+        rc = lib().bdpt_scene_image_build(v.ctypes.data if len(v) else None, m.ctypes.data if len(v) else None, len(v), C.byref(marr),
+                                          len(marr), int(source_key), C.byref(p), C.byref(n))
+        if rc:
+            raise BdptError("bdpt_scene_image_build failed (%d): %s" % (rc, lib().bdpt_scene_image_last_error().decode()))
+        return cls(p.value, n.value, "built")
+
+    @classmethod
+    def map(cls, path):
+        p, n = C.c_void_p(), C.c_uint64(0)
+        if lib().bdpt_scene_image_map(os.fsencode(path), C.byref(p), C.byref(n)):
+            raise BdptError(lib().bdpt_host_last_error().decode())
+        return cls(p.value, n.value, "mapped")
+
+    @classmethod
+    def from_bytes(cls, arr):
+        a = np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
+        return cls(a.ctypes.data, a.nbytes, "borrowed", keep=a)
+
+    def info(self, verify=False):
+        i = SceneImageInfo()
+        if lib().bdpt_scene_image_info(C.c_void_p(self.ptr), self.nbytes, 1 if verify else 0, C.byref(i)):
+            raise BdptError(lib().bdpt_scene_image_last_error().decode())
+        return {n: int(getattr(i, n)) for n, _ in SceneImageInfo._fields_}
+
+    def bytes(self):
+        """A numpy copy of the image bytes."""
+        return np.ctypeslib.as_array(C.cast(C.c_void_p(self.ptr), C.POINTER(C.c_uint8)), shape=(self.nbytes,)).copy()
+
+    def save(self, path):
+        if lib().bdpt_scene_image_save(os.fsencode(path), C.c_void_p(self.ptr), self.nbytes):
+            raise BdptError(lib().bdpt_host_last_error().decode())
+
+    def close(self):
+        if self._kind == "built" and self.ptr:
+            lib().bdpt_scene_image_free(C.c_void_p(self.ptr))
+        elif self._kind == "mapped" and self.ptr:
+            lib().bdpt_scene_image_unmap(C.c_void_p(self.ptr), self.nbytes)
+        self.ptr, self._keep = None, None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def scene_source_key(yaml_path):
+    k = C.c_uint64(0)
+    if lib().bdpt_scene_source_key(os.fsencode(yaml_path), C.byref(k)):
+        raise BdptError(lib().bdpt_host_last_error().decode())
+    return k.value
+
+
+class CachedSceneFile:
+    """bdpt_scene_file_open_cached: camera + scene image of a YAML scene, from `cache_path` when its key matches the
+    sources (`hit`), else loaded, built and written there."""
+
+    def __init__(self, yaml_path, cache_path):
+        self._h = C.c_void_p()
+        p, n, hit = C.c_void_p(), C.c_uint64(0), C.c_int(0)
+        if lib().bdpt_scene_file_open_cached(os.fsencode(yaml_path), os.fsencode(cache_path), C.byref(self._h), C.byref(p), C.byref(n),
+                                             C.byref(hit)):
+            raise BdptError("Failed to load scene: " + lib().bdpt_host_last_error().decode())
+        self.hit = bool(hit.value)
+        self.image = SceneImage(p.value, n.value, "borrowed", keep=self)
+        nt, nm, nl = C.c_uint64(0), C.c_uint32(0), C.c_uint64(0)
+        self.camera = Camera()
+        name = C.create_string_buffer(512)
+        lib().bdpt_scene_file_info(self._h, C.byref(nt), C.byref(nm), C.byref(nl), C.byref(self.camera), name, 512)
+        self.n_tris, self.n_mats, self.n_lights, self.output = nt.value, nm.value, nl.value, name.value.decode()
+
+    def close(self):
+        if self._h:
+            self.image.ptr = None
+            lib().bdpt_scene_file_free(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
 
 
 class SceneFile:
@@ -243,6 +367,13 @@ class Context:
         self._chk(lib().bdpt_scene_upload_ex(self._h, v.ctypes.data, m.ctypes.data, len(v), C.byref(marr), len(marr),
                                              UPLOAD_FAST_TREE_GPU if gpu_tree else 0), "bdpt_scene_upload")
         self.n_tris = len(v)
+        return self
+
+    def upload_image(self, image, verify=False):
+        """bdpt_scene_upload_image: one allocation + one host-to-device copy of a prebuilt SceneImage."""
+        self._chk(lib().bdpt_scene_upload_image(self._h, C.c_void_p(image.ptr), image.nbytes, IMAGE_VERIFY if verify else 0),
+                  "bdpt_scene_upload_image")
+        self.n_tris = image.info()["n_tris"]
         return self
 
     def bvh_info(self, bvh=BVH_REFERENCE):

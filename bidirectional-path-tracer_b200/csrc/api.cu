@@ -278,7 +278,7 @@ int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth
     if (!ctx) return BDPT_ERR_ARG;
     if (!ctx->have_scene) { ctx->err = "no scene uploaded"; return BDPT_ERR_STATE; }
     if (bvh == BDPT_BVH_REFERENCE) {
-        if (n_nodes) *n_nodes = ctx->host.ref_nodes.size();
+        if (n_nodes) *n_nodes = ctx->view.n_ref_nodes;
         if (max_depth) *max_depth = ctx->host.ref_depth;
     } else if (bvh == BDPT_BVH_FAST) {
         if (n_nodes) *n_nodes = ctx->view.n_fast_nodes;

@@ -25,8 +25,9 @@ void camera::render(const hittable& world, const hittable& lights) {
     if (auto b = dynamic_cast<const bvh_node*>(&world)) prims = &b->prims;
     else if (auto t = dynamic_cast<const triangle_collection*>(&world)) prims = &t->tris;
     if (!prims) throw std::runtime_error("camera::render: world must be a bvh_node or a triangle_collection");
+    const bool from_image = options.scene_image != nullptr;
     std::vector<double> verts; std::vector<uint32_t> mat_id; std::vector<bdpt_material> mats;
-    flatten_triangles(*prims, verts, mat_id, mats);
+    if (!from_image) flatten_triangles(*prims, verts, mat_id, mats);
 
     bdpt_camera c{};
     c.aspect_ratio = aspect_ratio; c.image_width = image_width; c.samples_per_pixel = samples_per_pixel;
@@ -46,7 +47,8 @@ void camera::render(const hittable& world, const hittable& lights) {
         try {
             guard ctx;
             if (bdpt_ctx_create(g, &ctx.c)) throw std::runtime_error(std::string("bdpt_ctx_create: ") + bdpt_last_error(nullptr));
-            check(bdpt_scene_upload(ctx.c, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx.c, "bdpt_scene_upload");
+            if (from_image) check(bdpt_scene_upload_image(ctx.c, options.scene_image, options.scene_image_bytes, 0), ctx.c, "bdpt_scene_upload_image");
+            else check(bdpt_scene_upload(ctx.c, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx.c, "bdpt_scene_upload");
             check(bdpt_film_clear(ctx.c, W, H), ctx.c, "bdpt_film_clear");
             bdpt_render_opts o{};
             o.seed = options.seed; o.stratum_begin = g; o.stratum_step = G; o.bvh = options.bvh;

@@ -7,11 +7,27 @@
 
 int main(int argc, char** argv) {
     if (argc < 2) {
-        std::cerr << "usage: bdpt scene.yaml [--res WxH] [--spp N] [--depth N] [--gpus N] [--bvh ref|fast] [--seed S] [--out name.png]\n";
+        std::cerr << "usage: bdpt scene.yaml [--res WxH] [--spp N] [--depth N] [--gpus N] [--bvh ref|fast] [--seed S] [--out name.png] [--cache file.bdptimg]\n";
         return 2;
     }
+    // --cache FILE: keep the scene image (flattened soup + both BVHs) beside the scene; a later run whose YAML and
+    // OBJ files are unchanged maps it and skips OBJ parsing, flattening and the tree builds
+    const char* cache = nullptr;
+    for (int i = 2; i + 1 < argc; ++i) if (!std::strcmp(argv[i], "--cache")) cache = argv[i + 1];
+    bdpt_scene_file* cached = nullptr;
+    struct closer { bdpt_scene_file*& f; ~closer() { if (f) bdpt_scene_file_free(f); } } close_cached{cached};
     try {
-        auto scene = load_scene_from_yaml(argv[1]);
+        scene_load_result scene;
+        if (cache) {
+            const void* image = nullptr;
+            uint64_t bytes = 0;
+            int hit = 0;
+            if (bdpt_scene_file_open_cached(argv[1], cache, &cached, &image, &bytes, &hit)) throw std::runtime_error(bdpt_host_last_error());
+            scene.cam = load_camera_from_yaml(argv[1]);
+            scene.cam.options.scene_image = image;
+            scene.cam.options.scene_image_bytes = bytes;
+            std::clog << "Scene image " << cache << (hit ? ": cache hit, " : ": built and written, ") << bytes / 1e6 << " MB\n";
+        } else scene = load_scene_from_yaml(argv[1]);
         for (int i = 2; i < argc; ++i) {
             auto next = [&](const char* flag) -> const char* {
                 if (i + 1 >= argc) throw std::runtime_error(std::string("missing value for ") + flag);
@@ -26,6 +42,7 @@ int main(int argc, char** argv) {
             else if (!std::strcmp(argv[i], "--gpus")) scene.cam.options.gpus = std::atoi(next("--gpus"));
             else if (!std::strcmp(argv[i], "--seed")) scene.cam.options.seed = std::strtoull(next("--seed"), nullptr, 0);
             else if (!std::strcmp(argv[i], "--out")) scene.cam.file_name = next("--out");
+            else if (!std::strcmp(argv[i], "--cache")) next("--cache");
             else if (!std::strcmp(argv[i], "--bvh")) scene.cam.options.bvh = std::strcmp(next("--bvh"), "ref") ? BDPT_BVH_FAST : BDPT_BVH_REFERENCE;
             else throw std::runtime_error(std::string("unknown flag ") + argv[i]);
         }

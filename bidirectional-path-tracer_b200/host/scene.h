@@ -117,6 +117,10 @@ struct render_options {         // overrides the CLI adds on top of the YAML (SU
     uint64_t seed = 0;
     bool quiet = false;
     bool write_file = true;     // write ./output/<file_name> like camera.h:139-142
+    // a prebuilt scene image (include/bdpt.h, bdpt_scene_image_build / _map): when set, render() uploads it instead
+    // of flattening `world` and building the trees, and `world` may be empty
+    const void* scene_image = nullptr;
+    uint64_t scene_image_bytes = 0;
 };
 
 struct render_report {
@@ -158,6 +162,10 @@ struct scene_load_result {      // scene_loader.h:22-26
 };
 
 scene_load_result load_scene_from_yaml(const std::string& path);   // scene_loader.h:480-523
+// Scene-image cache support (include/bdpt.h; not in the reference): the camera section alone, and a
+// key over the bytes of the YAML and of every OBJ file its `object` surfaces name, in scene order.
+camera load_camera_from_yaml(const std::string& path);
+uint64_t scene_source_key(const std::string& path);
 
 // image output, wpng.h:14-89
 void colors_to_rgb8(const std::vector<color>& framebuffer, int image_width, int image_height, int samples_per_pixel,

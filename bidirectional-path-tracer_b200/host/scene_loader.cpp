@@ -303,6 +303,56 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
     return result;
 }
 
+camera load_camera_from_yaml(const std::string& path) {
+    const node root = yaml_lite::load_file(path);
+    if (!root.is_map()) throw std::runtime_error("Scene root must be a mapping");
+    camera cam;
+    load_camera(root["camera"], cam);
+    return cam;
+}
+
+namespace {
+// word-wise multiply-xor mix (not cryptographic): detects edited, replaced or truncated source files
+uint64_t mix_bytes(uint64_t h, const char* p, size_t n) {
+    h ^= n * 0x9E3779B97F4A7C15ull;
+    uint64_t lane[4] = {h, h ^ 0xC2B2AE3D27D4EB4Full, h ^ 0x165667B19E3779F9ull, h ^ 0x27D4EB2F165667C5ull};
+    size_t i = 0;
+    for (; i + 32 <= n; i += 32) {
+        uint64_t w[4];
+        std::memcpy(w, p + i, 32);
+        for (int k = 0; k < 4; ++k) { lane[k] = (lane[k] ^ w[k]) * 0x100000001B3ull; lane[k] = (lane[k] << 29) | (lane[k] >> 35); }
+    }
+    for (; i < n; ++i) { lane[0] = (lane[0] ^ uint64_t(static_cast<unsigned char>(p[i]))) * 0x100000001B3ull; lane[0] = (lane[0] << 29) | (lane[0] >> 35); }
+    uint64_t r = n;
+    for (int k = 0; k < 4; ++k) { r = (r ^ lane[k]) * 0xFF51AFD7ED558CCDull; r ^= r >> 33; }
+    return r;
+}
+std::string slurp(const std::filesystem::path& path) {
+    std::ifstream in(path, std::ios::binary);
+    if (!in) throw std::runtime_error("Failed to open file: " + path.string());
+    return std::string((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+}
+}  // namespace
+
+uint64_t scene_source_key(const std::string& path) {
+    const std::string yaml = slurp(path);
+    uint64_t key = mix_bytes(0x42445054ull, yaml.data(), yaml.size());
+    const node root = yaml_lite::load_file(path);
+    if (!root.is_map()) throw std::runtime_error("Scene root must be a mapping");
+    const node* surfaces = &root["surfaces"];
+    if (!surfaces->defined()) surfaces = &root["scene"];
+    if (!surfaces->is_sequence()) throw std::runtime_error("Scene/surfaces field missing or not a sequence");
+    const std::filesystem::path dir = std::filesystem::path(path).parent_path();
+    std::vector<std::future<uint64_t>> jobs;
+    for (const auto& mesh : surfaces->seq)
+        if (mesh.is_map() && to_string(mesh["type"]) == "object" && !to_string(mesh["file"]).empty()) {
+            const std::filesystem::path obj = object_path(mesh, dir);
+            jobs.push_back(std::async(std::launch::async, [obj] { const std::string b = slurp(obj); return mix_bytes(1, b.data(), b.size()); }));
+        }
+    for (auto& j : jobs) { const uint64_t h = j.get(); key = mix_bytes(key, reinterpret_cast<const char*>(&h), sizeof h); }
+    return key ? key : 1;   // 0 means "no key" in an image header
+}
+
 void flatten_triangles(const std::vector<triangle>& tris, std::vector<double>& verts, std::vector<uint32_t>& mat_id,
                        std::vector<bdpt_material>& mats) {
     verts.resize(tris.size() * 9);

@@ -135,6 +135,31 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
 int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                          const bdpt_material* mats, uint32_t n_mats, uint32_t flags);
 int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth);
+
+/* ---- scene image: everything bdpt_scene_upload derives from the soup -- the flattened triangle
+ * records, the light list, the reference-topology tree (bvh.h:13-48) with its tie-rule side tables and the
+ * binned-SAH tree -- as ONE relocatable block in the kernels' own layout.  Build it once (host only, no CUDA
+ * device needed), keep it in memory or in a file, upload it with one allocation and one host-to-device copy:
+ * the reference rebuilds its BVH on every run (main.cpp:66).  Rendering from an image is bit-identical to
+ * rendering from bdpt_scene_upload of the same soup.  The image is tied to this library's record layouts
+ * (a mismatch is refused) and is not portable across endianness. */
+typedef struct {
+    uint64_t n_tris, n_ref_nodes, n_fast_nodes;
+    uint32_t n_mats, n_lights, ref_depth, fast_depth;
+    uint64_t source_key;     /* as passed to bdpt_scene_image_build */
+    uint64_t payload_hash;
+    uint64_t device_bytes;   /* what bdpt_scene_upload_image copies to the device */
+} bdpt_scene_image_info_t;
+/* *image is allocated by the library (4096-byte aligned); release with bdpt_scene_image_free. */
+int  bdpt_scene_image_build(const double* verts, const uint32_t* mat_id, uint64_t n_tris, const bdpt_material* mats,
+                            uint32_t n_mats, uint64_t source_key, void** image, uint64_t* bytes);
+void bdpt_scene_image_free(void* image);
+/* Header / section-table checks (always) and the payload hash (verify != 0); out may be NULL. */
+int  bdpt_scene_image_info(const void* image, uint64_t bytes, int verify, bdpt_scene_image_info_t* out);
+const char* bdpt_scene_image_last_error(void);
+#define BDPT_IMAGE_VERIFY 1u   /* check the payload hash before copying (one pass over the image on the host) */
+/* image: host memory, 8-byte aligned (pinned memory makes the copy faster); may be freed on return. */
+int  bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, uint32_t flags);
 /* DFS leaf order of the BDPT_BVH_REFERENCE build: order[k] = prim ID (n_tris entries) */
 int bdpt_bvh_leaf_order(bdpt_ctx* ctx, uint32_t* order);
 
@@ -179,6 +204,21 @@ int  bdpt_scene_file_info(const bdpt_scene_file* f, uint64_t* n_tris, uint32_t* 
 /* copies the flattened soup: verts n_tris*9, mat_id n_tris, mats n_mats (any may be NULL) */
 int  bdpt_scene_file_copy(const bdpt_scene_file* f, double* verts, uint32_t* mat_id, bdpt_material* mats);
 int  bdpt_write_png(const char* path, const uint8_t* rgb, int width, int height);
+/* Scene-image files: save writes to "<path>.tmp" and renames; map gives a read-only mapping of the file
+ * (page cache backed: nothing is copied until the upload reads it). */
+int  bdpt_scene_image_save(const char* path, const void* image, uint64_t bytes);
+int  bdpt_scene_image_map(const char* path, const void** image, uint64_t* bytes);
+void bdpt_scene_image_unmap(const void* image, uint64_t bytes);
+/* Key of a YAML scene's sources: a hash of the YAML bytes and of every OBJ file its `object` surfaces name, in
+ * scene order -- what bdpt_scene_file_open_cached compares with an image's source_key. */
+int  bdpt_scene_source_key(const char* yaml_path, uint64_t* key);
+/* load_scene_from_yaml with a scene-image cache beside it: when cache_path holds an image whose source_key
+ * matches, only the YAML is parsed (camera, output name) and the image is mapped -- no OBJ parsing, no
+ * flattening, no BVH build; otherwise the scene is loaded and flattened as bdpt_scene_file_load does, the
+ * image is built and written to cache_path.  *hit = 1 when the cache was used.  The image stays valid until
+ * bdpt_scene_file_free; bdpt_scene_file_copy on a cache hit fails (there is no soup). */
+int  bdpt_scene_file_open_cached(const char* yaml_path, const char* cache_path, bdpt_scene_file** out,
+                                 const void** image, uint64_t* image_bytes, int* hit);
 const char* bdpt_host_last_error(void);
 
 #ifdef __cplusplus
