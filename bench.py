@@ -55,35 +55,72 @@ def measured_peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md clocks line), read through NVML in
+    this process (nvidia_ml_py) every 10 ms; one `nvidia-smi` child per sample only if NVML cannot be loaded.  Under
+    torchrun only rank 0 samples: eight ranks each forking nvidia-smi (which enumerates every GPU of the box) stalled
+    kernel launches in the driver and cost the 8-GPU run 15 % of its step time."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = [0x8, 0x40, 0x20, 0x4]   # nvmlClocksEventReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
 
-    def __init__(self, index):
+    def __init__(self, index, enabled=True):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.index, self.rows, self._stop_evt, self.enabled = index, [], threading.Event(), enabled
+        self.nvml, self.handle, self.max_mhz, self.source = None, None, None, "nvidia-smi"
+        if not enabled:
+            return
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = int(vis.split(",")[index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml, self.source = pynvml, "nvml"
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n = self.nvml
+        mhz = int(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+        try:
+            mask = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+        except Exception:
+            mask = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+        self.rows.append((mhz, mask))
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+        parts = [x.strip() for x in out.strip().split(",")]
+        if len(parts) >= 6 and parts[0].isdigit():
+            mask = sum(b for k, b in enumerate(self.BITS) if parts[2 + k].lower().startswith("active"))
+            self.rows.append((int(parts[0]), mask))
+            if parts[1].isdigit():
+                self.max_mhz = int(parts[1])
+
+    def start(self):
+        if self.enabled:
+            super().start()
 
     def run(self):
         while not self._stop_evt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                parts = [x.strip() for x in out.strip().split(",")]
-                if len(parts) >= 6:
-                    self.rows.append(parts)
+                self._sample_nvml() if self.nvml else self._sample_smi()
             except Exception:
                 pass
-            self._stop_evt.wait(0.05)
+            self._stop_evt.wait(0.01 if self.nvml else 0.05)
 
     def stop(self):
+        if not self.enabled:
+            return None
         self._stop_evt.set()
         self.join(timeout=6)
-        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
-                "sm_max_mhz": int(self.rows[0][1]) if self.rows and self.rows[0][1].isdigit() else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        sm = sorted(r[0] for r in self.rows)
+        reasons = [n for n, b in zip(self.NAMES, self.BITS) if any(r[1] & b for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": reasons, "samples": len(self.rows), "source": self.source}
 
 
 def emit(line):
@@ -212,7 +249,7 @@ def run_ours(args):
         dist.reduce(film_t, dst=0)   # warm NCCL up too
     ctx.film_clear(WIDTH, HEIGHT)
     ctx.stats_reset()
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, enabled=(rank == 0))
     sync_all()
     sampler.start()
     t0 = time.perf_counter()
