@@ -21,6 +21,7 @@ std::string g_create_err;
 
 constexpr int kTraceBlock = 64;
 
+
 template <class T>
 int upload(bdpt_ctx* ctx, const std::vector<T>& h, const T** d) {
     void* p = nullptr;
@@ -40,12 +41,12 @@ void free_scene(bdpt_ctx* ctx) {
 
 // ---------------------------------------------------------------- batch kernels
 // hittable::hit over a ray batch (hittable.h:33, bvh.h:50-59)
-template <int BVH, bool ANY, bool STATS>
+template <int BVH, bool ANY, bool STATS, bool WIDE = false>
 __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_trace(SceneView sc, const bdpt_ray* __restrict__ rays, uint64_t n,
                                                       bdpt_hit* __restrict__ out, unsigned long long* stats) {
     // stack in local memory (as in the render kernels): 48 int32 levels for the reference tree = 24 StackEntry;
     // 32 StackEntry cover the fast tree (depth <= 23)
-    StackEntry l_stack[32];
+    StackEntry l_stack[WIDE ? kWideStackLevels : 32];
     const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
     TravStats st{0, 0};
     if (i < n) {
@@ -61,7 +62,7 @@ __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_trace(Scene
         else if (walk_eligible(sc, r)) {   // the render kernels' walk (fp32 FMA slabs); a tie goes to the reference tree
             Walk<ANY, STATS> W;
             W.init(sc, r);
-            const int rc = W.run(sc, l_stack, 0);
+            const int rc = WIDE ? W.run4(sc, l_stack, 0) : W.run(sc, l_stack, 0);
             if (STATS) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; }
             h = W.hit;
             found = rc == TR_DEFER ? traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st) : rc == TR_HIT;
@@ -237,6 +238,8 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
             t_fast = ms_since(t_b);
         } else if (!rc && !fast_err) {
             rc = upload(ctx, h.fast_nodes, &v.fast_nodes);
+            if (!rc) rc = upload(ctx, h.wide_nodes, &v.wide_nodes);
+            v.n_wide_nodes = uint32_t(h.wide_nodes.size());
             if (!rc) rc = upload(ctx, h.fast_prims, &v.fast_prims);
             if (!rc) rc = upload(ctx, h.fast_tris, &v.fast_tris);
             v.n_fast_nodes = uint32_t(h.fast_nodes.size());
@@ -254,6 +257,8 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
     if (!rc) rc = upload(ctx, h.ref_parent, &v.ref_parent);
     if (!rc) rc = upload(ctx, h.prim_leaf, &v.prim_leaf);
     if (!rc) rc = upload(ctx, h.chain_box, &v.chain_box);
+    v.use_wide = (!gpu_tree && 3u * h.wide_depth + 2u <= uint32_t(kWideStackLevels)) ? bdpt::wide_walk_mode() : 0u;
+    if (timing) std::fprintf(stderr, "bdpt_scene_upload: 4-wide tree: %zu nodes, depth %u, walk mode %u\n", h.wide_nodes.size(), h.wide_depth, v.use_wide);
     if (!rc && (h.ref_depth >= uint32_t(kRefStackLevels) || h.fast_depth + 2 > 32u)) {   // 64 int32 / 32 StackEntry slots of local stack
         ctx->err = "BVH deeper than the traversal stack";
         rc = BDPT_ERR_ARG;
@@ -331,6 +336,11 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
     if (bvh == BDPT_BVH_REFERENCE) {
         if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, false); }
         else     { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, false); }
+    } else if ((v.use_wide & (any ? 2u : 1u)) && v.wide_nodes) {
+#define BDPT_LAUNCH_W(A, S) k_trace<BDPT_BVH_FAST, A, S, true><<<grid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out, st)
+        if (any) { if (stats) BDPT_LAUNCH_W(true, true); else BDPT_LAUNCH_W(true, false); }
+        else     { if (stats) BDPT_LAUNCH_W(false, true); else BDPT_LAUNCH_W(false, false); }
+#undef BDPT_LAUNCH_W
     } else {
         if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_FAST, true, true); else BDPT_LAUNCH(BDPT_BVH_FAST, true, false); }
         else     { if (stats) BDPT_LAUNCH(BDPT_BVH_FAST, false, true); else BDPT_LAUNCH(BDPT_BVH_FAST, false, false); }

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -51,6 +52,13 @@ enum { ST_NODE = 0, ST_TRI = 1, ST_RAYS_CLOSEST = 2, ST_RAYS_SHADOW = 3, ST_CAM_
        ST_NODE_CLOSEST = 6, ST_TRI_CLOSEST = 7, ST_NODE_SHADOW = 8, ST_TRI_SHADOW = 9, ST_MAX_CLOSEST = 10, ST_MAX_SHADOW = 11, ST_DEFER_CLOSEST = 12, ST_DEFER_SHADOW = 13 };
 // kernel classes of the wavefront (bdpt_kernel_times)
 enum { KT_GENERATE = 0, KT_TRACE = 1, KT_SHADE = 2, KT_CONNECT = 3, KT_SHADOW = 4, KT_TRACE_EXACT = 5, KT_SHADOW_EXACT = 6, KT_COUNT = 7 };
+
+// bdpt_trace walks the 4-wide nodes: bit 0 = closest-hit queries (default on), bit 1 = any-hit queries (default off:
+// measured equal).  BDPT_WIDE overrides (0 = binary walk everywhere).
+inline uint32_t wide_walk_mode() {
+    const char* e = std::getenv("BDPT_WIDE");
+    return e ? uint32_t(std::atoi(e)) & 3u : 1u;
+}
 
 int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts);
 void render_free(bdpt_ctx* ctx);

@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <deque>
 #include <thread>
 #include <vector>
@@ -330,6 +331,67 @@ void build_fast_bvh(HostScene& s) {
     par_chunks(0, n, n_threads, [&](uint32_t cb, uint32_t ce, unsigned) {
         for (uint32_t k = cb; k < ce; ++k) s.fast_tris[k] = s.tris[s.fast_prims[k]];
     });
+    collapse_wide(s);
+    lap("collapsed to 4-wide");
+}
+
+// Binary -> 4-wide: a wide node starts from a binary node's two children and, while it has a free slot, replaces
+// the internal child of largest surface area by that child's two children.  Boxes are copied, never recomputed,
+// so the wide tree is exactly as conservative as the binary one; leaves are the same leaf codes.
+void collapse_wide(HostScene& s) {
+    struct Slot { int32_t link; float lo[3], hi[3]; };
+    auto slots_of = [&](int32_t b, Slot out[2]) {
+        const FastNode& nd = s.fast_nodes[size_t(b)];
+        out[0].link = nd.left; out[1].link = nd.right;
+        for (int k = 0; k < 3; ++k) { out[0].lo[k] = nd.l_lo[k]; out[0].hi[k] = nd.l_hi[k]; out[1].lo[k] = nd.r_lo[k]; out[1].hi[k] = nd.r_hi[k]; }
+    };
+    auto area = [](const Slot& c) {
+        const double dx = double(c.hi[0]) - c.lo[0], dy = double(c.hi[1]) - c.lo[1], dz = double(c.hi[2]) - c.lo[2];
+        return dx * dy + dy * dz + dz * dx;
+    };
+    struct Item { int32_t bin, wide; uint32_t depth; };
+    s.wide_nodes.clear();
+    s.wide_nodes.reserve(s.fast_nodes.size() / 2 + 4);
+    s.wide_nodes.push_back(WideNode());
+    std::vector<Item> todo{Item{0, 0, 1}};
+    uint32_t max_depth = 1;
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        max_depth = std::max(max_depth, it.depth);
+        Slot c[4];
+        int n = 2;
+        slots_of(it.bin, c);
+        while (n < 4) {
+            int best = -1;
+            double best_area = -1.0;
+            for (int k = 0; k < n; ++k)
+                if (c[k].link >= 0 && area(c[k]) > best_area) { best_area = area(c[k]); best = k; }
+            if (best < 0) break;
+            Slot two[2];
+            slots_of(c[best].link, two);
+            c[best] = two[0];
+            c[n++] = two[1];
+        }
+        WideNode w;
+        std::memset(&w, 0, sizeof w);
+        int32_t kids[4];
+        for (int k = 0; k < 4; ++k) {
+            if (k < n) {
+                w.lo_x[k] = c[k].lo[0]; w.lo_y[k] = c[k].lo[1]; w.lo_z[k] = c[k].lo[2];
+                w.hi_x[k] = c[k].hi[0]; w.hi_y[k] = c[k].hi[1]; w.hi_z[k] = c[k].hi[2];
+                if (c[k].link >= 0) {
+                    kids[k] = int32_t(s.wide_nodes.size());
+                    s.wide_nodes.push_back(WideNode());
+                    w.child[k] = kids[k];
+                } else { kids[k] = -1; w.child[k] = c[k].link; }
+            } else { kids[k] = -1; w.child[k] = kWideEmpty; }
+        }
+        s.wide_nodes[size_t(it.wide)] = w;
+        for (int k = n - 1; k >= 0; --k)
+            if (kids[k] >= 0) todo.push_back(Item{c[k].link, kids[k], it.depth + 1});
+    }
+    s.wide_depth = max_depth;
 }
 
 }  // namespace bdpt

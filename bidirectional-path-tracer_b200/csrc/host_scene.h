@@ -32,6 +32,8 @@ struct HostScene {
     std::vector<uint32_t> fast_prims;
     std::vector<TriGeom> fast_tris;    // tris[fast_prims[k]]: a leaf's triangles are contiguous, no id indirection on the walk
     uint32_t fast_depth = 0;
+    std::vector<WideNode> wide_nodes;  // the fast tree collapsed to 4-wide nodes (same leaves)
+    uint32_t wide_depth = 0;
     double extent = 0.0;               // largest side of the scene bounds
     double center[3] = {0, 0, 0};
 
@@ -44,6 +46,7 @@ void flatten_scene(const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                    uint32_t n_mats, HostScene& out);
 void build_ref_bvh(HostScene& s);
 void build_fast_bvh(HostScene& s);
+void collapse_wide(HostScene& s);   // fast_nodes -> wide_nodes
 void scene_bounds(HostScene& s, double lo[3], double hi[3]);
 
 }  // namespace bdpt

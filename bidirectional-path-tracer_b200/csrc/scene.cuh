@@ -54,7 +54,23 @@ struct __align__(16) FastNode {
 };
 static_assert(sizeof(FastNode) == 64, "FastNode must be 64 bytes");
 
+// ---- 4-wide form of the fast BVH (collapsed from the binary tree, fast_bvh.cu): the walk of a ray is a chain of
+// dependent node fetches, and a 4-wide node halves the length of that chain.  128 B = 8 x 16-byte loads, boxes
+// plane-major so one load brings the same plane of all four children.  child: >= 0 wide node index, < 0 leaf
+// code as in FastNode, kWideEmpty: no child in this slot.
+constexpr int32_t kWideEmpty = INT32_MIN;
+constexpr int kWideStackLevels = 64;   // 4-wide walk: up to three deferred children per level (depth <= 20)
+struct __align__(16) WideNode {
+    float lo_x[4], lo_y[4], lo_z[4], hi_x[4], hi_y[4], hi_z[4];
+    int32_t child[4];
+    uint32_t pad[4];
+};
+static_assert(sizeof(WideNode) == 128, "WideNode must be 128 bytes");
+
 struct SceneView {
+    const WideNode* wide_nodes;   // may be null (device-built tree): the binary walk is used
+    uint32_t n_wide_nodes;
+    uint32_t use_wide;
     const RefNode* ref_nodes;
     const FastNode* fast_nodes;
     const uint32_t* fast_prims;   // leaf-ordered prim IDs for the fast BVH

@@ -20,13 +20,13 @@ using namespace bdpt;
 namespace {
 
 enum Section {
-    SEC_TRIS = 0, SEC_SHADE, SEC_MATS, SEC_LIGHTS, SEC_LIGHT_AREA, SEC_FAST_NODES, SEC_FAST_PRIMS, SEC_FAST_TRIS,
+    SEC_TRIS = 0, SEC_SHADE, SEC_MATS, SEC_LIGHTS, SEC_LIGHT_AREA, SEC_FAST_NODES, SEC_WIDE_NODES, SEC_FAST_PRIMS, SEC_FAST_TRIS,
     SEC_REF_NODES, SEC_DFS_RANK, SEC_REF_PARENT, SEC_PRIM_LEAF, SEC_CHAIN_BOX,
     SEC_LEAF_ORDER,   // host only (bdpt_bvh_leaf_order): last, so the device copy stops before it
     SEC_COUNT
 };
 
-constexpr uint32_t kVersion = 1;
+constexpr uint32_t kVersion = 2;   // 2: + the 4-wide nodes
 constexpr uint64_t kAlign = 256;
 constexpr char kMagic[8] = {'B', 'D', 'P', 'T', 'I', 'M', 'G', '1'};
 
@@ -37,16 +37,17 @@ struct ImageHeader {
     uint64_t payload_hash;     // image_hash over [header_bytes, total_bytes)
     uint64_t source_key;       // the caller's key of what the image was built from (0 = none)
     uint64_t layout_sig;       // record sizes this library was compiled with
-    uint32_t n_tris, n_mats, n_lights, n_ref_nodes, n_fast_nodes, ref_depth, fast_depth, reserved;
+    uint32_t n_tris, n_mats, n_lights, n_ref_nodes, n_fast_nodes, ref_depth, fast_depth, n_wide_nodes;
+    uint32_t wide_depth, reserved;
     double light_total_area, extent, center[3];
     struct { uint64_t off, bytes; } sec[SEC_COUNT];
-    unsigned char pad[512 - (8 + 8 + 8 * 4 + 4 * 8 + 8 * 5 + 16 * SEC_COUNT)];
+    unsigned char pad[512 - (8 + 8 + 8 * 4 + 4 * 10 + 8 * 5 + 16 * SEC_COUNT)];
 };
 static_assert(sizeof(ImageHeader) == 512, "ImageHeader must be 512 bytes");
 
 constexpr uint64_t layout_sig() {
     return uint64_t(sizeof(RefNode)) | uint64_t(sizeof(FastNode)) << 8 | uint64_t(sizeof(TriGeom)) << 16 |
-           uint64_t(sizeof(TriShade)) << 24 | uint64_t(sizeof(Mat)) << 32 | uint64_t(SEC_COUNT) << 40 | uint64_t(kVersion) << 48;
+           uint64_t(sizeof(TriShade)) << 24 | uint64_t(sizeof(Mat)) << 32 | uint64_t(sizeof(WideNode) & 0xFF) << 56 | uint64_t(SEC_COUNT) << 40 | uint64_t(kVersion) << 48;
 }
 
 // Four independent multiply-xor lanes over 64-bit words (the payload is a multiple of 256 bytes): a few GB/s
@@ -84,6 +85,7 @@ void expected_bytes(const ImageHeader& h, uint64_t out[SEC_COUNT]) {
     out[SEC_LIGHTS] = uint64_t(h.n_lights) * sizeof(uint32_t);
     out[SEC_LIGHT_AREA] = uint64_t(h.n_lights) * sizeof(double);
     out[SEC_FAST_NODES] = uint64_t(h.n_fast_nodes) * sizeof(FastNode);
+    out[SEC_WIDE_NODES] = uint64_t(h.n_wide_nodes) * sizeof(WideNode);
     out[SEC_FAST_PRIMS] = n * sizeof(uint32_t);
     out[SEC_FAST_TRIS] = n * sizeof(TriGeom);
     out[SEC_REF_NODES] = uint64_t(h.n_ref_nodes) * sizeof(RefNode);
@@ -103,7 +105,7 @@ const ImageHeader* check_image(const void* image, uint64_t bytes, bool verify, s
     if (h->version != kVersion || h->header_bytes != sizeof(ImageHeader)) { why = "scene image: unknown version"; return nullptr; }
     if (h->layout_sig != layout_sig()) { why = "scene image: built by a library with different record layouts"; return nullptr; }
     if (h->total_bytes != bytes) { why = "scene image: truncated (header says " + std::to_string(h->total_bytes) + " bytes, got " + std::to_string(bytes) + ")"; return nullptr; }
-    if (h->n_tris == 0 || h->n_mats == 0 || h->n_lights == 0 || h->n_ref_nodes == 0 || h->n_fast_nodes == 0) { why = "scene image: empty scene"; return nullptr; }
+    if (h->n_tris == 0 || h->n_mats == 0 || h->n_lights == 0 || h->n_ref_nodes == 0 || h->n_fast_nodes == 0 || h->n_wide_nodes == 0) { why = "scene image: empty scene"; return nullptr; }
     uint64_t want[SEC_COUNT];
     expected_bytes(*h, want);
     uint64_t at = sizeof(ImageHeader);
@@ -153,6 +155,7 @@ int bdpt_scene_image_build(const double* verts, const uint32_t* mat_id, uint64_t
         h.n_tris = uint32_t(hs.tris.size()); h.n_mats = uint32_t(hs.mats.size()); h.n_lights = uint32_t(hs.lights.size());
         h.n_ref_nodes = uint32_t(hs.ref_nodes.size()); h.n_fast_nodes = uint32_t(hs.fast_nodes.size());
         h.ref_depth = hs.ref_depth; h.fast_depth = hs.fast_depth;
+        h.n_wide_nodes = uint32_t(hs.wide_nodes.size()); h.wide_depth = hs.wide_depth;
         h.light_total_area = hs.light_total_area; h.extent = hs.extent;
         for (int k = 0; k < 3; ++k) h.center[k] = hs.center[k];
         uint64_t want[SEC_COUNT];
@@ -169,7 +172,7 @@ int bdpt_scene_image_build(const double* verts, const uint32_t* mat_id, uint64_t
         try {
             put(base, h, SEC_TRIS, hs.tris); put(base, h, SEC_SHADE, hs.shade); put(base, h, SEC_MATS, hs.mats);
             put(base, h, SEC_LIGHTS, hs.lights); put(base, h, SEC_LIGHT_AREA, hs.light_area);
-            put(base, h, SEC_FAST_NODES, hs.fast_nodes); put(base, h, SEC_FAST_PRIMS, hs.fast_prims); put(base, h, SEC_FAST_TRIS, hs.fast_tris);
+            put(base, h, SEC_FAST_NODES, hs.fast_nodes); put(base, h, SEC_WIDE_NODES, hs.wide_nodes); put(base, h, SEC_FAST_PRIMS, hs.fast_prims); put(base, h, SEC_FAST_TRIS, hs.fast_tris);
             put(base, h, SEC_REF_NODES, hs.ref_nodes); put(base, h, SEC_DFS_RANK, hs.dfs_rank); put(base, h, SEC_REF_PARENT, hs.ref_parent);
             put(base, h, SEC_PRIM_LEAF, hs.prim_leaf); put(base, h, SEC_CHAIN_BOX, hs.chain_box); put(base, h, SEC_LEAF_ORDER, hs.leaf_order);
         } catch (...) { std::free(base); throw; }
@@ -236,6 +239,9 @@ int bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, ui
     v.lights = reinterpret_cast<const uint32_t*>(at(SEC_LIGHTS));
     v.light_area = reinterpret_cast<const double*>(at(SEC_LIGHT_AREA));
     v.fast_nodes = reinterpret_cast<const FastNode*>(at(SEC_FAST_NODES));
+    v.wide_nodes = reinterpret_cast<const WideNode*>(at(SEC_WIDE_NODES));
+    v.n_wide_nodes = h->n_wide_nodes;
+    v.use_wide = 3u * h->wide_depth + 2u <= uint32_t(kWideStackLevels) ? wide_walk_mode() : 0u;
     v.fast_prims = reinterpret_cast<const uint32_t*>(at(SEC_FAST_PRIMS));
     v.fast_tris = reinterpret_cast<const TriGeom*>(at(SEC_FAST_TRIS));
     v.ref_nodes = reinterpret_cast<const RefNode*>(at(SEC_REF_NODES));
@@ -250,7 +256,7 @@ int bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, ui
     // what the other calls read from the host copy: the tree depths (workspace sizing) and the DFS leaf order
     HostScene& hs = ctx->host;
     hs = HostScene{};
-    hs.ref_depth = h->ref_depth; hs.fast_depth = h->fast_depth;
+    hs.ref_depth = h->ref_depth; hs.fast_depth = h->fast_depth; hs.wide_depth = h->wide_depth;
     hs.extent = h->extent; hs.light_total_area = h->light_total_area;
     for (int k = 0; k < 3; ++k) hs.center[k] = h->center[k];
     const uint32_t* lo = reinterpret_cast<const uint32_t*>(src + h->sec[SEC_LEAF_ORDER].off);

@@ -91,6 +91,8 @@ struct Walk {
     // brings the warp back together: __activemask() inside the walk only sees the lanes that happen to be
     // scheduled together, not the lanes that still have work.
     __device__ __forceinline__ int run(const SceneView& sc, StackEntry* stack, int rounds, uint32_t limit = 0);
+    // The same over the 4-wide nodes (sc.wide_nodes): same leaves, same candidates' tests, up to three pushes per node.
+    __device__ __forceinline__ int run4(const SceneView& sc, StackEntry* stack, int rounds, uint32_t limit = 0);
     // The same walk for a whole warp in lock step (all 32 lanes must call it; `busy` = this lane has a ray):
     // every trip each walking lane opens ONE node, a lane that reaches a leaf postpones its triangle tests and
     // keeps walking, and the tests run for all postponed leaves at once when at least `t_leaf` lanes have one
@@ -146,6 +148,58 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
         const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
         work += cnt;
         if (limit && work > limit) return TR_SLOW;   // nothing decided: the caller parks the ray for a split walk
+        if (leaf_tests(sc, first, cnt)) return TR_HIT;
+        if (!pop(stack)) return finish(sc);
+        if (--rounds == 0) return WALK_YIELD;
+    }
+}
+
+// compare-exchange of (entry distance, child) pairs: the smaller distance ends in a
+__device__ __forceinline__ void cswap(float& da, int32_t& ca, float& db, int32_t& cb) {
+    const bool sw = db < da;
+    const float d0 = sw ? db : da, d1 = sw ? da : db;
+    const int32_t c0 = sw ? cb : ca, c1 = sw ? ca : cb;
+    da = d0; db = d1; ca = c0; cb = c1;
+}
+
+template <bool ANY, bool STATS>
+__device__ __forceinline__ int Walk<ANY, STATS>::run4(const SceneView& sc, StackEntry* stack, int rounds, uint32_t limit) {
+    const float kMissT = 3.402823466e+38f;
+    for (;;) {
+        while (cur >= 0) {
+            const float4* q = reinterpret_cast<const float4*>(sc.wide_nodes + cur);
+            const float4 lx = __ldg(q), ly = __ldg(q + 1), lz = __ldg(q + 2), hx = __ldg(q + 3), hy = __ldg(q + 4), hz = __ldg(q + 5);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(q + 6));
+            if (STATS) ++ts.nodes;
+            ++work;
+            float d0, d1, d2, d3;
+            int32_t c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
+#define BDPT_WIDE_CHILD(D, C, LX, HX, LY, HY, LZ, HZ)                              \
+            {                                                                      \
+                float tn = tmin_t, tf = best_t;                                    \
+                slab_fma(LX, HX, ox, ix, tn, tf);                                  \
+                slab_fma(LY, HY, oy, iy, tn, tf);                                  \
+                slab_fma(LZ, HZ, oz, iz, tn, tf);                                  \
+                D = (tn <= tf && C != kWideEmpty) ? tn : kMissT;                   \
+            }
+            BDPT_WIDE_CHILD(d0, c0, lx.x, hx.x, ly.x, hy.x, lz.x, hz.x)
+            BDPT_WIDE_CHILD(d1, c1, lx.y, hx.y, ly.y, hy.y, lz.y, hz.y)
+            BDPT_WIDE_CHILD(d2, c2, lx.z, hx.z, ly.z, hy.z, lz.z, hz.z)
+            BDPT_WIDE_CHILD(d3, c3, lx.w, hx.w, ly.w, hy.w, lz.w, hz.w)
+#undef BDPT_WIDE_CHILD
+            // sort by entry distance (misses carry FLT_MAX and end up last)
+            cswap(d0, c0, d1, c1); cswap(d2, c2, d3, c3); cswap(d0, c0, d2, c2); cswap(d1, c1, d3, c3); cswap(d1, c1, d2, c2);
+            if (d0 == kMissT) { if (!pop(stack)) return finish(sc); continue; }
+            // nearest child next; the others wait on the stack, farthest pushed first
+            if (d3 != kMissT) { stack[sp] = pack_entry(c3, d3); ++sp; }
+            if (d2 != kMissT) { stack[sp] = pack_entry(c2, d2); ++sp; }
+            if (d1 != kMissT) { stack[sp] = pack_entry(c1, d1); ++sp; }
+            cur = c0;
+        }
+        const uint32_t code = uint32_t(~cur);
+        const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;
+        work += cnt;
+        if (limit && work > limit) return TR_SLOW;
         if (leaf_tests(sc, first, cnt)) return TR_HIT;
         if (!pop(stack)) return finish(sc);
         if (--rounds == 0) return WALK_YIELD;

@@ -45,6 +45,36 @@ def test_image_reference_topology_matches_golden(bdpt, scenes, golden):
             assert np.array_equal(tail, g["leaf_order"])
 
 
+def image_sections(raw):
+    """{index: bytes} from the image's section table (header: 128 bytes of fields, then {offset, bytes} pairs)."""
+    n_sec = 15
+    table = raw[128:128 + 16 * n_sec].view(np.uint64).reshape(n_sec, 2)
+    return [raw[int(o):int(o) + int(b)] for o, b in table]
+
+
+def test_wide_tree_is_the_binary_tree_collapsed(bdpt, scenes):
+    """The 4-wide nodes (fast_bvh.cu: collapse_wide) must hold exactly the binary fast tree's leaves, each once, under
+    copied (never shrunk) boxes, with every wide node referenced once."""
+    for v, m, mats in (scenes["cornell_spheres"]()[:3], soup(5000, seed=4), soup(3, seed=1), soup(1, seed=2)):
+        with bdpt.SceneImage.build(v, m, mats) as img:
+            sec = image_sections(img.bytes())
+        fast = sec[5].view(np.dtype([("box", "<f4", 12), ("left", "<i4"), ("right", "<i4"), ("pad", "<u4", 2)]))
+        wide = sec[6].view(np.dtype([("box", "<f4", (6, 4)), ("child", "<i4", 4), ("pad", "<u4", 4)]))
+        links = np.concatenate([fast["left"], fast["right"]])
+        bin_leaves = np.sort(links[links < 0])
+        ch = wide["child"].reshape(-1)
+        empty = ch == np.iinfo(np.int32).min
+        wide_leaves = np.sort(ch[(ch < 0) & ~empty])
+        assert np.array_equal(bin_leaves, wide_leaves)
+        inner = np.sort(ch[ch >= 0])
+        assert np.array_equal(inner, np.arange(1, len(wide)))          # every node but the root has one parent
+        assert len(wide) <= len(fast) and (len(fast) < 8 or len(wide) < 0.75 * len(fast))
+        # every used child box of a wide node is one of the binary tree's child boxes
+        bin_boxes = {tuple(b) for b in np.concatenate([fast["box"][:, [0, 1, 2, 3, 4, 5]], fast["box"][:, [6, 7, 8, 9, 10, 11]]]).tolist()}
+        wb = wide["box"].transpose(0, 2, 1).reshape(-1, 6)[~empty]
+        assert all(tuple(b) in bin_boxes for b in wb.tolist())
+
+
 def test_image_rejects_damage(bdpt):
     v, m, mats = soup(500)
     with bdpt.SceneImage.build(v, m, mats) as img:

@@ -119,3 +119,44 @@ def test_split_walk_matches_reference_golden(name, bdpt, gpu_ctx, scenes, golden
     check_hits(h, g["prim"], g["t"], g["u"], g["v"], exact=True)
     ha = gpu_ctx.trace(g["rays"], bvh=1, any_hit=True, split=True)
     assert np.array_equal(ha["prim"] != 0xFFFFFFFF, g["prim"] != 0xFFFFFFFF)
+
+
+@pytest.mark.parametrize("mode", ["0", "3"])
+@pytest.mark.parametrize("name", NAMES)
+def test_wide_and_binary_walks_match_reference_golden(name, mode, bdpt, gpu_ctx, scenes, golden, monkeypatch):
+    """bdpt_trace on BVH_FAST walks the 4-wide nodes for closest-hit queries by default (traverse_walk.cuh: run4);
+    BDPT_WIDE=0 forces the binary walk, =3 also walks any-hit queries 4-wide.  The candidates' tests are the same,
+    so every flavour must reproduce the reference."""
+    g = golden(name)
+    v, m, mats, cam = scenes[name]()
+    monkeypatch.setenv("BDPT_WIDE", mode)
+    gpu_ctx.upload(v, m, mats)
+    monkeypatch.delenv("BDPT_WIDE")
+    h = gpu_ctx.trace(g["rays"], bvh=bdpt.BVH_FAST)
+    check_hits(h, g["prim"], g["t"], g["u"], g["v"], exact=True)
+    ha = gpu_ctx.trace(g["rays"], bvh=bdpt.BVH_FAST, any_hit=True)
+    assert np.array_equal(ha["prim"] != bdpt.MISS, g["prim"] != bdpt.MISS)
+    gpu_ctx.stats_reset()
+    gpu_ctx.trace(g["rays"], bvh=bdpt.BVH_FAST, stats=True)
+    wide_nodes = gpu_ctx.stats()["node_visits"]
+    assert wide_nodes > 0
+
+
+def test_wide_walk_large_soup_vs_port(bdpt, gpu_ctx, monkeypatch):
+    from oracle.oracle import Oracle
+    from tools import testscenes as ts
+    v, m, mats = ts.random_soup(60000, seed=21, extent=25.0, size=0.8)
+    rays = ts.ray_batch(v, 200000, seed=77)
+    o = Oracle("port").load(v, m, mats)
+    prim, t, u, w = o.trace(rays, nthreads=8)
+    visits = {}
+    for mode in ("0", "3"):
+        monkeypatch.setenv("BDPT_WIDE", mode)
+        gpu_ctx.upload(v, m, mats)
+        check_hits(gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST), prim, t, u, w, exact=True)
+        ha = gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST, any_hit=True)
+        assert np.array_equal(ha["prim"] != bdpt.MISS, prim != bdpt.MISS)
+        gpu_ctx.stats_reset()
+        gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST, stats=True)
+        visits[mode] = gpu_ctx.stats()["node_visits"]
+    assert visits["3"] < 0.8 * visits["0"]                       # the 4-wide walk opens far fewer nodes
