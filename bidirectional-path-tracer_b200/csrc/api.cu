@@ -20,6 +20,10 @@ namespace {
 std::string g_create_err;
 
 constexpr int kTraceBlock = 64;
+#ifndef BDPT_TRACE_SLICE
+#define BDPT_TRACE_SLICE 2
+#endif
+constexpr int kTraceSlice = BDPT_TRACE_SLICE;   // leaf visits between two meetings of a warp in k_trace
 
 
 template <class T>
@@ -49,25 +53,43 @@ __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_trace(Scene
     StackEntry l_stack[WIDE ? kWideStackLevels : 32];
     const uint64_t i = uint64_t(blockIdx.x) * kTraceBlock + threadIdx.x;
     TravStats st{0, 0};
+    RayD r;
+    HitD h;
+    h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS;
+    bool found = false;
     if (i < n) {
         const double2* q = reinterpret_cast<const double2*>(rays + i);
         double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
-        RayD r;
         r.o = mk(a.x, a.y, b.x); r.d = mk(b.y, c.x, c.y); r.tmin = e.x; r.tmax = e.y;
-        HitD h;
-        h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS;
-        bool found;
-        if (BVH == BDPT_BVH_REFERENCE)
-            found = traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st);
-        else if (walk_eligible(sc, r)) {   // the render kernels' walk (fp32 FMA slabs); a tie goes to the reference tree
-            Walk<ANY, STATS> W;
-            W.init(sc, r);
-            const int rc = WIDE ? W.run4(sc, l_stack, 0) : W.run(sc, l_stack, 0);
+    }
+    if (BVH == BDPT_BVH_REFERENCE) {
+        if (i < n) found = traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st);
+    } else {
+        // The render kernels' walk (fp32 FMA slabs) in time slices: a lane hands control back after kSlice leaf visits
+        // and the warp meets at __syncwarp before walking on.  Without that meeting point the lanes of a warp drift apart
+        // for the whole walk (ncu: 2 of 32 lanes active per instruction); with it they re-join every few leaves.
+        Walk<ANY, STATS> W;
+        const bool eligible = i < n && walk_eligible(sc, r);
+        bool busy = eligible;
+        int rc = TR_MISS;
+        const int slice = int(sc.use_wide >> (ANY ? 16 : 8)) & 0xFF;
+        if (busy) W.init(sc, r);
+        for (;;) {
+            __syncwarp();
+            if (busy) {
+                const int x = WIDE ? W.run4(sc, l_stack, slice) : W.run(sc, l_stack, slice);
+                if (x != WALK_YIELD) { rc = x; busy = false; }
+            }
+            if (!__any_sync(0xFFFFFFFFu, busy)) break;
+        }
+        if (eligible) {
             if (STATS) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; }
             h = W.hit;
-            found = rc == TR_DEFER ? traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st) : rc == TR_HIT;
-        } else
+            found = rc == TR_DEFER ? traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st) : rc == TR_HIT;   // a tie goes to the reference tree
+        } else if (i < n)
             found = traverse_fast<ANY, STATS, false>(sc, r, h, l_stack, 1, &st) == TR_HIT;
+    }
+    if (i < n) {
         double2* o = reinterpret_cast<double2*>(out + i);
         if (!found) { h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS; }
         o[0] = make_double2(h.t, h.u);
@@ -238,7 +260,7 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
             t_fast = ms_since(t_b);
         } else if (!rc && !fast_err) {
             rc = upload(ctx, h.fast_nodes, &v.fast_nodes);
-            if (!rc) rc = upload(ctx, h.wide_nodes, &v.wide_nodes);
+            if (!rc && !h.wide_nodes.empty()) rc = upload(ctx, h.wide_nodes, &v.wide_nodes);
             v.n_wide_nodes = uint32_t(h.wide_nodes.size());
             if (!rc) rc = upload(ctx, h.fast_prims, &v.fast_prims);
             if (!rc) rc = upload(ctx, h.fast_tris, &v.fast_tris);
@@ -257,8 +279,8 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
     if (!rc) rc = upload(ctx, h.ref_parent, &v.ref_parent);
     if (!rc) rc = upload(ctx, h.prim_leaf, &v.prim_leaf);
     if (!rc) rc = upload(ctx, h.chain_box, &v.chain_box);
-    v.use_wide = (!gpu_tree && 3u * h.wide_depth + 2u <= uint32_t(kWideStackLevels)) ? bdpt::wide_walk_mode() : 0u;
-    if (timing) std::fprintf(stderr, "bdpt_scene_upload: 4-wide tree: %zu nodes, depth %u, walk mode %u\n", h.wide_nodes.size(), h.wide_depth, v.use_wide);
+    v.use_wide = (!gpu_tree && !h.wide_nodes.empty() && 3u * h.wide_depth + 2u <= uint32_t(kWideStackLevels)) ? bdpt::wide_walk_mode() : 0u;
+    if (timing && !h.wide_nodes.empty()) std::fprintf(stderr, "bdpt_scene_upload: 4-wide tree: %zu nodes, depth %u, walk mode %u\n", h.wide_nodes.size(), h.wide_depth, v.use_wide);
     if (!rc && (h.ref_depth >= uint32_t(kRefStackLevels) || h.fast_depth + 2 > 32u)) {   // 64 int32 / 32 StackEntry slots of local stack
         ctx->err = "BVH deeper than the traversal stack";
         rc = BDPT_ERR_ARG;
@@ -323,6 +345,12 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
     const bool any = (flags & BDPT_TRACE_ANY) != 0, stats = (flags & BDPT_TRACE_STATS) != 0;
     const unsigned grid = unsigned((n + kTraceBlock - 1) / kTraceBlock);
     SceneView v = ctx->view;
+    {
+        const char* e = std::getenv("BDPT_TRACE_SLICE");
+        v.use_wide |= uint32_t((e ? std::atoi(e) : kTraceSlice) & 0xFF) << 8;
+        const char* ea = std::getenv("BDPT_TRACE_SLICE_ANY");
+        v.use_wide |= uint32_t((ea ? std::atoi(ea) : 0) & 0xFF) << 16;
+    }
     unsigned long long* st = ctx->d_stats;
     if ((flags & BDPT_TRACE_SPLIT) && bvh == BDPT_BVH_FAST) {
         const unsigned wgrid = unsigned((n * 32 + kTraceBlock - 1) / kTraceBlock);
@@ -336,7 +364,7 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
     if (bvh == BDPT_BVH_REFERENCE) {
         if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, false); }
         else     { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, false); }
-    } else if ((v.use_wide & (any ? 2u : 1u)) && v.wide_nodes) {
+    } else if ((v.use_wide & (any ? 2u : 1u)) && v.wide_nodes) {   // bits 8..15 of use_wide: the walk's time slice
 #define BDPT_LAUNCH_W(A, S) k_trace<BDPT_BVH_FAST, A, S, true><<<grid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out, st)
         if (any) { if (stats) BDPT_LAUNCH_W(true, true); else BDPT_LAUNCH_W(true, false); }
         else     { if (stats) BDPT_LAUNCH_W(false, true); else BDPT_LAUNCH_W(false, false); }

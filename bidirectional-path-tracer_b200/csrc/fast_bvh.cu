@@ -331,8 +331,12 @@ void build_fast_bvh(HostScene& s) {
     par_chunks(0, n, n_threads, [&](uint32_t cb, uint32_t ce, unsigned) {
         for (uint32_t k = cb; k < ce; ++k) s.fast_tris[k] = s.tris[s.fast_prims[k]];
     });
-    collapse_wide(s);
-    lap("collapsed to 4-wide");
+    // the 4-wide form is an option of bdpt_trace (BDPT_WIDE, ctx.h): built only when asked for
+    s.wide_nodes.clear();
+    s.wide_depth = 0;
+    if (const char* e = std::getenv("BDPT_WIDE")) {
+        if (std::atoi(e) & 3) { collapse_wide(s); lap("collapsed to 4-wide"); }
+    }
 }
 
 // Binary -> 4-wide: a wide node starts from a binary node's two children and, while it has a free slot, replaces

@@ -105,7 +105,7 @@ const ImageHeader* check_image(const void* image, uint64_t bytes, bool verify, s
     if (h->version != kVersion || h->header_bytes != sizeof(ImageHeader)) { why = "scene image: unknown version"; return nullptr; }
     if (h->layout_sig != layout_sig()) { why = "scene image: built by a library with different record layouts"; return nullptr; }
     if (h->total_bytes != bytes) { why = "scene image: truncated (header says " + std::to_string(h->total_bytes) + " bytes, got " + std::to_string(bytes) + ")"; return nullptr; }
-    if (h->n_tris == 0 || h->n_mats == 0 || h->n_lights == 0 || h->n_ref_nodes == 0 || h->n_fast_nodes == 0 || h->n_wide_nodes == 0) { why = "scene image: empty scene"; return nullptr; }
+    if (h->n_tris == 0 || h->n_mats == 0 || h->n_lights == 0 || h->n_ref_nodes == 0 || h->n_fast_nodes == 0) { why = "scene image: empty scene"; return nullptr; }
     uint64_t want[SEC_COUNT];
     expected_bytes(*h, want);
     uint64_t at = sizeof(ImageHeader);
@@ -239,9 +239,9 @@ int bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, ui
     v.lights = reinterpret_cast<const uint32_t*>(at(SEC_LIGHTS));
     v.light_area = reinterpret_cast<const double*>(at(SEC_LIGHT_AREA));
     v.fast_nodes = reinterpret_cast<const FastNode*>(at(SEC_FAST_NODES));
-    v.wide_nodes = reinterpret_cast<const WideNode*>(at(SEC_WIDE_NODES));
+    v.wide_nodes = h->n_wide_nodes ? reinterpret_cast<const WideNode*>(at(SEC_WIDE_NODES)) : nullptr;   // optional section
     v.n_wide_nodes = h->n_wide_nodes;
-    v.use_wide = 3u * h->wide_depth + 2u <= uint32_t(kWideStackLevels) ? wide_walk_mode() : 0u;
+    v.use_wide = (h->n_wide_nodes && 3u * h->wide_depth + 2u <= uint32_t(kWideStackLevels)) ? wide_walk_mode() : 0u;
     v.fast_prims = reinterpret_cast<const uint32_t*>(at(SEC_FAST_PRIMS));
     v.fast_tris = reinterpret_cast<const TriGeom*>(at(SEC_FAST_TRIS));
     v.ref_nodes = reinterpret_cast<const RefNode*>(at(SEC_REF_NODES));

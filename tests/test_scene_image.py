@@ -52,9 +52,12 @@ def image_sections(raw):
     return [raw[int(o):int(o) + int(b)] for o, b in table]
 
 
-def test_wide_tree_is_the_binary_tree_collapsed(bdpt, scenes):
-    """The 4-wide nodes (fast_bvh.cu: collapse_wide) must hold exactly the binary fast tree's leaves, each once, under
-    copied (never shrunk) boxes, with every wide node referenced once."""
+def test_wide_tree_is_the_binary_tree_collapsed(bdpt, scenes, monkeypatch):
+    """The 4-wide nodes (fast_bvh.cu: collapse_wide, built when BDPT_WIDE asks for them) must hold exactly the binary
+    fast tree's leaves, each once, under copied (never shrunk) boxes, with every wide node referenced once."""
+    with bdpt.SceneImage.build(*soup(100, seed=8)) as img:
+        assert len(image_sections(img.bytes())[6]) == 0                # the section is optional: empty by default
+    monkeypatch.setenv("BDPT_WIDE", "1")
     for v, m, mats in (scenes["cornell_spheres"]()[:3], soup(5000, seed=4), soup(3, seed=1), soup(1, seed=2)):
         with bdpt.SceneImage.build(v, m, mats) as img:
             sec = image_sections(img.bytes())

@@ -124,9 +124,9 @@ def test_split_walk_matches_reference_golden(name, bdpt, gpu_ctx, scenes, golden
 @pytest.mark.parametrize("mode", ["0", "3"])
 @pytest.mark.parametrize("name", NAMES)
 def test_wide_and_binary_walks_match_reference_golden(name, mode, bdpt, gpu_ctx, scenes, golden, monkeypatch):
-    """bdpt_trace on BVH_FAST walks the 4-wide nodes for closest-hit queries by default (traverse_walk.cuh: run4);
-    BDPT_WIDE=0 forces the binary walk, =3 also walks any-hit queries 4-wide.  The candidates' tests are the same,
-    so every flavour must reproduce the reference."""
+    """bdpt_trace on BVH_FAST: the binary walk (default, BDPT_WIDE=0) and the optional 4-wide walk (BDPT_WIDE=3:
+    closest- and any-hit queries through traverse_walk.cuh's run4) test the same candidates, so both must
+    reproduce the reference."""
     g = golden(name)
     v, m, mats, cam = scenes[name]()
     monkeypatch.setenv("BDPT_WIDE", mode)
