@@ -167,6 +167,19 @@ def cpu_reference(spp, steps, warmup, procs=None):
             "tri_tests_per_ray": sum(o["tri_tests"] for o in outs) / max(1, rays)}
 
 
+def cpu_reference_variant(spp, threads, rows):
+    """One process of the reference through tools/cpu_ref_worker.py: threads > 1 = its own thread-pool shape."""
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "cpu_ref_worker.py"), SCENE, str(WIDTH), str(HEIGHT), str(spp), str(DEPTH),
+           str(HEIGHT // 2), "1", "0", str(threads), str(rows)]
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, OMP_NUM_THREADS="1")).stdout
+        o = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+        return {"value": o["samples_per_step"] / sum(o["step_s"]) / 1e6, "unit": "Msamples/s", "threads": threads,
+                "sample": "%d row(s) of %dx%d at %d spp, depth %d (%d samples)" % (rows, WIDTH, HEIGHT, spp, DEPTH, o["samples_per_step"])}
+    except Exception as e:   # reporting only: never fail the arm over it
+        return {"unavailable": str(e)[:200]}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -182,6 +195,16 @@ def run_reference(args):
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "reference_counters": {k: r[k] for k in ("closest_rays_per_sample", "node_visits_per_ray", "tri_tests_per_ray")}}
+    # the other two ways of running the reference on these cores, reported beside the headline (iii)
+    if not args.skip_cpu:
+        cores = host_cores()
+        line["variants"] = {
+            "independent_processes": "the line's value (one single-thread process per core, disjoint rows)",
+            "single_thread": cpu_reference_variant(16, 1, 4),
+            "as_shipped_thread_pool": dict(cpu_reference_variant(16, cores + 1, 8),
+                                           note="hardware_concurrency()+1 threads sharing one unlocked mt19937 and the stats atomics "
+                                                "(camera.h:60, main.h:28-32, stats.h:8-16): what a user of the reference gets; racy, so "
+                                                "its image differs from run to run")}
     emit(line)
     return 0
 
