@@ -475,20 +475,40 @@ def bvh_microbench(args, pkg, bvh):
     with pkg.Context(int(os.environ.get("LOCAL_RANK", "0"))) as c:
         c.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
         res = {"rays": n, "triangles": len(sf.verts), "scene": "glass-of-water (stand-in geometry)"}
+        import torch
+        # device-resident: rays and hits live in HBM (torch owns the buffers), nothing is copied in the timed call
+        d_rays = torch.from_numpy(np.ascontiguousarray(rays, dtype=np.float64)).cuda()
+        d_hits = torch.empty(n * pkg.HIT_DTYPE.itemsize, dtype=torch.uint8, device="cuda")
+        # host buffers: the caller's rays and hit records in PINNED memory, through the C-ABI's chunked copy/trace pipeline
+        h_rays = torch.empty((n, 8), dtype=torch.float64, pin_memory=True)
+        h_rays.numpy()[:] = rays
+        h_hits = torch.empty(n * pkg.HIT_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(pkg.HIT_DTYPE)
+        torch.cuda.synchronize()
         for name, flavour in (("fast", pkg.BVH_FAST), ("reference_topology", pkg.BVH_REFERENCE)):
-            best_ms, best_wall = 1e30, 1e30
+            best_ms, best_wall, best_pageable = 1e30, 1e30, 1e30
+            for rep in range(3):
+                c.trace_device(d_rays.data_ptr(), n, d_hits.data_ptr(), bvh=flavour)
+                best_ms = min(best_ms, c.last_device_ms())
             for rep in range(3):
                 t0 = time.perf_counter()
-                h = c.trace(rays, bvh=flavour)
+                h = c.trace(h_rays.numpy(), bvh=flavour, out=h_hits)
                 best_wall = min(best_wall, time.perf_counter() - t0)
-                best_ms = min(best_ms, c.last_device_ms())
+            for rep in range(2):
+                t0 = time.perf_counter()
+                hp = c.trace(rays, bvh=flavour)                 # pageable numpy arrays, output allocated by the call
+                best_pageable = min(best_pageable, time.perf_counter() - t0)
+            dev_prim = d_hits.cpu().numpy().view(pkg.HIT_DTYPE)["prim"]
+            assert np.array_equal(dev_prim, h["prim"]) and np.array_equal(hp["prim"], h["prim"])
             c.stats_reset()
             c.trace(rays[: 1 << 20], bvh=flavour, stats=True)
             s = c.stats()
-            res[name] = {"mrays_per_s": n / best_ms / 1e3, "e2e_mrays_per_s": n / best_wall / 1e6, "device_ms": best_ms,
+            res[name] = {"mrays_per_s": n / best_ms / 1e3, "e2e_mrays_per_s": n / best_wall / 1e6,
+                         "e2e_pageable_mrays_per_s": n / best_pageable / 1e6, "device_ms": best_ms,
                          "nodes_per_ray": s["node_visits"] / (1 << 20), "tris_per_ray": s["tri_tests"] / (1 << 20),
                          "hit_fraction": float((h["prim"] != 0xFFFFFFFF).mean()),
                          "prim_checksum": int(h["prim"].astype(np.uint64).sum())}
+        res["e2e_note"] = ("e2e: rays and hit records in pinned host memory, bdpt_trace copies and traces in 2^20-ray chunks on two streams; "
+                           "e2e_pageable: plain numpy arrays, output allocated inside the call")
         res["prim_ids_equal_between_flavours"] = res["fast"]["prim_checksum"] == res["reference_topology"]["prim_checksum"]
     return res
 

@@ -386,10 +386,15 @@ class Context:
         self._chk(lib().bdpt_bvh_leaf_order(self._h, out.ctypes.data), "bdpt_bvh_leaf_order")
         return out
 
-    def trace(self, rays8, bvh=BVH_REFERENCE, any_hit=False, stats=False, split=False):
-        """Host buffers in, host buffers out (the e2e path). Returns structured HIT_DTYPE array."""
+    def trace(self, rays8, bvh=BVH_REFERENCE, any_hit=False, stats=False, split=False, out=None):
+        """Host buffers in, host buffers out (the e2e path). Returns structured HIT_DTYPE array.  `out`: a HIT_DTYPE
+        array of len(rays) to fill (e.g. a view of pinned memory; with pinned rays too the library's chunked copies
+        overlap the kernels)."""
         r = pack_rays(rays8)
-        out = np.empty(len(r), HIT_DTYPE)
+        if out is None:
+            out = np.empty(len(r), HIT_DTYPE)
+        elif out.dtype != HIT_DTYPE or len(out) != len(r) or not out.flags.c_contiguous:
+            raise ValueError("trace(out=...): need a C-contiguous HIT_DTYPE array of len(rays)")
         flags = (TRACE_ANY if any_hit else 0) | (TRACE_STATS if stats else 0) | (TRACE_SPLIT if split else 0)
         self._chk(lib().bdpt_trace(self._h, bvh, r.ctypes.data if len(r) else None, len(r),
                                    out.ctypes.data if len(r) else None, flags), "bdpt_trace")

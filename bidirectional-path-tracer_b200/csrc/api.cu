@@ -341,7 +341,7 @@ int bdpt_bvh_leaf_order(bdpt_ctx* ctx, uint32_t* order) {
     return BDPT_OK;
 }
 
-static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t n, bdpt_hit* d_out, int flags) {
+static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t n, bdpt_hit* d_out, int flags, cudaStream_t stream) {
     const bool any = (flags & BDPT_TRACE_ANY) != 0, stats = (flags & BDPT_TRACE_STATS) != 0;
     const unsigned grid = unsigned((n + kTraceBlock - 1) / kTraceBlock);
     SceneView v = ctx->view;
@@ -354,18 +354,18 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
     unsigned long long* st = ctx->d_stats;
     if ((flags & BDPT_TRACE_SPLIT) && bvh == BDPT_BVH_FAST) {
         const unsigned wgrid = unsigned((n * 32 + kTraceBlock - 1) / kTraceBlock);
-        if (any) k_trace_split<true><<<wgrid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out);
-        else k_trace_split<false><<<wgrid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out);
+        if (any) k_trace_split<true><<<wgrid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out);
+        else k_trace_split<false><<<wgrid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out);
         ctx->launches += 1;
         BDPT_CUDA(ctx, cudaGetLastError());
         return BDPT_OK;
     }
-#define BDPT_LAUNCH(B, A, S) k_trace<B, A, S><<<grid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out, st)
+#define BDPT_LAUNCH(B, A, S) k_trace<B, A, S><<<grid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st)
     if (bvh == BDPT_BVH_REFERENCE) {
         if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, false); }
         else     { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, false); }
     } else if ((v.use_wide & (any ? 2u : 1u)) && v.wide_nodes) {   // bits 8..15 of use_wide: the walk's time slice
-#define BDPT_LAUNCH_W(A, S) k_trace<BDPT_BVH_FAST, A, S, true><<<grid, kTraceBlock, 0, ctx->stream>>>(v, d_rays, n, d_out, st)
+#define BDPT_LAUNCH_W(A, S) k_trace<BDPT_BVH_FAST, A, S, true><<<grid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st)
         if (any) { if (stats) BDPT_LAUNCH_W(true, true); else BDPT_LAUNCH_W(true, false); }
         else     { if (stats) BDPT_LAUNCH_W(false, true); else BDPT_LAUNCH_W(false, false); }
 #undef BDPT_LAUNCH_W
@@ -388,27 +388,62 @@ int bdpt_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* rays, uint64_t n, bdpt_hi
     if (n > (uint64_t(1) << 31) * kTraceBlock) { ctx->err = "batch too large"; return BDPT_ERR_ARG; }
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
     const bool dev = (flags & BDPT_TRACE_DEVICE_PTRS) != 0;
-    const bdpt_ray* d_rays = rays;
-    bdpt_hit* d_out = out;
-    void *tmp_r = nullptr, *tmp_o = nullptr;
-    if (!dev) {
-        BDPT_CUDA(ctx, cudaMalloc(&tmp_r, n * sizeof(bdpt_ray)));
-        if (cudaMalloc(&tmp_o, n * sizeof(bdpt_hit)) != cudaSuccess) { cudaFree(tmp_r); ctx->err = "cudaMalloc hits"; return BDPT_ERR_NOMEM; }
-        BDPT_CUDA(ctx, cudaMemcpyAsync(tmp_r, rays, n * sizeof(bdpt_ray), cudaMemcpyHostToDevice, ctx->stream));
-        d_rays = static_cast<const bdpt_ray*>(tmp_r);
-        d_out = static_cast<bdpt_hit*>(tmp_o);
+    if (dev) {
+        BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+        int rc = launch_trace(ctx, bvh, rays, n, out, flags, ctx->stream);
+        if (rc) return rc;
+        BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) { ctx->err = std::string("trace: ") + cudaGetErrorString(e); return BDPT_ERR_CUDA; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+        ctx->last_ms = ms;
+        return BDPT_OK;
     }
-    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    int rc = launch_trace(ctx, bvh, d_rays, n, d_out, flags);
-    if (rc) { cudaFree(tmp_r); cudaFree(tmp_o); return rc; }
-    BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    if (!dev) BDPT_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * sizeof(bdpt_hit), cudaMemcpyDeviceToHost, ctx->stream));
-    cudaError_t e = cudaStreamSynchronize(ctx->stream);
-    if (!dev) { cudaFree(tmp_r); cudaFree(tmp_o); }
-    if (e != cudaSuccess) { ctx->err = std::string("trace: ") + cudaGetErrorString(e); return BDPT_ERR_CUDA; }
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
-    ctx->last_ms = ms;
+    // Host buffers: the batch goes through in chunks on two streams, so that a chunk's H2D copy, its kernel and its
+    // D2H copy overlap the neighbours' (full-duplex PCIe; really asynchronous only when the caller's buffers are
+    // pinned -- pageable memory degrades to what one big copy would do).  Device staging is two chunks, not n.
+    constexpr uint64_t kChunk = uint64_t(1) << 20;
+    constexpr int kLanes = 2;
+    const uint64_t chunk = std::min<uint64_t>(n, kChunk), n_chunks = (n + chunk - 1) / chunk;
+    struct Stage {
+        cudaStream_t st = nullptr;
+        void *r = nullptr, *o = nullptr;
+    } lane[kLanes];
+    std::vector<cudaEvent_t> ev(2 * n_chunks, nullptr);
+    cudaError_t e = cudaSuccess;
+    int rc = BDPT_OK;
+    const int lanes = int(std::min<uint64_t>(kLanes, n_chunks));
+    for (int k = 0; k < lanes && e == cudaSuccess; ++k) {
+        e = cudaStreamCreateWithFlags(&lane[k].st, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaMalloc(&lane[k].r, chunk * sizeof(bdpt_ray));
+        if (e == cudaSuccess) e = cudaMalloc(&lane[k].o, chunk * sizeof(bdpt_hit));
+    }
+    for (auto& x : ev) if (e == cudaSuccess) e = cudaEventCreate(&x);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // whatever was queued before (scene upload) is done
+    for (uint64_t c = 0; c < n_chunks && e == cudaSuccess && rc == BDPT_OK; ++c) {
+        Stage& L = lane[c % lanes];
+        const uint64_t at = c * chunk, cnt = std::min<uint64_t>(chunk, n - at);
+        e = cudaMemcpyAsync(L.r, rays + at, cnt * sizeof(bdpt_ray), cudaMemcpyHostToDevice, L.st);
+        if (e == cudaSuccess) e = cudaEventRecord(ev[2 * c], L.st);
+        if (e == cudaSuccess) rc = launch_trace(ctx, bvh, static_cast<const bdpt_ray*>(L.r), cnt, static_cast<bdpt_hit*>(L.o), flags, L.st);
+        if (e == cudaSuccess && rc == BDPT_OK) e = cudaEventRecord(ev[2 * c + 1], L.st);
+        if (e == cudaSuccess && rc == BDPT_OK) e = cudaMemcpyAsync(out + at, L.o, cnt * sizeof(bdpt_hit), cudaMemcpyDeviceToHost, L.st);
+    }
+    for (int k = 0; k < lanes; ++k)
+        if (lane[k].st) { const cudaError_t s2 = cudaStreamSynchronize(lane[k].st); if (e == cudaSuccess) e = s2; }
+    double total_ms = 0.0;   // kernel time only, summed over the chunks (they overlap the copies, not each other's kernels much)
+    if (e == cudaSuccess && rc == BDPT_OK)
+        for (uint64_t c = 0; c < n_chunks; ++c) { float ms = 0.f; if (cudaEventElapsedTime(&ms, ev[2 * c], ev[2 * c + 1]) == cudaSuccess) total_ms += ms; }
+    for (auto& x : ev) if (x) cudaEventDestroy(x);
+    for (int k = 0; k < lanes; ++k) {
+        if (lane[k].r) cudaFree(lane[k].r);
+        if (lane[k].o) cudaFree(lane[k].o);
+        if (lane[k].st) cudaStreamDestroy(lane[k].st);
+    }
+    if (rc) return rc;
+    if (e != cudaSuccess) { ctx->err = std::string("trace: ") + cudaGetErrorString(e); return e == cudaErrorMemoryAllocation ? BDPT_ERR_NOMEM : BDPT_ERR_CUDA; }
+    ctx->last_ms = total_ms;
     return BDPT_OK;
 }
 

@@ -160,3 +160,42 @@ def test_wide_walk_large_soup_vs_port(bdpt, gpu_ctx, monkeypatch):
         gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST, stats=True)
         visits[mode] = gpu_ctx.stats()["node_visits"]
     assert visits["3"] < 0.8 * visits["0"]                       # the 4-wide walk opens far fewer nodes
+
+
+def test_host_buffer_batches_are_chunked_without_a_seam(bdpt, gpu_ctx):
+    """bdpt_trace with host buffers runs 2^20-ray chunks on two streams (api.cu): a 2.3 M-ray batch (three chunks, the
+    last one ragged) must equal the single-launch device-pointer path everywhere and the oracle across the seams."""
+    import torch
+    from tools import testscenes as ts
+    v, m, mats = ts.random_soup(3000, seed=5, extent=12.0, size=0.9)
+    n = (1 << 21) + 250001
+    rays = ts.ray_batch(v, n, seed=99)
+    gpu_ctx.upload(v, m, mats)
+    for any_hit in (False, True):
+        h = gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST, any_hit=any_hit)
+        d_rays = torch.from_numpy(np.ascontiguousarray(rays, dtype=np.float64)).cuda()
+        d_hits = torch.zeros(n * bdpt.HIT_DTYPE.itemsize, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        gpu_ctx.trace_device(d_rays.data_ptr(), n, d_hits.data_ptr(), bvh=bdpt.BVH_FAST, any_hit=any_hit)
+        hd = d_hits.cpu().numpy().view(bdpt.HIT_DTYPE)
+        if any_hit:
+            assert np.array_equal(h["prim"] != bdpt.MISS, hd["prim"] != bdpt.MISS)
+        else:
+            for f in ("prim", "t", "u", "v"):
+                assert np.array_equal(h[f], hd[f]), f
+    # pinned caller buffers (the asynchronous case) and a caller-provided output
+    pr = torch.empty((n, 8), dtype=torch.float64, pin_memory=True)
+    pr.numpy()[:] = rays
+    po = torch.empty(n * bdpt.HIT_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(bdpt.HIT_DTYPE)
+    hp = gpu_ctx.trace(pr.numpy(), bvh=bdpt.BVH_FAST, out=po)
+    assert hp is po and np.array_equal(hp["prim"], hd["prim"] if False else gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST)["prim"])
+    assert gpu_ctx.last_device_ms() > 0
+    o = Oracle("port").load(v, m, mats)
+    for seam in (1 << 20, 1 << 21):
+        sl = slice(seam - 500, seam + 500)
+        prim, t, u, w = o.trace(rays[sl])
+        check_hits(hp[sl], prim, t, u, w, exact=True)
+    prim, t, u, w = o.trace(rays[-300:])
+    check_hits(hp[-300:], prim, t, u, w, exact=True)
+    with pytest.raises(ValueError):
+        gpu_ctx.trace(rays[:10], bvh=bdpt.BVH_FAST, out=po)
