@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libbdpt.so")
+LIB_PATH = os.environ.get("BDPT_LIB") or os.path.join(HERE, "libbdpt.so")   # BDPT_LIB: a differently built library (development A/B runs)
 
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_LIGHT = 0, 1, 2, 3
 BVH_REFERENCE, BVH_FAST = 0, 1
