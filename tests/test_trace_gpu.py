@@ -188,7 +188,7 @@ def test_host_buffer_batches_are_chunked_without_a_seam(bdpt, gpu_ctx):
     pr.numpy()[:] = rays
     po = torch.empty(n * bdpt.HIT_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True).numpy().view(bdpt.HIT_DTYPE)
     hp = gpu_ctx.trace(pr.numpy(), bvh=bdpt.BVH_FAST, out=po)
-    assert hp is po and np.array_equal(hp["prim"], hd["prim"] if False else gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST)["prim"])
+    assert hp is po and np.array_equal(hp["prim"], gpu_ctx.trace(rays, bvh=bdpt.BVH_FAST)["prim"])
     assert gpu_ctx.last_device_ms() > 0
     o = Oracle("port").load(v, m, mats)
     for seam in (1 << 20, 1 << 21):

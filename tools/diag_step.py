@@ -8,14 +8,15 @@ bench.ensure_scenes()
 sf = b.SceneFile(bench.SCENE)
 cam = sf.camera_with(bench.WIDTH, bench.HEIGHT, bench.SPP, bench.DEPTH)
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 6
+STREAMS, BATCH = int(os.environ.get("STREAMS", "0")), int(os.environ.get("BATCH", "0"))
 with b.Context(0) as ctx:
     ctx.upload(sf.verts, sf.mat_id, sf.materials)
     ctx.film_clear(bench.WIDTH, bench.HEIGHT)
     for s in range(3):
-        ctx.render(cam, seed=1, bvh=b.BVH_FAST, strata=(4 * s, 4 * s + 4, 1), clear=False, height=bench.HEIGHT)
+        ctx.render(cam, seed=1, bvh=b.BVH_FAST, strata=(4 * s, 4 * s + 4, 1), clear=False, height=bench.HEIGHT, streams=STREAMS, batch_samples=BATCH)
     ms = 0.0
     for s in range(3, 3 + K):
-        ctx.render(cam, seed=1, bvh=b.BVH_FAST, strata=(4 * s, 4 * s + 4, 1), clear=False, height=bench.HEIGHT)
+        ctx.render(cam, seed=1, bvh=b.BVH_FAST, strata=(4 * s, 4 * s + 4, 1), clear=False, height=bench.HEIGHT, streams=STREAMS, batch_samples=BATCH)
         ms += ctx.last_device_ms()
     kt = ctx.kernel_times()
     print(os.environ.get("TAG", ""), "%.1f Msamples/s  %.2f ms/step" % (bench.WIDTH * bench.HEIGHT * 4 * K / ms / 1e3, ms / K),
