@@ -25,9 +25,20 @@ void camera::render(const hittable& world, const hittable& lights) {
     if (auto b = dynamic_cast<const bvh_node*>(&world)) prims = &b->prims;
     else if (auto t = dynamic_cast<const triangle_collection*>(&world)) prims = &t->tris;
     if (!prims) throw std::runtime_error("camera::render: world must be a bvh_node or a triangle_collection");
-    const bool from_image = options.scene_image != nullptr;
+    bool from_image = options.scene_image != nullptr;
+    const void* image = options.scene_image;
+    uint64_t image_bytes = options.scene_image_bytes;
     std::vector<double> verts; std::vector<uint32_t> mat_id; std::vector<bdpt_material> mats;
     if (!from_image) flatten_triangles(*prims, verts, mat_id, mats);
+    // several GPUs: flatten and build the two trees ONCE into a scene image and hand every context the same block,
+    // instead of letting each worker's bdpt_scene_upload rebuild them side by side on the same host cores
+    struct image_owner { void* p = nullptr; ~image_owner() { if (p) bdpt_scene_image_free(p); } } built;
+    if (!from_image && options.gpus > 1) {
+        if (bdpt_scene_image_build(verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size()), 0, &built.p, &image_bytes))
+            throw std::runtime_error(std::string("bdpt_scene_image_build failed: ") + bdpt_scene_image_last_error());
+        image = built.p;
+        from_image = true;
+    }
 
     bdpt_camera c{};
     c.aspect_ratio = aspect_ratio; c.image_width = image_width; c.samples_per_pixel = samples_per_pixel;
@@ -47,7 +58,7 @@ void camera::render(const hittable& world, const hittable& lights) {
         try {
             guard ctx;
             if (bdpt_ctx_create(g, &ctx.c)) throw std::runtime_error(std::string("bdpt_ctx_create: ") + bdpt_last_error(nullptr));
-            if (from_image) check(bdpt_scene_upload_image(ctx.c, options.scene_image, options.scene_image_bytes, 0), ctx.c, "bdpt_scene_upload_image");
+            if (from_image) check(bdpt_scene_upload_image(ctx.c, image, image_bytes, 0), ctx.c, "bdpt_scene_upload_image");
             else check(bdpt_scene_upload(ctx.c, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx.c, "bdpt_scene_upload");
             check(bdpt_film_clear(ctx.c, W, H), ctx.c, "bdpt_film_clear");
             bdpt_render_opts o{};

@@ -252,3 +252,28 @@ def test_cli_cache_renders_the_same_png(bdpt, tmp_path):
     for p in pngs[1:]:
         d = np.abs(p.astype(int) - pngs[0].astype(int))
         assert d.max() <= 1 and (d > 0).mean() < 0.01
+
+
+@pytest.mark.gpu
+def test_cli_two_gpus_share_one_scene_image(bdpt, tmp_path):
+    """`bdpt --gpus 2`: camera::render builds the scene image once and uploads it to both contexts (host/camera.cpp);
+    strata are sharded, the films summed on the host -- the PNG must equal the one-GPU run's."""
+    import subprocess
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from test_loader import decode_png
+    from tools import make_standin_scenes as ms
+    ms.generate(detail=2, quiet=True)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "bidirectional-path-tracer_b200", "bdpt")
+    scene = os.path.join(root, "scenes", "coffee_machine.yaml")
+    pngs = []
+    for g in (1, 2):
+        r = subprocess.run([exe, scene, "--res", "96x54", "--spp", "16", "--depth", "8", "--seed", "4", "--gpus", str(g), "--out", "g%d.png" % g],
+                           cwd=tmp_path, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-1000:]
+        assert "on %d GPU(s)" % g in r.stderr
+        pngs.append(decode_png(tmp_path / "output" / ("g%d.png" % g)))
+    d = np.abs(pngs[0].astype(int) - pngs[1].astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 0.01
