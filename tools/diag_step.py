@@ -10,7 +10,11 @@ cam = sf.camera_with(bench.WIDTH, bench.HEIGHT, bench.SPP, bench.DEPTH)
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 6
 STREAMS, BATCH = int(os.environ.get("STREAMS", "0")), int(os.environ.get("BATCH", "0"))
 with b.Context(0) as ctx:
-    ctx.upload(sf.verts, sf.mat_id, sf.materials)
+    if os.environ.get("USE_IMAGE"):
+        with b.SceneImage.build(sf.verts, sf.mat_id, sf.materials) as img:
+            ctx.upload_image(img)
+    else:
+        ctx.upload(sf.verts, sf.mat_id, sf.materials)
     ctx.film_clear(bench.WIDTH, bench.HEIGHT)
     for s in range(3):
         ctx.render(cam, seed=1, bvh=b.BVH_FAST, strata=(4 * s, 4 * s + 4, 1), clear=False, height=bench.HEIGHT, streams=STREAMS, batch_samples=BATCH)
