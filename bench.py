@@ -14,7 +14,14 @@ reduce at the end of the timed region (one reduce per frame).
 
 value  = samples of all ranks / device time of the K steps (inputs resident in HBM).
 e2e    = same metric through the host-facing call sequence: scene upload from host buffers (BVH build +
-         H2D), K steps, film read-back (D2H) — everything a camera::render call pays.
+         H2D), K steps, film read-back (D2H) — everything a camera::render call pays.  Median of three passes,
+         each on a fresh context.
+e2e_scene_image = the same with the scene handed over as a prebuilt scene image in pinned host memory
+         (bdpt_scene_upload_image: one allocation + one H2D copy inside the timed region; flatten and tree
+         builds outside it, as the reference arm's BVH build is).  Reported beside e2e, never instead of it.
+bvh_microbench = BASELINE.json config 2 (16,777,216 fixed-seed rays): device-resident, pinned host buffers
+         through the C-ABI's chunked copy/trace pipeline, and pageable host buffers.
+clocks = SM clock and throttle reasons sampled through NVML every 10 ms during the timed region (rank 0).
 """
 import argparse
 import ctypes
