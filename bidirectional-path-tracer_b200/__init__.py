@@ -25,13 +25,13 @@ HIT_DTYPE = np.dtype([("t", "<f8"), ("u", "<f8"), ("v", "<f8"), ("prim", "<u4"),
 EXPORTS = [
     "bdpt_ctx_create", "bdpt_ctx_destroy", "bdpt_last_error", "bdpt_scene_upload", "bdpt_scene_upload_ex", "bdpt_bvh_info",
     "bdpt_bvh_leaf_order", "bdpt_host_bvh_build", "bdpt_trace", "bdpt_visible", "bdpt_render",
-    "bdpt_film_clear", "bdpt_film_device_ptr", "bdpt_film_download", "bdpt_film_to_rgb8", "bdpt_stats",
+    "bdpt_film_clear", "bdpt_film_device_ptr", "bdpt_film_download", "bdpt_film_size", "bdpt_film_to_rgb8", "bdpt_stats",
     "bdpt_stats_reset", "bdpt_last_device_ms", "bdpt_sync", "bdpt_kernel_times",
     "bdpt_scene_file_load", "bdpt_scene_file_free", "bdpt_scene_file_info", "bdpt_scene_file_copy",
     "bdpt_write_png", "bdpt_host_last_error",
     "bdpt_scene_image_build", "bdpt_scene_image_free", "bdpt_scene_image_info", "bdpt_scene_image_last_error",
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
-    "bdpt_scene_source_key", "bdpt_scene_file_open_cached",
+    "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
 ]
 
 
@@ -109,6 +109,8 @@ def lib():
         L.bdpt_film_clear.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.bdpt_film_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         L.bdpt_film_download.argtypes = [C.c_void_p, C.c_void_p]
+        L.bdpt_film_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.bdpt_test_filter32.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_double, C.c_int, C.POINTER(C.c_float)]
         L.bdpt_film_to_rgb8.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.bdpt_stats.argtypes = [C.c_void_p, C.c_void_p]
         L.bdpt_stats_reset.argtypes = [C.c_void_p]
@@ -151,10 +153,24 @@ def make_materials(mats):
     return arr
 
 
+def image_height(width, aspect_ratio):
+    """The reference's rule (camera.h:161-162), which bdpt_render applies: the film has this many rows."""
+    return max(1, int(width / aspect_ratio))
+
+
+def aspect_for(width, height):
+    """width / height (scene_loader.h:445) -- nudged down by ulps for the ~2 % of (W, H) pairs, e.g. 7x100 or
+    23x480, where int(W / (W / H)) truncates to H - 1, so that the reference's rule yields `height` rows."""
+    a = float(width) / float(height)
+    while image_height(width, a) != int(height):
+        a = float(np.nextafter(a, 0.0))
+    return a
+
+
 def make_camera(width, height, spp, depth, lookfrom, lookat, vfov=90.0, vup=(0, 1, 0), background=(0, 0, 0),
                 focus_dist=10.0):
     c = Camera()
-    c.aspect_ratio = float(width) / float(height)  # scene_loader.h:445
+    c.aspect_ratio = aspect_for(width, height)
     c.image_width, c.samples_per_pixel, c.max_depth = int(width), int(spp), int(depth)
     c.background[:] = background
     c.vfov = vfov
@@ -314,7 +330,7 @@ class SceneFile:
         c = Camera.from_buffer_copy(self.camera)
         if width and height:
             c.image_width = int(width)
-            c.aspect_ratio = float(width) / float(height)
+            c.aspect_ratio = aspect_for(width, height)
         if spp:
             c.samples_per_pixel = int(spp)
         if depth is not None:
@@ -418,9 +434,14 @@ class Context:
 
     def render(self, cam, seed=0, bvh=BVH_REFERENCE, strata=(0, 0, 1), rows=(0, 0), batch_samples=0, clear=True,
                height=None, stats=False, streams=0, serial=False):
-        """camera::render's sample loop; returns nothing — read the film with film()."""
+        """camera::render's sample loop; returns nothing — read the film with film().  The film's row count is
+        the reference's int(image_width / aspect_ratio) (camera.h:161-162), decided by the library; `height`, when
+        given, is only checked against it (make_camera / camera_with pick an aspect ratio that yields it)."""
         W = cam.image_width
-        H = height if height is not None else max(1, int(W / cam.aspect_ratio))
+        H = image_height(W, cam.aspect_ratio)
+        if height is not None and int(height) != H:
+            raise ValueError("height=%d, but image_width %d / aspect_ratio %r gives %d rows (camera.h:161); build the camera "
+                             "with make_camera(width, height, ...)" % (height, W, cam.aspect_ratio, H))
         if clear or self.film_shape != (H, W, 3):
             self.film_clear(W, H)
         o = RenderOpts()
@@ -432,6 +453,13 @@ class Context:
         o.flags = (RENDER_STATS if stats else 0) | (RENDER_SERIAL if serial else 0)
         o.streams = streams
         self._chk(lib().bdpt_render(self._h, C.byref(cam), C.byref(o)), "bdpt_render")
+        if self.film_size() != (W, H):   # one source of truth: the library's film
+            raise BdptError("film is %r after bdpt_render, expected %r" % (self.film_size(), (W, H)))
+
+    def film_size(self):
+        w, h = C.c_int(0), C.c_int(0)
+        self._chk(lib().bdpt_film_size(self._h, C.byref(w), C.byref(h)), "bdpt_film_size")
+        return w.value, h.value
 
     def film(self, out=None):
         """The fp64 RGB sum film (camera.h:55) copied to the host; `out`: a C-contiguous float64 array of

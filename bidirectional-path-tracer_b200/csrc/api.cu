@@ -3,6 +3,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <cmath>
 #include <cstring>
 #include <exception>
 #include <stdexcept>
@@ -12,6 +13,7 @@
 #include "traverse_ref.cuh"
 #include "traverse_fast.cuh"
 #include "traverse_walk.cuh"
+#include "traverse_w32.cuh"
 
 using namespace bdpt;
 
@@ -41,6 +43,13 @@ void free_scene(bdpt_ctx* ctx) {
     for (void* p : ctx->scene_allocs) cudaFree(p);
     ctx->scene_allocs.clear();
     ctx->have_scene = false;
+}
+
+// ---------------------------------------------------------------- fp32 triangle records of the walk's pre-filter
+__global__ void k_make_tris32(const TriGeom* __restrict__ fast_tris, const uint32_t* __restrict__ fast_prims, uint32_t n,
+                              Tri32* __restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) out[k] = make_tri32(fast_tris[k], fast_prims[k]);
 }
 
 // ---------------------------------------------------------------- batch kernels
@@ -97,6 +106,91 @@ __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_trace(Scene
         w.x = h.v;
         w.y = __longlong_as_double((long long)(unsigned long long)h.prim);
         o[1] = w;
+    }
+    if (STATS) {
+        atomicAdd(&stats[ST_NODE], (unsigned long long)st.nodes);
+        atomicAdd(&stats[ST_TRI], (unsigned long long)st.tris);
+    }
+}
+
+// hittable::hit over a ray batch on the warp-synchronous fp32 walk (traverse_w32.cuh): persistent warps pull rays
+// through one atomic cursor, so a lane whose ray is decided takes the next one instead of idling behind its warp's
+// longest walk.  The fp64 ray is re-read from the batch for the exact tests.  Rays the fp32 walk cannot take (zero
+// direction component, far origin) or that end in a tie / knife edge go through the reference tree right here.
+#ifndef BDPT_B32_BLOCKS
+#define BDPT_B32_BLOCKS 16
+#endif
+__device__ __forceinline__ RayD load_batch_ray(const bdpt_ray* __restrict__ rays, uint64_t i) {
+    const double2* q = reinterpret_cast<const double2*>(rays + i);
+    const double2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
+    RayD r;
+    r.o = mk(a.x, a.y, b.x); r.d = mk(b.y, c.x, c.y); r.tmin = e.x; r.tmax = e.y;
+    return r;
+}
+__device__ __forceinline__ void store_hit(bdpt_hit* __restrict__ out, uint64_t i, bool found, HitD h) {
+    double2* o = reinterpret_cast<double2*>(out + i);
+    if (!found) { h.t = 0.0; h.u = 0.0; h.v = 0.0; h.prim = BDPT_MISS; }
+    o[0] = make_double2(h.t, h.u);
+    double2 w;
+    w.x = h.v;
+    w.y = __longlong_as_double((long long)(unsigned long long)h.prim);
+    o[1] = w;
+}
+
+template <bool ANY, bool STATS>
+__global__ void __launch_bounds__(kTraceBlock, BDPT_B32_BLOCKS) k_trace_w32(SceneView sc, const bdpt_ray* __restrict__ rays, uint64_t n,
+                                                                            bdpt_hit* __restrict__ out, unsigned long long* stats,
+                                                                            unsigned long long* cursor, int knobs) {
+    StackEntry l_stack[32];
+    const int trips = knobs & 0x3F, nstep = (knobs >> 6) & 0xF, min_idle = (knobs >> 10) & 0x3F, t_leaf = (knobs >> 16) & 0xFF, t_node = (knobs >> 24) & 0xFF;
+    const int lane = threadIdx.x & 31;
+    Walk32<ANY, STATS> W;
+    W.cur = kWalkDry;
+    bool have = false, exhausted = false;
+    int result = WALK_YIELD;
+    uint64_t idx = 0;
+    TravStats st{0, 0};
+    for (;;) {
+        __syncwarp();
+        if (result == WALK32_FLUSH) {
+            HitD h;
+            W.decide(sc, load_batch_ray(rays, idx), h, false);
+            result = WALK_YIELD;
+        }
+        if (result != WALK_YIELD) {   // decided, or never walkable: the exact finish
+            const RayD r = load_batch_ray(rays, idx);
+            HitD h;
+            int rc = result;
+            if (rc == TR_HIT) rc = W.decide(sc, r, h, true);
+            if (STATS && have) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; }
+            bool found = rc == TR_HIT;
+            if (rc == TR_DEFER) found = traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st);
+            store_hit(out, idx, found, h);
+            have = false;
+            result = WALK_YIELD;
+        }
+        // refill the idle lanes
+        {
+            const bool need = !have;
+            const uint32_t mask = __ballot_sync(0xFFFFFFFFu, need);
+            if (mask && !exhausted && (mask == 0xFFFFFFFFu || __popc(mask) >= min_idle)) {
+                const int leader = __ffs(mask) - 1;
+                unsigned long long base = 0;
+                if (lane == leader) base = atomicAdd(cursor, (unsigned long long)__popc(mask));
+                base = __shfl_sync(0xFFFFFFFFu, base, leader);
+                if (base + uint64_t(__popc(mask)) >= n) exhausted = true;
+                const uint64_t my = base + uint64_t(__popc(mask & ((1u << lane) - 1u)));
+                if (need && my < n) {
+                    idx = my;
+                    const RayD r = load_batch_ray(rays, idx);
+                    if (walk_eligible(sc, r)) { W.init(sc, r); have = true; }
+                    else result = TR_DEFER;
+                }
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
+        const int rc = W.run(sc, l_stack, have, trips, nstep, t_leaf, t_node, exhausted ? 0 : min_idle);
+        if (have) result = rc;
     }
     if (STATS) {
         atomicAdd(&stats[ST_NODE], (unsigned long long)st.nodes);
@@ -163,6 +257,27 @@ __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_visible(Sce
 }
 
 }  // namespace
+
+// Everything the fp32 walk (traverse_w32.cuh) needs beyond the uploaded scene: the leaf-ordered triangles in fp32 and
+// the coordinate bound of its error terms.  Derived on the device (10^7 triangles: ~1 ms) for every way a scene
+// arrives -- host-built tree, device-built tree, scene image -- so neither the builders nor the image format change.
+int bdpt::derive_walk32(bdpt_ctx* ctx, SceneView& v) {
+    const double m = std::max(std::max(std::fabs(v.center.x), std::fabs(v.center.y)), std::fabs(v.center.z)) + 0.5 * v.extent;
+    float f = float(m * 1.000001);
+    if (double(f) < m) f = std::nextafterf(f, INFINITY);
+    v.vmax32 = f;
+    void* p = nullptr;
+    const size_t n = std::max<size_t>(v.n_tris, 1);
+    BDPT_CUDA(ctx, cudaMalloc(&p, n * sizeof(Tri32)));
+    ctx->scene_allocs.push_back(p);
+    if (v.n_tris) {
+        k_make_tris32<<<(v.n_tris + 255) / 256, 256, 0, ctx->stream>>>(v.fast_tris, v.fast_prims, v.n_tris, static_cast<Tri32*>(p));
+        ctx->launches += 1;
+        BDPT_CUDA(ctx, cudaGetLastError());
+    }
+    v.tris32 = static_cast<const Tri32*>(p);
+    return BDPT_OK;
+}
 
 // ---------------------------------------------------------------- C-ABI
 extern "C" {
@@ -292,6 +407,8 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
     v.light_total_area = h.light_total_area;
     v.extent = h.extent;
     v.center = mk(h.center[0], h.center[1], h.center[2]);
+    rc = derive_walk32(ctx, v);
+    if (rc) { free_scene(ctx); return rc; }
     BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->view = v;
     ctx->have_scene = true;
@@ -361,7 +478,24 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
         return BDPT_OK;
     }
 #define BDPT_LAUNCH(B, A, S) k_trace<B, A, S><<<grid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st)
-    if (bvh == BDPT_BVH_REFERENCE) {
+    static const bool walk32 = [] { const char* e = std::getenv("BDPT_WALK32"); return e ? std::atoi(e) != 0 : true; }();
+    if (bvh == BDPT_BVH_FAST && walk32 && !(v.use_wide & 3u)) {
+        // round 2: persistent warps on the warp-synchronous fp32 walk; the cursor is a stream-ordered scratch word
+        auto knob = [](const char* name, int dflt) { const char* e = std::getenv(name); return e ? std::atoi(e) : dflt; };
+        const int knobs = int(uint32_t(knob("BDPT_W32_TRIPS", 16) & 0x3F) | (uint32_t(knob("BDPT_W32_NSTEP", 4) & 0xF) << 6) |
+                              (uint32_t(knob("BDPT_W32_IDLE", 8) & 0x3F) << 10) | (uint32_t(knob("BDPT_W32_TLEAF", 8) & 0xFF) << 16) |
+                              (uint32_t(knob("BDPT_W32_TNODE", 4) & 0xFF) << 24));
+        unsigned long long* cursor = nullptr;
+        BDPT_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void**>(&cursor), sizeof(unsigned long long), stream));
+        BDPT_CUDA(ctx, cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), stream));
+        int sms = 148, per_sm = BDPT_B32_BLOCKS;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_w32<false, false>, kTraceBlock, 0) != cudaSuccess || per_sm < 1) per_sm = BDPT_B32_BLOCKS;
+        const unsigned pg = std::min<unsigned>(grid, unsigned(sms * per_sm));
+        if (any) { if (stats) k_trace_w32<true, true><<<pg, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st, cursor, knobs); else k_trace_w32<true, false><<<pg, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st, cursor, knobs); }
+        else     { if (stats) k_trace_w32<false, true><<<pg, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st, cursor, knobs); else k_trace_w32<false, false><<<pg, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st, cursor, knobs); }
+        BDPT_CUDA(ctx, cudaFreeAsync(cursor, stream));
+    } else if (bvh == BDPT_BVH_REFERENCE) {
         if (any) { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, true, false); }
         else     { if (stats) BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, true); else BDPT_LAUNCH(BDPT_BVH_REFERENCE, false, false); }
     } else if ((v.use_wide & (any ? 2u : 1u)) && v.wide_nodes) {   // bits 8..15 of use_wide: the walk's time slice
@@ -513,6 +647,14 @@ int bdpt_film_device_ptr(bdpt_ctx* ctx, void** ptr, uint64_t* n_doubles) {
     return BDPT_OK;
 }
 
+int bdpt_film_size(bdpt_ctx* ctx, int* width, int* height) {
+    if (!ctx) return BDPT_ERR_ARG;
+    if (!ctx->film) { ctx->err = "no film"; return BDPT_ERR_STATE; }
+    if (width) *width = ctx->film_w;
+    if (height) *height = ctx->film_h;
+    return BDPT_OK;
+}
+
 int bdpt_film_download(bdpt_ctx* ctx, double* film_sum) {
     if (!ctx || !film_sum) return BDPT_ERR_ARG;
     if (!ctx->film) { ctx->err = "no film"; return BDPT_ERR_STATE; }
@@ -590,6 +732,25 @@ int bdpt_sync(bdpt_ctx* ctx) {
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
     BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return BDPT_OK;
+}
+
+// Host-only test hook (tests/test_host.py): the walk's fp32 pre-filter (traverse_w32.cuh) on one ray / one triangle,
+// exactly the arithmetic the kernels run (the same inline functions compiled for the host; only the device's
+// approximate division differs, inside the stated inflation).  ray = o, d, tmin, tmax; best = current upper bound.
+// Returns 0 reject / 1 candidate / 2 certain, *t_hi as filter32.
+int bdpt_test_filter32(const double* ray, double best, const double* tri_v0e1e2, double vmax, int any, float* t_hi) {
+    if (!ray || !tri_v0e1e2) return BDPT_ERR_ARG;
+    TriGeom t{};
+    t.v0x = tri_v0e1e2[0]; t.v0y = tri_v0e1e2[1]; t.v0z = tri_v0e1e2[2];
+    t.e1x = tri_v0e1e2[3]; t.e1y = tri_v0e1e2[4]; t.e1z = tri_v0e1e2[5];
+    t.e2x = tri_v0e1e2[6]; t.e2y = tri_v0e1e2[7]; t.e2z = tri_v0e1e2[8];
+    const Tri32 T = make_tri32(t, 0u);
+    const Ray32 R = make_ray32(ray, ray + 3, ray[6], ray[7], f32_up(vmax * 1.000001));
+    float hi = 0.f;
+    const float b = f32_up(best);
+    const int f = any ? filter32<true>(R, b, T.q0, T.q1, T.q2, hi) : filter32<false>(R, b, T.q0, T.q1, T.q2, hi);
+    if (t_hi) *t_hi = hi;
+    return f;
 }
 
 }  // extern "C"

@@ -61,6 +61,8 @@ inline uint32_t wide_walk_mode() {
 }
 
 int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts);
+// api.cu: the fp32 triangle records + error scale of the warp-synchronous walk (traverse_w32.cuh), queued on ctx->stream
+int derive_walk32(bdpt_ctx* ctx, SceneView& v);
 void render_free(bdpt_ctx* ctx);
 // gpu_bvh.cu: the fast tree built on the device from triangles already uploaded (queued on ctx->stream)
 int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const double lo[3], const double hi[3], double extent,

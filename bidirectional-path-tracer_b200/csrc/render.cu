@@ -28,6 +28,7 @@
 #include "render_math.cuh"
 #include "traverse_fast.cuh"
 #include "traverse_walk.cuh"
+#include "traverse_w32.cuh"
 
 namespace bdpt {
 
@@ -508,6 +509,100 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
     }
 }
 
+
+// ------------------------------------------------------------------ K1, round 2: warp-synchronous fp32 walk + exact fp64 finish
+// (traverse_w32.cuh).  Same persistent-warp frame as k_trace_fast — dynamic fetch, front blocks for the rays
+// that need the reference tree — but the 32 lanes of a warp take every loop trip together, the walk carries no fp64
+// state (the ray is re-read from its path record for the exact tests at the meeting point), and the register
+// budget buys more resident warps.
+#ifndef BDPT_W32_BLOCKS
+#define BDPT_W32_BLOCKS 16
+#endif
+constexpr int kW32BlocksPerSM = BDPT_W32_BLOCKS;   // blocks of 64 threads per SM (register cap = 65536 / (64 * this))
+
+// knobs: bits 0-5 trips per slice | 6-9 node steps per trip | 10-15 idle lanes that end a slice (refill) | 16-23 waiting
+// leaves that start the pre-filter | 24-31 walkers at or below which it starts anyway
+struct W32Knobs { int trips, nstep, min_idle, t_leaf, t_node; };
+__device__ __forceinline__ W32Knobs unpack_knobs(int k) {
+    W32Knobs r;
+    r.trips = k & 0x3F; r.nstep = (k >> 6) & 0xF; r.min_idle = (k >> 10) & 0x3F; r.t_leaf = (k >> 16) & 0xFF; r.t_node = (k >> 24) & 0xFF;
+    return r;
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_trace_w32(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
+                                                                       const uint32_t* __restrict__ n_ptr, int dn, int ex,
+                                                                       uint32_t n_def_blocks, int knobs, double* film,
+                                                                       unsigned long long* stats) {
+    BDPT_DECLARE_STACK;
+    if (blockIdx.x < n_def_blocks) {   // rays the previous launch handed to the reference tree, one per warp (lane 0)
+        int cls = -1;
+        uint32_t pid = 0;
+        bool ended = false;
+        const uint32_t idx = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5);
+        if ((threadIdx.x & 31) == 0 && idx < w.counters[C_EXACT0 + (ex ^ 1)]) {
+            pid = w.q_exact[ex ^ 1][idx] & ~kSlowFlag;
+            const RayD r = load_path_ray(w, pid);
+            HitD h;
+            TravStats ts{0, 0};
+            const bool found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
+            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            cls = finish_trace(sc, f, w, pid, found, h, film);
+            ended = cls < 0;
+        }
+        bin_by_material(w, cls, pid);
+        retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+        return;
+    }
+    const uint32_t n = *n_ptr;
+    const W32Knobs kn = unpack_knobs(knobs);
+    Walk32<false, STATS> W;
+    W.cur = kWalkDry;
+    bool have = false, exhausted = false;
+    int result = WALK_YIELD;   // TR_HIT: walk over, decide | WALK32_FLUSH | TR_DEFER: not walkable here
+    uint32_t pid = 0;
+    for (;;) {
+        __syncwarp();
+        if (result == WALK32_FLUSH) {   // candidate list full: the exact test keeps the winner, the walk goes on
+            HitD h;
+            W.decide(sc, load_path_ray(w, pid), h, false);
+            result = WALK_YIELD;
+        }
+        const bool fin = result != WALK_YIELD;
+        if (__any_sync(0xFFFFFFFFu, fin)) {
+            int cls = -1;
+            bool ended = false, defer = false;
+            if (fin) {
+                int rc = result;
+                HitD h;
+                if (rc == TR_HIT) rc = W.decide(sc, load_path_ray(w, pid), h, true);
+                if (rc == TR_DEFER) defer = true;
+                else {
+                    if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+                    cls = finish_trace(sc, f, w, pid, rc == TR_HIT, h, film);
+                    ended = cls < 0;
+                }
+                have = false;
+                result = WALK_YIELD;
+            }
+            const uint32_t slot = warp_append(w.counters + C_EXACT0 + ex, defer);
+            if (defer) w.q_exact[ex][slot] = pid;
+            bin_by_material(w, cls, pid);
+            retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
+        }
+        const uint32_t my = warp_fetch(w.counters + C_CURSOR, !have, n, exhausted, kn.min_idle);
+        if (my != 0xFFFFFFFFu) {
+            pid = queue[my];
+            const RayD r = load_path_ray(w, pid);
+            if (walk_eligible(sc, r)) { W.init(sc, r); have = true; }
+            else result = TR_DEFER;   // fp64 slabs or the reference tree: the next launch's front blocks
+        }
+        if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
+        const int rc = W.run(sc, l_stack, have, kn.trips, kn.nstep, kn.t_leaf, kn.t_node, exhausted ? 0 : kn.min_idle);
+        if (have) result = rc;
+    }
+}
+
 // hit point and face-forwarded geometric normal (ray.h:21-23, hittable.h:20-26)
 struct Surf { D3 o, d, T, p, n; bool front; uint32_t prim, draws; int32_t remaining; };
 __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint32_t pid) {
@@ -975,6 +1070,92 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
     }
 }
 
+
+// ------------------------------------------------------------------ K4 stage 2, round 2: the shadow walk on traverse_w32.cuh
+// Any-hit: a triangle the fp32 filter finds certainly inside the segment ends the walk at once, without any fp64
+// work; only what the filter cannot decide (a graze, a hit within ~1e-5 of an end of the segment) reaches the
+// exact test.  The far endpoint's own triangle, which k_shadow_pre has already cleared, is skipped by ID.
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_shadow_w32(SceneView sc, WF w, SQ q, int sx, uint32_t n_slow_blocks, int knobs,
+                                                                        double* film, unsigned long long* stats) {
+    BDPT_DECLARE_STACK;
+    if (blockIdx.x < n_slow_blocks) {   // parked segments (they need the reference tree): one per warp at a time
+        const uint32_t n = min(w.counters[C_SLOW_S0 + (sx ^ 1)], uint32_t(w.sscap));
+        if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(&stats[ST_DEFER_SHADOW], (unsigned long long)n);
+        if ((threadIdx.x & 31) != 0) return;
+        for (uint32_t i = blockIdx.x * kFrontPerBlock + (threadIdx.x >> 5); i < n; i += n_slow_blocks * kFrontPerBlock) {
+            const SlowShadow* e = w.ss[sx ^ 1] + i;
+            const double2* pq = reinterpret_cast<const double2*>(e);
+            const double2 q0 = pq[0], q1 = pq[1], q2 = pq[2], q3 = pq[3], q4 = pq[4];
+            const int4 q5 = reinterpret_cast<const int4*>(e)[5];
+            RayD r;
+            r.o = mk(q0.x, q0.y, q1.x); r.d = mk(q1.y, q2.x, q2.y); r.tmin = 0.001; r.tmax = q3.x;
+            HitD h;
+            TravStats ts{0, 0};
+            const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
+            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
+        }
+        return;
+    }
+    const uint32_t n = q.cnt[SQ_LIVE];
+    const W32Knobs kn = unpack_knobs(knobs);
+    Walk32<true, STATS> W;
+    W.cur = kWalkDry;
+    bool have = false, exhausted = false;
+    int result = WALK_YIELD;
+    uint32_t idx = 0;
+    for (;;) {
+        __syncwarp();
+        if (result == WALK32_FLUSH) {
+            HitD h;
+            W.decide(sc, load_shadow_ray(q, idx), h, false);
+            result = WALK_YIELD;
+        }
+        const bool fin = result != WALK_YIELD;
+        if (__any_sync(0xFFFFFFFFu, fin)) {
+            bool park = false;
+            if (fin) {
+                int rc = result;
+                HitD h;
+                if (rc == TR_HIT) rc = W.occluded ? TR_HIT : W.decide(sc, load_shadow_ray(q, idx), h, true);
+                park = rc == TR_DEFER;
+                if (STATS && !park) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+                if (rc == TR_MISS) film_add(film, q.pix[idx], mk(q.cx[idx], q.cy[idx], q.cz[idx]));
+                have = false;
+                result = WALK_YIELD;
+            }
+            const uint32_t slot = warp_append(w.counters + C_SLOW_S0 + sx, park);
+            if (park) {
+                const RayD r = load_shadow_ray(q, idx);
+                const D3 c = mk(q.cx[idx], q.cy[idx], q.cz[idx]);
+                const uint32_t pix = q.pix[idx];
+                if (slot < uint32_t(w.sscap)) {
+                    SlowShadow* e = w.ss[sx] + slot;
+                    double2* pq = reinterpret_cast<double2*>(e);
+                    pq[0] = make_double2(r.o.x, r.o.y); pq[1] = make_double2(r.o.z, r.d.x); pq[2] = make_double2(r.d.y, r.d.z);
+                    pq[3] = make_double2(r.tmax, c.x); pq[4] = make_double2(c.y, c.z);
+                    reinterpret_cast<int4*>(e)[5] = make_int4(int(pix), 1, 0, 0);
+                } else {   // parking lot full: settle it here
+                    HitD h;
+                    const bool found = traverse_ref<true, false>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, nullptr);
+                    if (!found) film_add(film, pix, c);
+                }
+            }
+        }
+        const uint32_t my = warp_fetch(q.cnt + SQ_CURSOR, !have, n, exhausted, kn.min_idle);
+        if (my != 0xFFFFFFFFu) {
+            idx = q.live[my];
+            const RayD r = load_shadow_ray(q, idx);
+            if (walk_eligible(sc, r)) { W.init(sc, r, q.far[idx]); have = true; }
+            else result = TR_DEFER;
+        }
+        if (!__any_sync(0xFFFFFFFFu, have || result != WALK_YIELD)) break;
+        const int rc = W.run(sc, l_stack, have, kn.trips, kn.nstep, kn.t_leaf, kn.t_node, exhausted ? 0 : kn.min_idle);
+        if (have) result = rc;
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------ host side
@@ -1124,6 +1305,9 @@ struct Job {
     uint32_t limit, limit_shadow;    // work limits of the bulk traversal launches (traverse_walk.cuh); 0 = none
     unsigned resident_blocks;        // blocks of a traversal kernel the device keeps resident (persistent grids)
     int threshold;                   // dynamic fetch: a walk yields when fewer lanes than this are still walking
+    bool walk32;                     // bulk traversal = the warp-synchronous fp32 walk (traverse_w32.cuh); false: round 1's per-lane walk
+    int knobs32;                     // its time-slice / refill / leaf-batch parameters (unpack_knobs)
+    unsigned resident32;             // blocks of k_trace_w32 / k_shadow_w32 the device keeps resident
 };
 
 // One worker: a wavefront of B slots, refilled from the call's shared sample counter until it runs dry.
@@ -1164,8 +1348,11 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
                 wk.launches += 1;
             }
             // persistent: no more blocks than stay resident; the warps pull their segments from q.live
-            const unsigned gm = ns_bound ? std::min(grid_for(ns_bound, kBlock), J.resident_blocks) : 0u;
-            if (want_stats) k_shadow_fast<true><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.limit_shadow, J.film, J.d_stats);
+            const unsigned gm = ns_bound ? std::min(grid_for(ns_bound, kBlock), J.walk32 ? J.resident32 : J.resident_blocks) : 0u;
+            if (J.walk32) {
+                if (want_stats) k_shadow_w32<true><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.knobs32, J.film, J.d_stats);
+                else k_shadow_w32<false><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.knobs32, J.film, J.d_stats);
+            } else if (want_stats) k_shadow_fast<true><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.limit_shadow, J.film, J.d_stats);
             else k_shadow_fast<false><<<kFrontBlocks + gm, kBlock, 0, st2>>>(sc, wf, q, sx, kFrontBlocks, J.threshold, J.limit_shadow, J.film, J.d_stats);
             sx ^= 1;
         }
@@ -1199,8 +1386,11 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
 #define BDPT_TP(B, S) k_trace_paths<B, S><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.limit, J.film, J.d_stats)
         if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
         else {
-            const unsigned gp = std::min(g, J.resident_blocks);
-            if (want_stats) k_trace_fast<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
+            const unsigned gp = std::min(g, J.walk32 ? J.resident32 : J.resident_blocks);
+            if (J.walk32) {
+                if (want_stats) k_trace_w32<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.knobs32, J.film, J.d_stats);
+                else k_trace_w32<false><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.knobs32, J.film, J.d_stats);
+            } else if (want_stats) k_trace_fast<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
             else k_trace_fast<false><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
         }
 #undef BDPT_TP
@@ -1399,6 +1589,21 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (const char* e = std::getenv("BDPT_T_LEAF")) t_leaf = std::atoi(e);
     if (const char* e = std::getenv("BDPT_T_WALK")) t_walk = std::atoi(e);
     J.threshold = int(uint32_t(slice & 0xFF) | (uint32_t(min_idle & 0xFF) << 8) | (uint32_t(t_leaf & 0xFF) << 16) | (uint32_t(t_walk & 0xFF) << 24));
+    {
+        // round 2's bulk traversal (BDPT_WALK32=0: round 1's per-lane walk, kept for A/B runs)
+        J.walk32 = true;
+        if (const char* e = std::getenv("BDPT_WALK32")) J.walk32 = std::atoi(e) != 0;
+        int trips = 16, nstep = 4, idle = 8, tleaf = 8, tnode = 4;
+        if (const char* e = std::getenv("BDPT_W32_TRIPS")) trips = std::atoi(e);
+        if (const char* e = std::getenv("BDPT_W32_NSTEP")) nstep = std::atoi(e);
+        if (const char* e = std::getenv("BDPT_W32_IDLE")) idle = std::atoi(e);
+        if (const char* e = std::getenv("BDPT_W32_TLEAF")) tleaf = std::atoi(e);
+        if (const char* e = std::getenv("BDPT_W32_TNODE")) tnode = std::atoi(e);
+        J.knobs32 = int(uint32_t(trips & 0x3F) | (uint32_t(nstep & 0xF) << 6) | (uint32_t(idle & 0x3F) << 10) | (uint32_t(tleaf & 0xFF) << 16) | (uint32_t(tnode & 0xFF) << 24));
+        int per_sm = kW32BlocksPerSM;   // what the registers ptxas really used allow
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_w32<false>, kBlock, 0) != cudaSuccess || per_sm < 1) per_sm = kW32BlocksPerSM;
+        J.resident32 = unsigned(sms * per_sm);
+    }
     std::atomic<int64_t> next_sample{0};
     J.next = &next_sample;
 

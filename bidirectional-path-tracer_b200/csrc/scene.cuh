@@ -75,6 +75,8 @@ struct SceneView {
     const FastNode* fast_nodes;
     const uint32_t* fast_prims;   // leaf-ordered prim IDs for the fast BVH
     const TriGeom* fast_tris;     // the triangles in that order (copy): leaf k's triangles are fast_tris[first .. first+cnt)
+    const struct Tri32* tris32;   // the same triangles in fp32 for the walk's pre-filter (traverse_w32.cuh), built at upload
+    float vmax32;                 // >= the largest |coordinate| of any vertex (pre-filter error scale)
     const uint32_t* dfs_rank;     // prim ID -> last position in the reference DFS leaf order (tie rule)
     const int32_t* ref_parent;    // reference node -> parent node (-1 for the root)
     const int32_t* prim_leaf;     // prim ID -> reference leaf node holding it

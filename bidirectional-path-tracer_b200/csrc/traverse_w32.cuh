@@ -1,0 +1,334 @@
+// Warp-synchronous fp32 walk with an exact fp64 finish ("walk32") — the bulk traversal of round 2.
+//
+// Why: the per-lane while-while walk of traverse_walk.cuh carries the ray in fp64, tests every triangle of every
+// visited leaf with the reference's fp64 Moller-Trumbore and lets the 32 lanes of a warp drift apart; ncu put it at
+// 8.4 (closest) / 4.7 (shadow) active lanes per instruction and 43 % issue-active at a 64-register cap
+// (profiles/r1_ncu_full_k_trace_fast_final.csv).  Here
+//   * the walk itself is fp32 only: ray, slabs AND a conservative fp32 Moller-Trumbore PRE-FILTER with rigorous error
+//     bounds.  A triangle the filter rejects is one the reference's fp64 test (triangle.h:41-74) rejects too, with a
+//     margin of ~1e-5 of the ray length against an fp64 noise of ~1e-13; what it cannot reject becomes a CANDIDATE
+//     (a leaf-order index in a 4-entry list);
+//   * all 32 lanes of a warp run the same loop trips: a trip is a few "pop if needed, then open ONE node" steps; a
+//     lane that reaches a leaf waits there, and the triangle pre-filter runs for all waiting lanes at once as soon as
+//     `t_leaf` lanes wait (or few lanes still walk) — so both phases execute with many lanes instead of 8 and 5;
+//   * the reference's fp64 test, the tie / knife-edge flagging and the DFS-order rule of traverse_fast.cuh run ONCE per
+//     ray over its candidates (typically one), at the warp's meeting point, for all finished lanes together.
+// The answers are those of traverse_fast_t / Walk: the candidate set always contains every triangle the exact test
+// could accept within [tmin, best] plus everything within the flagging bands, and the decision logic over that set
+// (decide() below) restates Walk::leaf_tests + Walk::finish over a list.
+//
+// Error bounds of the pre-filter (delta = 2^-24, round to nearest; inputs are the fp64 values rounded to fp32, so
+// each carries a relative error <= delta; rho >= |o|_inf + |v0|_inf, |T| <= sqrt(3) rho):
+//   pvec = d x e2      |dP|_inf <= 4 delta |d||e2|
+//   det  = e1 . pvec   |dDet|   <= 11 delta |d||e1||e2|
+//   U    = T . pvec    |dU|     <= 21 delta rho |d||e2|        (T = o - v0, |dT_i| <= 2.01 delta rho)
+//   V    = d . (T x e1)|dV|     <= 24 delta rho |d||e1|
+//   TN   = e2 . (T x e1) |dTN|  <= 24 delta rho |e1||e2|
+// The filter uses K = 2^-17 = 128 delta in place of 11 / 21 / 24 delta: >= 5x slack, which also covers the rounding of
+// the comparisons themselves and the reference's own fp64 rounding by ten orders of magnitude.
+#pragma once
+#include <cmath>
+#include <cstring>
+
+#include "traverse_walk.cuh"
+
+namespace bdpt {
+
+enum { WALK32_FLUSH = -2 };                  // run(): the candidate list is full; call decide(last = false) and continue
+constexpr int32_t kWalkPop = INT32_MIN + 1;  // cur: take the next stack entry (never a leaf code: first < 2^28 - 1)
+constexpr int kMaxCand = 4;
+constexpr float kFilterK = 7.62939453125e-06f;   // 2^-17
+
+// One triangle of the fast tree's leaf order in fp32 for the pre-filter: 48 B = 3 x LDG.128.
+//   q0 = v0.xyz, e1.x | q1 = e1.yz, e2.xy | q2 = e2.z, |e1| (rounded up), |e2| (rounded up), prim ID (bits)
+// Built on the device at upload from fast_tris / fast_prims (derive_walk32, api.cu).
+struct __align__(16) Tri32 { float4 q0, q1, q2; };
+static_assert(sizeof(Tri32) == 48, "Tri32 must be 48 bytes");
+
+// ---- the parts of the walk that are plain arithmetic, shared with the host so that a CPU test can hammer the
+// pre-filter against the exact fp64 test without a GPU (bdpt_test_filter32, tests/test_host.py)
+BDPT_HD float f32_down(double v) {
+#ifdef __CUDA_ARCH__
+    return __double2float_rd(v);
+#else
+    float f = float(v);
+    if (double(f) > v) f = std::nextafterf(f, -INFINITY);
+    return f;
+#endif
+}
+BDPT_HD float f32_up(double v) {
+#ifdef __CUDA_ARCH__
+    return __double2float_ru(v);
+#else
+    float f = float(v);
+    if (double(f) < v) f = std::nextafterf(f, INFINITY);
+    return f;
+#endif
+}
+BDPT_HD float fma32(float a, float b, float c) {
+#ifdef __CUDA_ARCH__
+    return __fmaf_rn(a, b, c);
+#else
+    return std::fmaf(a, b, c);
+#endif
+}
+BDPT_HD float div32(float a, float b) {   // device: the 2-ulp approximate quotient; its error is inside the 1e-6 inflation below
+#ifdef __CUDA_ARCH__
+    return __fdividef(a, b);
+#else
+    return a / b;
+#endif
+}
+
+BDPT_HD Tri32 make_tri32(const TriGeom& t, uint32_t prim) {
+    Tri32 r;
+    r.q0.x = float(t.v0x); r.q0.y = float(t.v0y); r.q0.z = float(t.v0z); r.q0.w = float(t.e1x);
+    r.q1.x = float(t.e1y); r.q1.y = float(t.e1z); r.q1.z = float(t.e2x); r.q1.w = float(t.e2y);
+    const double n1 = sqrt(t.e1x * t.e1x + t.e1y * t.e1y + t.e1z * t.e1z), n2 = sqrt(t.e2x * t.e2x + t.e2y * t.e2y + t.e2z * t.e2z);
+    r.q2.x = float(t.e2z); r.q2.y = f32_up(n1 * 1.0000001); r.q2.z = f32_up(n2 * 1.0000001);
+#ifdef __CUDA_ARCH__
+    r.q2.w = __uint_as_float(prim);
+#else
+    std::memcpy(&r.q2.w, &prim, 4);
+#endif
+    return r;
+}
+
+// the fp32 image of a ray: what the pre-filter reads
+struct Ray32 {
+    float ox, oy, oz, dx, dy, dz;
+    float tmin_t, best_t;        // conservative fp32 images of [tmin, tmax]: rounded down / up
+    float tmin_hi, tmax_lo;      // tmin rounded up, tmax rounded down: "certainly inside the interval"
+    float kD, kU, kT;            // pre-filter error scales: K |d|, K rho |d|, K rho
+};
+BDPT_HD Ray32 make_ray32(const double o[3], const double d[3], double tmin, double tmax, float vmax32) {
+    Ray32 r;
+    r.ox = float(o[0]); r.oy = float(o[1]); r.oz = float(o[2]);
+    r.dx = float(d[0]); r.dy = float(d[1]); r.dz = float(d[2]);
+    r.tmin_t = f32_down(tmin); r.tmin_hi = f32_up(tmin);
+    r.best_t = f32_up(tmax); r.tmax_lo = f32_down(tmax);
+    const float dn = f32_up(sqrt(double(r.dx) * r.dx + double(r.dy) * r.dy + double(r.dz) * r.dz) * 1.000001);
+    const float rho = fmaxf(fabsf(r.ox), fmaxf(fabsf(r.oy), fabsf(r.oz))) * 1.000001f + vmax32;
+    r.kD = kFilterK * dn; r.kU = kFilterK * rho * dn; r.kT = kFilterK * rho;
+    return r;
+}
+
+// The conservative pre-filter.  0: the reference's test rejects this triangle (or it cannot matter: beyond the
+// current bound / before tmin by more than every flagging band).  1: candidate.  2: candidate that the reference
+// certainly accepts, with t <= t_hi (closest) / certainly inside (tmin, tmax) (ANY).
+template <bool ANY>
+BDPT_HD int filter32(const Ray32& R, float best_t, const float4& q0, const float4& q1, const float4& q2, float& t_hi) {
+    const float e1x = q0.w, e1y = q1.x, e1z = q1.y, e2x = q1.z, e2y = q1.w, e2z = q2.x, n1 = q2.y, n2 = q2.z;
+    const float px = fma32(R.dy, e2z, -(R.dz * e2y)), py = fma32(R.dz, e2x, -(R.dx * e2z)), pz = fma32(R.dx, e2y, -(R.dy * e2x));
+    const float det = fma32(e1x, px, fma32(e1y, py, e1z * pz));
+    const float tx = R.ox - q0.x, ty = R.oy - q0.y, tz = R.oz - q0.z;
+    const float U = fma32(tx, px, fma32(ty, py, tz * pz));
+    const float qx = fma32(ty, e1z, -(tz * e1y)), qy = fma32(tz, e1x, -(tx * e1z)), qz = fma32(tx, e1y, -(ty * e1x));
+    const float V = fma32(R.dx, qx, fma32(R.dy, qy, R.dz * qz));
+    const float TN = fma32(e2x, qx, fma32(e2y, qy, e2z * qz));
+    const float m12 = n1 * n2;
+    const float eD = fmaxf(R.kD * m12, 1e-30f), eU = R.kU * n2, eV = R.kU * n1, eT = R.kT * m12;
+    const float adet = fabsf(det);
+    if (!(adet > eD)) return 1;   // sign of det unknown (grazing, sliver, NaN): only the exact test can tell
+    const bool neg = det < 0.f;
+    const float Us = neg ? -U : U, Vs = neg ? -V : V, Ts = neg ? -TN : TN;
+    const float eS = eD + eU + eV;
+    if (Us < -eU || Vs < -eV || Us + Vs > adet + eS) return 0;          // u < 0, v < 0 or u + v > 1, beyond doubt
+    if (Ts - eT > best_t * (adet + eD)) return 0;                        // t > best, beyond doubt (best_t = inf: never)
+    if (Ts + eT < R.tmin_t * (adet - eD)) return 0;                      // t < tmin, beyond doubt
+    // certainly inside the triangle, |det| certainly >= 1e-8 (triangle.h:47), t certainly >= tmin?
+    if (Us > eU && Vs > eV && Us + Vs < adet - eS && adet - eD > 2e-8f) {
+        const float lo = div32(Ts - eT, adet + eD) * 0.999999f, hi = div32(Ts + eT, adet - eD) * 1.000001f;
+        if (lo >= R.tmin_hi && (!ANY || hi <= R.tmax_lo)) { t_hi = hi; return 2; }
+    }
+    return 1;
+}
+
+#ifdef __CUDACC__
+template <bool ANY, bool STATS>
+struct Walk32 {
+    Ray32 R;                     // origin, direction, interval images and error scales (pre-filter)
+    float ix, iy, iz, nox, noy, noz;   // slabs: 1/d (the fp64 quotient, rounded) and -o/d for one FMA per plane
+    float best_t;                // the walk's current upper bound (R.best_t is the ray's own tmax image)
+    int32_t cur;
+    int sp;
+    uint32_t c0, c1, c2, c3;     // candidates: leaf-order indices for the exact test (scalars: an indexed array would
+    int ncand;                   //   put the whole walk state in local memory)
+    uint32_t skip;               // ANY: prim that is known not to occlude (the far endpoint's triangle), else BDPT_MISS
+    bool flagged;                // an exact test saw a tie / knife edge: the reference tree decides
+    bool occluded;               // ANY: a certain occluder was found (c0 = its leaf-order index)
+    TravStats ts;
+
+    __device__ __forceinline__ void push(uint32_t k) {
+        if (ncand == 0) c0 = k; else if (ncand == 1) c1 = k; else if (ncand == 2) c2 = k; else c3 = k;
+        ++ncand;
+    }
+    __device__ __forceinline__ uint32_t get(int i) const { return i == 0 ? c0 : (i == 1 ? c1 : (i == 2 ? c2 : c3)); }
+
+    __device__ __forceinline__ void init(const SceneView& sc, const RayD& r, uint32_t skip_prim = 0xFFFFFFFFu) {
+        const double o[3] = {r.o.x, r.o.y, r.o.z}, d[3] = {r.d.x, r.d.y, r.d.z};
+        R = make_ray32(o, d, r.tmin, r.tmax, sc.vmax32);
+        ix = float(1.0 / r.d.x); iy = float(1.0 / r.d.y); iz = float(1.0 / r.d.z);
+        nox = -R.ox * ix; noy = -R.oy * iy; noz = -R.oz * iz;
+        best_t = R.best_t;
+        cur = 0; sp = 0; ncand = 0; c0 = c1 = c2 = c3 = 0; skip = skip_prim;
+        flagged = false; occluded = false;
+        ts.nodes = 0; ts.tris = 0;
+    }
+
+    __device__ __forceinline__ int filter(const Tri32* __restrict__ T, float& t_hi, uint32_t& prim) const {
+        const float4 q0 = __ldg(&T->q0), q1 = __ldg(&T->q1), q2 = __ldg(&T->q2);
+        prim = __float_as_uint(q2.w);
+        return filter32<ANY>(R, best_t, q0, q1, q2, t_hi);
+    }
+
+    // One time slice for the whole warp (all 32 lanes must call; busy = this lane holds a ray that is not finished).
+    // A trip = [the pre-filter for the lanes waiting at a leaf, when enough of them wait] + up to `nstep` node steps
+    // per lane with no vote in between (a lane that reaches a leaf sits out the rest of the trip) + one vote.
+    // Returns per lane: WALK_YIELD (call again), WALK32_FLUSH (call decide(last = false), then again) or TR_HIT (the
+    // walk is over: call decide(last = true)).  TR_HIT is only a "done" marker here.
+    __device__ __forceinline__ int run(const SceneView& sc, StackEntry* stack, bool busy, int trips, int nstep, int t_leaf, int t_node,
+                                       int min_idle) {
+        bool stalled = false;   // candidate list full: wait for the caller's flush
+        const uint32_t m_busy = __ballot_sync(0xFFFFFFFFu, busy);
+        for (int trip = 0; trip < trips; ++trip) {
+            const bool live = busy && !stalled && cur != kWalkDry;
+            const bool at_leaf = live && cur < 0 && cur != kWalkPop;
+            const uint32_t m_leaf = __ballot_sync(0xFFFFFFFFu, at_leaf);
+            // ---- leaf phase: the pre-filter for every waiting lane at once
+            if (m_leaf) {
+                const uint32_t m_walk = __ballot_sync(0xFFFFFFFFu, live && !at_leaf);
+                if (__popc(m_leaf) >= t_leaf || __popc(m_walk) <= t_node) {
+                    if (at_leaf) {
+                        const uint32_t code = uint32_t(~cur);
+                        const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;   // builders make leaves of 1 or 2 triangles
+                        if (ncand + int(cnt) > kMaxCand) stalled = true;
+                        else {
+                            const Tri32* T = sc.tris32 + first;
+                            bool done = false;
+#pragma unroll
+                            for (uint32_t k = 0; k < 2; ++k) {
+                                if (k < cnt && !done) {
+                                    if (STATS) ++ts.tris;
+                                    float t_hi;
+                                    uint32_t prim;
+                                    const int f = filter(T + k, t_hi, prim);
+                                    if (f != 0 && !(ANY && prim == skip)) {
+                                        if (ANY && f == 2) { occluded = true; c0 = first + k; done = true; }
+                                        else {
+                                            push(first + k);
+                                            if (!ANY && f == 2) best_t = fminf(best_t, t_hi);
+                                        }
+                                    }
+                                }
+                            }
+                            cur = done ? kWalkDry : kWalkPop;
+                        }
+                    }
+                }
+            }
+            // ---- node steps
+#pragma unroll 1
+            for (int s = 0; s < nstep; ++s) {
+                if (!(busy && !stalled && (cur >= 0 || cur == kWalkPop))) break;
+                if (cur == kWalkPop) {   // one stack entry per step; an entry a closer hit has put out of reach costs a step
+                    if (sp == 0) { cur = kWalkDry; break; }
+                    --sp;
+                    const StackEntry e = stack[sp];
+                    if (!(__uint_as_float(uint32_t(e)) <= best_t)) continue;
+                    cur = int32_t(uint32_t(e >> 32));
+                    if (cur < 0) break;   // a leaf
+                }
+                const float4* q = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
+                const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+                const int2 w = __ldg(reinterpret_cast<const int2*>(q + 3));
+                if (STATS) ++ts.nodes;
+                float ln = R.tmin_t, lf = best_t, rn = R.tmin_t, rf = best_t;
+                slab_fma(a.x, a.w, nox, ix, ln, lf);
+                slab_fma(a.y, b.x, noy, iy, ln, lf);
+                slab_fma(a.z, b.y, noz, iz, ln, lf);
+                slab_fma(b.z, c.y, nox, ix, rn, rf);
+                slab_fma(b.w, c.z, noy, iy, rn, rf);
+                slab_fma(c.x, c.w, noz, iz, rn, rf);
+                const bool hl = ln <= lf, hr = rn <= rf;
+                const bool swap = rn < ln;
+                if (hl && hr) {
+                    stack[sp] = pack_entry(swap ? w.x : w.y, swap ? ln : rn);
+                    ++sp;
+                    cur = swap ? w.y : w.x;
+                } else cur = hl ? w.x : (hr ? w.y : kWalkPop);
+            }
+            __syncwarp();
+            const uint32_t m_done = __ballot_sync(0xFFFFFFFFu, busy && (stalled || cur == kWalkDry));
+            if (m_done == m_busy || (min_idle > 0 && __popc(m_done) + (32 - __popc(m_busy)) >= min_idle)) break;
+        }
+        if (!busy) return WALK_YIELD;
+        if (cur == kWalkDry) return TR_HIT;
+        return stalled ? WALK32_FLUSH : WALK_YIELD;
+    }
+
+    // The exact decision over the candidate list: Walk::leaf_tests + Walk::finish of traverse_walk.cuh, restated for
+    // a list.  `last` = the walk is over (finish) / the list is full (flush: keep the winner, go on walking).
+    // Returns TR_HIT / TR_MISS / TR_DEFER when last, else WALK_YIELD.
+    __device__ __forceinline__ int decide(const SceneView& sc, const RayD& r, HitD& hit, bool last) {
+        const double inv_max = fmin(fabs(1.0 / r.d.x), fmin(fabs(1.0 / r.d.y), fabs(1.0 / r.d.z)));
+        const double band_abs = 1e-10 * sc.extent * inv_max;
+        if (ANY) {
+            if (occluded) { hit.prim = __ldg(sc.fast_prims + c0); hit.t = r.tmax; hit.u = 0.0; hit.v = 0.0; return TR_HIT; }
+#pragma unroll
+            for (int k = 0; k < kMaxCand; ++k) {
+                if (k >= ncand) break;
+                const uint32_t ck = get(k);
+                if (STATS) ++ts.tris;
+                double t, u, v;
+                if (!tri_candidate(sc.fast_tris + ck, r.o, r.d, t, u, v)) continue;
+                if (!(r.tmin <= t && t <= r.tmax)) continue;
+                const uint32_t prim = __ldg(sc.fast_prims + ck);
+                if (prim == skip) continue;
+                const double band = band_abs + 1e-10 * fabs(t);
+                const bool edge = fabs(t - r.tmin) <= band || fabs(t - r.tmax) <= band;
+                bool occ = true;
+                if (edge) {   // knife edge: occludes iff the reference's own box chain reaches it (traverse_fast.cuh)
+                    const D3 adinv = mk(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
+                    uint32_t walk = 0;
+                    occ = reference_reaches(sc, prim, r, adinv, walk);
+                    if (STATS) ts.nodes += walk;
+                }
+                if (occ) { occluded = true; c0 = ck; hit.prim = prim; hit.t = t; hit.u = u; hit.v = v; cur = kWalkDry; return TR_HIT; }
+            }
+            ncand = 0;
+            return last ? TR_MISS : WALK_YIELD;
+        } else {
+            double best = r.tmax;
+            bool found = false;
+            uint32_t best_k = 0;
+#pragma unroll
+            for (int k = 0; k < kMaxCand; ++k) {
+                if (k >= ncand) break;
+                const uint32_t ck = get(k);
+                if (STATS) ++ts.tris;
+                double t, u, v;
+                if (!tri_candidate(sc.fast_tris + ck, r.o, r.d, t, u, v)) continue;
+                const double band = band_abs + 1e-10 * fabs(t);
+                if (found && fabs(t - best) <= band) flagged = true;                          // tie with the current best
+                if (fabs(t - r.tmin) <= band || fabs(t - r.tmax) <= band) flagged = true;     // knife edge
+                if (r.tmin <= t && t <= best && (!found || t < best)) {
+                    best = t; found = true; best_k = ck;
+                    hit.t = t; hit.u = u; hit.v = v;
+                }
+            }
+            if (!last) {
+                ncand = 0;
+                if (found) { c0 = best_k; ncand = 1; best_t = fminf(best_t, __double2float_ru(best)); }
+                return WALK_YIELD;
+            }
+            if (flagged) return TR_DEFER;
+            if (!found) return TR_MISS;
+            hit.prim = __ldg(sc.fast_prims + best_k);
+            return TR_HIT;
+        }
+    }
+};
+#endif  // __CUDACC__
+
+}  // namespace bdpt

@@ -183,6 +183,10 @@ int bdpt_film_clear(bdpt_ctx* ctx, int width, int height);
 /* device pointer of the film (W*H*3 doubles) so a caller can reduce it across GPUs in place */
 int bdpt_film_device_ptr(bdpt_ctx* ctx, void** ptr, uint64_t* n_doubles);
 int bdpt_film_download(bdpt_ctx* ctx, double* film_sum /* W*H*3 */);
+/* Dimensions of the context's film.  bdpt_render sizes the film by the reference's own rule, image_height =
+ * max(1, int(image_width / aspect_ratio)) (camera.h:161-162), so this is the one source of truth for the buffer a
+ * caller hands to bdpt_film_download / bdpt_film_to_rgb8. */
+int bdpt_film_size(bdpt_ctx* ctx, int* width, int* height);
 /* wpng.h:14-35 on the device film: average, clamp [0,0.999], sqrt, 256x truncate. out: W*H*3 bytes (host) */
 int bdpt_film_to_rgb8(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out);
 
@@ -220,6 +224,11 @@ int  bdpt_scene_source_key(const char* yaml_path, uint64_t* key);
 int  bdpt_scene_file_open_cached(const char* yaml_path, const char* cache_path, bdpt_scene_file** out,
                                  const void** image, uint64_t* image_bytes, int* hit);
 const char* bdpt_host_last_error(void);
+
+/* Test hook, host only: the fp32 pre-filter of the warp-synchronous walk (csrc/traverse_w32.cuh) on one ray
+ * (o, d, tmin, tmax) and one triangle (v0, e1, e2); best = the walk's current upper bound, vmax >= the largest
+ * |coordinate| of the scene.  0 = rejected, 1 = candidate for the exact fp64 test, 2 = certainly accepted. */
+int  bdpt_test_filter32(const double* ray, double best, const double* tri_v0e1e2, double vmax, int any, float* t_hi);
 
 #ifdef __cplusplus
 }

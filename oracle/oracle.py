@@ -37,6 +37,8 @@ def make_camera(width, height, spp, depth, lookfrom, lookat, vfov=90.0, vup=(0, 
                 focus_dist=10.0):
     c = Camera()
     c.aspect_ratio = float(width) / float(height)  # scene_loader.h:445
+    while max(1, int(width / c.aspect_ratio)) != int(height):   # camera.h:161 truncates: ~2 % of (W, H) pairs lose a row
+        c.aspect_ratio = float(np.nextafter(c.aspect_ratio, 0.0))
     c.image_width, c.samples_per_pixel, c.max_depth = int(width), int(spp), int(depth)
     c.background[:] = background
     c.vfov = vfov
