@@ -61,3 +61,70 @@ def test_relmse_converges_like_the_reference(bdpt, gpu_ctx, scenes):
     assert abs(slope_g - slope_c) <= 0.1
     for a, b in zip(g, c):
         assert 0.8 <= a / b <= 1.25, (g, c)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# The NAMED scenes against a CPU-rendered ground truth (north_star: "relative MSE against a high-spp reference CPU
+# render must converge at the same rate as the reference's own output at equal spp").
+#   ground truth = tests/golden/truth_<scene>.npz: 4,096 spp rendered by the reference's own headers (oracle/_ref),
+#                  committed by tools/make_convergence_truth.py (reduced resolution: 4,096 spp on the CPU costs
+#                  ~2 min per scene at 64x64 / 96x54 and hours at the configs' full resolutions)
+#   GPU arm      = libbdpt, Philox stream; CPU arm = the port in mt19937 mode (bit-identical to oracle/_ref,
+#                  tests/test_oracle.py), independent seeds, rendered side by side on the host cores
+#   gates        = as above: |slope_gpu - slope_cpu| <= 0.1 over spp 1, 4, 16, 64; relMSE ratio in [0.8, 1.25] at every spp
+import json
+import os
+from concurrent.futures import ThreadPoolExecutor
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NAMED_SEEDS = 12
+
+
+@pytest.fixture(scope="module")
+def standins():
+    from tools import make_standin_scenes as ms
+    ms.generate(detail=2, quiet=True)
+
+
+@pytest.mark.parametrize("name", ["glass_of_water", "coffee_machine"])
+def test_named_scene_relmse_vs_cpu_ground_truth(name, bdpt, gpu_ctx, standins):
+    from oracle.oracle import Camera as OCamera
+    g = np.load(os.path.join(ROOT, "tests", "golden", "truth_%s.npz" % name))
+    meta = json.loads(str(g["meta"]))
+    ref = g["film"].astype(np.float64)
+    Wn, Hn, depth = meta["width"], meta["height"], meta["depth"] or None
+    assert ref.shape == (Hn, Wn, 3) and ref.max() > 0
+    sf = bdpt.SceneFile(os.path.join(ROOT, meta["scene"]))
+    gpu_ctx.upload(sf.verts, sf.mat_id, sf.materials)
+    cpu = Oracle("port").load(sf.verts, sf.mat_id, sf.material_list())
+
+    def cpu_render(args):
+        spp, seed = args
+        cam = OCamera.from_buffer_copy(bytes(sf.camera_with(Wn, Hn, spp, depth)))
+        return rel_mse(cpu.render(cam, rng_mode=RNG_MT19937, seed=seed, height=Hn), int(np.sqrt(spp)) ** 2, ref)
+
+    jobs = [(spp, 7000 + 131 * k + spp) for spp in SPPS for k in range(NAMED_SEEDS)]
+    with ThreadPoolExecutor(max_workers=os.cpu_count() or 8) as pool:
+        fut = pool.map(cpu_render, jobs)                       # the CPU arm runs while the GPU arm does
+        gm = []
+        for spp in SPPS:
+            e = []
+            for k in range(NAMED_SEEDS):
+                gpu_ctx.render(sf.camera_with(Wn, Hn, spp, depth), seed=3000 + 17 * k + spp, bvh=bdpt.BVH_FAST, height=Hn)
+                e.append(rel_mse(gpu_ctx.film(), spp, ref))
+            gm.append(float(np.mean(e)))
+        ce = list(fut)
+    cpu.close()
+    cm = [float(np.mean(ce[i * NAMED_SEEDS:(i + 1) * NAMED_SEEDS])) for i in range(len(SPPS))]
+    lx = np.log(np.array(SPPS, dtype=np.float64))
+    slope_g, slope_c = np.polyfit(lx, np.log(gm), 1)[0], np.polyfit(lx, np.log(cm), 1)[0]
+    table = {"scene": meta["scene"], "resolution": [Wn, Hn], "depth": meta["depth"], "truth_spp": meta["spp"], "spp": list(SPPS),
+             "relmse_gpu": gm, "relmse_cpu_reference": cm, "slope_gpu": slope_g, "slope_cpu": slope_c, "seeds": NAMED_SEEDS}
+    print("relMSE", json.dumps(table))
+    out_dir = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out_dir):
+        json.dump(table, open(os.path.join(out_dir, "relmse_%s.json" % name), "w"))
+    assert gm[-1] < 0.5 * gm[0] and cm[-1] < 0.5 * cm[0]
+    assert abs(slope_g - slope_c) <= 0.1, table
+    for a, b in zip(gm, cm):
+        assert 0.8 <= a / b <= 1.25, table
