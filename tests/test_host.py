@@ -90,3 +90,85 @@ def test_host_bvh_large_tied_scene_matches_the_reference_build(bdpt):
             raise
         assert n_ref == o.node_count()
         assert np.array_equal(order, o.leaf_order()), kind
+
+
+# ---------------------------------------------------------------- the fp32 pre-filter of the warp-synchronous walk
+def _exact_mt(o, d, v0, e1, e2):
+    """triangle.h:41-67 in fp64: (line hit?, t)."""
+    pvec = np.cross(d, e2)
+    det = float(np.dot(e1, pvec))
+    if abs(det) < 1e-8:
+        return False, 0.0
+    inv = 1.0 / det
+    tvec = o - v0
+    u = float(np.dot(tvec, pvec)) * inv
+    if u < 0.0 or u > 1.0:
+        return False, 0.0
+    qvec = np.cross(tvec, e1)
+    v = float(np.dot(d, qvec)) * inv
+    if v < 0.0 or u + v > 1.0:
+        return False, 0.0
+    return True, float(np.dot(e2, qvec)) * inv
+
+
+def test_prefilter_is_conservative(bdpt):
+    """csrc/traverse_w32.cuh: a triangle the fp32 filter REJECTS (0) is never one the reference's fp64 test accepts
+    inside [tmin, best]; a triangle it calls CERTAIN (2) is always accepted, with tmin <= t <= t_hi (closest) or
+    strictly inside the segment (any-hit).  Rays are aimed at, just inside and just outside edges and vertices, at
+    grazing angles, at slivers, from near and far, across triangle sizes from 1e-4 to 10 of a 100-unit scene."""
+    L = bdpt.lib()
+    rng = np.random.default_rng(20261105)
+    vmax = 60.0
+    n_certain = n_reject = n_maybe = n_hits = 0
+    hi = ctypes.c_float(0)
+    offs = np.array([-1e-3, -1e-5, -1e-7, -1e-9, 0.0, 1e-9, 1e-7, 1e-5, 1e-3, 0.3, 0.5])
+    for it in range(60000):
+        s = 10.0 ** rng.uniform(-4, 1)
+        v0 = rng.uniform(-50, 50, 3)
+        e1 = rng.normal(size=3) * s
+        e2 = rng.normal(size=3) * s
+        if it % 7 == 0:                                    # sliver: e2 nearly parallel to e1
+            e2 = e1 * rng.uniform(0.2, 2.0) + rng.normal(size=3) * s * 1e-5
+        a, b = rng.choice(offs), rng.choice(offs)
+        if it % 3 == 0:
+            a = 1.0 - b + rng.choice(offs) * (1 if it % 2 else -1)      # around the u + v = 1 edge
+        target = v0 + a * e1 + b * e2
+        o = target + rng.normal(size=3) * 10.0 ** rng.uniform(-3, 2)
+        if it % 11 == 0:                                   # grazing: origin almost in the triangle's plane
+            n = np.cross(e1, e2)
+            nn = np.linalg.norm(n)
+            if nn > 0:
+                o = o - (np.dot(o - v0, n / nn) * (1 - 10.0 ** rng.uniform(-8, -2))) * (n / nn)
+        o = np.clip(o, -400, 400)
+        d = target - o
+        if it % 2:
+            d = d / max(np.linalg.norm(d), 1e-300)
+        d = d * 10.0 ** rng.uniform(-1, 1) if it % 5 == 0 else d
+        o, d = o.astype(np.float32).astype(np.float64), d.astype(np.float32).astype(np.float64)   # as bdpt's fixed batches
+        if np.any(d == 0):
+            continue
+        hit, t = _exact_mt(o, d, v0, e1, e2)
+        tmin = 0.001
+        tmax = np.inf if it % 4 else abs(t) * rng.choice([0.5, 1 - 1e-6, 1 - 1e-9, 1.0, 1 + 1e-9, 1 + 1e-6, 2.0]) + 1e-3
+        best = tmax if it % 9 else min(tmax, abs(t) * rng.choice([0.999999, 1.0, 1.000001, 1.5]) + 1e-12)
+        ray = np.array([*o, *d, tmin, tmax])
+        tri = np.array([*v0, *e1, *e2])
+        for any_hit in (0, 1):
+            f = L.bdpt_test_filter32(ray.ctypes.data, float(best), tri.ctypes.data, vmax, any_hit, ctypes.byref(hi))
+            accepted = hit and tmin <= t <= best
+            if f == 0:
+                n_reject += 1
+                assert not accepted, (it, any_hit, o, d, v0, e1, e2, t, best)
+            elif f == 2:
+                n_certain += 1
+                assert hit and t >= tmin, (it, any_hit, t)
+                if any_hit:
+                    assert tmin < t < tmax, (it, t, tmax)
+                else:
+                    assert t <= float(hi.value), (it, t, hi.value)
+            else:
+                n_maybe += 1
+        n_hits += hit
+    # the filter must also be SHARP, or the walk degenerates into fp64 tests: most decisions are not "maybe"
+    assert n_certain > 1000 and n_reject > 10000, (n_certain, n_reject, n_maybe)
+    print("prefilter: reject %d, maybe %d, certain %d, line hits %d" % (n_reject, n_maybe, n_certain, n_hits))
