@@ -129,19 +129,21 @@ BDPT_HD int filter32(const Ray32& R, float best_t, const float4& q0, const float
     const float m12 = n1 * n2;
     const float eD = fmaxf(R.kD * m12, 1e-30f), eU = R.kU * n2, eV = R.kU * n1, eT = R.kT * m12;
     const float adet = fabsf(det);
-    if (!(adet > eD)) return 1;   // sign of det unknown (grazing, sliver, NaN): only the exact test can tell
+    // one exit: the lanes of a warp take this function together, an early return would split them for the rest of it
+    const bool sign_known = adet > eD;   // else (grazing, sliver, NaN): only the exact test can tell
     const bool neg = det < 0.f;
     const float Us = neg ? -U : U, Vs = neg ? -V : V, Ts = neg ? -TN : TN;
     const float eS = eD + eU + eV;
-    if (Us < -eU || Vs < -eV || Us + Vs > adet + eS) return 0;          // u < 0, v < 0 or u + v > 1, beyond doubt
-    if (Ts - eT > best_t * (adet + eD)) return 0;                        // t > best, beyond doubt (best_t = inf: never)
-    if (Ts + eT < R.tmin_t * (adet - eD)) return 0;                      // t < tmin, beyond doubt
+    const bool outside = Us < -eU || Vs < -eV || Us + Vs > adet + eS;      // u < 0, v < 0 or u + v > 1, beyond doubt
+    const bool beyond = Ts - eT > best_t * (adet + eD);                     // t > best, beyond doubt (best_t = inf: never)
+    const bool before = Ts + eT < R.tmin_t * (adet - eD);                   // t < tmin, beyond doubt
+    int res = (sign_known && (outside || beyond || before)) ? 0 : 1;
     // certainly inside the triangle, |det| certainly >= 1e-8 (triangle.h:47), t certainly >= tmin?
-    if (Us > eU && Vs > eV && Us + Vs < adet - eS && adet - eD > 2e-8f) {
+    if (res == 1 && sign_known && Us > eU && Vs > eV && Us + Vs < adet - eS && adet - eD > 2e-8f) {
         const float lo = div32(Ts - eT, adet + eD) * 0.999999f, hi = div32(Ts + eT, adet - eD) * 1.000001f;
-        if (lo >= R.tmin_hi && (!ANY || hi <= R.tmax_lo)) { t_hi = hi; return 2; }
+        if (lo >= R.tmin_hi && (!ANY || hi <= R.tmax_lo)) { t_hi = hi; res = 2; }
     }
-    return 1;
+    return res;
 }
 
 #ifdef __CUDACC__
@@ -202,63 +204,65 @@ struct Walk32 {
                     if (at_leaf) {
                         const uint32_t code = uint32_t(~cur);
                         const uint32_t first = code >> 3, cnt = (code & 7u) + 1u;   // builders make leaves of 1 or 2 triangles
-                        if (ncand + int(cnt) > kMaxCand) stalled = true;
-                        else {
-                            const Tri32* T = sc.tris32 + first;
-                            bool done = false;
+                        const bool room = ncand + int(cnt) <= kMaxCand;
+                        if (!room) stalled = true;
+                        const Tri32* T = sc.tris32 + first;
+                        bool done = false;
 #pragma unroll
-                            for (uint32_t k = 0; k < 2; ++k) {
-                                if (k < cnt && !done) {
-                                    if (STATS) ++ts.tris;
-                                    float t_hi;
-                                    uint32_t prim;
-                                    const int f = filter(T + k, t_hi, prim);
-                                    if (f != 0 && !(ANY && prim == skip)) {
-                                        if (ANY && f == 2) { occluded = true; c0 = first + k; done = true; }
-                                        else {
-                                            push(first + k);
-                                            if (!ANY && f == 2) best_t = fminf(best_t, t_hi);
-                                        }
+                        for (uint32_t k = 0; k < 2; ++k) {
+                            __syncwarp(m_leaf);   // the waiting lanes test their k-th triangles together
+                            if (room && k < cnt && !done) {
+                                if (STATS) ++ts.tris;
+                                float t_hi = 0.f;
+                                uint32_t prim;
+                                const int f = filter(T + k, t_hi, prim);
+                                if (f != 0 && !(ANY && prim == skip)) {
+                                    if (ANY && f == 2) { occluded = true; c0 = first + k; done = true; }
+                                    else {
+                                        push(first + k);
+                                        if (!ANY && f == 2) best_t = fminf(best_t, t_hi);
                                     }
                                 }
                             }
-                            cur = done ? kWalkDry : kWalkPop;
                         }
+                        if (room) cur = done ? kWalkDry : kWalkPop;
                     }
                 }
             }
-            // ---- node steps
+            __syncwarp();
+            // ---- node steps: every lane takes every step (predicated), so the warp is whole at each node fetch
 #pragma unroll 1
             for (int s = 0; s < nstep; ++s) {
-                if (!(busy && !stalled && (cur >= 0 || cur == kWalkPop))) break;
-                if (cur == kWalkPop) {   // one stack entry per step; an entry a closer hit has put out of reach costs a step
-                    if (sp == 0) { cur = kWalkDry; break; }
-                    --sp;
-                    const StackEntry e = stack[sp];
-                    if (!(__uint_as_float(uint32_t(e)) <= best_t)) continue;
-                    cur = int32_t(uint32_t(e >> 32));
-                    if (cur < 0) break;   // a leaf
+                const bool act = busy && !stalled && (cur >= 0 || cur == kWalkPop);
+                if (!__any_sync(0xFFFFFFFFu, act)) break;
+                if (act && cur == kWalkPop) {   // one stack entry per step; an entry a closer hit has put out of reach costs a step
+                    if (sp == 0) cur = kWalkDry;
+                    else {
+                        --sp;
+                        const StackEntry e = stack[sp];
+                        if (__uint_as_float(uint32_t(e)) <= best_t) cur = int32_t(uint32_t(e >> 32));
+                    }
                 }
-                const float4* q = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
-                const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
-                const int2 w = __ldg(reinterpret_cast<const int2*>(q + 3));
-                if (STATS) ++ts.nodes;
-                float ln = R.tmin_t, lf = best_t, rn = R.tmin_t, rf = best_t;
-                slab_fma(a.x, a.w, nox, ix, ln, lf);
-                slab_fma(a.y, b.x, noy, iy, ln, lf);
-                slab_fma(a.z, b.y, noz, iz, ln, lf);
-                slab_fma(b.z, c.y, nox, ix, rn, rf);
-                slab_fma(b.w, c.z, noy, iy, rn, rf);
-                slab_fma(c.x, c.w, noz, iz, rn, rf);
-                const bool hl = ln <= lf, hr = rn <= rf;
-                const bool swap = rn < ln;
-                if (hl && hr) {
-                    stack[sp] = pack_entry(swap ? w.x : w.y, swap ? ln : rn);
-                    ++sp;
-                    cur = swap ? w.y : w.x;
-                } else cur = hl ? w.x : (hr ? w.y : kWalkPop);
+                __syncwarp();
+                if (act && cur >= 0) {
+                    const float4* q = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
+                    const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+                    const int2 w = __ldg(reinterpret_cast<const int2*>(q + 3));
+                    if (STATS) ++ts.nodes;
+                    float ln = R.tmin_t, lf = best_t, rn = R.tmin_t, rf = best_t;
+                    slab_fma(a.x, a.w, nox, ix, ln, lf);
+                    slab_fma(a.y, b.x, noy, iy, ln, lf);
+                    slab_fma(a.z, b.y, noz, iz, ln, lf);
+                    slab_fma(b.z, c.y, nox, ix, rn, rf);
+                    slab_fma(b.w, c.z, noy, iy, rn, rf);
+                    slab_fma(c.x, c.w, noz, iz, rn, rf);
+                    const bool hl = ln <= lf, hr = rn <= rf;
+                    const bool swap = rn < ln;
+                    if (hl && hr) { stack[sp] = pack_entry(swap ? w.x : w.y, swap ? ln : rn); ++sp; }
+                    cur = (hl && hr) ? (swap ? w.y : w.x) : (hl ? w.x : (hr ? w.y : kWalkPop));
+                }
+                __syncwarp();
             }
-            __syncwarp();
             const uint32_t m_done = __ballot_sync(0xFFFFFFFFu, busy && (stalled || cur == kWalkDry));
             if (m_done == m_busy || (min_idle > 0 && __popc(m_done) + (32 - __popc(m_busy)) >= min_idle)) break;
         }
