@@ -478,7 +478,7 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
         return BDPT_OK;
     }
 #define BDPT_LAUNCH(B, A, S) k_trace<B, A, S><<<grid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st)
-    static const bool walk32 = [] { const char* e = std::getenv("BDPT_WALK32"); return e ? std::atoi(e) != 0 : true; }();
+    static const bool walk32 = [] { const char* e = std::getenv("BDPT_WALK32"); return e ? std::atoi(e) != 0 : false; }();   // opt-in: measured slower than the per-lane walk
     if (bvh == BDPT_BVH_FAST && walk32 && !(v.use_wide & 3u)) {
         // round 2: persistent warps on the warp-synchronous fp32 walk; the cursor is a stream-ordered scratch word
         auto knob = [](const char* name, int dflt) { const char* e = std::getenv(name); return e ? std::atoi(e) : dflt; };

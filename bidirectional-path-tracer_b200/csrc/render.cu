@@ -1590,8 +1590,11 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (const char* e = std::getenv("BDPT_T_WALK")) t_walk = std::atoi(e);
     J.threshold = int(uint32_t(slice & 0xFF) | (uint32_t(min_idle & 0xFF) << 8) | (uint32_t(t_leaf & 0xFF) << 16) | (uint32_t(t_walk & 0xFF) << 24));
     {
-        // round 2's bulk traversal (BDPT_WALK32=0: round 1's per-lane walk, kept for A/B runs)
-        J.walk32 = true;
+        // BDPT_WALK32=1: the warp-synchronous fp32 walk (traverse_w32.cuh).  Parity-green and at 15.3 instead of 8.4
+        // active lanes per instruction, but measured SLOWER (31.9 vs 21.7 ms per bench step): the walk is bound by
+        // dependent-load latency, and a warp in lock step waits for the slowest of its lanes at every node.
+        // The default therefore stays the per-lane walk of traverse_walk.cuh.
+        J.walk32 = false;
         if (const char* e = std::getenv("BDPT_WALK32")) J.walk32 = std::atoi(e) != 0;
         int trips = 16, nstep = 4, idle = 8, tleaf = 8, tnode = 4;
         if (const char* e = std::getenv("BDPT_W32_TRIPS")) trips = std::atoi(e);
