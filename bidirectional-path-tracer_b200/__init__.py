@@ -32,6 +32,7 @@ EXPORTS = [
     "bdpt_scene_image_build", "bdpt_scene_image_free", "bdpt_scene_image_info", "bdpt_scene_image_last_error",
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
+    "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress",
 ]
 
 
@@ -56,7 +57,8 @@ class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_closest", "rays_shadow", "node_visits", "tri_tests", "samples",
                                           "kernel_launches", "camera_vertices", "light_vertices", "nodes_closest",
                                           "tris_closest", "nodes_shadow", "tris_shadow", "max_work_closest",
-                                          "max_work_shadow", "deferred_closest", "deferred_shadow")]
+                                          "max_work_shadow", "deferred_closest", "deferred_shadow", "aabb_tests", "aabb_hits",
+                                          "triangle_hits", "bvh_nodes_built")]
 
 
 class SceneImageInfo(C.Structure):
@@ -109,6 +111,11 @@ def lib():
         L.bdpt_film_clear.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.bdpt_film_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         L.bdpt_film_download.argtypes = [C.c_void_p, C.c_void_p]
+        L.bdpt_film_reduce.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int]
+        L.bdpt_comm_unique_id.argtypes = [C.c_void_p]
+        L.bdpt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.bdpt_film_reduce_comm.argtypes = [C.c_void_p, C.c_int]
+        L.bdpt_render_progress.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.bdpt_film_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.bdpt_test_filter32.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_double, C.c_int, C.POINTER(C.c_float)]
         L.bdpt_film_to_rgb8.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -504,8 +511,41 @@ class Context:
     def sync(self):
         self._chk(lib().bdpt_sync(self._h), "bdpt_sync")
 
+    def comm_init(self, nranks, rank, unique_id):
+        """Join the NCCL communicator of the film reduce (one process per GPU); unique_id: the 128 bytes of
+        comm_unique_id() from one rank, carried to the others by the launcher (torch.distributed, MPI, a file)."""
+        buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
+        self._chk(lib().bdpt_comm_init(self._h, int(nranks), int(rank), buf), "bdpt_comm_init")
+
+    def film_reduce(self, root=0):
+        """The one exchange step of a frame: NCCL sum-reduce of the ranks' device films onto `root`, in place."""
+        self._chk(lib().bdpt_film_reduce_comm(self._h, int(root)), "bdpt_film_reduce_comm")
+        return self.last_device_ms()
+
+    def progress(self):
+        d, t = C.c_uint64(0), C.c_uint64(0)
+        self._chk(lib().bdpt_render_progress(self._h, C.byref(d), C.byref(t)), "bdpt_render_progress")
+        return d.value, t.value
+
 
 # ---------------------------------------------------------------- multi-GPU: stratum sharding (SURVEY 8e)
+def comm_unique_id():
+    """128 bytes naming a new NCCL communicator (bdpt_comm_unique_id): create on one rank, send to the others."""
+    buf = (C.c_char * 128)()
+    if lib().bdpt_comm_unique_id(buf):
+        raise BdptError("bdpt_comm_unique_id failed (is libnccl.so.2 loadable?)")
+    return bytes(buf)
+
+
+def film_reduce(contexts, root=0):
+    """bdpt_film_reduce: one process, several devices -- sums the contexts' films onto contexts[root] over NCCL."""
+    arr = (C.c_void_p * len(contexts))(*[c._h for c in contexts])
+    rc = lib().bdpt_film_reduce(arr, len(contexts), int(root))
+    if rc:
+        raise BdptError("bdpt_film_reduce failed (%d): %s" % (rc, lib().bdpt_last_error(contexts[root]._h).decode()))
+    return contexts[root].last_device_ms()
+
+
 def shard_strata(rank, world, samples_per_pixel):
     """The strata rank `rank` of `world` renders: (begin, end, step) for bdpt_render_opts — stratum s belongs to
     rank s mod world, which keeps the reference's stratification (camera.h:164,213-223) and gives every rank the
@@ -531,17 +571,22 @@ def reduce_film(film, dist, dst=0):
     return film
 
 
+def join_comm(ctx, dist):
+    """bdpt_comm_init for the ranks of an initialised torch.distributed group: rank 0 creates the id, the group's
+    own broadcast carries it (plumbing only; the reduce itself is the library's)."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    box = [comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    ctx.comm_init(world, rank, box[0])
+
+
 def render_sharded(ctx, cam, dist=None, seed=0, bvh=BVH_FAST, height=None, device=None):
     """camera::render across the ranks of an initialised torch.distributed group: every rank renders its strata
-    into its own film, then one reduce. Returns the summed film (numpy, H x W x 3) on rank 0, None elsewhere.
+    into its own film, then ONE film reduce inside the library (bdpt_film_reduce_comm; the context must have joined
+    the communicator, join_comm). Returns the summed film (numpy, H x W x 3) on rank 0, None elsewhere.
     With dist=None it is a plain single-GPU render."""
     rank, world = (dist.get_rank(), dist.get_world_size()) if dist is not None else (0, 1)
     ctx.render(cam, seed=seed, bvh=bvh, strata=shard_strata(rank, world, cam.samples_per_pixel), clear=True, height=height)
     if dist is not None and world > 1:
-        import torch
-        ptr, n = ctx.film_device_ptr()
-        ctx.sync()
-        t = torch.as_tensor(CudaArray(ptr, n), device=device if device is not None else torch.device("cuda", torch.cuda.current_device()))
-        reduce_film(t, dist, dst=0)
-        torch.cuda.synchronize()
+        ctx.film_reduce(root=0)
     return ctx.film() if rank == 0 else None

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_trace(Scene
             if (!__any_sync(0xFFFFFFFFu, busy)) break;
         }
         if (eligible) {
-            if (STATS) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; }
+            if (STATS) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; st.box_hits += W.ts.box_hits; st.tri_hits += W.ts.tri_hits; }
             h = W.hit;
             found = rc == TR_DEFER ? traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st) : rc == TR_HIT;   // a tie goes to the reference tree
         } else if (i < n)
@@ -107,10 +107,7 @@ __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_trace(Scene
         w.y = __longlong_as_double((long long)(unsigned long long)h.prim);
         o[1] = w;
     }
-    if (STATS) {
-        atomicAdd(&stats[ST_NODE], (unsigned long long)st.nodes);
-        atomicAdd(&stats[ST_TRI], (unsigned long long)st.tris);
-    }
+    if (STATS) add_trav<2, BVH == BDPT_BVH_REFERENCE>(stats, st);
 }
 
 // hittable::hit over a ray batch on the warp-synchronous fp32 walk (traverse_w32.cuh): persistent warps pull rays
@@ -162,7 +159,7 @@ __global__ void __launch_bounds__(kTraceBlock, BDPT_B32_BLOCKS) k_trace_w32(Scen
             HitD h;
             int rc = result;
             if (rc == TR_HIT) rc = W.decide(sc, r, h, true);
-            if (STATS && have) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; }
+            if (STATS && have) { st.nodes += W.ts.nodes; st.tris += W.ts.tris; st.box_hits += W.ts.box_hits; st.tri_hits += W.ts.tri_hits; }
             bool found = rc == TR_HIT;
             if (rc == TR_DEFER) found = traverse_ref<ANY, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &st);
             store_hit(out, idx, found, h);
@@ -192,10 +189,7 @@ __global__ void __launch_bounds__(kTraceBlock, BDPT_B32_BLOCKS) k_trace_w32(Scen
         const int rc = W.run(sc, l_stack, have, trips, nstep, t_leaf, t_node, exhausted ? 0 : min_idle);
         if (have) result = rc;
     }
-    if (STATS) {
-        atomicAdd(&stats[ST_NODE], (unsigned long long)st.nodes);
-        atomicAdd(&stats[ST_TRI], (unsigned long long)st.tris);
-    }
+    if (STATS) add_trav<2, false>(stats, st);
 }
 
 // the same, one ray per WARP through split_walk (traverse_walk.cuh); ties found on the way fall back to the
@@ -304,8 +298,8 @@ int bdpt_ctx_create(int device, bdpt_ctx** out) {
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&ctx->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
-    if ((e = cudaMalloc(&ctx->d_stats, 16 * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc", e);
-    cudaMemset(ctx->d_stats, 0, 16 * sizeof(unsigned long long));
+    if ((e = cudaMalloc(&ctx->d_stats, ST_COUNT * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc", e);
+    cudaMemset(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long));
     *out = ctx;
     return BDPT_OK;
 }
@@ -315,6 +309,7 @@ void bdpt_ctx_destroy(bdpt_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     render_free(ctx);
+    comm_free(ctx);
     free_scene(ctx);
     if (ctx->film) cudaFree(ctx->film);
     if (ctx->d_stats) cudaFree(ctx->d_stats);
@@ -692,7 +687,7 @@ int bdpt_render(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 int bdpt_stats(bdpt_ctx* ctx, bdpt_stats_t* out) {
     if (!ctx || !out) return BDPT_ERR_ARG;
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
-    unsigned long long h[16];
+    unsigned long long h[ST_COUNT];
     BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     BDPT_CUDA(ctx, cudaMemcpy(h, ctx->d_stats, sizeof h, cudaMemcpyDeviceToHost));
     out->node_visits = h[ST_NODE]; out->tri_tests = h[ST_TRI];
@@ -703,13 +698,15 @@ int bdpt_stats(bdpt_ctx* ctx, bdpt_stats_t* out) {
     out->nodes_shadow = h[ST_NODE_SHADOW]; out->tris_shadow = h[ST_TRI_SHADOW];
     out->max_work_closest = h[ST_MAX_CLOSEST]; out->max_work_shadow = h[ST_MAX_SHADOW];
     out->deferred_closest = h[ST_DEFER_CLOSEST]; out->deferred_shadow = h[ST_DEFER_SHADOW];
+    out->aabb_tests = h[ST_BOX_TESTS]; out->aabb_hits = h[ST_BOX_HITS]; out->triangle_hits = h[ST_TRI_HITS];
+    out->bvh_nodes_built = ctx->have_scene ? ctx->view.n_ref_nodes : 0;
     return BDPT_OK;
 }
 
 int bdpt_stats_reset(bdpt_ctx* ctx) {
     if (!ctx) return BDPT_ERR_ARG;
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
-    BDPT_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, 16 * sizeof(unsigned long long), ctx->stream));
+    BDPT_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
     ctx->samples = 0; ctx->launches = 0;
     for (int i = 0; i < 8; ++i) { ctx->kernel_ms[i] = 0.0; ctx->kernel_launches[i] = 0; }
     return BDPT_OK;
@@ -724,6 +721,15 @@ int bdpt_last_device_ms(bdpt_ctx* ctx, double* ms) {
 int bdpt_kernel_times(bdpt_ctx* ctx, double* ms, uint64_t* launches) {
     if (!ctx || !ms) return BDPT_ERR_ARG;
     for (int i = 0; i < KT_COUNT; ++i) { ms[i] = ctx->kernel_ms[i]; if (launches) launches[i] = ctx->kernel_launches[i]; }
+    return BDPT_OK;
+}
+
+int bdpt_render_progress(bdpt_ctx* ctx, uint64_t* samples_done, uint64_t* samples_total) {
+    if (!ctx) return BDPT_ERR_ARG;
+    const int64_t t = ctx->progress_total.load(std::memory_order_relaxed);
+    const int64_t d = std::min(t, ctx->progress_done.load(std::memory_order_relaxed));
+    if (samples_done) *samples_done = uint64_t(d < 0 ? 0 : d);
+    if (samples_total) *samples_total = uint64_t(t < 0 ? 0 : t);
     return BDPT_OK;
 }
 

@@ -2,11 +2,14 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdlib>
+#include <cstring>
 #include <string>
 #include <vector>
 
 #include "host_scene.h"
+#include "traverse_ref.cuh"
 
 struct bdpt_ctx {
     int device = 0;
@@ -29,6 +32,12 @@ struct bdpt_ctx {
     uint64_t launches = 0;
     uint64_t samples = 0;
 
+    // NCCL communicator of bdpt_comm_init (film_reduce.cu); ncclComm_t
+    void* comm = nullptr;
+    int comm_rank = 0, comm_size = 1;
+    // samples handed to the wavefronts by the bdpt_render call in flight (bdpt_render_progress reads them from any thread)
+    std::atomic<int64_t> progress_done{0}, progress_total{0};
+
     // wavefront workspace (render.cu)
     void* wf = nullptr;
     void* timers = nullptr;
@@ -49,7 +58,21 @@ namespace bdpt {
 
 // device counter slots
 enum { ST_NODE = 0, ST_TRI = 1, ST_RAYS_CLOSEST = 2, ST_RAYS_SHADOW = 3, ST_CAM_VERTS = 4, ST_LIGHT_VERTS = 5,
-       ST_NODE_CLOSEST = 6, ST_TRI_CLOSEST = 7, ST_NODE_SHADOW = 8, ST_TRI_SHADOW = 9, ST_MAX_CLOSEST = 10, ST_MAX_SHADOW = 11, ST_DEFER_CLOSEST = 12, ST_DEFER_SHADOW = 13 };
+       ST_NODE_CLOSEST = 6, ST_TRI_CLOSEST = 7, ST_NODE_SHADOW = 8, ST_TRI_SHADOW = 9, ST_MAX_CLOSEST = 10, ST_MAX_SHADOW = 11, ST_DEFER_CLOSEST = 12, ST_DEFER_SHADOW = 13,
+       ST_BOX_TESTS = 14, ST_BOX_HITS = 15, ST_TRI_HITS = 16, ST_COUNT = 24 };
+// the reference's seven BvhStats counters (stats.h:8-16) need the box / hit tallies beside nodes and triangles
+#ifdef __CUDACC__
+template <int KIND /* 0 closest, 1 shadow, 2 batch trace */, bool REF_TREE>
+__device__ __forceinline__ void add_trav(unsigned long long* stats, const TravStats& ts) {
+    const int sn = KIND == 0 ? ST_NODE_CLOSEST : (KIND == 1 ? ST_NODE_SHADOW : ST_NODE), st = KIND == 0 ? ST_TRI_CLOSEST : (KIND == 1 ? ST_TRI_SHADOW : ST_TRI);
+    atomicAdd(&stats[sn], (unsigned long long)ts.nodes);
+    atomicAdd(&stats[st], (unsigned long long)ts.tris);
+    if (KIND < 2) atomicMax(&stats[KIND == 0 ? ST_MAX_CLOSEST : ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris));
+    atomicAdd(&stats[ST_BOX_TESTS], (unsigned long long)ts.nodes * (REF_TREE ? 1ull : 2ull));
+    atomicAdd(&stats[ST_BOX_HITS], (unsigned long long)ts.box_hits);
+    atomicAdd(&stats[ST_TRI_HITS], (unsigned long long)ts.tri_hits);
+}
+#endif
 // kernel classes of the wavefront (bdpt_kernel_times)
 enum { KT_GENERATE = 0, KT_TRACE = 1, KT_SHADE = 2, KT_CONNECT = 3, KT_SHADOW = 4, KT_TRACE_EXACT = 5, KT_SHADOW_EXACT = 6, KT_COUNT = 7 };
 
@@ -63,6 +86,7 @@ inline uint32_t wide_walk_mode() {
 int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts);
 // api.cu: the fp32 triangle records + error scale of the warp-synchronous walk (traverse_w32.cuh), queued on ctx->stream
 int derive_walk32(bdpt_ctx* ctx, SceneView& v);
+void comm_free(bdpt_ctx* ctx);   // film_reduce.cu
 void render_free(bdpt_ctx* ctx);
 // gpu_bvh.cu: the fast tree built on the device from triangles already uploaded (queued on ctx->stream)
 int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const double lo[3], const double hi[3], double extent,

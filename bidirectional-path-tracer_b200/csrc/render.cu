@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_paths(SceneV
                 found = traverse_fast<false, STATS, false>(sc, r, h, l_stack, 1, &ts) == TR_HIT;
             else
                 found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
-            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<0, BVH == BDPT_BVH_REFERENCE>(stats, ts);
             cls = finish_trace(sc, f, w, pid, found, h, film);
             ended = cls < 0;
         }
@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_paths(SceneV
                 defer = rc == TR_DEFER || rc == TR_SLOW;
                 defer_tag = rc == TR_SLOW ? kSlowFlag : 0u;
             }
-            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<0, BVH == BDPT_BVH_REFERENCE>(stats, ts);
             if (!defer) { cls = finish_trace(sc, f, w, pid, found, h, film); ended = cls < 0; }
         }
     }
@@ -452,7 +452,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
             if (e & kSlowFlag) rc = split_walk<false, STATS>(sc, r, h, l_stack, ts);
             if (lane0) {
             const bool found = rc == TR_DEFER ? traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts) : rc == TR_HIT;
-            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<0, false>(stats, ts);
             cls = finish_trace(sc, f, w, pid, found, h, film);
             ended = cls < 0;
             }
@@ -474,7 +474,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
             int cls = -1;
             bool ended = false, defer = false;
             if (fin) {
-                if (STATS && result != TR_DEFER && result != TR_SLOW) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+                if (STATS && result != TR_DEFER && result != TR_SLOW) add_trav<0, false>(stats, W.ts);
                 if (result == TR_DEFER || result == TR_SLOW) defer = true;
                 else { cls = finish_trace(sc, f, w, pid, result == TR_HIT, W.hit, film); ended = cls < 0; }
             }
@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_trace_w32(SceneView
             HitD h;
             TravStats ts{0, 0};
             const bool found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
-            if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<0, true>(stats, ts);
             cls = finish_trace(sc, f, w, pid, found, h, film);
             ended = cls < 0;
         }
@@ -578,7 +578,7 @@ __global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_trace_w32(SceneView
                 if (rc == TR_HIT) rc = W.decide(sc, load_path_ray(w, pid), h, true);
                 if (rc == TR_DEFER) defer = true;
                 else {
-                    if (STATS) { atomicAdd(&stats[ST_NODE_CLOSEST], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_CLOSEST], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_CLOSEST], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+                    if (STATS) add_trav<0, false>(stats, W.ts);
                     cls = finish_trace(sc, f, w, pid, rc == TR_HIT, h, film);
                     ended = cls < 0;
                 }
@@ -893,7 +893,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow_pre(SceneView sc, WF w, SQ q,
         const RayD r = load_shadow_ray(q, idx);
         TravStats ts{0, 0};
         live = !far_endpoint_occludes(sc, r, q.far[idx], STATS ? &ts : nullptr);
-        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+        if (STATS) add_trav<1, false>(stats, ts);
     }
     const uint32_t slot = warp_append(q.cnt + SQ_LIVE, live);
     if (live) q.live[slot] = idx;
@@ -915,7 +915,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView s
             HitD h;
             TravStats ts{0, 0};
             const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
-            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<1, true>(stats, ts);
             if (!found) film_add(film, q.pix[i], mk(q.cx[i], q.cy[i], q.cz[i]));
         }
         return;
@@ -936,7 +936,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView s
             bool found;
             if (q5.y) found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
             else found = traverse_fast<true, STATS, false>(sc, r, h, l_stack, 1, &ts) == TR_HIT;
-            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<1, false>(stats, ts);
             if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
         }
         return;
@@ -954,7 +954,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView s
         const int rc = traverse_fast<true, STATS, true>(sc, r, h, l_stack, 1, &ts, limit);
         park = rc == TR_DEFER || rc == TR_SLOW;
         kind = rc == TR_DEFER ? 1 : 0;
-        if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+        if (STATS) add_trav<1, false>(stats, ts);
         if (rc == TR_MISS) film_add(film, q.pix[idx], mk(q.cx[idx], q.cy[idx], q.cz[idx]));
     }
     const uint32_t slot = warp_append(w.counters + C_SLOW_S0 + sx, park);
@@ -971,7 +971,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView s
             HitD h;
             TravStats ts{0, 0};
             const bool found = traverse_fast<true, STATS, false>(sc, r, h, l_stack, 1, &ts) == TR_HIT;
-            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); }
+            if (STATS) add_trav<1, false>(stats, ts);
             if (!found) film_add(film, pix, c);
         }
     }
@@ -1003,7 +1003,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
             if (q5.y == 0) rc = split_walk<true, STATS>(sc, r, h, l_stack, ts);
             if (!lane0) continue;
             const bool found = rc == TR_DEFER ? traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts) : rc == TR_HIT;
-            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<1, false>(stats, ts);
             if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
         }
         return;
@@ -1026,7 +1026,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow_fast(SceneV
         const bool fin = result != WALK_YIELD;
         if (__any_sync(0xFFFFFFFFu, fin)) {
             const bool park = fin && (result == TR_DEFER || result == TR_SLOW);
-            if (fin && STATS && !park) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+            if (fin && STATS && !park) add_trav<1, false>(stats, W.ts);
             if (fin && result == TR_MISS) film_add(film, q.pix[idx], mk(q.cx[idx], q.cy[idx], q.cz[idx]));
             const uint32_t slot = warp_append(w.counters + C_SLOW_S0 + sx, park);
             if (park) {
@@ -1093,7 +1093,7 @@ __global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_shadow_w32(SceneVie
             HitD h;
             TravStats ts{0, 0};
             const bool found = traverse_ref<true, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
-            if (STATS) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(ts.nodes + ts.tris)); }
+            if (STATS) add_trav<1, true>(stats, ts);
             if (!found) film_add(film, uint32_t(q5.x), mk(q3.y, q4.x, q4.y));
         }
         return;
@@ -1120,7 +1120,7 @@ __global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_shadow_w32(SceneVie
                 HitD h;
                 if (rc == TR_HIT) rc = W.occluded ? TR_HIT : W.decide(sc, load_shadow_ray(q, idx), h, true);
                 park = rc == TR_DEFER;
-                if (STATS && !park) { atomicAdd(&stats[ST_NODE_SHADOW], (unsigned long long)W.ts.nodes); atomicAdd(&stats[ST_TRI_SHADOW], (unsigned long long)W.ts.tris); atomicMax(&stats[ST_MAX_SHADOW], (unsigned long long)(W.ts.nodes + W.ts.tris)); }
+                if (STATS && !park) add_trav<1, false>(stats, W.ts);
                 if (rc == TR_MISS) film_add(film, q.pix[idx], mk(q.cx[idx], q.cy[idx], q.cz[idx]));
                 have = false;
                 result = WALK_YIELD;
@@ -1302,6 +1302,7 @@ struct Job {
     size_t smem; unsigned exact_grid; int device; int n_workers;
     int64_t B;                       // sample slots per wavefront (every worker's workspace holds at least this many)
     std::atomic<int64_t>* next;      // next sample of this call not yet handed to a worker
+    std::atomic<int64_t>* progress;  // the context's public copy of it (bdpt_render_progress)
     uint32_t limit, limit_shadow;    // work limits of the bulk traversal launches (traverse_walk.cuh); 0 = none
     unsigned resident_blocks;        // blocks of a traversal kernel the device keeps resident (persistent grids)
     int threshold;                   // dynamic fetch: a walk yields when fewer lanes than this are still walking
@@ -1363,6 +1364,7 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         int64_t ngen = 0, gen_base = 0;
         if (n_free > 0) {
             gen_base = J.next->fetch_add(n_free);
+            J.progress->store(std::min<int64_t>(J.total, gen_base + n_free), std::memory_order_relaxed);
             ngen = std::max<int64_t>(0, std::min<int64_t>(n_free, J.total - gen_base));
         }
         if (ngen == 0 && n_active == 0 && n_def == 0) break;
@@ -1609,6 +1611,9 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     }
     std::atomic<int64_t> next_sample{0};
     J.next = &next_sample;
+    J.progress = &ctx->progress_done;
+    ctx->progress_done.store(0, std::memory_order_relaxed);
+    ctx->progress_total.store(total, std::memory_order_relaxed);
 
     // the film clear (and anything else queued on the context stream) happens-before the workers
     BDPT_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
@@ -1629,7 +1634,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_ms = ms;
     // tallies go into the device counter block so bdpt_stats reads one place
-    unsigned long long cur_stats[16];
+    unsigned long long cur_stats[ST_COUNT];
     BDPT_CUDA(ctx, cudaMemcpy(cur_stats, ctx->d_stats, sizeof cur_stats, cudaMemcpyDeviceToHost));
     for (int i = 0; i < S; ++i) {
         const Worker& wk = *ws->w[i];

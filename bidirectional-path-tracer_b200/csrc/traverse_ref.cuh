@@ -25,7 +25,9 @@ struct HitD {
     uint32_t prim;
 };
 
-struct TravStats { uint32_t nodes, tris; };
+// nodes = boxes fetched (the reference tree: one aabb test each, bvh.h:51 + aabb.h:42; the fast tree: two child boxes
+// each), box_hits = boxes passed (aabb.h:64), tris = triangle tests (triangle.h:42), tri_hits = accepted (triangle.h:72)
+struct TravStats { uint32_t nodes, tris, box_hits, tri_hits; };
 
 __device__ __forceinline__ RefNode load_ref_node(const RefNode* p) {
     // 4 x LDG.128 through the read-only path
@@ -100,20 +102,23 @@ __device__ __forceinline__ bool traverse_ref(const SceneView& sc, const RayD& r,
     bool found = false;
     int sp = 0;
     int32_t cur = 0;  // root
-    uint32_t nn = 0, nt = 0;
+    uint32_t nn = 0, nt = 0, nb = 0, nh = 0;
     for (;;) {
         RefNode n = load_ref_node(sc.ref_nodes + cur);
         if (STATS) ++nn;
         bool descend = false;
         if (box_hit(n, r.o, adinv, r.tmin, best)) {
+            if (STATS) ++nb;
             if (n.leaf) {
                 if (STATS) nt += 2;
                 if (tri_hit(sc.tris + n.left, r.o, r.d, r.tmin, best, hit.t, hit.u, hit.v)) {
                     best = hit.t; hit.prim = uint32_t(n.left); found = true;
+                    if (STATS) ++nh;
                     if (ANY) break;
                 }
                 if (tri_hit(sc.tris + n.right, r.o, r.d, r.tmin, best, hit.t, hit.u, hit.v)) {
                     best = hit.t; hit.prim = uint32_t(n.right); found = true;
+                    if (STATS) ++nh;
                     if (ANY) break;
                 }
             } else {
@@ -129,7 +134,7 @@ __device__ __forceinline__ bool traverse_ref(const SceneView& sc, const RayD& r,
             cur = stack[sp * stride];
         }
     }
-    if (STATS && st) { st->nodes += nn; st->tris += nt; }
+    if (STATS && st) { st->nodes += nn; st->tris += nt; st->box_hits += nb; st->tri_hits += nh; }
     return found;
 }
 

@@ -175,7 +175,7 @@ struct Walk32 {
         best_t = R.best_t;
         cur = 0; sp = 0; ncand = 0; c0 = c1 = c2 = c3 = 0; skip = skip_prim;
         flagged = false; occluded = false;
-        ts.nodes = 0; ts.tris = 0;
+        ts.nodes = 0; ts.tris = 0; ts.box_hits = 0; ts.tri_hits = 0;
     }
 
     __device__ __forceinline__ int filter(const Tri32* __restrict__ T, float& t_hi, uint32_t& prim) const {
@@ -257,6 +257,7 @@ struct Walk32 {
                     slab_fma(b.w, c.z, noy, iy, rn, rf);
                     slab_fma(c.x, c.w, noz, iz, rn, rf);
                     const bool hl = ln <= lf, hr = rn <= rf;
+                    if (STATS) ts.box_hits += uint32_t(hl) + uint32_t(hr);
                     const bool swap = rn < ln;
                     if (hl && hr) { stack[sp] = pack_entry(swap ? w.x : w.y, swap ? ln : rn); ++sp; }
                     cur = (hl && hr) ? (swap ? w.y : w.x) : (hl ? w.x : (hr ? w.y : kWalkPop));
@@ -317,6 +318,7 @@ struct Walk32 {
                 if (found && fabs(t - best) <= band) flagged = true;                          // tie with the current best
                 if (fabs(t - r.tmin) <= band || fabs(t - r.tmax) <= band) flagged = true;     // knife edge
                 if (r.tmin <= t && t <= best && (!found || t < best)) {
+                    if (STATS && last) ++ts.tri_hits;
                     best = t; found = true; best_k = ck;
                     hit.t = t; hit.u = u; hit.v = v;
                 }

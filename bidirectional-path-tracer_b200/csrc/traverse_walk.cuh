@@ -72,7 +72,7 @@ struct Walk {
         found = false; flagged = false;
         sp = 0; cur = 0; pend = 0;
         n_edge = 0;
-        ts.nodes = 0; ts.tris = 0;
+        ts.nodes = 0; ts.tris = 0; ts.box_hits = 0; ts.tri_hits = 0;
     }
 
     // pops until a child still within reach is found; false when the stack is empty
@@ -125,6 +125,7 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run(const SceneView& sc, StackE
             slab_fma(b.w, c.z, oy, iy, rn, rf);
             slab_fma(c.x, c.w, oz, iz, rn, rf);
             const bool hl = ln <= lf, hr = rn <= rf;
+            if (STATS) ts.box_hits += uint32_t(hl) + uint32_t(hr);
             int32_t lc = w.x, rc = w.y;
             if (hl && hr) {
                 float far_t = rn;
@@ -224,6 +225,7 @@ __device__ __forceinline__ bool Walk<ANY, STATS>::leaf_tests(const SceneView& sc
             }
             if (r.tmin <= t && t <= r.tmax) {                  // certain occluder
                 hit.t = t; hit.u = u; hit.v = v; hit.prim = prim; found = true;
+                if (STATS) ++ts.tri_hits;
                 return true;
             }
         } else {
@@ -233,6 +235,7 @@ __device__ __forceinline__ bool Walk<ANY, STATS>::leaf_tests(const SceneView& sc
             // tie is inside the band above, so the ray is flagged and re-traced through the reference tree
             if (r.tmin <= t && t <= best) {
                 if (!found || t < best) {
+                    if (STATS) ++ts.tri_hits;
                     best = t; found = true;
                     best_t = fminf(__double2float_ru(best), cull_hi);
                     hit.u = u; hit.v = v; hit.prim = prim;   // hit.t: `best`, copied by finish()

@@ -1,8 +1,12 @@
 // camera::render (src/camera.h:43-145): the frame loop, re-hosted on libbdpt.  The worker threads and the
 // shared-mt19937 sample loop of the reference are replaced by one host thread per GPU driving the
-// wavefront kernels; strata are sharded across GPUs and the film sums are added on the host
-// (the NCCL path lives in the torch.distributed harness of bench.py; this CLI has no NCCL dependency).
+// wavefront kernels; strata are sharded across GPUs and the per-GPU film sums are added by ONE NCCL
+// sum-reduce over NVLink onto GPU 0 (bdpt_film_reduce), which alone is read back.  The progress bar (camera.h:67-109)
+// and the BvhStats block (stats.h:34-50, camera.h:144) keep the reference's format on std::clog.
+#include <atomic>
 #include <chrono>
+#include <cmath>
+#include <iomanip>
 #include <iostream>
 #include <stdexcept>
 #include <thread>
@@ -10,14 +14,23 @@
 #include "scene.h"
 
 namespace {
-struct guard {
-    bdpt_ctx* c = nullptr;
-    ~guard() { if (c) bdpt_ctx_destroy(c); }
+struct ctx_set {
+    std::vector<bdpt_ctx*> c;
+    ~ctx_set() { for (auto* x : c) if (x) bdpt_ctx_destroy(x); }
 };
 void check(int rc, bdpt_ctx* ctx, const char* what) {
     if (rc) throw std::runtime_error(std::string(what) + " failed: " + bdpt_last_error(ctx));
 }
 }  // namespace
+
+void print_bvh_stats(std::ostream& os, const render_report& r) {   // stats.h:34-50, same lines
+    os << "\nBVH Stats:\n";
+    os << "  Rays traced:         " << r.rays_closest << "\n";
+    os << "  BVH nodes built:     " << r.bvh_nodes_built << "\n";
+    os << "  AABB tests:          " << r.aabb_tests << " (hits: " << r.aabb_hits << ")\n";
+    os << "  BVH node visits:     " << r.bvh_node_visits << "\n";
+    os << "  Triangle tests:      " << r.triangle_tests << " (hits: " << r.triangle_hits << ")\n";
+}
 
 void camera::render(const hittable& world, const hittable& lights) {
     (void)lights;
@@ -49,57 +62,98 @@ void camera::render(const hittable& world, const hittable& lights) {
     const int W = image_width;
     const int G = options.gpus < 1 ? 1 : options.gpus;
 
-    const auto t0 = std::chrono::steady_clock::now();
-    std::vector<std::vector<double>> films(G);
+    using clock = std::chrono::steady_clock;
+    const auto t0 = clock::now();
+    ctx_set ctxs;
+    ctxs.c.assign(G, nullptr);
+    for (int g = 0; g < G; ++g)
+        if (bdpt_ctx_create(g, &ctxs.c[g])) throw std::runtime_error(std::string("bdpt_ctx_create: ") + bdpt_last_error(nullptr));
     std::vector<std::string> errors(G);
     std::vector<bdpt_stats_t> stats(G);
     std::vector<double> ms(G, 0.0);
+    std::atomic<int> rendering{G};
     auto worker = [&](int g) {
         try {
-            guard ctx;
-            if (bdpt_ctx_create(g, &ctx.c)) throw std::runtime_error(std::string("bdpt_ctx_create: ") + bdpt_last_error(nullptr));
-            if (from_image) check(bdpt_scene_upload_image(ctx.c, image, image_bytes, 0), ctx.c, "bdpt_scene_upload_image");
-            else check(bdpt_scene_upload(ctx.c, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx.c, "bdpt_scene_upload");
-            check(bdpt_film_clear(ctx.c, W, H), ctx.c, "bdpt_film_clear");
+            bdpt_ctx* ctx = ctxs.c[g];
+            if (from_image) check(bdpt_scene_upload_image(ctx, image, image_bytes, 0), ctx, "bdpt_scene_upload_image");
+            else check(bdpt_scene_upload(ctx, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx, "bdpt_scene_upload");
+            check(bdpt_film_clear(ctx, W, H), ctx, "bdpt_film_clear");
             bdpt_render_opts o{};
             o.seed = options.seed; o.stratum_begin = g; o.stratum_step = G; o.bvh = options.bvh;
-            check(bdpt_render(ctx.c, &c, &o), ctx.c, "bdpt_render");
-            films[g].resize(size_t(W) * H * 3);
-            check(bdpt_film_download(ctx.c, films[g].data()), ctx.c, "bdpt_film_download");
-            bdpt_stats(ctx.c, &stats[g]);
-            bdpt_last_device_ms(ctx.c, &ms[g]);
+            o.flags = options.stats ? BDPT_RENDER_STATS : 0;
+            check(bdpt_render(ctx, &c, &o), ctx, "bdpt_render");
+            bdpt_stats(ctx, &stats[g]);
+            bdpt_last_device_ms(ctx, &ms[g]);
         } catch (const std::exception& e) { errors[g] = e.what(); }
+        rendering.fetch_sub(1);
     };
+    // Progress bar, camera.h:67-109: the reference counts finished rows; here the samples handed to the GPUs, in rows
+    const int barWidth = progress_bar_length;
+    const int total_rows = H;
+    auto put_time = [](std::ostream& os, double seconds) {
+        const int rem = int(std::ceil(seconds)), hrs = rem / 3600, mins = (rem % 3600) / 60, secs = rem % 60;
+        os << (hrs > 0 ? (std::to_string(hrs) + ":") : "") << std::setfill('0') << std::setw(2) << mins << ':' << std::setw(2) << secs << std::setfill(' ');
+    };
+    std::thread reporter([&] {
+        if (options.quiet || barWidth <= 0) return;
+        while (rendering.load() > 0) {
+            uint64_t done_s = 0, total_s = 0;
+            for (int g = 0; g < G; ++g) { uint64_t d = 0, t = 0; bdpt_render_progress(ctxs.c[g], &d, &t); done_s += d; total_s += t; }
+            const double progress = total_s ? double(done_s) / double(total_s) : 0.0;
+            const int done = int(progress * total_rows), filled = int(progress * barWidth + 0.5);
+            const double dt = std::chrono::duration<double>(clock::now() - t0).count();
+            const double rps = dt > 0.0 ? done / dt : 0.0, sec_left = rps > 0.0 ? (total_rows - done) / rps : 0.0;
+            std::clog << '\r' << '[' << std::string(filled, '#') << std::string(barWidth - filled, ' ') << "] " << std::setw(3) << int(progress * 100)
+                      << "% | " << done << "/" << total_rows << " | ETA: ";
+            put_time(std::clog, sec_left);
+            std::clog << std::flush;
+            for (int k = 0; k < 10 && rendering.load() > 0; ++k) std::this_thread::sleep_for(std::chrono::milliseconds(100));
+        }
+        std::clog << "\r[" << std::string(barWidth, '#') << "] 100% | " << total_rows << "/" << total_rows << " | Runtime: ";
+        put_time(std::clog, std::chrono::duration<double>(clock::now() - t0).count());
+        std::clog << "\n";
+    });
     std::vector<std::thread> pool;
     for (int g = 1; g < G; ++g) pool.emplace_back(worker, g);
     worker(0);
     for (auto& th : pool) th.join();
+    reporter.join();
     for (int g = 0; g < G; ++g) if (!errors[g].empty()) throw std::runtime_error("GPU " + std::to_string(g) + ": " + errors[g]);
 
     render_report rep;
     rep.width = W; rep.height = H;
-    rep.film = films[0];
-    for (int g = 1; g < G; ++g) for (size_t i = 0; i < rep.film.size(); ++i) rep.film[i] += films[g][i];
+    if (G > 1) {   // the one exchange step of the frame: NCCL sum-reduce of the films onto GPU 0
+        check(bdpt_film_reduce(ctxs.c.data(), G, 0), ctxs.c[0], "bdpt_film_reduce");
+        bdpt_last_device_ms(ctxs.c[0], &rep.film_reduce_ms);
+    }
+    rep.film.resize(size_t(W) * H * 3);
+    check(bdpt_film_download(ctxs.c[0], rep.film.data()), ctxs.c[0], "bdpt_film_download");
     for (int g = 0; g < G; ++g) {
         rep.samples += stats[g].samples; rep.rays_closest += stats[g].rays_closest; rep.rays_shadow += stats[g].rays_shadow;
         rep.launches += stats[g].kernel_launches; rep.device_ms = std::max(rep.device_ms, ms[g]);
+        rep.aabb_tests += stats[g].aabb_tests; rep.aabb_hits += stats[g].aabb_hits; rep.triangle_hits += stats[g].triangle_hits;
+        rep.bvh_node_visits += stats[g].nodes_closest + stats[g].nodes_shadow;
+        rep.triangle_tests += stats[g].tris_closest + stats[g].tris_shadow;
     }
-    rep.wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    rep.bvh_nodes_built = stats[0].bvh_nodes_built;
+    rep.wall_s = std::chrono::duration<double>(clock::now() - t0).count();
 
     if (options.write_file) {
         const int n = int(std::sqrt(double(samples_per_pixel)));
-        std::vector<color> fb(size_t(W) * H);
-        for (size_t i = 0; i < fb.size(); ++i) fb[i] = color(rep.film[3 * i], rep.film[3 * i + 1], rep.film[3 * i + 2]);
-        std::vector<uint8_t> rgb;
-        colors_to_rgb8(fb, W, H, n * n, rgb);          // camera.h:139-141
+        std::vector<uint8_t> rgb(size_t(W) * H * 3);
+        check(bdpt_film_to_rgb8(ctxs.c[0], n * n, rgb.data()), ctxs.c[0], "bdpt_film_to_rgb8");   // camera.h:139-141 (wpng.h:14-35 on the device film)
         write_png(file_name, rgb, W, H);               // camera.h:142
     }
     if (!options.quiet) {
+        print_bvh_stats(std::clog, rep);               // camera.h:144
+        if (!options.stats) std::clog << "  (box / node / triangle counters need --stats; rays traced = closest-hit queries, camera.h:334)\n";
         std::clog << "Rendered " << W << "x" << H << " @ " << rep.samples / double(size_t(W) * H) << " spp on " << G << " GPU(s): "
                   << rep.device_ms << " ms device, " << rep.wall_s << " s wall, "
                   << rep.samples / (rep.device_ms * 1e3) << " Msamples/s, "
                   << (rep.rays_closest + rep.rays_shadow) / (rep.device_ms * 1e3) << " Mrays/s ("
-                  << rep.rays_closest << " closest + " << rep.rays_shadow << " shadow), " << rep.launches << " kernel launches\n";
+                  << rep.rays_closest << " closest + " << rep.rays_shadow << " shadow), " << rep.launches << " kernel launches";
+        if (G > 1) std::clog << ", film reduce (NCCL) " << rep.film_reduce_ms << " ms";
+        std::clog << "\n";
     }
     last_report = std::move(rep);
 }

@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdint>
 #include <memory>
+#include <ostream>
 #include <string>
 #include <vector>
 
@@ -116,6 +117,7 @@ struct render_options {         // overrides the CLI adds on top of the YAML (SU
     int bvh = BDPT_BVH_FAST;    // both give the reference's hits; REFERENCE also walks its topology
     uint64_t seed = 0;
     bool quiet = false;
+    bool stats = false;         // count the reference's BvhStats (stats.h:8-16) during the render (BDPT_RENDER_STATS: slower)
     bool write_file = true;     // write ./output/<file_name> like camera.h:139-142
     // a prebuilt scene image (include/bdpt.h, bdpt_scene_image_build / _map): when set, render() uploads it instead
     // of flattening `world` and building the trees, and `world` may be empty
@@ -126,6 +128,9 @@ struct render_options {         // overrides the CLI adds on top of the YAML (SU
 struct render_report {
     double device_ms = 0, wall_s = 0;
     uint64_t samples = 0, rays_closest = 0, rays_shadow = 0, launches = 0;
+    // stats.h:8-16, summed over the GPUs (all but rays_traced / bvh_nodes_built are 0 unless options.stats)
+    uint64_t aabb_tests = 0, aabb_hits = 0, bvh_node_visits = 0, triangle_tests = 0, triangle_hits = 0, bvh_nodes_built = 0;
+    double film_reduce_ms = 0;  // several GPUs: the NCCL sum-reduce of the film onto GPU 0
     int width = 0, height = 0;
     std::vector<double> film;   // W*H*3 fp64 SUM over strata (camera.h:55)
 };
@@ -144,6 +149,7 @@ class camera {
     vec3 vup = vec3(0, 1, 0);
     double defocus_angle = 0;
     double focus_dist = 10;
+    int progress_bar_length = 30;   // camera.h:39: width of the progress bar on std::clog
     std::string file_name = "image.png";
 
     render_options options;     // not in the reference: device-side knobs
@@ -166,6 +172,9 @@ scene_load_result load_scene_from_yaml(const std::string& path);   // scene_load
 // key over the bytes of the YAML and of every OBJ file its `object` surfaces name, in scene order.
 camera load_camera_from_yaml(const std::string& path);
 uint64_t scene_source_key(const std::string& path);
+
+// stats.h:34-50: the block camera::render prints on std::clog when it is done (camera.h:144)
+void print_bvh_stats(std::ostream& os, const render_report& r);
 
 // image output, wpng.h:14-89
 void colors_to_rgb8(const std::vector<color>& framebuffer, int image_width, int image_height, int samples_per_pixel,

@@ -94,6 +94,12 @@ typedef struct {
     uint64_t max_work_closest, max_work_shadow;
     /* rays the fast traversal handed to the reference-exact kernels (ties, knife edges, zero direction components) */
     uint64_t deferred_closest, deferred_shadow;
+    /* The rest of the reference's BvhStats (stats.h:8-16), counted with node_visits / tri_tests (BDPT_TRACE_STATS,
+     * BDPT_RENDER_STATS).  Through BDPT_BVH_REFERENCE they are the reference's own numbers for closest-hit queries
+     * (aabb_tests == bvh_node_visits there: bvh.h:51-52); through BDPT_BVH_FAST a node holds both child boxes, so
+     * aabb_tests = 2 x nodes fetched and aabb_hits = child boxes passed.  bvh_nodes_built = nodes of the reference
+     * topology (stats.h:15; bvh.h:14). */
+    uint64_t aabb_tests, aabb_hits, triangle_hits, bvh_nodes_built;
 } bdpt_stats_t;
 
 /* Device time per kernel class of bdpt_render since the last bdpt_stats_reset, from CUDA event pairs on
@@ -189,6 +195,22 @@ int bdpt_film_download(bdpt_ctx* ctx, double* film_sum /* W*H*3 */);
 int bdpt_film_size(bdpt_ctx* ctx, int* width, int* height);
 /* wpng.h:14-35 on the device film: average, clamp [0,0.999], sqrt, 256x truncate. out: W*H*3 bytes (host) */
 int bdpt_film_to_rgb8(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out);
+
+/* ---- the film reduce: the one exchange step of a multi-GPU frame.  Every rank renders its strata
+ * (bdpt_render_opts.stratum_begin / stratum_step) into its own film; ONE ncclReduce(sum, fp64) over NVLink then adds
+ * the films in place onto `root` -- what camera.h:117-124 does with `pixel_color +=` on one framebuffer.
+ * libnccl.so.2 is opened on first use (a process that already holds an NCCL, e.g. torch's, shares it).
+ *   one process, n devices:   bdpt_film_reduce(ctxs, n, root)           (communicators are created once per device list)
+ *   one process per GPU:      id from bdpt_comm_unique_id on one rank, carried to the others by the launcher;
+ *                             bdpt_comm_init on every rank; bdpt_film_reduce_comm(ctx, root) per frame.
+ * Both are blocking; bdpt_last_device_ms then gives the device time of the reduce on the calling / root context. */
+int bdpt_film_reduce(bdpt_ctx** ctxs, int n, int root);
+int bdpt_comm_unique_id(void* id128 /* 128 bytes out */);
+int bdpt_comm_init(bdpt_ctx* ctx, int nranks, int rank, const void* id128);
+int bdpt_film_reduce_comm(bdpt_ctx* ctx, int root);
+/* Samples of the bdpt_render call in flight already handed to the GPU, out of how many: callable from another
+ * thread while bdpt_render runs (the progress bar of camera::render, camera.h:67-109). */
+int bdpt_render_progress(bdpt_ctx* ctx, uint64_t* samples_done, uint64_t* samples_total);
 
 int bdpt_stats(bdpt_ctx* ctx, bdpt_stats_t* out);
 int bdpt_stats_reset(bdpt_ctx* ctx);

@@ -64,6 +64,11 @@ def test_trace_stats_counts_match_oracle(bdpt, gpu_ctx, scenes):
     gs = gpu_ctx.stats()
     assert gs["node_visits"] == s["node_visits"]
     assert gs["tri_tests"] == s["tri_tests"]
+    # the rest of the reference's BvhStats (stats.h:8-16): every counter of its end-of-render block
+    assert gs["aabb_tests"] == s["aabb_tests"] == s["node_visits"]
+    assert gs["aabb_hits"] == s["aabb_hits"]
+    assert gs["triangle_hits"] == s["tri_hits"]
+    assert gs["bvh_nodes_built"] == o.node_count()
     gpu_ctx.stats_reset()
     gpu_ctx.trace(rays, bvh=1, stats=True)
     fs = gpu_ctx.stats()
