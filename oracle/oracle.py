@@ -14,6 +14,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_LIGHT = 0, 1, 2, 3
 RNG_MT19937, RNG_PHILOX = 0, 1
+WEIGHT_REF_SUM, WEIGHT_MIS = 0, 1
 MISS = 0xFFFFFFFF
 
 
@@ -90,6 +91,12 @@ class Oracle:
         self._visible = f("visible"); self._visible.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]
         self._render = f("render"); self._render.restype = C.c_int
         self._render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        if kind == "port":
+            self._render_ex = self.lib.port_render_ex; self._render_ex.restype = C.c_int
+            self._render_ex.argtypes = self._render.argtypes + [C.c_int]
+        else:
+            self._render_pt = self.lib.ref_render_pt; self._render_pt.restype = C.c_int
+            self._render_pt.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p]
         self._stats = f("stats_get"); self._stats.argtypes = [C.c_void_p]
         self._stats_reset = f("stats_reset")
         self._rgb8 = f("colors_to_rgb8"); self._rgb8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
@@ -128,11 +135,25 @@ class Oracle:
         self._visible(self.scene, a.ctypes.data, b.ctypes.data, len(a), out.ctypes.data, nthreads)
         return out.astype(bool)
 
-    def render(self, cam, rng_mode=RNG_MT19937, seed=0, row0=0, row1=1 << 30, nthreads=1, height=None):
+    def render(self, cam, rng_mode=RNG_MT19937, seed=0, row0=0, row1=1 << 30, nthreads=1, height=None, weighting=WEIGHT_REF_SUM):
         W = cam.image_width
         H = height if height is not None else max(1, int(W / cam.aspect_ratio))
         film = np.zeros((H, W, 3), dtype=np.float64)
-        h = self._render(self.scene, C.byref(cam), rng_mode, seed, row0, row1, film.ctypes.data, nthreads)
+        if weighting != WEIGHT_REF_SUM:
+            assert self.kind == "port", "the reference has one estimator; MIS exists in the port only"
+            h = self._render_ex(self.scene, C.byref(cam), rng_mode, seed, row0, row1, film.ctypes.data, nthreads, weighting)
+        else:
+            h = self._render(self.scene, C.byref(cam), rng_mode, seed, row0, row1, film.ctypes.data, nthreads)
+        assert h == H, (h, H)
+        return film
+
+    def render_pt(self, cam, seed=0, row0=0, row1=1 << 30, height=None):
+        """ref only: the reference's own unbiased path tracer (camera::path_trace_color, camera.h:255-292)."""
+        assert self.kind == "ref"
+        W = cam.image_width
+        H = height if height is not None else max(1, int(W / cam.aspect_ratio))
+        film = np.zeros((H, W, 3), dtype=np.float64)
+        h = self._render_pt(self.scene, C.byref(cam), seed, row0, row1, film.ctypes.data)
         assert h == H, (h, H)
         return film
 

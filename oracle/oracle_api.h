@@ -82,6 +82,15 @@ void     ORC(visible)(void* scene, const double* a, const double* b, uint64_t n,
  * written). rng_mode MT19937 requires nthreads==1 for a reproducible stream. Returns image height. */
 int      ORC(render)(void* scene, const orc_camera* cam, int rng_mode, uint64_t seed, int row0,
                      int row1, double* film, int nthreads);
+/* port only: the same with the estimator chosen.  ORC_WEIGHT_REF_SUM = the reference's unweighted sum
+ * (camera.h:294-323); ORC_WEIGHT_MIS = balance-heuristic BDPT with light-tracing splats (film must be zeroed by
+ * the caller: splats ADD into pixels outside [row0,row1)).
+ * ref only: render_pt = the reference's own unbiased path tracer, camera::path_trace_color (camera.h:255-292), over the
+ * same sample loop -- the yardstick the MIS estimator is validated against. */
+enum { ORC_WEIGHT_REF_SUM = 0, ORC_WEIGHT_MIS = 1 };
+int      port_render_ex(void* scene, const orc_camera* cam, int rng_mode, uint64_t seed, int row0, int row1, double* film,
+                        int nthreads, int weighting);
+int      ref_render_pt(void* scene, const orc_camera* cam, uint64_t seed, int row0, int row1, double* film);
 void     ORC(stats_get)(orc_stats* out);
 void     ORC(stats_reset)(void);
 /* wpng.h:14-35 */

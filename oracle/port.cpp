@@ -15,8 +15,10 @@
 #include <atomic>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <mutex>
 #include <random>
 #include <thread>
 #include <vector>
@@ -334,6 +336,8 @@ struct Cam {  // camera.h:148-197
     int H, sqrt_spp;
     double recip_sqrt_spp;
     V3 center, pixel00, du, dv, background;
+    V3 fwd, ul;            // MIS / light tracing only: viewing direction, upper-left corner of the viewport
+    double plane_dist_px;  // distance of the image plane in units of one pixel's side
     explicit Cam(const orc_camera& in) : c(in) {
         H = int(c.image_width / c.aspect_ratio);
         H = (H < 1) ? 1 : H;
@@ -354,8 +358,10 @@ struct Cam {  // camera.h:148-197
         V3 vv = vh * -v;
         du = vu / c.image_width;
         dv = vv / H;
-        V3 ul = center - (c.focus_dist * w) - vu / 2 - vv / 2;
+        ul = center - (c.focus_dist * w) - vu / 2 - vv / 2;
         pixel00 = ul + 0.5 * (du + dv);
+        fwd = -w;
+        plane_dist_px = c.focus_dist / len(du);
     }
     void get_ray(int i, int j, int s_i, int s_j, Rng& r, V3& o, V3& d) const {  // camera.h:199-223
         double px = ((s_i + r.next()) * recip_sqrt_spp) - 0.5;
@@ -516,6 +522,214 @@ struct Integrator {
         return contrib;
     }
 
+    // ------------------------------------------------------------ weighting = MIS (not in the reference: SURVEY F3, 8f-3)
+    // The same two random walks as above (same draws, same vertices), combined with balance-heuristic weights over
+    // every way of building the path: camera path hits the light (s = 0), connection to the light subpath's emitter
+    // point (s = 1), vertex connections (s >= 2) and light tracing onto the film (t = 1, a SPLAT into another pixel).
+    // Weights are kept in the recursive form of Georgiev's vertex-connection formulation (two running quantities
+    // per subpath, dVCM and dVC), which makes every connection O(1).  Differences from the reference's unweighted
+    // sum that an unbiased estimator needs: a lambertian surface reflects only to the side the path arrived on
+    // (material.h:47-52 samples about the face-forwarded normal; the reference's connection uses |cos| on both
+    // sides), emitters are one-sided absorbers on both walks (material.h:140, camera.h:409), a full path holds at
+    // most max_depth surface vertices (what path_trace_color's depth counter allows, camera.h:255-292), and the
+    // shadow segment stops short of the far surface instead of on it.  Metal stays a delta vertex even
+    // when fuzzy, as material.h:85 declares it.
+    // ORC_MIS_ONLY=<mask> (test hook): bit 0 s=0, 1 s=1, 2 s>=2, 3 t=1 -- the chosen strategies with weight 1, the rest
+    // with weight 0, so each family of strategies can be checked on its own against the reference's path tracer
+    static int mis_only() { static const int m = [] { const char* e = std::getenv("ORC_MIS_ONLY"); return e ? std::atoi(e) : 0; }(); return m; }
+    static double pick_w(double w, int bit) { const int m = mis_only(); return m == 0 ? w : ((m >> bit) & 1 ? 1.0 : 0.0); }
+
+    struct MisVertex {
+        V3 p, n, T, albedo;        // position, normal facing the arriving path, throughput up to here
+        double dVCM, dVC, cos_in;
+        int len;                   // surface vertices of the subpath up to and including this one
+    };
+
+    bool visible_mis(V3 a, V3 b) const {
+        V3 dir = b - a;
+        double dist = len(dir);
+        if (dist <= 0) return false;
+        V3 du = dir / dist;
+        double max_t = dist - 0.001 - 1e-6 * (1.0 + dist);   // stops short of b's own surface
+        if (max_t <= 0.001) return false;
+        Hit tmp;
+        ++tl_stats.shadow;
+        return !sc.hit(a + (0.001 * du), du, 0.001, max_t, tmp);
+    }
+
+    double light_area() const {
+        double total = 0.0;
+        for (uint32_t id : sc.lights) total += sc.tris[id].area;
+        return total;
+    }
+
+    // one subpath; `verts` receives its connectable (lambertian) vertices.  camera: adds the s = 0 terms to *result.
+    void walk_mis(V3 o, V3 d, int depth, int len0, V3 T, double dVCM, double dVC, bool camera, double pdfA_light,
+                  std::vector<MisVertex>& verts, V3* result, Rng& rng) const {
+        int length = len0;   // surface vertices already on the subpath (light subpath: the emitter = 1)
+        for (int bounce = 0; bounce < depth; ++bounce) {
+            Hit rec;
+            if (!sc.hit(o, d, 0.001, kInf, rec)) {
+                if (camera) *result = *result + T * cam.background;
+                break;
+            }
+            ++length;
+            const orc_material& m = sc.mats[sc.tris[rec.prim].mat];
+            const double dist2 = rec.t * rec.t * len2(d);
+            const double cos_in = std::fabs(dot(rec.normal, unit(-d)));
+            dVCM *= dist2;
+            dVCM /= cos_in; dVC /= cos_in;
+            if (m.type == ORC_MAT_LIGHT) {           // absorbs; a camera path that arrives on the emitting side sees it
+                if (camera && rec.front) {
+                    V3 Le{m.rgb[0], m.rgb[1], m.rgb[2]};
+                    double w = 1.0;
+                    if (length > 1) {
+                        const double directPdfA = pdfA_light, emissionPdfW = pdfA_light * cos_in / kPi;
+                        w = pick_w(1.0 / (1.0 + directPdfA * dVCM + emissionPdfW * dVC), 0);
+                    }
+                    *result = *result + w * (T * Le);
+                }
+                break;
+            }
+            V3 att{m.rgb[0], m.rgb[1], m.rgb[2]};
+            if (m.type == ORC_MAT_METAL || m.type == ORC_MAT_DIELECTRIC) {
+                V3 dir;
+                if (m.type == ORC_MAT_METAL) {
+                    V3 refl = reflect(d, rec.normal);
+                    dir = unit(refl) + (m.param * random_unit_vector(rng));
+                    T = T * att;
+                } else {
+                    double ri = rec.front ? (1.0 / m.param) : m.param;
+                    V3 ud = unit(d);
+                    double cos_theta = std::fmin(dot(-ud, rec.normal), 1.0);
+                    double sin_theta = std::sqrt(1.0 - cos_theta * cos_theta);
+                    bool refl = ri * sin_theta > 1.0;
+                    if (!refl) {
+                        double r0 = (1 - ri) / (1 + ri);
+                        r0 = r0 * r0;
+                        double rf = r0 + (1 - r0) * (rng.det ? det_pow5(1 - cos_theta) : std::pow((1 - cos_theta), 5));
+                        refl = rf > rng.next();
+                    }
+                    dir = refl ? reflect(ud, rec.normal) : refract(ud, rec.normal, ri);
+                    T = T * V3{1.0, 1.0, 1.0};
+                }
+                const double cos_out = std::fabs(dot(rec.normal, unit(dir)));
+                dVCM = 0.0; dVC *= cos_out;          // a delta vertex cannot be connected to
+                o = rec.p; d = dir;
+                continue;
+            }
+            MisVertex v;
+            v.p = rec.p; v.n = rec.normal; v.T = T; v.albedo = att; v.dVCM = dVCM; v.dVC = dVC; v.cos_in = cos_in; v.len = length;
+            verts.push_back(v);
+            Onb uvw(rec.normal);
+            V3 sd = uvw.transform(random_cosine_direction(rng));
+            double pdf_value = std::fmax(0, dot(unit(sd), uvw.a2) / kPi);
+            if (pdf_value <= 0) break;
+            double ct = dot(rec.normal, unit(sd));
+            double spdf = ct < 0 ? 0 : ct / kPi;
+            T = T * att * spdf / pdf_value;
+            const double dirPdfW = pdf_value, revPdfW = cos_in / kPi;
+            dVC = (ct / dirPdfW) * (dVC * revPdfW + dVCM);
+            dVCM = 1.0 / dirPdfW;
+            o = rec.p; d = sd;
+        }
+    }
+
+    // one sample: returns what lands in its own pixel; light-tracing splats go through `splat(pixel, colour)`
+    template <class Splat>
+    V3 sample_mis(V3 o, V3 d, int depth, Rng& cam_rng, Rng& light_rng, int W, int H, Splat splat) const {
+        const double n_light = double(W) * double(H);   // light subpaths per pass over the frame: every one may splat anywhere
+        V3 result{0, 0, 0};
+        std::vector<MisVertex> cp, lp;
+        const double total = light_area();
+        const double pdfA = total > 0 ? 1.0 / total : 0.0;
+        {   // camera subpath: the pdf of a primary ray per unit solid angle, for an image plane measured in pixels
+            const double c = dot(unit(d), cam.fwd);
+            const double cameraPdfW = cam.plane_dist_px * cam.plane_dist_px / (c * c * c);
+            walk_mis(o, d, depth, 0, {1, 1, 1}, n_light / cameraPdfW, 0.0, true, pdfA, cp, &result, cam_rng);
+        }
+        // light subpath: build_light_path's emitter and first direction (camera.h:372-414), same draws
+        if (depth <= 0 || sc.lights.empty() || total <= 0.0) return result;
+        double pick = light_rng.next(0.0, total);
+        const Tri* chosen = &sc.tris[sc.lights.back()];
+        double accum = 0.0;
+        for (uint32_t id : sc.lights) {
+            accum += sc.tris[id].area;
+            if (pick <= accum) { chosen = &sc.tris[id]; break; }
+        }
+        double u = light_rng.next(), v = light_rng.next();
+        if (u + v > 1.0) { u = 1.0 - u; v = 1.0 - v; }
+        const V3 y0 = chosen->v0 + (u * chosen->e1) + (v * chosen->e2), n0 = chosen->normal;
+        const V3 Le = emitted(sc.mats[chosen->mat], true);
+        if (len2(Le) <= 0) return result;
+        {
+            V3 dir = Onb(n0).transform(random_cosine_direction(light_rng));
+            V3 du = unit(dir);
+            double cos_theta = std::max(0.0, dot(n0, du));
+            if (cos_theta > 0) {
+                const double emissionPdfW = pdfA * std::max(cos_theta / kPi, 1e-8);
+                V3 T = (V3{1.0, 1.0, 1.0} / std::max(pdfA, 1e-8)) * Le * (cos_theta / std::max(cos_theta / kPi, 1e-8));
+                walk_mis(y0 + (0.001 * n0), du, depth - 1, 1, T, pdfA / emissionPdfW, cos_theta / emissionPdfW, false, pdfA, lp, nullptr, light_rng);
+            }
+        }
+        for (const MisVertex& c : cp) {
+            const V3 fc = c.albedo / kPi;
+            // s = 1: the emitter point itself
+            if (c.len + 1 <= depth) {
+                V3 dir = y0 - c.p;
+                double dist2 = len2(dir);
+                if (dist2 > 0) {
+                    V3 du = unit(dir);
+                    const double cosToLight = dot(c.n, du), cosAtLight = dot(n0, -du);
+                    if (cosToLight > 0 && cosAtLight > 0 && visible_mis(c.p, y0)) {
+                        const double directPdfW = pdfA * dist2 / cosAtLight, emissionPdfW = pdfA * cosAtLight / kPi;
+                        const double wLight = (cosToLight / kPi) / directPdfW;
+                        const double wCamera = (emissionPdfW * cosToLight / (directPdfW * cosAtLight)) * (c.dVCM + c.dVC * (c.cos_in / kPi));
+                        const double w = pick_w(1.0 / (wLight + 1.0 + wCamera), 1);
+                        result = result + (w * cosToLight / directPdfW) * (c.T * fc * Le);
+                    }
+                }
+            }
+            // s >= 2
+            for (const MisVertex& l : lp) {
+                if (c.len + l.len > depth) continue;
+                V3 dir = l.p - c.p;
+                double dist2 = len2(dir);
+                if (dist2 <= 0) continue;
+                V3 du = unit(dir);
+                const double cosCamera = dot(c.n, du), cosLight = dot(l.n, -du);
+                if (cosCamera <= 0 || cosLight <= 0) continue;
+                if (!visible_mis(c.p, l.p)) continue;
+                const double camDirPdfA = (cosCamera / kPi) * cosLight / dist2, lightDirPdfA = (cosLight / kPi) * cosCamera / dist2;
+                const double wLight = camDirPdfA * (l.dVCM + l.dVC * (l.cos_in / kPi));
+                const double wCamera = lightDirPdfA * (c.dVCM + c.dVC * (c.cos_in / kPi));
+                const double w = pick_w(1.0 / (wLight + 1.0 + wCamera), 2);
+                result = result + (w * cosLight * cosCamera / dist2) * (c.T * fc * l.T * (l.albedo / kPi));
+            }
+        }
+        // t = 1: every light-subpath vertex seen from the camera lands on the film, wherever that is
+        for (const MisVertex& l : lp) {
+            V3 dir = cam.center - l.p;
+            double dist2 = len2(dir);
+            if (dist2 <= 0) continue;
+            V3 du = unit(dir);
+            const double cosToCamera = dot(l.n, du), cosAtCamera = dot(cam.fwd, -du);
+            if (cosToCamera <= 0 || cosAtCamera <= 0) continue;
+            // where the line camera -> vertex crosses the viewport, in pixel coordinates from its upper-left corner
+            V3 P = cam.center + (cam.c.focus_dist / cosAtCamera) * (-du);
+            V3 rel = P - cam.ul;
+            const double xc = dot(rel, cam.du) / len2(cam.du), yc = dot(rel, cam.dv) / len2(cam.dv);
+            if (!(xc >= 0 && yc >= 0 && xc < W && yc < H)) continue;
+            if (!visible_mis(l.p, cam.center)) continue;
+            const double ipcd = cam.plane_dist_px / cosAtCamera;
+            const double imageToSurface = (ipcd * ipcd / cosAtCamera) * cosToCamera / dist2;
+            const double wLight = (imageToSurface / n_light) * (l.dVCM + l.dVC * (l.cos_in / kPi));
+            const double w = pick_w(1.0 / (wLight + 1.0), 3);
+            splat(int(yc) * W + int(xc), (w * imageToSurface / n_light) * (l.T * (l.albedo / kPi)));
+        }
+        return result;
+    }
+
     V3 sample(V3 o, V3 d, int depth, Rng& cam_rng, Rng& light_rng) const {  // camera.h:294-323
         std::vector<Vertex> cp, lp;
         cp.reserve(depth);
@@ -602,7 +816,8 @@ void port_visible(void* p, const double* a, const double* b, uint64_t n, uint8_t
     });
 }
 
-int port_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int row0, int row1, double* film, int nthreads) {
+int port_render_ex(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int row0, int row1, double* film, int nthreads,
+                   int weighting) {
     auto* s = static_cast<Scene*>(p);
     Cam cam(*c);
     Integrator integ(*s, cam);
@@ -614,6 +829,11 @@ int port_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int r
     std::mt19937 mt;  // default seed, as the reference's static generator (main.h:28-32) ...
     if (seed) mt.seed(uint32_t(seed));  // ... unless the caller asks for an independent stream (convergence tests)
     std::uniform_real_distribution<double> dist(0.0, 1.0);
+    std::mutex splat_mu;   // MIS: light-tracing splats land in other threads' rows
+    auto splat = [&](int pix, V3 cval) {
+        std::lock_guard<std::mutex> lock(splat_mu);
+        film[3 * size_t(pix)] += cval.x; film[3 * size_t(pix) + 1] += cval.y; film[3 * size_t(pix) + 2] += cval.z;
+    };
     parallel_for(uint64_t(row1 - row0), nthreads, [&](uint64_t a, uint64_t b) {
         Rng cr, lr;
         if (rng_mode == ORC_RNG_MT19937) { cr.mt = lr.mt = &mt; cr.dist = lr.dist = &dist; }
@@ -631,13 +851,21 @@ int port_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int r
                         }
                         V3 o, d;
                         cam.get_ray(i, j, s_i, s_j, cr, o, d);
-                        px = px + integ.sample(o, d, c->max_depth, cr, lr);
+                        px = px + (weighting == ORC_WEIGHT_MIS ? integ.sample_mis(o, d, c->max_depth, cr, lr, W, H, splat)
+                                                              : integ.sample(o, d, c->max_depth, cr, lr));
                     }
-                double* out = film + 3 * (size_t(j) * W + i);
-                out[0] = px.x; out[1] = px.y; out[2] = px.z;
+                if (weighting == ORC_WEIGHT_MIS) splat(j * W + i, px);   // the film already holds splats: add, under the lock
+                else {
+                    double* out = film + 3 * (size_t(j) * W + i);
+                    out[0] = px.x; out[1] = px.y; out[2] = px.z;
+                }
             }
     });
     return H;
+}
+
+int port_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int row0, int row1, double* film, int nthreads) {
+    return port_render_ex(p, c, rng_mode, seed, row0, row1, film, nthreads, ORC_WEIGHT_REF_SUM);
 }
 
 void port_stats_get(orc_stats* o) {

@@ -221,6 +221,32 @@ int ref_render(void* p, const orc_camera* c, int rng_mode, uint64_t seed, int ro
     return H;
 }
 
+int ref_render_pt(void* p, const orc_camera* c, uint64_t seed, int row0, int row1, double* film) {
+    for (uint64_t k = 0, n = (seed % 4096u) * 100003ull; k < n; ++k) (void)random_double();   // see ref_render
+    auto* s = static_cast<ref_scene*>(p);
+    camera cam;
+    set_camera(cam, c);
+    cam.initialize();
+    const int W = cam.image_width, H = cam.image_height;
+    row0 = std::max(0, row0);
+    row1 = std::min(H, row1);
+    const triangle_collection& lights = s->lights.empty() ? s->world : s->lights;   // main.cpp:67
+    const hittable& world = *s->bvh;
+    const hittable& as_hittable = lights;   // path_trace_color takes the lights as a plain hittable (camera.h:255)
+    for (int j = row0; j < row1; ++j)
+        for (int i = 0; i < W; ++i) {
+            color pixel_color(0, 0, 0);
+            for (int s_j = 0; s_j < cam.sqrt_spp; s_j++)
+                for (int s_i = 0; s_i < cam.sqrt_spp; s_i++) {
+                    ray r = cam.get_ray(i, j, s_i, s_j);
+                    pixel_color += cam.path_trace_color(r, cam.max_depth, world, as_hittable);
+                }
+            double* o = film + 3 * (size_t(j) * W + i);
+            o[0] = pixel_color.x(); o[1] = pixel_color.y(); o[2] = pixel_color.z();
+        }
+    return H;
+}
+
 void ref_stats_get(orc_stats* o) {
     auto& s = bvh_stats();
     o->rays = s.rays_traced.load();
