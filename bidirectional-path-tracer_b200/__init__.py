@@ -16,6 +16,7 @@ LIB_PATH = os.environ.get("BDPT_LIB") or os.path.join(HERE, "libbdpt.so")   # BD
 
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_LIGHT = 0, 1, 2, 3
 BVH_REFERENCE, BVH_FAST = 0, 1
+WEIGHT_REF_SUM, WEIGHT_MIS = 0, 1
 TRACE_CLOSEST, TRACE_ANY, TRACE_DEVICE_PTRS, TRACE_STATS, TRACE_SPLIT = 0, 1, 16, 32, 64
 MISS = 0xFFFFFFFF
 
@@ -50,7 +51,8 @@ class Camera(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("stratum_begin", C.c_int32), ("stratum_end", C.c_int32),
                 ("stratum_step", C.c_int32), ("bvh", C.c_int32), ("row_begin", C.c_int32),
-                ("row_end", C.c_int32), ("batch_samples", C.c_int64), ("flags", C.c_int32), ("streams", C.c_int32)]
+                ("row_end", C.c_int32), ("batch_samples", C.c_int64), ("flags", C.c_int32), ("streams", C.c_int32),
+                ("weighting", C.c_int32), ("pad", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -440,7 +442,7 @@ class Context:
         self.film_shape = (int(height), int(width), 3)
 
     def render(self, cam, seed=0, bvh=BVH_REFERENCE, strata=(0, 0, 1), rows=(0, 0), batch_samples=0, clear=True,
-               height=None, stats=False, streams=0, serial=False):
+               height=None, stats=False, streams=0, serial=False, weighting=WEIGHT_REF_SUM):
         """camera::render's sample loop; returns nothing — read the film with film().  The film's row count is
         the reference's int(image_width / aspect_ratio) (camera.h:161-162), decided by the library; `height`, when
         given, is only checked against it (make_camera / camera_with pick an aspect ratio that yields it)."""
@@ -459,6 +461,7 @@ class Context:
         o.batch_samples = batch_samples
         o.flags = (RENDER_STATS if stats else 0) | (RENDER_SERIAL if serial else 0)
         o.streams = streams
+        o.weighting = weighting
         self._chk(lib().bdpt_render(self._h, C.byref(cam), C.byref(o)), "bdpt_render")
         if self.film_size() != (W, H):   # one source of truth: the library's film
             raise BdptError("film is %r after bdpt_render, expected %r" % (self.film_size(), (W, H)))

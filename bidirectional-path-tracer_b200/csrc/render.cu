@@ -57,6 +57,10 @@ struct Frame {           // camera.h:148-197 derived values + this call's sample
     int s_begin, s_step; // selected strata: s_begin + k*s_step
     uint64_t seed;
     int64_t npix;        // rows * W
+    // BDPT_WEIGHT_MIS only: viewing direction, upper-left corner of the viewport, |du|^2, |dv|^2, distance of the image
+    // plane in pixel sides, focus distance, light subpaths per pass over the frame (= W * H)
+    D3 fwd, ul;
+    double du2, dv2, plane_px, focus, n_light;
 };
 
 // Subpath state and path vertices are gathered through queues of arbitrary ids, so they are stored as
@@ -78,6 +82,13 @@ struct __align__(32) VertRec {   // 64 B = 2 sectors
     uint32_t pad[3];
 };
 static_assert(sizeof(VertRec) == 64, "VertRec must be 64 bytes");
+
+// BDPT_WEIGHT_MIS: the two running quantities of the recursive balance-heuristic weights (Georgiev's vertex-connection
+// form: every connection then costs O(1)), per subpath and, frozen at the moment of the hit, per stored vertex.
+struct __align__(16) PathMis { double dVCM, dVC; };
+struct __align__(32) VertMis { double dVCM, dVC, cos_in; uint32_t len, pad; };   // len = surface vertices of the subpath up to this one
+static_assert(sizeof(VertMis) == 32, "VertMis must be 32 bytes");
+constexpr uint32_t kBackFlag = 0x40000000u;   // VertRec.prim: the path arrived on the back side (the facing normal is -n)
 
 struct __align__(32) SlowShadow {   // a parked shadow segment: ray, finished contribution, pixel; 96 B
     double ox, oy, oz, dx, dy, dz, tmax, cx, cy, cz;
@@ -115,6 +126,9 @@ struct WF {              // wavefront workspace, all device pointers
     uint32_t *ncam, *nlight;
     SQ sq[2];                        // shadow queues, ping-pong: the shadow stage of one iteration runs on its own
                                      // stream while the main stream already traces the next
+    int mis;                         // BDPT_WEIGHT_MIS: the three arrays below exist
+    PathMis* pmis;                   // per path id
+    VertMis *cvm, *lvm;              // beside cv / lv
     void* base;
     size_t bytes;
 };
@@ -227,6 +241,7 @@ __device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
 // Fills `ngen` free slots (free_list, or slots 0..ngen-1 on a worker's first iteration) with samples
 // gen_base .. gen_base+ngen-1 of this call; consecutive threads take consecutive samples = neighbouring
 // pixels, so the primary rays of a refill are coherent.
+template <bool MIS>
 __global__ void __launch_bounds__(kGen) k_generate(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ free_list,
                                                    int64_t gen_base, int64_t ngen, int cur, int dn) {
     const int64_t gi = int64_t(blockIdx.x) * kGen + threadIdx.x;
@@ -246,6 +261,12 @@ __global__ void __launch_bounds__(kGen) k_generate(SceneView sc, Frame f, WF w, 
         const D3 d = ps - f.center;
         (void)rc.next();  // ray time (camera.h:210): drawn, never used
         store_path(w.path + b, f.center, d, mk(1.0, 1.0, 1.0), rc.draws, f.depth);
+        if (MIS) {   // pdf of this primary ray per unit solid angle, for an image plane measured in pixels
+            const double c = dot(unit(d), f.fwd);
+            PathMis pm;
+            pm.dVCM = f.n_light / (f.plane_px * f.plane_px / (c * c * c)); pm.dVC = 0.0;
+            w.pmis[b] = pm;
+        }
         w.ncam[b] = 0;
         cam_live = f.depth > 0;
 
@@ -284,6 +305,12 @@ __global__ void __launch_bounds__(kGen) k_generate(SceneView sc, Frame f, WF w, 
                     const D3 T = T0 * emission * (cos_theta / pdf_dir);
                     const D3 o = pos + (0.001 * n);
                     store_path(w.path + lp, o, du, T, rl.draws, f.depth - 1);
+                    if (MIS) {
+                        const double emissionPdfW = pdf * pdf_dir;
+                        PathMis pm;
+                        pm.dVCM = pdf / emissionPdfW; pm.dVC = cos_theta / emissionPdfW;
+                        w.pmis[lp] = pm;
+                    }
                     light_live = true;
                 }
             }
@@ -604,7 +631,7 @@ __global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_trace_w32(SceneView
 }
 
 // hit point and face-forwarded geometric normal (ray.h:21-23, hittable.h:20-26)
-struct Surf { D3 o, d, T, p, n; bool front; uint32_t prim, draws; int32_t remaining; };
+struct Surf { D3 o, d, T, p, n; double t; bool front; uint32_t prim, draws; int32_t remaining; };
 __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint32_t pid) {
     Surf s;
     const double2* q = reinterpret_cast<const double2*>(w.path + pid);
@@ -617,12 +644,27 @@ __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint
     s.draws = uint32_t(q5.x);
     s.remaining = q5.z;
     const double t = q4.y;
+    s.t = t;
     s.p = s.o + t * s.d;
     const TriShade sh = sc.shade[s.prim];
     const D3 n = mk(sh.nx, sh.ny, sh.nz);
     s.front = dot(s.d, n) < 0;
     s.n = s.front ? n : -n;
     return s;
+}
+
+// BDPT_WEIGHT_MIS: the subpath's running weight quantities as they stand ON this vertex (the hit just found):
+// the segment's area conversion and the arrival cosine go in
+struct MisAtHit { double dVCM, dVC, cos_in; uint32_t len; };
+__device__ __forceinline__ MisAtHit mis_arrive(const Frame& f, const WF& w, uint32_t pid, const Surf& s) {
+    MisAtHit m;
+    const PathMis pm = w.pmis[pid];
+    m.cos_in = fabs(dot(s.n, unit(-s.d)));
+    const double dist2 = s.t * s.t * len2(s.d);
+    m.dVCM = pm.dVCM * dist2 / m.cos_in;
+    m.dVC = pm.dVC / m.cos_in;
+    m.len = uint32_t(f.depth - s.remaining + 1);   // camera: remaining starts at depth; light: at depth - 1 behind the emitter
+    return m;
 }
 
 __device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d, D3 T, uint32_t draws, int32_t remaining) {
@@ -633,6 +675,7 @@ __device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d,
 // scatter() is false: the subpath ends here.  Camera subpath: bidirectional_color adds throughput *
 // emission for this non-delta vertex (camera.h:305-309); it never connects (evaluate_bsdf = 0).
 // Light subpath: the vertex is connectable with f_light = emission when hit from the front (camera.h:463).
+template <bool MIS>
 __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, double* film) {
     {
         const bool is_cam = pid < uint32_t(w.B);
@@ -642,8 +685,16 @@ __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f,
         const D3 Le = mk(m.r, m.g, m.b);
         if (s.front && len2(Le) > 0) {   // emitted() is one-sided (material.h:140)
             if (is_cam) {
-                film_add(film, decode_sample(f, w.sample[b]).pix, s.T * Le);
-            } else {
+                double wgt = 1.0;
+                if (MIS) {   // s = 0: weighed against every way the light subpath could have produced this path
+                    const MisAtHit h = mis_arrive(f, w, pid, s);
+                    if (h.len > 1) {
+                        const double pdfA = 1.0 / sc.light_total_area;
+                        wgt = 1.0 / (1.0 + pdfA * h.dVCM + (pdfA * h.cos_in / kPi) * h.dVC);
+                    }
+                }
+                film_add(film, decode_sample(f, w.sample[b]).pix, MIS ? wgt * (s.T * Le) : s.T * Le);
+            } else if (!MIS) {   // MIS: an emitter absorbs; a light-subpath vertex on it connects to nothing
                 const uint32_t slot = w.nlight[b];
                 store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | kLightFlag);
                 w.nlight[b] = slot + 1;
@@ -654,10 +705,14 @@ __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f,
 }
 
 // ------------------------------------------------------------------ K2: lambertian (material.h:42-67)
+template <bool MIS>
 __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
     {
         const Surf s = load_surf(sc, w, pid);
+        MisAtHit mh{0.0, 0.0, 0.0, 0u};
+        if (MIS) mh = mis_arrive(f, w, pid, s);
+        const uint32_t side = (MIS && !s.front) ? kBackFlag : 0u;
         const Mat m = sc.mats[sc.shade[s.prim].mat];
         const D3 albedo = mk(m.r, m.g, m.b);
         const bool is_cam = pid < uint32_t(w.B);
@@ -669,11 +724,13 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
             if (is_cam) {
                 const uint32_t slot = w.ncam[b];
                 const D3 tf = s.T * fr;   // camera.h:471: cam_v.throughput * f_cam
-                store_vertex(w.cv + size_t(b) * size_t(w.depth) + slot, s.p, tf, s.prim);
+                store_vertex(w.cv + size_t(b) * size_t(w.depth) + slot, s.p, tf, s.prim | side);
+                if (MIS) { VertMis vm; vm.dVCM = mh.dVCM; vm.dVC = mh.dVC; vm.cos_in = mh.cos_in; vm.len = mh.len; vm.pad = 0; w.cvm[size_t(b) * size_t(w.depth) + slot] = vm; }
                 w.ncam[b] = slot + 1;
             } else {
                 const uint32_t slot = w.nlight[b];
-                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim);
+                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | side);
+                if (MIS) { VertMis vm; vm.dVCM = mh.dVCM; vm.dVC = mh.dVC; vm.cos_in = mh.cos_in; vm.len = mh.len; vm.pad = 0; w.lvm[size_t(b) * size_t(w.depth) + slot] = vm; }
                 w.nlight[b] = slot + 1;
             }
         }
@@ -690,6 +747,12 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
                 const double spdf = ct < 0 ? 0 : ct / kPi;
                 const D3 T = s.T * albedo * spdf / pdf_value;                  // camera.h:366
                 store_ray(w, pid, s.p, sd, T, rng.draws, remaining);           // camera.h:367: ray(rec.p, dir)
+                if (MIS) {   // the sampled direction's pdf forwards, the arrival direction's pdf backwards
+                    PathMis pm;
+                    pm.dVC = (ct / pdf_value) * (mh.dVC * (mh.cos_in / kPi) + mh.dVCM);
+                    pm.dVCM = 1.0 / pdf_value;
+                    w.pmis[pid] = pm;
+                }
                 live = true;
             }
         }
@@ -700,6 +763,7 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
 // ------------------------------------------------------------------ K2: metal (material.h:69-90)
 // Always a delta vertex, even when fuzzy (material.h:85): never stored, never connected.  The fuzzed
 // direction is not rejected when it points below the surface (material.h:74-82).
+template <bool MIS>
 __device__ __forceinline__ bool shade_metal(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
     {
@@ -715,6 +779,12 @@ __device__ __forceinline__ bool shade_metal(const SceneView& sc, const Frame& f,
             refl = unit(refl) + (m.param * random_unit_vector(rng));
             const D3 T = s.T * mk(m.r, m.g, m.b);                              // camera.h:355
             store_ray(w, pid, s.p, refl, T, rng.draws, remaining);
+            if (MIS) {   // a delta vertex (material.h:85): nothing connects to it
+                const MisAtHit mh = mis_arrive(f, w, pid, s);
+                PathMis pm;
+                pm.dVCM = 0.0; pm.dVC = mh.dVC * fabs(dot(s.n, unit(refl)));
+                w.pmis[pid] = pm;
+            }
             live = true;
         }
     }
@@ -722,6 +792,7 @@ __device__ __forceinline__ bool shade_metal(const SceneView& sc, const Frame& f,
 }
 
 // ------------------------------------------------------------------ K2: dielectric (material.h:92-131)
+template <bool MIS>
 __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
     {
@@ -747,6 +818,12 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
             const D3 dir = refl ? reflect(ud, s.n) : refract(ud, s.n, ri);
             const D3 T = s.T * mk(1.0, 1.0, 1.0);
             store_ray(w, pid, s.p, dir, T, rng.draws, remaining);
+            if (MIS) {
+                const MisAtHit mh = mis_arrive(f, w, pid, s);
+                PathMis pm;
+                pm.dVCM = 0.0; pm.dVC = mh.dVC * fabs(dot(s.n, unit(dir)));
+                w.pmis[pid] = pm;
+            }
             live = true;
         }
     }
@@ -757,6 +834,7 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
 // Thread idx walks the concatenation light | lambertian | metal | dielectric of the queues k_trace_* filled, so
 // a warp straddles at most one class boundary; the survivors' queue append and the retirement of ended
 // subpaths are shared.
+template <bool MIS>
 __global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
     const uint32_t idx = blockIdx.x * kWide + threadIdx.x;
     const uint32_t n_li = w.counters[C_MAT0 + BDPT_MAT_LIGHT], n_la = w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN],
@@ -765,10 +843,10 @@ __global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w,
     bool live = false;
     uint32_t pid = 0;
     if (valid) {
-        if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light(sc, f, w, pid, film); }
-        else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert(sc, f, w, pid); }
-        else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal(sc, f, w, pid); }
-        else { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric(sc, f, w, pid); }
+        if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light<MIS>(sc, f, w, pid, film); }
+        else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert<MIS>(sc, f, w, pid); }
+        else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal<MIS>(sc, f, w, pid); }
+        else { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric<MIS>(sc, f, w, pid); }
     }
     const uint32_t slot = block_append<kWide>(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
@@ -782,7 +860,7 @@ __global__ void __launch_bounds__(256) k_counts(WF w, int dn) {
     if (i < w.counters[C_DONE0 + dn]) { const uint32_t b = w.q_slots[dn][i]; nc = w.ncam[b]; nl = w.nlight[b]; }
     const uint32_t mc = __reduce_max_sync(0xFFFFFFFFu, nc), ml = __reduce_max_sync(0xFFFFFFFFu, nl);
     const uint32_t sc_ = __reduce_add_sync(0xFFFFFFFFu, nc), sl = __reduce_add_sync(0xFFFFFFFFu, nl);
-    const uint32_t pairs = __reduce_add_sync(0xFFFFFFFFu, nc * nl);   // <= 32 * depth^2
+    const uint32_t pairs = __reduce_add_sync(0xFFFFFFFFu, nc * nl + (w.mis ? nl : 0u));   // <= 32 * (depth^2 + depth); MIS: + the splats
     if ((threadIdx.x & 31) == 0) {
         if (pairs) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_PAIRS_LO), (unsigned long long)pairs);
         if (mc) atomicMax(w.counters + C_MAXNC, mc);
@@ -869,6 +947,132 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
     }
 }
 
+// ------------------------------------------------------------------ K3, BDPT_WEIGHT_MIS
+// The same pairing as k_connect, with balance-heuristic weights in O(1) per pair from the vertices' frozen dVCM / dVC
+// (oracle/port.cpp sample_mis states the same arithmetic): light vertex 0 is the emitter point (s = 1), the others are
+// surface vertices (s >= 2); a lambertian surface reflects only to the side the path arrived on; a full path holds at
+// most `depth` surface vertices.  The thread of camera slot 0 also emits the sample's light-tracing SPLATS (t = 1): each
+// light-subpath surface vertex, seen from the pinhole, lands in whatever pixel it projects to.  All of it goes through
+// the shadow queue (the segment stops short of the far surface: SURVEY F4 is a property of the reference's estimator,
+// not of this one) and reaches the film as atomic adds.
+__device__ __forceinline__ void push_segment(const WF& w, const SQ& q, bool emit, D3 from, D3 to_dir_unit, double dist, D3 contrib, uint32_t pix) {
+    const double max_t = dist - 0.001 - 1e-6 * (1.0 + dist);
+    emit = emit && max_t > 0.001;
+    const uint32_t slot = warp_append(q.cnt + SQ_N, emit);
+    if (emit) {
+        if (slot < uint32_t(w.scap)) {
+            const D3 so = from + (0.001 * to_dir_unit);
+            q.ox[slot] = so.x; q.oy[slot] = so.y; q.oz[slot] = so.z;
+            q.dx[slot] = to_dir_unit.x; q.dy[slot] = to_dir_unit.y; q.dz[slot] = to_dir_unit.z;
+            q.tmax[slot] = max_t;
+            q.cx[slot] = contrib.x; q.cy[slot] = contrib.y; q.cz[slot] = contrib.z;
+            q.pix[slot] = pix;
+            q.far[slot] = BDPT_MISS;   // no far-endpoint shortcut: the far surface is outside the segment by construction
+        } else {
+            q.cnt[SQ_OVERFLOW] = 1;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, WF w, SQ q, const uint32_t* __restrict__ done, int64_t nb,
+                                                       int k0, int k1) {
+    const int64_t idx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int64_t total = int64_t(k1 - k0) * nb;
+    const bool valid = idx < total;
+    const int k = valid ? k0 + int(idx / nb) : 0;
+    const int64_t b = valid ? int64_t(done[idx % nb]) : 0;
+    const uint32_t nl = valid ? w.nlight[b] : 0u;
+    const bool have_cam = valid && uint32_t(k) < w.ncam[b];
+    D3 cp = mk(0, 0, 0), ctf = mk(0, 0, 0), cn = mk(0, 0, 0);
+    VertMis cm{0.0, 0.0, 0.0, 0u, 0u};
+    uint32_t pix = 0;
+    if (have_cam) {
+        uint32_t cprim;
+        load_vertex(w.cv + size_t(b) * size_t(w.depth) + size_t(k), cp, ctf, cprim);
+        const TriShade sh = sc.shade[cprim & ~(kBackFlag | kLightFlag)];
+        cn = mk(sh.nx, sh.ny, sh.nz);
+        if (cprim & kBackFlag) cn = -cn;
+        cm = w.cvm[size_t(b) * size_t(w.depth) + size_t(k)];
+        pix = decode_sample(f, w.sample[b]).pix;
+    }
+    const bool splatter = valid && k == 0;   // one thread per sample also walks the light vertices for the t = 1 strategy
+    const uint32_t nl_max = __reduce_max_sync(0xFFFFFFFFu, (have_cam || splatter) ? nl : 0u);
+    const double pdfA = 1.0 / sc.light_total_area;
+    for (uint32_t m = 0; m < nl_max; ++m) {
+        bool emit = false, emit_splat = false;
+        D3 dirc = mk(0, 0, 0), dirs = mk(0, 0, 0), contrib = mk(0, 0, 0), contrib_s = mk(0, 0, 0), lp = mk(0, 0, 0);
+        double distc = 0, dists = 0;
+        uint32_t spix = 0;
+        if (m < nl && (have_cam || splatter)) {
+            D3 lT;
+            uint32_t lprim;
+            load_vertex(w.lv + size_t(b) * size_t(w.depth) + size_t(m), lp, lT, lprim);
+            const TriShade lsh = sc.shade[lprim & ~(kBackFlag | kLightFlag)];
+            D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
+            if (lprim & kBackFlag) ln = -ln;
+            const Mat lm = sc.mats[lsh.mat];
+            const D3 lrgb = mk(lm.r, lm.g, lm.b);
+            if (have_cam) {
+                const D3 dir = lp - cp;
+                const double dist2 = len2(dir);
+                if (dist2 > 0) {
+                    const D3 du = unit(dir);
+                    const double cosCamera = dot(cn, du), cosLight = dot(ln, -du);
+                    if (cosCamera > 0 && cosLight > 0) {
+                        if (lprim & kLightFlag) {   // s = 1: the emitter point (ctf = T * f of the camera vertex)
+                            if (cm.len + 1u <= uint32_t(f.depth)) {
+                                const double directPdfW = pdfA * dist2 / cosLight, emissionPdfW = pdfA * cosLight / kPi;
+                                const double wLight = (cosCamera / kPi) / directPdfW;
+                                const double wCamera = (emissionPdfW * cosCamera / (directPdfW * cosLight)) * (cm.dVCM + cm.dVC * (cm.cos_in / kPi));
+                                const double wgt = 1.0 / (wLight + 1.0 + wCamera);
+                                contrib = (wgt * cosCamera / directPdfW) * (ctf * lrgb);
+                                emit = true;
+                            }
+                        } else {
+                            const VertMis vm = w.lvm[size_t(b) * size_t(w.depth) + size_t(m)];
+                            if (cm.len + vm.len <= uint32_t(f.depth)) {
+                                const double camDirPdfA = (cosCamera / kPi) * cosLight / dist2, lightDirPdfA = (cosLight / kPi) * cosCamera / dist2;
+                                const double wLight = camDirPdfA * (vm.dVCM + vm.dVC * (vm.cos_in / kPi));
+                                const double wCamera = lightDirPdfA * (cm.dVCM + cm.dVC * (cm.cos_in / kPi));
+                                const double wgt = 1.0 / (wLight + 1.0 + wCamera);
+                                contrib = (wgt * cosLight * cosCamera / dist2) * (ctf * lT * (lrgb / kPi));
+                                emit = true;
+                            }
+                        }
+                        dirc = du; distc = len(dir);
+                    }
+                }
+            }
+            if (splatter && !(lprim & kLightFlag)) {   // t = 1
+                const D3 dir = f.center - lp;
+                const double dist2 = len2(dir);
+                if (dist2 > 0) {
+                    const D3 du = unit(dir);
+                    const double cosToCamera = dot(ln, du), cosAtCamera = dot(f.fwd, -du);
+                    if (cosToCamera > 0 && cosAtCamera > 0) {
+                        const D3 P = f.center + (f.focus / cosAtCamera) * (-du);
+                        const D3 rel = P - f.ul;
+                        const double xc = dot(rel, f.du) / f.du2, yc = dot(rel, f.dv) / f.dv2;
+                        if (xc >= 0 && yc >= 0 && xc < f.W && yc < f.H) {
+                            const VertMis vm = w.lvm[size_t(b) * size_t(w.depth) + size_t(m)];
+                            const double ipcd = f.plane_px / cosAtCamera;
+                            const double imageToSurface = (ipcd * ipcd / cosAtCamera) * cosToCamera / dist2;
+                            const double wLight = (imageToSurface / f.n_light) * (vm.dVCM + vm.dVC * (vm.cos_in / kPi));
+                            const double wgt = 1.0 / (wLight + 1.0);
+                            contrib_s = (wgt * imageToSurface / f.n_light) * (lT * (lrgb / kPi));
+                            spix = uint32_t(int(yc)) * uint32_t(f.W) + uint32_t(int(xc));
+                            dirs = du; dists = len(dir);
+                            emit_splat = true;
+                        }
+                    }
+                }
+            }
+        }
+        push_segment(w, q, emit, cp, dirc, distc, contrib, pix);
+        push_segment(w, q, emit_splat, lp, dirs, dists, contrib_s, spix);
+    }
+}
+
 // ------------------------------------------------------------------ K4
 // visible() (camera.h:437: world.hit over [0.001, dist-0.001], inclusive ends — SURVEY F4) and the
 // film accumulation of every unoccluded connection.
@@ -892,7 +1096,8 @@ __global__ void __launch_bounds__(kBlock) k_shadow_pre(SceneView sc, WF w, SQ q,
     if (idx < q.cnt[SQ_N]) {
         const RayD r = load_shadow_ray(q, idx);
         TravStats ts{0, 0};
-        live = !far_endpoint_occludes(sc, r, q.far[idx], STATS ? &ts : nullptr);
+        const uint32_t far = q.far[idx];   // BDPT_MISS (MIS segments): there is no far surface inside the segment to test first
+        live = far == BDPT_MISS || !far_endpoint_occludes(sc, r, far, STATS ? &ts : nullptr);
         if (STATS) add_trav<1, false>(stats, ts);
     }
     const uint32_t slot = warp_append(q.cnt + SQ_LIVE, live);
@@ -1184,6 +1389,7 @@ void carve(WF& w, char* base) {
     w.counters = c.take<uint32_t>(C_COUNT);
     w.cv = c.take<VertRec>(V); w.lv = c.take<VertRec>(V);
     w.ncam = c.take<uint32_t>(B); w.nlight = c.take<uint32_t>(B);
+    if (w.mis) { w.pmis = c.take<PathMis>(P); w.cvm = c.take<VertMis>(V); w.lvm = c.take<VertMis>(V); }
     for (int k = 0; k < 2; ++k) {
         SQ& q = w.sq[k];
         double** sq[] = {&q.ox, &q.oy, &q.oz, &q.dx, &q.dy, &q.dz, &q.tmax, &q.cx, &q.cy, &q.cz};
@@ -1218,6 +1424,11 @@ Frame make_frame(const bdpt_camera& c, int H) {
     f.dv = vv / H;
     const D3 ul = f.center - (c.focus_dist * w) - vu / 2 - vv / 2;
     f.pixel00 = ul + 0.5 * (f.du + f.dv);
+    f.fwd = -w; f.ul = ul;
+    f.du2 = len2(f.du); f.dv2 = len2(f.dv);
+    f.plane_px = c.focus_dist / len(f.du);
+    f.focus = c.focus_dist;
+    f.n_light = double(f.W) * double(f.H);
     return f;
 }
 
@@ -1306,6 +1517,7 @@ struct Job {
     uint32_t limit, limit_shadow;    // work limits of the bulk traversal launches (traverse_walk.cuh); 0 = none
     unsigned resident_blocks;        // blocks of a traversal kernel the device keeps resident (persistent grids)
     int threshold;                   // dynamic fetch: a walk yields when fewer lanes than this are still walking
+    bool mis;                        // BDPT_WEIGHT_MIS
     bool walk32;                     // bulk traversal = the warp-synchronous fp32 walk (traverse_w32.cuh); false: round 1's per-lane walk
     int knobs32;                     // its time-slice / refill / leaf-batch parameters (unpack_knobs)
     unsigned resident32;             // blocks of k_trace_w32 / k_shadow_w32 the device keeps resident
@@ -1376,7 +1588,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT0 + ex, 0, sizeof(uint32_t), st));
         if (ngen > 0) {
             tm.begin(KT_GENERATE, st);
-            k_generate<<<grid_for(ngen, kGen), kGen, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
+            if (J.mis) k_generate<true><<<grid_for(ngen, kGen), kGen, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
+            else k_generate<false><<<grid_for(ngen, kGen), kGen, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
             tm.end(KT_GENERATE, st);
             wk.launches += 1;
             wk.samples += uint64_t(ngen);
@@ -1399,7 +1612,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         tm.end(KT_TRACE, st);
         tm.begin(KT_SHADE, st);
         const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kWide);   // the lagged rays of the front blocks are shaded too
-        k_shade<<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film);
+        if (J.mis) k_shade<true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film);
+        else k_shade<false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film);
         k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
         tm.end(KT_SHADE, st);
         wk.launches += 3;
@@ -1411,20 +1625,22 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         ex ^= 1;
         n_active = hc[C_ACTIVE0 + nxt];
         const int64_t n_done = hc[C_DONE0 + dn];
-        const int max_nc = int(hc[C_MAXNC]), max_nl = int(hc[C_MAXNL]);
+        const int max_nl = int(hc[C_MAXNL]);
+        const int max_nc = J.mis ? std::max(1, int(hc[C_MAXNC])) : int(hc[C_MAXNC]);   // MIS: camera slot 0's thread also emits the splats
         wk.cam_verts += hc[C_SUMNC]; wk.light_verts += hc[C_SUMNL];
         // connections of the samples that finished in this iteration
         if (n_done > 0 && max_nc > 0 && max_nl > 0) {
             // every (camera vertex, light vertex) pair is at most one shadow ray: if they all fit, one round
             const uint64_t pairs = uint64_t(hc[C_PAIRS_LO]) | (uint64_t(hc[C_PAIRS_HI]) << 32);
-            const int slots_per_round = pairs <= uint64_t(wf.scap) ? max_nc : int(std::max<int64_t>(1, wf.scap / (n_done * int64_t(max_nl))));
+            const int slots_per_round = pairs <= uint64_t(wf.scap) ? max_nc : int(std::max<int64_t>(1, wf.scap / (n_done * int64_t(max_nl)) - (J.mis ? 1 : 0)));
             for (int k0 = 0; k0 < max_nc; k0 += slots_per_round) {
                 const int k1 = std::min(max_nc, k0 + slots_per_round);
                 const SQ& q = wf.sq[sb];
                 WK_CUDA(cudaStreamWaitEvent(st, wk.ev_shadow[sb], 0));   // the shadow stage that last read this queue
                 WK_CUDA(cudaMemsetAsync(q.cnt, 0, SQ_COUNT * sizeof(uint32_t), st));
                 tm.begin(KT_CONNECT, st);
-                k_connect<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
+                if (J.mis) k_connect_mis<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
+                else k_connect<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
                 tm.end(KT_CONNECT, st);
                 wk.launches += 1;
                 // one round: size the shadow launch by the pair count (an upper bound) and skip the read-back
@@ -1474,6 +1690,8 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     }
     if (cam->defocus_angle > 0) { ctx->err = "defocus blur is off in the reference's loader (scene_loader.h:463)"; return BDPT_ERR_ARG; }
     if (o.bvh != BDPT_BVH_REFERENCE && o.bvh != BDPT_BVH_FAST) { ctx->err = "unknown bvh flavour"; return BDPT_ERR_ARG; }
+    if (o.weighting != BDPT_WEIGHT_REF_SUM && o.weighting != BDPT_WEIGHT_MIS) { ctx->err = "unknown weighting"; return BDPT_ERR_ARG; }
+    const bool mis = o.weighting == BDPT_WEIGHT_MIS;
     int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
     H = H < 1 ? 1 : H;
     if (!ctx->film || ctx->film_w != cam->image_width || ctx->film_h != H) {
@@ -1509,8 +1727,8 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
         // the default takes at most half of the free device memory: a slot costs ~5 KB at depth 16 and ~25 KB at
         // depth 80 (vertex pools and shadow queues grow with the depth)
         WF probe{};
-        probe.B = 65536; probe.depth = f.depth;
-        probe.scap = std::max<int64_t>(probe.B * 8, int64_t(f.depth) * probe.B);
+        probe.B = 65536; probe.depth = f.depth; probe.mis = mis ? 1 : 0;
+        probe.scap = std::max<int64_t>(probe.B * 8, int64_t(f.depth) * probe.B * (mis ? 2 : 1));
         probe.sscap = std::max<int64_t>(4096, probe.scap / 8);
         carve(probe, nullptr);
         const double per_slot = double(probe.bytes) / double(probe.B);
@@ -1535,11 +1753,11 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             for (auto& e : wk.ev_shadow) BDPT_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             BDPT_CUDA(ctx, cudaMallocHost(&wk.hc, (C_COUNT + SQ_COUNT) * sizeof(uint32_t)));
         }
-        if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth) {
+        if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth || wk.wf.mis != (mis ? 1 : 0)) {
             if (wk.wf.base) { BDPT_CUDA(ctx, cudaStreamSynchronize(wk.stream)); cudaFree(wk.wf.base); }
             std::memset(&wk.wf, 0, sizeof(WF));
-            wk.wf.B = B; wk.wf.depth = f.depth;
-            wk.wf.scap = std::max<int64_t>(B * 8, int64_t(f.depth) * B);   // >= one camera slot against every light vertex
+            wk.wf.B = B; wk.wf.depth = f.depth; wk.wf.mis = mis ? 1 : 0;
+            wk.wf.scap = std::max<int64_t>(B * 8, int64_t(f.depth) * B * (mis ? 2 : 1));   // >= one camera slot against every light vertex (MIS: + the splats)
             wk.wf.scap = std::min<int64_t>(wk.wf.scap, int64_t(0xFFFFFFF0u));
             wk.wf.sscap = std::max<int64_t>(4096, wk.wf.scap / 8);
             carve(wk.wf, nullptr);
@@ -1557,6 +1775,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 
     Job J;
     J.sc = ctx->view; J.f = f; J.o = o; J.total = total; J.film = ctx->film; J.d_stats = ctx->d_stats;
+    J.mis = mis;
     // traversal stack: one StackEntry per tree level per thread (deferred children only)
     const size_t levels = size_t(std::max(ctx->host.fast_depth, ctx->host.ref_depth)) + 2;
     if (ctx->host.fast_depth + 2 > uint32_t(kStackLevels) || ctx->host.ref_depth + 2 > uint32_t(2 * kStackLevels)) {

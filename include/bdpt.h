@@ -118,7 +118,17 @@ typedef struct {
     int64_t  batch_samples;  /* wavefront size; <=0 picks a default */
     int32_t  flags;          /* BDPT_RENDER_* */
     int32_t  streams;        /* wavefronts kept in flight on separate CUDA streams; <=0 picks a default (4) */
+    int32_t  weighting;      /* BDPT_WEIGHT_*: how the sampling strategies of a path are combined */
+    int32_t  pad;
 } bdpt_render_opts;
+/* BDPT_WEIGHT_REF_SUM (default, the parity gate): the reference's estimator, bidirectional_color camera.h:294-323 --
+ *   emission at every camera vertex plus every camera x light vertex connection, all with weight 1.
+ * BDPT_WEIGHT_MIS: the same two random walks per sample combined with balance-heuristic weights over all
+ *   strategies -- camera path hits a light (s = 0), connection to the emitter point (s = 1), vertex connections
+ *   (s >= 2) and light tracing (t = 1), whose contributions are SPLATS: atomic adds into whatever pixel the light
+ *   vertex projects to.  Unbiased: its expectation is that of the reference's own path_trace_color
+ *   (camera.h:255-292), at most max_depth surface vertices per path; not a reference behaviour. */
+enum { BDPT_WEIGHT_REF_SUM = 0, BDPT_WEIGHT_MIS = 1 };
 enum { BDPT_RENDER_STATS = 1,  /* count node visits / triangle tests of the traversal kernels (slower) */
        BDPT_RENDER_SERIAL = 2  /* keep every kernel of a wavefront on ONE stream (the shadow stage normally overlaps the
                                   next iteration on a side stream): per-kernel event times are then each kernel's own */ };

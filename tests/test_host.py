@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol(bdpt):
 def test_struct_layouts_match_header(bdpt):
     assert ctypes.sizeof(bdpt.Material) == 40
     assert ctypes.sizeof(bdpt.Camera) == 144
-    assert ctypes.sizeof(bdpt.RenderOpts) == 48
+    assert ctypes.sizeof(bdpt.RenderOpts) == 56
     assert ctypes.sizeof(bdpt.Stats) == 160   # 16 + the four remaining BvhStats counters
     assert bdpt.RAY_DTYPE.itemsize == 64 and bdpt.HIT_DTYPE.itemsize == 32
 

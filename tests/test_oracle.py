@@ -65,3 +65,23 @@ def test_philox_mode_statistically_equals_mt_mode(scenes):
     from oracle.oracle import RNG_PHILOX
     b = o.render(c, rng_mode=RNG_PHILOX, seed=5, nthreads=4, height=12).mean()
     assert abs(a - b) / a < 0.06
+
+
+def test_mis_estimator_agrees_with_the_reference_path_tracer():
+    """the MIS-weighted estimator (port; the CUDA path equals it sample for sample, tests/test_mis_gpu.py)
+    is unbiased: its image mean equals that of the reference's OWN path tracer, camera::path_trace_color
+    (camera.h:255-292) run through oracle/_ref, within Monte-Carlo error -- while the reference's unweighted sum
+    (camera.h:294-323), which counts a path once per strategy, is far off."""
+    from oracle.oracle import WEIGHT_MIS
+    if not available("ref"):
+        pytest.skip("oracle/_ref not built")
+    from tools import testscenes as ts
+    for scene, tol in ((ts.cornell(False), 0.03), (ts.unit_room(seed=1, n_blobs=6), 0.05)):
+        v, m, mats, cam = scene
+        W = H = 16
+        c = make_camera(W, H, 400, 6, **cam)
+        mis = Oracle("port").load(v, m, mats).render(c, rng_mode=RNG_PHILOX, seed=3, nthreads=8, height=H, weighting=WEIGHT_MIS).mean()
+        ref_sum = Oracle("port").load(v, m, mats).render(c, rng_mode=RNG_PHILOX, seed=3, nthreads=8, height=H).mean()
+        pt = Oracle("ref").load(v, m, mats).render_pt(c, seed=5, height=H).mean()
+        assert abs(mis / pt - 1.0) < tol, (mis, pt)
+        assert abs(ref_sum / pt - 1.0) > 0.15, (ref_sum, pt)
