@@ -72,7 +72,7 @@ def test_mis_estimator_agrees_with_the_reference_path_tracer():
     is unbiased: its image mean equals that of the reference's OWN path tracer, camera::path_trace_color
     (camera.h:255-292) run through oracle/_ref, within Monte-Carlo error -- while the reference's unweighted sum
     (camera.h:294-323), which counts a path once per strategy, is far off."""
-    from oracle.oracle import WEIGHT_MIS
+    from oracle.oracle import WEIGHT_MIS, RNG_PHILOX, available, Oracle, make_camera
     if not available("ref"):
         pytest.skip("oracle/_ref not built")
     from tools import testscenes as ts
