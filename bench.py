@@ -143,41 +143,60 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_reference(spp, steps, warmup, procs=None):
-    """The reference CPU renderer on this box's host cores: `procs` independent single-thread processes,
-    each rendering one full-width row of the workload per step at `spp` samples per pixel."""
+def dump_soup():
+    """The workload's triangle soup as an .npz, written by a child process (tools/dump_soup.py): the reference arm's
+    own processes then never map libbdpt.so."""
     ensure_scenes()
+    out = os.path.join(ROOT, "gpurun_out" if os.path.isdir(os.path.join(ROOT, "gpurun_out")) else ".", "_soup_coffee_machine.npz")
+    out = os.path.abspath(out)
+    if not os.path.exists(out) or os.path.getmtime(out) < os.path.getmtime(SCENE):
+        subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "dump_soup.py"), SCENE, out], stdout=subprocess.DEVNULL)
+    return out
+
+
+def cpu_reference(spp, steps, warmup, procs=None, rows=2):
+    """The reference CPU renderer on this box's host cores: `procs` independent single-thread processes, each
+    rendering `rows` full-width rows of the workload per step at `spp` samples per pixel; every worker's rows are spread
+    over the image height and interleaved with the others', so all of them see the same mix of cheap and dear rows.
+    The rate is the SUM of the processes' own rates (samples_i / seconds_i): a core that finishes early is not
+    counted as idle."""
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-s"], stdout=subprocess.DEVNULL)
+    soup = dump_soup()
     procs = procs or host_cores()
-    cmd = [sys.executable, os.path.join(ROOT, "tools", "cpu_ref_worker.py"), SCENE, str(WIDTH), str(HEIGHT), str(spp), str(DEPTH)]
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "cpu_ref_worker.py"), soup, str(WIDTH), str(HEIGHT), str(spp), str(DEPTH)]
     env = dict(os.environ, OMP_NUM_THREADS="1")
-    ps = [subprocess.Popen(cmd + [str(int((p + 0.5) * HEIGHT / procs)), str(steps), str(warmup)], stdout=subprocess.PIPE,
-                           stderr=subprocess.DEVNULL, text=True, env=env) for p in range(procs)]
-    outs = []
-    for p in ps:
-        out, _ = p.communicate()
+    ps = [subprocess.Popen(cmd + [str(p), str(procs), str(steps), str(warmup), "1", str(rows)], stdout=subprocess.PIPE,
+                           stderr=subprocess.PIPE, text=True, env=env) for p in range(procs)]
+    outs, failed = [], []
+    for k, p in enumerate(ps):
+        out, err = p.communicate()
         lines = [l for l in out.splitlines() if l.startswith("{")]
         if p.returncode == 0 and lines:
             outs.append(json.loads(lines[-1]))
-    if not outs:
-        raise RuntimeError("CPU reference workers failed")
+        else:
+            failed.append("worker %d rc=%s: %s" % (k, p.returncode, err.strip().splitlines()[-1] if err.strip() else ""))
+    if failed:
+        raise RuntimeError("CPU reference workers failed: " + "; ".join(failed[:3]))
     samples = sum(o["samples_per_step"] * len(o["step_s"]) for o in outs)
+    rate = sum(o["samples_per_step"] * len(o["step_s"]) / sum(o["step_s"]) for o in outs)      # samples/s, summed over the cores
     wall = max(sum(o["step_s"]) for o in outs)
     rays = sum(o["rays"] for o in outs)
     all_samples = sum(o["samples_per_step"] * o["all_steps"] for o in outs)
-    return {"value": samples / wall / 1e6, "unit": "Msamples/s", "cores": len(outs), "kind": outs[0]["kind"],
-            "sample": "%d independent single-thread processes x %d step(s) x 1 row of %dx%d at %d spp, depth %d "
-                      "(%d samples timed); reference headers compiled -O2, BVH build excluded"
-                      % (len(outs), steps, WIDTH, HEIGHT, spp, DEPTH, samples),
+    return {"value": rate / 1e6, "unit": "Msamples/s", "cores": len(outs), "kind": outs[0]["kind"],
+            "sample": "%d independent single-thread processes x %d step(s) x %d interleaved row(s) of %dx%d at %d spp (%dx%d strata), depth %d "
+                      "(%d samples timed; per-sample cost does not depend on the stratum count); sum of the processes' rates; "
+                      "reference headers compiled -O2, BVH build excluded"
+                      % (len(outs), steps, rows, WIDTH, HEIGHT, spp, int(spp ** 0.5), int(spp ** 0.5), DEPTH, samples),
             "ms_per_step": 1e3 * wall / max(1, steps), "closest_rays_per_sample": rays / max(1, all_samples),
             "node_visits_per_ray": sum(o["node_visits"] for o in outs) / max(1, rays),
-            "tri_tests_per_ray": sum(o["tri_tests"] for o in outs) / max(1, rays)}
+            "tri_tests_per_ray": sum(o["tri_tests"] for o in outs) / max(1, rays),
+            "slowest_over_fastest_worker": max(sum(o["step_s"]) for o in outs) / max(1e-9, min(sum(o["step_s"]) for o in outs))}
 
 
 def cpu_reference_variant(spp, threads, rows):
     """One process of the reference through tools/cpu_ref_worker.py: threads > 1 = its own thread-pool shape."""
-    cmd = [sys.executable, os.path.join(ROOT, "tools", "cpu_ref_worker.py"), SCENE, str(WIDTH), str(HEIGHT), str(spp), str(DEPTH),
-           str(HEIGHT // 2), "1", "0", str(threads), str(rows)]
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "cpu_ref_worker.py"), dump_soup(), str(WIDTH), str(HEIGHT), str(spp), str(DEPTH),
+           "0", "1", "1", "0", str(threads), str(rows)]
     try:
         out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, OMP_NUM_THREADS="1")).stdout
         o = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
@@ -191,22 +210,22 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    # one row at 256 spp costs ~10-20 s per process; shrink the per-step sample when many steps are asked for
-    n_steps = args.steps + args.warmup
-    spp = 256 if n_steps <= 2 else (64 if n_steps <= 6 else 16)   # ~75 s / ~19 s / ~5 s per step on 8 cores
-    r = cpu_reference(spp, args.steps, args.warmup)
+    # a row at 16 spp (4x4 strata) costs ~1 s per process; two interleaved rows per step keep a step bounded however many
+    # steps are asked for.  The workload's 256 spp differ only in the number of strata: the cost per SAMPLE is the same.
+    r = cpu_reference(16, args.steps, args.warmup, rows=2)
+    cfg = dict(workload_config(), reference_sample="each step: 2 interleaved rows per process at 16 spp (4x4 strata of the workload's 16x16)")
     line = {"impl": "reference", "metric": "BDPT Msamples/s", "value": r["value"], "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(),
+            "config": cfg,
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "reference_counters": {k: r[k] for k in ("closest_rays_per_sample", "node_visits_per_ray", "tri_tests_per_ray")}}
+            "reference_counters": {k: r[k] for k in ("closest_rays_per_sample", "node_visits_per_ray", "tri_tests_per_ray", "slowest_over_fastest_worker")}}
     # the other two ways of running the reference on these cores, reported beside the headline (iii)
     if not args.skip_cpu:
         cores = host_cores()
         line["variants"] = {
-            "independent_processes": "the line's value (one single-thread process per core, disjoint rows)",
+            "independent_processes": "the line's value (one single-thread process per core, interleaved rows)",
             "single_thread": cpu_reference_variant(16, 1, 4),
             "as_shipped_thread_pool": dict(cpu_reference_variant(16, cores + 1, 8),
                                            note="hardware_concurrency()+1 threads sharing one unlocked mt19937 and the stats atomics "
@@ -271,12 +290,12 @@ def run_ours(args):
     # ---------------- device-resident measurement
     ctx.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
     ctx.film_clear(WIDTH, HEIGHT)
-    fptr, fn = ctx.film_device_ptr()
-    film_t = torch.as_tensor(CudaArray(fptr, fn), device=torch.device("cuda", local))
+    if dist:
+        pkg.join_comm(ctx, dist)     # the film reduce is the library's own (bdpt_film_reduce_comm over NCCL); torch only carries the id
     for s in range(Wm):
         ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
     if dist:
-        dist.reduce(film_t, dst=0)   # warm NCCL up too
+        ctx.film_reduce(0)           # warm NCCL up too
     ctx.film_clear(WIDTH, HEIGHT)
     ctx.stats_reset()
     sampler = ClockSampler(local, enabled=(rank == 0))
@@ -287,14 +306,9 @@ def run_ours(args):
     for s in range(K):
         ctx.render(cam, seed=args.seed, bvh=bvh, strata=strata_of(Wm + s), clear=False, height=HEIGHT, batch_samples=args.batch, streams=args.streams)
         dev_ms += ctx.last_device_ms()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     red_ms = 0.0
     if dist:
-        ev0.record()
-        dist.reduce(film_t, dst=0)   # the one film reduce per frame
-        ev1.record()
-        torch.cuda.synchronize()
-        red_ms = ev0.elapsed_time(ev1)
+        red_ms = ctx.film_reduce(0)  # the one film reduce per frame: device time of ncclReduce on the library's stream
     sync_all()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop()
@@ -313,11 +327,29 @@ def run_ours(args):
     # context) otherwise decides a 250 ms measurement.
     film_buf = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64, pin_memory=True).numpy()   # the caller's frame buffer, pinned
 
+    shm = "/dev/shm/bdpt_bench_%s.bdptimg" % os.environ.get("MASTER_PORT", "0")
+
+    def upload_cold(c):
+        """From the flattened soup in host buffers.  One rank: bdpt_scene_upload (flatten + both tree builds + H2D).
+        Several ranks: rank 0 builds the scene image ONCE (the same flatten + tree builds) into shared memory and every
+        rank uploads that block -- what `bdpt --gpus N` does inside one process (host/camera.cpp); N ranks building
+        the same two trees side by side on the same host cores cost the 8-GPU e2e 12 % in round 1."""
+        if not dist:
+            return c.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
+        if rank == 0:
+            with pkg.SceneImage.build(sf.verts, sf.mat_id, sf.materials) as img:
+                img.save(shm)
+        dist.barrier()
+        with pkg.SceneImage.map(shm) as img:
+            c.upload_image(img)
+
     def e2e_passes(upload):
         passes = []
         film_host = None
         for _ in range(int(os.environ.get("BENCH_E2E_PASSES", "3"))):
             ctx2 = pkg.Context(local)
+            if dist:
+                pkg.join_comm(ctx2, dist)
             sync_all()
             t0 = time.perf_counter()
             upload(ctx2)
@@ -330,8 +362,7 @@ def run_ours(args):
                 per_call.append(round((time.perf_counter() - tc) * 1e3, 2))
             t_rd = time.perf_counter()
             if dist:
-                p2, n2_ = ctx2.film_device_ptr()
-                dist.reduce(torch.as_tensor(CudaArray(p2, n2_), device=torch.device("cuda", local)), dst=0)
+                ctx2.film_reduce(0)
             film_host = ctx2.film(out=film_buf)
             sync_all()
             t_end = time.perf_counter()
@@ -343,7 +374,9 @@ def run_ours(args):
             ctx2.close()
         return passes, sorted(passes, key=lambda p: p["seconds_max_over_ranks"])[len(passes) // 2], film_host
 
-    passes, e2e_parts, film_host = e2e_passes(lambda c: c.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree))
+    passes, e2e_parts, film_host = e2e_passes(upload_cold)
+    if dist and rank == 0 and os.path.exists(shm):
+        os.unlink(shm)
     e2e_value = samples / e2e_parts["seconds_max_over_ranks"] / 1e6
     film_checksum = float(np.nan_to_num(film_host).sum())
 
@@ -364,9 +397,14 @@ def run_ours(args):
     h2d = sf.verts.nbytes + sf.mat_id.nbytes
     d2h = film_host.nbytes
 
+    frame = None
+    if not args.skip_frame:
+        frame = frame_leg(args, pkg, ctx, sf, bvh, dist, rank, world, sync_all)
     extra = {}
     if rank == 0:
         extra = rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K)
+        if frame:
+            extra["config4_frame"] = frame
     ctx.close()
     if rank == 0:
         line = {"metric": "BDPT Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": Wm,
@@ -375,8 +413,9 @@ def run_ours(args):
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
                         "rank0_ms": e2e_parts, "all_passes_msamples_per_s": [samples / p["seconds_max_over_ranks"] / 1e6 for p in passes],
                         "all_passes_rank0_ms": passes,
-                        "note": "scene upload from host buffers (host BVH build + H2D) + K steps + film read-back into a pinned host frame buffer; "
-                                "median of three passes, each on a fresh context"},
+                        "note": "scene upload from host buffers (flatten + both host BVH builds + H2D; several ranks: rank 0 builds one "
+                                "scene image in shared memory, all upload it) + K steps + NCCL film reduce + film read-back into a pinned host "
+                                "frame buffer; median of three passes, each on a fresh context"},
                 "gpu_launches": st["kernel_launches"], "clocks": clocks, "wall_ms_per_step": wall_ms / K,
                 "film_reduce_ms": red_ms,
                 "mrays_per_s": (st["rays_closest"] + st["rays_shadow"]) * world / (total_ms * 1e3),
@@ -398,10 +437,52 @@ def run_ours(args):
     return 0
 
 
+FRAME_W, FRAME_H, FRAME_SPP = 3840, 2160, 1024
+
+
+def frame_leg(args, pkg, ctx, sf, bvh, dist, rank, world, sync_all):
+    """BASELINE.json config 4: ONE whole coffee_machine frame at 3840x2160, 1024 spp (32x32 strata), depth 16, its strata
+    sharded over the ranks (rank g renders strata g, g+N, ...), the NCCL film reduce inside the timed region, then the
+    read-back of the summed film on rank 0.  Total work is fixed -> the per-N values of this leg are STRONG scaling."""
+    import torch
+    cam4 = sf.camera_with(FRAME_W, FRAME_H, FRAME_SPP, DEPTH)
+    n2 = int(FRAME_SPP ** 0.5) ** 2
+    ctx.render(cam4, seed=args.seed, bvh=bvh, strata=(rank, min(n2, world), world), clear=True, height=FRAME_H)   # warm-up: one stratum (sizes the film)
+    if dist:
+        ctx.film_reduce(0)
+    host = torch.empty((FRAME_H, FRAME_W, 3), dtype=torch.float64, pin_memory=True).numpy() if rank == 0 else None
+    sync_all()
+    t0 = time.perf_counter()
+    ctx.render(cam4, seed=args.seed, bvh=bvh, strata=pkg.shard_strata(rank, world, FRAME_SPP), clear=True, height=FRAME_H)
+    render_ms = ctx.last_device_ms()
+    red_ms = ctx.film_reduce(0) if dist else 0.0
+    t_dev = time.perf_counter()
+    if rank == 0:
+        ctx.film(out=host)
+    sync_all()
+    t1 = time.perf_counter()
+    st = ctx.stats()
+    v = torch.tensor([render_ms + red_ms, t_dev - t0, t1 - t0, render_ms], dtype=torch.float64, device="cuda")
+    lo = v.clone()
+    if dist:
+        dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    samples = FRAME_W * FRAME_H * n2
+    return {"workload": "scenes/coffee_machine.yaml %dx%d, %d spp, max depth %d: one whole frame, strata sharded over %d GPU(s), film reduce inside"
+                        % (FRAME_W, FRAME_H, FRAME_SPP, DEPTH, world),
+            "scaling": "strong", "samples": samples, "frame_s": float(v[0]) / 1e3, "msamples_per_s": samples / (float(v[0]) * 1e3),
+            "film_reduce_ms": red_ms, "film_bytes": FRAME_W * FRAME_H * 24,
+            "render_ms_slowest_rank": float(v[3]), "render_ms_fastest_rank": float(lo[3]),
+            "wall_s_render_and_reduce": float(v[1]), "e2e_frame_s_with_readback": float(v[2]),
+            "e2e_msamples_per_s": samples / float(v[2]) / 1e6,
+            "film_checksum": float(np.nan_to_num(host).sum()) if rank == 0 else None,
+            "timing": "device: CUDA events around the render + the reduce, max over ranks; e2e: wall clock, barrier on both sides"}
+
+
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel`, from the committed ncu --set full
     summary of this round (profiles/): a number measured under the profiler, quoted, not re-measured here."""
-    path = os.path.join(ROOT, "profiles", "r1_ncu_full_%s.csv" % kernel)
+    path = os.path.join(ROOT, "profiles", "r2_ncu_full_%s.csv" % kernel)   # this round's capture of the build being benchmarked
     try:
         vals = {}
         for line in open(path):
@@ -409,7 +490,7 @@ def ncu_traffic(kernel):
             if len(p) >= 3 and p[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                 vals[p[0]] = float(p[1]) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[p[2]]
         if len(vals) == 2:
-            return sum(vals.values()), "bytes of the captured launch in profiles/%s (the first, largest launch of a step)" % os.path.basename(path)
+            return sum(vals.values()), "bytes of the launch captured in profiles/%s" % os.path.basename(path)
     except Exception:
         pass
     return None, "no ncu capture committed for this kernel"
@@ -447,9 +528,18 @@ def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
     fast = bvh == pkg.BVH_FAST
     kname = ("k_trace_fast" if fast else "k_trace_paths") if dom == "trace" else ("k_shadow_fast" if fast else "k_shadow")
     traffic, traffic_note = ncu_traffic(kname)
+    try:   # the named scenes are L2-resident by design: the L2 read peak (48 MiB buffer, 16-byte loads) beside the HBM figure
+        l2_peak = ctx.bench_read(48 << 20, reps=40)
+        hbm_read = ctx.bench_read(4 << 30, reps=4)
+    except Exception:
+        l2_peak, hbm_read = None, None
     out["roofline"] = {"bound": "hbm", "kernel": kname, "achieved": achieved,
                        "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
                        "peak_source": peak_src,
+                       "l2_peak": l2_peak, "l2_frac": (achieved / l2_peak) if l2_peak else None, "hbm_read_probe": hbm_read,
+                       "l2_note": "l2_peak: bdpt_bench_read over a 48 MiB resident buffer, measured in this run; the algorithmic bytes of "
+                                  "this scene are served by L1/L2 (the 60 MB scene is L2-resident), so l2_frac is the bound that applies and "
+                                  "frac (of HBM) a figure of merit; hbm_read_probe: the same probe over 4 GiB",
                        "avg_launch_ms": ms_dom / max(1, launches_dom), "launches": launches_dom,
                        "algorithmic_bytes_per_ray": per[dom]["bytes_per_ray"],
                        "algorithmic_bytes_per_launch": rays_dom * per[dom]["bytes_per_ray"] / max(1, launches_dom),
@@ -462,12 +552,99 @@ def rank0_extras(args, pkg, ctx, sf, cam, bvh, st, kt, K):
     out["traversal_work"] = per
     if not args.skip_micro:
         out["bvh_microbench"] = bvh_microbench(args, pkg, bvh)
+    if not args.skip_configs:
+        try:
+            out.update(config_legs(args, pkg, bvh, peak))
+        except Exception as e:   # the headline stands on its own
+            out["config_legs_error"] = str(e)[:300]
     if not args.skip_cpu:
         try:
             r = cpu_reference(64, 1, 0)
             out["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         except Exception as e:  # the GPU numbers stand on their own
             out["cpu_baseline"] = {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": "failed: %s" % e}
+    return out
+
+
+def config_legs(args, pkg, bvh, peak):
+    """BASELINE.json configs 1 and 5 as legs of the line (rank 0, after the headline measurement).
+    config 1: glass-of-water 512x512, 16 spp, the YAML's own depth (80): one whole frame, device time and end to end.
+    config 5: the 10,000,008-triangle sphere grid, 1920x1080, 64 spp, depth 32 -- the one config whose trees do NOT fit
+    the L2, i.e. where the HBM roofline really binds: steps of 2 strata, the trace kernel's algorithmic bytes / time."""
+    import torch
+    from tools import testscenes as ts
+    out = {}
+    dev = int(os.environ.get("LOCAL_RANK", "0"))
+    # ---- config 1
+    sf = pkg.SceneFile(MICRO_SCENE)
+    cam1 = sf.camera_with(512, 512, 16, None)
+    host = torch.empty((512, 512, 3), dtype=torch.float64, pin_memory=True).numpy()
+    with pkg.Context(dev) as c:
+        c.upload(sf.verts, sf.mat_id, sf.materials)
+        c.render(cam1, seed=args.seed, bvh=bvh, height=512)            # warm-up frame
+        c.stats_reset()
+        ms = []
+        for k in range(3):
+            c.render(cam1, seed=args.seed + k, bvh=bvh, height=512)
+            ms.append(c.last_device_ms())
+        st = c.stats()
+    t0 = time.perf_counter()
+    with pkg.Context(dev) as c:
+        c.upload(sf.verts, sf.mat_id, sf.materials)
+        c.render(cam1, seed=args.seed, bvh=bvh, height=512)
+        c.film(out=host)
+    e2e_s = time.perf_counter() - t0
+    n1 = 512 * 512 * 16
+    out["config1_glass_of_water"] = {
+        "workload": "scenes/glass-of-water.yaml 512x512, 16 spp (4x4 strata), max depth %d (the YAML's), stand-in geometry, %d triangles" % (cam1.max_depth, len(sf.verts)),
+        "msamples_per_s": n1 / min(ms) / 1e3, "frame_ms": min(ms), "frame_ms_all": ms,
+        "e2e_msamples_per_s": n1 / e2e_s / 1e6, "e2e_frame_s": e2e_s,
+        "e2e_note": "fresh context: scene upload from host buffers (both BVH builds) + one frame + film read-back; dominated by the ~0.1 s of "
+                    "context and workspace set-up at this frame size",
+        "rays_per_sample": {"closest": st["rays_closest"] / max(1, st["samples"]), "shadow": st["rays_shadow"] / max(1, st["samples"])},
+        "film_checksum": float(np.nan_to_num(host).sum())}
+    # ---- config 5
+    v, m, mats, camkw = ts.sphere_grid(50)
+    W5, H5, SPP5, D5, S5 = 1920, 1080, 64, 32, 2
+    cam5 = pkg.make_camera(W5, H5, SPP5, D5, **camkw)
+    with pkg.Context(dev) as c:
+        t0 = time.perf_counter()
+        c.upload(v, m, mats, gpu_tree=args.gpu_tree)
+        up_s = time.perf_counter() - t0
+        c.film_clear(W5, H5)
+        for s_ in range(2):
+            c.render(cam5, seed=1, bvh=bvh, strata=(s_ * S5, (s_ + 1) * S5, 1), clear=False, height=H5)
+        c.stats_reset()
+        ms, steps = 0.0, 4
+        for s_ in range(steps):
+            c.render(cam5, seed=1, bvh=bvh, strata=((2 + s_) * S5, (3 + s_) * S5, 1), clear=False, height=H5)
+            ms += c.last_device_ms()
+        st = c.stats()
+        c.stats_reset()
+        c.render(cam5, seed=1, bvh=bvh, strata=(0, 1, 1), clear=True, height=H5, stats=True)
+        s2 = c.stats()
+        c.stats_reset()
+        c.render(cam5, seed=1, bvh=bvh, strata=(20, 22, 1), clear=True, height=H5, streams=1, serial=True)
+        st1, kt = c.stats(), c.kernel_times()
+        nodes, fastn = c.bvh_info(pkg.BVH_REFERENCE), c.bvh_info(pkg.BVH_FAST)
+    rays = max(1, s2["rays_closest"])
+    bpr = 48.0 + 32.0 * s2["nodes_closest"] / rays + 48.0 * s2["tris_closest"] / rays
+    tms, tl = kt["trace"]
+    ach = st1["rays_closest"] * bpr / (tms * 1e-3) / 1e9 if tms > 0 else 0.0
+    samples = W5 * H5 * S5 * steps
+    out["config5_ten_million_triangles"] = {
+        "workload": "synthetic sphere grid 50x50, %d triangles, %dx%d, %d spp, max depth %d, mixed dielectric / fuzzy metal / lambertian; step = %d strata"
+                    % (len(v), W5, H5, SPP5, D5, S5),
+        "msamples_per_s": samples / ms / 1e3, "ms_per_step": ms / steps,
+        "mrays_per_s": (st["rays_closest"] + st["rays_shadow"]) / ms / 1e3,
+        "rays_per_sample": {"closest": st["rays_closest"] / max(1, st["samples"]), "shadow": st["rays_shadow"] / max(1, st["samples"])},
+        "bvh_nodes": {"reference_topology": nodes, "fast": fastn}, "scene_upload_s": up_s,
+        "roofline": {"bound": "hbm", "kernel": "k_trace_fast", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                     "traffic": ncu_traffic("k_trace_fast_10m_triangles")[0],
+                     "algorithmic_bytes_per_ray": bpr, "nodes_per_ray": s2["nodes_closest"] / rays, "tris_per_ray": s2["tris_closest"] / rays,
+                     "avg_launch_ms": tms / max(1, tl), "launches": tl, "mrays_per_s_in_kernel": st1["rays_closest"] / (tms * 1e3) if tms > 0 else 0.0,
+                     "timing": "CUDA events per launch on the launching stream, streams=1 pass over one step",
+                     "note": "the trees (~0.4 GB of nodes, ~0.8 GB of fp64 triangles) do not fit the 126 MB L2: the one config bound by HBM latency/bandwidth"}}
     return out
 
 
@@ -496,10 +673,13 @@ def bvh_microbench(args, pkg, bvh):
             for rep in range(3):
                 c.trace_device(d_rays.data_ptr(), n, d_hits.data_ptr(), bvh=flavour)
                 best_ms = min(best_ms, c.last_device_ms())
-            for rep in range(3):
+            c.trace(h_rays.numpy()[: 1 << 21], bvh=flavour, out=h_hits[: 1 << 21])   # warm the pinned path (staging, first touch)
+            walls = []
+            for rep in range(5):
                 t0 = time.perf_counter()
                 h = c.trace(h_rays.numpy(), bvh=flavour, out=h_hits)
-                best_wall = min(best_wall, time.perf_counter() - t0)
+                walls.append(time.perf_counter() - t0)
+            best_wall = min(walls)
             for rep in range(2):
                 t0 = time.perf_counter()
                 hp = c.trace(rays, bvh=flavour)                 # pageable numpy arrays, output allocated by the call
@@ -510,11 +690,12 @@ def bvh_microbench(args, pkg, bvh):
             c.trace(rays[: 1 << 20], bvh=flavour, stats=True)
             s = c.stats()
             res[name] = {"mrays_per_s": n / best_ms / 1e3, "e2e_mrays_per_s": n / best_wall / 1e6,
+                         "e2e_mrays_per_s_median": n / sorted(walls)[len(walls) // 2] / 1e6,
                          "e2e_pageable_mrays_per_s": n / best_pageable / 1e6, "device_ms": best_ms,
                          "nodes_per_ray": s["node_visits"] / (1 << 20), "tris_per_ray": s["tri_tests"] / (1 << 20),
                          "hit_fraction": float((h["prim"] != 0xFFFFFFFF).mean()),
                          "prim_checksum": int(h["prim"].astype(np.uint64).sum())}
-        res["e2e_note"] = ("e2e: rays and hit records in pinned host memory, bdpt_trace copies and traces in 2^20-ray chunks on two streams; "
+        res["e2e_note"] = ("e2e: rays and hit records in pinned host memory, bdpt_trace copies and traces in 2^20-ray chunks on two streams, best and median of 5 after one warm-up call; "
                            "e2e_pageable: plain numpy arrays, output allocated inside the call")
         res["prim_ids_equal_between_flavours"] = res["fast"]["prim_checksum"] == res["reference_topology"]["prim_checksum"]
     return res
@@ -533,6 +714,8 @@ def main():
     ap.add_argument("--streams", type=int, default=0, help="wavefronts in flight (0 = library default)")
     ap.add_argument("--gpu-tree", action="store_true", help="build the fast tree on the device (Morton order) instead of the host binned-SAH build")
     ap.add_argument("--skip-micro", action="store_true")
+    ap.add_argument("--skip-frame", action="store_true", help="skip the whole-frame leg (BASELINE.json config 4: 23 s on one GPU)")
+    ap.add_argument("--skip-configs", action="store_true", help="skip the config 1 / config 5 legs")
     ap.add_argument("--skip-cpu", action="store_true")
     args = ap.parse_args()
     args.steps = max(1, args.steps)

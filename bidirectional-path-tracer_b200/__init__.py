@@ -33,7 +33,7 @@ EXPORTS = [
     "bdpt_scene_image_build", "bdpt_scene_image_free", "bdpt_scene_image_info", "bdpt_scene_image_last_error",
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
-    "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress",
+    "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read",
 ]
 
 
@@ -118,6 +118,7 @@ def lib():
         L.bdpt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.bdpt_film_reduce_comm.argtypes = [C.c_void_p, C.c_int]
         L.bdpt_render_progress.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.bdpt_bench_read.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
         L.bdpt_film_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.bdpt_test_filter32.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_double, C.c_int, C.POINTER(C.c_float)]
         L.bdpt_film_to_rgb8.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -513,6 +514,12 @@ class Context:
 
     def sync(self):
         self._chk(lib().bdpt_sync(self._h), "bdpt_sync")
+
+    def bench_read(self, nbytes, reps=20):
+        """Read bandwidth in GB/s of an nbytes device buffer (bdpt_bench_read): L2-resident when it fits the L2."""
+        g = C.c_double(0)
+        self._chk(lib().bdpt_bench_read(self._h, int(nbytes), int(reps), C.byref(g)), "bdpt_bench_read")
+        return g.value
 
     def comm_init(self, nranks, rank, unique_id):
         """Join the NCCL communicator of the film reduce (one process per GPU); unique_id: the 128 bytes of

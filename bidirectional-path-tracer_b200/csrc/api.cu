@@ -45,6 +45,16 @@ void free_scene(bdpt_ctx* ctx) {
     ctx->have_scene = false;
 }
 
+// ---------------------------------------------------------------- read-bandwidth probe (bdpt_bench_read)
+__global__ void __launch_bounds__(256) k_read_probe(const uint4* __restrict__ buf, uint64_t n16, unsigned long long* sink) {
+    uint4 acc = make_uint4(0, 0, 0, 0);
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n16; i += uint64_t(gridDim.x) * blockDim.x) {
+        const uint4 v = __ldg(buf + i);
+        acc.x ^= v.x; acc.y ^= v.y; acc.z ^= v.z; acc.w ^= v.w;
+    }
+    if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x9E3779B9u) atomicAdd(sink, 1ull);   // keeps the loads alive; practically never true
+}
+
 // ---------------------------------------------------------------- fp32 triangle records of the walk's pre-filter
 __global__ void k_make_tris32(const TriGeom* __restrict__ fast_tris, const uint32_t* __restrict__ fast_prims, uint32_t n,
                               Tri32* __restrict__ out) {
@@ -730,6 +740,33 @@ int bdpt_render_progress(bdpt_ctx* ctx, uint64_t* samples_done, uint64_t* sample
     const int64_t d = std::min(t, ctx->progress_done.load(std::memory_order_relaxed));
     if (samples_done) *samples_done = uint64_t(d < 0 ? 0 : d);
     if (samples_total) *samples_total = uint64_t(t < 0 ? 0 : t);
+    return BDPT_OK;
+}
+
+// Read bandwidth of a device buffer of `bytes` bytes, streamed `reps` times by a grid of 16-byte loads (after two
+// untimed passes): with a buffer well inside the 126 MB L2 this is the L2-resident read peak the traversal kernels'
+// roofline is quoted against beside the HBM figure; with a buffer far beyond it, the HBM read rate.
+int bdpt_bench_read(bdpt_ctx* ctx, uint64_t bytes, int reps, double* gb_per_s) {
+    if (!ctx || !gb_per_s || bytes < 4096 || reps < 1) return BDPT_ERR_ARG;
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    void* buf = nullptr;
+    BDPT_CUDA(ctx, cudaMalloc(&buf, bytes));
+    cudaMemsetAsync(buf, 1, bytes, ctx->stream);
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    const uint64_t n16 = bytes / 16;
+    const unsigned grid = unsigned(sms * 8);
+    for (int k = 0; k < 2; ++k) k_read_probe<<<grid, 256, 0, ctx->stream>>>(static_cast<const uint4*>(buf), n16, ctx->d_stats + ST_COUNT - 1);
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    for (int k = 0; k < reps; ++k) k_read_probe<<<grid, 256, 0, ctx->stream>>>(static_cast<const uint4*>(buf), n16, ctx->d_stats + ST_COUNT - 1);
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(buf);
+    ctx->launches += uint64_t(reps) + 2;
+    if (e != cudaSuccess) { ctx->err = std::string("bdpt_bench_read: ") + cudaGetErrorString(e); return BDPT_ERR_CUDA; }
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    *gb_per_s = double(n16 * 16) * reps / (double(ms) * 1e-3) / 1e9;
     return BDPT_OK;
 }
 

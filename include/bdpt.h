@@ -228,6 +228,9 @@ int bdpt_stats_reset(bdpt_ctx* ctx);
  * device work, excluding host<->device copies. */
 int bdpt_last_device_ms(bdpt_ctx* ctx, double* ms);
 int bdpt_sync(bdpt_ctx* ctx);
+/* Measurement aid: read bandwidth (GB/s) of a `bytes`-byte device buffer streamed `reps` times with 16-byte loads.
+ * bytes well inside the L2 (e.g. 48 MiB) = the L2-resident read peak; bytes far beyond it = the HBM read rate. */
+int bdpt_bench_read(bdpt_ctx* ctx, uint64_t bytes, int reps, double* gb_per_s);
 int bdpt_kernel_times(bdpt_ctx* ctx, double* ms /* BDPT_KT_COUNT */, uint64_t* launches /* BDPT_KT_COUNT */);
 
 /* ---- scene files: the host front-end behind load_scene_from_yaml (scene_loader.h:480-523) and
