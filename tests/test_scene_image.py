@@ -257,7 +257,8 @@ def test_cli_cache_renders_the_same_png(bdpt, tmp_path):
 @pytest.mark.gpu
 def test_cli_two_gpus_share_one_scene_image(bdpt, tmp_path):
     """`bdpt --gpus 2`: camera::render builds the scene image once and uploads it to both contexts (host/camera.cpp);
-    strata are sharded, the films summed on the host -- the PNG must equal the one-GPU run's."""
+    strata are sharded, the films summed by ONE NCCL reduce inside the library (bdpt_film_reduce) -- the PNG must equal
+    the one-GPU run's, and the run must say that the reduce happened."""
     import subprocess
     import torch
     if torch.cuda.device_count() < 2:
@@ -274,6 +275,29 @@ def test_cli_two_gpus_share_one_scene_image(bdpt, tmp_path):
                            cwd=tmp_path, capture_output=True, text=True, timeout=300)
         assert r.returncode == 0, r.stderr[-1000:]
         assert "on %d GPU(s)" % g in r.stderr
+        assert ("film reduce (NCCL)" in r.stderr) == (g == 2)
+        assert "BVH Stats:" in r.stderr and "Rays traced:" in r.stderr      # stats.h:34-50 at the end of camera::render
         pngs.append(decode_png(tmp_path / "output" / ("g%d.png" % g)))
     d = np.abs(pngs[0].astype(int) - pngs[1].astype(int))
     assert d.max() <= 1 and (d > 0).mean() < 0.01
+
+
+@pytest.mark.gpu
+def test_film_reduce_sums_the_shards_on_two_gpus(bdpt, scenes):
+    """bdpt_film_reduce (one process, two devices): each context renders its strata, one NCCL sum-reduce onto context 0;
+    the result equals the single-GPU film up to fp64 summation order."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    v, m, mats, cam = scenes["cornell_spheres"]()
+    c = bdpt.make_camera(48, 32, 16, 6, **cam)
+    with bdpt.Context(0) as a, bdpt.Context(1) as b:
+        for ctx in (a, b):
+            ctx.upload(v, m, mats)
+        a.render(c, seed=9, bvh=bdpt.BVH_FAST, height=32)
+        whole = a.film().copy()
+        a.render(c, seed=9, bvh=bdpt.BVH_FAST, height=32, strata=bdpt.shard_strata(0, 2, 16))
+        b.render(c, seed=9, bvh=bdpt.BVH_FAST, height=32, strata=bdpt.shard_strata(1, 2, 16))
+        ms = bdpt.film_reduce([a, b], root=0)
+        assert ms >= 0
+        assert np.abs(a.film() - whole).max() / np.abs(whole).max() < 1e-12
