@@ -33,7 +33,7 @@ EXPORTS = [
     "bdpt_scene_image_build", "bdpt_scene_image_free", "bdpt_scene_image_info", "bdpt_scene_image_last_error",
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
-    "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read",
+    "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read", "bdpt_comm_attach",
 ]
 
 
@@ -117,6 +117,7 @@ def lib():
         L.bdpt_comm_unique_id.argtypes = [C.c_void_p]
         L.bdpt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.bdpt_film_reduce_comm.argtypes = [C.c_void_p, C.c_int]
+        L.bdpt_comm_attach.argtypes = [C.c_void_p]
         L.bdpt_render_progress.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.bdpt_bench_read.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
         L.bdpt_film_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -526,6 +527,10 @@ class Context:
         comm_unique_id() from one rank, carried to the others by the launcher (torch.distributed, MPI, a file)."""
         buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
         self._chk(lib().bdpt_comm_init(self._h, int(nranks), int(rank), buf), "bdpt_comm_init")
+
+    def comm_attach(self):
+        """Take over the communicator an earlier context of this process joined on the same device."""
+        self._chk(lib().bdpt_comm_attach(self._h), "bdpt_comm_attach")
 
     def film_reduce(self, root=0):
         """The one exchange step of a frame: NCCL sum-reduce of the ranks' device films onto `root`, in place."""

@@ -71,15 +71,15 @@ int fail(bdpt_ctx* ctx, const std::string& what) {
 std::mutex g_mu;
 std::map<std::vector<int>, std::vector<ncclComm_t>> g_comms;
 
+// communicators of bdpt_comm_init: one per device of this process, kept until the next bdpt_comm_init for that device;
+// a context only borrows it (a new communicator costs a rendezvous plus ~2 s of lazy channel set-up at its first
+// collective: an application joins once and renders many frames, possibly through many contexts)
+struct ProcComm { ncclComm_t comm = nullptr; int rank = 0, size = 1; };
+std::map<int, ProcComm> g_proc_comm;
+
 }  // namespace
 
-void bdpt::comm_free(bdpt_ctx* ctx) {
-    if (ctx->comm) {
-        Nccl* N = nccl();
-        if (N->CommDestroy) N->CommDestroy(static_cast<ncclComm_t>(ctx->comm));
-        ctx->comm = nullptr;
-    }
-}
+void bdpt::comm_free(bdpt_ctx* ctx) { ctx->comm = nullptr; }
 
 extern "C" {
 
@@ -96,12 +96,24 @@ int bdpt_comm_init(bdpt_ctx* ctx, int nranks, int rank, const void* id128) {
     Nccl* N = nccl();
     if (!N->err.empty()) return fail(ctx, N->err);
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
-    comm_free(ctx);
+    std::lock_guard<std::mutex> lock(g_mu);
+    ProcComm& pc = g_proc_comm[ctx->device];
+    if (pc.comm) { N->CommDestroy(pc.comm); pc.comm = nullptr; }
     ncclUniqueId id;
     std::memcpy(&id, id128, sizeof id);
     ncclComm_t c = nullptr;
     BDPT_NCCL(ctx, N->CommInitRank(&c, nranks, id, rank));
+    pc.comm = c; pc.rank = rank; pc.size = nranks;
     ctx->comm = c; ctx->comm_rank = rank; ctx->comm_size = nranks;
+    return BDPT_OK;
+}
+
+int bdpt_comm_attach(bdpt_ctx* ctx) {
+    if (!ctx) return BDPT_ERR_ARG;
+    std::lock_guard<std::mutex> lock(g_mu);
+    auto it = g_proc_comm.find(ctx->device);
+    if (it == g_proc_comm.end() || !it->second.comm) { ctx->err = "bdpt_comm_attach: no communicator was initialised for this device"; return BDPT_ERR_STATE; }
+    ctx->comm = it->second.comm; ctx->comm_rank = it->second.rank; ctx->comm_size = it->second.size;
     return BDPT_OK;
 }
 

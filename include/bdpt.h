@@ -212,12 +212,15 @@ int bdpt_film_to_rgb8(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out);
  * libnccl.so.2 is opened on first use (a process that already holds an NCCL, e.g. torch's, shares it).
  *   one process, n devices:   bdpt_film_reduce(ctxs, n, root)           (communicators are created once per device list)
  *   one process per GPU:      id from bdpt_comm_unique_id on one rank, carried to the others by the launcher;
- *                             bdpt_comm_init on every rank; bdpt_film_reduce_comm(ctx, root) per frame.
+ *                             bdpt_comm_init on every rank, once; bdpt_film_reduce_comm(ctx, root) per frame.
  * Both are blocking; bdpt_last_device_ms then gives the device time of the reduce on the calling / root context. */
 int bdpt_film_reduce(bdpt_ctx** ctxs, int n, int root);
 int bdpt_comm_unique_id(void* id128 /* 128 bytes out */);
 int bdpt_comm_init(bdpt_ctx* ctx, int nranks, int rank, const void* id128);
 int bdpt_film_reduce_comm(bdpt_ctx* ctx, int root);
+/* The communicator of bdpt_comm_init belongs to the process (one per device) and outlives the context that joined:
+ * another context on the same device takes it over with bdpt_comm_attach instead of a new rendezvous. */
+int bdpt_comm_attach(bdpt_ctx* ctx);
 /* Samples of the bdpt_render call in flight already handed to the GPU, out of how many: callable from another
  * thread while bdpt_render runs (the progress bar of camera::render, camera.h:67-109). */
 int bdpt_render_progress(bdpt_ctx* ctx, uint64_t* samples_done, uint64_t* samples_total);
