@@ -322,6 +322,8 @@ void bdpt_ctx_destroy(bdpt_ctx* ctx) {
     comm_free(ctx);
     free_scene(ctx);
     if (ctx->film) cudaFree(ctx->film);
+    if (ctx->d_tex) cudaFree(ctx->d_tex);
+    if (ctx->d_tex_data) cudaFree(ctx->d_tex_data);
     if (ctx->d_stats) cudaFree(ctx->d_stats);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -414,12 +416,53 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
     v.center = mk(h.center[0], h.center[1], h.center[2]);
     rc = derive_walk32(ctx, v);
     if (rc) { free_scene(ctx); return rc; }
+    apply_textures(ctx, v);
     BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->view = v;
     ctx->have_scene = true;
     if (timing)
         std::fprintf(stderr, "bdpt_scene_upload: %llu triangles: flatten %.1f ms, reference tree %.1f ms || fast tree %.1f ms, total %.1f ms\n",
                      (unsigned long long)n_tris, t_flat, t_ref, t_fast, ms_since(t_start));
+    return BDPT_OK;
+}
+
+int bdpt_scene_set_textures(bdpt_ctx* ctx, const bdpt_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes) {
+    if (!ctx || (n_tex && !tex) || (data_bytes && !data)) return BDPT_ERR_ARG;
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    std::vector<Tex> h(n_tex);
+    for (uint32_t i = 0; i < n_tex; ++i) {
+        const bdpt_texture& t = tex[i];
+        if (t.type > BDPT_TEX_IMAGE) { ctx->err = "unknown texture type"; return BDPT_ERR_ARG; }
+        uint64_t need = 0;
+        if (t.type == BDPT_TEX_NOISE) need = 256 * 3 * sizeof(double) + 3 * 256 * sizeof(int32_t);
+        if (t.type == BDPT_TEX_IMAGE) {
+            if (t.width < 0 || t.height < 0) { ctx->err = "image texture: negative size"; return BDPT_ERR_ARG; }
+            need = uint64_t(t.width) * uint64_t(t.height) * 3;
+        }
+        if (need && ((t.data_offset & 7u) || t.data_offset > data_bytes || need > data_bytes - t.data_offset)) {
+            ctx->err = "texture data outside the blob (or not 8-byte aligned)"; return BDPT_ERR_ARG;
+        }
+        if (t.type == BDPT_TEX_CHECKER && !(t.scale != 0.0)) { ctx->err = "checker texture: scale 0"; return BDPT_ERR_ARG; }
+        if (t.type == BDPT_TEX_NOISE) {   // perm entries index randvec
+            const int32_t* perm = reinterpret_cast<const int32_t*>(static_cast<const unsigned char*>(data) + t.data_offset + 256 * 3 * sizeof(double));
+            for (int k = 0; k < 768; ++k) if (perm[k] < 0 || perm[k] > 255) { ctx->err = "noise texture: permutation entry outside 0..255"; return BDPT_ERR_ARG; }
+        }
+        Tex& d = h[i];
+        d.ar = t.a[0]; d.ag = t.a[1]; d.ab = t.a[2]; d.br = t.b[0]; d.bg = t.b[1]; d.bb = t.b[2];
+        d.scale = t.scale; d.data = t.data_offset; d.type = t.type; d.width = t.width; d.height = t.height; d.pad = 0;
+    }
+    if (ctx->d_tex) { cudaFree(ctx->d_tex); ctx->d_tex = nullptr; }
+    if (ctx->d_tex_data) { cudaFree(ctx->d_tex_data); ctx->d_tex_data = nullptr; }
+    ctx->n_tex = 0;
+    if (n_tex) {
+        BDPT_CUDA(ctx, cudaMalloc(&ctx->d_tex, n_tex * sizeof(Tex)));
+        BDPT_CUDA(ctx, cudaMemcpy(ctx->d_tex, h.data(), n_tex * sizeof(Tex), cudaMemcpyHostToDevice));
+        BDPT_CUDA(ctx, cudaMalloc(&ctx->d_tex_data, std::max<uint64_t>(data_bytes, 16)));
+        if (data_bytes) BDPT_CUDA(ctx, cudaMemcpy(ctx->d_tex_data, data, data_bytes, cudaMemcpyHostToDevice));
+        ctx->n_tex = n_tex;
+    }
+    apply_textures(ctx, ctx->view);
     return BDPT_OK;
 }
 

@@ -32,6 +32,11 @@ struct bdpt_ctx {
     uint64_t launches = 0;
     uint64_t samples = 0;
 
+    // texture table of bdpt_scene_set_textures: belongs to the context, survives scene uploads
+    bdpt::Tex* d_tex = nullptr;
+    unsigned char* d_tex_data = nullptr;
+    uint32_t n_tex = 0;
+
     // NCCL communicator of bdpt_comm_init (film_reduce.cu); ncclComm_t
     void* comm = nullptr;
     int comm_rank = 0, comm_size = 1;
@@ -87,6 +92,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 // api.cu: the fp32 triangle records + error scale of the warp-synchronous walk (traverse_w32.cuh), queued on ctx->stream
 int derive_walk32(bdpt_ctx* ctx, SceneView& v);
 void comm_free(bdpt_ctx* ctx);   // film_reduce.cu
+inline void apply_textures(bdpt_ctx* ctx, SceneView& v) { v.tex = ctx->d_tex; v.tex_data = ctx->d_tex_data; v.n_tex = ctx->n_tex; }
 void render_free(bdpt_ctx* ctx);
 // gpu_bvh.cu: the fast tree built on the device from triangles already uploaded (queued on ctx->stream)
 int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const double lo[3], const double hi[3], double extent,

@@ -161,7 +161,8 @@ void flatten_scene(const double* verts, const uint32_t* mat_id, uint64_t n, cons
         m.param = mats[i].param;
         if (mats[i].type == BDPT_MAT_METAL && m.param > 1.0) m.param = 1.0;  // material.h:71
         m.type = mats[i].type;
-        m.pad[0] = m.pad[1] = m.pad[2] = 0;
+        m.tex = mats[i].tex;
+        m.pad[0] = m.pad[1] = 0;
         out.mats[i] = m;
     }
     out.tris.resize(n); out.shade.resize(n); out.area.resize(n); out.tri_box.resize(6 * n);

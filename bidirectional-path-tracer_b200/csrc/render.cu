@@ -26,6 +26,7 @@
 
 #include "ctx.h"
 #include "render_math.cuh"
+#include "texture.cuh"
 #include "traverse_fast.cuh"
 #include "traverse_walk.cuh"
 #include "traverse_w32.cuh"
@@ -126,6 +127,8 @@ struct WF {              // wavefront workspace, all device pointers
     uint32_t *ncam, *nlight;
     SQ sq[2];                        // shadow queues, ping-pong: the shadow stage of one iteration runs on its own
                                      // stream while the main stream already traces the next
+    int textured;                    // the scene has textures: lcol exists
+    D3* lcol;                        // beside lv: the light vertex's colour as connect_vertices needs it (emission / albedo at that point)
     int mis;                         // BDPT_WEIGHT_MIS: the three arrays below exist
     PathMis* pmis;                   // per path id
     VertMis *cvm, *lvm;              // beside cv / lv
@@ -241,7 +244,7 @@ __device__ __forceinline__ SampleId decode_sample(const Frame& f, int64_t L) {
 // Fills `ngen` free slots (free_list, or slots 0..ngen-1 on a worker's first iteration) with samples
 // gen_base .. gen_base+ngen-1 of this call; consecutive threads take consecutive samples = neighbouring
 // pixels, so the primary rays of a refill are coherent.
-template <bool MIS>
+template <bool MIS, bool TEX>
 __global__ void __launch_bounds__(kGen) k_generate(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ free_list,
                                                    int64_t gen_base, int64_t ngen, int cur, int dn) {
     const int64_t gi = int64_t(blockIdx.x) * kGen + threadIdx.x;
@@ -292,10 +295,12 @@ __global__ void __launch_bounds__(kGen) k_generate(SceneView sc, Frame f, WF w, 
             const D3 n = mk(sh.nx, sh.ny, sh.nz);
             const double pdf = 1.0 / sc.light_total_area;
             const Mat m = sc.mats[sh.mat];
-            const D3 emission = (m.type == BDPT_MAT_LIGHT) ? mk(m.r, m.g, m.b) : mk(0, 0, 0);  // emitted(front=true)
+            // emitted(front = true, u = v = 0, p), camera.h:386-392
+            const D3 emission = (m.type != BDPT_MAT_LIGHT) ? mk(0, 0, 0) : (TEX ? mat_colour(sc, m, pos, [](double& tu, double& tv) { tu = 0.0; tv = 0.0; }) : mk(m.r, m.g, m.b));
             if (len2(emission) > 0) {
                 const D3 T0 = mk(1.0, 1.0, 1.0) / fmax(pdf, 1e-8);
                 store_vertex(w.lv + size_t(b) * size_t(w.depth), pos, T0, prim | kLightFlag);
+                if (TEX) w.lcol[size_t(b) * size_t(w.depth)] = emission;
                 nl = 1;
                 const D3 dir = Onb(n).transform(random_cosine_direction(rl));
                 const D3 du = unit(dir);
@@ -653,6 +658,15 @@ __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint
     return s;
 }
 
+// (u, v) of the hit as triangle::hit left them in the record (triangle.h:66-67): the same arithmetic on the same inputs
+struct HitUV {
+    const SceneView& sc; const Surf& s;
+    __device__ __forceinline__ void operator()(double& u, double& v) const {
+        double t;
+        if (!tri_candidate(sc.tris + s.prim, s.o, s.d, t, u, v)) { u = 0.0; v = 0.0; }
+    }
+};
+
 // BDPT_WEIGHT_MIS: the subpath's running weight quantities as they stand ON this vertex (the hit just found):
 // the segment's area conversion and the arrival cosine go in
 struct MisAtHit { double dVCM, dVC, cos_in; uint32_t len; };
@@ -675,14 +689,14 @@ __device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d,
 // scatter() is false: the subpath ends here.  Camera subpath: bidirectional_color adds throughput *
 // emission for this non-delta vertex (camera.h:305-309); it never connects (evaluate_bsdf = 0).
 // Light subpath: the vertex is connectable with f_light = emission when hit from the front (camera.h:463).
-template <bool MIS>
+template <bool MIS, bool TEX>
 __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, double* film) {
     {
         const bool is_cam = pid < uint32_t(w.B);
         const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
         const Surf s = load_surf(sc, w, pid);
         const Mat m = sc.mats[sc.shade[s.prim].mat];
-        const D3 Le = mk(m.r, m.g, m.b);
+        const D3 Le = TEX ? mat_colour(sc, m, s.p, HitUV{sc, s}) : mk(m.r, m.g, m.b);
         if (s.front && len2(Le) > 0) {   // emitted() is one-sided (material.h:140)
             if (is_cam) {
                 double wgt = 1.0;
@@ -697,6 +711,7 @@ __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f,
             } else if (!MIS) {   // MIS: an emitter absorbs; a light-subpath vertex on it connects to nothing
                 const uint32_t slot = w.nlight[b];
                 store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | kLightFlag);
+                if (TEX) w.lcol[size_t(b) * size_t(w.depth) + slot] = Le;
                 w.nlight[b] = slot + 1;
             }
         }
@@ -705,7 +720,7 @@ __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f,
 }
 
 // ------------------------------------------------------------------ K2: lambertian (material.h:42-67)
-template <bool MIS>
+template <bool MIS, bool TEX>
 __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
     {
@@ -714,7 +729,7 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
         if (MIS) mh = mis_arrive(f, w, pid, s);
         const uint32_t side = (MIS && !s.front) ? kBackFlag : 0u;
         const Mat m = sc.mats[sc.shade[s.prim].mat];
-        const D3 albedo = mk(m.r, m.g, m.b);
+        const D3 albedo = TEX ? mat_colour(sc, m, s.p, HitUV{sc, s}) : mk(m.r, m.g, m.b);   // tex->value(rec.u, rec.v, rec.p), material.h:47,61
         const bool is_cam = pid < uint32_t(w.B);
         const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
         // vertex push (camera.h:342-349) — only vertices that can contribute: evaluate_bsdf = albedo/pi
@@ -730,6 +745,7 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
             } else {
                 const uint32_t slot = w.nlight[b];
                 store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | side);
+                if (TEX) w.lcol[size_t(b) * size_t(w.depth) + slot] = albedo;
                 if (MIS) { VertMis vm; vm.dVCM = mh.dVCM; vm.dVC = mh.dVC; vm.cos_in = mh.cos_in; vm.len = mh.len; vm.pad = 0; w.lvm[size_t(b) * size_t(w.depth) + slot] = vm; }
                 w.nlight[b] = slot + 1;
             }
@@ -834,7 +850,7 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
 // Thread idx walks the concatenation light | lambertian | metal | dielectric of the queues k_trace_* filled, so
 // a warp straddles at most one class boundary; the survivors' queue append and the retirement of ended
 // subpaths are shared.
-template <bool MIS>
+template <bool MIS, bool TEX>
 __global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
     const uint32_t idx = blockIdx.x * kWide + threadIdx.x;
     const uint32_t n_li = w.counters[C_MAT0 + BDPT_MAT_LIGHT], n_la = w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN],
@@ -843,8 +859,8 @@ __global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w,
     bool live = false;
     uint32_t pid = 0;
     if (valid) {
-        if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light<MIS>(sc, f, w, pid, film); }
-        else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert<MIS>(sc, f, w, pid); }
+        if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light<MIS, TEX>(sc, f, w, pid, film); }
+        else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert<MIS, TEX>(sc, f, w, pid); }
         else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal<MIS>(sc, f, w, pid); }
         else { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric<MIS>(sc, f, w, pid); }
     }
@@ -918,7 +934,7 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                     max_t = dist - 0.001;
                     if (dist > 0 && max_t > 0) {
                         const Mat lm = sc.mats[lsh.mat];
-                        const D3 lrgb = mk(lm.r, lm.g, lm.b);
+                        const D3 lrgb = w.lcol ? w.lcol[size_t(b) * size_t(w.depth) + size_t(m)] : mk(lm.r, lm.g, lm.b);
                         const D3 f_light = (lprim & kLightFlag) ? lrgb : lrgb / kPi;   // camera.h:463-466
                         if (len2(f_light) > 0) {
                             contrib = ctf * lT * f_light;                               // camera.h:471-472
@@ -1011,7 +1027,7 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
             D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
             if (lprim & kBackFlag) ln = -ln;
             const Mat lm = sc.mats[lsh.mat];
-            const D3 lrgb = mk(lm.r, lm.g, lm.b);
+            const D3 lrgb = w.lcol ? w.lcol[size_t(b) * size_t(w.depth) + size_t(m)] : mk(lm.r, lm.g, lm.b);
             if (have_cam) {
                 const D3 dir = lp - cp;
                 const double dist2 = len2(dir);
@@ -1389,6 +1405,7 @@ void carve(WF& w, char* base) {
     w.counters = c.take<uint32_t>(C_COUNT);
     w.cv = c.take<VertRec>(V); w.lv = c.take<VertRec>(V);
     w.ncam = c.take<uint32_t>(B); w.nlight = c.take<uint32_t>(B);
+    if (w.textured) w.lcol = c.take<D3>(V);
     if (w.mis) { w.pmis = c.take<PathMis>(P); w.cvm = c.take<VertMis>(V); w.lvm = c.take<VertMis>(V); }
     for (int k = 0; k < 2; ++k) {
         SQ& q = w.sq[k];
@@ -1518,6 +1535,7 @@ struct Job {
     unsigned resident_blocks;        // blocks of a traversal kernel the device keeps resident (persistent grids)
     int threshold;                   // dynamic fetch: a walk yields when fewer lanes than this are still walking
     bool mis;                        // BDPT_WEIGHT_MIS
+    bool tex;                        // the scene has textures
     bool walk32;                     // bulk traversal = the warp-synchronous fp32 walk (traverse_w32.cuh); false: round 1's per-lane walk
     int knobs32;                     // its time-slice / refill / leaf-batch parameters (unpack_knobs)
     unsigned resident32;             // blocks of k_trace_w32 / k_shadow_w32 the device keeps resident
@@ -1588,8 +1606,12 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT0 + ex, 0, sizeof(uint32_t), st));
         if (ngen > 0) {
             tm.begin(KT_GENERATE, st);
-            if (J.mis) k_generate<true><<<grid_for(ngen, kGen), kGen, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
-            else k_generate<false><<<grid_for(ngen, kGen), kGen, 0, st>>>(sc, f, wf, first ? nullptr : wf.q_slots[dn ^ 1], gen_base, ngen, cur, dn);
+            {
+                const uint32_t* fl = first ? nullptr : wf.q_slots[dn ^ 1];
+                const unsigned gg = grid_for(ngen, kGen);
+                if (J.mis) { if (J.tex) k_generate<true, true><<<gg, kGen, 0, st>>>(sc, f, wf, fl, gen_base, ngen, cur, dn); else k_generate<true, false><<<gg, kGen, 0, st>>>(sc, f, wf, fl, gen_base, ngen, cur, dn); }
+                else { if (J.tex) k_generate<false, true><<<gg, kGen, 0, st>>>(sc, f, wf, fl, gen_base, ngen, cur, dn); else k_generate<false, false><<<gg, kGen, 0, st>>>(sc, f, wf, fl, gen_base, ngen, cur, dn); }
+            }
             tm.end(KT_GENERATE, st);
             wk.launches += 1;
             wk.samples += uint64_t(ngen);
@@ -1612,8 +1634,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         tm.end(KT_TRACE, st);
         tm.begin(KT_SHADE, st);
         const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kWide);   // the lagged rays of the front blocks are shaded too
-        if (J.mis) k_shade<true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film);
-        else k_shade<false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film);
+        if (J.mis) { if (J.tex) k_shade<true, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<true, false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
+        else { if (J.tex) k_shade<false, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<false, false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
         k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
         tm.end(KT_SHADE, st);
         wk.launches += 3;
@@ -1692,6 +1714,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (o.bvh != BDPT_BVH_REFERENCE && o.bvh != BDPT_BVH_FAST) { ctx->err = "unknown bvh flavour"; return BDPT_ERR_ARG; }
     if (o.weighting != BDPT_WEIGHT_REF_SUM && o.weighting != BDPT_WEIGHT_MIS) { ctx->err = "unknown weighting"; return BDPT_ERR_ARG; }
     const bool mis = o.weighting == BDPT_WEIGHT_MIS;
+    const bool textured = ctx->view.n_tex > 0;
     int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
     H = H < 1 ? 1 : H;
     if (!ctx->film || ctx->film_w != cam->image_width || ctx->film_h != H) {
@@ -1727,7 +1750,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
         // the default takes at most half of the free device memory: a slot costs ~5 KB at depth 16 and ~25 KB at
         // depth 80 (vertex pools and shadow queues grow with the depth)
         WF probe{};
-        probe.B = 65536; probe.depth = f.depth; probe.mis = mis ? 1 : 0;
+        probe.B = 65536; probe.depth = f.depth; probe.mis = mis ? 1 : 0; probe.textured = textured ? 1 : 0;
         probe.scap = std::max<int64_t>(probe.B * 8, int64_t(f.depth) * probe.B * (mis ? 2 : 1));
         probe.sscap = std::max<int64_t>(4096, probe.scap / 8);
         carve(probe, nullptr);
@@ -1753,10 +1776,10 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             for (auto& e : wk.ev_shadow) BDPT_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             BDPT_CUDA(ctx, cudaMallocHost(&wk.hc, (C_COUNT + SQ_COUNT) * sizeof(uint32_t)));
         }
-        if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth || wk.wf.mis != (mis ? 1 : 0)) {
+        if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth || wk.wf.mis != (mis ? 1 : 0) || wk.wf.textured != (textured ? 1 : 0)) {
             if (wk.wf.base) { BDPT_CUDA(ctx, cudaStreamSynchronize(wk.stream)); cudaFree(wk.wf.base); }
             std::memset(&wk.wf, 0, sizeof(WF));
-            wk.wf.B = B; wk.wf.depth = f.depth; wk.wf.mis = mis ? 1 : 0;
+            wk.wf.B = B; wk.wf.depth = f.depth; wk.wf.mis = mis ? 1 : 0; wk.wf.textured = textured ? 1 : 0;
             wk.wf.scap = std::max<int64_t>(B * 8, int64_t(f.depth) * B * (mis ? 2 : 1));   // >= one camera slot against every light vertex (MIS: + the splats)
             wk.wf.scap = std::min<int64_t>(wk.wf.scap, int64_t(0xFFFFFFF0u));
             wk.wf.sscap = std::max<int64_t>(4096, wk.wf.scap / 8);
@@ -1775,7 +1798,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 
     Job J;
     J.sc = ctx->view; J.f = f; J.o = o; J.total = total; J.film = ctx->film; J.d_stats = ctx->d_stats;
-    J.mis = mis;
+    J.mis = mis; J.tex = textured;
     // traversal stack: one StackEntry per tree level per thread (deferred children only)
     const size_t levels = size_t(std::max(ctx->host.fast_depth, ctx->host.ref_depth)) + 2;
     if (ctx->host.fast_depth + 2 > uint32_t(kStackLevels) || ctx->host.ref_depth + 2 > uint32_t(2 * kStackLevels)) {

@@ -39,7 +39,8 @@ struct __align__(16) Mat {
     double r, g, b;
     double param;
     uint32_t type;
-    uint32_t pad[3];
+    uint32_t tex;      // 0: (r, g, b) is the colour; k > 0: texture k - 1
+    uint32_t pad[2];
 };
 static_assert(sizeof(Mat) == 48, "Mat must be 48 bytes");
 
@@ -67,6 +68,17 @@ struct __align__(16) WideNode {
 };
 static_assert(sizeof(WideNode) == 128, "WideNode must be 128 bytes");
 
+// texture table entry (texture.h:14-87), 80 B
+struct __align__(16) Tex {
+    double ar, ag, ab, br, bg, bb;   // solid / checker even; checker odd
+    double scale;
+    uint64_t data;                   // byte offset into tex_data
+    uint32_t type;
+    int32_t width, height;
+    uint32_t pad;
+};
+static_assert(sizeof(Tex) == 80, "Tex must be 80 bytes");
+
 struct SceneView {
     const WideNode* wide_nodes;   // may be null (device-built tree): the binary walk is used
     uint32_t n_wide_nodes;
@@ -84,6 +96,9 @@ struct SceneView {
     const TriGeom* tris;
     const TriShade* shade;
     const Mat* mats;
+    const Tex* tex;               // texture table (bdpt_scene_set_textures), null when the scene has none
+    const unsigned char* tex_data;
+    uint32_t n_tex;
     const uint32_t* lights;       // prim IDs, reference light-list order
     const double* light_area;     // running sums of light triangle areas in list order (triangle.h:206-212)
     uint32_t n_lights;

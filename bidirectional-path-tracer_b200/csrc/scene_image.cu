@@ -252,6 +252,7 @@ int bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, ui
     v.n_lights = h->n_lights; v.n_tris = h->n_tris; v.n_ref_nodes = h->n_ref_nodes; v.n_fast_nodes = h->n_fast_nodes;
     v.light_total_area = h->light_total_area; v.extent = h->extent;
     v.center = mk(h->center[0], h->center[1], h->center[2]);
+    apply_textures(ctx, v);
     if (int rc = derive_walk32(ctx, v)) { for (void* p : ctx->scene_allocs) cudaFree(p); ctx->scene_allocs.clear(); return rc; }
 
     // what the other calls read from the host copy: the tree depths (workspace sizing) and the DFS leaf order

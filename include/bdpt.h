@@ -33,10 +33,27 @@ enum { BDPT_MAT_LAMBERTIAN = 0, BDPT_MAT_METAL = 1, BDPT_MAT_DIELECTRIC = 2, BDP
 
 typedef struct {
     uint32_t type;    /* BDPT_MAT_* */
-    uint32_t pad;
+    uint32_t tex;     /* 0: the colour is rgb (solid_color, texture.h:14-26); k > 0: texture k-1 of bdpt_scene_set_textures
+                         gives the lambertian albedo / the light's emission (material.h:45,136) */
     double   rgb[3];  /* albedo (lambertian, metal) or emission (light); unused for dielectric */
     double   param;   /* metal: fuzz, clamped to <=1 as material.h:71; dielectric: refraction index */
 } bdpt_material;
+
+/* Textures (texture.h:28-87, perlin.h).  The reference's loader can construct none of them
+ * (scene_loader.h:101-170 only ever makes solid colours), so they are an extension of the scene surface; the arithmetic
+ * is the reference's: texture::value(u, v, p) with (u, v) = the triangle's barycentric hit coordinates
+ * (triangle.h:66-67) and p the hit point.  Checker colours are solid colours (texture.h:34-35). */
+enum { BDPT_TEX_SOLID = 0, BDPT_TEX_CHECKER = 1, BDPT_TEX_NOISE = 2, BDPT_TEX_IMAGE = 3 };
+typedef struct {
+    uint32_t type;         /* BDPT_TEX_* */
+    uint32_t pad;
+    double   a[3];         /* solid: the colour; checker: the even colour */
+    double   b[3];         /* checker: the odd colour */
+    double   scale;        /* checker: cell size (texture.h:31); noise: frequency of the sine (texture.h:80) */
+    uint64_t data_offset;  /* into the data blob, 8-byte aligned.  noise: perlin's tables (perlin.h:62-66): 256 x 3 doubles
+                              randvec, then perm_x, perm_y, perm_z as 3 x 256 int32.  image: width * height * 3 bytes, rows top to bottom */
+    int32_t  width, height;/* image */
+} bdpt_texture;
 
 /* The public camera fields of camera.h:26-41 that shape the image. */
 typedef struct {
@@ -150,6 +167,10 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
 #define BDPT_UPLOAD_FAST_TREE_GPU 1u
 int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                          const bdpt_material* mats, uint32_t n_mats, uint32_t flags);
+/* The texture table bdpt_material.tex refers to, with its data blob (copied; may be freed on return).  Belongs to the
+ * context, not to the scene: call it before or after bdpt_scene_upload / bdpt_scene_upload_image, again to replace it,
+ * with n_tex = 0 to drop it. */
+int bdpt_scene_set_textures(bdpt_ctx* ctx, const bdpt_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes);
 int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth);
 
 /* ---- scene image: everything bdpt_scene_upload derives from the soup -- the flattened triangle
