@@ -33,12 +33,20 @@ EXPORTS = [
     "bdpt_scene_image_build", "bdpt_scene_image_free", "bdpt_scene_image_info", "bdpt_scene_image_last_error",
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
-    "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read", "bdpt_comm_attach",
+    "bdpt_scene_set_textures", "bdpt_scene_file_textures", "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read", "bdpt_comm_attach",
 ]
 
 
 class Material(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("pad", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+    _fields_ = [("type", C.c_uint32), ("tex", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+
+
+class Texture(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("pad", C.c_uint32), ("a", C.c_double * 3), ("b", C.c_double * 3), ("scale", C.c_double),
+                ("data_offset", C.c_uint64), ("width", C.c_int32), ("height", C.c_int32)]
+
+
+TEX_SOLID, TEX_CHECKER, TEX_NOISE, TEX_IMAGE = 0, 1, 2, 3
 
 
 class Camera(C.Structure):
@@ -104,6 +112,7 @@ def lib():
         L.bdpt_ctx_destroy.restype = None
         L.bdpt_scene_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32]
         L.bdpt_scene_upload_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.bdpt_scene_set_textures.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.bdpt_bvh_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
         L.bdpt_bvh_leaf_order.argtypes = [C.c_void_p, C.c_void_p]
         L.bdpt_host_bvh_build.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -133,6 +142,7 @@ def lib():
         L.bdpt_scene_file_free.restype = None
         L.bdpt_scene_file_info.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64),
                                            C.c_void_p, C.c_char_p, C.c_uint64]
+        L.bdpt_scene_file_textures.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]
         L.bdpt_scene_file_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.bdpt_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
         L.bdpt_host_last_error.restype = C.c_char_p
@@ -155,13 +165,34 @@ def lib():
 
 
 def make_materials(mats):
-    """mats: list of (type, (r,g,b), param)"""
+    """mats: list of (type, (r,g,b), param[, tex]); tex = 1-based index into the texture table, 0 / absent = none"""
     arr = (Material * len(mats))()
-    for i, (t, rgb, p) in enumerate(mats):
-        arr[i].type = int(t)
-        arr[i].rgb[:] = [float(x) for x in rgb]
-        arr[i].param = float(p)
+    for i, mt in enumerate(mats):
+        arr[i].type = int(mt[0])
+        arr[i].rgb[:] = [float(x) for x in mt[1]]
+        arr[i].param = float(mt[2])
+        arr[i].tex = int(mt[3]) if len(mt) > 3 else 0
     return arr
+
+
+def make_textures(textures):
+    """textures: list of dicts {type, a, b, scale, width, height, data} -> (Texture array, uint8 blob); data = the
+    noise tables (256 x 3 doubles + 3 x 256 int32, perlin.h:62-66) or the image's width*height*3 bytes."""
+    arr = (Texture * max(1, len(textures)))()
+    blob = bytearray()
+    for i, t in enumerate(textures):
+        arr[i].type = int(t["type"])
+        arr[i].a[:] = [float(x) for x in t.get("a", (0, 0, 0))]
+        arr[i].b[:] = [float(x) for x in t.get("b", (0, 0, 0))]
+        arr[i].scale = float(t.get("scale", 1.0))
+        arr[i].width, arr[i].height = int(t.get("width", 0)), int(t.get("height", 0))
+        while len(blob) % 8:
+            blob.append(0)
+        arr[i].data_offset = len(blob)
+        d = t.get("data")
+        if d is not None:
+            blob += bytes(d) if isinstance(d, (bytes, bytearray)) else np.ascontiguousarray(d).tobytes()
+    return arr, np.frombuffer(bytes(blob) + bytes(8), dtype=np.uint8).copy()
 
 
 def image_height(width, aspect_ratio):
@@ -330,11 +361,24 @@ class SceneFile:
             self.materials = (Material * max(1, nm.value))()
             lib().bdpt_scene_file_copy(h, self.verts.ctypes.data, self.mat_id.ctypes.data, C.byref(self.materials))
             self.n_mats = nm.value
+            nt_, nb_ = C.c_uint32(0), C.c_uint64(0)
+            lib().bdpt_scene_file_textures(h, C.byref(nt_), None, C.byref(nb_), None)
+            tarr = (Texture * max(1, nt_.value))()
+            blob = np.zeros(max(8, nb_.value), np.uint8)
+            lib().bdpt_scene_file_textures(h, None, C.byref(tarr), None, blob.ctypes.data)
+            self.textures = []   # dicts as Context.set_textures / make_textures take them
+            for k in range(nt_.value):
+                t = tarr[k]
+                n = (256 * 3 * 8 + 3 * 256 * 4) if t.type == TEX_NOISE else (t.width * t.height * 3 if t.type == TEX_IMAGE else 0)
+                self.textures.append(dict(type=int(t.type), a=tuple(t.a), b=tuple(t.b), scale=float(t.scale), width=int(t.width),
+                                          height=int(t.height), data=blob[t.data_offset:t.data_offset + n].copy() if n else None))
         finally:
             lib().bdpt_scene_file_free(h)
 
     def material_list(self):
-        return [(int(m.type), tuple(m.rgb), float(m.param)) for m in list(self.materials)[:self.n_mats]]
+        """(type, rgb, param) per material; a textured one carries a 4th entry, its 1-based texture index."""
+        return [(int(m.type), tuple(m.rgb), float(m.param)) + ((int(m.tex),) if m.tex else ())
+                for m in list(self.materials)[:self.n_mats]]
 
     def camera_with(self, width=None, height=None, spp=None, depth=None):
         """The CLI's --res/--spp/--depth overrides (BASELINE.json configs differ from the YAML values)."""
@@ -394,6 +438,13 @@ class Context:
         self._chk(lib().bdpt_scene_upload_ex(self._h, v.ctypes.data, m.ctypes.data, len(v), C.byref(marr), len(marr),
                                              UPLOAD_FAST_TREE_GPU if gpu_tree else 0), "bdpt_scene_upload")
         self.n_tris = len(v)
+        return self
+
+    def set_textures(self, textures):
+        """bdpt_scene_set_textures: the table bdpt_material.tex refers to (list of dicts as make_textures takes; [] drops it)."""
+        arr, blob = make_textures(textures)
+        self._chk(lib().bdpt_scene_set_textures(self._h, C.byref(arr) if textures else None, len(textures),
+                                                blob.ctypes.data if textures else None, len(blob) if textures else 0), "bdpt_scene_set_textures")
         return self
 
     def upload_image(self, image, verify=False):

@@ -42,7 +42,11 @@ void camera::render(const hittable& world, const hittable& lights) {
     const void* image = options.scene_image;
     uint64_t image_bytes = options.scene_image_bytes;
     std::vector<double> verts; std::vector<uint32_t> mat_id; std::vector<bdpt_material> mats;
-    if (!from_image) flatten_triangles(*prims, verts, mat_id, mats);
+    std::vector<bdpt_texture> textures; std::vector<unsigned char> tex_data;
+    if (!from_image) {
+        flatten_triangles(*prims, verts, mat_id, mats);
+        flatten_textures(*prims, mats, textures, tex_data);
+    }
     // several GPUs: flatten and build the two trees ONCE into a scene image and hand every context the same block,
     // instead of letting each worker's bdpt_scene_upload rebuild them side by side on the same host cores
     struct image_owner { void* p = nullptr; ~image_owner() { if (p) bdpt_scene_image_free(p); } } built;
@@ -77,6 +81,8 @@ void camera::render(const hittable& world, const hittable& lights) {
             bdpt_ctx* ctx = ctxs.c[g];
             if (from_image) check(bdpt_scene_upload_image(ctx, image, image_bytes, 0), ctx, "bdpt_scene_upload_image");
             else check(bdpt_scene_upload(ctx, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx, "bdpt_scene_upload");
+            if (!textures.empty())
+                check(bdpt_scene_set_textures(ctx, textures.data(), uint32_t(textures.size()), tex_data.data(), tex_data.size()), ctx, "bdpt_scene_set_textures");
             check(bdpt_film_clear(ctx, W, H), ctx, "bdpt_film_clear");
             bdpt_render_opts o{};
             o.seed = options.seed; o.stratum_begin = g; o.stratum_step = G; o.bvh = options.bvh;

@@ -17,6 +17,8 @@ struct bdpt_scene_file {
     std::vector<double> verts;
     std::vector<uint32_t> mat_id;
     std::vector<bdpt_material> mats;
+    std::vector<bdpt_texture> textures;
+    std::vector<unsigned char> tex_data;
     // scene-image cache (bdpt_scene_file_open_cached)
     const void* image = nullptr;
     uint64_t image_bytes = 0;
@@ -43,6 +45,7 @@ int bdpt_scene_file_load(const char* yaml_path, bdpt_scene_file** out) {
         auto* f = new bdpt_scene_file;
         f->scene = load_scene_from_yaml(yaml_path);
         flatten_triangles(f->scene.world.tris, f->verts, f->mat_id, f->mats);
+        flatten_textures(f->scene.world.tris, f->mats, f->textures, f->tex_data);
         *out = f;
     } catch (const std::exception& e) {
         g_host_err = e.what();
@@ -52,6 +55,15 @@ int bdpt_scene_file_load(const char* yaml_path, bdpt_scene_file** out) {
 }
 
 void bdpt_scene_file_free(bdpt_scene_file* f) { delete f; }
+
+int bdpt_scene_file_textures(const bdpt_scene_file* f, uint32_t* n_tex, bdpt_texture* tex, uint64_t* data_bytes, void* data) {
+    if (!f) return BDPT_ERR_ARG;
+    if (n_tex) *n_tex = uint32_t(f->textures.size());
+    if (data_bytes) *data_bytes = f->tex_data.size();
+    if (tex && !f->textures.empty()) std::memcpy(tex, f->textures.data(), f->textures.size() * sizeof(bdpt_texture));
+    if (data && !f->tex_data.empty()) std::memcpy(data, f->tex_data.data(), f->tex_data.size());
+    return BDPT_OK;
+}
 
 int bdpt_scene_file_info(const bdpt_scene_file* f, uint64_t* n_tris, uint32_t* n_mats, uint64_t* n_lights,
                          bdpt_camera* cam, char* output_name, uint64_t output_cap) {

@@ -37,6 +37,38 @@ class vec3 {
 using point3 = vec3;
 using color = vec3;
 
+// texture.h:7-87 as descriptors (the arithmetic of value() runs on the GPU: csrc/texture.cuh).  noise_texture draws its
+// perlin tables on the host exactly as perlin.h:6-14,68-75 does, from a default-seeded mt19937 of its own standing in for
+// main.h:28-32's (so the first noise texture of a scene gets the tables the reference would give it); image_texture reads
+// binary PPM (P6) files and applies rtw_image's float round trip (rtw_stb_image.h:45-60,90-112 over stb's gamma 2.2).
+class texture {
+  public:
+    enum kind_t { Solid = BDPT_TEX_SOLID, Checker = BDPT_TEX_CHECKER, Noise = BDPT_TEX_NOISE, Image = BDPT_TEX_IMAGE };
+    virtual ~texture() = default;
+    kind_t kind = Solid;
+    color a, b;                       // solid / checker even, checker odd
+    double scale = 1.0;
+    int width = 0, height = 0;        // image
+    std::vector<unsigned char> data;  // noise: 768 doubles + 768 int32; image: width * height * 3 bytes
+};
+class solid_color : public texture {
+  public:
+    explicit solid_color(const color& albedo) { kind = Solid; a = albedo; }
+    solid_color(double r, double g, double bl) : solid_color(color(r, g, bl)) {}
+};
+class checker_texture : public texture {   // texture.h:28-49 (the two-colour constructor, :34-35)
+  public:
+    checker_texture(double scale_, const color& c1, const color& c2) { kind = Checker; scale = scale_; a = c1; b = c2; }
+};
+class noise_texture : public texture {     // texture.h:75-85
+  public:
+    explicit noise_texture(double scale_);
+};
+class image_texture : public texture {     // texture.h:51-73
+  public:
+    explicit image_texture(const char* filename);
+};
+
 class material {
   public:
     enum kind_t { Lambertian = BDPT_MAT_LAMBERTIAN, Metal = BDPT_MAT_METAL, Dielectric = BDPT_MAT_DIELECTRIC,
@@ -45,6 +77,7 @@ class material {
     kind_t kind;
     color rgb;       // albedo or emission
     double param;    // fuzz or refraction index
+    shared_ptr<texture> tex;   // lambertian albedo / light emission through a texture (material.h:45,136), else null
     virtual bool is_delta() const { return kind == Metal || kind == Dielectric; }   // material.h:38,85,118
   protected:
     material(kind_t k, const color& c, double p) : kind(k), rgb(c), param(p) {}
@@ -52,6 +85,7 @@ class material {
 class lambertian : public material {   // material.h:42-67
   public:
     explicit lambertian(const color& albedo) : material(Lambertian, albedo, 0.0) {}
+    explicit lambertian(shared_ptr<texture> t) : material(Lambertian, color(0.5, 0.5, 0.5), 0.0) { tex = std::move(t); }   // material.h:45
 };
 class metal : public material {        // material.h:69-90 (fuzz clamped to <= 1, :71)
   public:
@@ -64,6 +98,7 @@ class dielectric : public material {   // material.h:92-131
 class diffuse_light : public material {  // material.h:133-147
   public:
     explicit diffuse_light(const color& emit) : material(DiffuseLight, emit, 0.0) {}
+    explicit diffuse_light(shared_ptr<texture> t) : material(DiffuseLight, color(1, 1, 1), 0.0) { tex = std::move(t); }   // material.h:135
 };
 
 class hittable {
@@ -185,3 +220,7 @@ void write_png_path(const std::string& path, const uint8_t* rgb, int image_width
 // flatten a primitive list to the C-ABI's soup (prim ID = list order); material table dedups by pointer
 void flatten_triangles(const std::vector<triangle>& tris, std::vector<double>& verts, std::vector<uint32_t>& mat_id,
                        std::vector<bdpt_material>& mats);
+// the texture table of a flattened scene for bdpt_scene_set_textures; sets bdpt_material.tex of `mats` (same order as
+// flatten_triangles made them)
+void flatten_textures(const std::vector<triangle>& tris, std::vector<bdpt_material>& mats, std::vector<bdpt_texture>& tex,
+                      std::vector<unsigned char>& data);

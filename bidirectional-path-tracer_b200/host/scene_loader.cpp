@@ -1,6 +1,7 @@
 // YAML + OBJ scene front-end: behaviour of the reference's src/scene/scene_loader.h (schema in SURVEY
 // Appendix B), written against yaml_lite instead of yaml-cpp.  Not on the timed path.
 #include <algorithm>
+#include <random>
 #include <array>
 #include <charconv>
 #include <future>
@@ -44,10 +45,37 @@ color read_color_scaled(const node& n, const color& fallback) {     // scene_loa
     return color(r, g, b);
 }
 
+// Extension of the reference's schema (its loader only ever builds solid colours): a `texture:` map inside a
+// lambertian or light material -- {type: checker, scale: s, even: [r,g,b], odd: [r,g,b]} | {type: noise, scale: s} |
+// {type: image, file: picture.ppm (relative to the YAML)} -- builds the reference's checker_texture / noise_texture /
+// image_texture (texture.h:28-87) and the material's texture constructor (material.h:45,135).
+std::string g_scene_dir;
+void reset_scene_rng();   // a scene load starts at the head of the random stream, like a fresh run of the reference
+shared_ptr<texture> build_texture(const node& n, bool emission) {
+    if (!n.is_map()) return nullptr;
+    const std::string type = to_string(n["type"], "");
+    // colours follow the material they sit in: albedo 0-255 -> 0-1 (scene_loader.h:81-92), emission linear HDR (:123-125)
+    auto col = [&](const node& c, const color& fallback) { return emission ? read_color(c, fallback) : read_color_scaled(c, fallback); };
+    if (type == "checker")
+        return make_shared<checker_texture>(to_double(n["scale"], 1.0), col(n["even"], color(1, 1, 1)), col(n["odd"], color(0, 0, 0)));
+    if (type == "noise") return make_shared<noise_texture>(to_double(n["scale"], 1.0));
+    if (type == "image") {
+        std::string file = to_string(n["file"], "");
+        if (!file.empty() && file[0] != '/' && !g_scene_dir.empty()) file = g_scene_dir + "/" + file;
+        return make_shared<image_texture>(file.c_str());
+    }
+    if (type == "solid") return make_shared<solid_color>(col(n["color"], color(0, 0, 0)));
+    throw std::runtime_error("unknown texture type '" + type + "'");
+}
+
 shared_ptr<material> build_material(const node& n) {                 // scene_loader.h:101-170
     if (!n.is_map()) throw std::runtime_error("Material must be a mapping");
     const color black(0, 0, 0);
     const std::string type = to_string(n["type"], "");
+    if (!type.empty() && n["texture"].defined()) {
+        if (type == "lambertian") return make_shared<lambertian>(build_texture(n["texture"], false));
+        if (type == "light" || type == "diffuse_light") return make_shared<diffuse_light>(build_texture(n["texture"], true));
+    }
     if (!type.empty()) {
         const color c = read_color_scaled(n["color"], read_color_scaled(n["albedo"],
                         read_color_scaled(n["base_color"], read_color_scaled(n["base_colour"], black))));
@@ -278,6 +306,8 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
     if (!root.is_map()) throw std::runtime_error("Scene root must be a mapping");
     scene_load_result result;
     load_camera(root["camera"], result.cam);
+    g_scene_dir = std::filesystem::path(path).parent_path().string();
+    reset_scene_rng();
     const material_map mats = load_materials(root["materials"]);
     const node* surfaces = &root["surfaces"];
     if (!surfaces->defined()) surfaces = &root["scene"];
@@ -351,6 +381,84 @@ uint64_t scene_source_key(const std::string& path) {
         }
     for (auto& j : jobs) { const uint64_t h = j.get(); key = mix_bytes(key, reinterpret_cast<const char*>(&h), sizeof h); }
     return key ? key : 1;   // 0 means "no key" in an image header
+}
+
+// ---------------------------------------------------------------- textures (texture.h, perlin.h, rtw_stb_image.h)
+namespace {
+struct host_rng {   // main.h:28-37: one default-seeded mt19937 + uniform_real_distribution
+    std::mt19937 gen;
+    std::uniform_real_distribution<double> dist{0.0, 1.0};
+    double next() { return dist(gen); }
+    double next(double mn, double mx) { return mn + (mx - mn) * next(); }
+    int next_int(int mn, int mx) { return int(next(mn, mx + 1)); }   // main.h:39-42
+};
+host_rng& scene_rng() { static host_rng r; return r; }
+void reset_scene_rng() { scene_rng() = host_rng(); }
+}  // namespace
+
+noise_texture::noise_texture(double scale_) {
+    kind = Noise; scale = scale_;
+    host_rng& r = scene_rng();
+    data.resize(256 * 3 * sizeof(double) + 3 * 256 * sizeof(int32_t));
+    double* randvec = reinterpret_cast<double*>(data.data());
+    int32_t* perm = reinterpret_cast<int32_t*>(data.data() + 256 * 3 * sizeof(double));
+    for (int i = 0; i < 256; ++i) {   // perlin.h:7-9: unit_vector(vec3::random(-1, 1)); g++ evaluates the arguments z, y, x
+        const double z = r.next(-1, 1), y = r.next(-1, 1), x = r.next(-1, 1);
+        const double inv = 1 / std::sqrt(x * x + y * y + z * z);      // vec3.h:114-116: v / length = (1/length) * v
+        randvec[3 * i] = inv * x; randvec[3 * i + 1] = inv * y; randvec[3 * i + 2] = inv * z;
+    }
+    for (int t = 0; t < 3; ++t) {     // perlin.h:11-13,68-84
+        int32_t* p = perm + 256 * t;
+        for (int i = 0; i < 256; ++i) p[i] = i;
+        for (int i = 255; i > 0; --i) std::swap(p[i], p[r.next_int(0, i)]);
+    }
+}
+
+image_texture::image_texture(const char* filename) {
+    kind = Image;
+    std::ifstream f(filename, std::ios::binary);
+    std::string magic;
+    int maxv = 0;
+    if (!(f >> magic >> width >> height >> maxv) || magic != "P6" || maxv != 255 || width <= 0 || height <= 0) {
+        std::cerr << "ERROR: Could not load image file '" << filename << "' (binary PPM, P6, maxval 255).\n";   // rtw_stb_image.h:36
+        width = height = 0;
+        return;
+    }
+    f.get();
+    std::vector<unsigned char> raw(size_t(width) * height * 3);
+    f.read(reinterpret_cast<char*>(raw.data()), std::streamsize(raw.size()));
+    data.resize(raw.size());
+    for (size_t i = 0; i < raw.size(); ++i) {
+        // stb_image's stbi__ldr_to_hdr: (float)(pow(byte / 255.0f, 2.2f) * 1.0f) in float; then rtw_stb_image.h:90-97
+        const float value = std::pow(float(raw[i]) / 255.0f, 2.2f) * 1.0f;
+        data[i] = value <= 0.0 ? 0 : (1.0 <= value ? 255 : static_cast<unsigned char>(256.0 * value));
+    }
+}
+
+void flatten_textures(const std::vector<triangle>& tris, std::vector<bdpt_material>& mats, std::vector<bdpt_texture>& tex,
+                      std::vector<unsigned char>& data) {
+    tex.clear(); data.clear();
+    std::unordered_map<const material*, uint32_t> mat_index;
+    std::unordered_map<const texture*, uint32_t> tex_index;
+    for (const triangle& t : tris) {
+        if (mat_index.count(t.mat.get())) continue;
+        const uint32_t mi = uint32_t(mat_index.size());
+        mat_index.emplace(t.mat.get(), mi);
+        if (!t.mat->tex || mi >= mats.size()) continue;
+        const texture* tx = t.mat->tex.get();
+        auto it = tex_index.find(tx);
+        if (it == tex_index.end()) {
+            bdpt_texture d{};
+            d.type = uint32_t(tx->kind); d.scale = tx->scale; d.width = tx->width; d.height = tx->height;
+            for (int k = 0; k < 3; ++k) { d.a[k] = tx->a[k]; d.b[k] = tx->b[k]; }
+            while (data.size() % 8) data.push_back(0);
+            d.data_offset = data.size();
+            data.insert(data.end(), tx->data.begin(), tx->data.end());
+            it = tex_index.emplace(tx, uint32_t(tex.size())).first;
+            tex.push_back(d);
+        }
+        mats[mi].tex = it->second + 1;
+    }
 }
 
 void flatten_triangles(const std::vector<triangle>& tris, std::vector<double>& verts, std::vector<uint32_t>& mat_id,

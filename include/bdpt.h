@@ -266,6 +266,9 @@ int  bdpt_scene_file_info(const bdpt_scene_file* f, uint64_t* n_tris, uint32_t* 
                           bdpt_camera* cam, char* output_name, uint64_t output_cap);
 /* copies the flattened soup: verts n_tris*9, mat_id n_tris, mats n_mats (any may be NULL) */
 int  bdpt_scene_file_copy(const bdpt_scene_file* f, double* verts, uint32_t* mat_id, bdpt_material* mats);
+/* The scene's texture table for bdpt_scene_set_textures (a `texture:` map in a lambertian / light material: checker, noise,
+ * image -- an extension of the reference's schema, host/scene_loader.cpp).  Call with tex = data = NULL for the sizes. */
+int  bdpt_scene_file_textures(const bdpt_scene_file* f, uint32_t* n_tex, bdpt_texture* tex, uint64_t* data_bytes, void* data);
 int  bdpt_write_png(const char* path, const uint8_t* rgb, int width, int height);
 /* Scene-image files: save writes to "<path>.tmp" and renames; map gives a read-only mapping of the file
  * (page cache backed: nothing is copied until the upload reads it). */

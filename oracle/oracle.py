@@ -19,7 +19,16 @@ MISS = 0xFFFFFFFF
 
 
 class Material(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("pad", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+    _fields_ = [("type", C.c_uint32), ("tex", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+
+
+class Texture(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("pad", C.c_uint32), ("a", C.c_double * 3), ("b", C.c_double * 3), ("scale", C.c_double),
+                ("data_offset", C.c_uint64), ("width", C.c_int32), ("height", C.c_int32)]
+
+
+TEX_SOLID, TEX_CHECKER, TEX_NOISE, TEX_IMAGE = 0, 1, 2, 3
+NOISE_BYTES = 256 * 3 * 8 + 3 * 256 * 4
 
 
 class Camera(C.Structure):
@@ -52,13 +61,36 @@ def make_camera(width, height, spp, depth, lookfrom, lookat, vfov=90.0, vup=(0, 
 
 
 def make_materials(mats):
-    """mats: list of (type, (r,g,b), param)"""
+    """mats: list of (type, (r,g,b), param[, tex]) -- tex = 1-based index into the texture table, 0 / absent = none"""
     arr = (Material * len(mats))()
-    for i, (t, rgb, p) in enumerate(mats):
-        arr[i].type = t
-        arr[i].rgb[:] = rgb
-        arr[i].param = p
+    for i, mt in enumerate(mats):
+        arr[i].type = mt[0]
+        arr[i].rgb[:] = mt[1]
+        arr[i].param = mt[2]
+        arr[i].tex = mt[3] if len(mt) > 3 else 0
     return arr
+
+
+def make_textures(textures):
+    """textures: list of dicts {type, a, b, scale, width, height, data (bytes / uint8 array / None)} -> (Texture array, blob).
+    Noise textures without data get room for their tables (filled later from the reference: Oracle.texture_data)."""
+    arr = (Texture * max(1, len(textures)))()
+    blob = bytearray()
+    for i, t in enumerate(textures):
+        arr[i].type = t["type"]
+        arr[i].a[:] = t.get("a", (0, 0, 0))
+        arr[i].b[:] = t.get("b", (0, 0, 0))
+        arr[i].scale = t.get("scale", 1.0)
+        arr[i].width, arr[i].height = t.get("width", 0), t.get("height", 0)
+        while len(blob) % 8:
+            blob.append(0)
+        arr[i].data_offset = len(blob)
+        d = t.get("data")
+        if d is not None:
+            blob += bytes(np.ascontiguousarray(d).tobytes() if not isinstance(d, (bytes, bytearray)) else d)
+        elif t["type"] == TEX_NOISE:
+            blob += bytes(NOISE_BYTES)
+    return arr, np.frombuffer(bytes(blob) + b"\0" * 8, dtype=np.uint8).copy()
 
 
 def build(which="all"):
@@ -84,6 +116,8 @@ class Oracle:
         f = lambda n: getattr(self.lib, p + n)
         self._create = f("scene_create"); self._create.restype = C.c_void_p
         self._create.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32]
+        self._create_tex = f("scene_create_tex"); self._create_tex.restype = C.c_void_p
+        self._create_tex.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         self._destroy = f("scene_destroy"); self._destroy.argtypes = [C.c_void_p]
         self._nodes = f("bvh_node_count"); self._nodes.restype = C.c_uint64; self._nodes.argtypes = [C.c_void_p]
         self._order = f("bvh_leaf_order"); self._order.argtypes = [C.c_void_p, C.c_void_p]
@@ -102,7 +136,8 @@ class Oracle:
         self._rgb8 = f("colors_to_rgb8"); self._rgb8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         self.scene = None
 
-    def load(self, verts, mat_id, mats):
+    def load(self, verts, mat_id, mats, textures=None):
+        """textures: (Texture array, n, uint8 blob) as make_textures returns them with the count, or None."""
         verts = np.ascontiguousarray(verts, dtype=np.float64).reshape(-1, 9)
         mat_id = np.ascontiguousarray(mat_id, dtype=np.uint32)
         assert len(mat_id) == len(verts)
@@ -110,8 +145,32 @@ class Oracle:
         marr = make_materials(mats) if isinstance(mats, list) else mats
         if self.scene:
             self._destroy(self.scene)
-        self.scene = self._create(verts.ctypes.data, mat_id.ctypes.data, len(verts), C.byref(marr), len(marr))
+        if textures is not None:
+            tarr, n_tex, blob = textures
+            self.scene = self._create_tex(verts.ctypes.data, mat_id.ctypes.data, len(verts), C.byref(marr), len(marr), C.byref(tarr), n_tex,
+                                          blob.ctypes.data, len(blob))
+        else:
+            self.scene = self._create(verts.ctypes.data, mat_id.ctypes.data, len(verts), C.byref(marr), len(marr))
         return self
+
+    def texture_value(self, k, uvp):
+        uvp = np.ascontiguousarray(uvp, dtype=np.float64).reshape(-1, 5)
+        out = np.empty((len(uvp), 3), np.float64)
+        f = getattr(self.lib, ("port_" if self.kind == "port" else "ref_") + "texture_value")
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p]
+        f.restype = None
+        f(self.scene, k, len(uvp), uvp.ctypes.data, out.ctypes.data)
+        return out
+
+    def texture_data(self, k, nbytes):
+        """ref only: what the reference's own texture object k holds (perlin tables / image bytes after its float round trip)."""
+        assert self.kind == "ref"
+        out = np.zeros(nbytes, np.uint8)
+        f = self.lib.ref_texture_data
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        rc = f(self.scene, k, out.ctypes.data)
+        assert rc == 0, rc
+        return out
 
     def node_count(self):
         return int(self._nodes(self.scene))

@@ -24,7 +24,7 @@ enum { ORC_MAT_LAMBERTIAN = 0, ORC_MAT_METAL = 1, ORC_MAT_DIELECTRIC = 2, ORC_MA
 
 typedef struct {
     uint32_t type;    /* ORC_MAT_* */
-    uint32_t pad;
+    uint32_t tex;     /* 0: rgb is the colour; k > 0: texture k-1 of scene_create_tex (lambertian albedo / light emission) */
     double   rgb[3];  /* albedo (lambertian, metal) or emission (light) */
     double   param;   /* metal: fuzz (already clamped to <=1), dielectric: refraction index */
 } orc_material;
@@ -44,6 +44,17 @@ typedef struct {
     double defocus_angle;   /* must be <= 0: the YAML loader forces it off (scene_loader.h:463) */
     double focus_dist;
 } orc_camera;
+
+/* texture.h:14-87 / perlin.h (not reachable from the reference's loader: SURVEY F8, 8f-4) */
+enum { ORC_TEX_SOLID = 0, ORC_TEX_CHECKER = 1, ORC_TEX_NOISE = 2, ORC_TEX_IMAGE = 3 };
+typedef struct {
+    uint32_t type, pad;
+    double   a[3], b[3];   /* solid colour / checker even; checker odd */
+    double   scale;
+    uint64_t data_offset;  /* noise: 768 doubles randvec + 768 int32 perm_x|y|z; image: width*height*3 bytes as the
+                              reference's rtw_image holds them (after its float round trip) */
+    int32_t  width, height;
+} orc_texture;
 
 enum { ORC_RNG_MT19937 = 0,   /* the reference's global default-seeded mt19937 stream (main.h:28-32) */
        ORC_RNG_PHILOX  = 1 }; /* counter-based stream keyed (seed, pixel, stratum, subpath); port only  */
@@ -68,6 +79,16 @@ typedef struct {
 
 void*    ORC(scene_create)(const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                            const orc_material* mats, uint32_t n_mats);
+/* The same with a texture table.  port: `data` holds every table / image as described above.  ref: builds the
+ * reference's own checker_texture / noise_texture / image_texture objects; a noise texture makes its OWN perlin tables
+ * (perlin.h:6-14, from the global RNG) and an image texture is loaded by the reference's rtw_image from a PPM file the
+ * harness writes from `data` (raw RGB there) -- ref_texture_data then exports what the reference ended up with, so
+ * that the port and the CUDA path can be given bit-identical tables. */
+void*    ORC(scene_create_tex)(const double* verts, const uint32_t* mat_id, uint64_t n_tris, const orc_material* mats,
+                               uint32_t n_mats, const orc_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes);
+/* texture k evaluated at n points: uvp = n x 5 doubles (u, v, px, py, pz) -> rgb = n x 3 doubles (texture.h value()) */
+void     ORC(texture_value)(void* scene, uint32_t tex_index, uint64_t n, const double* uvp, double* rgb);
+int      ref_texture_data(void* scene, uint32_t tex_index, void* out /* noise: 6144 + 3072 bytes; image: w*h*3 */);
 void     ORC(scene_destroy)(void* scene);
 uint64_t ORC(bvh_node_count)(void* scene);
 /* DFS leaf order: order[k] = prim ID of the k-th triangle in the builder's final array. */

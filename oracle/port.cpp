@@ -278,6 +278,61 @@ struct Node {
 struct Scene {
     std::vector<Tri> tris;
     std::vector<orc_material> mats;
+    std::vector<orc_texture> tex;
+    std::vector<unsigned char> tex_data;
+
+    // perlin::noise / turb, perlin.h:16-49,77-91
+    double perlin_noise(const unsigned char* tables, V3 p) const {
+        const double* randvec = reinterpret_cast<const double*>(tables);
+        const int32_t* perm = reinterpret_cast<const int32_t*>(tables + 256 * 3 * sizeof(double));
+        double u = p.x - std::floor(p.x), v = p.y - std::floor(p.y), w = p.z - std::floor(p.z);
+        int i = int(std::floor(p.x)), j = int(std::floor(p.y)), k = int(std::floor(p.z));
+        double uu = u * u * (3 - 2 * u), vv = v * v * (3 - 2 * v), ww = w * w * (3 - 2 * w);
+        double accum = 0.0;
+        for (int di = 0; di < 2; di++)
+            for (int dj = 0; dj < 2; dj++)
+                for (int dk = 0; dk < 2; dk++) {
+                    int idx = perm[(i + di) & 255] ^ perm[256 + ((j + dj) & 255)] ^ perm[512 + ((k + dk) & 255)];
+                    V3 c{randvec[3 * idx], randvec[3 * idx + 1], randvec[3 * idx + 2]};
+                    V3 weight_v{u - di, v - dj, w - dk};
+                    accum += (di * uu + (1 - di) * (1 - uu)) * (dj * vv + (1 - dj) * (1 - vv)) * (dk * ww + (1 - dk) * (1 - ww)) * dot(c, weight_v);
+                }
+        return accum;
+    }
+    double perlin_turb(const unsigned char* tables, V3 p, int depth) const {
+        double accum = 0.0, weight = 1.0;
+        V3 tp = p;
+        for (int i = 0; i < depth; i++) {
+            accum += weight * perlin_noise(tables, tp);
+            weight *= 0.5;
+            tp = {tp.x * 2, tp.y * 2, tp.z * 2};
+        }
+        return std::fabs(accum);
+    }
+    // texture::value(u, v, p), texture.h:14-87
+    V3 colour(const orc_material& m, double u, double v, V3 p) const {
+        if (m.tex == 0 || m.tex > tex.size()) return {m.rgb[0], m.rgb[1], m.rgb[2]};
+        const orc_texture& t = tex[m.tex - 1];
+        if (t.type == ORC_TEX_CHECKER) {
+            double inv_scale = 1.0 / t.scale;
+            int xi = int(std::floor(inv_scale * p.x)), yi = int(std::floor(inv_scale * p.y)), zi = int(std::floor(inv_scale * p.z));
+            return ((xi + yi + zi) % 2 == 0) ? V3{t.a[0], t.a[1], t.a[2]} : V3{t.b[0], t.b[1], t.b[2]};
+        }
+        if (t.type == ORC_TEX_NOISE)
+            return V3{.5, .5, .5} * (1 + std::sin(t.scale * p.z + 10 * perlin_turb(tex_data.data() + t.data_offset, p, 7)));
+        if (t.type == ORC_TEX_IMAGE) {
+            if (t.height <= 0) return {0, 1, 1};
+            u = u < 0 ? 0 : (u > 1 ? 1 : u);
+            v = 1.0 - (v < 0 ? 0 : (v > 1 ? 1 : v));
+            int i = int(u * t.width), j = int(v * t.height);
+            i = i < 0 ? 0 : (i < t.width ? i : t.width - 1);
+            j = j < 0 ? 0 : (j < t.height ? j : t.height - 1);
+            const unsigned char* px = tex_data.data() + t.data_offset + (size_t(j) * t.width + i) * 3;
+            double color_scale = 1.0 / 255.0;
+            return {color_scale * px[0], color_scale * px[1], color_scale * px[2]};
+        }
+        return {t.a[0], t.a[1], t.a[2]};
+    }
     std::vector<uint32_t> lights;  // prim IDs in reference light-list order (scene_loader.h:190-202; main.cpp:67)
     std::vector<Node> nodes;
     std::vector<uint32_t> order;   // builder's working array == DFS leaf order when finished
@@ -374,7 +429,7 @@ struct Cam {  // camera.h:148-197
 };
 
 struct Vertex {  // camera.h:236-243
-    V3 p, normal, throughput, wi, emission;
+    V3 p, normal, throughput, wi, emission, albedo;
     uint32_t mat;
     bool delta, is_light;
 };
@@ -385,14 +440,14 @@ struct Integrator {
     Integrator(const Scene& s, const Cam& c) : sc(s), cam(c) {}
 
     // material.h:133-147
-    V3 emitted(const orc_material& m, bool front) const {
+    V3 emitted(const orc_material& m, bool front, double u = 0, double v = 0, V3 p = V3{0, 0, 0}) const {
         if (m.type != ORC_MAT_LIGHT || !front) return {0, 0, 0};
-        return {m.rgb[0], m.rgb[1], m.rgb[2]};
+        return sc.colour(m, u, v, p);
     }
     // material.h:60-63; everything but lambertian evaluates to zero (material.h:35-37)
-    V3 eval_bsdf(const orc_material& m) const {
+    V3 eval_bsdf(const orc_material& m, V3 albedo) const {   // albedo = tex->value(rec.u, rec.v, rec.p) of that vertex
         if (m.type != ORC_MAT_LAMBERTIAN) return {0, 0, 0};
-        return V3{m.rgb[0], m.rgb[1], m.rgb[2]} / kPi;
+        return albedo / kPi;
     }
 
     void trace_path(V3 o, V3 d, int depth, std::vector<Vertex>& path, V3 T, V3* bg, Rng& rng) const {  // camera.h:325-370
@@ -407,13 +462,14 @@ struct Integrator {
             vx.p = rec.p; vx.normal = rec.normal; vx.mat = sc.tris[rec.prim].mat;
             vx.throughput = T;
             vx.wi = unit(-d);
-            vx.emission = emitted(m, rec.front);
+            vx.emission = emitted(m, rec.front, rec.u, rec.v, rec.p);
+            vx.albedo = (m.type == ORC_MAT_LAMBERTIAN) ? sc.colour(m, rec.u, rec.v, rec.p) : V3{0, 0, 0};
             vx.delta = (m.type == ORC_MAT_METAL || m.type == ORC_MAT_DIELECTRIC);
             vx.is_light = (m.type == ORC_MAT_LIGHT);
             path.push_back(vx);
 
             if (m.type == ORC_MAT_LIGHT) break;  // material.h:22-24: scatter() false
-            V3 att{m.rgb[0], m.rgb[1], m.rgb[2]};
+            V3 att = (m.type == ORC_MAT_LAMBERTIAN) ? vx.albedo : V3{m.rgb[0], m.rgb[1], m.rgb[2]};
             if (m.type == ORC_MAT_METAL) {  // material.h:73-83
                 V3 refl = reflect(d, rec.normal);
                 refl = unit(refl) + (m.param * random_unit_vector(rng));
@@ -471,13 +527,13 @@ struct Integrator {
         V3 n = chosen->normal;
         double pdf = 1.0 / total;
         const orc_material& m = sc.mats[chosen->mat];
-        V3 emission = emitted(m, true);
+        V3 emission = emitted(m, true, 0, 0, pos);   // camera.h:389-392: u = v = 0
         if (len2(emission) <= 0) return false;
 
         Vertex ev;
         ev.p = pos; ev.normal = n; ev.mat = chosen->mat;
         ev.throughput = V3{1.0, 1.0, 1.0} / std::max(pdf, 1e-8);
-        ev.wi = n; ev.emission = emission; ev.delta = false; ev.is_light = true;
+        ev.wi = n; ev.emission = emission; ev.albedo = V3{0, 0, 0}; ev.delta = false; ev.is_light = true;
         path.push_back(ev);
 
         V3 dir = Onb(n).transform(random_cosine_direction(rng));
@@ -512,9 +568,9 @@ struct Integrator {
         double cos_light = std::fabs(dot(lv.normal, -du));
         if (cos_cam <= 0 || cos_light <= 0) return {0, 0, 0};
         if (!visible(cv.p, lv.p)) return {0, 0, 0};
-        V3 f_cam = eval_bsdf(sc.mats[cv.mat]);
+        V3 f_cam = eval_bsdf(sc.mats[cv.mat], cv.albedo);
         if (len2(f_cam) <= 0) return {0, 0, 0};
-        V3 f_light = lv.is_light ? lv.emission : eval_bsdf(sc.mats[lv.mat]);
+        V3 f_light = lv.is_light ? lv.emission : eval_bsdf(sc.mats[lv.mat], lv.albedo);
         if (len2(f_light) <= 0) return {0, 0, 0};
         V3 contrib = cv.throughput * f_cam;
         contrib = contrib * lv.throughput * f_light;
@@ -581,7 +637,7 @@ struct Integrator {
             dVCM /= cos_in; dVC /= cos_in;
             if (m.type == ORC_MAT_LIGHT) {           // absorbs; a camera path that arrives on the emitting side sees it
                 if (camera && rec.front) {
-                    V3 Le{m.rgb[0], m.rgb[1], m.rgb[2]};
+                    V3 Le = sc.colour(m, rec.u, rec.v, rec.p);
                     double w = 1.0;
                     if (length > 1) {
                         const double directPdfA = pdfA_light, emissionPdfW = pdfA_light * cos_in / kPi;
@@ -591,7 +647,7 @@ struct Integrator {
                 }
                 break;
             }
-            V3 att{m.rgb[0], m.rgb[1], m.rgb[2]};
+            V3 att = (m.type == ORC_MAT_LAMBERTIAN) ? sc.colour(m, rec.u, rec.v, rec.p) : V3{m.rgb[0], m.rgb[1], m.rgb[2]};
             if (m.type == ORC_MAT_METAL || m.type == ORC_MAT_DIELECTRIC) {
                 V3 dir;
                 if (m.type == ORC_MAT_METAL) {
@@ -660,7 +716,7 @@ struct Integrator {
         double u = light_rng.next(), v = light_rng.next();
         if (u + v > 1.0) { u = 1.0 - u; v = 1.0 - v; }
         const V3 y0 = chosen->v0 + (u * chosen->e1) + (v * chosen->e2), n0 = chosen->normal;
-        const V3 Le = emitted(sc.mats[chosen->mat], true);
+        const V3 Le = emitted(sc.mats[chosen->mat], true, 0, 0, y0);
         if (len2(Le) <= 0) return result;
         {
             V3 dir = Onb(n0).transform(random_cosine_direction(light_rng));
@@ -779,6 +835,23 @@ void* port_scene_create(const double* v, const uint32_t* mat_id, uint64_t n, con
     s->root = s->build(0, n);
     g_stats[6] = s->nodes.size();
     return s;
+}
+void* port_scene_create_tex(const double* v, const uint32_t* mat_id, uint64_t n, const orc_material* mats, uint32_t n_mats,
+                            const orc_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes) {
+    auto* s = static_cast<Scene*>(port_scene_create(v, mat_id, n, mats, n_mats));
+    s->tex.assign(tex, tex + n_tex);
+    const unsigned char* d = static_cast<const unsigned char*>(data);
+    s->tex_data.assign(d, d + data_bytes);
+    return s;
+}
+void port_texture_value(void* p, uint32_t k, uint64_t n, const double* uvp, double* rgb) {
+    auto* s = static_cast<Scene*>(p);
+    orc_material m{};
+    m.type = ORC_MAT_LAMBERTIAN; m.tex = k + 1;
+    for (uint64_t i = 0; i < n; ++i) {
+        V3 c = s->colour(m, uvp[5 * i], uvp[5 * i + 1], {uvp[5 * i + 2], uvp[5 * i + 3], uvp[5 * i + 4]});
+        rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+    }
 }
 void port_scene_destroy(void* p) { delete static_cast<Scene*>(p); }
 uint64_t port_bvh_node_count(void* p) { return static_cast<Scene*>(p)->nodes.size(); }

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstring>
 #include <cstdlib>
 #include <filesystem>
 #include <fstream>
@@ -32,6 +33,7 @@
 #include <string>
 #include <thread>
 #include <vector>
+#include <unistd.h>
 
 #define private public
 #include "main.h"
@@ -62,6 +64,8 @@ class id_triangle : public triangle {
 };
 
 struct ref_scene {
+    std::vector<shared_ptr<texture>> textures;   // the reference's own texture objects (scene_create_tex)
+    std::vector<orc_texture> tex_desc;
     triangle_collection world;
     triangle_collection lights;
     std::vector<shared_ptr<material>> mats;
@@ -70,8 +74,12 @@ struct ref_scene {
     uint64_t nodes = 0;
 };
 
-shared_ptr<material> make_mat(const orc_material& m) {
+shared_ptr<material> make_mat(const orc_material& m, const std::vector<shared_ptr<texture>>* textures = nullptr) {
     color c(m.rgb[0], m.rgb[1], m.rgb[2]);
+    if (textures && m.tex > 0 && m.tex <= textures->size()) {   // material.h:45,136: the texture constructors
+        if (m.type == ORC_MAT_LAMBERTIAN) return make_shared<lambertian>((*textures)[m.tex - 1]);
+        if (m.type == ORC_MAT_LIGHT) return make_shared<diffuse_light>((*textures)[m.tex - 1]);
+    }
     switch (m.type) {
         case ORC_MAT_LAMBERTIAN: return make_shared<lambertian>(c);
         case ORC_MAT_METAL:      return make_shared<metal>(c, m.param);
@@ -119,10 +127,72 @@ void parallel_for(uint64_t n, int nthreads, F f) {
 
 extern "C" {
 
+static void* create_scene(const double* v, const uint32_t* mat_id, uint64_t n, const orc_material* mats, uint32_t n_mats,
+                          const orc_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes);
+
 void* ref_scene_create(const double* v, const uint32_t* mat_id, uint64_t n, const orc_material* mats,
                        uint32_t n_mats) {
+    return create_scene(v, mat_id, n, mats, n_mats, nullptr, 0, nullptr, 0);
+}
+void* ref_scene_create_tex(const double* v, const uint32_t* mat_id, uint64_t n, const orc_material* mats, uint32_t n_mats,
+                           const orc_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes) {
+    return create_scene(v, mat_id, n, mats, n_mats, tex, n_tex, data, data_bytes);
+}
+
+void ref_texture_value(void* p, uint32_t k, uint64_t n, const double* uvp, double* rgb) {
+    auto* s = static_cast<ref_scene*>(p);
+    for (uint64_t i = 0; i < n; ++i) {
+        color c = s->textures[k]->value(uvp[5 * i], uvp[5 * i + 1], point3(uvp[5 * i + 2], uvp[5 * i + 3], uvp[5 * i + 4]));
+        rgb[3 * i] = c.x(); rgb[3 * i + 1] = c.y(); rgb[3 * i + 2] = c.z();
+    }
+}
+
+// what the reference's own objects hold after construction: perlin's tables (perlin.h:62-66) / rtw_image's bytes
+int ref_texture_data(void* p, uint32_t k, void* out) {
+    auto* s = static_cast<ref_scene*>(p);
+    if (k >= s->textures.size()) return -1;
+    if (auto nt = std::dynamic_pointer_cast<noise_texture>(s->textures[k])) {
+        double* rv = static_cast<double*>(out);
+        for (int i = 0; i < 256; ++i) for (int c = 0; c < 3; ++c) rv[3 * i + c] = nt->noise.randvec[i][c];
+        int32_t* pm = reinterpret_cast<int32_t*>(static_cast<unsigned char*>(out) + 256 * 3 * sizeof(double));
+        for (int i = 0; i < 256; ++i) { pm[i] = nt->noise.perm_x[i]; pm[256 + i] = nt->noise.perm_y[i]; pm[512 + i] = nt->noise.perm_z[i]; }
+        return 0;
+    }
+    if (auto it = std::dynamic_pointer_cast<image_texture>(s->textures[k])) {
+        const int w = it->image.width(), h = it->image.height();
+        if (w <= 0 || h <= 0 || !it->image.bdata) return -2;
+        std::memcpy(out, it->image.bdata, size_t(w) * h * 3);
+        return 0;
+    }
+    return -3;
+}
+
+static void* create_scene(const double* v, const uint32_t* mat_id, uint64_t n, const orc_material* mats, uint32_t n_mats,
+                          const orc_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes) {
+    (void)data_bytes;
     auto* s = new ref_scene;
-    for (uint32_t i = 0; i < n_mats; ++i) s->mats.push_back(make_mat(mats[i]));
+    for (uint32_t k = 0; k < n_tex; ++k) {
+        const orc_texture& t = tex[k];
+        color a(t.a[0], t.a[1], t.a[2]), b(t.b[0], t.b[1], t.b[2]);
+        shared_ptr<texture> obj;
+        if (t.type == ORC_TEX_CHECKER) obj = make_shared<checker_texture>(t.scale, a, b);
+        else if (t.type == ORC_TEX_NOISE) obj = make_shared<noise_texture>(t.scale);   // draws its tables from the global RNG
+        else if (t.type == ORC_TEX_IMAGE) {
+            // the reference reads image FILES (rtw_stb_image.h): hand it a binary PPM of the raw RGB bytes
+            char path[128];
+            std::snprintf(path, sizeof path, "/tmp/orc_tex_%ld_%u.ppm", long(::getpid()), k);
+            if (FILE* fp = std::fopen(path, "wb")) {
+                std::fprintf(fp, "P6\n%d %d\n255\n", t.width, t.height);
+                std::fwrite(static_cast<const unsigned char*>(data) + t.data_offset, 1, size_t(t.width) * t.height * 3, fp);
+                std::fclose(fp);
+            }
+            obj = make_shared<image_texture>(path);
+            std::remove(path);
+        } else obj = make_shared<solid_color>(a);
+        s->textures.push_back(obj);
+        s->tex_desc.push_back(t);
+    }
+    for (uint32_t i = 0; i < n_mats; ++i) s->mats.push_back(make_mat(mats[i], &s->textures));
     for (uint64_t i = 0; i < n; ++i) {
         const double* p = v + 9 * i;
         auto mat = s->mats[mat_id[i]];

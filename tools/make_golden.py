@@ -48,11 +48,52 @@ def render_child(name):
     np.save(os.path.join(GOLD, "_tmp_film.npy"), film)
 
 
+TEXTURED_RENDER = (20, 20, 4, 6)
+
+
+def textured_child():
+    """cornell_textured WITHOUT the noise box, so that the render starts at the head of the reference's mt19937 stream
+    (a noise_texture draws its tables from it when it is built, perlin.h:6-14)."""
+    from oracle import oracle as O
+    v, m, mats, cam, texs = ts.cornell_textured(noise=False)
+    tarr, blob = O.make_textures(texs)
+    o = O.Oracle("ref").load(v, m, mats, textures=(tarr, len(texs), blob))
+    W, H, spp, depth = TEXTURED_RENDER
+    np.save(os.path.join(GOLD, "_tmp_film.npy"), o.render(make_camera(W, H, spp, depth, **cam), height=H))
+
+
+def textured_fixture():
+    """What the reference's own texture objects hold and return: the image bytes after rtw_image's float round trip,
+    a noise texture's perlin tables, texture::value at 4,000 points for each texture, and a whole render."""
+    from oracle import oracle as O
+    v, m, mats, cam, texs = ts.cornell_textured(noise=True)
+    tarr, blob = O.make_textures(texs)
+    o = O.Oracle("ref").load(v, m, mats, textures=(tarr, len(texs), blob))
+    image_bytes = o.texture_data(1, 12 * 9 * 3)
+    noise_tables = o.texture_data(3, O.NOISE_BYTES)
+    rng = np.random.default_rng(5)
+    uvp = np.concatenate([rng.uniform(-0.2, 1.2, (4000, 2)), rng.uniform(-50, 600, (4000, 3))], axis=1)
+    values = np.stack([o.texture_value(k, uvp) for k in range(len(texs))])
+    subprocess.check_call([sys.executable, os.path.abspath(__file__), "--textured-child"])
+    film = np.load(os.path.join(GOLD, "_tmp_film.npy"))
+    os.remove(os.path.join(GOLD, "_tmp_film.npy"))
+    np.savez_compressed(os.path.join(GOLD, "cornell_textured.npz"), image_bytes=image_bytes, noise_tables=noise_tables, uvp=uvp,
+                        values=values, film=film, render=np.array(TEXTURED_RENDER))
+    print("cornell_textured", len(v), "tris, film mean", film.mean(), "image bytes changed by the loader:", (image_bytes != texs[1]["data"].reshape(-1)).mean())
+
+
 def main():
     if len(sys.argv) == 3 and sys.argv[1] == "--render-child":
         render_child(sys.argv[2])
         return
+    if len(sys.argv) == 2 and sys.argv[1] == "--textured-child":
+        textured_child()
+        return
+    if len(sys.argv) == 2 and sys.argv[1] == "--textured":
+        textured_fixture()
+        return
     os.makedirs(GOLD, exist_ok=True)
+    textured_fixture()
     for name, mk in SCENES.items():
         v, m, mats, cam = mk()
         o = Oracle("ref").load(v, m, mats)

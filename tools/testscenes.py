@@ -98,6 +98,42 @@ def cornell(spheres=True, sphere_steps=(16, 32), f32_round=False):
     return v, m, mats, cam
 
 
+TEX_SOLID, TEX_CHECKER, TEX_NOISE, TEX_IMAGE = 0, 1, 2, 3
+
+
+def cornell_textured(noise=True):
+    """The Cornell room with the reference's texture classes on it (texture.h:28-87): a checker floor, an
+    image on the back wall (a 12 x 9 procedural RGB pattern, raw bytes), a checker-textured LIGHT, a Perlin-marble box
+    (noise=True) and plain red / green side walls.  Returns (verts, mat_id, mats, cam, textures): mats carry a 4th entry,
+    the 1-based texture index; textures are dicts as oracle.make_textures / Context.set_textures take them."""
+    sb = SceneBuilder()
+    yy, xx = np.mgrid[0:9, 0:12]
+    img = np.stack([(xx * 23 + yy * 7) % 256, (xx * xx * 5 + 40 * yy) % 256, (255 - 20 * xx + 3 * yy * yy) % 256], -1).astype(np.uint8)
+    textures = [dict(type=TEX_CHECKER, a=(.8, .8, .8), b=(.15, .2, .6), scale=60.0),
+                dict(type=TEX_IMAGE, width=12, height=9, data=img),
+                dict(type=TEX_CHECKER, a=(15, 15, 15), b=(15, 6, 2), scale=25.0)]
+    if noise:
+        textures.append(dict(type=TEX_NOISE, scale=0.04))
+
+    def mat(t, rgb, param=0.0, tex=0):
+        sb.mats.append((t, tuple(float(x) for x in rgb), float(param), int(tex)))
+        return len(sb.mats) - 1
+
+    red = mat(LAMB, (.65, .05, .05)); green = mat(LAMB, (.12, .45, .15)); white = mat(LAMB, (.73, .73, .73))
+    floor = mat(LAMB, (.5, .5, .5), tex=1); back = mat(LAMB, (.5, .5, .5), tex=2); light = mat(LIGHT, (15, 15, 15), tex=3)
+    boxm = mat(LAMB, (.73, .73, .73), tex=4 if noise else 0)
+    sb.add(quad((555, 0, 0), (0, 0, 555), (0, 555, 0)), green)
+    sb.add(quad((0, 0, 555), (0, 0, -555), (0, 555, 0)), red)
+    sb.add(quad((0, 555, 0), (555, 0, 0), (0, 0, 555)), white)
+    sb.add(quad((0, 0, 555), (555, 0, 0), (0, 0, -555)), floor)
+    sb.add(quad((555, 0, 555), (-555, 0, 0), (0, 555, 0)), back)
+    sb.add(quad((213, 554, 227), (130, 0, 0), (0, 0, 105)), light)
+    sb.add(box((0, 0, 0), (165, 330, 165), 15.0, (265, 0, 295)), boxm)
+    v, m, mats = sb.done()
+    cam = dict(lookfrom=(278, 278, -800), lookat=(278, 278, 0), vfov=40.0, background=(0, 0, 0))
+    return v, m, mats, cam, textures
+
+
 def unit_room(seed=1, n_blobs=6):
     """1-unit-scale open scene (coffee_machine-like scale): floor, three light quads, random small
     lambertian/metal/glass spheres; non-black background so misses contribute."""
