@@ -19,6 +19,7 @@ BVH_REFERENCE, BVH_FAST = 0, 1
 WEIGHT_REF_SUM, WEIGHT_MIS = 0, 1
 TRACE_CLOSEST, TRACE_ANY, TRACE_DEVICE_PTRS, TRACE_STATS, TRACE_SPLIT = 0, 1, 16, 32, 64
 MISS = 0xFFFFFFFF
+NOALLOC_RGB8_MAX_BYTES = 32 << 20   # BDPT_NOALLOC_RGB8_MAX_BYTES
 
 RAY_DTYPE = np.dtype([("o", "<f8", 3), ("d", "<f8", 3), ("tmin", "<f8"), ("tmax", "<f8")])
 HIT_DTYPE = np.dtype([("t", "<f8"), ("u", "<f8"), ("v", "<f8"), ("prim", "<u4"), ("pad", "<u4")])
@@ -34,6 +35,7 @@ EXPORTS = [
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
     "bdpt_scene_set_textures", "bdpt_scene_file_textures", "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read", "bdpt_comm_attach",
+    "bdpt_film_to_rgb8_noalloc",
 ]
 
 
@@ -132,6 +134,7 @@ def lib():
         L.bdpt_film_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.bdpt_test_filter32.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_double, C.c_int, C.POINTER(C.c_float)]
         L.bdpt_film_to_rgb8.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.bdpt_film_to_rgb8_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.bdpt_stats.argtypes = [C.c_void_p, C.c_void_p]
         L.bdpt_stats_reset.argtypes = [C.c_void_p]
         L.bdpt_last_device_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
@@ -542,6 +545,14 @@ class Context:
     def film_rgb8(self, spp):
         out = np.empty(self.film_shape, np.uint8)
         self._chk(lib().bdpt_film_to_rgb8(self._h, int(spp), out.ctypes.data), "bdpt_film_to_rgb8")
+        return out
+
+    def film_rgb8_noalloc(self, spp, out=None):
+        """bdpt_film_to_rgb8_noalloc: the same bytes through the library's static device scratch (no cudaMalloc);
+        films beyond NOALLOC_RGB8_MAX_BYTES are refused."""
+        if out is None:
+            out = np.empty(self.film_shape, np.uint8)
+        self._chk(lib().bdpt_film_to_rgb8_noalloc(self._h, int(spp), out.ctypes.data), "bdpt_film_to_rgb8_noalloc")
         return out
 
     def stats(self):

@@ -730,6 +730,59 @@ int bdpt_film_to_rgb8(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out) {
     return BDPT_OK;
 }
 
+// ---------------------------------------------------------------- bdpt_film_to_rgb8_noalloc
+// The tone-map's device staging (W*H*3 bytes between k_tonemap and the D2H copy) in a file-scope device array instead of a
+// cudaMalloc per call: for callers that may not allocate (CUDA graph capture around them, serving loops, harnesses that
+// forbid cudaMalloc).  Every GPU that loads libbdpt holds the array until exit.  All calls on a device share it and it
+// keeps the last call's bytes: nothing has to start at zero (k_tonemap writes every byte of [0, W*H*3) before the copy
+// reads it), but two calls that overlap on the GPU race on it.
+static __device__ __align__(256) unsigned char g_rgb8_scratch[BDPT_NOALLOC_RGB8_MAX_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::atomic<unsigned char*> g_rgb8_scratch_dev[kMaxDevices];   // device address of g_rgb8_scratch, per device ordinal
+
+// In host code `g_rgb8_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress with the device current.  Looked up once per device.
+int rgb8_scratch_for(bdpt_ctx* ctx, unsigned char** out) {
+    if (ctx->device < 0 || ctx->device >= kMaxDevices) { ctx->err = "device ordinal beyond the no-alloc scratch table"; return BDPT_ERR_ARG; }
+    unsigned char* p = g_rgb8_scratch_dev[ctx->device].load(std::memory_order_acquire);
+    if (!p) {
+        BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+        void* sym = nullptr;
+        BDPT_CUDA(ctx, cudaGetSymbolAddress(&sym, g_rgb8_scratch));
+        if (!sym) { ctx->err = "cudaGetSymbolAddress returned a null scratch address"; return BDPT_ERR_CUDA; }
+        p = static_cast<unsigned char*>(sym);
+        g_rgb8_scratch_dev[ctx->device].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return BDPT_OK;
+}
+}  // namespace
+
+int bdpt_film_to_rgb8_noalloc(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out) {
+    if (!ctx || !out) return BDPT_ERR_ARG;
+    if (!ctx->film) { ctx->err = "no film"; return BDPT_ERR_STATE; }
+    const uint64_t n = uint64_t(ctx->film_w) * ctx->film_h * 3;
+    if (n > uint64_t(BDPT_NOALLOC_RGB8_MAX_BYTES)) {
+        ctx->err = "bdpt_film_to_rgb8_noalloc: film of " + std::to_string(ctx->film_w) + " x " + std::to_string(ctx->film_h) + " needs " +
+                   std::to_string(n) + " bytes of staging, the static scratch holds " + std::to_string(uint64_t(BDPT_NOALLOC_RGB8_MAX_BYTES)) +
+                   " (BDPT_NOALLOC_RGB8_MAX_BYTES); use bdpt_film_to_rgb8";
+        return BDPT_ERR_ARG;
+    }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned char* d = nullptr;
+    if (int rc = rgb8_scratch_for(ctx, &d)) return rc;
+    const double scale = 1.0 / double(samples_per_pixel > 1 ? samples_per_pixel : 1);  // wpng.h:18
+    k_tonemap<<<unsigned((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->film, n, scale, d);
+    ctx->launches += 1;
+    BDPT_CUDA(ctx, cudaGetLastError());
+    cudaError_t e = cudaMemcpyAsync(out, d, n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { ctx->err = std::string("tonemap (no-alloc): ") + cudaGetErrorString(e); return BDPT_ERR_CUDA; }
+    return BDPT_OK;
+}
+
 int bdpt_render(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* opts) {
     if (!ctx || !cam) return BDPT_ERR_ARG;
     if (!ctx->have_scene) { ctx->err = "no scene uploaded"; return BDPT_ERR_STATE; }

@@ -226,6 +226,16 @@ int bdpt_film_download(bdpt_ctx* ctx, double* film_sum /* W*H*3 */);
 int bdpt_film_size(bdpt_ctx* ctx, int* width, int* height);
 /* wpng.h:14-35 on the device film: average, clamp [0,0.999], sqrt, 256x truncate. out: W*H*3 bytes (host) */
 int bdpt_film_to_rgb8(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as bdpt_film_to_rgb8, byte
+ * for byte, but the W*H*3 bytes of device staging between the tone-map kernel and the copy to `out` live in a static
+ * device array of BDPT_NOALLOC_RGB8_MAX_BYTES (32 MiB: up to 3840 x 2160; held by every GPU that loads the library
+ * until exit) instead of a cudaMalloc/cudaFree pair per call: the call allocates nothing on the device or the host.
+ * A film larger than the limit is refused with BDPT_ERR_ARG and a message naming both sizes.  All calls on a device
+ * share the array, which keeps the previous call's bytes (none of them is read: every byte is written before the copy);
+ * calls that overlap on the GPU -- two contexts of one device from two threads -- race on it: serialise them. */
+#define BDPT_NOALLOC_RGB8_MAX_BYTES (32u << 20)
+int bdpt_film_to_rgb8_noalloc(bdpt_ctx* ctx, int samples_per_pixel, uint8_t* out);
 
 /* ---- the film reduce: the one exchange step of a multi-GPU frame.  Every rank renders its strata
  * (bdpt_render_opts.stratum_begin / stratum_step) into its own film; ONE ncclReduce(sum, fp64) over NVLink then adds
