@@ -80,6 +80,7 @@ class SceneImageInfo(C.Structure):
 
 
 IMAGE_VERIFY = 1
+IMAGE_TRUSTED = 2
 RENDER_STATS = 1
 RENDER_SERIAL = 2
 UPLOAD_FAST_TREE_GPU = 1
@@ -278,9 +279,9 @@ class SceneImage:
         a = np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
         return cls(a.ctypes.data, a.nbytes, "borrowed", keep=a)
 
-    def info(self, verify=False):
+    def info(self, verify=False, validate=False):
         i = SceneImageInfo()
-        if lib().bdpt_scene_image_info(C.c_void_p(self.ptr), self.nbytes, 1 if verify else 0, C.byref(i)):
+        if lib().bdpt_scene_image_info(C.c_void_p(self.ptr), self.nbytes, (1 if verify else 0) | (2 if validate else 0), C.byref(i)):
             raise BdptError(lib().bdpt_scene_image_last_error().decode())
         return {n: int(getattr(i, n)) for n, _ in SceneImageInfo._fields_}
 
@@ -450,9 +451,15 @@ class Context:
                                                 blob.ctypes.data if textures else None, len(blob) if textures else 0), "bdpt_scene_set_textures")
         return self
 
-    def upload_image(self, image, verify=False):
-        """bdpt_scene_upload_image: one allocation + one host-to-device copy of a prebuilt SceneImage."""
-        self._chk(lib().bdpt_scene_upload_image(self._h, C.c_void_p(image.ptr), image.nbytes, IMAGE_VERIFY if verify else 0),
+    def upload_image(self, image, verify=None, trusted=None):
+        """bdpt_scene_upload_image: one allocation + one host-to-device copy of a prebuilt SceneImage.  verify: check the
+        payload hash first (default: for images mapped from files); trusted: skip the range check of the payload's
+        links and indices (default: only for images built by this process)."""
+        kind = getattr(image, "_kind", "borrowed")
+        verify = (kind == "mapped") if verify is None else verify
+        trusted = (kind == "built") if trusted is None else trusted
+        self._chk(lib().bdpt_scene_upload_image(self._h, C.c_void_p(image.ptr), image.nbytes,
+                                                (IMAGE_VERIFY if verify else 0) | (IMAGE_TRUSTED if trusted else 0)),
                   "bdpt_scene_upload_image")
         self.n_tris = image.info()["n_tris"]
         return self

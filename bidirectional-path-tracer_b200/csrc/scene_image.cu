@@ -122,6 +122,49 @@ const ImageHeader* check_image(const void* image, uint64_t bytes, bool verify, s
     return h;
 }
 
+// One linear pass over the payload: every index a kernel follows must stay inside its array.  The header check above
+// only ties the section SIZES to the counts; a bit-rotted or crafted file that passes it would otherwise send the walk
+// to wild addresses (a device fault an operator has to clear).  ~1 ms per million triangles.
+template <class T> const T* sec(const ImageHeader* h, int s) { return reinterpret_cast<const T*>(reinterpret_cast<const unsigned char*>(h) + h->sec[s].off); }
+bool validate_payload(const ImageHeader* h, std::string& why) {
+    const uint64_t n = h->n_tris;
+    auto bad = [&](const char* what) { why = std::string("scene image: ") + what + " out of range (corrupt payload)"; return false; };
+    auto leaf_ok = [&](int32_t c) { const uint32_t code = uint32_t(~c); return uint64_t(code >> 3) + (code & 7u) + 1u <= n; };
+    const FastNode* fn = sec<FastNode>(h, SEC_FAST_NODES);
+    for (uint32_t i = 0; i < h->n_fast_nodes; ++i)
+        for (int32_t c : {fn[i].left, fn[i].right})
+            if (c >= 0 ? uint32_t(c) >= h->n_fast_nodes : !leaf_ok(c)) return bad("fast-tree link");
+    const WideNode* wn = sec<WideNode>(h, SEC_WIDE_NODES);
+    for (uint32_t i = 0; i < h->n_wide_nodes; ++i)
+        for (int32_t c : wn[i].child)
+            if (c != kWideEmpty && (c >= 0 ? uint32_t(c) >= h->n_wide_nodes : !leaf_ok(c))) return bad("wide-tree link");
+    const RefNode* rn = sec<RefNode>(h, SEC_REF_NODES);
+    const int32_t* parent = sec<int32_t>(h, SEC_REF_PARENT);
+    for (uint32_t i = 0; i < h->n_ref_nodes; ++i) {
+        const uint64_t lim = rn[i].leaf ? n : h->n_ref_nodes;
+        if (rn[i].left < 0 || rn[i].right < 0 || uint64_t(rn[i].left) >= lim || uint64_t(rn[i].right) >= lim) return bad("reference-tree link");
+        if (parent[i] < -1 || parent[i] >= int64_t(h->n_ref_nodes)) return bad("reference-tree parent");
+    }
+    const TriGeom* tris = sec<TriGeom>(h, SEC_TRIS);
+    const TriGeom* ftris = sec<TriGeom>(h, SEC_FAST_TRIS);
+    const TriShade* shade = sec<TriShade>(h, SEC_SHADE);
+    const uint32_t* fprims = sec<uint32_t>(h, SEC_FAST_PRIMS);
+    const uint32_t* rank = sec<uint32_t>(h, SEC_DFS_RANK);
+    const int32_t* pleaf = sec<int32_t>(h, SEC_PRIM_LEAF);
+    const uint32_t* order = sec<uint32_t>(h, SEC_LEAF_ORDER);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (tris[i].mat >= h->n_mats || ftris[i].mat >= h->n_mats || shade[i].mat >= h->n_mats) return bad("material id");
+        if (fprims[i] >= n || order[i] >= n) return bad("prim id");
+        if (rank[i] >= 2 * n) return bad("DFS rank");   // a span-1 leaf lists its triangle twice (bvh.h:35-39)
+        if (pleaf[i] < 0 || uint32_t(pleaf[i]) >= h->n_ref_nodes) return bad("prim leaf");
+    }
+    const uint32_t* lights = sec<uint32_t>(h, SEC_LIGHTS);
+    for (uint32_t i = 0; i < h->n_lights; ++i) if (lights[i] >= n) return bad("light id");
+    const Mat* mats = sec<Mat>(h, SEC_MATS);
+    for (uint32_t i = 0; i < h->n_mats; ++i) if (mats[i].type > BDPT_MAT_LIGHT) return bad("material class");
+    return true;
+}
+
 template <class T>
 void put(unsigned char* base, const ImageHeader& h, int s, const std::vector<T>& v) {
     if (v.size() * sizeof(T) != h.sec[s].bytes) throw std::runtime_error("scene image: internal section size mismatch");
@@ -193,7 +236,8 @@ const char* bdpt_scene_image_last_error(void) { return g_image_err.c_str(); }
 
 int bdpt_scene_image_info(const void* image, uint64_t bytes, int verify, bdpt_scene_image_info_t* out) {
     std::string why;
-    const ImageHeader* h = check_image(image, bytes, verify != 0, why);
+    const ImageHeader* h = check_image(image, bytes, (verify & 1) != 0, why);
+    if (h && (verify & 2) && !validate_payload(h, why)) h = nullptr;
     if (!h) { g_image_err = why; return BDPT_ERR_ARG; }
     if (out) {
         out->n_tris = h->n_tris; out->n_mats = h->n_mats; out->n_lights = h->n_lights;
@@ -207,30 +251,36 @@ int bdpt_scene_image_info(const void* image, uint64_t bytes, int verify, bdpt_sc
 
 int bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, uint32_t flags) {
     if (!ctx) return BDPT_ERR_ARG;
-    if (flags & ~BDPT_IMAGE_VERIFY) { ctx->err = "unknown image upload flags"; return BDPT_ERR_ARG; }
+    if (flags & ~(BDPT_IMAGE_VERIFY | BDPT_IMAGE_TRUSTED)) { ctx->err = "unknown image upload flags"; return BDPT_ERR_ARG; }
     const bool timing = std::getenv("BDPT_TIMING") != nullptr;
     const auto t0 = std::chrono::steady_clock::now();
     std::string why;
     const ImageHeader* h = check_image(image, bytes, (flags & BDPT_IMAGE_VERIFY) != 0, why);
     if (!h) { ctx->err = why; return BDPT_ERR_ARG; }
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
-    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    for (void* p : ctx->scene_allocs) cudaFree(p);
-    ctx->scene_allocs.clear();
-    ctx->have_scene = false;
-
+    // The new block is allocated and its copy started BEFORE the resident scene is touched: the payload's range check
+    // runs on the host while the copy is in flight, and a refused image leaves the old scene in place.
     const unsigned char* src = static_cast<const unsigned char*>(image);
     const uint64_t dev_bytes = h->sec[SEC_LEAF_ORDER].off - sizeof(ImageHeader);
     unsigned char* d = nullptr;
     BDPT_CUDA(ctx, cudaMalloc(&d, dev_bytes));
-    ctx->scene_allocs.push_back(d);
     cudaError_t e = cudaMemcpyAsync(d, src + sizeof(ImageHeader), dev_bytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e != cudaSuccess) {
         cudaFree(d);
-        ctx->scene_allocs.clear();
         ctx->err = std::string("cudaMemcpyAsync(scene image): ") + cudaGetErrorString(e);
         return BDPT_ERR_CUDA;
     }
+    if (!(flags & BDPT_IMAGE_TRUSTED) && !validate_payload(h, why)) {   // every link and index must stay inside its array
+        cudaStreamSynchronize(ctx->stream);
+        cudaFree(d);
+        ctx->err = why;
+        return BDPT_ERR_ARG;
+    }
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // the copy, and whatever still read the old scene
+    for (void* p : ctx->scene_allocs) cudaFree(p);
+    ctx->scene_allocs.clear();
+    ctx->have_scene = false;
+    ctx->scene_allocs.push_back(d);
     auto at = [&](int s) { return d + (h->sec[s].off - sizeof(ImageHeader)); };
     SceneView v{};
     v.tris = reinterpret_cast<const TriGeom*>(at(SEC_TRIS));

@@ -14,6 +14,13 @@
 
 namespace bdpt {
 
+// The inline fallback to the reference traversal reuses the caller's StackEntry array as int32 slots.  A thread-private
+// stack (stride 1: every caller today) is contiguous, so all 2 x levels int32 slots are usable -- the reference tree may
+// be up to kRefStackLevels - 1 deep, more than the StackEntry count; a column of a [levels][blockDim] array can only
+// use the first word of every entry.
+__device__ __forceinline__ int ref_stride(int stride) { return stride == 1 ? 1 : 2 * stride; }
+
+
 // One slab of a child box in scalar type T (float on the normal path, double for rays whose origin is so
 // far outside the scene that fp32 would eat the outward padding).  NaN (0 * inf, origin exactly on a slab
 // plane of a zero-direction axis) is dropped by fmin/fmax, which keeps the slab: conservative.
@@ -220,7 +227,7 @@ __device__ __forceinline__ int traverse_fast_t(const SceneView& sc, const RayD& 
         return found ? TR_HIT : TR_MISS;
     }
     if (DEFER) return TR_DEFER;
-    return traverse_ref<ANY, STATS>(sc, r, hit, reinterpret_cast<int32_t*>(stack), 2 * stride, st) ? TR_HIT : TR_MISS;
+    return traverse_ref<ANY, STATS>(sc, r, hit, reinterpret_cast<int32_t*>(stack), ref_stride(stride), st) ? TR_HIT : TR_MISS;
 }
 
 // Entry point: picks the arithmetic of the box tests.
@@ -232,7 +239,7 @@ __device__ __forceinline__ int traverse_fast(const SceneView& sc, const RayD& r,
                                              int stride, TravStats* st, uint32_t limit = 0) {
     if (r.d.x == 0.0 || r.d.y == 0.0 || r.d.z == 0.0) {
         if (DEFER) return TR_DEFER;
-        return traverse_ref<ANY, STATS>(sc, r, hit, reinterpret_cast<int32_t*>(stack), 2 * stride, st) ? TR_HIT : TR_MISS;
+        return traverse_ref<ANY, STATS>(sc, r, hit, reinterpret_cast<int32_t*>(stack), ref_stride(stride), st) ? TR_HIT : TR_MISS;
     }
     const double far = 8.0 * sc.extent;
     const bool near_scene = fabs(r.o.x - sc.center.x) <= far && fabs(r.o.y - sc.center.y) <= far && fabs(r.o.z - sc.center.z) <= far &&

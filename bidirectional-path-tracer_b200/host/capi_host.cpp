@@ -5,6 +5,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -104,11 +105,23 @@ int bdpt_write_png(const char* path, const uint8_t* rgb, int width, int height) 
 
 int bdpt_scene_image_save(const char* path, const void* image, uint64_t bytes) {
     if (!path || !image || !bytes) return BDPT_ERR_ARG;
-    const std::string tmp = std::string(path) + ".tmp";
-    std::FILE* fp = std::fopen(tmp.c_str(), "wb");
-    if (!fp) { g_host_err = "cannot write " + tmp; return BDPT_ERR_ARG; }
-    const bool ok = std::fwrite(image, 1, bytes, fp) == bytes;
-    if (std::fclose(fp) != 0 || !ok || std::rename(tmp.c_str(), path) != 0) {
+    // A temporary file of this call's own: several ranks or processes that miss the same cache at once must not
+    // truncate each other's half-written file (a reader maps with MAP_POPULATE and would take a SIGBUS).  The last
+    // rename wins; every one of them publishes a complete image of the same sources.
+    static std::atomic<unsigned> serial{0};
+    const std::string tmp = std::string(path) + "." + std::to_string(long(::getpid())) + "." + std::to_string(serial.fetch_add(1)) + ".tmp";
+    const int fd = ::open(tmp.c_str(), O_WRONLY | O_CREAT | O_EXCL, 0644);
+    if (fd < 0) { g_host_err = "cannot write " + tmp; return BDPT_ERR_ARG; }
+    const unsigned char* p = static_cast<const unsigned char*>(image);
+    uint64_t left = bytes;
+    bool ok = true;
+    while (left && ok) {
+        const ssize_t w = ::write(fd, p, size_t(std::min<uint64_t>(left, uint64_t(1) << 30)));
+        if (w <= 0) ok = false; else { p += w; left -= uint64_t(w); }
+    }
+    if (ok && ::fsync(fd) != 0) ok = false;
+    if (::close(fd) != 0) ok = false;
+    if (!ok || std::rename(tmp.c_str(), path) != 0) {
         std::remove(tmp.c_str());
         g_host_err = std::string("cannot write ") + path;
         return BDPT_ERR_ARG;

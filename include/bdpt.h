@@ -191,10 +191,15 @@ typedef struct {
 int  bdpt_scene_image_build(const double* verts, const uint32_t* mat_id, uint64_t n_tris, const bdpt_material* mats,
                             uint32_t n_mats, uint64_t source_key, void** image, uint64_t* bytes);
 void bdpt_scene_image_free(void* image);
-/* Header / section-table checks (always) and the payload hash (verify != 0); out may be NULL. */
+/* Header / section-table checks (always); verify & 1: the payload hash; verify & 2: the range check of every link and
+ * index in the payload (what bdpt_scene_upload_image runs unless told BDPT_IMAGE_TRUSTED); out may be NULL. */
 int  bdpt_scene_image_info(const void* image, uint64_t bytes, int verify, bdpt_scene_image_info_t* out);
 const char* bdpt_scene_image_last_error(void);
-#define BDPT_IMAGE_VERIFY 1u   /* check the payload hash before copying (one pass over the image on the host) */
+#define BDPT_IMAGE_VERIFY 1u   /* check the payload hash before copying (one pass over the image on the host); the file
+                                  front-end (bdpt_scene_file_open_cached, bdpt --cache) checks it when it opens the file */
+#define BDPT_IMAGE_TRUSTED 2u  /* skip the range check of the payload's links and indices (tree links, prim / material / light
+                                  ids), which otherwise runs on the host while the copy is in flight (~1 ms per 30 k triangles):
+                                  only for an image this process has just built itself */
 /* image: host memory, 8-byte aligned (pinned memory makes the copy faster); may be freed on return. */
 int  bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, uint32_t flags);
 /* DFS leaf order of the BDPT_BVH_REFERENCE build: order[k] = prim ID (n_tris entries) */
@@ -280,7 +285,8 @@ int  bdpt_scene_file_copy(const bdpt_scene_file* f, double* verts, uint32_t* mat
  * image -- an extension of the reference's schema, host/scene_loader.cpp).  Call with tex = data = NULL for the sizes. */
 int  bdpt_scene_file_textures(const bdpt_scene_file* f, uint32_t* n_tex, bdpt_texture* tex, uint64_t* data_bytes, void* data);
 int  bdpt_write_png(const char* path, const uint8_t* rgb, int width, int height);
-/* Scene-image files: save writes to "<path>.tmp" and renames; map gives a read-only mapping of the file
+/* Scene-image files: save writes to a temporary file of its own beside `path` ("<path>.<pid>.<n>.tmp"), syncs it and
+ * renames it over `path`, so concurrent savers (ranks missing the same cache) never write into each other's file; map gives a read-only mapping of the file
  * (page cache backed: nothing is copied until the upload reads it). */
 int  bdpt_scene_image_save(const char* path, const void* image, uint64_t bytes);
 int  bdpt_scene_image_map(const char* path, const void** image, uint64_t* bytes);

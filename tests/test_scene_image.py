@@ -213,6 +213,76 @@ def test_image_upload_renders_the_same_film(bdpt, gpu_ctx, scenes, tmp_path):
     assert rel_err(gpu_ctx.film(), ref_film) < 1e-12
 
 
+def corrupt_fast_link(good):
+    """One FastNode child link sent far outside the tree; the payload hash is left stale (a caller that does not ask for
+    the hash check must still be stopped by the range check)."""
+    import struct
+    bad = good.copy()
+    off = struct.unpack_from("<Q", bad, 128 + 16 * 5)[0]        # section table (header offset 128), SEC_FAST_NODES = 5
+    bad[off + 48:off + 52] = np.frombuffer(np.int32(0x7FFFFF00).tobytes(), np.uint8)   # node 0, left link (after 12 floats)
+    return bad
+
+
+def test_image_range_check_catches_wild_links(bdpt):
+    """links / prim / material / light ids of the payload are range-checked (bdpt_scene_image_info verify & 2,
+    and every bdpt_scene_upload_image without BDPT_IMAGE_TRUSTED)."""
+    import struct
+    v, m, mats = soup(500)
+    with bdpt.SceneImage.build(v, m, mats) as img:
+        good = img.bytes()
+        assert img.info(verify=True, validate=True)["n_tris"] == 500
+    bad = corrupt_fast_link(good)
+    assert bdpt.SceneImage.from_bytes(bad).info()["n_tris"] == 500          # header and section table are intact
+    with pytest.raises(bdpt.BdptError, match="fast-tree link out of range"):
+        bdpt.SceneImage.from_bytes(bad).info(validate=True)
+    bad = good.copy()
+    off = struct.unpack_from("<Q", bad, 128 + 16 * 0)[0]                    # SEC_TRIS: TriGeom.mat at byte 72
+    bad[off + 72:off + 76] = np.frombuffer(np.uint32(77).tobytes(), np.uint8)
+    with pytest.raises(bdpt.BdptError, match="material id out of range"):
+        bdpt.SceneImage.from_bytes(bad).info(validate=True)
+    bad = good.copy()
+    off = struct.unpack_from("<Q", bad, 128 + 16 * 3)[0]                    # SEC_LIGHTS
+    bad[off:off + 4] = np.frombuffer(np.uint32(500).tobytes(), np.uint8)
+    with pytest.raises(bdpt.BdptError, match="light id out of range"):
+        bdpt.SceneImage.from_bytes(bad).info(validate=True)
+
+
+def test_concurrent_savers_do_not_tear_the_cache_file(bdpt, tmp_path):
+    """several ranks missing the same cache at once each write a temporary file of their own."""
+    import threading
+    v, m, mats = soup(2000)
+    path = str(tmp_path / "shared.bdptimg")
+    with bdpt.SceneImage.build(v, m, mats) as img:
+        good = img.bytes()
+        errs = []
+        def save():
+            try:
+                for _ in range(5):
+                    img.save(path)
+                    with bdpt.SceneImage.map(path) as mp:
+                        assert mp.info(verify=True)["n_tris"] == 2000
+            except Exception as e:   # noqa: BLE001
+                errs.append(e)
+        ts = [threading.Thread(target=save) for _ in range(6)]
+        [t.start() for t in ts]; [t.join() for t in ts]
+    assert not errs
+    assert sorted(os.listdir(tmp_path)) == ["shared.bdptimg"]               # no temporary file left behind
+    assert np.array_equal(np.fromfile(path, np.uint8), good)
+
+
+@pytest.mark.gpu
+def test_image_upload_refuses_wild_links_and_keeps_the_old_scene(bdpt, gpu_ctx, scenes, golden):
+    g = golden("cornell_box")
+    v, m, mats, cam = scenes["cornell_box"]()
+    gpu_ctx.upload(v, m, mats)
+    with bdpt.SceneImage.build(v, m, mats) as img:
+        bad = corrupt_fast_link(img.bytes())
+    with pytest.raises(bdpt.BdptError, match="out of range"):
+        gpu_ctx.upload_image(bdpt.SceneImage.from_bytes(bad), verify=False)   # no hash check asked for: the range check stops it
+    h = gpu_ctx.trace(g["rays"], bvh=bdpt.BVH_FAST)
+    check_hits(h, g["prim"], g["t"], g["u"], g["v"], exact=True)
+
+
 @pytest.mark.gpu
 def test_image_upload_refuses_damage_and_keeps_the_old_scene(bdpt, gpu_ctx, scenes, golden):
     g = golden("cornell_box")
