@@ -9,11 +9,22 @@
 // answers are those of traverse_fast_t<.., float>; rays that need fp64 slabs or the reference tree are
 // not started here at all (walk_eligible) and go to the deferred list.
 #pragma once
+#include "prefilter32.cuh"
 #include "traverse_fast.cuh"
 
 namespace bdpt {
 
 enum { WALK_YIELD = -1 };
+
+// -DBDPT_PREFILTER=1: leaf_tests rejects triangles with the conservative fp32 pre-filter (prefilter32.cuh) before the
+// reference's fp64 test (most triangles of a visited leaf are misses; ~35 full-rate fp32 instructions against ~80 half-rate
+// fp64 ones).  Parity-green (the filter only rejects what the exact test rejects, or what lies beyond the bound / before
+// tmin by far more than the flagging bands), but MEASURED SLOWER and therefore off: bench step 21.85 -> 23.3 ms, shadow
+// stage +12 %, config-2-style batch 2,604 -> 2,486 Mrays/s (profiles/r2_rejected_experiments.txt).  The walk waits on
+// dependent loads, not on issue slots: the filter's 48-byte record is one more load in front of the 80-byte one.
+#ifndef BDPT_PREFILTER
+#define BDPT_PREFILTER 0
+#endif
 
 // fp32 slabs are valid for this ray (see traverse_fast): no zero direction component, origin and scene
 // within 8 extents of each other and of the world origin
@@ -41,6 +52,9 @@ struct Walk {
     float ox, oy, oz, ix, iy, iz, tmin_t, best_t;   // ox.. hold -o * inv: one FMA per slab plane
     float cull_hi;     // upper end of the part of the ray this walk is responsible for (split walks), else FLT_MAX
     uint32_t work;     // nodes + triangles touched so far
+#if BDPT_PREFILTER
+    float kD, kU, kT;  // error scales of the fp32 pre-filter for this ray (make_ray32)
+#endif
     double best, band_abs;
     // answer so far
     HitD hit;
@@ -68,6 +82,14 @@ struct Walk {
         cull_hi = cull_hi_;
         best = r.tmax;
         best_t = fminf(__double2float_ru(best), cull_hi);
+#if BDPT_PREFILTER
+        {
+            const float fx = float(r.d.x), fy = float(r.d.y), fz = float(r.d.z);
+            const float dn = __double2float_ru(sqrt(double(fx) * fx + double(fy) * fy + double(fz) * fz) * 1.000001);
+            const float rho = fmaxf(fabsf(float(r.o.x)), fmaxf(fabsf(float(r.o.y)), fabsf(float(r.o.z)))) * 1.000001f + sc.vmax32;
+            kD = kFilterK * dn; kU = kFilterK * rho * dn; kT = kFilterK * rho;
+        }
+#endif
         work = 0;
         found = false; flagged = false;
         sp = 0; cur = 0; pend = 0;
@@ -209,8 +231,19 @@ __device__ __forceinline__ int Walk<ANY, STATS>::run4(const SceneView& sc, Stack
 
 template <bool ANY, bool STATS>
 __device__ __forceinline__ bool Walk<ANY, STATS>::leaf_tests(const SceneView& sc, uint32_t first, uint32_t cnt) {
+#if BDPT_PREFILTER
+    const float fox = float(r.o.x), foy = float(r.o.y), foz = float(r.o.z), fdx = float(r.d.x), fdy = float(r.d.y), fdz = float(r.d.z);
+    const float f_tmin = __double2float_rd(r.tmin), f_best = __double2float_ru(ANY ? r.tmax : best);   // the RAY's interval, not a split walk's part
+#endif
     for (uint32_t k = 0; k < cnt; ++k) {
         if (STATS) ++ts.tris;
+#if BDPT_PREFILTER
+        if (sc.tris32) {
+            const Tri32* T = sc.tris32 + first + k;
+            const float4 q0 = __ldg(&T->q0), q1 = __ldg(&T->q1), q2 = __ldg(&T->q2);
+            if (prefilter_rejects(fox, foy, foz, fdx, fdy, fdz, f_tmin, f_best, kD, kU, kT, q0, q1, q2)) continue;
+        }
+#endif
         double t, u, v;
         if (!tri_candidate(sc.fast_tris + first + k, r.o, r.d, t, u, v)) continue;
         const uint32_t prim = __ldg(sc.fast_prims + first + k);   // only candidates need their id
