@@ -23,6 +23,37 @@ void check(int rc, bdpt_ctx* ctx, const char* what) {
 }
 }  // namespace
 
+// hittable.h:81-84: the angle's sine and cosine, once
+rotate_y::rotate_y(shared_ptr<hittable> obj, double angle_degrees) : object(std::move(obj)) {
+    const double radians = angle_degrees * 3.1415926535897932385 / 180.0;   // degrees_to_radians, main.h:24-26
+    sin_theta = std::sin(radians);
+    cos_theta = std::cos(radians);
+}
+
+void collect_triangles(const hittable& h, std::vector<triangle>& out) {
+    if (auto t = dynamic_cast<const triangle*>(&h)) { out.push_back(*t); return; }
+    if (auto c = dynamic_cast<const triangle_collection*>(&h)) { out.insert(out.end(), c->tris.begin(), c->tris.end()); return; }
+    if (auto b = dynamic_cast<const bvh_node*>(&h)) { out.insert(out.end(), b->prims.begin(), b->prims.end()); return; }
+    if (auto l = dynamic_cast<const hittable_list*>(&h)) { for (const auto& o : l->objects) collect_triangles(*o, out); return; }
+    const size_t first = out.size();
+    if (auto tr = dynamic_cast<const translate*>(&h)) {
+        collect_triangles(*tr->object, out);
+        for (size_t i = first; i < out.size(); ++i)
+            for (point3* p : {&out[i].v0, &out[i].v1, &out[i].v2})   // hittable.h:64: rec.p += offset
+                *p = point3(p->x() + tr->offset.x(), p->y() + tr->offset.y(), p->z() + tr->offset.z());
+        return;
+    }
+    if (auto ro = dynamic_cast<const rotate_y*>(&h)) {
+        collect_triangles(*ro->object, out);
+        const double c = ro->cos_theta, s = ro->sin_theta;
+        for (size_t i = first; i < out.size(); ++i)
+            for (point3* p : {&out[i].v0, &out[i].v1, &out[i].v2})   // object -> world, hittable.h:134-138
+                *p = point3((c * p->x()) + (s * p->z()), p->y(), (-s * p->x()) + (c * p->z()));
+        return;
+    }
+    throw std::runtime_error("collect_triangles: unknown hittable (triangle, triangle_collection, hittable_list, bvh_node, translate, rotate_y)");
+}
+
 void print_bvh_stats(std::ostream& os, const render_report& r) {   // stats.h:34-50, same lines
     os << "\nBVH Stats:\n";
     os << "  Rays traced:         " << r.rays_closest << "\n";
@@ -35,9 +66,10 @@ void print_bvh_stats(std::ostream& os, const render_report& r) {   // stats.h:34
 void camera::render(const hittable& world, const hittable& lights) {
     (void)lights;
     const std::vector<triangle>* prims = nullptr;
+    std::vector<triangle> collected;
     if (auto b = dynamic_cast<const bvh_node*>(&world)) prims = &b->prims;
     else if (auto t = dynamic_cast<const triangle_collection*>(&world)) prims = &t->tris;
-    if (!prims) throw std::runtime_error("camera::render: world must be a bvh_node or a triangle_collection");
+    else { collect_triangles(world, collected); prims = &collected; }   // hittable_list, translate, rotate_y (hittable.h:46-157)
     bool from_image = options.scene_image != nullptr;
     const void* image = options.scene_image;
     uint64_t image_bytes = options.scene_image_bytes;

@@ -135,14 +135,34 @@ class triangle_collection : public hittable {
     }
 };
 
+// Instancing (hittable.h:46-157).  The reference moves the RAY into the object's frame at every hit query; here the
+// wrapped object's triangles are moved into the world frame ONCE, when the scene is flattened (collect_triangles): the
+// device walks one tree of world-space triangles and pays nothing per ray.  Same geometry, not the same rounding: hit
+// distances agree with the reference's ray-transform form to ~1e-12 relative, prim IDs except on knife edges
+// (tests/test_instancing.py).  translate(rotate_y(obj, deg), offset) is the usual order.
+class translate : public hittable {      // hittable.h:46-77
+  public:
+    translate(shared_ptr<hittable> obj, const vec3& off) : object(std::move(obj)), offset(off) {}
+    shared_ptr<hittable> object;
+    vec3 offset;
+};
+class rotate_y : public hittable {       // hittable.h:79-157 (angle in degrees, counter-clockwise seen from +y)
+  public:
+    rotate_y(shared_ptr<hittable> obj, double angle_degrees);
+    shared_ptr<hittable> object;
+    double sin_theta, cos_theta;
+};
+// the triangles of any object graph (triangle, triangle_collection, hittable_list, bvh_node, translate, rotate_y), in
+// traversal order (= prim ID), in world space; throws on a hittable it does not know
+void collect_triangles(const hittable& h, std::vector<class triangle>& out);
+
 // bvh_node(hittable_list) (bvh.h:13-18): here it only records the primitives, in list order (= prim ID);
 // both trees (reference topology and SAH) are built inside bdpt_scene_upload.
 class bvh_node : public hittable {
   public:
     explicit bvh_node(hittable_list list) {
         prims.reserve(list.objects.size());
-        for (auto& o : list.objects)
-            if (auto t = std::dynamic_pointer_cast<triangle>(o)) prims.push_back(*t);
+        for (auto& o : list.objects) collect_triangles(*o, prims);   // triangles as they are; instances baked (above)
     }
     std::vector<triangle> prims;
 };

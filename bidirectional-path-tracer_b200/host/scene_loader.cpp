@@ -323,11 +323,34 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
         if (!mesh.is_map()) throw std::runtime_error("Scene entries must be mappings");
         const std::string type = to_string(mesh["type"]);
         if (type.empty()) throw std::runtime_error("Mesh missing type field");
+        const size_t w0 = result.world.size(), l0 = result.lights.size();
         if (type == "TriMesh") load_tri_mesh(mesh, out);
         else if (type == "Sphere") load_sphere(mesh, out);
         else if (type == "mesh") load_indexed_mesh(mesh, out, mats);
         else if (type == "object") load_object(mesh, dir, out, mats, jobs);
         else std::cerr << "Unknown mesh type: " << type << "\n";
+        // Extension of the reference's schema (it can construct no translate / rotate_y, hittable.h:46-157):
+        //   transform: {rotate_y: <degrees>, translate: [x, y, z]}   = translate(rotate_y(surface, deg), offset)
+        // applied to the triangles this surface just added (world and light list alike), baked like collect_triangles does.
+        const node& tf = mesh["transform"];
+        if (tf.is_map()) {
+            const double deg = to_double(tf["rotate_y"], 0.0);
+            const auto off = to_double_list(tf["translate"]);
+            if (tf["translate"].defined() && off.size() != 3) throw std::runtime_error("transform.translate must be [x, y, z]");
+            auto bake = [&](std::vector<triangle>& tris, size_t first) {
+                if (first >= tris.size()) return;
+                auto span = make_shared<triangle_collection>();
+                span->tris.assign(tris.begin() + long(first), tris.end());
+                shared_ptr<hittable> obj = span;
+                if (tf["rotate_y"].defined()) obj = make_shared<rotate_y>(obj, deg);
+                if (off.size() == 3) obj = make_shared<translate>(obj, vec3(off[0], off[1], off[2]));
+                std::vector<triangle> moved;
+                collect_triangles(*obj, moved);
+                std::copy(moved.begin(), moved.end(), tris.begin() + long(first));
+            };
+            bake(result.world.tris, w0);
+            bake(result.lights.tris, l0);
+        } else if (tf.defined()) throw std::runtime_error("transform must be a mapping {rotate_y: deg, translate: [x, y, z]}");
     }
     std::cout << "Triangles: " << result.world.size() << "\n";
     return result;

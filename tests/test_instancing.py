@@ -1,0 +1,97 @@
+"""translate / rotate_y (/root/reference/src/objects/hittable.h:46-157).  The reference moves the RAY into the
+object's frame at every hit query; this repo moves the object's triangles into the world frame once, when the scene is
+flattened (host/camera.cpp: collect_triangles; YAML: a `transform:` map on a surface).
+  CPU: the baked vertices are the reference's own object-to-world formulas (hittable.h:64,134-138), bit for bit.
+  GPU: tracing WORLD rays against the baked soup agrees with the reference's form -- the oracle tracing the
+       object-frame rays of hittable.h:52-53,110-122 against the untransformed soup -- on prim IDs (all but knife
+       edges, tolerance 1e-4 of the rays) and hit distances (tolerance 1e-9 relative: same geometry, different rounding)."""
+import math
+
+import numpy as np
+import pytest
+
+YAML = """
+camera:
+  resolution: [32, 32]
+  location: [0, 1, 5]
+  look_at: [0, 0, 0]
+materials:
+  grey: {type: diffuse, color: [200, 200, 200]}
+  lamp: {type: light, color: [10, 10, 10]}
+surfaces:
+  - type: mesh
+    material: grey
+    vertices: [[0.25, 0.5, 0.125], [1.5, 0.0, -0.75], [0.0, 2.0, 0.375], [-1.0, -1.0, 1.0]]
+    triangles: [[0, 1, 2], [0, 2, 3]]
+%s
+  - type: mesh
+    material: lamp
+    vertices: [[-1, 3, -1], [1, 3, -1], [1, 3, 1]]
+    triangles: [[0, 1, 2]]
+    transform:
+      translate: [0.5, -0.25, 2.0]
+"""
+
+
+def bake(v, deg=None, off=None):
+    """hittable.h:134-138 (object -> world of rotate_y), then :64 (translate), in plain Python floats (the same libm)."""
+    v = np.array(v, np.float64).reshape(-1, 3).copy()
+    if deg is not None:
+        r = deg * 3.1415926535897932385 / 180.0
+        c, s = math.cos(r), math.sin(r)
+        x, z = v[:, 0].copy(), v[:, 2].copy()
+        v[:, 0] = (c * x) + (s * z)
+        v[:, 2] = (-s * x) + (c * z)
+    if off is not None:
+        v += np.array(off, np.float64)
+    return v
+
+
+def test_yaml_transform_bakes_the_reference_formulas(bdpt, tmp_path):
+    base = np.array([[0.25, 0.5, 0.125], [1.5, 0.0, -0.75], [0.0, 2.0, 0.375], [-1.0, -1.0, 1.0]])
+    tri = np.array([[0, 1, 2], [0, 2, 3]])
+    plain = tmp_path / "plain.yaml"
+    plain.write_text(YAML % "")
+    moved = tmp_path / "moved.yaml"
+    moved.write_text(YAML % "    transform:\n      rotate_y: 33.5\n      translate: [1.0, 2.0, -3.0]")
+    a, b = bdpt.SceneFile(str(plain)), bdpt.SceneFile(str(moved))
+    want_plain = base[tri].reshape(-1, 9)
+    assert np.array_equal(a.verts[:2], want_plain)
+    want = bake(base, 33.5, (1.0, 2.0, -3.0))[tri].reshape(-1, 9)
+    assert np.array_equal(b.verts[:2], want)                       # rotate first, then translate; bit for bit
+    lamp = bake([[-1, 3, -1], [1, 3, -1], [1, 3, 1]], None, (0.5, -0.25, 2.0)).reshape(-1, 9)
+    assert np.array_equal(a.verts[2:], lamp) and np.array_equal(b.verts[2:], lamp)
+    assert a.n_lights == 1 and b.n_lights == 1                      # the light list is moved with the world
+    bad = tmp_path / "bad.yaml"
+    bad.write_text(YAML % "    transform:\n      translate: [1.0, 2.0]")
+    with pytest.raises(bdpt.BdptError, match="translate"):
+        bdpt.SceneFile(str(bad))
+
+
+@pytest.mark.gpu
+def test_baked_instance_traces_like_the_reference_ray_transform(bdpt, gpu_ctx, scenes):
+    from oracle.oracle import Oracle
+    from tools import testscenes as ts
+    v, m, mats, cam = scenes["cornell_spheres"]()
+    v = np.asarray(v, np.float64).reshape(-1, 9)
+    deg, off = 27.0, np.array([35.0, -12.5, 60.0])
+    world = bake(v.reshape(-1, 3), deg, off).reshape(-1, 9)
+    rays = ts.ray_batch(world, 200_000, seed=7, cam=None)
+    # the reference's translate::hit then rotate_y::hit: origin - offset, then both rotated into the object frame
+    r = deg * 3.1415926535897932385 / 180.0
+    c, s = math.cos(r), math.sin(r)
+    rays = np.asarray(rays, np.float64).reshape(-1, 8)              # ox oy oz dx dy dz tmin tmax
+    obj = rays.copy()
+    o = rays[:, 0:3] - off
+    d = rays[:, 3:6]
+    obj[:, 0] = (c * o[:, 0]) - (s * o[:, 2]); obj[:, 1] = o[:, 1]; obj[:, 2] = (s * o[:, 0]) + (c * o[:, 2])
+    obj[:, 3] = (c * d[:, 0]) - (s * d[:, 2]); obj[:, 4] = d[:, 1]; obj[:, 5] = (s * d[:, 0]) + (c * d[:, 2])
+    prim, t, _, _ = Oracle("port").load(v, m, mats).trace(obj)
+    gpu_ctx.upload(world, m, mats)
+    for bvh in (bdpt.BVH_REFERENCE, bdpt.BVH_FAST):
+        h = gpu_ctx.trace(rays, bvh=bvh)
+        same = h["prim"] == prim
+        assert same.mean() > 1 - 1e-4, "prim IDs differ on %d rays" % (~same).sum()
+        hit = same & (prim != bdpt.MISS)
+        assert hit.sum() > 50_000
+        assert np.abs(h["t"][hit] - t[hit]).max() <= 1e-9 * np.abs(t[hit]).max()
