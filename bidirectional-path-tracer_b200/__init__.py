@@ -35,12 +35,16 @@ EXPORTS = [
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
     "bdpt_scene_set_textures", "bdpt_scene_file_textures", "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read", "bdpt_comm_attach",
-    "bdpt_film_to_rgb8_noalloc",
+    "bdpt_film_to_rgb8_noalloc", "bdpt_scene_set_media",
 ]
 
 
 class Material(C.Structure):
     _fields_ = [("type", C.c_uint32), ("tex", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+
+
+class Medium(C.Structure):
+    _fields_ = [("density", C.c_double), ("albedo", C.c_double * 3), ("first_tri", C.c_uint64), ("n_tris", C.c_uint64)]
 
 
 class Texture(C.Structure):
@@ -116,6 +120,7 @@ def lib():
         L.bdpt_scene_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32]
         L.bdpt_scene_upload_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32]
         L.bdpt_scene_set_textures.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.bdpt_scene_set_media.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.bdpt_bvh_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
         L.bdpt_bvh_leaf_order.argtypes = [C.c_void_p, C.c_void_p]
         L.bdpt_host_bvh_build.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -499,6 +504,21 @@ class Context:
         out = np.empty(len(a), np.uint8)
         self._chk(lib().bdpt_visible(self._h, bvh, a.ctypes.data, b.ctypes.data, len(a), out.ctypes.data, 0), "bdpt_visible")
         return out.astype(bool)
+
+    def set_media(self, media):
+        """bdpt_scene_set_media: constant_medium + isotropic (constant_medium.h:8-61, material.h:149-171).  media: list of
+        (density, (r, g, b), boundary triangles n x 9), closed convex meshes; [] drops them."""
+        arr = (Medium * max(1, len(media)))()
+        soup, first = [], 0
+        for k, (density, rgb, tris) in enumerate(media):
+            t = np.ascontiguousarray(tris, dtype=np.float64).reshape(-1, 9)
+            arr[k].density = float(density)
+            arr[k].albedo[:] = [float(x) for x in rgb]
+            arr[k].first_tri, arr[k].n_tris = first, len(t)
+            soup.append(t); first += len(t)
+        b = np.ascontiguousarray(np.concatenate(soup) if soup else np.zeros((0, 9)), dtype=np.float64)
+        self._chk(lib().bdpt_scene_set_media(self._h, C.byref(arr) if media else None, len(media), b.ctypes.data if len(b) else None, len(b)),
+                  "bdpt_scene_set_media")
 
     def film_clear(self, width, height):
         self._chk(lib().bdpt_film_clear(self._h, int(width), int(height)), "bdpt_film_clear")

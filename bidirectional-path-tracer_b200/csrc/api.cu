@@ -324,6 +324,8 @@ void bdpt_ctx_destroy(bdpt_ctx* ctx) {
     if (ctx->film) cudaFree(ctx->film);
     if (ctx->d_tex) cudaFree(ctx->d_tex);
     if (ctx->d_tex_data) cudaFree(ctx->d_tex_data);
+    if (ctx->d_media) cudaFree(ctx->d_media);
+    if (ctx->d_med_tris) cudaFree(ctx->d_med_tris);
     if (ctx->d_stats) cudaFree(ctx->d_stats);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -461,6 +463,58 @@ int bdpt_scene_set_textures(bdpt_ctx* ctx, const bdpt_texture* tex, uint32_t n_t
         BDPT_CUDA(ctx, cudaMalloc(&ctx->d_tex_data, std::max<uint64_t>(data_bytes, 16)));
         if (data_bytes) BDPT_CUDA(ctx, cudaMemcpy(ctx->d_tex_data, data, data_bytes, cudaMemcpyHostToDevice));
         ctx->n_tex = n_tex;
+    }
+    apply_textures(ctx, ctx->view);
+    return BDPT_OK;
+}
+
+int bdpt_scene_set_media(bdpt_ctx* ctx, const bdpt_medium* media, uint32_t n_media, const double* boundary_verts, uint64_t n_boundary_tris) {
+    if (!ctx || (n_media && (!media || !boundary_verts))) return BDPT_ERR_ARG;
+    if (n_media > 16) { ctx->err = "at most 16 media"; return BDPT_ERR_ARG; }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    std::vector<MediumDev> h(n_media);
+    std::vector<TriGeom> tris(n_boundary_tris);
+    for (uint64_t i = 0; i < n_boundary_tris; ++i) {   // triangle.h:21-31: v0, edge1, edge2
+        const double* p = boundary_verts + 9 * i;
+        TriGeom g;
+        g.v0x = p[0]; g.v0y = p[1]; g.v0z = p[2];
+        g.e1x = p[3] - p[0]; g.e1y = p[4] - p[1]; g.e1z = p[5] - p[2];
+        g.e2x = p[6] - p[0]; g.e2y = p[7] - p[1]; g.e2z = p[8] - p[2];
+        g.mat = 0; g.pad = 0;
+        tris[i] = g;
+    }
+    for (uint32_t k = 0; k < n_media; ++k) {
+        const bdpt_medium& m = media[k];
+        if (!(m.density > 0.0)) { ctx->err = "medium: density must be > 0"; return BDPT_ERR_ARG; }
+        if (m.n_tris == 0 || m.n_tris > 4096 || m.first_tri > n_boundary_tris || m.n_tris > n_boundary_tris - m.first_tri) {
+            ctx->err = "medium: boundary triangles outside the soup (1..4096 per medium)"; return BDPT_ERR_ARG;
+        }
+        MediumDev& d = h[k];
+        d.neg_inv_density = -1 / m.density;   // constant_medium.h:12
+        d.r = m.albedo[0]; d.g = m.albedo[1]; d.b = m.albedo[2];
+        for (int c = 0; c < 3; ++c) { d.lo[c] = INFINITY; d.hi[c] = -INFINITY; }
+        for (uint64_t i = m.first_tri; i < m.first_tri + m.n_tris; ++i)
+            for (int vtx = 0; vtx < 3; ++vtx)
+                for (int c = 0; c < 3; ++c) {
+                    const double x = boundary_verts[9 * i + 3 * vtx + c];
+                    d.lo[c] = std::fmin(d.lo[c], x); d.hi[c] = std::fmax(d.hi[c], x);
+                }
+        for (int c = 0; c < 3; ++c) {   // generous: the bounds only skip rays that cannot meet the mesh
+            const double pad = 1e-6 * (std::fabs(d.lo[c]) + std::fabs(d.hi[c]) + (d.hi[c] - d.lo[c])) + 1e-12;
+            d.lo[c] -= pad; d.hi[c] += pad;
+        }
+        d.first = uint32_t(m.first_tri); d.count = uint32_t(m.n_tris);
+    }
+    if (ctx->d_media) { cudaFree(ctx->d_media); ctx->d_media = nullptr; }
+    if (ctx->d_med_tris) { cudaFree(ctx->d_med_tris); ctx->d_med_tris = nullptr; }
+    ctx->n_media = 0;
+    if (n_media) {
+        BDPT_CUDA(ctx, cudaMalloc(&ctx->d_media, n_media * sizeof(MediumDev)));
+        BDPT_CUDA(ctx, cudaMemcpy(ctx->d_media, h.data(), n_media * sizeof(MediumDev), cudaMemcpyHostToDevice));
+        BDPT_CUDA(ctx, cudaMalloc(&ctx->d_med_tris, std::max<uint64_t>(tris.size(), 1) * sizeof(TriGeom)));
+        BDPT_CUDA(ctx, cudaMemcpy(ctx->d_med_tris, tris.data(), tris.size() * sizeof(TriGeom), cudaMemcpyHostToDevice));
+        ctx->n_media = n_media;
     }
     apply_textures(ctx, ctx->view);
     return BDPT_OK;

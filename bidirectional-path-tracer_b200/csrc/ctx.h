@@ -36,6 +36,10 @@ struct bdpt_ctx {
     bdpt::Tex* d_tex = nullptr;
     unsigned char* d_tex_data = nullptr;
     uint32_t n_tex = 0;
+    // media of bdpt_scene_set_media: likewise
+    bdpt::MediumDev* d_media = nullptr;
+    bdpt::TriGeom* d_med_tris = nullptr;
+    uint32_t n_media = 0;
 
     // NCCL communicator of bdpt_comm_init (film_reduce.cu); ncclComm_t
     void* comm = nullptr;
@@ -92,7 +96,10 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 // api.cu: the fp32 triangle records + error scale of the warp-synchronous walk (traverse_w32.cuh), queued on ctx->stream
 int derive_walk32(bdpt_ctx* ctx, SceneView& v);
 void comm_free(bdpt_ctx* ctx);   // film_reduce.cu
-inline void apply_textures(bdpt_ctx* ctx, SceneView& v) { v.tex = ctx->d_tex; v.tex_data = ctx->d_tex_data; v.n_tex = ctx->n_tex; }
+inline void apply_textures(bdpt_ctx* ctx, SceneView& v) {
+    v.tex = ctx->d_tex; v.tex_data = ctx->d_tex_data; v.n_tex = ctx->n_tex;
+    v.media = ctx->d_media; v.med_tris = ctx->d_med_tris; v.n_media = ctx->n_media;
+}
 void render_free(bdpt_ctx* ctx);
 // gpu_bvh.cu: the fast tree built on the device from triangles already uploaded (queued on ctx->stream)
 int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const double lo[3], const double hi[3], double extent,

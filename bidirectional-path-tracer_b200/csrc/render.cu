@@ -47,6 +47,7 @@ constexpr uint32_t kSlowFlag = 0x80000000u;   // q_exact entry: re-run the FAST 
 enum { C_ACTIVE0 = 0, C_ACTIVE1 = 1, C_MAT0 = 2 /* ..5 */, C_SHADOW = 6, C_MAXNC = 7, C_MAXNL = 8, C_SUMNC = 9,
        C_SUMNL = 10, C_OVERFLOW = 11, C_PAIRS_LO = 12, C_PAIRS_HI = 13 /* 64-bit, 8-byte aligned */, C_CURSOR = 14 /* dynamic-fetch cursor of the trace launch */, C_EXACT_SHADOW = 15,
        C_DONE0 = 16, C_DONE1 = 17, C_SHADOW_TOTAL = 18 /* ..19: 64-bit, shadow rays of the whole worker run */, C_SHADOW_LIVE = 20, C_EXACT0 = 21, C_EXACT1 = 22,
+       C_MAT4 = 23 /* fifth material queue: scatter points inside a medium (isotropic) */,
        C_SLOW_S0 = 24, C_SLOW_S1 = 25 /* parked shadow segments, ping-pong */, C_COUNT = 28 };
 
 struct Frame {           // camera.h:148-197 derived values + this call's sample selection
@@ -117,7 +118,7 @@ struct WF {              // wavefront workspace, all device pointers
     int64_t* sample;
     uint32_t* live;
     uint32_t* q_slots[2];            // slots whose subpaths have both ended (ping-pong: done list -> free list)
-    uint32_t *q_active[2], *q_mat[4];
+    uint32_t *q_active[2], *q_mat[5];   // q_mat[4]: isotropic (scatter points inside media)
     uint32_t* q_exact[2];            // path rays for the next launch's front blocks (reference traversal or unbounded re-run), ping-pong
     SlowShadow* ss[2];               // parked shadow segments, ping-pong
     int64_t sscap;
@@ -194,15 +195,19 @@ __device__ __forceinline__ void store_path(PathRec* r, D3 o, D3 d, D3 T, uint32_
     q[3] = make_double2(T.x, T.y); q[4] = make_double2(T.z, 0.0);
     reinterpret_cast<int4*>(r)[5] = make_int4(int(draws), -1, remaining, 0);
 }
-__device__ __forceinline__ void store_vertex(VertRec* r, D3 p, D3 a, uint32_t prim) {
+// index: the vertex's position on its subpath (camera: bounce; light: 0 = the emitter, then 1 + bounce) -- keys the shadow
+// stream's draws when the scene has media
+__device__ __forceinline__ void store_vertex(VertRec* r, D3 p, D3 a, uint32_t prim, uint32_t index = 0) {
     double2* q = reinterpret_cast<double2*>(r);
     q[0] = make_double2(p.x, p.y); q[1] = make_double2(p.z, a.x); q[2] = make_double2(a.y, a.z);
-    reinterpret_cast<int4*>(r)[3] = make_int4(int(prim), 0, 0, 0);
+    reinterpret_cast<int4*>(r)[3] = make_int4(int(prim), int(index), 0, 0);
 }
-__device__ __forceinline__ void load_vertex(const VertRec* r, D3& p, D3& a, uint32_t& prim) {
+__device__ __forceinline__ void load_vertex(const VertRec* r, D3& p, D3& a, uint32_t& prim, uint32_t* index = nullptr) {
     const double2* q = reinterpret_cast<const double2*>(r);
     const double2 q0 = q[0], q1 = q[1], q2 = q[2];
-    prim = uint32_t(reinterpret_cast<const int4*>(r)[3].x);
+    const int4 tail = reinterpret_cast<const int4*>(r)[3];
+    prim = uint32_t(tail.x);
+    if (index) *index = uint32_t(tail.y);
     p = mk(q0.x, q0.y, q1.x); a = mk(q1.y, q2.x, q2.y);
 }
 
@@ -337,12 +342,93 @@ __global__ void __launch_bounds__(kGen) k_generate(SceneView sc, Frame f, WF w, 
 // for a camera subpath, adds throughput * background (camera.h:337-340).  Hits are binned by material
 // class so each shading kernel runs divergence-free over its own queue.
 // result of one closest-hit query: record the hit and pick the material queue, or finish the subpath
+// ------------------------------------------------------------------ participating media (constant_medium.h:8-61)
+// boundary->hit(r, [tmin, tmax]) over the boundary triangles in order (triangle_collection::hit, triangle.h:150-164): only t matters
+__device__ __forceinline__ bool boundary_hit(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double tmin,
+                                             double tmax, double& t_out) {
+    bool any = false;
+    double closest = tmax;
+    for (uint32_t i = 0; i < m.count; ++i) {
+        double t, u, v;
+        if (tri_candidate(med_tris + m.first + i, o, d, t, u, v) && tmin <= t && t <= closest) { any = true; closest = t; }
+    }
+    t_out = closest;
+    return any;
+}
+// false: the ray's LINE certainly misses the (padded) bounds of the boundary mesh, so neither boundary hit exists
+__device__ __forceinline__ bool line_meets_bounds(const MediumDev& m, const D3& o, const D3& d) {
+    const double oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+    double tn = -__longlong_as_double(0x7FF0000000000000LL), tf = __longlong_as_double(0x7FF0000000000000LL);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        if (dd[k] == 0.0) { if (oo[k] < m.lo[k] || oo[k] > m.hi[k]) return false; }
+        else {
+            const double a = (m.lo[k] - oo[k]) / dd[k], b = (m.hi[k] - oo[k]) / dd[k];
+            tn = fmax(tn, fmin(a, b)); tf = fmin(tf, fmax(a, b));
+        }
+    }
+    return !(tn > tf);
+}
+// constant_medium::hit, constant_medium.h:22-58 (oracle/port.cpp: medium_hit).  ONE draw, only when the part of the ray inside
+// the boundary overlaps [tmin, tmax].
+__device__ __forceinline__ bool medium_hit(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double tmin,
+                                           double tmax, Rng& rng, double& t_out) {
+    if (!line_meets_bounds(m, o, d)) return false;
+    const double inf = __longlong_as_double(0x7FF0000000000000LL);
+    double t1, t2;
+    if (!boundary_hit(med_tris, m, o, d, -inf, inf, t1)) return false;
+    if (!boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2)) return false;
+    if (t1 < tmin) t1 = tmin;
+    if (t2 > tmax) t2 = tmax;
+    if (t1 >= t2) return false;
+    if (t1 < 0) t1 = 0;
+    const double ray_length = len(d);
+    const double distance_inside_boundary = (t2 - t1) * ray_length;
+    const double hit_distance = m.neg_inv_density * det_log(rng.next());
+    if (hit_distance > distance_inside_boundary) return false;
+    t_out = t1 + hit_distance / ray_length;
+    return true;
+}
+
+constexpr int kClsIsotropic = 4;   // material queue of the scatter points inside media (after BDPT_MAT_* 0..3)
+
+// world.hit's media for one path ray.  Out of line on purpose: inlined into finish_trace its fp64 triangle loops raise the
+// register pressure of every traversal kernel (k_trace_fast: 150 -> 538 bytes of spills), scenes without media included.
+struct MediaOut { double t; uint32_t prim, found; };
+__device__ __noinline__ void media_after_triangles(const MediumDev* __restrict__ media, const TriGeom* __restrict__ med_tris, uint32_t n_media,
+                                                   PathRec* path, uint64_t seed, uint32_t stream, uint64_t sid, MediaOut* io) {
+    const double2* q = reinterpret_cast<const double2*>(path);
+    const double2 q0 = q[0], q1 = q[1], q2 = q[2];
+    const D3 o = mk(q0.x, q0.y, q1.x), d = mk(q1.y, q2.x, q2.y);
+    Rng rng;
+    rng.init(seed, stream, sid, path->draws);
+    const uint32_t d0 = rng.draws;
+    double best = io->found ? io->t : __longlong_as_double(0x7FF0000000000000LL);
+    for (uint32_t k = 0; k < n_media; ++k) {
+        double tm;
+        if (medium_hit(med_tris, media[k], o, d, 0.001, best, rng, tm)) { io->found = 1u; best = tm; io->t = tm; io->prim = kMediumPrim | k; }
+    }
+    if (rng.draws != d0) path->draws = rng.draws;
+}
+
+template <bool MEDIA = false>
 __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, bool found,
                                             const HitD& h, double* film) {
+    uint32_t prim = h.prim;
+    double t = h.t;
+    if (MEDIA && sc.n_media) {   // the media of the world list, asked after the triangles with the bound found so far (port: hit_world)
+        const bool is_cam = pid < uint32_t(w.B);
+        const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
+        MediaOut mo;
+        mo.found = found ? 1u : 0u; mo.prim = prim; mo.t = t;
+        media_after_triangles(sc.media, sc.med_tris, sc.n_media, w.path + pid, f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, &mo);
+        found = mo.found != 0; prim = mo.prim; t = mo.t;
+    }
     if (found) {
-        w.path[pid].hit_prim = h.prim;
-        w.path[pid].hit_t = h.t;
-        return int(sc.mats[__ldg(&sc.shade[h.prim].mat)].type);
+        w.path[pid].hit_prim = prim;
+        w.path[pid].hit_t = t;
+        if (MEDIA && (prim & kMediumPrim)) return kClsIsotropic;
+        return int(sc.mats[__ldg(&sc.shade[prim].mat)].type);
     }
     if (pid < uint32_t(w.B)) {
         const PathRec& pr = w.path[pid];
@@ -362,11 +448,16 @@ __device__ __forceinline__ RayD load_path_ray(const WF& w, uint32_t pid) {
     r.tmax = __longlong_as_double(0x7FF0000000000000LL);
     return r;
 }
+template <bool MEDIA = false>
 __device__ __forceinline__ void bin_by_material(const WF& w, int cls, uint32_t pid) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const uint32_t slot = warp_append(w.counters + C_MAT0 + k, cls == k);
         if (cls == k) w.q_mat[k][slot] = pid;
+    }
+    if (MEDIA && __any_sync(0xFFFFFFFFu, cls == kClsIsotropic)) {   // scenes with media only
+        const uint32_t slot = warp_append(w.counters + C_MAT4, cls == kClsIsotropic);
+        if (cls == kClsIsotropic) w.q_mat[kClsIsotropic][slot] = pid;
     }
 }
 
@@ -387,7 +478,7 @@ constexpr int kStackLevels = 32;              // StackEntry slots (fast tree, de
 // per launch but each walks ~1000 nodes of the reference tree, so instead of a launch of their own (whose
 // duration would be one thread's latency chain) they ride at the front of the next bulk launch and their
 // paths simply lag one iteration behind — path regeneration makes that free.
-template <int BVH, bool STATS>
+template <int BVH, bool STATS, bool MEDIA = false>
 __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_paths(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
                                                        const uint32_t* __restrict__ n_ptr, int dn, int ex, uint32_t n_def_blocks,
                                                        uint32_t limit, double* film, unsigned long long* stats) {
@@ -409,7 +500,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_paths(SceneV
             else
                 found = traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts);
             if (STATS) add_trav<0, BVH == BDPT_BVH_REFERENCE>(stats, ts);
-            cls = finish_trace(sc, f, w, pid, found, h, film);
+            cls = finish_trace<MEDIA>(sc, f, w, pid, found, h, film);
             ended = cls < 0;
         }
     } else {
@@ -429,14 +520,14 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_paths(SceneV
                 defer_tag = rc == TR_SLOW ? kSlowFlag : 0u;
             }
             if (STATS) add_trav<0, BVH == BDPT_BVH_REFERENCE>(stats, ts);
-            if (!defer) { cls = finish_trace(sc, f, w, pid, found, h, film); ended = cls < 0; }
+            if (!defer) { cls = finish_trace<MEDIA>(sc, f, w, pid, found, h, film); ended = cls < 0; }
         }
     }
     if (BVH != BDPT_BVH_REFERENCE) {   // rays that need the reference tree: compacted for the next launch's front blocks
         const uint32_t slot = warp_append(w.counters + C_EXACT0 + ex, defer);
         if (defer) w.q_exact[ex][slot] = pid | defer_tag;
     }
-    bin_by_material(w, cls, pid);
+    bin_by_material<MEDIA>(w, cls, pid);
     retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
 }
 
@@ -460,7 +551,7 @@ __device__ __forceinline__ uint32_t warp_fetch(uint32_t* cursor, bool need, uint
     return (need && my < n) ? my : 0xFFFFFFFFu;
 }
 
-template <bool STATS>
+template <bool STATS, bool MEDIA = false>
 __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneView sc, Frame f, WF w, const uint32_t* __restrict__ queue,
                                                                         const uint32_t* __restrict__ n_ptr, int dn, int ex,
                                                                         uint32_t n_def_blocks, int threshold, uint32_t limit, double* film,
@@ -485,11 +576,11 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
             if (lane0) {
             const bool found = rc == TR_DEFER ? traverse_ref<false, STATS>(sc, r, h, reinterpret_cast<int32_t*>(l_stack), 1, &ts) : rc == TR_HIT;
             if (STATS) add_trav<0, false>(stats, ts);
-            cls = finish_trace(sc, f, w, pid, found, h, film);
+            cls = finish_trace<MEDIA>(sc, f, w, pid, found, h, film);
             ended = cls < 0;
             }
         }
-        bin_by_material(w, cls, pid);
+        bin_by_material<MEDIA>(w, cls, pid);
         retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
         return;
     }
@@ -508,11 +599,11 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_trace_fast(SceneVi
             if (fin) {
                 if (STATS && result != TR_DEFER && result != TR_SLOW) add_trav<0, false>(stats, W.ts);
                 if (result == TR_DEFER || result == TR_SLOW) defer = true;
-                else { cls = finish_trace(sc, f, w, pid, result == TR_HIT, W.hit, film); ended = cls < 0; }
+                else { cls = finish_trace<MEDIA>(sc, f, w, pid, result == TR_HIT, W.hit, film); ended = cls < 0; }
             }
             const uint32_t slot = warp_append(w.counters + C_EXACT0 + ex, defer);
             if (defer) w.q_exact[ex][slot] = pid | (result == TR_SLOW ? kSlowFlag : 0u);
-            bin_by_material(w, cls, pid);
+            bin_by_material<MEDIA>(w, cls, pid);
             retire(w, ended, pid < uint32_t(w.B) ? pid : pid - uint32_t(w.B), dn);
             result = WALK_YIELD;
         }
@@ -710,7 +801,7 @@ __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f,
                 film_add(film, decode_sample(f, w.sample[b]).pix, MIS ? wgt * (s.T * Le) : s.T * Le);
             } else if (!MIS) {   // MIS: an emitter absorbs; a light-subpath vertex on it connects to nothing
                 const uint32_t slot = w.nlight[b];
-                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | kLightFlag);
+                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | kLightFlag, uint32_t(f.depth - s.remaining));
                 if (TEX) w.lcol[size_t(b) * size_t(w.depth) + slot] = Le;
                 w.nlight[b] = slot + 1;
             }
@@ -739,12 +830,12 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
             if (is_cam) {
                 const uint32_t slot = w.ncam[b];
                 const D3 tf = s.T * fr;   // camera.h:471: cam_v.throughput * f_cam
-                store_vertex(w.cv + size_t(b) * size_t(w.depth) + slot, s.p, tf, s.prim | side);
+                store_vertex(w.cv + size_t(b) * size_t(w.depth) + slot, s.p, tf, s.prim | side, uint32_t(f.depth - s.remaining));
                 if (MIS) { VertMis vm; vm.dVCM = mh.dVCM; vm.dVC = mh.dVC; vm.cos_in = mh.cos_in; vm.len = mh.len; vm.pad = 0; w.cvm[size_t(b) * size_t(w.depth) + slot] = vm; }
                 w.ncam[b] = slot + 1;
             } else {
                 const uint32_t slot = w.nlight[b];
-                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | side);
+                store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, s.p, s.T, s.prim | side, uint32_t(f.depth - s.remaining));
                 if (TEX) w.lcol[size_t(b) * size_t(w.depth) + slot] = albedo;
                 if (MIS) { VertMis vm; vm.dVCM = mh.dVCM; vm.dVC = mh.dVC; vm.cos_in = mh.cos_in; vm.len = mh.len; vm.pad = 0; w.lvm[size_t(b) * size_t(w.depth) + slot] = vm; }
                 w.nlight[b] = slot + 1;
@@ -774,6 +865,49 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
         }
     }
     return live;
+}
+
+// ------------------------------------------------------------------ K2: isotropic (material.h:149-171), the phase function of a
+// constant_medium (constant_medium.h:14,54).  The vertex is a point INSIDE the medium: no triangle, the reference's arbitrary normal
+// (1,0,0) and front_face = true (constant_medium.h:52-53).  Not delta: evaluate_bsdf = albedo / (4 pi) (material.h:166-168), so the
+// vertex is stored and connected; scatter: attenuation = albedo, sphere_pdf (pdf.h:18-29): direction = random_unit_vector(), pdf =
+// scattering_pdf = 1 / (4 pi) (material.h:154-164; camera.h:361-368).  BDPT_WEIGHT_REF_SUM only.
+__device__ __forceinline__ bool shade_isotropic(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
+    const double2* q = reinterpret_cast<const double2*>(w.path + pid);
+    const double2 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3], q4 = q[4];
+    const int4 q5 = reinterpret_cast<const int4*>(w.path + pid)[5];
+    const D3 o = mk(q0.x, q0.y, q1.x), d = mk(q1.y, q2.x, q2.y), T = mk(q3.x, q3.y, q4.x);
+    const D3 p = o + q4.y * d;   // rec.p = r.at(rec.t), constant_medium.h:50
+    const uint32_t prim = uint32_t(q5.y), draws = uint32_t(q5.x);
+    const int32_t remaining_in = q5.z;
+    const MediumDev md = sc.media[prim & ~kMediumPrim];
+    const D3 albedo = mk(md.r, md.g, md.b);
+    const bool is_cam = pid < uint32_t(w.B);
+    const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
+    const uint32_t index = uint32_t(f.depth - remaining_in);
+    const D3 fr = albedo / (4 * kPi);
+    if (len2(fr) > 0) {
+        if (is_cam) {
+            const uint32_t slot = w.ncam[b];
+            store_vertex(w.cv + size_t(b) * size_t(w.depth) + slot, p, T * fr, prim, index);
+            w.ncam[b] = slot + 1;
+        } else {
+            const uint32_t slot = w.nlight[b];
+            store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, p, T, prim, index);
+            if (w.lcol) w.lcol[size_t(b) * size_t(w.depth) + slot] = albedo;
+            w.nlight[b] = slot + 1;
+        }
+    }
+    const int32_t remaining = remaining_in - 1;
+    if (remaining <= 0) return false;
+    Rng rng;
+    rng.init(f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, draws);
+    const D3 sd = random_unit_vector(rng);
+    const double pdf_value = 1 / (4 * kPi);
+    const double spdf = 1 / (4 * kPi);
+    const D3 T2 = T * albedo * spdf / pdf_value;   // camera.h:366
+    store_ray(w, pid, p, sd, T2, rng.draws, remaining);
+    return true;
 }
 
 // ------------------------------------------------------------------ K2: metal (material.h:69-90)
@@ -850,19 +984,21 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
 // Thread idx walks the concatenation light | lambertian | metal | dielectric of the queues k_trace_* filled, so
 // a warp straddles at most one class boundary; the survivors' queue append and the retirement of ended
 // subpaths are shared.
-template <bool MIS, bool TEX>
+template <bool MIS, bool TEX, bool MEDIA = false>
 __global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
     const uint32_t idx = blockIdx.x * kWide + threadIdx.x;
     const uint32_t n_li = w.counters[C_MAT0 + BDPT_MAT_LIGHT], n_la = w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN],
                    n_me = w.counters[C_MAT0 + BDPT_MAT_METAL], n_di = w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
-    const bool valid = idx < n_li + n_la + n_me + n_di;
+    const uint32_t n_iso = MEDIA ? w.counters[C_MAT4] : 0u;
+    const bool valid = idx < n_li + n_la + n_me + n_di + n_iso;
     bool live = false;
     uint32_t pid = 0;
     if (valid) {
         if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light<MIS, TEX>(sc, f, w, pid, film); }
         else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert<MIS, TEX>(sc, f, w, pid); }
         else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal<MIS>(sc, f, w, pid); }
-        else { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric<MIS>(sc, f, w, pid); }
+        else if (idx < n_li + n_la + n_me + n_di) { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric<MIS>(sc, f, w, pid); }
+        else if (MEDIA) { pid = w.q_mat[kClsIsotropic][idx - n_li - n_la - n_me - n_di]; live = shade_isotropic(sc, f, w, pid); }
     }
     const uint32_t slot = block_append<kWide>(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
@@ -890,6 +1026,7 @@ __global__ void __launch_bounds__(256) k_counts(WF w, int dn) {
 // connect_vertices (camera.h:440-475) for camera-vertex slots [k0, k1) of every finished sample (the done
 // list) against all of the sample's light vertices.  Everything except visible() is evaluated here; pairs that survive the
 // early-outs become shadow rays carrying their finished contribution.
+template <bool MEDIA>
 __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w, SQ q, const uint32_t* __restrict__ done, int64_t nb,
                                                    int k0, int k1) {
     const int64_t idx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
@@ -899,14 +1036,19 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
     const int64_t b = valid ? int64_t(done[idx % nb]) : 0;
     uint32_t nl = 0;
     D3 cp = mk(0, 0, 0), ctf = mk(0, 0, 0), cn = mk(0, 0, 0);
-    uint32_t pix = 0;
+    uint32_t pix = 0, cindex = 0;
+    uint64_t sid = 0;
     if (valid && uint32_t(k) < w.ncam[b]) {
         nl = w.nlight[b];
         uint32_t cprim;
-        load_vertex(w.cv + size_t(b) * size_t(w.depth) + size_t(k), cp, ctf, cprim);
-        const TriShade sh = sc.shade[cprim];
-        cn = mk(sh.nx, sh.ny, sh.nz);   // |dot| below makes the face flip irrelevant (camera.h:451-452)
-        pix = decode_sample(f, w.sample[b]).pix;
+        load_vertex(w.cv + size_t(b) * size_t(w.depth) + size_t(k), cp, ctf, cprim, &cindex);
+        if (MEDIA && (cprim & kMediumPrim)) cn = mk(1.0, 0.0, 0.0);   // a scatter point inside a medium: constant_medium.h:52
+        else {
+            const TriShade sh = sc.shade[cprim];
+            cn = mk(sh.nx, sh.ny, sh.nz);   // |dot| below makes the face flip irrelevant (camera.h:451-452)
+        }
+        const SampleId sm = decode_sample(f, w.sample[b]);
+        pix = sm.pix; sid = sm.sid;
     }
     const uint32_t nl_max = __reduce_max_sync(0xFFFFFFFFu, nl);
     for (uint32_t m = 0; m < nl_max; ++m) {
@@ -916,14 +1058,17 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
         uint32_t far_prim = 0;
         if (m < nl) {
             D3 lp, lT;
-            uint32_t lprim;
-            load_vertex(w.lv + size_t(b) * size_t(w.depth) + size_t(m), lp, lT, lprim);
+            uint32_t lprim, lindex;
+            load_vertex(w.lv + size_t(b) * size_t(w.depth) + size_t(m), lp, lT, lprim, &lindex);
             const D3 dir = lp - cp;
             const double dist2 = len2(dir);
             if (dist2 > 0) {
                 const D3 du = unit(dir);
                 far_prim = lprim & ~kLightFlag;
-                const TriShade lsh = sc.shade[far_prim];
+                const bool l_medium = MEDIA && (far_prim & kMediumPrim) != 0;
+                TriShade lsh;
+                lsh.nx = 1.0; lsh.ny = 0.0; lsh.nz = 0.0; lsh.mat = 0; lsh.pad = 0;
+                if (!l_medium) lsh = sc.shade[far_prim];
                 const D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
                 const double cos_cam = fabs(dot(cn, du));
                 const double cos_light = fabs(dot(ln, -du));
@@ -933,15 +1078,26 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                     const D3 vdu = dir / dist;
                     max_t = dist - 0.001;
                     if (dist > 0 && max_t > 0) {
-                        const Mat lm = sc.mats[lsh.mat];
-                        const D3 lrgb = w.lcol ? w.lcol[size_t(b) * size_t(w.depth) + size_t(m)] : mk(lm.r, lm.g, lm.b);
-                        const D3 f_light = (lprim & kLightFlag) ? lrgb : lrgb / kPi;   // camera.h:463-466
+                        D3 lrgb;
+                        if (w.lcol) lrgb = w.lcol[size_t(b) * size_t(w.depth) + size_t(m)];
+                        else if (l_medium) { const MediumDev md = sc.media[far_prim & ~kMediumPrim]; lrgb = mk(md.r, md.g, md.b); }
+                        else { const Mat lm = sc.mats[lsh.mat]; lrgb = mk(lm.r, lm.g, lm.b); }
+                        const D3 f_light = (lprim & kLightFlag) ? lrgb : (l_medium ? lrgb / (4 * kPi) : lrgb / kPi);   // camera.h:463-466; material.h:166-168
                         if (len2(f_light) > 0) {
                             contrib = ctf * lT * f_light;                               // camera.h:471-472
                             contrib = contrib * (cos_cam * cos_light) / dist2;          // camera.h:473
                             so = cp + (0.001 * vdu);
                             sd = vdu;
                             emit = true;
+                            if (l_medium) far_prim = BDPT_MISS;   // no far-endpoint triangle to test first
+                            // media between the two vertices scatter the shadow ray (world.hit inside visible(), camera.h:437): one draw
+                            // of the sample's shadow stream per (pair, medium) -- oracle/port.cpp: visible_media
+                            for (uint32_t mk_ = 0; MEDIA && mk_ < sc.n_media && emit; ++mk_) {
+                                Rng srng;
+                                srng.init(f.seed, 2u, sid, (cindex * 128u + lindex) * 16u + mk_);
+                                double tm;
+                                if (medium_hit(sc.med_tris, sc.media[mk_], so, sd, 0.001, max_t, srng, tm)) emit = false;
+                            }
                         }
                     }
                 }
@@ -1399,7 +1555,7 @@ void carve(WF& w, char* base) {
     w.sample = c.take<int64_t>(B); w.live = c.take<uint32_t>(B);
     for (int k = 0; k < 2; ++k) w.q_slots[k] = c.take<uint32_t>(B);
     for (int k = 0; k < 2; ++k) w.q_active[k] = c.take<uint32_t>(P);
-    for (int k = 0; k < 4; ++k) w.q_mat[k] = c.take<uint32_t>(P);
+    for (int k = 0; k < 5; ++k) w.q_mat[k] = c.take<uint32_t>(P);
     for (int k = 0; k < 2; ++k) w.q_exact[k] = c.take<uint32_t>(P);
     for (int k = 0; k < 2; ++k) w.ss[k] = c.take<SlowShadow>(size_t(w.sscap));
     w.counters = c.take<uint32_t>(C_COUNT);
@@ -1536,6 +1692,7 @@ struct Job {
     int threshold;                   // dynamic fetch: a walk yields when fewer lanes than this are still walking
     bool mis;                        // BDPT_WEIGHT_MIS
     bool tex;                        // the scene has textures
+    bool media;                      // the scene has participating media: the MEDIA flavours of trace / shade / connect run
     bool walk32;                     // bulk traversal = the warp-synchronous fp32 walk (traverse_w32.cuh); false: round 1's per-lane walk
     int knobs32;                     // its time-slice / refill / leaf-batch parameters (unpack_knobs)
     unsigned resident32;             // blocks of k_trace_w32 / k_shadow_w32 the device keeps resident
@@ -1602,6 +1759,7 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         // counters of this iteration's outputs (ACTIVE[cur] keeps the survivors of the last one)
         WK_CUDA(cudaMemsetAsync(wf.counters + C_ACTIVE0 + nxt, 0, sizeof(uint32_t), st));
         WK_CUDA(cudaMemsetAsync(wf.counters + C_MAT0, 0, (C_EXACT_SHADOW + 1 - C_MAT0) * sizeof(uint32_t), st));
+        if (J.media) WK_CUDA(cudaMemsetAsync(wf.counters + C_MAT4, 0, sizeof(uint32_t), st));
         WK_CUDA(cudaMemsetAsync(wf.counters + C_DONE0 + dn, 0, sizeof(uint32_t), st));
         WK_CUDA(cudaMemsetAsync(wf.counters + C_EXACT0 + ex, 0, sizeof(uint32_t), st));
         if (ngen > 0) {
@@ -1620,13 +1778,17 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         const unsigned g = grid_for(n_active + 2 * ngen, kBlock);   // upper bound; the kernels read the device count
         const unsigned gd = n_def ? grid_for(n_def, kFrontPerBlock) : 0u;
         tm.begin(KT_TRACE, st);
-#define BDPT_TP(B, S) k_trace_paths<B, S><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.limit, J.film, J.d_stats)
+#define BDPT_TP(B, S) do { if (J.media) k_trace_paths<B, S, true><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.limit, J.film, J.d_stats); \
+                            else k_trace_paths<B, S, false><<<g + gd, kBlock, smem, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.limit, J.film, J.d_stats); } while (0)
         if (o.bvh == BDPT_BVH_REFERENCE) { if (want_stats) BDPT_TP(BDPT_BVH_REFERENCE, true); else BDPT_TP(BDPT_BVH_REFERENCE, false); }
         else {
             const unsigned gp = std::min(g, J.walk32 ? J.resident32 : J.resident_blocks);
             if (J.walk32) {
                 if (want_stats) k_trace_w32<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.knobs32, J.film, J.d_stats);
                 else k_trace_w32<false><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.knobs32, J.film, J.d_stats);
+            } else if (J.media) {
+                if (want_stats) k_trace_fast<true, true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
+                else k_trace_fast<false, true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
             } else if (want_stats) k_trace_fast<true><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
             else k_trace_fast<false><<<gd + gp, kBlock, 0, st>>>(sc, f, wf, wf.q_active[cur], wf.counters + C_ACTIVE0 + cur, dn, ex, gd, J.threshold, J.limit, J.film, J.d_stats);
         }
@@ -1635,6 +1797,7 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         tm.begin(KT_SHADE, st);
         const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kWide);   // the lagged rays of the front blocks are shaded too
         if (J.mis) { if (J.tex) k_shade<true, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<true, false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
+        else if (J.media) { if (J.tex) k_shade<false, true, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<false, false, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
         else { if (J.tex) k_shade<false, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<false, false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
         k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
         tm.end(KT_SHADE, st);
@@ -1662,7 +1825,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
                 WK_CUDA(cudaMemsetAsync(q.cnt, 0, SQ_COUNT * sizeof(uint32_t), st));
                 tm.begin(KT_CONNECT, st);
                 if (J.mis) k_connect_mis<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
-                else k_connect<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
+                else if (J.media) k_connect<true><<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
+                else k_connect<false><<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
                 tm.end(KT_CONNECT, st);
                 wk.launches += 1;
                 // one round: size the shadow launch by the pair count (an upper bound) and skip the read-back
@@ -1715,6 +1879,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (o.weighting != BDPT_WEIGHT_REF_SUM && o.weighting != BDPT_WEIGHT_MIS) { ctx->err = "unknown weighting"; return BDPT_ERR_ARG; }
     const bool mis = o.weighting == BDPT_WEIGHT_MIS;
     const bool textured = ctx->view.n_tex > 0;
+    if (mis && ctx->view.n_media > 0) { ctx->err = "BDPT_WEIGHT_MIS does not support participating media (bdpt_scene_set_media)"; return BDPT_ERR_ARG; }
     int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
     H = H < 1 ? 1 : H;
     if (!ctx->film || ctx->film_w != cam->image_width || ctx->film_h != H) {
@@ -1798,7 +1963,8 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 
     Job J;
     J.sc = ctx->view; J.f = f; J.o = o; J.total = total; J.film = ctx->film; J.d_stats = ctx->d_stats;
-    J.mis = mis; J.tex = textured;
+    J.mis = mis; J.tex = textured; J.media = ctx->view.n_media > 0;
+    if (J.media && std::getenv("BDPT_WALK32") && std::atoi(std::getenv("BDPT_WALK32")) != 0) { ctx->err = "BDPT_WALK32 does not support participating media"; return BDPT_ERR_ARG; }
     // traversal stack: one StackEntry per tree level per thread (deferred children only)
     const size_t levels = size_t(std::max(ctx->host.fast_depth, ctx->host.ref_depth)) + 2;
     if (ctx->host.fast_depth + 2 > uint32_t(kStackLevels) || ctx->host.ref_depth + 2 > uint32_t(2 * kStackLevels)) {

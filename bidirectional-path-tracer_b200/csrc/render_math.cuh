@@ -71,6 +71,26 @@ __device__ __forceinline__ void det_sincos(double phi, double& s_out, double& c_
         default: s_out = -c; c_out = s; break;
     }
 }
+// log as a fixed sequence of IEEE +, -, *, / (fdlibm's __ieee754_log on mantissa and exponent; -fmad=false): the draw inside
+// constant_medium::hit (constant_medium.h:44) must come out bit for bit as in the oracle port (oracle/port.cpp: det_log, the same
+// constants in the same order), for the same reason as det_sincos.  x in [0, 1): 0 -> -inf; no subnormals (draws are k * 2^-53).
+__device__ __forceinline__ double det_log(double x) {
+    if (!(x > 0.0)) return -__longlong_as_double(0x7FF0000000000000LL);
+    unsigned long long bits = (unsigned long long)__double_as_longlong(x);
+    int e = int((bits >> 52) & 0x7FFull) - 1023;
+    bits = (bits & 0x000FFFFFFFFFFFFFull) | 0x3FF0000000000000ull;
+    double m = __longlong_as_double((long long)bits);
+    if (m > 1.4142135623730951) { m = m * 0.5; e += 1; }
+    const double f = m - 1.0;
+    const double s_ = f / (2.0 + f);
+    const double z = s_ * s_, w = z * z;
+    const double t1 = w * (3.999999999940941908e-01 + w * (2.222219843214978396e-01 + w * 1.531383769920937332e-01));
+    const double t2 = z * (6.666666666666735130e-01 + w * (2.857142874366239149e-01 + w * (1.818357216161805012e-01 + w * 1.479819860511658591e-01)));
+    const double R = t2 + t1;
+    const double hfsq = 0.5 * f * f;
+    const double dk = double(e);
+    return dk * 6.93147180369123816490e-01 - ((hfsq - (s_ * (hfsq + R) + dk * 1.90821492927058770002e-10)) - f);
+}
 __device__ __forceinline__ double det_pow5(double x) { const double x2 = x * x; const double x4 = x2 * x2; return x4 * x; }
 
 constexpr double kPi = 3.1415926535897932385;  // main.h:20

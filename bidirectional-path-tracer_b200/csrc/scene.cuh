@@ -79,6 +79,16 @@ struct __align__(16) Tex {
 };
 static_assert(sizeof(Tex) == 80, "Tex must be 80 bytes");
 
+// constant_medium (constant_medium.h:8-61) + isotropic (material.h:149-171): bdpt_scene_set_media
+struct __align__(16) MediumDev {
+    double neg_inv_density;          // constant_medium.h:12
+    double r, g, b;                  // isotropic's colour
+    double lo[3], hi[3];             // bounds of the boundary mesh: a ray that misses them has no boundary hit
+    uint32_t first, count;           // boundary triangles in med_tris
+};
+static_assert(sizeof(MediumDev) == 96, "MediumDev must be 96 bytes");
+constexpr uint32_t kMediumPrim = 0x20000000u;   // hit / vertex prim of a scatter point inside medium k: kMediumPrim | k (prim IDs stay below 2^28)
+
 struct SceneView {
     const WideNode* wide_nodes;   // may be null (device-built tree): the binary walk is used
     uint32_t n_wide_nodes;
@@ -99,6 +109,9 @@ struct SceneView {
     const Tex* tex;               // texture table (bdpt_scene_set_textures), null when the scene has none
     const unsigned char* tex_data;
     uint32_t n_tex;
+    const MediumDev* media;       // participating media (bdpt_scene_set_media), null when the scene has none
+    const TriGeom* med_tris;      // their boundary meshes
+    uint32_t n_media;
     const uint32_t* lights;       // prim IDs, reference light-list order
     const double* light_area;     // running sums of light triangle areas in list order (triangle.h:206-212)
     uint32_t n_lights;

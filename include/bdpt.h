@@ -171,6 +171,25 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
  * context, not to the scene: call it before or after bdpt_scene_upload / bdpt_scene_upload_image, again to replace it,
  * with n_tex = 0 to drop it. */
 int bdpt_scene_set_textures(bdpt_ctx* ctx, const bdpt_texture* tex, uint32_t n_tex, const void* data, uint64_t data_bytes);
+/* Participating media: constant_medium (materials/volumes/constant_medium.h:8-61) with its isotropic phase function
+ * (material.h:149-171); SURVEY 8f-4.  Not reachable from the reference's loader either, so an extension of the scene surface
+ * like the textures.  A medium is a closed boundary mesh (a convex one for the reference's two-hit logic to mean "inside"),
+ * a density and a colour.  The boundary triangles are NOT world prims: they have no prim ID, no material and occlude nothing.
+ * bdpt_render then makes world.hit what it is in the reference with the media in the world list: after the triangle walk
+ * every medium is asked with the interval [tmin, nearest hit so far] (constant_medium.h:22-58: two boundary hits, clamp,
+ * ONE random draw, scatter distance -1/density * log(xi)); a scatter point is a path vertex with the isotropic material
+ * (uniform sphere scatter, f = albedo / 4 pi, the reference's arbitrary normal (1,0,0)); visible() lets a medium
+ * between two vertices scatter the shadow ray with the same probability.  BDPT_WEIGHT_REF_SUM only (BDPT_WEIGHT_MIS with
+ * media is refused); bdpt_trace / bdpt_visible stay triangle queries.  Limits: 16 media, 4096 boundary triangles each.
+ * Belongs to the context like the texture table: before or after the scene upload, again to replace, n_media = 0 to drop. */
+typedef struct {
+    double   density;        /* > 0 */
+    double   albedo[3];      /* isotropic's solid colour */
+    uint64_t first_tri;      /* boundary triangles [first_tri, first_tri + n_tris) of boundary_verts */
+    uint64_t n_tris;
+} bdpt_medium;
+int bdpt_scene_set_media(bdpt_ctx* ctx, const bdpt_medium* media, uint32_t n_media, const double* boundary_verts /* n x 9 */,
+                         uint64_t n_boundary_tris);
 int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth);
 
 /* ---- scene image: everything bdpt_scene_upload derives from the soup -- the flattened triangle

@@ -153,6 +153,21 @@ class Oracle:
             self.scene = self._create(verts.ctypes.data, mat_id.ctypes.data, len(verts), C.byref(marr), len(marr))
         return self
 
+    def set_media(self, media):
+        """media: list of (density, (r, g, b), boundary triangles as n x 9) -- constant_medium + isotropic."""
+        rows, soup, first = [], [], 0
+        for density, rgb, tris in media:
+            t = np.ascontiguousarray(tris, dtype=np.float64).reshape(-1, 9)
+            rows.append([float(density), float(rgb[0]), float(rgb[1]), float(rgb[2]), float(first), float(len(t))])
+            soup.append(t); first += len(t)
+        m6 = np.ascontiguousarray(rows, dtype=np.float64).reshape(-1, 6)
+        b = np.ascontiguousarray(np.concatenate(soup) if soup else np.zeros((0, 9)), dtype=np.float64)
+        f = getattr(self.lib, ("port_" if self.kind == "port" else "ref_") + "scene_set_media")
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+        f.restype = None
+        f(self.scene, m6.ctypes.data, len(m6), b.ctypes.data)
+        return self
+
     def texture_value(self, k, uvp):
         uvp = np.ascontiguousarray(uvp, dtype=np.float64).reshape(-1, 5)
         out = np.empty((len(uvp), 3), np.float64)

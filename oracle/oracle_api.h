@@ -89,6 +89,12 @@ void*    ORC(scene_create_tex)(const double* verts, const uint32_t* mat_id, uint
 /* texture k evaluated at n points: uvp = n x 5 doubles (u, v, px, py, pz) -> rgb = n x 3 doubles (texture.h value()) */
 void     ORC(texture_value)(void* scene, uint32_t tex_index, uint64_t n, const double* uvp, double* rgb);
 int      ref_texture_data(void* scene, uint32_t tex_index, void* out /* noise: 6144 + 3072 bytes; image: w*h*3 */);
+/* constant_medium (materials/volumes/constant_medium.h:8-61) + isotropic (material.h:149-171), SURVEY 8f-4: n_media x 6
+ * doubles {density, r, g, b, first boundary triangle, boundary triangle count} and the boundary soup (triangles x 9
+ * doubles, closed meshes; NOT world prims).  port: media are tested after the triangle walk, in list order (oracle/port.cpp
+ * hit_world); ref: real constant_medium objects around a bvh_node of the boundary, added to the world list. */
+void     ORC(scene_set_media)(void* scene, const double* media6, uint32_t n_media, const double* boundary_verts);
+double   port_det_log(double x);
 void     ORC(scene_destroy)(void* scene);
 uint64_t ORC(bvh_node_count)(void* scene);
 /* DFS leaf order: order[k] = prim ID of the k-th triangle in the builder's final array. */

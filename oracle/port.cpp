@@ -97,6 +97,30 @@ inline void det_sincos(double phi, double& s_out, double& c_out) {
 }
 inline double det_pow5(double x) { const double x2 = x * x; const double x4 = x2 * x2; return x4 * x; }
 
+// Deterministic natural logarithm for ORC_RNG_PHILOX mode (constant_medium.h:44 draws log(random_double()) inside hit()):
+// fdlibm's __ieee754_log as a fixed sequence of IEEE +, -, *, / on the argument's mantissa and exponent, so the CUDA
+// kernels (csrc/render_math.cuh: det_log, same constants, same order, -fmad=false) and this port agree bit for bit.
+// x in [0, 1): 0 -> -inf; the smallest non-zero draw is 2^-53, a normal number.
+inline double det_log(double x) {
+    if (!(x > 0.0)) return -std::numeric_limits<double>::infinity();
+    uint64_t bits;
+    std::memcpy(&bits, &x, 8);
+    int e = int((bits >> 52) & 0x7FF) - 1023;
+    bits = (bits & 0x000FFFFFFFFFFFFFull) | 0x3FF0000000000000ull;
+    double m;
+    std::memcpy(&m, &bits, 8);
+    if (m > 1.4142135623730951) { m = m * 0.5; e += 1; }
+    const double f = m - 1.0;
+    const double s_ = f / (2.0 + f);
+    const double z = s_ * s_, w = z * z;
+    const double t1 = w * (3.999999999940941908e-01 + w * (2.222219843214978396e-01 + w * 1.531383769920937332e-01));
+    const double t2 = z * (6.666666666666735130e-01 + w * (2.857142874366239149e-01 + w * (1.818357216161805012e-01 + w * 1.479819860511658591e-01)));
+    const double R = t2 + t1;
+    const double hfsq = 0.5 * f * f;
+    const double dk = double(e);
+    return dk * 6.93147180369123816490e-01 - ((hfsq - (s_ * (hfsq + R) + dk * 1.90821492927058770002e-10)) - f);
+}
+
 struct Rng {
     bool det = false;  // PHILOX mode: deterministic sin/cos/pow5 (see above)
     // mode MT: all streams alias one engine, exactly the reference's single global stream
@@ -275,7 +299,17 @@ struct Node {
     bool leaf;
 };
 
+// constant_medium (materials/volumes/constant_medium.h:8-61) with its isotropic phase function (material.h:149-171): a closed
+// boundary mesh, kept OUTSIDE the world soup (its triangles have no prim ID and no material), a density and a colour.
+constexpr uint32_t kMediumPrim = 0x20000000u;   // Hit.prim of a scatter point inside medium k: kMediumPrim | k
+struct Medium {
+    double neg_inv_density;
+    V3 albedo;
+    std::vector<Tri> boundary;
+};
+
 struct Scene {
+    std::vector<Medium> media;
     std::vector<Tri> tris;
     std::vector<orc_material> mats;
     std::vector<orc_texture> tex;
@@ -383,6 +417,56 @@ struct Scene {
         ++tl_stats.rays;
         return hit_node(root, o, d, tmin, tmax, rec);
     }
+
+    // boundary->hit(r, ray_t): the boundary as a list of triangles in order (triangle_collection::hit, triangle.h:150-164);
+    // only t is used by the medium
+    static bool boundary_hit(const Medium& m, V3 o, V3 d, double tmin, double tmax, double& t_out) {
+        bool any = false;
+        double closest = tmax;
+        Hit tmp;
+        for (const Tri& tr : m.boundary)
+            if (tri_hit(tr, 0, o, d, tmin, closest, tmp)) { any = true; closest = tmp.t; }
+        t_out = closest;
+        return any;
+    }
+    // constant_medium::hit, constant_medium.h:22-58.  ONE draw, taken only when the ray's part inside the boundary
+    // overlaps ray_t.
+    static bool medium_hit(const Medium& m, V3 o, V3 d, double tmin, double tmax, Rng& rng, double& t_out) {
+        double t1, t2;
+        if (!boundary_hit(m, o, d, -kInf, kInf, t1)) return false;
+        if (!boundary_hit(m, o, d, t1 + 0.0001, kInf, t2)) return false;
+        if (t1 < tmin) t1 = tmin;
+        if (t2 > tmax) t2 = tmax;
+        if (t1 >= t2) return false;
+        if (t1 < 0) t1 = 0;
+        const double ray_length = len(d);
+        const double distance_inside_boundary = (t2 - t1) * ray_length;
+        const double xi = rng.next();
+        const double hit_distance = m.neg_inv_density * (rng.det ? det_log(xi) : std::log(xi));
+        if (hit_distance > distance_inside_boundary) return false;
+        t_out = t1 + hit_distance / ray_length;
+        return true;
+    }
+    // world.hit with media in the world list.  The reference reaches a medium whenever its BVH walk gets to it, with the
+    // bound found so far; here the triangles go first and every medium then sees [tmin, best]: one draw per medium either
+    // way, and the same event decides (scatter before the nearer of exit and best), so the outcome has the same
+    // distribution whatever the visiting order.  `key`: ORC_RNG_PHILOX draw index of medium 0 for this query (media take
+    // key, key + 1, ...; the path streams pass their running counter and get it back advanced by the draws taken).
+    bool hit_world(V3 o, V3 d, double tmin, double tmax, Hit& rec, Rng& rng) const {
+        bool found = hit(o, d, tmin, tmax, rec);
+        double best = found ? rec.t : tmax;
+        for (size_t k = 0; k < media.size(); ++k) {
+            double t;
+            if (medium_hit(media[k], o, d, tmin, best, rng, t)) {
+                found = true; best = t;
+                rec.t = t; rec.p = o + t * d;
+                rec.normal = V3{1, 0, 0}; rec.front = true;   // constant_medium.h:52-53: arbitrary
+                rec.u = 0; rec.v = 0;
+                rec.prim = kMediumPrim | uint32_t(k);
+            }
+        }
+        return found;
+    }
 };
 
 // ---------------------------------------------------------------- camera.h
@@ -432,6 +516,8 @@ struct Vertex {  // camera.h:236-243
     V3 p, normal, throughput, wi, emission, albedo;
     uint32_t mat;
     bool delta, is_light;
+    bool iso = false;   // a scatter point inside a constant_medium: the material is its isotropic phase function
+    int index = 0;      // position on its subpath (camera: bounce; light: 0 = the emitter, then 1 + bounce)
 };
 
 struct Integrator {
@@ -449,16 +535,40 @@ struct Integrator {
         if (m.type != ORC_MAT_LAMBERTIAN) return {0, 0, 0};
         return albedo / kPi;
     }
+    V3 eval_bsdf(const Vertex& v) const {
+        if (v.iso) return v.albedo / (4 * kPi);               // isotropic::evaluate_bsdf, material.h:166-168
+        return eval_bsdf(sc.mats[v.mat], v.albedo);
+    }
 
-    void trace_path(V3 o, V3 d, int depth, std::vector<Vertex>& path, V3 T, V3* bg, Rng& rng) const {  // camera.h:325-370
+    void trace_path(V3 o, V3 d, int depth, std::vector<Vertex>& path, V3 T, V3* bg, Rng& rng, int index0 = 0) const {  // camera.h:325-370
         for (int bounce = 0; bounce < depth; ++bounce) {
             Hit rec;
-            if (!sc.hit(o, d, 0.001, kInf, rec)) {
+            if (!(sc.media.empty() ? sc.hit(o, d, 0.001, kInf, rec) : sc.hit_world(o, d, 0.001, kInf, rec, rng))) {
                 if (bg) *bg = *bg + T * cam.background;
                 break;
             }
+            if (rec.prim & kMediumPrim) {   // scattered inside a medium: isotropic (material.h:149-171)
+                const Medium& md = sc.media[rec.prim & ~kMediumPrim];
+                Vertex vx;
+                vx.p = rec.p; vx.normal = rec.normal; vx.mat = 0;
+                vx.throughput = T;
+                vx.wi = unit(-d);
+                vx.emission = V3{0, 0, 0};
+                vx.albedo = md.albedo;
+                vx.delta = false; vx.is_light = false; vx.iso = true; vx.index = index0 + bounce;
+                path.push_back(vx);
+                // scatter: attenuation = albedo, sphere_pdf (pdf.h:18-29): generate() = random_unit_vector, value = 1/(4 pi);
+                // scattering_pdf = 1/(4 pi) (material.h:161-164); camera.h:361-368
+                V3 sd = random_unit_vector(rng);
+                double pdf_value = 1 / (4 * kPi);
+                double spdf = 1 / (4 * kPi);
+                T = T * md.albedo * spdf / pdf_value;
+                o = rec.p; d = sd;
+                continue;
+            }
             const orc_material& m = sc.mats[sc.tris[rec.prim].mat];
             Vertex vx;
+            vx.index = index0 + bounce;
             vx.p = rec.p; vx.normal = rec.normal; vx.mat = sc.tris[rec.prim].mat;
             vx.throughput = T;
             vx.wi = unit(-d);
@@ -542,7 +652,7 @@ struct Integrator {
         if (cos_theta <= 0) return true;
         double pdf_dir = std::max(cos_theta / kPi, 1e-8);
         V3 T = ev.throughput * emission * (cos_theta / pdf_dir);
-        trace_path(pos + (0.001 * n), du, depth - 1, path, T, nullptr, rng);
+        trace_path(pos + (0.001 * n), du, depth - 1, path, T, nullptr, rng, 1);
         return true;
     }
 
@@ -557,8 +667,28 @@ struct Integrator {
         ++tl_stats.shadow;
         return !sc.hit(a + (0.001 * du), du, 0.001, max_t, tmp);
     }
+    // the same with media in the world: a medium between the two points scatters the shadow ray with the probability
+    // constant_medium::hit gives it (one draw per medium crossed).  ORC_RNG_PHILOX: the draw of medium k for the pair
+    // (camera vertex ci, light vertex li) is draw ((ci * 128 + li) * 16 + k) of the sample's shadow stream (stream 2).
+    bool visible_media(V3 a, V3 b, Rng& shadow_rng, int ci, int li) const {
+        V3 dir = b - a;
+        double dist = len(dir);
+        if (dist <= 0) return false;
+        V3 du = dir / dist;
+        double max_t = dist - 0.001;
+        if (max_t <= 0) return false;
+        ++tl_stats.shadow;
+        const V3 so = a + (0.001 * du);
+        for (size_t k = 0; k < sc.media.size(); ++k) {
+            if (!shadow_rng.mt) shadow_rng.draws = uint32_t((ci * 128 + li) * 16 + int(k));
+            double t;
+            if (Scene::medium_hit(sc.media[k], so, du, 0.001, max_t, shadow_rng, t)) return false;
+        }
+        Hit tmp;
+        return !sc.hit(so, du, 0.001, max_t, tmp);
+    }
 
-    V3 connect(const Vertex& cv, const Vertex& lv) const {  // camera.h:440-475
+    V3 connect(const Vertex& cv, const Vertex& lv, Rng* shadow_rng = nullptr) const {  // camera.h:440-475
         if (cv.delta || lv.delta) return {0, 0, 0};
         V3 dir = lv.p - cv.p;
         double dist2 = len2(dir);
@@ -567,10 +697,10 @@ struct Integrator {
         double cos_cam = std::fabs(dot(cv.normal, du));
         double cos_light = std::fabs(dot(lv.normal, -du));
         if (cos_cam <= 0 || cos_light <= 0) return {0, 0, 0};
-        if (!visible(cv.p, lv.p)) return {0, 0, 0};
-        V3 f_cam = eval_bsdf(sc.mats[cv.mat], cv.albedo);
+        if (!(sc.media.empty() ? visible(cv.p, lv.p) : visible_media(cv.p, lv.p, *shadow_rng, cv.index, lv.index))) return {0, 0, 0};
+        V3 f_cam = eval_bsdf(cv);
         if (len2(f_cam) <= 0) return {0, 0, 0};
-        V3 f_light = lv.is_light ? lv.emission : eval_bsdf(sc.mats[lv.mat], lv.albedo);
+        V3 f_light = lv.is_light ? lv.emission : eval_bsdf(lv);
         if (len2(f_light) <= 0) return {0, 0, 0};
         V3 contrib = cv.throughput * f_cam;
         contrib = contrib * lv.throughput * f_light;
@@ -796,8 +926,10 @@ struct Integrator {
             if (!vx.delta && len2(vx.emission) > 0) result = result + vx.throughput * vx.emission;
         lp.reserve(depth);
         if (!build_light_path(depth, lp, light_rng)) return result;
+        Rng shadow = cam_rng;   // media only: the sample's shadow stream (MT mode: the one global stream, as the reference)
+        if (!shadow.mt) { shadow.stream = 2; shadow.draws = 0; }
         for (const auto& cv : cp)
-            for (const auto& lv : lp) result = result + connect(cv, lv);
+            for (const auto& lv : lp) result = result + connect(cv, lv, &shadow);
         return result;
     }
 };
@@ -854,6 +986,25 @@ void port_texture_value(void* p, uint32_t k, uint64_t n, const double* uvp, doub
     }
 }
 void port_scene_destroy(void* p) { delete static_cast<Scene*>(p); }
+
+// media: n x {density, r, g, b, first boundary triangle, boundary triangle count} as doubles; boundary: triangles x 9 doubles
+void port_scene_set_media(void* p, const double* media6, uint32_t n_media, const double* boundary) {
+    auto* s = static_cast<Scene*>(p);
+    s->media.clear();
+    for (uint32_t k = 0; k < n_media; ++k) {
+        const double* m = media6 + 6 * k;
+        Medium md;
+        md.neg_inv_density = -1 / m[0];   // constant_medium.h:12
+        md.albedo = V3{m[1], m[2], m[3]};
+        const uint64_t first = uint64_t(m[4]), cnt = uint64_t(m[5]);
+        for (uint64_t i = first; i < first + cnt; ++i) {
+            const double* q = boundary + 9 * i;
+            md.boundary.push_back(make_tri({q[0], q[1], q[2]}, {q[3], q[4], q[5]}, {q[6], q[7], q[8]}, 0));
+        }
+        s->media.push_back(md);
+    }
+}
+double port_det_log(double x) { return det_log(x); }
 uint64_t port_bvh_node_count(void* p) { return static_cast<Scene*>(p)->nodes.size(); }
 void port_bvh_leaf_order(void* p, uint32_t* order) {
     auto* s = static_cast<Scene*>(p);

@@ -43,6 +43,7 @@
 #include "material.h"
 #include "triangle.h"
 #include "texture.h"
+#include "constant_medium.h"
 #undef private
 
 #define ORC_PREFIX ref_
@@ -210,6 +211,26 @@ static void* create_scene(const double* v, const uint32_t* mat_id, uint64_t n, c
     s->nodes = bvh_stats().bvh_nodes_built.load();
     collect_leaf_order(s->bvh.get(), s->leaf_order);
     return s;
+}
+
+// constant_medium (constant_medium.h:8-61) objects of the reference's own, each around a bvh_node of its boundary triangles,
+// added to the world list beside the id-carrying triangles; the world BVH is rebuilt over all of them (main.cpp:66).
+void ref_scene_set_media(void* p, const double* media6, uint32_t n_media, const double* boundary) {
+    auto* s = static_cast<ref_scene*>(p);
+    hittable_list list;
+    for (size_t i = 0; i < s->world.tris.size(); ++i) list.add(make_shared<id_triangle>(s->world.tris[i], uint32_t(i)));
+    auto skin = make_shared<lambertian>(color(0, 0, 0));   // a boundary is only ever asked for t
+    for (uint32_t k = 0; k < n_media; ++k) {
+        const double* m = media6 + 6 * k;
+        hittable_list b;
+        const uint64_t first = uint64_t(m[4]), cnt = uint64_t(m[5]);
+        for (uint64_t i = first; i < first + cnt; ++i) {
+            const double* q = boundary + 9 * i;
+            b.add(make_shared<triangle>(point3(q[0], q[1], q[2]), point3(q[3], q[4], q[5]), point3(q[6], q[7], q[8]), skin));
+        }
+        list.add(make_shared<constant_medium>(make_shared<bvh_node>(b), m[0], color(m[1], m[2], m[3])));
+    }
+    s->bvh = make_shared<bvh_node>(list);
 }
 
 void ref_scene_destroy(void* p) { delete static_cast<ref_scene*>(p); }

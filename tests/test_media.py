@@ -1,0 +1,77 @@
+"""Participating media: constant_medium + isotropic (/root/reference/src/materials/volumes/constant_medium.h:8-61,
+materials/material.h:149-171) -- bdpt_scene_set_media.
+  CPU: the port's restatement (oracle/port.cpp: hit_world / medium_hit / visible_media) against the reference's OWN
+       constant_medium objects in a bvh_node world (oracle/_ref): the two draw their random numbers in different orders
+       (the reference whenever its BVH walk reaches the medium, the port after the triangle walk), so the pin is
+       statistical -- image means within Monte-Carlo error, and far from the medium-free image.
+  GPU: film equal to the port's sample for sample on the counter-based stream (tolerance 1e-9 of the peak: fp64 atomics
+       reorder the adds), both tree flavours; the draw inside constant_medium::hit goes through a deterministic log shared
+       bit for bit by the kernels and the port."""
+import numpy as np
+import pytest
+
+from oracle.oracle import Oracle, available, make_camera as ocam, RNG_MT19937, RNG_PHILOX
+from tools import testscenes as ts
+
+
+def rel_err(a, b):
+    return float(np.abs(a - b).max() / max(1e-300, np.abs(b).max()))
+
+
+@pytest.mark.skipif(not available("ref"), reason="oracle/_ref not shipped")
+def test_port_media_agree_with_the_references_own_constant_medium():
+    v, m, mats, cam = ts.cornell(False)
+    media = ts.cornell_media()
+    W = H = 20
+    spp, depth, seeds = 36, 6, 4
+    c = ocam(W, H, spp, depth, **cam)
+    port = sum(Oracle("port").load(v, m, mats).set_media(media).render(c, rng_mode=RNG_MT19937, seed=s, height=H) for s in range(1, 1 + seeds))
+    ref = sum(Oracle("ref").load(v, m, mats).set_media(media).render(c, rng_mode=RNG_MT19937, seed=50 + s, height=H) for s in range(1, 1 + seeds))
+    clear = sum(Oracle("port").load(v, m, mats).render(c, rng_mode=RNG_MT19937, seed=s, height=H) for s in range(1, 1 + seeds))
+    mp, mr = port.mean(axis=(0, 1)), ref.mean(axis=(0, 1))
+    assert np.all(np.abs(mp / mr - 1.0) < 0.06), (mp, mr)           # 4 x 36 spp x 400 pixels: ~2 % noise on the mean
+    assert clear.mean() / ref.mean() > 1.08                          # the smoke is not a no-op (per-seed means: 7.8 against 6.8)
+
+
+def test_det_log_is_log_to_the_last_bit_or_so():
+    import ctypes as C
+    import math
+    f = Oracle("port").lib.port_det_log
+    f.restype = C.c_double; f.argtypes = [C.c_double]
+    rng = np.random.default_rng(5)
+    xs = np.concatenate([rng.random(20000), rng.random(500) * 1e-12, [2.0 ** -53, 0.5, 1 - 2.0 ** -53, 0.70710678, 0.70710679]])
+    assert max(abs(f(float(x)) - math.log(x)) / abs(math.log(x)) for x in xs) < 4e-16
+    assert f(0.0) == -math.inf
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bvh", [0, 1])
+@pytest.mark.parametrize("name", ["cornell_box", "cornell_spheres"])
+def test_media_film_equals_the_port_sample_for_sample(name, bvh, bdpt, scenes):
+    v, m, mats, cam = scenes[name]()
+    media = ts.cornell_media()
+    W, H, spp, depth = 36, 28, 4, 7
+    ref = Oracle("port").load(v, m, mats).set_media(media).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=42,
+                                                                  nthreads=8, height=H)
+    clear = Oracle("port").load(v, m, mats).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=42, nthreads=8, height=H)
+    assert rel_err(clear, ref) > 0.05                              # the media change the image
+    with bdpt.Context(0) as ctx:
+        ctx.set_media(media)                                        # before the upload: belongs to the context
+        ctx.upload(v, m, mats)
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H)
+        assert rel_err(ctx.film(), ref) < 1e-9
+        with pytest.raises(bdpt.BdptError, match="media"):
+            ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
+        ctx.set_media([])                                           # dropped: the plain scene again
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H)
+        assert rel_err(ctx.film(), clear) < 1e-9
+
+
+@pytest.mark.gpu
+def test_media_argument_checks(bdpt):
+    with bdpt.Context(0) as ctx:
+        box = ts.box_mesh((0, 0, 0), (1, 1, 1))
+        with pytest.raises(bdpt.BdptError, match="density"):
+            ctx.set_media([(0.0, (1, 1, 1), box)])
+        with pytest.raises(bdpt.BdptError, match="16"):
+            ctx.set_media([(1.0, (1, 1, 1), box)] * 17)

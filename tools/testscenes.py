@@ -237,3 +237,20 @@ def sphere_grid(g=50, lat_steps=41, lon_steps=50, spacing=2.5, radius=1.0):
     v, mid, mats = sb.done()
     cam = dict(lookfrom=(0.0, 0.55 * ext, -0.75 * ext), lookat=(0.0, 0.0, 0.0), vfov=40.0)
     return v, mid, mats, cam
+
+
+def box_mesh(lo, hi):
+    """The 12 triangles of an axis-aligned box (a closed convex boundary for constant_medium), n x 9."""
+    lo = np.asarray(lo, np.float64); hi = np.asarray(hi, np.float64)
+    c = np.array([[lo[0] if not i & 1 else hi[0], lo[1] if not i & 2 else hi[1], lo[2] if not i & 4 else hi[2]] for i in range(8)])
+    faces = [(0, 1, 3, 2), (4, 6, 7, 5), (0, 4, 5, 1), (2, 3, 7, 6), (0, 2, 6, 4), (1, 5, 7, 3)]
+    t = []
+    for a, b, cc, d in faces:
+        t.append(np.concatenate([c[a], c[b], c[cc]])); t.append(np.concatenate([c[a], c[cc], c[d]]))
+    return np.array(t)
+
+
+def cornell_media():
+    """Two overlapping box-shaped media for the Cornell room: a dense white smoke and a thin blue one (density, colour, boundary)."""
+    return [(0.01, (0.9, 0.9, 0.9), box_mesh((100, 0, 100), (300, 300, 300))),
+            (0.004, (0.2, 0.4, 0.9), box_mesh((250, 150, 50), (500, 400, 250)))]
