@@ -30,28 +30,66 @@ rotate_y::rotate_y(shared_ptr<hittable> obj, double angle_degrees) : object(std:
     cos_theta = std::cos(radians);
 }
 
-void collect_triangles(const hittable& h, std::vector<triangle>& out) {
+void collect_triangles(const hittable& h, std::vector<triangle>& out, std::vector<constant_medium>* media) {
     if (auto t = dynamic_cast<const triangle*>(&h)) { out.push_back(*t); return; }
     if (auto c = dynamic_cast<const triangle_collection*>(&h)) { out.insert(out.end(), c->tris.begin(), c->tris.end()); return; }
-    if (auto b = dynamic_cast<const bvh_node*>(&h)) { out.insert(out.end(), b->prims.begin(), b->prims.end()); return; }
-    if (auto l = dynamic_cast<const hittable_list*>(&h)) { for (const auto& o : l->objects) collect_triangles(*o, out); return; }
-    const size_t first = out.size();
+    if (auto b = dynamic_cast<const bvh_node*>(&h)) {
+        out.insert(out.end(), b->prims.begin(), b->prims.end());
+        if (!b->media.empty()) {
+            if (!media) throw std::runtime_error("collect_triangles: a constant_medium where only triangles are allowed");
+            media->insert(media->end(), b->media.begin(), b->media.end());
+        }
+        return;
+    }
+    if (auto l = dynamic_cast<const hittable_list*>(&h)) { for (const auto& o : l->objects) collect_triangles(*o, out, media); return; }
+    if (auto cm = dynamic_cast<const constant_medium*>(&h)) {
+        if (!media) throw std::runtime_error("collect_triangles: a constant_medium where only triangles are allowed");
+        media->push_back(*cm);
+        return;
+    }
+    const size_t first = out.size(), first_medium = media ? media->size() : 0;
+    // a transform around a medium moves its boundary: the medium's boundary is replaced by the moved triangles
+    auto move_media = [&](auto&& wrap) {
+        if (!media) return;
+        for (size_t k = first_medium; k < media->size(); ++k) {
+            auto moved = make_shared<triangle_collection>();
+            collect_triangles(*wrap((*media)[k].boundary), moved->tris);
+            (*media)[k].boundary = moved;
+        }
+    };
     if (auto tr = dynamic_cast<const translate*>(&h)) {
-        collect_triangles(*tr->object, out);
+        collect_triangles(*tr->object, out, media);
         for (size_t i = first; i < out.size(); ++i)
             for (point3* p : {&out[i].v0, &out[i].v1, &out[i].v2})   // hittable.h:64: rec.p += offset
                 *p = point3(p->x() + tr->offset.x(), p->y() + tr->offset.y(), p->z() + tr->offset.z());
+        move_media([&](const shared_ptr<hittable>& b) { return make_shared<translate>(b, tr->offset); });
         return;
     }
     if (auto ro = dynamic_cast<const rotate_y*>(&h)) {
-        collect_triangles(*ro->object, out);
+        collect_triangles(*ro->object, out, media);
         const double c = ro->cos_theta, s = ro->sin_theta;
         for (size_t i = first; i < out.size(); ++i)
             for (point3* p : {&out[i].v0, &out[i].v1, &out[i].v2})   // object -> world, hittable.h:134-138
                 *p = point3((c * p->x()) + (s * p->z()), p->y(), (-s * p->x()) + (c * p->z()));
+        move_media([&](const shared_ptr<hittable>& b) { auto r = make_shared<rotate_y>(b, 0.0); r->sin_theta = s; r->cos_theta = c; return r; });
         return;
     }
     throw std::runtime_error("collect_triangles: unknown hittable (triangle, triangle_collection, hittable_list, bvh_node, translate, rotate_y)");
+}
+
+void flatten_media(const std::vector<constant_medium>& media, std::vector<bdpt_medium>& out, std::vector<double>& boundary_verts) {
+    out.clear(); boundary_verts.clear();
+    for (const constant_medium& m : media) {
+        std::vector<triangle> tris;
+        collect_triangles(*m.boundary, tris);
+        bdpt_medium d{};
+        d.density = m.density;
+        d.albedo[0] = m.albedo.x(); d.albedo[1] = m.albedo.y(); d.albedo[2] = m.albedo.z();
+        d.first_tri = boundary_verts.size() / 9; d.n_tris = tris.size();
+        for (const triangle& t : tris)
+            for (const point3* p : {&t.v0, &t.v1, &t.v2}) { boundary_verts.push_back(p->x()); boundary_verts.push_back(p->y()); boundary_verts.push_back(p->z()); }
+        out.push_back(d);
+    }
 }
 
 void print_bvh_stats(std::ostream& os, const render_report& r) {   // stats.h:34-50, same lines
@@ -67,9 +105,13 @@ void camera::render(const hittable& world, const hittable& lights) {
     (void)lights;
     const std::vector<triangle>* prims = nullptr;
     std::vector<triangle> collected;
-    if (auto b = dynamic_cast<const bvh_node*>(&world)) prims = &b->prims;
+    std::vector<constant_medium> media = options.media;
+    if (auto b = dynamic_cast<const bvh_node*>(&world)) { prims = &b->prims; media.insert(media.end(), b->media.begin(), b->media.end()); }
     else if (auto t = dynamic_cast<const triangle_collection*>(&world)) prims = &t->tris;
-    else { collect_triangles(world, collected); prims = &collected; }   // hittable_list, translate, rotate_y (hittable.h:46-157)
+    else { collect_triangles(world, collected, &media); prims = &collected; }   // hittable_list, translate, rotate_y, constant_medium
+    std::vector<bdpt_medium> media_desc;
+    std::vector<double> media_verts;
+    flatten_media(media, media_desc, media_verts);
     bool from_image = options.scene_image != nullptr;
     const void* image = options.scene_image;
     uint64_t image_bytes = options.scene_image_bytes;
@@ -115,6 +157,8 @@ void camera::render(const hittable& world, const hittable& lights) {
             else check(bdpt_scene_upload(ctx, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx, "bdpt_scene_upload");
             if (!textures.empty())
                 check(bdpt_scene_set_textures(ctx, textures.data(), uint32_t(textures.size()), tex_data.data(), tex_data.size()), ctx, "bdpt_scene_set_textures");
+            if (!media_desc.empty())
+                check(bdpt_scene_set_media(ctx, media_desc.data(), uint32_t(media_desc.size()), media_verts.data(), media_verts.size() / 9), ctx, "bdpt_scene_set_media");
             check(bdpt_film_clear(ctx, W, H), ctx, "bdpt_film_clear");
             bdpt_render_opts o{};
             o.seed = options.seed; o.stratum_begin = g; o.stratum_step = G; o.bvh = options.bvh;

@@ -66,6 +66,20 @@ int bdpt_scene_file_textures(const bdpt_scene_file* f, uint32_t* n_tex, bdpt_tex
     return BDPT_OK;
 }
 
+int bdpt_scene_file_media(const bdpt_scene_file* f, uint32_t* n_media, bdpt_medium* media, uint64_t* n_boundary_tris, double* boundary_verts) {
+    if (!f) return BDPT_ERR_ARG;
+    try {
+        std::vector<bdpt_medium> d;
+        std::vector<double> v;
+        flatten_media(f->scene.cam.options.media, d, v);
+        if (n_media) *n_media = uint32_t(d.size());
+        if (n_boundary_tris) *n_boundary_tris = v.size() / 9;
+        if (media && !d.empty()) std::memcpy(media, d.data(), d.size() * sizeof(bdpt_medium));
+        if (boundary_verts && !v.empty()) std::memcpy(boundary_verts, v.data(), v.size() * sizeof(double));
+    } catch (const std::exception& e) { g_host_err = e.what(); return BDPT_ERR_ARG; }
+    return BDPT_OK;
+}
+
 int bdpt_scene_file_info(const bdpt_scene_file* f, uint64_t* n_tris, uint32_t* n_mats, uint64_t* n_lights,
                          bdpt_camera* cam, char* output_name, uint64_t output_cap) {
     if (!f) return BDPT_ERR_ARG;

@@ -78,6 +78,7 @@ class material {
     color rgb;       // albedo or emission
     double param;    // fuzz or refraction index
     shared_ptr<texture> tex;   // lambertian albedo / light emission through a texture (material.h:45,136), else null
+    bool phase = false;        // isotropic: only meaningful inside a constant_medium (flatten_triangles refuses it on a triangle)
     virtual bool is_delta() const { return kind == Metal || kind == Dielectric; }   // material.h:38,85,118
   protected:
     material(kind_t k, const color& c, double p) : kind(k), rgb(c), param(p) {}
@@ -99,6 +100,11 @@ class diffuse_light : public material {  // material.h:133-147
   public:
     explicit diffuse_light(const color& emit) : material(DiffuseLight, emit, 0.0) {}
     explicit diffuse_light(shared_ptr<texture> t) : material(DiffuseLight, color(1, 1, 1), 0.0) { tex = std::move(t); }   // material.h:135
+};
+
+class isotropic : public material {      // material.h:149-171: the phase function of a constant_medium; not a surface material here
+  public:
+    explicit isotropic(const color& albedo) : material(Lambertian, albedo, 0.0) { phase = true; }
 };
 
 class hittable {
@@ -152,9 +158,24 @@ class rotate_y : public hittable {       // hittable.h:79-157 (angle in degrees,
     shared_ptr<hittable> object;
     double sin_theta, cos_theta;
 };
+// constant_medium (materials/volumes/constant_medium.h:8-61): a closed (convex) boundary, a density, the colour of its
+// isotropic phase function.  On the device: bdpt_scene_set_media (include/bdpt.h) -- the boundary's triangles are NOT
+// world prims.  Put one into the world list (hittable_list / bvh_node) like the reference does, or into
+// camera::options.media (what the YAML loader's `media:` section does).
+class constant_medium : public hittable {
+  public:
+    constant_medium(shared_ptr<hittable> boundary_, double density_, const color& albedo_)
+        : boundary(std::move(boundary_)), density(density_), albedo(albedo_) {}
+    shared_ptr<hittable> boundary;
+    double density;
+    color albedo;
+};
 // the triangles of any object graph (triangle, triangle_collection, hittable_list, bvh_node, translate, rotate_y), in
-// traversal order (= prim ID), in world space; throws on a hittable it does not know
-void collect_triangles(const hittable& h, std::vector<class triangle>& out);
+// traversal order (= prim ID), in world space; throws on a hittable it does not know.  constant_medium objects met on the
+// way go to `media` (with the transforms above them applied to their boundaries) when it is given, else they are an error.
+void collect_triangles(const hittable& h, std::vector<class triangle>& out, std::vector<constant_medium>* media = nullptr);
+// bdpt_scene_set_media's arguments from a list of media (boundaries flattened with collect_triangles)
+void flatten_media(const std::vector<constant_medium>& media, std::vector<bdpt_medium>& out, std::vector<double>& boundary_verts);
 
 // bvh_node(hittable_list) (bvh.h:13-18): here it only records the primitives, in list order (= prim ID);
 // both trees (reference topology and SAH) are built inside bdpt_scene_upload.
@@ -162,9 +183,10 @@ class bvh_node : public hittable {
   public:
     explicit bvh_node(hittable_list list) {
         prims.reserve(list.objects.size());
-        for (auto& o : list.objects) collect_triangles(*o, prims);   // triangles as they are; instances baked (above)
+        for (auto& o : list.objects) collect_triangles(*o, prims, &media);   // triangles as they are; instances baked (above)
     }
     std::vector<triangle> prims;
+    std::vector<constant_medium> media;   // constant_medium objects of the list
 };
 
 struct render_options {         // overrides the CLI adds on top of the YAML
@@ -178,6 +200,9 @@ struct render_options {         // overrides the CLI adds on top of the YAML (SU
     // of flattening `world` and building the trees, and `world` may be empty
     const void* scene_image = nullptr;
     uint64_t scene_image_bytes = 0;
+    // participating media beside the world (the YAML loader's `media:` section puts them here; a constant_medium inside the
+    // world list is found by render() itself)
+    std::vector<constant_medium> media;
 };
 
 struct render_report {

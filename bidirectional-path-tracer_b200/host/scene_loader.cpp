@@ -301,6 +301,57 @@ void load_camera(const node& n, camera& cam) {                       // scene_lo
 
 }  // namespace
 
+namespace {
+void load_media(const node& root, camera& cam) {
+    // Extension of the reference's schema (it can construct no constant_medium, constant_medium.h:8-61):
+    //   media:
+    //     - density: 0.01
+    //       color: [230, 230, 230]                  (0-255 or 0-1, like a material's)
+    //       box: [[x0, y0, z0], [x1, y1, z1]]       an axis-aligned box as the boundary, or
+    //       vertices: [...] / triangles: [...]      a closed convex mesh, as a `mesh` surface spells it
+    //       transform: {rotate_y: deg, translate: [x, y, z]}
+    // They land in cam.options.media: camera::render hands them to bdpt_scene_set_media beside the world.
+    const node& media = root["media"];
+    if (media.is_sequence()) {
+        for (const auto& md : media.seq) {
+            if (!md.is_map()) throw std::runtime_error("media entries must be mappings");
+            const double density = to_double(md["density"], 0.0);
+            if (!(density > 0.0)) throw std::runtime_error("medium: density must be > 0");
+            auto boundary = make_shared<triangle_collection>();
+            auto skin = make_shared<lambertian>(color(0, 0, 0));
+            const auto box = md["box"];
+            if (box.is_sequence()) {
+                if (box.seq.size() != 2) throw std::runtime_error("medium: box must be [[x0, y0, z0], [x1, y1, z1]]");
+                const auto lo = to_double_list(box.seq[0]), hi = to_double_list(box.seq[1]);
+                if (lo.size() != 3 || hi.size() != 3) throw std::runtime_error("medium: box must be [[x0, y0, z0], [x1, y1, z1]]");
+                point3 c[8];
+                for (int i = 0; i < 8; ++i) c[i] = point3(i & 1 ? hi[0] : lo[0], i & 2 ? hi[1] : lo[1], i & 4 ? hi[2] : lo[2]);
+                static const int faces[6][4] = {{0, 1, 3, 2}, {4, 6, 7, 5}, {0, 4, 5, 1}, {2, 3, 7, 6}, {0, 2, 6, 4}, {1, 5, 7, 3}};
+                for (const auto& q : faces) {
+                    boundary->add(triangle(c[q[0]], c[q[1]], c[q[2]], skin));
+                    boundary->add(triangle(c[q[0]], c[q[2]], c[q[3]], skin));
+                }
+            } else {
+                triangle_collection none;
+                sink bs{*boundary, none};
+                material_map no_mats;
+                load_indexed_mesh(md, bs, no_mats);
+            }
+            if (boundary->empty()) throw std::runtime_error("medium: empty boundary (give `box` or `vertices` + `triangles`)");
+            shared_ptr<hittable> obj = boundary;
+            const node& tf = md["transform"];
+            if (tf.is_map()) {
+                const auto off = to_double_list(tf["translate"]);
+                if (tf["translate"].defined() && off.size() != 3) throw std::runtime_error("transform.translate must be [x, y, z]");
+                if (tf["rotate_y"].defined()) obj = make_shared<rotate_y>(obj, to_double(tf["rotate_y"], 0.0));
+                if (off.size() == 3) obj = make_shared<translate>(obj, vec3(off[0], off[1], off[2]));
+            }
+            cam.options.media.emplace_back(obj, density, read_color_scaled(md["color"], color(1, 1, 1)));
+        }
+    } else if (media.defined()) throw std::runtime_error("media must be a sequence");
+}
+}  // namespace
+
 scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_loader.h:480-523
     const node root = yaml_lite::load_file(path);
     if (!root.is_map()) throw std::runtime_error("Scene root must be a mapping");
@@ -352,6 +403,7 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
             bake(result.lights.tris, l0);
         } else if (tf.defined()) throw std::runtime_error("transform must be a mapping {rotate_y: deg, translate: [x, y, z]}");
     }
+    load_media(root, result.cam);
     std::cout << "Triangles: " << result.world.size() << "\n";
     return result;
 }
@@ -361,6 +413,7 @@ camera load_camera_from_yaml(const std::string& path) {
     if (!root.is_map()) throw std::runtime_error("Scene root must be a mapping");
     camera cam;
     load_camera(root["camera"], cam);
+    load_media(root, cam);   // the scene-image cache holds the world only: media are re-read with the camera
     return cam;
 }
 
@@ -496,6 +549,7 @@ void flatten_triangles(const std::vector<triangle>& tris, std::vector<double>& v
         for (int k = 0; k < 3; ++k) for (int c = 0; c < 3; ++c) verts[9 * i + 3 * k + c] = (*p[k])[c];
         auto it = index.find(t.mat.get());
         if (it == index.end()) {
+            if (t.mat->phase) throw std::runtime_error("isotropic is the phase function of a constant_medium, not a surface material");
             bdpt_material m{};
             m.type = uint32_t(t.mat->kind);
             m.rgb[0] = t.mat->rgb.x(); m.rgb[1] = t.mat->rgb.y(); m.rgb[2] = t.mat->rgb.z();

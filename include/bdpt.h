@@ -303,6 +303,9 @@ int  bdpt_scene_file_copy(const bdpt_scene_file* f, double* verts, uint32_t* mat
 /* The scene's texture table for bdpt_scene_set_textures (a `texture:` map in a lambertian / light material: checker, noise,
  * image -- an extension of the reference's schema, host/scene_loader.cpp).  Call with tex = data = NULL for the sizes. */
 int  bdpt_scene_file_textures(const bdpt_scene_file* f, uint32_t* n_tex, bdpt_texture* tex, uint64_t* data_bytes, void* data);
+/* The scene's participating media for bdpt_scene_set_media (a `media:` section in the YAML -- an extension of the
+ * reference's schema, host/scene_loader.cpp).  Call with media = boundary_verts = NULL for the sizes. */
+int  bdpt_scene_file_media(const bdpt_scene_file* f, uint32_t* n_media, bdpt_medium* media, uint64_t* n_boundary_tris, double* boundary_verts);
 int  bdpt_write_png(const char* path, const uint8_t* rgb, int width, int height);
 /* Scene-image files: save writes to a temporary file of its own beside `path` ("<path>.<pid>.<n>.tmp"), syncs it and
  * renames it over `path`, so concurrent savers (ranks missing the same cache) never write into each other's file; map gives a read-only mapping of the file

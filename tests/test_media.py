@@ -75,3 +75,86 @@ def test_media_argument_checks(bdpt):
             ctx.set_media([(0.0, (1, 1, 1), box)])
         with pytest.raises(bdpt.BdptError, match="16"):
             ctx.set_media([(1.0, (1, 1, 1), box)] * 17)
+
+
+YAML = """
+camera:
+  resolution: [24, 24]
+  location: [278, 278, -800]
+  look_at: [278, 278, 0]
+  vfov: 40
+  samples_per_pixel: 4
+  max_depth: 6
+materials:
+  white: {type: lambertian, color: [186, 186, 186]}
+  lamp: {type: light, emission: [15, 15, 15]}
+surfaces:
+  - type: mesh
+    material: white
+    vertices: [[0, 0, 0], [555, 0, 0], [555, 0, 555], [0, 0, 555], [0, 555, 555], [555, 555, 555]]
+    triangles: [[0, 1, 2], [0, 2, 3], [3, 2, 5], [3, 5, 4]]
+  - type: mesh
+    material: lamp
+    vertices: [[213, 554, 227], [343, 554, 227], [343, 554, 332], [213, 554, 332]]
+    triangles: [[0, 1, 2], [0, 2, 3]]
+media:
+  - density: 0.01
+    color: [230, 230, 230]
+    box: [[100, 0, 100], [300, 300, 300]]
+  - density: 0.004
+    color: [0.2, 0.4, 0.9]
+    vertices: [[0, 0, 0], [250, 0, 0], [0, 250, 0], [0, 0, 200]]
+    triangles: [[0, 2, 1], [0, 1, 3], [0, 3, 2], [1, 2, 3]]
+    transform:
+      rotate_y: 30
+      translate: [250, 150, 50]
+"""
+
+
+def test_yaml_media_section(bdpt, tmp_path):
+    """The loader's `media:` section (an extension, like `texture:` and `transform:`): a box and a transformed tetrahedron."""
+    import math
+    path = tmp_path / "smoke.yaml"
+    path.write_text(YAML)
+    s = bdpt.SceneFile(str(path))
+    assert len(s.media) == 2 and len(s.verts) == 6
+    d0, c0, b0 = s.media[0]
+    assert d0 == 0.01 and np.allclose(c0, [230 / 255.0] * 3, rtol=0, atol=1e-15) and b0.shape == (12, 9)
+    assert np.array_equal(b0.reshape(-1, 3).min(axis=0), [100, 0, 100]) and np.array_equal(b0.reshape(-1, 3).max(axis=0), [300, 300, 300])
+    assert np.array_equal(np.sort(b0.reshape(-1, 9), axis=0), np.sort(ts.box_mesh((100, 0, 100), (300, 300, 300)), axis=0))
+    d1, c1, b1 = s.media[1]
+    assert d1 == 0.004 and c1 == (0.2, 0.4, 0.9) and b1.shape == (4, 9)
+    r = 30 * 3.1415926535897932385 / 180.0
+    c, sn = math.cos(r), math.sin(r)
+    corner = np.array([250.0, 0.0, 0.0])                          # vertex 1 of the tetrahedron: rotate_y, then translate
+    want = np.array([(c * corner[0]) + (sn * corner[2]) + 250, corner[1] + 150, (-sn * corner[0]) + (c * corner[2]) + 50])
+    assert any(np.array_equal(p, want) for p in b1.reshape(-1, 3))
+    bad = tmp_path / "bad.yaml"
+    bad.write_text(YAML.replace("density: 0.01", "density: 0"))
+    with pytest.raises(bdpt.BdptError, match="density"):
+        bdpt.SceneFile(str(bad))
+
+
+@pytest.mark.gpu
+def test_cli_renders_a_yaml_scene_with_media(bdpt, tmp_path):
+    """bdpt scene.yaml (host/main.cpp -> camera::render -> bdpt_scene_set_media) writes the PNG the ctypes path computes."""
+    import os
+    import subprocess
+    path = tmp_path / "smoke.yaml"
+    path.write_text(YAML.replace("resolution: [24, 24]", "resolution: [24, 24]\n  output: smoke.png"))
+    exe = os.path.join(os.path.dirname(bdpt.LIB_PATH), "bdpt")
+    r = subprocess.run([exe, str(path), "--seed", "9", "--quiet"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    s = bdpt.SceneFile(str(path))
+    with bdpt.Context(0) as ctx:
+        ctx.set_media(s.media)
+        ctx.upload(s.verts, s.mat_id, s.materials)
+        ctx.render(s.camera, seed=9, bvh=bdpt.BVH_FAST)
+        rgb = ctx.film_rgb8(4)
+        ctx.set_media([])
+        ctx.render(s.camera, seed=9, bvh=bdpt.BVH_FAST)
+        clear = ctx.film_rgb8(4)
+    assert (rgb != clear).mean() > 0.05
+    ref_png = tmp_path / "ctypes.png"
+    bdpt.write_png(str(ref_png), rgb)
+    assert (tmp_path / "output" / "smoke.png").read_bytes() == ref_png.read_bytes()
