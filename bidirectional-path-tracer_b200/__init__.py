@@ -35,12 +35,16 @@ EXPORTS = [
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
     "bdpt_scene_set_textures", "bdpt_scene_file_textures", "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read", "bdpt_comm_attach",
-    "bdpt_film_to_rgb8_noalloc", "bdpt_scene_set_media", "bdpt_scene_file_media",
+    "bdpt_film_to_rgb8_noalloc", "bdpt_scene_set_media", "bdpt_scene_file_media", "bdpt_scene_set_spheres",
 ]
 
 
 class Material(C.Structure):
     _fields_ = [("type", C.c_uint32), ("tex", C.c_uint32), ("rgb", C.c_double * 3), ("param", C.c_double)]
+
+
+class Sphere(C.Structure):
+    _fields_ = [("center", C.c_double * 3), ("radius", C.c_double), ("mat_id", C.c_uint32), ("pad", C.c_uint32)]
 
 
 class Medium(C.Structure):
@@ -121,6 +125,7 @@ def lib():
         L.bdpt_scene_upload_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32]
         L.bdpt_scene_set_textures.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.bdpt_scene_set_media.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.bdpt_scene_set_spheres.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.bdpt_bvh_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
         L.bdpt_bvh_leaf_order.argtypes = [C.c_void_p, C.c_void_p]
         L.bdpt_host_bvh_build.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -513,6 +518,15 @@ class Context:
         out = np.empty(len(a), np.uint8)
         self._chk(lib().bdpt_visible(self._h, bvh, a.ctypes.data, b.ctypes.data, len(a), out.ctypes.data, 0), "bdpt_visible")
         return out.astype(bool)
+
+    def set_spheres(self, spheres):
+        """bdpt_scene_set_spheres: analytic sphere prims (an extension; the reference tessellates).  spheres: list of
+        ((cx, cy, cz), radius, material index into the uploaded scene's table); [] drops them."""
+        arr = (Sphere * max(1, len(spheres)))()
+        for k, (c, r, m) in enumerate(spheres):
+            arr[k].center[:] = [float(x) for x in c]
+            arr[k].radius, arr[k].mat_id = float(r), int(m)
+        self._chk(lib().bdpt_scene_set_spheres(self._h, C.byref(arr) if spheres else None, len(spheres)), "bdpt_scene_set_spheres")
 
     def set_media(self, media):
         """bdpt_scene_set_media: constant_medium + isotropic (constant_medium.h:8-61, material.h:149-171).  media: list of

@@ -325,6 +325,7 @@ void bdpt_ctx_destroy(bdpt_ctx* ctx) {
     if (ctx->d_tex) cudaFree(ctx->d_tex);
     if (ctx->d_tex_data) cudaFree(ctx->d_tex_data);
     if (ctx->d_media) cudaFree(ctx->d_media);
+    if (ctx->d_spheres) cudaFree(ctx->d_spheres);
     if (ctx->d_med_tris) cudaFree(ctx->d_med_tris);
     if (ctx->d_stats) cudaFree(ctx->d_stats);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -411,6 +412,7 @@ int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat
     }
     if (rc) { free_scene(ctx); return rc; }
     v.n_lights = uint32_t(h.lights.size());
+    v.n_mats = uint32_t(h.mats.size());
     v.n_tris = uint32_t(h.tris.size());
     v.n_ref_nodes = uint32_t(h.ref_nodes.size());
     v.light_total_area = h.light_total_area;
@@ -463,6 +465,31 @@ int bdpt_scene_set_textures(bdpt_ctx* ctx, const bdpt_texture* tex, uint32_t n_t
         BDPT_CUDA(ctx, cudaMalloc(&ctx->d_tex_data, std::max<uint64_t>(data_bytes, 16)));
         if (data_bytes) BDPT_CUDA(ctx, cudaMemcpy(ctx->d_tex_data, data, data_bytes, cudaMemcpyHostToDevice));
         ctx->n_tex = n_tex;
+    }
+    apply_textures(ctx, ctx->view);
+    return BDPT_OK;
+}
+
+int bdpt_scene_set_spheres(bdpt_ctx* ctx, const bdpt_sphere* spheres, uint32_t n_spheres) {
+    if (!ctx || (n_spheres && !spheres)) return BDPT_ERR_ARG;
+    if (n_spheres > 256) { ctx->err = "at most 256 analytic spheres (a side list, not a tree)"; return BDPT_ERR_ARG; }
+    BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
+    BDPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    std::vector<SphereDev> h(n_spheres);
+    uint32_t max_mat = 0;
+    for (uint32_t k = 0; k < n_spheres; ++k) {
+        if (!(spheres[k].radius > 0.0)) { ctx->err = "sphere: radius must be > 0"; return BDPT_ERR_ARG; }
+        SphereDev d{};
+        d.cx = spheres[k].center[0]; d.cy = spheres[k].center[1]; d.cz = spheres[k].center[2]; d.r = spheres[k].radius; d.mat = spheres[k].mat_id;
+        max_mat = std::max(max_mat, d.mat);
+        h[k] = d;
+    }
+    if (ctx->d_spheres) { cudaFree(ctx->d_spheres); ctx->d_spheres = nullptr; }
+    ctx->n_spheres = 0; ctx->spheres_max_mat = 0;
+    if (n_spheres) {
+        BDPT_CUDA(ctx, cudaMalloc(&ctx->d_spheres, n_spheres * sizeof(SphereDev)));
+        BDPT_CUDA(ctx, cudaMemcpy(ctx->d_spheres, h.data(), n_spheres * sizeof(SphereDev), cudaMemcpyHostToDevice));
+        ctx->n_spheres = n_spheres; ctx->spheres_max_mat = max_mat;
     }
     apply_textures(ctx, ctx->view);
     return BDPT_OK;

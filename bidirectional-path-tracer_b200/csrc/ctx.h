@@ -40,6 +40,9 @@ struct bdpt_ctx {
     bdpt::MediumDev* d_media = nullptr;
     bdpt::TriGeom* d_med_tris = nullptr;
     uint32_t n_media = 0;
+    bdpt::SphereDev* d_spheres = nullptr;   // bdpt_scene_set_spheres
+    uint32_t n_spheres = 0;
+    uint32_t spheres_max_mat = 0;           // largest material index a sphere names (checked against the scene at render time)
 
     // NCCL communicator of bdpt_comm_init (film_reduce.cu); ncclComm_t
     void* comm = nullptr;
@@ -99,6 +102,7 @@ void comm_free(bdpt_ctx* ctx);   // film_reduce.cu
 inline void apply_textures(bdpt_ctx* ctx, SceneView& v) {
     v.tex = ctx->d_tex; v.tex_data = ctx->d_tex_data; v.n_tex = ctx->n_tex;
     v.media = ctx->d_media; v.med_tris = ctx->d_med_tris; v.n_media = ctx->n_media;
+    v.spheres = ctx->d_spheres; v.n_spheres = ctx->n_spheres;
 }
 void render_free(bdpt_ctx* ctx);
 // gpu_bvh.cu: the fast tree built on the device from triangles already uploaded (queued on ctx->stream)

@@ -392,10 +392,38 @@ __device__ __forceinline__ bool medium_hit(const TriGeom* __restrict__ med_tris,
 
 constexpr int kClsIsotropic = 4;   // material queue of the scatter points inside media (after BDPT_MAT_* 0..3)
 
+// ------------------------------------------------------------------ analytic spheres (bdpt_scene_set_spheres; oracle/port.cpp: sphere_hit)
+// The quadratic in the reference's own style: inclusive interval like triangle.h:68, nearer root first, then the farther one.
+__device__ __forceinline__ bool sphere_hit_t(const SphereDev& sp, const D3& o, const D3& d, double tmin, double tmax, double& t_out) {
+    const D3 oc = mk(sp.cx, sp.cy, sp.cz) - o;
+    const double a = len2(d);
+    const double h = dot(d, oc);
+    const double c = len2(oc) - sp.r * sp.r;
+    const double discriminant = h * h - a * c;
+    if (discriminant < 0) return false;
+    const double sqrtd = sqrt(discriminant);
+    double root = (h - sqrtd) / a;
+    if (!(tmin <= root && root <= tmax)) {
+        root = (h + sqrtd) / a;
+        if (!(tmin <= root && root <= tmax)) return false;
+    }
+    t_out = root;
+    return true;
+}
+// outward unit normal of sphere k at p: (p - c) / r
+__device__ __forceinline__ D3 sphere_normal(const SphereDev& sp, const D3& p) { return (p - mk(sp.cx, sp.cy, sp.cz)) / sp.r; }
+// material index and geometric normal of a stored vertex's prim (triangle or, in the flavours that know them, sphere)
+template <bool EX>
+__device__ __forceinline__ uint32_t prim_mat(const SceneView& sc, uint32_t prim) {
+    if (EX && (prim & kSpherePrim)) return sc.spheres[prim & ~kSpherePrim].mat;
+    return sc.shade[prim].mat;
+}
+
 // world.hit's media for one path ray.  Out of line on purpose: inlined into finish_trace its fp64 triangle loops raise the
 // register pressure of every traversal kernel (k_trace_fast: 150 -> 538 bytes of spills), scenes without media included.
 struct MediaOut { double t; uint32_t prim, found; };
 __device__ __noinline__ void media_after_triangles(const MediumDev* __restrict__ media, const TriGeom* __restrict__ med_tris, uint32_t n_media,
+                                                   const SphereDev* __restrict__ spheres, uint32_t n_spheres,
                                                    PathRec* path, uint64_t seed, uint32_t stream, uint64_t sid, MediaOut* io) {
     const double2* q = reinterpret_cast<const double2*>(path);
     const double2 q0 = q[0], q1 = q[1], q2 = q[2];
@@ -404,6 +432,10 @@ __device__ __noinline__ void media_after_triangles(const MediumDev* __restrict__
     rng.init(seed, stream, sid, path->draws);
     const uint32_t d0 = rng.draws;
     double best = io->found ? io->t : __longlong_as_double(0x7FF0000000000000LL);
+    for (uint32_t k = 0; k < n_spheres; ++k) {   // the sphere prims of the side list, in order, against the bound so far
+        double ts;
+        if (sphere_hit_t(spheres[k], o, d, 0.001, best, ts)) { io->found = 1u; best = ts; io->t = ts; io->prim = kSpherePrim | k; }
+    }
     for (uint32_t k = 0; k < n_media; ++k) {
         double tm;
         if (medium_hit(med_tris, media[k], o, d, 0.001, best, rng, tm)) { io->found = 1u; best = tm; io->t = tm; io->prim = kMediumPrim | k; }
@@ -416,18 +448,19 @@ __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f,
                                             const HitD& h, double* film) {
     uint32_t prim = h.prim;
     double t = h.t;
-    if (MEDIA && sc.n_media) {   // the media of the world list, asked after the triangles with the bound found so far (port: hit_world)
+    if (MEDIA && (sc.n_media | sc.n_spheres)) {   // the side lists of the world (sphere prims, media), asked after the triangles with the bound found so far (port: hit_world)
         const bool is_cam = pid < uint32_t(w.B);
         const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
         MediaOut mo;
         mo.found = found ? 1u : 0u; mo.prim = prim; mo.t = t;
-        media_after_triangles(sc.media, sc.med_tris, sc.n_media, w.path + pid, f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, &mo);
+        media_after_triangles(sc.media, sc.med_tris, sc.n_media, sc.spheres, sc.n_spheres, w.path + pid, f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, &mo);
         found = mo.found != 0; prim = mo.prim; t = mo.t;
     }
     if (found) {
         w.path[pid].hit_prim = prim;
         w.path[pid].hit_t = t;
         if (MEDIA && (prim & kMediumPrim)) return kClsIsotropic;
+        if (MEDIA && (prim & kSpherePrim)) return int(sc.mats[sc.spheres[prim & ~kSpherePrim].mat].type);
         return int(sc.mats[__ldg(&sc.shade[prim].mat)].type);
     }
     if (pid < uint32_t(w.B)) {
@@ -728,6 +761,7 @@ __global__ void __launch_bounds__(kBlock, kW32BlocksPerSM) k_trace_w32(SceneView
 
 // hit point and face-forwarded geometric normal (ray.h:21-23, hittable.h:20-26)
 struct Surf { D3 o, d, T, p, n; double t; bool front; uint32_t prim, draws; int32_t remaining; };
+template <bool EX = false>
 __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint32_t pid) {
     Surf s;
     const double2* q = reinterpret_cast<const double2*>(w.path + pid);
@@ -742,8 +776,9 @@ __device__ __forceinline__ Surf load_surf(const SceneView& sc, const WF& w, uint
     const double t = q4.y;
     s.t = t;
     s.p = s.o + t * s.d;
-    const TriShade sh = sc.shade[s.prim];
-    const D3 n = mk(sh.nx, sh.ny, sh.nz);
+    D3 n;
+    if (EX && (s.prim & kSpherePrim)) n = sphere_normal(sc.spheres[s.prim & ~kSpherePrim], s.p);
+    else { const TriShade sh = sc.shade[s.prim]; n = mk(sh.nx, sh.ny, sh.nz); }
     s.front = dot(s.d, n) < 0;
     s.n = s.front ? n : -n;
     return s;
@@ -754,7 +789,7 @@ struct HitUV {
     const SceneView& sc; const Surf& s;
     __device__ __forceinline__ void operator()(double& u, double& v) const {
         double t;
-        if (!tri_candidate(sc.tris + s.prim, s.o, s.d, t, u, v)) { u = 0.0; v = 0.0; }
+        if ((s.prim & kSpherePrim) || !tri_candidate(sc.tris + s.prim, s.o, s.d, t, u, v)) { u = 0.0; v = 0.0; }   // a sphere prim: u = v = 0
     }
 };
 
@@ -780,13 +815,13 @@ __device__ __forceinline__ void store_ray(const WF& w, uint32_t pid, D3 o, D3 d,
 // scatter() is false: the subpath ends here.  Camera subpath: bidirectional_color adds throughput *
 // emission for this non-delta vertex (camera.h:305-309); it never connects (evaluate_bsdf = 0).
 // Light subpath: the vertex is connectable with f_light = emission when hit from the front (camera.h:463).
-template <bool MIS, bool TEX>
+template <bool MIS, bool TEX, bool EX = false>
 __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, double* film) {
     {
         const bool is_cam = pid < uint32_t(w.B);
         const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
-        const Surf s = load_surf(sc, w, pid);
-        const Mat m = sc.mats[sc.shade[s.prim].mat];
+        const Surf s = load_surf<EX>(sc, w, pid);
+        const Mat m = sc.mats[prim_mat<EX>(sc, s.prim)];
         const D3 Le = TEX ? mat_colour(sc, m, s.p, HitUV{sc, s}) : mk(m.r, m.g, m.b);
         if (s.front && len2(Le) > 0) {   // emitted() is one-sided (material.h:140)
             if (is_cam) {
@@ -811,15 +846,15 @@ __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f,
 }
 
 // ------------------------------------------------------------------ K2: lambertian (material.h:42-67)
-template <bool MIS, bool TEX>
+template <bool MIS, bool TEX, bool EX = false>
 __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
     {
-        const Surf s = load_surf(sc, w, pid);
+        const Surf s = load_surf<EX>(sc, w, pid);
         MisAtHit mh{0.0, 0.0, 0.0, 0u};
         if (MIS) mh = mis_arrive(f, w, pid, s);
         const uint32_t side = (MIS && !s.front) ? kBackFlag : 0u;
-        const Mat m = sc.mats[sc.shade[s.prim].mat];
+        const Mat m = sc.mats[prim_mat<EX>(sc, s.prim)];
         const D3 albedo = TEX ? mat_colour(sc, m, s.p, HitUV{sc, s}) : mk(m.r, m.g, m.b);   // tex->value(rec.u, rec.v, rec.p), material.h:47,61
         const bool is_cam = pid < uint32_t(w.B);
         const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
@@ -913,14 +948,14 @@ __device__ __forceinline__ bool shade_isotropic(const SceneView& sc, const Frame
 // ------------------------------------------------------------------ K2: metal (material.h:69-90)
 // Always a delta vertex, even when fuzzy (material.h:85): never stored, never connected.  The fuzzed
 // direction is not rejected when it points below the surface (material.h:74-82).
-template <bool MIS>
+template <bool MIS, bool EX = false>
 __device__ __forceinline__ bool shade_metal(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
     {
         const int32_t remaining = w.path[pid].remaining - 1;
         if (remaining > 0) {
-            const Surf s = load_surf(sc, w, pid);
-            const Mat m = sc.mats[sc.shade[s.prim].mat];
+            const Surf s = load_surf<EX>(sc, w, pid);
+            const Mat m = sc.mats[prim_mat<EX>(sc, s.prim)];
             const bool is_cam = pid < uint32_t(w.B);
             const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
             Rng rng;
@@ -942,14 +977,14 @@ __device__ __forceinline__ bool shade_metal(const SceneView& sc, const Frame& f,
 }
 
 // ------------------------------------------------------------------ K2: dielectric (material.h:92-131)
-template <bool MIS>
+template <bool MIS, bool EX = false>
 __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     bool live = false;
     {
         const int32_t remaining = w.path[pid].remaining - 1;
         if (remaining > 0) {
-            const Surf s = load_surf(sc, w, pid);
-            const Mat m = sc.mats[sc.shade[s.prim].mat];
+            const Surf s = load_surf<EX>(sc, w, pid);
+            const Mat m = sc.mats[prim_mat<EX>(sc, s.prim)];
             const bool is_cam = pid < uint32_t(w.B);
             const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
             Rng rng;
@@ -994,10 +1029,10 @@ __global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w,
     bool live = false;
     uint32_t pid = 0;
     if (valid) {
-        if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light<MIS, TEX>(sc, f, w, pid, film); }
-        else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert<MIS, TEX>(sc, f, w, pid); }
-        else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal<MIS>(sc, f, w, pid); }
-        else if (idx < n_li + n_la + n_me + n_di) { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric<MIS>(sc, f, w, pid); }
+        if (idx < n_li) { pid = w.q_mat[BDPT_MAT_LIGHT][idx]; live = shade_light<MIS, TEX, MEDIA>(sc, f, w, pid, film); }
+        else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert<MIS, TEX, MEDIA>(sc, f, w, pid); }
+        else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal<MIS, MEDIA>(sc, f, w, pid); }
+        else if (idx < n_li + n_la + n_me + n_di) { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric<MIS, MEDIA>(sc, f, w, pid); }
         else if (MEDIA) { pid = w.q_mat[kClsIsotropic][idx - n_li - n_la - n_me - n_di]; live = shade_isotropic(sc, f, w, pid); }
     }
     const uint32_t slot = block_append<kWide>(w.counters + C_ACTIVE0 + nxt, live);
@@ -1043,6 +1078,7 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
         uint32_t cprim;
         load_vertex(w.cv + size_t(b) * size_t(w.depth) + size_t(k), cp, ctf, cprim, &cindex);
         if (MEDIA && (cprim & kMediumPrim)) cn = mk(1.0, 0.0, 0.0);   // a scatter point inside a medium: constant_medium.h:52
+        else if (MEDIA && (cprim & kSpherePrim)) cn = sphere_normal(sc.spheres[cprim & ~kSpherePrim], cp);
         else {
             const TriShade sh = sc.shade[cprim];
             cn = mk(sh.nx, sh.ny, sh.nz);   // |dot| below makes the face flip irrelevant (camera.h:451-452)
@@ -1068,7 +1104,12 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                 const bool l_medium = MEDIA && (far_prim & kMediumPrim) != 0;
                 TriShade lsh;
                 lsh.nx = 1.0; lsh.ny = 0.0; lsh.nz = 0.0; lsh.mat = 0; lsh.pad = 0;
-                if (!l_medium) lsh = sc.shade[far_prim];
+                const bool l_sphere = MEDIA && (far_prim & kSpherePrim) != 0;
+                if (l_sphere) {
+                    const SphereDev sp = sc.spheres[far_prim & ~kSpherePrim];
+                    const D3 sn = sphere_normal(sp, lp);
+                    lsh.nx = sn.x; lsh.ny = sn.y; lsh.nz = sn.z; lsh.mat = sp.mat;
+                } else if (!l_medium) lsh = sc.shade[far_prim];
                 const D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
                 const double cos_cam = fabs(dot(cn, du));
                 const double cos_light = fabs(dot(ln, -du));
@@ -1089,7 +1130,12 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                             so = cp + (0.001 * vdu);
                             sd = vdu;
                             emit = true;
-                            if (l_medium) far_prim = BDPT_MISS;   // no far-endpoint triangle to test first
+                            if (l_medium || l_sphere) far_prim = BDPT_MISS;   // no far-endpoint triangle to test first
+                            // the sphere prims of the side list occlude like any prim (oracle/port.cpp: spheres_occlude)
+                            for (uint32_t sk = 0; MEDIA && sk < sc.n_spheres && emit; ++sk) {
+                                double ts;
+                                if (sphere_hit_t(sc.spheres[sk], so, sd, 0.001, max_t, ts)) emit = false;
+                            }
                             // media between the two vertices scatter the shadow ray (world.hit inside visible(), camera.h:437): one draw
                             // of the sample's shadow stream per (pair, medium) -- oracle/port.cpp: visible_media
                             for (uint32_t mk_ = 0; MEDIA && mk_ < sc.n_media && emit; ++mk_) {
@@ -1879,7 +1925,8 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (o.weighting != BDPT_WEIGHT_REF_SUM && o.weighting != BDPT_WEIGHT_MIS) { ctx->err = "unknown weighting"; return BDPT_ERR_ARG; }
     const bool mis = o.weighting == BDPT_WEIGHT_MIS;
     const bool textured = ctx->view.n_tex > 0;
-    if (mis && ctx->view.n_media > 0) { ctx->err = "BDPT_WEIGHT_MIS does not support participating media (bdpt_scene_set_media)"; return BDPT_ERR_ARG; }
+    if (mis && (ctx->view.n_media > 0 || ctx->view.n_spheres > 0)) { ctx->err = "BDPT_WEIGHT_MIS does not support participating media or analytic spheres (bdpt_scene_set_media / bdpt_scene_set_spheres)"; return BDPT_ERR_ARG; }
+    if (ctx->view.n_spheres > 0 && ctx->spheres_max_mat >= ctx->view.n_mats) { ctx->err = "a sphere names a material outside the scene's table"; return BDPT_ERR_ARG; }
     int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
     H = H < 1 ? 1 : H;
     if (!ctx->film || ctx->film_w != cam->image_width || ctx->film_h != H) {
@@ -1963,8 +2010,8 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
 
     Job J;
     J.sc = ctx->view; J.f = f; J.o = o; J.total = total; J.film = ctx->film; J.d_stats = ctx->d_stats;
-    J.mis = mis; J.tex = textured; J.media = ctx->view.n_media > 0;
-    if (J.media && std::getenv("BDPT_WALK32") && std::atoi(std::getenv("BDPT_WALK32")) != 0) { ctx->err = "BDPT_WALK32 does not support participating media"; return BDPT_ERR_ARG; }
+    J.mis = mis; J.tex = textured; J.media = ctx->view.n_media > 0 || ctx->view.n_spheres > 0;
+    if (J.media && std::getenv("BDPT_WALK32") && std::atoi(std::getenv("BDPT_WALK32")) != 0) { ctx->err = "BDPT_WALK32 does not support participating media or analytic spheres"; return BDPT_ERR_ARG; }
     // traversal stack: one StackEntry per tree level per thread (deferred children only)
     const size_t levels = size_t(std::max(ctx->host.fast_depth, ctx->host.ref_depth)) + 2;
     if (ctx->host.fast_depth + 2 > uint32_t(kStackLevels) || ctx->host.ref_depth + 2 > uint32_t(2 * kStackLevels)) {

@@ -87,6 +87,10 @@ struct __align__(16) MediumDev {
     uint32_t first, count;           // boundary triangles in med_tris
 };
 static_assert(sizeof(MediumDev) == 96, "MediumDev must be 96 bytes");
+// analytic sphere of bdpt_scene_set_spheres: a world prim of a side list (the reference only tessellates)
+struct __align__(16) SphereDev { double cx, cy, cz, r; uint32_t mat; uint32_t pad[3]; };
+static_assert(sizeof(SphereDev) == 48, "SphereDev must be 48 bytes");
+constexpr uint32_t kSpherePrim = 0x10000000u;   // hit / vertex prim of a hit on sphere k: kSpherePrim | k
 constexpr uint32_t kMediumPrim = 0x20000000u;   // hit / vertex prim of a scatter point inside medium k: kMediumPrim | k (prim IDs stay below 2^28)
 
 struct SceneView {
@@ -112,9 +116,12 @@ struct SceneView {
     const MediumDev* media;       // participating media (bdpt_scene_set_media), null when the scene has none
     const TriGeom* med_tris;      // their boundary meshes
     uint32_t n_media;
+    const SphereDev* spheres;     // analytic spheres (bdpt_scene_set_spheres), null when the scene has none
+    uint32_t n_spheres;
     const uint32_t* lights;       // prim IDs, reference light-list order
     const double* light_area;     // running sums of light triangle areas in list order (triangle.h:206-212)
     uint32_t n_lights;
+    uint32_t n_mats;
     uint32_t n_tris;
     uint32_t n_ref_nodes;
     uint32_t n_fast_nodes;

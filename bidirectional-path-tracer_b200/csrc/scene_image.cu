@@ -299,7 +299,7 @@ int bdpt_scene_upload_image(bdpt_ctx* ctx, const void* image, uint64_t bytes, ui
     v.ref_parent = reinterpret_cast<const int32_t*>(at(SEC_REF_PARENT));
     v.prim_leaf = reinterpret_cast<const int32_t*>(at(SEC_PRIM_LEAF));
     v.chain_box = reinterpret_cast<const double*>(at(SEC_CHAIN_BOX));
-    v.n_lights = h->n_lights; v.n_tris = h->n_tris; v.n_ref_nodes = h->n_ref_nodes; v.n_fast_nodes = h->n_fast_nodes;
+    v.n_lights = h->n_lights; v.n_mats = h->n_mats; v.n_tris = h->n_tris; v.n_ref_nodes = h->n_ref_nodes; v.n_fast_nodes = h->n_fast_nodes;
     v.light_total_area = h->light_total_area; v.extent = h->extent;
     v.center = mk(h->center[0], h->center[1], h->center[2]);
     apply_textures(ctx, v);

@@ -190,6 +190,16 @@ typedef struct {
 } bdpt_medium;
 int bdpt_scene_set_media(bdpt_ctx* ctx, const bdpt_medium* media, uint32_t n_media, const double* boundary_verts /* n x 9 */,
                          uint64_t n_boundary_tris);
+/* Analytic spheres (north_star: "ray-triangle/sphere intersection").  NOT a reference behaviour: the reference tessellates every
+ * sphere into 960 triangles (scene_loader.h:212-242,274-294) and that stays the default of the loader; this is the opt-in exact
+ * primitive.  A sphere is a world prim with a material of the scene's table (lambertian, metal or dielectric; an emitter must be
+ * triangles: lights are sampled by area over triangles, triangle.h:199-224), kept in a side list of at most 256 that every
+ * world.hit asks after the triangle walk, in list order, with the bound found so far (closest hit), and that every visible()
+ * query asks for any hit.  Intersection: the quadratic in fp64, nearer root first, inclusive interval like triangle.h:68, outward
+ * normal (p - c) / r face-forwarded like hittable.h:20-26.  BDPT_WEIGHT_REF_SUM only; bdpt_trace / bdpt_visible stay triangle
+ * queries.  Belongs to the context like textures and media; mat_id is checked against the uploaded scene when rendering. */
+typedef struct { double center[3]; double radius; uint32_t mat_id; uint32_t pad; } bdpt_sphere;
+int bdpt_scene_set_spheres(bdpt_ctx* ctx, const bdpt_sphere* spheres, uint32_t n_spheres);
 int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth);
 
 /* ---- scene image: everything bdpt_scene_upload derives from the soup -- the flattened triangle

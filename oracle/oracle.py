@@ -168,6 +168,16 @@ class Oracle:
         f(self.scene, m6.ctypes.data, len(m6), b.ctypes.data)
         return self
 
+    def set_spheres(self, spheres):
+        """port only.  spheres: list of ((cx, cy, cz), radius, material index) -- analytic sphere prims (an extension)."""
+        assert self.kind == "port"
+        a = np.ascontiguousarray([[c[0], c[1], c[2], r, m] for c, r, m in spheres], dtype=np.float64).reshape(-1, 5)
+        f = self.lib.port_scene_set_spheres
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        f.restype = None
+        f(self.scene, a.ctypes.data, len(a))
+        return self
+
     def texture_value(self, k, uvp):
         uvp = np.ascontiguousarray(uvp, dtype=np.float64).reshape(-1, 5)
         out = np.empty((len(uvp), 3), np.float64)

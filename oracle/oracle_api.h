@@ -95,6 +95,9 @@ int      ref_texture_data(void* scene, uint32_t tex_index, void* out /* noise: 6
  * hit_world); ref: real constant_medium objects around a bvh_node of the boundary, added to the world list. */
 void     ORC(scene_set_media)(void* scene, const double* media6, uint32_t n_media, const double* boundary_verts);
 double   port_det_log(double x);
+/* port only: analytic spheres (an extension; the reference tessellates): n x 5 doubles {cx, cy, cz, radius, material index}, world
+ * prims of a side list asked after the triangle walk (oracle/port.cpp: sphere_hit, hit_world). */
+void     port_scene_set_spheres(void* scene, const double* spheres5, uint32_t n);
 void     ORC(scene_destroy)(void* scene);
 uint64_t ORC(bvh_node_count)(void* scene);
 /* DFS leaf order: order[k] = prim ID of the k-th triangle in the builder's final array. */

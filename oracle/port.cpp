@@ -308,7 +308,37 @@ struct Medium {
     std::vector<Tri> boundary;
 };
 
+// Analytic sphere (an extension: the reference only tessellates its spheres, scene_loader.h:212-242; SURVEY 8 "sphere row").  A world
+// prim with a material, kept in a side list and asked after the triangle walk, in list order, with the bound found so far.
+constexpr uint32_t kSpherePrim = 0x10000000u;   // Hit.prim of a hit on sphere k: kSpherePrim | k
+struct Sphere { V3 c; double r; uint32_t mat; };
+// The classic quadratic in the reference's own style: inclusive interval like triangle.h:68 (interval.h:22-24), outward normal
+// (p - c) / r face-forwarded like hittable.h:20-26; u = v = 0.  Nearer root first, then the farther one.
+inline bool sphere_hit(const Sphere& sp, uint32_t id, V3 o, V3 d, double tmin, double tmax, Hit& rec) {
+    V3 oc = sp.c - o;
+    double a = len2(d);
+    double h = dot(d, oc);
+    double c = len2(oc) - sp.r * sp.r;
+    double discriminant = h * h - a * c;
+    if (discriminant < 0) return false;
+    double sqrtd = std::sqrt(discriminant);
+    double root = (h - sqrtd) / a;
+    if (!(tmin <= root && root <= tmax)) {
+        root = (h + sqrtd) / a;
+        if (!(tmin <= root && root <= tmax)) return false;
+    }
+    rec.t = root;
+    rec.p = o + root * d;
+    V3 outward = (rec.p - sp.c) / sp.r;
+    rec.front = dot(d, outward) < 0;
+    rec.normal = rec.front ? outward : -outward;
+    rec.u = 0; rec.v = 0;
+    rec.prim = kSpherePrim | id;
+    return true;
+}
+
 struct Scene {
+    std::vector<Sphere> spheres;
     std::vector<Medium> media;
     std::vector<Tri> tris;
     std::vector<orc_material> mats;
@@ -452,9 +482,19 @@ struct Scene {
     // way, and the same event decides (scatter before the nearer of exit and best), so the outcome has the same
     // distribution whatever the visiting order.  `key`: ORC_RNG_PHILOX draw index of medium 0 for this query (media take
     // key, key + 1, ...; the path streams pass their running counter and get it back advanced by the draws taken).
+    uint32_t mat_of(uint32_t prim) const { return (prim & kSpherePrim) ? spheres[prim & ~kSpherePrim].mat : tris[prim].mat; }
+    bool extras() const { return !media.empty() || !spheres.empty(); }
+    // any sphere within [tmin, tmax]?  (the shadow query's share of the side list)
+    bool spheres_occlude(V3 o, V3 d, double tmin, double tmax) const {
+        Hit tmp;
+        for (size_t k = 0; k < spheres.size(); ++k) if (sphere_hit(spheres[k], uint32_t(k), o, d, tmin, tmax, tmp)) return true;
+        return false;
+    }
     bool hit_world(V3 o, V3 d, double tmin, double tmax, Hit& rec, Rng& rng) const {
         bool found = hit(o, d, tmin, tmax, rec);
         double best = found ? rec.t : tmax;
+        for (size_t k = 0; k < spheres.size(); ++k)
+            if (sphere_hit(spheres[k], uint32_t(k), o, d, tmin, best, rec)) { found = true; best = rec.t; }
         for (size_t k = 0; k < media.size(); ++k) {
             double t;
             if (medium_hit(media[k], o, d, tmin, best, rng, t)) {
@@ -543,7 +583,7 @@ struct Integrator {
     void trace_path(V3 o, V3 d, int depth, std::vector<Vertex>& path, V3 T, V3* bg, Rng& rng, int index0 = 0) const {  // camera.h:325-370
         for (int bounce = 0; bounce < depth; ++bounce) {
             Hit rec;
-            if (!(sc.media.empty() ? sc.hit(o, d, 0.001, kInf, rec) : sc.hit_world(o, d, 0.001, kInf, rec, rng))) {
+            if (!(sc.extras() ? sc.hit_world(o, d, 0.001, kInf, rec, rng) : sc.hit(o, d, 0.001, kInf, rec))) {
                 if (bg) *bg = *bg + T * cam.background;
                 break;
             }
@@ -566,10 +606,10 @@ struct Integrator {
                 o = rec.p; d = sd;
                 continue;
             }
-            const orc_material& m = sc.mats[sc.tris[rec.prim].mat];
+            const orc_material& m = sc.mats[sc.mat_of(rec.prim)];
             Vertex vx;
             vx.index = index0 + bounce;
-            vx.p = rec.p; vx.normal = rec.normal; vx.mat = sc.tris[rec.prim].mat;
+            vx.p = rec.p; vx.normal = rec.normal; vx.mat = sc.mat_of(rec.prim);
             vx.throughput = T;
             vx.wi = unit(-d);
             vx.emission = emitted(m, rec.front, rec.u, rec.v, rec.p);
@@ -684,6 +724,7 @@ struct Integrator {
             double t;
             if (Scene::medium_hit(sc.media[k], so, du, 0.001, max_t, shadow_rng, t)) return false;
         }
+        if (sc.spheres_occlude(so, du, 0.001, max_t)) return false;
         Hit tmp;
         return !sc.hit(so, du, 0.001, max_t, tmp);
     }
@@ -697,7 +738,7 @@ struct Integrator {
         double cos_cam = std::fabs(dot(cv.normal, du));
         double cos_light = std::fabs(dot(lv.normal, -du));
         if (cos_cam <= 0 || cos_light <= 0) return {0, 0, 0};
-        if (!(sc.media.empty() ? visible(cv.p, lv.p) : visible_media(cv.p, lv.p, *shadow_rng, cv.index, lv.index))) return {0, 0, 0};
+        if (!(sc.extras() ? visible_media(cv.p, lv.p, *shadow_rng, cv.index, lv.index) : visible(cv.p, lv.p))) return {0, 0, 0};
         V3 f_cam = eval_bsdf(cv);
         if (len2(f_cam) <= 0) return {0, 0, 0};
         V3 f_light = lv.is_light ? lv.emission : eval_bsdf(lv);
@@ -1005,6 +1046,15 @@ void port_scene_set_media(void* p, const double* media6, uint32_t n_media, const
     }
 }
 double port_det_log(double x) { return det_log(x); }
+// spheres: n x {cx, cy, cz, radius, material index} as doubles
+void port_scene_set_spheres(void* p, const double* spheres5, uint32_t n) {
+    auto* s = static_cast<Scene*>(p);
+    s->spheres.clear();
+    for (uint32_t k = 0; k < n; ++k) {
+        const double* q = spheres5 + 5 * k;
+        s->spheres.push_back(Sphere{V3{q[0], q[1], q[2]}, q[3], uint32_t(q[4])});
+    }
+}
 uint64_t port_bvh_node_count(void* p) { return static_cast<Scene*>(p)->nodes.size(); }
 void port_bvh_leaf_order(void* p, uint32_t* order) {
     auto* s = static_cast<Scene*>(p);
@@ -1018,6 +1068,9 @@ void port_trace(void* p, const double* rays, uint64_t n, uint32_t* prim, double*
             const double* q = rays + 8 * i;
             Hit rec;
             bool h = s->hit({q[0], q[1], q[2]}, {q[3], q[4], q[5]}, q[6], q[7], rec);
+            double best = h ? rec.t : q[7];   // the sphere prims of the side list, as hit_world asks them (media draw numbers: not here)
+            for (size_t k = 0; k < s->spheres.size(); ++k)
+                if (sphere_hit(s->spheres[k], uint32_t(k), {q[0], q[1], q[2]}, {q[3], q[4], q[5]}, q[6], best, rec)) { h = true; best = rec.t; }
             if (prim) prim[i] = h ? rec.prim : 0xFFFFFFFFu;
             if (t) t[i] = h ? rec.t : 0.0;
             if (u) u[i] = h ? rec.u : 0.0;

@@ -1,0 +1,122 @@
+"""Analytic sphere prims (bdpt_scene_set_spheres; north_star: "ray-triangle/sphere intersection").  NOT a reference behaviour:
+the reference tessellates every sphere into 960 triangles (scene_loader.h:212-242) -- so there is no reference code to pin
+this against, and the oracle is the port's own restatement (oracle/port.cpp: sphere_hit), itself checked against the closed
+form and against ever finer tessellations of the same sphere traced by the reference-pinned triangle path.
+  GPU: film equal to the port's sample for sample (1e-9 of the peak), both tree flavours, alone and together with media."""
+import numpy as np
+import pytest
+
+from oracle.oracle import Oracle, make_camera as ocam, RNG_PHILOX
+from tools import testscenes as ts
+
+LAMB, METAL, GLASS, LIGHT = 0, 1, 2, 3
+
+
+def rel_err(a, b):
+    return float(np.abs(a - b).max() / max(1e-300, np.abs(b).max()))
+
+
+def room_with_sphere_materials():
+    """The Cornell room plus three materials for spheres (glass, fuzzy metal, lambertian); returns the sphere list too."""
+    v, m, mats, cam = ts.cornell(False)
+    mats = list(mats) + [(GLASS, (1, 1, 1), 1.5), (METAL, (0.8, 0.85, 0.88), 0.1), (LAMB, (0.2, 0.6, 0.3), 0.0)]
+    n = len(mats)
+    spheres = [((190.0, 90.0, 190.0), 90.0, n - 3), ((400.0, 120.0, 350.0), 120.0, n - 2), ((300.0, 400.0, 300.0), 60.0, n - 1)]
+    return v, m, mats, cam, spheres
+
+
+def test_port_sphere_hit_is_the_closed_form():
+    """port_trace asks the sphere side list after the triangles (hit_world's deterministic part): nearer root from outside, farther
+    root from inside, misses, the interval's inclusive ends, and a triangle in front wins."""
+    c, r = np.array([1.0, 2.0, 3.0]), 2.5
+    far = np.array([[100.0, 100, 100, 101, 100, 100, 100, 101, 100]])          # one triangle far away: the scene needs a world
+    o = Oracle("port").load(far, np.zeros(1, np.uint32), [(LAMB, (0.5, 0.5, 0.5), 0.0)]).set_spheres([(tuple(c), r, 0)])
+    rng = np.random.default_rng(3)
+    n = 5000
+    org = c + rng.normal(size=(n, 3)) * 6.0
+    d = (c + rng.normal(size=(n, 3)) * r * 0.9) - org
+    d *= rng.uniform(0.2, 3.0, size=(n, 1))                                      # un-normalised directions
+    rays = np.concatenate([org, d, np.full((n, 1), 0.001), np.full((n, 1), np.inf)], axis=1)
+    prim, t, _, _ = o.trace(rays)
+    a = (d * d).sum(1); h = (d * (c - org)).sum(1); cc = ((c - org) ** 2).sum(1) - r * r
+    disc = h * h - a * cc
+    sq = np.sqrt(np.maximum(disc, 0))
+    t0, t1 = (h - sq) / a, (h + sq) / a
+    want = np.where(disc < 0, np.inf, np.where(t0 >= 0.001, t0, np.where(t1 >= 0.001, t1, np.inf)))
+    hit = np.isfinite(want)
+    assert hit.sum() > 2000 and (~hit).sum() > 10
+    assert np.all(prim[hit] == 0x10000000) and np.all(prim[~hit] == 0xFFFFFFFF)
+    assert np.abs(t[hit] - want[hit]).max() <= 1e-12 * np.abs(want[hit]).max()
+    inside = ((org - c) ** 2).sum(1) < r * r
+    assert inside.sum() > 50 and np.all(t[inside & hit] == ((h + sq) / a)[inside & hit])   # bit for bit: the same formula
+    # interval ends are inclusive (interval.h:22-24, as triangle.h:68 uses them)
+    k = int(np.flatnonzero(hit & ~inside)[0])
+    one = rays[k:k + 1].copy(); one[0, 7] = t[k]
+    assert o.trace(one)[0][0] == 0x10000000
+    one[0, 7] = np.nextafter(t[k], 0)
+    assert o.trace(one)[0][0] == 0xFFFFFFFF
+    # a triangle in front of the sphere wins
+    wall = np.array([[-50.0, -50, -2, 50, -50, -2, 0, 50, -2]])
+    o2 = Oracle("port").load(wall, np.zeros(1, np.uint32), [(LAMB, (0.5, 0.5, 0.5), 0.0)]).set_spheres([(tuple(c), r, 0)])
+    p2, t2, _, _ = o2.trace(np.array([[1.0, 2.0, -10.0, 0, 0, 1, 0.001, np.inf]]))
+    assert p2[0] == 0 and t2[0] == 8.0
+
+
+def test_port_render_with_analytic_spheres_looks_like_the_tessellated_scene():
+    """Same room, same three spheres: analytic prims against 40 x 80-step tessellations (6,240 triangles each).  Means agree
+    within Monte-Carlo noise and the faceting error; the sphere-free room is far away."""
+    v, m, mats, cam, spheres = room_with_sphere_materials()
+    W = H = 24
+    spp, depth = 64, 6
+    c = ocam(W, H, spp, depth, **cam)
+    ana = Oracle("port").load(v, m, mats).set_spheres(spheres).render(c, rng_mode=RNG_PHILOX, seed=5, nthreads=8, height=H)
+    tv, tm = [np.asarray(v).reshape(-1, 9)], [np.asarray(m)]
+    for ctr, rad, mat in spheres:
+        tess = ts.uv_sphere(ctr, rad, 40, 80).reshape(-1, 9)
+        tv.append(tess); tm.append(np.full(len(tess), mat, np.uint32))
+    tes = Oracle("port").load(np.concatenate(tv), np.concatenate(tm), mats).render(c, rng_mode=RNG_PHILOX, seed=6, nthreads=8, height=H)
+    bare = Oracle("port").load(v, m, mats).render(c, rng_mode=RNG_PHILOX, seed=5, nthreads=8, height=H)
+    assert abs(ana.mean() / tes.mean() - 1.0) < 0.08
+    assert np.mean(np.abs(ana - bare) > 1e-9) > 0.2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bvh", [0, 1])
+def test_sphere_film_equals_the_port_sample_for_sample(bvh, bdpt):
+    v, m, mats, cam, spheres = room_with_sphere_materials()
+    W, H, spp, depth = 40, 30, 4, 8
+    ref = Oracle("port").load(v, m, mats).set_spheres(spheres).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=11, nthreads=8, height=H)
+    bare = Oracle("port").load(v, m, mats).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=11, nthreads=8, height=H)
+    assert rel_err(bare, ref) > 0.05
+    with bdpt.Context(0) as ctx:
+        ctx.upload(v, m, mats)
+        ctx.set_spheres(spheres)
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=11, bvh=bvh, height=H)
+        assert rel_err(ctx.film(), ref) < 1e-9
+        # together with media
+        media = ts.cornell_media()
+        both = Oracle("port").load(v, m, mats).set_spheres(spheres).set_media(media).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX,
+                                                                                          seed=11, nthreads=8, height=H)
+        ctx.set_media(media)
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=11, bvh=bvh, height=H)
+        assert rel_err(ctx.film(), both) < 1e-9
+        ctx.set_media([]); ctx.set_spheres([])
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=11, bvh=bvh, height=H)
+        assert rel_err(ctx.film(), bare) < 1e-9
+
+
+@pytest.mark.gpu
+def test_sphere_argument_checks(bdpt):
+    v, m, mats, cam, spheres = room_with_sphere_materials()
+    with bdpt.Context(0) as ctx:
+        with pytest.raises(bdpt.BdptError, match="radius"):
+            ctx.set_spheres([((0, 0, 0), 0.0, 0)])
+        with pytest.raises(bdpt.BdptError, match="256"):
+            ctx.set_spheres([((0, 0, 0), 1.0, 0)] * 257)
+        ctx.upload(v, m, mats)
+        ctx.set_spheres([((278, 100, 278), 50.0, 99)])
+        with pytest.raises(bdpt.BdptError, match="material"):
+            ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8)
+        ctx.set_spheres(spheres)
+        with pytest.raises(bdpt.BdptError, match="spheres"):
+            ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8, weighting=bdpt.WEIGHT_MIS)
