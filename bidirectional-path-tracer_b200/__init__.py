@@ -35,7 +35,7 @@ EXPORTS = [
     "bdpt_scene_upload_image", "bdpt_scene_image_save", "bdpt_scene_image_map", "bdpt_scene_image_unmap",
     "bdpt_scene_source_key", "bdpt_scene_file_open_cached", "bdpt_test_filter32",
     "bdpt_scene_set_textures", "bdpt_scene_file_textures", "bdpt_film_reduce", "bdpt_comm_unique_id", "bdpt_comm_init", "bdpt_film_reduce_comm", "bdpt_render_progress", "bdpt_bench_read", "bdpt_comm_attach",
-    "bdpt_film_to_rgb8_noalloc", "bdpt_scene_set_media", "bdpt_scene_file_media", "bdpt_scene_set_spheres",
+    "bdpt_film_to_rgb8_noalloc", "bdpt_scene_set_media", "bdpt_scene_file_media", "bdpt_scene_set_spheres", "bdpt_scene_file_spheres",
 ]
 
 
@@ -158,6 +158,7 @@ def lib():
                                            C.c_void_p, C.c_char_p, C.c_uint64]
         L.bdpt_scene_file_textures.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]
         L.bdpt_scene_file_media.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]
+        L.bdpt_scene_file_spheres.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p]
         L.bdpt_scene_file_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.bdpt_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
         L.bdpt_host_last_error.restype = C.c_char_p
@@ -387,6 +388,11 @@ class SceneFile:
                 n = (256 * 3 * 8 + 3 * 256 * 4) if t.type == TEX_NOISE else (t.width * t.height * 3 if t.type == TEX_IMAGE else 0)
                 self.textures.append(dict(type=int(t.type), a=tuple(t.a), b=tuple(t.b), scale=float(t.scale), width=int(t.width),
                                           height=int(t.height), data=blob[t.data_offset:t.data_offset + n].copy() if n else None))
+            ns_ = C.c_uint32(0)
+            lib().bdpt_scene_file_spheres(h, C.byref(ns_), None)
+            sarr = (Sphere * max(1, ns_.value))()
+            lib().bdpt_scene_file_spheres(h, None, C.byref(sarr))
+            self.spheres = [(tuple(sarr[k].center), float(sarr[k].radius), int(sarr[k].mat_id)) for k in range(ns_.value)]   # as Context.set_spheres takes them
             nm_, nbt = C.c_uint32(0), C.c_uint64(0)
             if lib().bdpt_scene_file_media(h, C.byref(nm_), None, C.byref(nbt), None):
                 raise BdptError("Failed to load scene: " + lib().bdpt_host_last_error().decode())

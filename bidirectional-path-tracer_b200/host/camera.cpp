@@ -8,6 +8,7 @@
 #include <cmath>
 #include <iomanip>
 #include <iostream>
+#include <map>
 #include <stdexcept>
 #include <thread>
 
@@ -30,7 +31,7 @@ rotate_y::rotate_y(shared_ptr<hittable> obj, double angle_degrees) : object(std:
     cos_theta = std::cos(radians);
 }
 
-void collect_triangles(const hittable& h, std::vector<triangle>& out, std::vector<constant_medium>* media) {
+void collect_triangles(const hittable& h, std::vector<triangle>& out, std::vector<constant_medium>* media, std::vector<sphere>* spheres) {
     if (auto t = dynamic_cast<const triangle*>(&h)) { out.push_back(*t); return; }
     if (auto c = dynamic_cast<const triangle_collection*>(&h)) { out.insert(out.end(), c->tris.begin(), c->tris.end()); return; }
     if (auto b = dynamic_cast<const bvh_node*>(&h)) {
@@ -39,15 +40,24 @@ void collect_triangles(const hittable& h, std::vector<triangle>& out, std::vecto
             if (!media) throw std::runtime_error("collect_triangles: a constant_medium where only triangles are allowed");
             media->insert(media->end(), b->media.begin(), b->media.end());
         }
+        if (!b->spheres.empty()) {
+            if (!spheres) throw std::runtime_error("collect_triangles: an analytic sphere where only triangles are allowed");
+            spheres->insert(spheres->end(), b->spheres.begin(), b->spheres.end());
+        }
         return;
     }
-    if (auto l = dynamic_cast<const hittable_list*>(&h)) { for (const auto& o : l->objects) collect_triangles(*o, out, media); return; }
+    if (auto l = dynamic_cast<const hittable_list*>(&h)) { for (const auto& o : l->objects) collect_triangles(*o, out, media, spheres); return; }
+    if (auto sp = dynamic_cast<const sphere*>(&h)) {
+        if (!spheres) throw std::runtime_error("collect_triangles: an analytic sphere where only triangles are allowed");
+        spheres->push_back(*sp);
+        return;
+    }
     if (auto cm = dynamic_cast<const constant_medium*>(&h)) {
         if (!media) throw std::runtime_error("collect_triangles: a constant_medium where only triangles are allowed");
         media->push_back(*cm);
         return;
     }
-    const size_t first = out.size(), first_medium = media ? media->size() : 0;
+    const size_t first = out.size(), first_medium = media ? media->size() : 0, first_sphere = spheres ? spheres->size() : 0;
     // a transform around a medium moves its boundary: the medium's boundary is replaced by the moved triangles
     auto move_media = [&](auto&& wrap) {
         if (!media) return;
@@ -58,23 +68,58 @@ void collect_triangles(const hittable& h, std::vector<triangle>& out, std::vecto
         }
     };
     if (auto tr = dynamic_cast<const translate*>(&h)) {
-        collect_triangles(*tr->object, out, media);
+        collect_triangles(*tr->object, out, media, spheres);
         for (size_t i = first; i < out.size(); ++i)
             for (point3* p : {&out[i].v0, &out[i].v1, &out[i].v2})   // hittable.h:64: rec.p += offset
                 *p = point3(p->x() + tr->offset.x(), p->y() + tr->offset.y(), p->z() + tr->offset.z());
+        for (size_t i = first_sphere; spheres && i < spheres->size(); ++i) {
+            point3& c = (*spheres)[i].center;
+            c = point3(c.x() + tr->offset.x(), c.y() + tr->offset.y(), c.z() + tr->offset.z());
+        }
         move_media([&](const shared_ptr<hittable>& b) { return make_shared<translate>(b, tr->offset); });
         return;
     }
     if (auto ro = dynamic_cast<const rotate_y*>(&h)) {
-        collect_triangles(*ro->object, out, media);
+        collect_triangles(*ro->object, out, media, spheres);
         const double c = ro->cos_theta, s = ro->sin_theta;
         for (size_t i = first; i < out.size(); ++i)
             for (point3* p : {&out[i].v0, &out[i].v1, &out[i].v2})   // object -> world, hittable.h:134-138
                 *p = point3((c * p->x()) + (s * p->z()), p->y(), (-s * p->x()) + (c * p->z()));
+        for (size_t i = first_sphere; spheres && i < spheres->size(); ++i) {
+            point3& q = (*spheres)[i].center;
+            q = point3((c * q.x()) + (s * q.z()), q.y(), (-s * q.x()) + (c * q.z()));
+        }
         move_media([&](const shared_ptr<hittable>& b) { auto r = make_shared<rotate_y>(b, 0.0); r->sin_theta = s; r->cos_theta = c; return r; });
         return;
     }
     throw std::runtime_error("collect_triangles: unknown hittable (triangle, triangle_collection, hittable_list, bvh_node, translate, rotate_y)");
+}
+
+void flatten_spheres(const std::vector<sphere>& spheres, const std::vector<triangle>& tris, std::vector<bdpt_material>& mats,
+                     std::vector<bdpt_sphere>& out) {
+    out.clear();
+    if (spheres.empty()) return;
+    // the table's order is first use over the triangles (flatten_triangles): rebuild its index, then look up / append
+    std::map<const material*, uint32_t> index;
+    for (const triangle& t : tris) index.emplace(t.mat.get(), uint32_t(index.size()));
+    if (index.size() != mats.size()) throw std::runtime_error("flatten_spheres: the material table does not belong to these triangles");
+    for (const sphere& sp : spheres) {
+        if (!sp.mat || sp.mat->phase) throw std::runtime_error("sphere: needs a surface material");
+        if (!(sp.radius > 0.0)) throw std::runtime_error("sphere: radius must be > 0");
+        auto it = index.find(sp.mat.get());
+        if (it == index.end()) {
+            bdpt_material m{};
+            m.type = uint32_t(sp.mat->kind);
+            m.rgb[0] = sp.mat->rgb.x(); m.rgb[1] = sp.mat->rgb.y(); m.rgb[2] = sp.mat->rgb.z();
+            m.param = sp.mat->param;
+            it = index.emplace(sp.mat.get(), uint32_t(mats.size())).first;
+            mats.push_back(m);
+        }
+        bdpt_sphere d{};
+        d.center[0] = sp.center.x(); d.center[1] = sp.center.y(); d.center[2] = sp.center.z();
+        d.radius = sp.radius; d.mat_id = it->second;
+        out.push_back(d);
+    }
 }
 
 void flatten_media(const std::vector<constant_medium>& media, std::vector<bdpt_medium>& out, std::vector<double>& boundary_verts) {
@@ -106,9 +151,13 @@ void camera::render(const hittable& world, const hittable& lights) {
     const std::vector<triangle>* prims = nullptr;
     std::vector<triangle> collected;
     std::vector<constant_medium> media = options.media;
-    if (auto b = dynamic_cast<const bvh_node*>(&world)) { prims = &b->prims; media.insert(media.end(), b->media.begin(), b->media.end()); }
-    else if (auto t = dynamic_cast<const triangle_collection*>(&world)) prims = &t->tris;
-    else { collect_triangles(world, collected, &media); prims = &collected; }   // hittable_list, translate, rotate_y, constant_medium
+    std::vector<sphere> spheres = options.spheres;
+    if (auto b = dynamic_cast<const bvh_node*>(&world)) {
+        prims = &b->prims;
+        media.insert(media.end(), b->media.begin(), b->media.end());
+        spheres.insert(spheres.end(), b->spheres.begin(), b->spheres.end());
+    } else if (auto t = dynamic_cast<const triangle_collection*>(&world)) prims = &t->tris;
+    else { collect_triangles(world, collected, &media, &spheres); prims = &collected; }   // hittable_list, translate, rotate_y, constant_medium, sphere
     std::vector<bdpt_medium> media_desc;
     std::vector<double> media_verts;
     flatten_media(media, media_desc, media_verts);
@@ -117,10 +166,13 @@ void camera::render(const hittable& world, const hittable& lights) {
     uint64_t image_bytes = options.scene_image_bytes;
     std::vector<double> verts; std::vector<uint32_t> mat_id; std::vector<bdpt_material> mats;
     std::vector<bdpt_texture> textures; std::vector<unsigned char> tex_data;
+    std::vector<bdpt_sphere> sphere_desc;
     if (!from_image) {
         flatten_triangles(*prims, verts, mat_id, mats);
         flatten_textures(*prims, mats, textures, tex_data);
-    }
+        flatten_spheres(spheres, *prims, mats, sphere_desc);   // may append the spheres' materials to the table
+    } else if (!spheres.empty())
+        throw std::runtime_error("camera::render: analytic spheres need the scene's material table, which a scene image does not expose; render without the image");
     // several GPUs: flatten and build the two trees ONCE into a scene image and hand every context the same block,
     // instead of letting each worker's bdpt_scene_upload rebuild them side by side on the same host cores
     struct image_owner { void* p = nullptr; ~image_owner() { if (p) bdpt_scene_image_free(p); } } built;
@@ -157,6 +209,8 @@ void camera::render(const hittable& world, const hittable& lights) {
             else check(bdpt_scene_upload(ctx, verts.data(), mat_id.data(), mat_id.size(), mats.data(), uint32_t(mats.size())), ctx, "bdpt_scene_upload");
             if (!textures.empty())
                 check(bdpt_scene_set_textures(ctx, textures.data(), uint32_t(textures.size()), tex_data.data(), tex_data.size()), ctx, "bdpt_scene_set_textures");
+            if (!sphere_desc.empty())
+                check(bdpt_scene_set_spheres(ctx, sphere_desc.data(), uint32_t(sphere_desc.size())), ctx, "bdpt_scene_set_spheres");
             if (!media_desc.empty())
                 check(bdpt_scene_set_media(ctx, media_desc.data(), uint32_t(media_desc.size()), media_verts.data(), media_verts.size() / 9), ctx, "bdpt_scene_set_media");
             check(bdpt_film_clear(ctx, W, H), ctx, "bdpt_film_clear");

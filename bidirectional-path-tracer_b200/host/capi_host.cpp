@@ -20,6 +20,7 @@ struct bdpt_scene_file {
     std::vector<bdpt_material> mats;
     std::vector<bdpt_texture> textures;
     std::vector<unsigned char> tex_data;
+    std::vector<bdpt_sphere> spheres;
     // scene-image cache (bdpt_scene_file_open_cached)
     const void* image = nullptr;
     uint64_t image_bytes = 0;
@@ -47,6 +48,7 @@ int bdpt_scene_file_load(const char* yaml_path, bdpt_scene_file** out) {
         f->scene = load_scene_from_yaml(yaml_path);
         flatten_triangles(f->scene.world.tris, f->verts, f->mat_id, f->mats);
         flatten_textures(f->scene.world.tris, f->mats, f->textures, f->tex_data);
+        flatten_spheres(f->scene.cam.options.spheres, f->scene.world.tris, f->mats, f->spheres);   // may append their materials
         *out = f;
     } catch (const std::exception& e) {
         g_host_err = e.what();
@@ -63,6 +65,13 @@ int bdpt_scene_file_textures(const bdpt_scene_file* f, uint32_t* n_tex, bdpt_tex
     if (data_bytes) *data_bytes = f->tex_data.size();
     if (tex && !f->textures.empty()) std::memcpy(tex, f->textures.data(), f->textures.size() * sizeof(bdpt_texture));
     if (data && !f->tex_data.empty()) std::memcpy(data, f->tex_data.data(), f->tex_data.size());
+    return BDPT_OK;
+}
+
+int bdpt_scene_file_spheres(const bdpt_scene_file* f, uint32_t* n_spheres, bdpt_sphere* spheres) {
+    if (!f) return BDPT_ERR_ARG;
+    if (n_spheres) *n_spheres = uint32_t(f->spheres.size());
+    if (spheres && !f->spheres.empty()) std::memcpy(spheres, f->spheres.data(), f->spheres.size() * sizeof(bdpt_sphere));
     return BDPT_OK;
 }
 

@@ -170,10 +170,23 @@ class constant_medium : public hittable {
     double density;
     color albedo;
 };
+// An analytic sphere prim (include/bdpt.h: bdpt_scene_set_spheres).  NOT a reference class: the reference's loader tessellates its
+// `Sphere` surfaces into 960 triangles (scene_loader.h:212-242), and so does this one unless the surface says `analytic: true`.
+class sphere : public hittable {
+  public:
+    sphere(const point3& c, double r, shared_ptr<material> m) : center(c), radius(r), mat(std::move(m)) {}
+    point3 center;
+    double radius;
+    shared_ptr<material> mat;
+};
 // the triangles of any object graph (triangle, triangle_collection, hittable_list, bvh_node, translate, rotate_y), in
-// traversal order (= prim ID), in world space; throws on a hittable it does not know.  constant_medium objects met on the
-// way go to `media` (with the transforms above them applied to their boundaries) when it is given, else they are an error.
-void collect_triangles(const hittable& h, std::vector<class triangle>& out, std::vector<constant_medium>* media = nullptr);
+// traversal order (= prim ID), in world space; throws on a hittable it does not know.  constant_medium and sphere objects met on
+// the way go to `media` / `spheres` (with the transforms above them applied) when those are given, else they are an error.
+void collect_triangles(const hittable& h, std::vector<class triangle>& out, std::vector<constant_medium>* media = nullptr,
+                       std::vector<sphere>* spheres = nullptr);
+// bdpt_scene_set_spheres' argument: the spheres' materials are looked up in (or appended to) the table flatten_triangles made of `tris`
+void flatten_spheres(const std::vector<sphere>& spheres, const std::vector<class triangle>& tris, std::vector<bdpt_material>& mats,
+                     std::vector<bdpt_sphere>& out);
 // bdpt_scene_set_media's arguments from a list of media (boundaries flattened with collect_triangles)
 void flatten_media(const std::vector<constant_medium>& media, std::vector<bdpt_medium>& out, std::vector<double>& boundary_verts);
 
@@ -183,10 +196,11 @@ class bvh_node : public hittable {
   public:
     explicit bvh_node(hittable_list list) {
         prims.reserve(list.objects.size());
-        for (auto& o : list.objects) collect_triangles(*o, prims, &media);   // triangles as they are; instances baked (above)
+        for (auto& o : list.objects) collect_triangles(*o, prims, &media, &spheres);   // triangles as they are; instances baked (above)
     }
     std::vector<triangle> prims;
     std::vector<constant_medium> media;   // constant_medium objects of the list
+    std::vector<sphere> spheres;          // analytic sphere objects of the list
 };
 
 struct render_options {         // overrides the CLI adds on top of the YAML
@@ -203,6 +217,9 @@ struct render_options {         // overrides the CLI adds on top of the YAML (SU
     // participating media beside the world (the YAML loader's `media:` section puts them here; a constant_medium inside the
     // world list is found by render() itself)
     std::vector<constant_medium> media;
+    // analytic sphere prims beside the world (`analytic: true` on a YAML Sphere surface); a sphere inside the world list is found
+    // by render() itself
+    std::vector<sphere> spheres;
 };
 
 struct render_report {

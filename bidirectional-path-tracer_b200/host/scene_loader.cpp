@@ -152,7 +152,9 @@ point3 sphere_point(double theta, double phi, const point3& c, double r) {   // 
     return point3(c.x() + x, c.y() + y, c.z() + z);
 }
 
-void load_sphere(const node& mesh, sink& out) {                      // scene_loader.h:212-242,274-294
+// `analytic: true` (extension; SURVEY 8 "sphere row"): the sphere becomes ONE exact prim (bdpt_scene_set_spheres) instead of the
+// reference's 960 triangles; it lands in `analytic` (cam.options.spheres)
+void load_sphere(const node& mesh, sink& out, std::vector<sphere>& analytic) {   // scene_loader.h:212-242,274-294
     if (!mesh["material"].defined()) throw std::runtime_error("Missing material field");
     const auto mat = build_material(mesh["material"]);
     const node& data = mesh["data"];
@@ -161,6 +163,12 @@ void load_sphere(const node& mesh, sink& out) {                      // scene_lo
     const point3 center = cv.size() < 3 ? point3(0, 0, 0) : point3(cv[0], cv[1], cv[2]);
     const double radius = to_double(data["radius"], 0.0);
     if (radius <= 0.0) throw std::runtime_error("Missing or invalid radius field");
+    const std::string an = to_string(mesh["analytic"], "");
+    if (an == "true" || an == "True" || an == "yes" || an == "1") {
+        if (mat->kind == material::DiffuseLight) throw std::runtime_error("an analytic sphere cannot be a light (lights are sampled over triangles): drop `analytic`");
+        analytic.emplace_back(center, radius, mat);
+        return;
+    }
     const int lat_steps = 16, lon_steps = 32;   // 960 triangles
     const double pi = 3.14159265358979323846;
     for (int lat = 0; lat < lat_steps; ++lat) {
@@ -374,9 +382,9 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
         if (!mesh.is_map()) throw std::runtime_error("Scene entries must be mappings");
         const std::string type = to_string(mesh["type"]);
         if (type.empty()) throw std::runtime_error("Mesh missing type field");
-        const size_t w0 = result.world.size(), l0 = result.lights.size();
+        const size_t w0 = result.world.size(), l0 = result.lights.size(), s0 = result.cam.options.spheres.size();
         if (type == "TriMesh") load_tri_mesh(mesh, out);
-        else if (type == "Sphere") load_sphere(mesh, out);
+        else if (type == "Sphere") load_sphere(mesh, out, result.cam.options.spheres);
         else if (type == "mesh") load_indexed_mesh(mesh, out, mats);
         else if (type == "object") load_object(mesh, dir, out, mats, jobs);
         else std::cerr << "Unknown mesh type: " << type << "\n";
@@ -401,6 +409,16 @@ scene_load_result load_scene_from_yaml(const std::string& path) {    // scene_lo
             };
             bake(result.world.tris, w0);
             bake(result.lights.tris, l0);
+            for (size_t i = s0; i < result.cam.options.spheres.size(); ++i) {   // an analytic sphere of this surface: its centre moves
+                sphere& sp = result.cam.options.spheres[i];
+                shared_ptr<hittable> obj = make_shared<sphere>(sp);
+                if (tf["rotate_y"].defined()) obj = make_shared<rotate_y>(obj, deg);
+                if (off.size() == 3) obj = make_shared<translate>(obj, vec3(off[0], off[1], off[2]));
+                std::vector<triangle> none;
+                std::vector<sphere> moved;
+                collect_triangles(*obj, none, nullptr, &moved);
+                sp = moved.at(0);
+            }
         } else if (tf.defined()) throw std::runtime_error("transform must be a mapping {rotate_y: deg, translate: [x, y, z]}");
     }
     load_media(root, result.cam);
@@ -414,6 +432,12 @@ camera load_camera_from_yaml(const std::string& path) {
     camera cam;
     load_camera(root["camera"], cam);
     load_media(root, cam);   // the scene-image cache holds the world only: media are re-read with the camera
+    const node* surfaces = &root["surfaces"];
+    if (!surfaces->defined()) surfaces = &root["scene"];
+    if (surfaces->is_sequence())
+        for (const auto& mesh : surfaces->seq)
+            if (mesh.is_map() && mesh["analytic"].defined())
+                throw std::runtime_error("analytic spheres need the scene's material table, which a scene image does not expose: render this scene without --cache");
     return cam;
 }
 

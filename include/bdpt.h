@@ -316,6 +316,10 @@ int  bdpt_scene_file_textures(const bdpt_scene_file* f, uint32_t* n_tex, bdpt_te
 /* The scene's participating media for bdpt_scene_set_media (a `media:` section in the YAML -- an extension of the
  * reference's schema, host/scene_loader.cpp).  Call with media = boundary_verts = NULL for the sizes. */
 int  bdpt_scene_file_media(const bdpt_scene_file* f, uint32_t* n_media, bdpt_medium* media, uint64_t* n_boundary_tris, double* boundary_verts);
+/* The scene's analytic spheres for bdpt_scene_set_spheres (`analytic: true` on a YAML Sphere surface: an extension; without it the
+ * surface is tessellated like the reference does).  Their materials are part of the table bdpt_scene_file_copy returns (appended
+ * after the triangles' materials).  Call with spheres = NULL for the count. */
+int  bdpt_scene_file_spheres(const bdpt_scene_file* f, uint32_t* n_spheres, bdpt_sphere* spheres);
 int  bdpt_write_png(const char* path, const uint8_t* rgb, int width, int height);
 /* Scene-image files: save writes to a temporary file of its own beside `path` ("<path>.<pid>.<n>.tmp"), syncs it and
  * renames it over `path`, so concurrent savers (ranks missing the same cache) never write into each other's file; map gives a read-only mapping of the file

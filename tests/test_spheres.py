@@ -120,3 +120,87 @@ def test_sphere_argument_checks(bdpt):
         ctx.set_spheres(spheres)
         with pytest.raises(bdpt.BdptError, match="spheres"):
             ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8, weighting=bdpt.WEIGHT_MIS)
+
+
+YAML = """
+camera:
+  resolution: [32, 24]
+  location: [278, 278, -800]
+  look_at: [278, 278, 0]
+  vfov: 40
+  samples_per_pixel: 4
+  max_depth: 8
+  output: balls.png
+materials:
+  white: {type: lambertian, color: [186, 186, 186]}
+  lamp: {type: light, emission: [15, 15, 15]}
+surfaces:
+  - type: mesh
+    material: white
+    vertices: [[0, 0, 0], [555, 0, 0], [555, 0, 555], [0, 0, 555], [0, 555, 555], [555, 555, 555]]
+    triangles: [[0, 1, 2], [0, 2, 3], [3, 2, 5], [3, 5, 4]]
+  - type: mesh
+    material: lamp
+    vertices: [[213, 554, 227], [343, 554, 227], [343, 554, 332], [213, 554, 332]]
+    triangles: [[0, 1, 2], [0, 2, 3]]
+  - type: Sphere
+    analytic: true
+    material: {type: dielectric, ior: 1.5}
+    data: {center: [190, 90, 190], radius: 90}
+  - type: Sphere
+    analytic: true
+    material: {type: metal, color: [204, 217, 224], roughness: 0.1}
+    data: {center: [100, 120, 0], radius: 120}
+    transform:
+      rotate_y: 90
+      translate: [300, 0, 250]
+  - type: Sphere
+    material: {type: lambertian, color: [50, 150, 75]}
+    data: {center: [300, 400, 300], radius: 60}
+"""
+
+
+def test_yaml_analytic_flag(bdpt, tmp_path):
+    """`analytic: true` makes a Sphere surface one exact prim; without it the surface is the reference's 960 triangles."""
+    import math
+    path = tmp_path / "balls.yaml"
+    path.write_text(YAML)
+    s = bdpt.SceneFile(str(path))
+    assert len(s.verts) == 6 + 960 and len(s.spheres) == 2
+    mats = s.material_list()
+    (c0, r0, m0), (c1, r1, m1) = s.spheres
+    assert c0 == (190.0, 90.0, 190.0) and r0 == 90.0 and mats[m0][0] == bdpt.MAT_DIELECTRIC and mats[m0][2] == 1.5
+    r = 90 * 3.1415926535897932385 / 180.0
+    c, sn = math.cos(r), math.sin(r)
+    assert c1 == ((c * 100.0) + (sn * 0.0) + 300, 120.0, (-sn * 100.0) + (c * 0.0) + 250) and r1 == 120.0   # rotate_y, then translate
+    assert mats[m1][0] == bdpt.MAT_METAL and mats[m1][2] == 0.1 and m0 != m1 and max(m0, m1) == len(mats) - 1
+    bad = tmp_path / "bad.yaml"
+    bad.write_text(YAML.replace("material: {type: dielectric, ior: 1.5}", "material: {type: light, emission: [5, 5, 5]}"))
+    with pytest.raises(bdpt.BdptError, match="light"):
+        bdpt.SceneFile(str(bad))
+
+
+@pytest.mark.gpu
+def test_cli_renders_a_yaml_scene_with_analytic_spheres(bdpt, tmp_path):
+    import os
+    import subprocess
+    path = tmp_path / "balls.yaml"
+    path.write_text(YAML)
+    exe = os.path.join(os.path.dirname(bdpt.LIB_PATH), "bdpt")
+    r = subprocess.run([exe, str(path), "--seed", "4", "--quiet"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    s = bdpt.SceneFile(str(path))
+    with bdpt.Context(0) as ctx:
+        ctx.upload(s.verts, s.mat_id, s.materials)
+        ctx.set_spheres(s.spheres)
+        ctx.render(s.camera, seed=4, bvh=bdpt.BVH_FAST)
+        rgb = ctx.film_rgb8(4)
+        ctx.set_spheres([])
+        ctx.render(s.camera, seed=4, bvh=bdpt.BVH_FAST)
+        bare = ctx.film_rgb8(4)
+    assert (rgb != bare).mean() > 0.05
+    ref_png = tmp_path / "ctypes.png"
+    bdpt.write_png(str(ref_png), rgb)
+    assert (tmp_path / "output" / "balls.png").read_bytes() == ref_png.read_bytes()
+    r = subprocess.run([exe, str(path), "--cache", str(tmp_path / "c.bdptimg"), "--quiet"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 1 and "without --cache" in r.stderr
