@@ -14,6 +14,14 @@
 //                    own boxes (fp64), padded and rounded outward like the host builder (fast_bvh.cu).
 // Node ids are handed out per level by an atomic counter, so levels are contiguous in memory (the top of the
 // tree shares cache lines); ids within a level vary from run to run, results do not.
+//
+// Round 2, SAH bottoms (default; BDPT_GPU_TREE_LBVH=1 gives the plain tree above): a range of at most kSahLeaf triangles is
+// not split by its Morton codes but by the exact surface-area heuristic -- its triangles sorted by centroid on each axis in
+// turn, every position swept, the cheapest kept and the range's ids re-ordered accordingly (one thread per node, everything
+// in local memory).  Most of a ray's node visits are in the last levels above the surface it hits, which is where Z-order
+// splits of a few dozen triangles of a surface are poor (long overlapping boxes); the spatial-median top stays.  A variant
+// with a binned-SAH TOP over Morton clusters (HLBVH's scheme) measured no better than the plain tree and was dropped
+// (profiles/r2_rejected_experiments.txt).
 #include "ctx.h"
 
 #include <cub/device/device_radix_sort.cuh>
@@ -78,11 +86,73 @@ __global__ void __launch_bounds__(kBuildBlock) k_gather(const TriGeom* __restric
 
 __device__ __forceinline__ int32_t leaf_code(uint32_t first, uint32_t cnt) { return int32_t(~((first << 3) | (cnt - 1u))); }
 
+// fp32 box of every triangle, by prim id (outward-rounded; only the split heuristic reads them)
+struct __align__(16) PBox { float lx, ly, lz, p0, hx, hy, hz, p1; };
+static_assert(sizeof(PBox) == 32, "PBox must be 32 bytes");
+__global__ void __launch_bounds__(kBuildBlock) k_prim_boxes(const TriGeom* __restrict__ tris, uint32_t n, PBox* __restrict__ pbox) {
+    const uint32_t i = blockIdx.x * kBuildBlock + threadIdx.x;
+    if (i >= n) return;
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    grow_tri(tris[i], lo, hi);
+    pbox[i] = PBox{__double2float_rd(lo[0]), __double2float_rd(lo[1]), __double2float_rd(lo[2]), 0.f,
+                   __double2float_ru(hi[0]), __double2float_ru(hi[1]), __double2float_ru(hi[2]), 0.f};
+}
+
+constexpr int kSahLeafMax = 32;   // ranges up to this many triangles are split by the exact SAH sweep (local arrays of this size)
+
+// Exact SAH split of ids[b, e) (cnt <= kSahLeafMax): returns the split position (b < mid < e) and leaves ids re-ordered so that
+// [b, mid) and [mid, e) are the two sides.  Cost of a split after k triangles of an axis-sorted order: A(L) k + A(R) (cnt - k).
+__device__ __forceinline__ uint32_t sah_split_small(uint32_t* __restrict__ ids, const PBox* __restrict__ pbox, uint32_t b, uint32_t cnt) {
+    uint32_t id[kSahLeafMax];
+    float lo[kSahLeafMax][3], hi[kSahLeafMax][3], key[kSahLeafMax];
+    uint8_t ord[kSahLeafMax], best_ord[kSahLeafMax];
+    for (uint32_t k = 0; k < cnt; ++k) {
+        id[k] = ids[b + k];
+        const float4 a = __ldg(reinterpret_cast<const float4*>(pbox + id[k])), c = __ldg(reinterpret_cast<const float4*>(pbox + id[k]) + 1);
+        lo[k][0] = a.x; lo[k][1] = a.y; lo[k][2] = a.z; hi[k][0] = c.x; hi[k][1] = c.y; hi[k][2] = c.z;
+        best_ord[k] = uint8_t(k);
+    }
+    float best = INFINITY;
+    uint32_t best_k = cnt / 2;
+    float rarea[kSahLeafMax];
+    for (int axis = 0; axis < 3; ++axis) {
+        for (uint32_t k = 0; k < cnt; ++k) { ord[k] = uint8_t(k); key[k] = lo[k][axis] + hi[k][axis]; }
+        for (uint32_t k = 1; k < cnt; ++k) {   // insertion sort of ord by centroid (ties: by position, deterministic)
+            const uint8_t o = ord[k];
+            const float v = key[o];
+            uint32_t j = k;
+            while (j > 0 && key[ord[j - 1]] > v) { ord[j] = ord[j - 1]; --j; }
+            ord[j] = o;
+        }
+        float l3[3] = {INFINITY, INFINITY, INFINITY}, h3[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t k = cnt; k-- > 1;) {   // suffix areas: rarea[k] = area of ord[k..cnt)
+            const uint8_t o = ord[k];
+            for (int c = 0; c < 3; ++c) { l3[c] = fminf(l3[c], lo[o][c]); h3[c] = fmaxf(h3[c], hi[o][c]); }
+            const float dx = h3[0] - l3[0], dy = h3[1] - l3[1], dz = h3[2] - l3[2];
+            rarea[k] = dx * dy + dy * dz + dz * dx;
+        }
+        for (int c = 0; c < 3; ++c) { l3[c] = INFINITY; h3[c] = -INFINITY; }
+        for (uint32_t k = 1; k < cnt; ++k) {   // split after k triangles
+            const uint8_t o = ord[k - 1];
+            for (int c = 0; c < 3; ++c) { l3[c] = fminf(l3[c], lo[o][c]); h3[c] = fmaxf(h3[c], hi[o][c]); }
+            const float dx = h3[0] - l3[0], dy = h3[1] - l3[1], dz = h3[2] - l3[2];
+            const float cost = (dx * dy + dy * dz + dz * dx) * float(k) + rarea[k] * float(cnt - k);
+            if (cost < best) {
+                best = cost; best_k = k;
+                for (uint32_t q = 0; q < cnt; ++q) best_ord[q] = ord[q];
+            }
+        }
+    }
+    for (uint32_t k = 0; k < cnt; ++k) ids[b + k] = id[best_ord[k]];
+    return b + best_k;
+}
+
 // nodes [first_node, first_node + n_level) of one level split their ranges; children that stay internal get ids
 // from `counter` (all of them on the next level)
 __global__ void __launch_bounds__(kBuildBlock) k_split(const unsigned long long* __restrict__ keys, uint32_t* __restrict__ nb,
                                                        uint32_t* __restrict__ ne, FastNode* __restrict__ nodes, uint32_t* counter,
-                                                       uint32_t first_node, uint32_t n_level, int level) {
+                                                       uint32_t first_node, uint32_t n_level, int level,
+                                                       uint32_t* __restrict__ ids, const PBox* __restrict__ pbox, uint32_t sah_leaf) {
     const uint32_t j = blockIdx.x * kBuildBlock + threadIdx.x;
     if (j >= n_level) return;
     const uint32_t i = first_node + j;
@@ -93,7 +163,8 @@ __global__ void __launch_bounds__(kBuildBlock) k_split(const unsigned long long*
     } else {
         const unsigned long long kf = keys[b], kl = keys[e - 1];
         uint32_t mid;
-        if (kf == kl) mid = b + cnt / 2;
+        if (cnt <= sah_leaf) mid = sah_split_small(ids, pbox, b, cnt);   // (keys are not read again below this node)
+        else if (kf == kl) mid = b + cnt / 2;
         else {
             const int p = __clzll((long long)(kf ^ kl));
             uint32_t lo = b, hi = e - 1;   // keys[lo] shares more than p leading bits with kf, keys[hi] exactly p
@@ -214,7 +285,13 @@ int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const d
     GB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys, keys_sorted, ids, prims, int(n), 0, 63, st));
     GB_CUDA(tmp.take(reinterpret_cast<char**>(&sort_tmp), sort_bytes));
     GB_CUDA(cub::DeviceRadixSort::SortPairs(sort_tmp, sort_bytes, keys, keys_sorted, ids, prims, int(n), 0, 63, st));
-    k_gather<<<grid_n, kBuildBlock, 0, st>>>(d_tris, prims, n, ftris);
+    // exact-SAH bottoms: ranges of <= sah_leaf triangles are split by the surface-area sweep over fp32 triangle boxes
+    uint32_t sah_leaf = kSahLeafMax;
+    if (const char* e = std::getenv("BDPT_GPU_TREE_LBVH")) if (std::atoi(e) != 0) sah_leaf = 0;
+    if (const char* e = std::getenv("BDPT_GPU_TREE_SAH_LEAF")) sah_leaf = uint32_t(std::max(0, std::min(kSahLeafMax, std::atoi(e))));
+    PBox* pbox = nullptr;
+    GB_CUDA(tmp.take(&pbox, n));
+    k_prim_boxes<<<grid_n, kBuildBlock, 0, st>>>(d_tris, n, pbox);
     // ---- top-down
     const uint32_t root_range[2] = {0u, n};
     const uint32_t one = 1u;
@@ -228,13 +305,15 @@ int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const d
         const uint32_t first = level_first.back(), cnt = total - first;
         if (cnt == 0) { level_first.pop_back(); break; }
         if (level > kMaxLevel) { ctx->err = "gpu bvh build: depth bound violated"; return BDPT_ERR_CUDA; }
-        k_split<<<(cnt + kBuildBlock - 1) / kBuildBlock, kBuildBlock, 0, st>>>(keys_sorted, nb, ne, nodes, counter, first, cnt, level);
+        k_split<<<(cnt + kBuildBlock - 1) / kBuildBlock, kBuildBlock, 0, st>>>(keys_sorted, nb, ne, nodes, counter, first, cnt, level, prims, pbox, sah_leaf);
         uint32_t now = 0;
         GB_CUDA(cudaMemcpyAsync(&now, counter, 4, cudaMemcpyDeviceToHost, st));
         GB_CUDA(cudaStreamSynchronize(st));
         level_first.push_back(total);
         total = now;
     }
+    // the triangles in their final order (the SAH bottoms re-ordered the ids inside their ranges)
+    k_gather<<<grid_n, kBuildBlock, 0, st>>>(d_tris, prims, n, ftris);
     // ---- bottom-up
     const double eps = std::max(extent, 1e-30) * (1.0 / 65536.0);   // the host builder's outward padding
     for (size_t l = level_first.size(); l-- > 0;) {

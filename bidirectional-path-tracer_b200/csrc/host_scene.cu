@@ -225,7 +225,8 @@ void build_ref_bvh(HostScene& s) {
     auto lap = [&](const char* what) {
         if (timing) std::fprintf(stderr, "  reference tree: %s at %.1f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     };
-    b.build(0, n, 0, 0, 4);   // up to 16 subtrees in flight
+    static const int fork_levels = [] { const char* e = std::getenv("BDPT_REF_FORKS"); return e ? std::atoi(e) : 4; }();
+    b.build(0, n, 0, 0, fork_levels);   // up to 2^fork_levels subtrees in flight (4: 16)
     lap("nodes built");
     s.ref_depth = b.max_depth.load() + 1;
     s.dfs_rank.resize(n);

@@ -1,5 +1,5 @@
 """Development aid: quality and speed of the three fast-tree builders on bench.py's scene (config 3) --
-host binned SAH, device SAH over the Morton order, device LBVH (BDPT_GPU_TREE_LBVH (not in the tree any more)=1)."""
+host binned SAH, device SAH over the Morton order, device LBVH (BDPT_GPU_TREE_LBVH=1)."""
 import importlib, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
@@ -8,8 +8,8 @@ bench.ensure_scenes()
 sf = b.SceneFile(os.environ.get("SCENE", bench.SCENE))
 cam = sf.camera_with(bench.WIDTH, bench.HEIGHT, bench.SPP, bench.DEPTH)
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 4
-for tag, gpu_tree, lbvh in (("host_sah", False, "0"), ("gpu_sah_morton", True, "0"), ("gpu_lbvh", True, "1")):
-    os.environ["BDPT_GPU_TREE_LBVH (not in the tree any more)"] = lbvh
+for tag, gpu_tree, lbvh in (("host_sah", False, "0"), ("gpu_sah_bottoms", True, "0"), ("gpu_lbvh", True, "1")):
+    os.environ["BDPT_GPU_TREE_LBVH"] = lbvh
     with b.Context(0) as ctx:
         ctx.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=gpu_tree)          # warm
         t0 = time.perf_counter(); ctx.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=gpu_tree); up = time.perf_counter() - t0
