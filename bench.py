@@ -409,7 +409,7 @@ def run_ours(args):
     if rank == 0:
         line = {"metric": "BDPT Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": Wm,
                 "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic", "config": dict(workload_config(), bvh=args.bvh, fast_tree="device, Morton order" if args.gpu_tree else "host, binned SAH"),
+                "dtype": "f64", "data": "synthetic", "config": dict(workload_config(), bvh=args.bvh, fast_tree="host, binned SAH" if args.gpu_tree is False else "device, binned SAH (library default)"),
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
                         "rank0_ms": e2e_parts, "all_passes_msamples_per_s": [samples / p["seconds_max_over_ranks"] / 1e6 for p in passes],
                         "all_passes_rank0_ms": passes,
@@ -712,7 +712,8 @@ def main():
     ap.add_argument("--seed", type=int, default=20261104)
     ap.add_argument("--batch", type=int, default=0, help="sample slots per wavefront (0 = library default)")
     ap.add_argument("--streams", type=int, default=0, help="wavefronts in flight (0 = library default)")
-    ap.add_argument("--gpu-tree", action="store_true", help="build the fast tree on the device (Morton order) instead of the host binned-SAH build")
+    ap.add_argument("--host-tree", dest="gpu_tree", action="store_const", const=False, default=None, help="build the fast tree with the host's binned-SAH builder instead of on the device (the library's default)")
+    ap.add_argument("--gpu-tree", dest="gpu_tree", action="store_const", const=True, help="build the fast tree on the device (the default)")
     ap.add_argument("--skip-micro", action="store_true")
     ap.add_argument("--skip-frame", action="store_true", help="skip the whole-frame leg (BASELINE.json config 4: 23 s on one GPU)")
     ap.add_argument("--skip-configs", action="store_true", help="skip the config 1 / config 5 legs")

@@ -92,6 +92,7 @@ IMAGE_TRUSTED = 2
 RENDER_STATS = 1
 RENDER_SERIAL = 2
 UPLOAD_FAST_TREE_GPU = 1
+UPLOAD_FAST_TREE_HOST = 2
 KERNEL_CLASSES = ("generate", "trace", "shade", "connect", "shadow", "trace_exact", "shadow_exact")
 
 
@@ -457,15 +458,16 @@ class Context:
     def __exit__(self, *a):
         self.close()
 
-    def upload(self, verts, mat_id, mats, gpu_tree=False):
-        """bdpt_scene_upload; gpu_tree: build the BVH_FAST tree on the device (UPLOAD_FAST_TREE_GPU)."""
+    def upload(self, verts, mat_id, mats, gpu_tree=None):
+        """bdpt_scene_upload; gpu_tree: where the BVH_FAST tree is built -- None: the library's default (the device), True:
+        the device (UPLOAD_FAST_TREE_GPU), False: the host's binned-SAH build (UPLOAD_FAST_TREE_HOST)."""
         v = np.ascontiguousarray(verts, dtype=np.float64).reshape(-1, 9)
         m = np.ascontiguousarray(mat_id, dtype=np.uint32)
         if len(m) != len(v):
             raise ValueError("mat_id length")
         marr = make_materials(mats) if isinstance(mats, list) else mats
         self._chk(lib().bdpt_scene_upload_ex(self._h, v.ctypes.data, m.ctypes.data, len(v), C.byref(marr), len(marr),
-                                             UPLOAD_FAST_TREE_GPU if gpu_tree else 0), "bdpt_scene_upload")
+                                             0 if gpu_tree is None else (UPLOAD_FAST_TREE_GPU if gpu_tree else UPLOAD_FAST_TREE_HOST)), "bdpt_scene_upload")
         self.n_tris = len(v)
         return self
 

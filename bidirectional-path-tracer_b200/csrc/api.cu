@@ -344,8 +344,9 @@ int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id
 int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                          const bdpt_material* mats, uint32_t n_mats, uint32_t flags) {
     if (!ctx) return BDPT_ERR_ARG;
-    if (flags & ~BDPT_UPLOAD_FAST_TREE_GPU) { ctx->err = "unknown upload flags"; return BDPT_ERR_ARG; }
-    const bool gpu_tree = (flags & BDPT_UPLOAD_FAST_TREE_GPU) != 0;
+    if (flags & ~(BDPT_UPLOAD_FAST_TREE_GPU | BDPT_UPLOAD_FAST_TREE_HOST)) { ctx->err = "unknown upload flags"; return BDPT_ERR_ARG; }
+    // the fast tree is built on the device unless the host build is asked for (or its 4-wide form is: BDPT_WIDE)
+    const bool gpu_tree = (flags & BDPT_UPLOAD_FAST_TREE_GPU) != 0 || (!(flags & BDPT_UPLOAD_FAST_TREE_HOST) && bdpt::wide_walk_mode() == 0u);
     BDPT_CUDA(ctx, cudaSetDevice(ctx->device));
     const bool timing = std::getenv("BDPT_TIMING") != nullptr;
     auto now = [] { return std::chrono::steady_clock::now(); };

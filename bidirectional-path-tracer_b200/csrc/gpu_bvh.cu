@@ -15,8 +15,11 @@
 // Node ids are handed out per level by an atomic counter, so levels are contiguous in memory (the top of the
 // tree shares cache lines); ids within a level vary from run to run, results do not.
 //
-// Round 2, SAH bottoms (default; BDPT_GPU_TREE_LBVH=1 gives the plain tree above): a range of at most kSahLeaf triangles is
-// not split by its Morton codes but by the exact surface-area heuristic -- its triangles sorted by centroid on each axis in
+// Round 2, SAH at every level (default; BDPT_GPU_TREE_SAH=0 keeps the Morton splits above the bottoms, BDPT_GPU_TREE_LBVH=1 gives
+// the plain tree above): ranges of more than kSahLeafMax triangles are split by binned SAH with an in-place, stable partition
+// (k_sah_big: one thread block per node, 16 bins on each axis, the host builder's algorithm one level at a time; the Morton sort
+// stays as the initial order, which makes the bins of neighbouring triangles coincide and the partition's writes coalesce), and
+// a range of at most kSahLeafMax triangles is not split by its Morton codes but by the exact surface-area heuristic -- its triangles sorted by centroid on each axis in
 // turn, every position swept, the cheapest kept and the range's ids re-ordered accordingly (one thread per node, everything
 // in local memory).  Most of a ray's node visits are in the last levels above the surface it hits, which is where Z-order
 // splits of a few dozen triangles of a surface are poor (long overlapping boxes); the spatial-median top stays.  A variant
@@ -152,11 +155,12 @@ __device__ __forceinline__ uint32_t sah_split_small(uint32_t* __restrict__ ids, 
 __global__ void __launch_bounds__(kBuildBlock) k_split(const unsigned long long* __restrict__ keys, uint32_t* __restrict__ nb,
                                                        uint32_t* __restrict__ ne, FastNode* __restrict__ nodes, uint32_t* counter,
                                                        uint32_t first_node, uint32_t n_level, int level,
-                                                       uint32_t* __restrict__ ids, const PBox* __restrict__ pbox, uint32_t sah_leaf) {
+                                                       uint32_t* __restrict__ ids, const PBox* __restrict__ pbox, uint32_t sah_leaf, int sah_all) {
     const uint32_t j = blockIdx.x * kBuildBlock + threadIdx.x;
     if (j >= n_level) return;
     const uint32_t i = first_node + j;
     const uint32_t b = nb[i], e = ne[i], cnt = e - b;
+    if (sah_all && cnt > sah_leaf) return;   // k_sah_big's node
     int32_t link[2];
     if (cnt == 1) {   // a one-triangle scene: the root needs two children
         link[0] = link[1] = leaf_code(b, 1);
@@ -192,6 +196,194 @@ __global__ void __launch_bounds__(kBuildBlock) k_split(const unsigned long long*
     nodes[i].left = link[0];
     nodes[i].right = link[1];
     nodes[i].pad[0] = 0; nodes[i].pad[1] = 0;
+}
+
+
+// ---------------------------------------------------------------- binned SAH for the ranges above kSahLeafMax (BDPT_GPU_TREE_SAH=1)
+// One thread block per node: centroid bounds, 16 bins on each of the three axes in shared memory, the cheapest of the 45
+// planes (A(L) |L| + A(R) |R|), the range's ids partitioned in place through ids_tmp.  The algorithm of the host builder
+// (fast_bvh.cu) one level at a time; a node's cost is one block streaming its range three times, so the top levels of a
+// 10^7-triangle scene are slow (one block per huge node) -- what this variant is for is tree QUALITY on the device.
+constexpr int kSahBlock = 128;
+constexpr int kBins = 16;
+__device__ __forceinline__ void atomic_min_f(float* a, float v) {
+    if (v >= 0.f) atomicMin(reinterpret_cast<int*>(a), __float_as_int(v)); else atomicMax(reinterpret_cast<unsigned*>(a), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_f(float* a, float v) {
+    if (v >= 0.f) atomicMax(reinterpret_cast<int*>(a), __float_as_int(v)); else atomicMin(reinterpret_cast<unsigned*>(a), __float_as_uint(v));
+}
+__device__ __forceinline__ void load_pbox(const PBox* __restrict__ pbox, uint32_t id, float lo[3], float hi[3]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(pbox + id)), c = __ldg(reinterpret_cast<const float4*>(pbox + id) + 1);
+    lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = c.x; hi[1] = c.y; hi[2] = c.z;
+}
+
+__device__ __forceinline__ void load_box_plain(const PBox* pb, uint32_t k, float lo[3], float hi[3]) {   // pcur is written by this kernel: no read-only path
+    const float4 a = reinterpret_cast<const float4*>(pb + k)[0], c = reinterpret_cast<const float4*>(pb + k)[1];
+    lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = c.x; hi[1] = c.y; hi[2] = c.z;
+}
+// boxes into position order (pcur[k] = pbox[ids[k]]): the big-node passes then read their ranges sequentially
+__global__ void __launch_bounds__(kBuildBlock) k_gather_boxes(const PBox* __restrict__ pbox, const uint32_t* __restrict__ ids, uint32_t n, PBox* __restrict__ pcur) {
+    const uint32_t i = blockIdx.x * kBuildBlock + threadIdx.x;
+    if (i >= n) return;
+    const float4* s4 = reinterpret_cast<const float4*>(pbox + ids[i]);
+    float4* d4 = reinterpret_cast<float4*>(pcur + i);
+    d4[0] = __ldg(s4); d4[1] = __ldg(s4 + 1);
+}
+
+// NT threads per node; nodes with cnt in (lo_cnt, hi_cnt] are this launch's (two launches per level: big blocks for the few huge
+// ranges at the top, small blocks for the many ranges further down).  Each thread walks a CONTIGUOUS chunk of the range and keeps
+// a running (bin, count, box) per axis that is flushed to the shared bins only when the bin changes: the range is in Morton order
+// (the partition below is stable), neighbours fall into the same bin, and the shared-memory atomics stop being 32-way conflicts.
+template <int NT>
+__global__ void __launch_bounds__(NT) k_sah_big(PBox* __restrict__ pcur, PBox* __restrict__ ptmp, uint32_t* __restrict__ ids, uint32_t* __restrict__ ids_tmp,
+                                                uint32_t* __restrict__ nb, uint32_t* __restrict__ ne, FastNode* __restrict__ nodes,
+                                                uint32_t* counter, uint32_t first_node, int level, uint32_t lo_cnt, uint32_t hi_cnt) {
+    const uint32_t i = first_node + blockIdx.x;
+    const uint32_t b = nb[i], e = ne[i], cnt = e - b;
+    if (cnt <= lo_cnt || cnt > hi_cnt) return;
+    __shared__ float s_clo[3], s_chi[3];
+    __shared__ unsigned s_cnt[3][kBins];
+    __shared__ float s_lo[3][kBins][3], s_hi[3][kBins][3];
+    __shared__ float s_best_cost[3];
+    __shared__ int s_best_plane[3];
+    __shared__ int s_axis, s_plane;
+    __shared__ unsigned s_scan[NT];
+    __shared__ unsigned s_nleft;
+    const int t = threadIdx.x;
+    if (t < 3) { s_clo[t] = INFINITY; s_chi[t] = -INFINITY; }
+    for (int k = t; k < 3 * kBins; k += NT) {
+        const int a = k / kBins, bi = k % kBins;
+        s_cnt[a][bi] = 0;
+        for (int c = 0; c < 3; ++c) { s_lo[a][bi][c] = INFINITY; s_hi[a][bi][c] = -INFINITY; }
+    }
+    __syncthreads();
+    const uint32_t per = (cnt + NT - 1) / NT;
+    const uint32_t c0 = min(cnt, uint32_t(t) * per), c1 = min(cnt, c0 + per);
+    {   // centroid bounds (twice the centroid: lo + hi)
+        float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t k = c0; k < c1; ++k) {
+            float lo[3], hi[3];
+            load_box_plain(pcur, b + k, lo, hi);
+            for (int a = 0; a < 3; ++a) { const float c2 = lo[a] + hi[a]; mn[a] = fminf(mn[a], c2); mx[a] = fmaxf(mx[a], c2); }
+        }
+        for (int a = 0; a < 3; ++a) { if (mn[a] <= mx[a]) { atomic_min_f(&s_clo[a], mn[a]); atomic_max_f(&s_chi[a], mx[a]); } }
+    }
+    __syncthreads();
+    float scale[3];
+    for (int a = 0; a < 3; ++a) { const float ext = s_chi[a] - s_clo[a]; scale[a] = ext > 0.f ? float(kBins) * 0.999999f / ext : 0.f; }
+    {   // binning with run-length accumulation per axis
+        int cur[3] = {-1, -1, -1};
+        unsigned rc[3] = {0, 0, 0};
+        float rl[3][3], rh[3][3];
+        auto flush = [&](int a) {
+            if (cur[a] < 0 || rc[a] == 0) return;
+            atomicAdd(&s_cnt[a][cur[a]], rc[a]);
+            for (int c = 0; c < 3; ++c) { atomic_min_f(&s_lo[a][cur[a]][c], rl[a][c]); atomic_max_f(&s_hi[a][cur[a]][c], rh[a][c]); }
+        };
+        for (uint32_t k = c0; k < c1; ++k) {
+            float lo[3], hi[3];
+            load_box_plain(pcur, b + k, lo, hi);
+            for (int a = 0; a < 3; ++a) {
+                const int bi = min(kBins - 1, max(0, int(((lo[a] + hi[a]) - s_clo[a]) * scale[a])));
+                if (bi != cur[a]) {
+                    flush(a);
+                    cur[a] = bi; rc[a] = 0;
+                    for (int c = 0; c < 3; ++c) { rl[a][c] = INFINITY; rh[a][c] = -INFINITY; }
+                }
+                ++rc[a];
+                for (int c = 0; c < 3; ++c) { rl[a][c] = fminf(rl[a][c], lo[c]); rh[a][c] = fmaxf(rh[a][c], hi[c]); }
+            }
+        }
+        for (int a = 0; a < 3; ++a) flush(a);
+    }
+    __syncthreads();
+    if (t < 3) {   // one axis per thread: suffix boxes, then the sweep
+        float best = INFINITY;
+        int plane = -1;
+        float rarea[kBins];
+        unsigned rn[kBins];
+        float l3[3] = {INFINITY, INFINITY, INFINITY}, h3[3] = {-INFINITY, -INFINITY, -INFINITY};
+        unsigned acc = 0;
+        for (int k = kBins - 1; k >= 0; --k) {
+            acc += s_cnt[t][k];
+            for (int c = 0; c < 3; ++c) { l3[c] = fminf(l3[c], s_lo[t][k][c]); h3[c] = fmaxf(h3[c], s_hi[t][k][c]); }
+            rn[k] = acc;
+            const float dx = h3[0] - l3[0], dy = h3[1] - l3[1], dz = h3[2] - l3[2];
+            rarea[k] = acc ? dx * dy + dy * dz + dz * dx : 0.f;
+        }
+        for (int c = 0; c < 3; ++c) { l3[c] = INFINITY; h3[c] = -INFINITY; }
+        acc = 0;
+        for (int k = 0; k + 1 < kBins; ++k) {   // plane between bins k and k + 1
+            acc += s_cnt[t][k];
+            for (int c = 0; c < 3; ++c) { l3[c] = fminf(l3[c], s_lo[t][k][c]); h3[c] = fmaxf(h3[c], s_hi[t][k][c]); }
+            const unsigned nr = rn[k + 1];
+            if (acc == 0 || nr == 0) continue;
+            const float dx = h3[0] - l3[0], dy = h3[1] - l3[1], dz = h3[2] - l3[2];
+            const float cost = (dx * dy + dy * dz + dz * dx) * float(acc) + rarea[k + 1] * float(nr);
+            if (cost < best) { best = cost; plane = k + 1; }
+        }
+        s_best_cost[t] = best; s_best_plane[t] = plane;
+    }
+    __syncthreads();
+    if (t == 0) {
+        int axis = -1;
+        float best = INFINITY;
+        for (int a = 0; a < 3; ++a) if (s_best_plane[a] > 0 && s_best_cost[a] < best) { best = s_best_cost[a]; axis = a; }
+        s_axis = axis; s_plane = axis >= 0 ? s_best_plane[axis] : 0;
+        if (axis >= 0) {   // depth bound: no child may hold more than 2^(kMaxLevel - level) triangles (as in split_node)
+            const uint32_t cap = 1u << (kMaxLevel - level);
+            unsigned nl = 0;
+            for (int k = 0; k < s_plane; ++k) nl += s_cnt[axis][k];
+            if (nl > cap || cnt - nl > cap) s_axis = -1;
+        }
+    }
+    __syncthreads();
+    const int axis = s_axis, plane = s_plane;
+    uint32_t n_left;
+    if (axis < 0) n_left = cnt / 2;   // no plane (coincident centroids) or the depth bound: split the list where it stands
+    else {
+        unsigned mine = 0;
+        for (uint32_t k = c0; k < c1; ++k) {
+            float lo[3], hi[3];
+            load_box_plain(pcur, b + k, lo, hi);
+            const int bi = min(kBins - 1, max(0, int(((lo[axis] + hi[axis]) - s_clo[axis]) * scale[axis])));
+            mine += bi < plane ? 1u : 0u;
+        }
+        s_scan[t] = mine;
+        __syncthreads();
+        if (t == 0) { unsigned run = 0; for (int k = 0; k < NT; ++k) { const unsigned v = s_scan[k]; s_scan[k] = run; run += v; } s_nleft = run; }
+        __syncthreads();
+        n_left = s_nleft;
+        uint32_t lpos = s_scan[t], rpos = n_left + (c0 - s_scan[t]);
+        for (uint32_t k = c0; k < c1; ++k) {   // stable: both sides keep their relative (Morton) order
+            const float4 q0 = reinterpret_cast<const float4*>(pcur + b + k)[0], q1 = reinterpret_cast<const float4*>(pcur + b + k)[1];
+            const int bi = min(kBins - 1, max(0, int(((axis == 0 ? q0.x + q1.x : (axis == 1 ? q0.y + q1.y : q0.z + q1.z)) - s_clo[axis]) * scale[axis])));
+            const uint32_t dst = b + (bi < plane ? lpos++ : rpos++);
+            ids_tmp[dst] = ids[b + k];
+            reinterpret_cast<float4*>(ptmp + dst)[0] = q0; reinterpret_cast<float4*>(ptmp + dst)[1] = q1;
+        }
+        __syncthreads();
+        for (uint32_t k = b + t; k < e; k += NT) {
+            ids[k] = ids_tmp[k];
+            reinterpret_cast<float4*>(pcur + k)[0] = reinterpret_cast<const float4*>(ptmp + k)[0];
+            reinterpret_cast<float4*>(pcur + k)[1] = reinterpret_cast<const float4*>(ptmp + k)[1];
+        }
+    }
+    if (t == 0) {
+        const uint32_t cb[2] = {b, b + n_left}, ce[2] = {b + n_left, e};
+        int32_t link[2];
+        for (int s = 0; s < 2; ++s) {
+            const uint32_t c = ce[s] - cb[s];
+            if (c <= 2) link[s] = leaf_code(cb[s], c);
+            else {
+                const uint32_t id = atomicAdd(counter, 1u);
+                nb[id] = cb[s]; ne[id] = ce[s];
+                link[s] = int32_t(id);
+            }
+        }
+        nodes[i].left = link[0]; nodes[i].right = link[1];
+        nodes[i].pad[0] = 0; nodes[i].pad[1] = 0;
+    }
 }
 
 __global__ void __launch_bounds__(kBuildBlock) k_boxes(const TriGeom* __restrict__ ftris, FastNode* __restrict__ nodes, double* __restrict__ own,
@@ -292,6 +484,16 @@ int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const d
     PBox* pbox = nullptr;
     GB_CUDA(tmp.take(&pbox, n));
     k_prim_boxes<<<grid_n, kBuildBlock, 0, st>>>(d_tris, n, pbox);
+    int sah_all = sah_leaf >= 2 ? 1 : 0;   // binned SAH above the exact-sweep ranges as well (k_sah_big); BDPT_GPU_TREE_SAH=0: Morton splits there
+    if (const char* e = std::getenv("BDPT_GPU_TREE_SAH")) sah_all = std::atoi(e) != 0 && sah_leaf >= 2 ? 1 : 0;
+    uint32_t* ids_tmp = nullptr;
+    PBox *pcur = nullptr, *ptmp = nullptr;
+    if (sah_all) {
+        GB_CUDA(tmp.take(&ids_tmp, n));
+        GB_CUDA(tmp.take(&pcur, n));
+        GB_CUDA(tmp.take(&ptmp, n));
+        k_gather_boxes<<<grid_n, kBuildBlock, 0, st>>>(pbox, prims, n, pcur);
+    }
     // ---- top-down
     const uint32_t root_range[2] = {0u, n};
     const uint32_t one = 1u;
@@ -305,7 +507,12 @@ int build_fast_bvh_gpu(bdpt_ctx* ctx, const TriGeom* d_tris, uint32_t n, const d
         const uint32_t first = level_first.back(), cnt = total - first;
         if (cnt == 0) { level_first.pop_back(); break; }
         if (level > kMaxLevel) { ctx->err = "gpu bvh build: depth bound violated"; return BDPT_ERR_CUDA; }
-        k_split<<<(cnt + kBuildBlock - 1) / kBuildBlock, kBuildBlock, 0, st>>>(keys_sorted, nb, ne, nodes, counter, first, cnt, level, prims, pbox, sah_leaf);
+        if (sah_all) {
+            constexpr uint32_t kHuge = 8192;   // ranges above this get 1024 threads, the others 128
+            if (level <= 12) k_sah_big<1024><<<cnt, 1024, 0, st>>>(pcur, ptmp, prims, ids_tmp, nb, ne, nodes, counter, first, level, kHuge, 0xFFFFFFFFu);
+            k_sah_big<kSahBlock><<<cnt, kSahBlock, 0, st>>>(pcur, ptmp, prims, ids_tmp, nb, ne, nodes, counter, first, level, sah_leaf, level <= 12 ? kHuge : 0xFFFFFFFFu);
+        }
+        k_split<<<(cnt + kBuildBlock - 1) / kBuildBlock, kBuildBlock, 0, st>>>(keys_sorted, nb, ne, nodes, counter, first, cnt, level, prims, pbox, sah_leaf, sah_all);
         uint32_t now = 0;
         GB_CUDA(cudaMemcpyAsync(&now, counter, 4, cudaMemcpyDeviceToHost, st));
         GB_CUDA(cudaStreamSynchronize(st));

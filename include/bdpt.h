@@ -157,14 +157,19 @@ const char* bdpt_last_error(bdpt_ctx* ctx);   /* ctx may be NULL: last creation 
 /* Triangle soup in scene.world insertion order (prim ID = index); verts is n_tris x 9
  * doubles (v0,v1,v2: triangle.h:21). Lights are the triangles whose material is BDPT_MAT_LIGHT, in
  * insertion order (scene_loader.h:190-202); if there are none every triangle is a light (main.cpp:67).
- * Builds both BVH flavours on the host and uploads them. */
+ * Builds both BVH flavours (the reference topology on the host, the fast tree on the device) and uploads them. */
 int bdpt_scene_upload(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                       const bdpt_material* mats, uint32_t n_mats);
-/* The same with options.  BDPT_UPLOAD_FAST_TREE_GPU: the BDPT_BVH_FAST tree is built on the device (Morton
- * sort + top-down splits with a depth bound, csrc/gpu_bvh.cu) instead of the host's binned-SAH build: a few
- * ms for 10^7 triangles against seconds, for a tree that costs the walk more node visits per ray.  Results
- * are identical either way (the tree only selects candidates for the exact test).  SURVEY 8f-1. */
+/* The same with options.  Where the BDPT_BVH_FAST tree is built (results are identical either way: the tree only selects
+ * candidates for the exact test):
+ *   default (0) / BDPT_UPLOAD_FAST_TREE_GPU   on the device (csrc/gpu_bvh.cu): Morton sort, then binned SAH with in-place
+ *       partition at every level down to ranges of 32 triangles and the exact SAH sweep below -- the host builder's algorithm
+ *       and its tree quality (20.2 nodes per closest ray on the bench scene for both), 11 ms for 180 k triangles against 35-45;
+ *       the reference-topology tree (bvh.h:20-48) is built on the host meanwhile
+ *   BDPT_UPLOAD_FAST_TREE_HOST               the host's threaded binned-SAH build (also what bdpt_scene_image_build uses, which
+ *       needs no device, and what carries the optional 4-wide tree of BDPT_WIDE) */
 #define BDPT_UPLOAD_FAST_TREE_GPU 1u
+#define BDPT_UPLOAD_FAST_TREE_HOST 2u
 int bdpt_scene_upload_ex(bdpt_ctx* ctx, const double* verts, const uint32_t* mat_id, uint64_t n_tris,
                          const bdpt_material* mats, uint32_t n_mats, uint32_t flags);
 /* The texture table bdpt_material.tex refers to, with its data blob (copied; may be freed on return).  Belongs to the

@@ -12,7 +12,7 @@ from tools import testscenes as ts
 
 g = int(sys.argv[1]) if len(sys.argv) > 1 else 50
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
-gpu_tree = bool(int(sys.argv[3])) if len(sys.argv) > 3 else False
+gpu_tree = bool(int(sys.argv[3])) if len(sys.argv) > 3 else None
 W, H, SPP, DEPTH, STRATA = 1920, 1080, 64, 32, 2
 pkg = importlib.import_module("bidirectional-path-tracer_b200")
 t0 = time.perf_counter()
@@ -41,5 +41,5 @@ with pkg.Context(0) as ctx:
             "ms_per_step": ms / steps, "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow": st["rays_shadow"] / st["samples"]},
             "nodes_per_closest_ray": s2["nodes_closest"] / max(1, s2["rays_closest"]), "tris_per_closest_ray": s2["tris_closest"] / max(1, s2["rays_closest"]),
             "bvh_nodes": {"fast": ctx.bvh_info(pkg.BVH_FAST), "reference": ctx.bvh_info(pkg.BVH_REFERENCE)},
-            "fast_tree": "device, Morton order" if gpu_tree else "host, binned SAH", "host_s": {"generate": t_gen, "upload_and_both_bvh_builds": t_up}, "deferred_closest": st["deferred_closest"]}
+            "fast_tree": "host, binned SAH" if gpu_tree is False else "device, binned SAH", "host_s": {"generate": t_gen, "upload_and_both_bvh_builds": t_up}, "deferred_closest": st["deferred_closest"]}
     print(json.dumps(line))

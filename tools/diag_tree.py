@@ -8,8 +8,9 @@ bench.ensure_scenes()
 sf = b.SceneFile(os.environ.get("SCENE", bench.SCENE))
 cam = sf.camera_with(bench.WIDTH, bench.HEIGHT, bench.SPP, bench.DEPTH)
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 4
-for tag, gpu_tree, lbvh in (("host_sah", False, "0"), ("gpu_sah_bottoms", True, "0"), ("gpu_lbvh", True, "1")):
+for tag, gpu_tree, lbvh, sah in (("host_sah", False, "0", "1"), ("gpu_sah_all", True, "0", "1"), ("gpu_sah_bottoms", True, "0", "0"), ("gpu_lbvh", True, "1", "0")):
     os.environ["BDPT_GPU_TREE_LBVH"] = lbvh
+    os.environ["BDPT_GPU_TREE_SAH"] = sah
     with b.Context(0) as ctx:
         ctx.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=gpu_tree)          # warm
         t0 = time.perf_counter(); ctx.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=gpu_tree); up = time.perf_counter() - t0
