@@ -122,11 +122,14 @@ struct RefBuilder {
             // permutation equals that of sorting the pointers, without a cache miss per comparison.
             const double* tb = s.tri_box.data();
             struct KeyId { double key; uint32_t id; };
-            std::vector<KeyId> tmp(span);
+            KeyId few[128];                 // most nodes are small: no heap allocation for them (92 k nodes for 180 k triangles)
+            std::vector<KeyId> many;
+            KeyId* tmp = few;
+            if (span > 128) { many.resize(span); tmp = many.data(); }
             for (size_t i = 0; i < span; ++i) { const uint32_t p = order[start + i]; tmp[i] = KeyId{tb[6 * size_t(p) + axis], p}; }
             auto by_key = [](const KeyId& a, const KeyId& b) { return a.key < b.key; };
-            if (fork_levels > 0 && span > 32768) sort_like_std(tmp.begin(), tmp.end(), by_key, fork_levels);
-            else std::sort(tmp.begin(), tmp.end(), by_key);
+            if (fork_levels > 0 && span > 32768) sort_like_std(tmp, tmp + span, by_key, fork_levels);
+            else std::sort(tmp, tmp + span, by_key);   // the same introsort over pointers as over vector iterators: the same permutation
             for (size_t i = 0; i < span; ++i) order[start + i] = tmp[i].id;
             const size_t mid = start + span / 2;
             const size_t left = me + 1, right = me + 1 + count(mid - start);   // preorder
