@@ -1019,8 +1019,11 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
 // Thread idx walks the concatenation light | lambertian | metal | dielectric of the queues k_trace_* filled, so
 // a warp straddles at most one class boundary; the survivors' queue append and the retirement of ended
 // subpaths are shared.
+#ifndef BDPT_SHADE_BLOCKS
+#define BDPT_SHADE_BLOCKS 3
+#endif
 template <bool MIS, bool TEX, bool MEDIA = false>
-__global__ void __launch_bounds__(kWide, 3) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
+__global__ void __launch_bounds__(kWide, BDPT_SHADE_BLOCKS) k_shade(SceneView sc, Frame f, WF w, int nxt, int dn, double* film) {
     const uint32_t idx = blockIdx.x * kWide + threadIdx.x;
     const uint32_t n_li = w.counters[C_MAT0 + BDPT_MAT_LIGHT], n_la = w.counters[C_MAT0 + BDPT_MAT_LAMBERTIAN],
                    n_me = w.counters[C_MAT0 + BDPT_MAT_METAL], n_di = w.counters[C_MAT0 + BDPT_MAT_DIELECTRIC];
