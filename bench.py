@@ -257,6 +257,11 @@ def run_ours(args):
     import torch
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and "BDPT_REF_FORKS" not in os.environ:
+        # several ranks build their reference-topology trees side by side: cores / world subtrees in flight per rank (the
+        # library's default of 16 assumes the box to itself)
+        per_rank = max(2, (os.cpu_count() or 16) // world)
+        os.environ["BDPT_REF_FORKS"] = str(max(1, min(4, per_rank.bit_length() - 1)))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local)
@@ -330,11 +335,12 @@ def run_ours(args):
     shm = "/dev/shm/bdpt_bench_%s.bdptimg" % os.environ.get("MASTER_PORT", "0")
 
     def upload_cold(c):
-        """From the flattened soup in host buffers.  One rank: bdpt_scene_upload (flatten + both tree builds + H2D).
-        Several ranks: rank 0 builds the scene image ONCE (the same flatten + tree builds) into shared memory and every
-        rank uploads that block -- what `bdpt --gpus N` does inside one process (host/camera.cpp); N ranks building
-        the same two trees side by side on the same host cores cost the 8-GPU e2e 12 % in round 1."""
-        if not dist:
+        """From the flattened soup in host buffers: bdpt_scene_upload on every rank (flatten + the reference-topology tree on
+        the host, the fast tree on the rank's own device, H2D).  With several ranks the host builds share the box's cores, so
+        each rank's reference build forks into cores / world subtrees (BDPT_REF_FORKS, set in main before the first upload).
+        BENCH_E2E_SHARED_IMAGE=1 gives round 2's first scheme instead: rank 0 builds ONE scene image (both trees on the host)
+        into shared memory and every rank uploads that block -- what `bdpt --gpus N` does inside one process."""
+        if not dist or not os.environ.get("BENCH_E2E_SHARED_IMAGE"):
             return c.upload(sf.verts, sf.mat_id, sf.materials, gpu_tree=args.gpu_tree)
         if rank == 0:
             with pkg.SceneImage.build(sf.verts, sf.mat_id, sf.materials) as img:
