@@ -1183,9 +1183,17 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
 // light-subpath surface vertex, seen from the pinhole, lands in whatever pixel it projects to.  All of it goes through
 // the shadow queue (the segment stops short of the far surface: SURVEY F4 is a property of the reference's estimator,
 // not of this one) and reaches the film as atomic adds.
-__device__ __forceinline__ void push_segment(const WF& w, const SQ& q, bool emit, D3 from, D3 to_dir_unit, double dist, D3 contrib, uint32_t pix) {
+template <bool EX>
+__device__ __forceinline__ void push_segment(const SceneView& sc, const WF& w, const SQ& q, bool emit, D3 from, D3 to_dir_unit, double dist, D3 contrib, uint32_t pix) {
     const double max_t = dist - 0.001 - 1e-6 * (1.0 + dist);
     emit = emit && max_t > 0.001;
+    if (EX && emit) {   // the sphere prims of the side list occlude like any prim (oracle/port.cpp: visible_mis)
+        const D3 so = from + (0.001 * to_dir_unit);
+        for (uint32_t sk = 0; sk < sc.n_spheres && emit; ++sk) {
+            double ts;
+            if (sphere_hit_t(sc.spheres[sk], so, to_dir_unit, 0.001, max_t, ts)) emit = false;
+        }
+    }
     const uint32_t slot = warp_append(q.cnt + SQ_N, emit);
     if (emit) {
         if (slot < uint32_t(w.scap)) {
@@ -1202,6 +1210,7 @@ __device__ __forceinline__ void push_segment(const WF& w, const SQ& q, bool emit
     }
 }
 
+template <bool EX>
 __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, WF w, SQ q, const uint32_t* __restrict__ done, int64_t nb,
                                                        int k0, int k1) {
     const int64_t idx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
@@ -1217,8 +1226,9 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
     if (have_cam) {
         uint32_t cprim;
         load_vertex(w.cv + size_t(b) * size_t(w.depth) + size_t(k), cp, ctf, cprim);
-        const TriShade sh = sc.shade[cprim & ~(kBackFlag | kLightFlag)];
-        cn = mk(sh.nx, sh.ny, sh.nz);
+        const uint32_t cid = cprim & ~(kBackFlag | kLightFlag);
+        if (EX && (cid & kSpherePrim)) cn = sphere_normal(sc.spheres[cid & ~kSpherePrim], cp);
+        else { const TriShade sh = sc.shade[cid]; cn = mk(sh.nx, sh.ny, sh.nz); }
         if (cprim & kBackFlag) cn = -cn;
         cm = w.cvm[size_t(b) * size_t(w.depth) + size_t(k)];
         pix = decode_sample(f, w.sample[b]).pix;
@@ -1235,10 +1245,13 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
             D3 lT;
             uint32_t lprim;
             load_vertex(w.lv + size_t(b) * size_t(w.depth) + size_t(m), lp, lT, lprim);
-            const TriShade lsh = sc.shade[lprim & ~(kBackFlag | kLightFlag)];
-            D3 ln = mk(lsh.nx, lsh.ny, lsh.nz);
+            const uint32_t lid = lprim & ~(kBackFlag | kLightFlag);
+            D3 ln;
+            uint32_t lmat;
+            if (EX && (lid & kSpherePrim)) { const SphereDev sp = sc.spheres[lid & ~kSpherePrim]; ln = sphere_normal(sp, lp); lmat = sp.mat; }
+            else { const TriShade lsh = sc.shade[lid]; ln = mk(lsh.nx, lsh.ny, lsh.nz); lmat = lsh.mat; }
             if (lprim & kBackFlag) ln = -ln;
-            const Mat lm = sc.mats[lsh.mat];
+            const Mat lm = sc.mats[lmat];
             const D3 lrgb = w.lcol ? w.lcol[size_t(b) * size_t(w.depth) + size_t(m)] : mk(lm.r, lm.g, lm.b);
             if (have_cam) {
                 const D3 dir = lp - cp;
@@ -1296,8 +1309,8 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                 }
             }
         }
-        push_segment(w, q, emit, cp, dirc, distc, contrib, pix);
-        push_segment(w, q, emit_splat, lp, dirs, dists, contrib_s, spix);
+        push_segment<EX>(sc, w, q, emit, cp, dirc, distc, contrib, pix);
+        push_segment<EX>(sc, w, q, emit_splat, lp, dirs, dists, contrib_s, spix);
     }
 }
 
@@ -1864,7 +1877,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
         tm.end(KT_TRACE, st);
         tm.begin(KT_SHADE, st);
         const unsigned gsh = grid_for(n_active + 2 * ngen + int64_t(n_def), kWide);   // the lagged rays of the front blocks are shaded too
-        if (J.mis) { if (J.tex) k_shade<true, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<true, false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
+        if (J.mis && J.media) { if (J.tex) k_shade<true, true, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<true, false, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
+        else if (J.mis) { if (J.tex) k_shade<true, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<true, false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
         else if (J.media) { if (J.tex) k_shade<false, true, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<false, false, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
         else { if (J.tex) k_shade<false, true><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); else k_shade<false, false><<<gsh, kWide, 0, st>>>(sc, f, wf, nxt, dn, J.film); }
         k_counts<<<grid_for(J.B, 256), 256, 0, st>>>(wf, dn);
@@ -1900,7 +1914,8 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
                     WK_CUDA(cudaMemsetAsync(q.cnt, 0, SQ_COUNT * sizeof(uint32_t), st));
                 }
                 tm.begin(KT_CONNECT, st);
-                if (J.mis) k_connect_mis<<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
+                if (J.mis && J.media) k_connect_mis<true><<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
+                else if (J.mis) k_connect_mis<false><<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
                 else if (J.media) k_connect<true><<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
                 else k_connect<false><<<grid_for(int64_t(k1 - k0) * n_done, kBlock), kBlock, 0, st>>>(sc, f, wf, q, wf.q_slots[dn], n_done, k0, k1);
                 tm.end(KT_CONNECT, st);
@@ -1964,7 +1979,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (o.weighting != BDPT_WEIGHT_REF_SUM && o.weighting != BDPT_WEIGHT_MIS) { ctx->err = "unknown weighting"; return BDPT_ERR_ARG; }
     const bool mis = o.weighting == BDPT_WEIGHT_MIS;
     const bool textured = ctx->view.n_tex > 0;
-    if (mis && (ctx->view.n_media > 0 || ctx->view.n_spheres > 0)) { ctx->err = "BDPT_WEIGHT_MIS does not support participating media or analytic spheres (bdpt_scene_set_media / bdpt_scene_set_spheres)"; return BDPT_ERR_ARG; }
+    if (mis && ctx->view.n_media > 0) { ctx->err = "BDPT_WEIGHT_MIS does not support participating media (bdpt_scene_set_media)"; return BDPT_ERR_ARG; }
     if (ctx->view.n_spheres > 0 && ctx->spheres_max_mat >= ctx->view.n_mats) { ctx->err = "a sphere names a material outside the scene's table"; return BDPT_ERR_ARG; }
     int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
     H = H < 1 ? 1 : H;

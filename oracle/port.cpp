@@ -490,6 +490,14 @@ struct Scene {
         for (size_t k = 0; k < spheres.size(); ++k) if (sphere_hit(spheres[k], uint32_t(k), o, d, tmin, tmax, tmp)) return true;
         return false;
     }
+    // triangles, then the sphere prims (no media: they draw random numbers) -- world.hit of the MIS estimator
+    bool hit_prims(V3 o, V3 d, double tmin, double tmax, Hit& rec) const {
+        bool found = hit(o, d, tmin, tmax, rec);
+        double best = found ? rec.t : tmax;
+        for (size_t k = 0; k < spheres.size(); ++k)
+            if (sphere_hit(spheres[k], uint32_t(k), o, d, tmin, best, rec)) { found = true; best = rec.t; }
+        return found;
+    }
     bool hit_world(V3 o, V3 d, double tmin, double tmax, Hit& rec, Rng& rng) const {
         bool found = hit(o, d, tmin, tmax, rec);
         double best = found ? rec.t : tmax;
@@ -781,6 +789,7 @@ struct Integrator {
         if (max_t <= 0.001) return false;
         Hit tmp;
         ++tl_stats.shadow;
+        if (sc.spheres_occlude(a + (0.001 * du), du, 0.001, max_t)) return false;   // the sphere prims of the side list
         return !sc.hit(a + (0.001 * du), du, 0.001, max_t, tmp);
     }
 
@@ -796,12 +805,12 @@ struct Integrator {
         int length = len0;   // surface vertices already on the subpath (light subpath: the emitter = 1)
         for (int bounce = 0; bounce < depth; ++bounce) {
             Hit rec;
-            if (!sc.hit(o, d, 0.001, kInf, rec)) {
+            if (!sc.hit_prims(o, d, 0.001, kInf, rec)) {
                 if (camera) *result = *result + T * cam.background;
                 break;
             }
             ++length;
-            const orc_material& m = sc.mats[sc.tris[rec.prim].mat];
+            const orc_material& m = sc.mats[sc.mat_of(rec.prim)];
             const double dist2 = rec.t * rec.t * len2(d);
             const double cos_in = std::fabs(dot(rec.normal, unit(-d)));
             dVCM *= dist2;

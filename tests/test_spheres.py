@@ -118,8 +118,54 @@ def test_sphere_argument_checks(bdpt):
         with pytest.raises(bdpt.BdptError, match="material"):
             ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8)
         ctx.set_spheres(spheres)
-        with pytest.raises(bdpt.BdptError, match="spheres"):
+        ctx.set_media(ts.cornell_media())
+        with pytest.raises(bdpt.BdptError, match="media"):   # spheres alone are fine under MIS (below); media are not
             ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8, weighting=bdpt.WEIGHT_MIS)
+
+
+def test_port_mis_with_analytic_spheres_agrees_with_the_reference_sum_free_estimate():
+    """BDPT_WEIGHT_MIS over triangles + sphere prims (oracle/port.cpp: walk_mis asks hit_prims, visible_mis asks spheres_occlude):
+    an unbiased estimator, so its mean must agree with the MIS render of the same room with the spheres finely tessellated
+    (the reference-pinned triangle path), and differ from the sphere-free room."""
+    from oracle.oracle import WEIGHT_MIS
+    v, m, mats, cam, spheres = room_with_sphere_materials()
+    W = H = 20
+    spp, depth = 100, 6
+    c = ocam(W, H, spp, depth, **cam)
+    ana = Oracle("port").load(v, m, mats).set_spheres(spheres).render(c, rng_mode=RNG_PHILOX, seed=5, nthreads=8, height=H, weighting=WEIGHT_MIS)
+    tv, tm = [np.asarray(v).reshape(-1, 9)], [np.asarray(m)]
+    for ctr, rad, mat in spheres:
+        tess = ts.uv_sphere(ctr, rad, 40, 80).reshape(-1, 9)
+        tv.append(tess); tm.append(np.full(len(tess), mat, np.uint32))
+    tes = Oracle("port").load(np.concatenate(tv), np.concatenate(tm), mats).render(c, rng_mode=RNG_PHILOX, seed=6, nthreads=8, height=H,
+                                                                                    weighting=WEIGHT_MIS)
+    bare = Oracle("port").load(v, m, mats).render(c, rng_mode=RNG_PHILOX, seed=5, nthreads=8, height=H, weighting=WEIGHT_MIS)
+    assert abs(ana.mean() / tes.mean() - 1.0) < 0.05
+    assert abs(bare.mean() / tes.mean() - 1.0) > 0.02 or np.mean(np.abs(ana - bare) > 1e-9) > 0.2
+    # block-wise (5 x 5 pixel) means agree too: the spheres are where they should be
+    blk = lambda f: f.reshape(H // 5, 5, W // 5, 5, 3).mean(axis=(1, 3, 4))
+    assert np.abs(blk(ana) / blk(tes) - 1.0).max() < 0.35
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bvh", [0, 1])
+def test_mis_sphere_film_equals_the_port_sample_for_sample(bvh, bdpt):
+    from oracle.oracle import WEIGHT_MIS
+    v, m, mats, cam, spheres = room_with_sphere_materials()
+    W, H, spp, depth = 40, 30, 4, 8
+    ref = Oracle("port").load(v, m, mats).set_spheres(spheres).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=13, nthreads=8,
+                                                                       height=H, weighting=WEIGHT_MIS)
+    bare = Oracle("port").load(v, m, mats).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=13, nthreads=8, height=H,
+                                                  weighting=WEIGHT_MIS)
+    assert rel_err(bare, ref) > 0.05
+    with bdpt.Context(0) as ctx:
+        ctx.upload(v, m, mats)
+        ctx.set_spheres(spheres)
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=13, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
+        assert rel_err(ctx.film(), ref) < 1e-9          # fp64 atomics: only the order of the adds differs
+        ctx.set_spheres([])
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=13, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
+        assert rel_err(ctx.film(), bare) < 1e-9
 
 
 YAML = """
