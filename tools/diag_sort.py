@@ -1,16 +1,24 @@
 """How much does ray ordering buy the traversal kernel?  Incoherent rays (uniform origins in the scene box,
-uniform directions) against the coffee_machine stand-in, traced as generated and after sorting by
-(direction octant, 30-bit Morton code of the origin)."""
+uniform directions) against the coffee_machine stand-in (or, with the argument `grid50`, config 5's 10 M-triangle sphere
+grid, whose trees do not fit the L2), traced as generated and after sorting by (direction octant, 30-bit Morton code of the origin)."""
 import importlib, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
 pkg = importlib.import_module("bidirectional-path-tracer_b200")
 bench.ensure_scenes()
-sf = pkg.SceneFile(bench.SCENE)
+if len(sys.argv) > 1 and sys.argv[1].startswith("grid"):
+    from tools import testscenes as ts
+    class _S: pass
+    sf = _S()
+    sf.verts, sf.mat_id, sf.materials, _ = ts.sphere_grid(int(sys.argv[1][4:]))
+    sf.verts = np.asarray(sf.verts)
+else:
+    sf = pkg.SceneFile(bench.SCENE)
 n = 4_000_000
 rng = np.random.default_rng(7)
 lo, hi = sf.verts.reshape(-1, 3).min(0), sf.verts.reshape(-1, 3).max(0)
+if len(sys.argv) > 1 and sys.argv[1].startswith("grid"): hi[1] = 3.0   # among the spheres, like the paths' bounce rays (the lights hang far above)
 o = (lo + (hi - lo) * rng.random((n, 3))).astype(np.float32).astype(np.float64)
 d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True); d = d.astype(np.float32).astype(np.float64)
 rays = np.concatenate([o, d, np.full((n, 1), 0.001), np.full((n, 1), np.inf)], 1)
