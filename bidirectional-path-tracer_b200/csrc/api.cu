@@ -260,6 +260,46 @@ __global__ void __launch_bounds__(kTraceBlock, 1024 / kTraceBlock) k_visible(Sce
     out[i] = vis;
 }
 
+// The sphere prims of the side list (bdpt_scene_set_spheres) after the triangle walk of a batch query, as world.hit asks them
+// (oracle/port.cpp: port_trace): in list order against the bound found so far; ANY: only rays no triangle occludes.
+template <bool ANY>
+__global__ void __launch_bounds__(256) k_trace_spheres(const SphereDev* __restrict__ spheres, uint32_t n_spheres, const bdpt_ray* __restrict__ rays,
+                                                       uint64_t n, bdpt_hit* __restrict__ out) {
+    const uint64_t i = uint64_t(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= n) return;
+    const RayD r = load_batch_ray(rays, i);
+    bdpt_hit h = out[i];
+    if (ANY && h.prim != BDPT_MISS) return;
+    double best = h.prim != BDPT_MISS ? h.t : r.tmax;
+    bool changed = false;
+    for (uint32_t k = 0; k < n_spheres; ++k) {
+        double ts;
+        if (sphere_hit_t(spheres[k], r.o, r.d, r.tmin, best, ts)) {
+            best = ts; changed = true;
+            h.t = ANY ? 0.0 : ts; h.u = 0.0; h.v = 0.0; h.prim = kSpherePrim | k;
+            if (ANY) break;
+        }
+    }
+    if (changed) out[i] = h;
+}
+// the same for bdpt_visible: a segment no triangle blocks may still meet a sphere
+__global__ void __launch_bounds__(256) k_visible_spheres(const SphereDev* __restrict__ spheres, uint32_t n_spheres, const double* __restrict__ a,
+                                                         const double* __restrict__ b, uint64_t n, uint8_t* __restrict__ out) {
+    const uint64_t i = uint64_t(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= n || out[i] == 0) return;
+    const D3 pa = mk(a[3 * i], a[3 * i + 1], a[3 * i + 2]), pb = mk(b[3 * i], b[3 * i + 1], b[3 * i + 2]);
+    const D3 dir = pb - pa;
+    const double dist = len(dir);
+    const D3 du = dir / dist;                      // out[i] == 1: dist > 0 and max_t > 0 (k_visible)
+    const double max_t = dist - 0.001;
+    const D3 so = pa + (0.001 * du);
+    for (uint32_t k = 0; k < n_spheres; ++k) {
+        double ts;
+        if (sphere_hit_t(spheres[k], so, du, 0.001, max_t, ts)) { out[i] = 0; return; }
+    }
+}
+
+
 }  // namespace
 
 // Everything the fp32 walk (traverse_w32.cuh) needs beyond the uploaded scene: the leaf-ordered triangles in fp32 and
@@ -588,6 +628,17 @@ int bdpt_bvh_leaf_order(bdpt_ctx* ctx, uint32_t* order) {
     return BDPT_OK;
 }
 
+// world.hit's second half for a batch: the sphere side list, when the context has one
+static int trace_spheres(bdpt_ctx* ctx, const bdpt_ray* d_rays, uint64_t n, bdpt_hit* d_out, bool any, cudaStream_t stream) {
+    if (ctx->n_spheres == 0) return BDPT_OK;
+    const unsigned grid = unsigned((n + 255) / 256);
+    if (any) k_trace_spheres<true><<<grid, 256, 0, stream>>>(ctx->d_spheres, ctx->n_spheres, d_rays, n, d_out);
+    else k_trace_spheres<false><<<grid, 256, 0, stream>>>(ctx->d_spheres, ctx->n_spheres, d_rays, n, d_out);
+    ctx->launches += 1;
+    BDPT_CUDA(ctx, cudaGetLastError());
+    return BDPT_OK;
+}
+
 static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t n, bdpt_hit* d_out, int flags, cudaStream_t stream) {
     const bool any = (flags & BDPT_TRACE_ANY) != 0, stats = (flags & BDPT_TRACE_STATS) != 0;
     const unsigned grid = unsigned((n + kTraceBlock - 1) / kTraceBlock);
@@ -605,7 +656,7 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
         else k_trace_split<false><<<wgrid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out);
         ctx->launches += 1;
         BDPT_CUDA(ctx, cudaGetLastError());
-        return BDPT_OK;
+        return trace_spheres(ctx, d_rays, n, d_out, any, stream);
     }
 #define BDPT_LAUNCH(B, A, S) k_trace<B, A, S><<<grid, kTraceBlock, 0, stream>>>(v, d_rays, n, d_out, st)
     static const bool walk32 = [] { const char* e = std::getenv("BDPT_WALK32"); return e ? std::atoi(e) != 0 : false; }();   // opt-in: measured slower than the per-lane walk
@@ -640,7 +691,7 @@ static int launch_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* d_rays, uint64_t
 #undef BDPT_LAUNCH
     ctx->launches += 1;
     BDPT_CUDA(ctx, cudaGetLastError());
-    return BDPT_OK;
+    return trace_spheres(ctx, d_rays, n, d_out, any, stream);
 }
 
 int bdpt_trace(bdpt_ctx* ctx, int bvh, const bdpt_ray* rays, uint64_t n, bdpt_hit* out, int flags) {
@@ -735,6 +786,10 @@ int bdpt_visible(bdpt_ctx* ctx, int bvh, const double* a, const double* b, uint6
     if (bvh == BDPT_BVH_REFERENCE) k_visible<BDPT_BVH_REFERENCE><<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->view, da, db, n, dout);
     else k_visible<BDPT_BVH_FAST><<<grid, kTraceBlock, 0, ctx->stream>>>(ctx->view, da, db, n, dout);
     ctx->launches += 1;
+    if (ctx->n_spheres) {
+        k_visible_spheres<<<unsigned((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_spheres, ctx->n_spheres, da, db, n, dout);
+        ctx->launches += 1;
+    }
     BDPT_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
     if (!dev) BDPT_CUDA(ctx, cudaMemcpyAsync(out, dout, n, cudaMemcpyDeviceToHost, ctx->stream));
     cudaError_t e = cudaStreamSynchronize(ctx->stream);

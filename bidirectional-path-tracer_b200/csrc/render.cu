@@ -392,26 +392,7 @@ __device__ __forceinline__ bool medium_hit(const TriGeom* __restrict__ med_tris,
 
 constexpr int kClsIsotropic = 4;   // material queue of the scatter points inside media (after BDPT_MAT_* 0..3)
 
-// ------------------------------------------------------------------ analytic spheres (bdpt_scene_set_spheres; oracle/port.cpp: sphere_hit)
-// The quadratic in the reference's own style: inclusive interval like triangle.h:68, nearer root first, then the farther one.
-__device__ __forceinline__ bool sphere_hit_t(const SphereDev& sp, const D3& o, const D3& d, double tmin, double tmax, double& t_out) {
-    const D3 oc = mk(sp.cx, sp.cy, sp.cz) - o;
-    const double a = len2(d);
-    const double h = dot(d, oc);
-    const double c = len2(oc) - sp.r * sp.r;
-    const double discriminant = h * h - a * c;
-    if (discriminant < 0) return false;
-    const double sqrtd = sqrt(discriminant);
-    double root = (h - sqrtd) / a;
-    if (!(tmin <= root && root <= tmax)) {
-        root = (h + sqrtd) / a;
-        if (!(tmin <= root && root <= tmax)) return false;
-    }
-    t_out = root;
-    return true;
-}
-// outward unit normal of sphere k at p: (p - c) / r
-__device__ __forceinline__ D3 sphere_normal(const SphereDev& sp, const D3& p) { return (p - mk(sp.cx, sp.cy, sp.cz)) / sp.r; }
+// analytic spheres: sphere_hit_t / sphere_normal live in scene.cuh (bdpt_trace asks the side list too)
 // material index and geometric normal of a stored vertex's prim (triangle or, in the flavours that know them, sphere)
 template <bool EX>
 __device__ __forceinline__ uint32_t prim_mat(const SceneView& sc, uint32_t prim) {

@@ -92,6 +92,28 @@ struct __align__(16) SphereDev { double cx, cy, cz, r; uint32_t mat; uint32_t pa
 static_assert(sizeof(SphereDev) == 48, "SphereDev must be 48 bytes");
 constexpr uint32_t kSpherePrim = 0x10000000u;   // hit / vertex prim of a hit on sphere k: kSpherePrim | k
 constexpr uint32_t kMediumPrim = 0x20000000u;   // hit / vertex prim of a scatter point inside medium k: kMediumPrim | k (prim IDs stay below 2^28)
+#ifdef __CUDACC__
+// sphere prims (oracle/port.cpp: sphere_hit), shared by the render kernels and the batch queries.
+// The quadratic in the reference's own style: inclusive interval like triangle.h:68, nearer root first, then the farther one.
+__device__ __forceinline__ bool sphere_hit_t(const SphereDev& sp, const D3& o, const D3& d, double tmin, double tmax, double& t_out) {
+    const D3 oc = mk(sp.cx, sp.cy, sp.cz) - o;
+    const double a = len2(d);
+    const double h = dot(d, oc);
+    const double c = len2(oc) - sp.r * sp.r;
+    const double discriminant = h * h - a * c;
+    if (discriminant < 0) return false;
+    const double sqrtd = sqrt(discriminant);
+    double root = (h - sqrtd) / a;
+    if (!(tmin <= root && root <= tmax)) {
+        root = (h + sqrtd) / a;
+        if (!(tmin <= root && root <= tmax)) return false;
+    }
+    t_out = root;
+    return true;
+}
+// outward unit normal of sphere k at p: (p - c) / r
+__device__ __forceinline__ D3 sphere_normal(const SphereDev& sp, const D3& p) { return (p - mk(sp.cx, sp.cy, sp.cz)) / sp.r; }
+#endif
 
 struct SceneView {
     const WideNode* wide_nodes;   // may be null (device-built tree): the binary walk is used

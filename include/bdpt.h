@@ -202,7 +202,8 @@ int bdpt_scene_set_media(bdpt_ctx* ctx, const bdpt_medium* media, uint32_t n_med
  * world.hit asks after the triangle walk, in list order, with the bound found so far (closest hit), and that every visible()
  * query asks for any hit.  Intersection: the quadratic in fp64, nearer root first, inclusive interval like triangle.h:68, outward
  * normal (p - c) / r face-forwarded like hittable.h:20-26.  Either weighting (under BDPT_WEIGHT_MIS together with media: refused, as
- * media are); bdpt_trace / bdpt_visible stay triangle queries.  Belongs to the context like textures and media; mat_id is checked against the uploaded scene when rendering. */
+ * media are).  bdpt_trace / bdpt_visible ask the sphere list too while one is set (world queries: a hit on sphere k reports
+ * prim = 0x10000000 | k, u = v = 0); media draw random numbers and stay out of the batch queries.  Belongs to the context like textures and media; mat_id is checked against the uploaded scene when rendering. */
 typedef struct { double center[3]; double radius; uint32_t mat_id; uint32_t pad; } bdpt_sphere;
 int bdpt_scene_set_spheres(bdpt_ctx* ctx, const bdpt_sphere* spheres, uint32_t n_spheres);
 int bdpt_bvh_info(bdpt_ctx* ctx, int bvh, uint64_t* n_nodes, uint32_t* max_depth);

@@ -713,6 +713,7 @@ struct Integrator {
         if (max_t <= 0) return false;
         Hit tmp;
         ++tl_stats.shadow;
+        if (sc.spheres_occlude(a + (0.001 * du), du, 0.001, max_t)) return false;   // the sphere prims of the side list (none: a no-op)
         return !sc.hit(a + (0.001 * du), du, 0.001, max_t, tmp);
     }
     // the same with media in the world: a medium between the two points scatters the shadow ray with the probability

@@ -168,6 +168,40 @@ def test_mis_sphere_film_equals_the_port_sample_for_sample(bvh, bdpt):
         assert rel_err(ctx.film(), bare) < 1e-9
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("bvh", [0, 1])
+def test_batch_queries_ask_the_sphere_side_list(bvh, bdpt):
+    """bdpt_trace / bdpt_visible with spheres set are world queries (hittable::hit on the world list, hittable.h:33): triangles,
+    then the sphere prims in list order against the bound so far -- port_trace / port_visible do the same.  Bit for bit."""
+    v, m, mats, cam, spheres = room_with_sphere_materials()
+    port = Oracle("port").load(v, m, mats).set_spheres(spheres)
+    rays = ts.ray_batch(v, 60000, seed=21, cam=cam, width=64, height=64)
+    rng = np.random.default_rng(4)
+    rays[::7, 7] = rng.uniform(50.0, 700.0, size=len(rays[::7]))      # some finite tmax: spheres beyond it must not answer
+    p_prim, p_t, p_u, p_v = port.trace(rays, nthreads=8)
+    on_sphere = (p_prim & 0xF0000000) == 0x10000000
+    assert on_sphere.sum() > 3000 and (p_prim == 0xFFFFFFFF).sum() > 100 and (~on_sphere & (p_prim != 0xFFFFFFFF)).sum() > 3000
+    a = rng.uniform(20.0, 530.0, size=(40000, 3)); b = rng.uniform(20.0, 530.0, size=(40000, 3))
+    p_vis = port.visible(a, b, nthreads=8)
+    with bdpt.Context(0) as ctx:
+        ctx.upload(v, m, mats)
+        bare = ctx.trace(rays, bvh=bvh)
+        bare_vis = ctx.visible(a, b, bvh=bvh)
+        ctx.set_spheres(spheres)
+        hit = ctx.trace(rays, bvh=bvh)
+        assert np.array_equal(hit["prim"], p_prim)
+        assert np.array_equal(hit["t"], p_t) and np.array_equal(hit["u"], p_u) and np.array_equal(hit["v"], p_v)
+        anyh = ctx.trace(rays, bvh=bvh, any_hit=True)
+        assert np.array_equal(anyh["prim"] == 0xFFFFFFFF, p_prim == 0xFFFFFFFF)
+        only_sphere = (bare["prim"] == 0xFFFFFFFF) & (p_prim != 0xFFFFFFFF)
+        assert only_sphere.sum() > 20 and np.all((anyh["prim"][only_sphere] & 0xF0000000) == 0x10000000)
+        vis = ctx.visible(a, b, bvh=bvh)
+        assert np.array_equal(vis, p_vis)
+        assert (bare_vis & ~vis).sum() > 500 and not (vis & ~bare_vis).any()     # spheres only ever block
+        ctx.set_spheres([])
+        assert np.array_equal(ctx.trace(rays, bvh=bvh)["prim"], bare["prim"])
+
+
 YAML = """
 camera:
   resolution: [32, 24]
