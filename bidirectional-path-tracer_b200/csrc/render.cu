@@ -390,6 +390,33 @@ __device__ __forceinline__ bool medium_hit(const TriGeom* __restrict__ med_tris,
     return true;
 }
 
+// The part of [tmin, tmax] the ray spends inside medium m as constant_medium::hit measures it (medium_hit without the draw);
+// oracle/port.cpp: medium_overlap.
+__device__ __forceinline__ double medium_overlap(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double tmin,
+                                                 double tmax) {
+    if (!line_meets_bounds(m, o, d)) return 0.0;
+    const double inf = __longlong_as_double(0x7FF0000000000000LL);
+    double t1, t2;
+    if (!boundary_hit(med_tris, m, o, d, -inf, inf, t1)) return 0.0;
+    if (!boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2)) return 0.0;
+    if (t1 < tmin) t1 = tmin;
+    if (t2 > tmax) t2 = tmax;
+    if (t1 >= t2) return 0.0;
+    if (t1 < 0) t1 = 0;
+    return (t2 - t1) * len(d);
+}
+// Transmittance of all media along o + t d, t in [tmin, tmax] (oracle/port.cpp: transmittance): what BDPT_WEIGHT_MIS weighs with.
+// Rare and heavy (a loop over every boundary triangle): kept out of line.
+__device__ __noinline__ double media_transmittance(const MediumDev* __restrict__ media, const TriGeom* __restrict__ med_tris, uint32_t n_media,
+                                                   D3 o, D3 d, double tmin, double tmax) {
+    double tau = 0.0;
+    for (uint32_t k = 0; k < n_media; ++k) {
+        const MediumDev md = media[k];
+        tau += medium_overlap(med_tris, md, o, d, tmin, tmax) / -md.neg_inv_density;
+    }
+    return tau > 0.0 ? exp(-tau) : 1.0;
+}
+
 constexpr int kClsIsotropic = 4;   // material queue of the scatter points inside media (after BDPT_MAT_* 0..3)
 
 // analytic spheres: sphere_hit_t / sphere_normal live in scene.cuh (bdpt_trace asks the side list too)
@@ -777,11 +804,14 @@ struct HitUV {
 // BDPT_WEIGHT_MIS: the subpath's running weight quantities as they stand ON this vertex (the hit just found):
 // the segment's area conversion and the arrival cosine go in
 struct MisAtHit { double dVCM, dVC, cos_in; uint32_t len; };
-__device__ __forceinline__ MisAtHit mis_arrive(const Frame& f, const WF& w, uint32_t pid, const Surf& s) {
+template <bool EX = false>
+__device__ __forceinline__ MisAtHit mis_arrive(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, const Surf& s) {
     MisAtHit m;
     const PathMis pm = w.pmis[pid];
     m.cos_in = fabs(dot(s.n, unit(-s.d)));
-    const double dist2 = s.t * s.t * len2(s.d);
+    double dist2 = s.t * s.t * len2(s.d);
+    // media: the pdf of getting this far holds the segment's transmittance -- 1/dist^2 becomes Tr/dist^2 (port: walk_mis)
+    if (EX && sc.n_media) dist2 = dist2 / media_transmittance(sc.media, sc.med_tris, sc.n_media, s.o, s.d, 0.001, s.t);
     m.dVCM = pm.dVCM * dist2 / m.cos_in;
     m.dVC = pm.dVC / m.cos_in;
     m.len = uint32_t(f.depth - s.remaining + 1);   // camera: remaining starts at depth; light: at depth - 1 behind the emitter
@@ -808,7 +838,7 @@ __device__ __forceinline__ bool shade_light(const SceneView& sc, const Frame& f,
             if (is_cam) {
                 double wgt = 1.0;
                 if (MIS) {   // s = 0: weighed against every way the light subpath could have produced this path
-                    const MisAtHit h = mis_arrive(f, w, pid, s);
+                    const MisAtHit h = mis_arrive<EX>(sc, f, w, pid, s);
                     if (h.len > 1) {
                         const double pdfA = 1.0 / sc.light_total_area;
                         wgt = 1.0 / (1.0 + pdfA * h.dVCM + (pdfA * h.cos_in / kPi) * h.dVC);
@@ -833,7 +863,7 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
     {
         const Surf s = load_surf<EX>(sc, w, pid);
         MisAtHit mh{0.0, 0.0, 0.0, 0u};
-        if (MIS) mh = mis_arrive(f, w, pid, s);
+        if (MIS) mh = mis_arrive<EX>(sc, f, w, pid, s);
         const uint32_t side = (MIS && !s.front) ? kBackFlag : 0u;
         const Mat m = sc.mats[prim_mat<EX>(sc, s.prim)];
         const D3 albedo = TEX ? mat_colour(sc, m, s.p, HitUV{sc, s}) : mk(m.r, m.g, m.b);   // tex->value(rec.u, rec.v, rec.p), material.h:47,61
@@ -887,7 +917,9 @@ __device__ __forceinline__ bool shade_lambert(const SceneView& sc, const Frame& 
 // constant_medium (constant_medium.h:14,54).  The vertex is a point INSIDE the medium: no triangle, the reference's arbitrary normal
 // (1,0,0) and front_face = true (constant_medium.h:52-53).  Not delta: evaluate_bsdf = albedo / (4 pi) (material.h:166-168), so the
 // vertex is stored and connected; scatter: attenuation = albedo, sphere_pdf (pdf.h:18-29): direction = random_unit_vector(), pdf =
-// scattering_pdf = 1 / (4 pi) (material.h:154-164; camera.h:361-368).  BDPT_WEIGHT_REF_SUM only.
+// scattering_pdf = 1 / (4 pi) (material.h:154-164; camera.h:361-368).  BDPT_WEIGHT_MIS: a connectable vertex without a cosine, 1 / (4 pi) in
+// both directions (oracle/port.cpp: walk_mis).
+template <bool MIS>
 __device__ __forceinline__ bool shade_isotropic(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid) {
     const double2* q = reinterpret_cast<const double2*>(w.path + pid);
     const double2 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3], q4 = q[4];
@@ -902,15 +934,25 @@ __device__ __forceinline__ bool shade_isotropic(const SceneView& sc, const Frame
     const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
     const uint32_t index = uint32_t(f.depth - remaining_in);
     const D3 fr = albedo / (4 * kPi);
+    VertMis vm{0.0, 0.0, 1.0, 0u, 0u};
+    if (MIS) {   // the running weight quantities as they stand on this vertex: no arrival cosine, the segment's transmittance
+        const PathMis pm = w.pmis[pid];
+        const double dist2 = q4.y * q4.y * len2(d);
+        vm.dVCM = pm.dVCM * (dist2 / media_transmittance(sc.media, sc.med_tris, sc.n_media, o, d, 0.001, q4.y));
+        vm.dVC = pm.dVC;
+        vm.len = uint32_t(f.depth - remaining_in + 1);
+    }
     if (len2(fr) > 0) {
         if (is_cam) {
             const uint32_t slot = w.ncam[b];
             store_vertex(w.cv + size_t(b) * size_t(w.depth) + slot, p, T * fr, prim, index);
+            if (MIS) w.cvm[size_t(b) * size_t(w.depth) + slot] = vm;
             w.ncam[b] = slot + 1;
         } else {
             const uint32_t slot = w.nlight[b];
             store_vertex(w.lv + size_t(b) * size_t(w.depth) + slot, p, T, prim, index);
             if (w.lcol) w.lcol[size_t(b) * size_t(w.depth) + slot] = albedo;
+            if (MIS) w.lvm[size_t(b) * size_t(w.depth) + slot] = vm;
             w.nlight[b] = slot + 1;
         }
     }
@@ -923,6 +965,12 @@ __device__ __forceinline__ bool shade_isotropic(const SceneView& sc, const Frame
     const double spdf = 1 / (4 * kPi);
     const D3 T2 = T * albedo * spdf / pdf_value;   // camera.h:366
     store_ray(w, pid, p, sd, T2, rng.draws, remaining);
+    if (MIS) {
+        PathMis pm;
+        pm.dVC = (1.0 / pdf_value) * (vm.dVC * spdf + vm.dVCM);
+        pm.dVCM = 1.0 / pdf_value;
+        w.pmis[pid] = pm;
+    }
     return true;
 }
 
@@ -946,7 +994,7 @@ __device__ __forceinline__ bool shade_metal(const SceneView& sc, const Frame& f,
             const D3 T = s.T * mk(m.r, m.g, m.b);                              // camera.h:355
             store_ray(w, pid, s.p, refl, T, rng.draws, remaining);
             if (MIS) {   // a delta vertex (material.h:85): nothing connects to it
-                const MisAtHit mh = mis_arrive(f, w, pid, s);
+                const MisAtHit mh = mis_arrive<EX>(sc, f, w, pid, s);
                 PathMis pm;
                 pm.dVCM = 0.0; pm.dVC = mh.dVC * fabs(dot(s.n, unit(refl)));
                 w.pmis[pid] = pm;
@@ -985,7 +1033,7 @@ __device__ __forceinline__ bool shade_dielectric(const SceneView& sc, const Fram
             const D3 T = s.T * mk(1.0, 1.0, 1.0);
             store_ray(w, pid, s.p, dir, T, rng.draws, remaining);
             if (MIS) {
-                const MisAtHit mh = mis_arrive(f, w, pid, s);
+                const MisAtHit mh = mis_arrive<EX>(sc, f, w, pid, s);
                 PathMis pm;
                 pm.dVCM = 0.0; pm.dVC = mh.dVC * fabs(dot(s.n, unit(dir)));
                 w.pmis[pid] = pm;
@@ -1017,7 +1065,7 @@ __global__ void __launch_bounds__(kWide, BDPT_SHADE_BLOCKS) k_shade(SceneView sc
         else if (idx < n_li + n_la) { pid = w.q_mat[BDPT_MAT_LAMBERTIAN][idx - n_li]; live = shade_lambert<MIS, TEX, MEDIA>(sc, f, w, pid); }
         else if (idx < n_li + n_la + n_me) { pid = w.q_mat[BDPT_MAT_METAL][idx - n_li - n_la]; live = shade_metal<MIS, MEDIA>(sc, f, w, pid); }
         else if (idx < n_li + n_la + n_me + n_di) { pid = w.q_mat[BDPT_MAT_DIELECTRIC][idx - n_li - n_la - n_me]; live = shade_dielectric<MIS, MEDIA>(sc, f, w, pid); }
-        else if (MEDIA) { pid = w.q_mat[kClsIsotropic][idx - n_li - n_la - n_me - n_di]; live = shade_isotropic(sc, f, w, pid); }
+        else if (MEDIA) { pid = w.q_mat[kClsIsotropic][idx - n_li - n_la - n_me - n_di]; live = shade_isotropic<MIS>(sc, f, w, pid); }
     }
     const uint32_t slot = block_append<kWide>(w.counters + C_ACTIVE0 + nxt, live);
     if (live) w.q_active[nxt][slot] = pid;
@@ -1191,6 +1239,12 @@ __device__ __forceinline__ void push_segment(const SceneView& sc, const WF& w, c
     }
 }
 
+// transmittance of the media along the segment push_segment queues (oracle/port.cpp: tr_mis)
+__device__ __forceinline__ double segment_transmittance(const SceneView& sc, D3 from, D3 to_dir_unit, double dist) {
+    const double max_t = dist - 0.001 - 1e-6 * (1.0 + dist);
+    return media_transmittance(sc.media, sc.med_tris, sc.n_media, from + (0.001 * to_dir_unit), to_dir_unit, 0.001, max_t);
+}
+
 template <bool EX>
 __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, WF w, SQ q, const uint32_t* __restrict__ done, int64_t nb,
                                                        int k0, int k1) {
@@ -1204,11 +1258,14 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
     D3 cp = mk(0, 0, 0), ctf = mk(0, 0, 0), cn = mk(0, 0, 0);
     VertMis cm{0.0, 0.0, 0.0, 0u, 0u};
     uint32_t pix = 0;
+    bool c_med = false;
     if (have_cam) {
         uint32_t cprim;
         load_vertex(w.cv + size_t(b) * size_t(w.depth) + size_t(k), cp, ctf, cprim);
         const uint32_t cid = cprim & ~(kBackFlag | kLightFlag);
-        if (EX && (cid & kSpherePrim)) cn = sphere_normal(sc.spheres[cid & ~kSpherePrim], cp);
+        c_med = EX && (cid & kMediumPrim) != 0;   // a scatter point inside a medium: no cosine, 1 / (4 pi) both ways
+        if (c_med) cn = mk(1.0, 0.0, 0.0);
+        else if (EX && (cid & kSpherePrim)) cn = sphere_normal(sc.spheres[cid & ~kSpherePrim], cp);
         else { const TriShade sh = sc.shade[cid]; cn = mk(sh.nx, sh.ny, sh.nz); }
         if (cprim & kBackFlag) cn = -cn;
         cm = w.cvm[size_t(b) * size_t(w.depth) + size_t(k)];
@@ -1227,41 +1284,51 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
             uint32_t lprim;
             load_vertex(w.lv + size_t(b) * size_t(w.depth) + size_t(m), lp, lT, lprim);
             const uint32_t lid = lprim & ~(kBackFlag | kLightFlag);
-            D3 ln;
-            uint32_t lmat;
-            if (EX && (lid & kSpherePrim)) { const SphereDev sp = sc.spheres[lid & ~kSpherePrim]; ln = sphere_normal(sp, lp); lmat = sp.mat; }
+            const bool l_med = EX && (lid & kMediumPrim) != 0;
+            D3 ln = mk(1.0, 0.0, 0.0);
+            uint32_t lmat = 0;
+            if (l_med) {}
+            else if (EX && (lid & kSpherePrim)) { const SphereDev sp = sc.spheres[lid & ~kSpherePrim]; ln = sphere_normal(sp, lp); lmat = sp.mat; }
             else { const TriShade lsh = sc.shade[lid]; ln = mk(lsh.nx, lsh.ny, lsh.nz); lmat = lsh.mat; }
             if (lprim & kBackFlag) ln = -ln;
-            const Mat lm = sc.mats[lmat];
-            const D3 lrgb = w.lcol ? w.lcol[size_t(b) * size_t(w.depth) + size_t(m)] : mk(lm.r, lm.g, lm.b);
+            D3 lrgb;
+            if (w.lcol) lrgb = w.lcol[size_t(b) * size_t(w.depth) + size_t(m)];
+            else if (l_med) { const MediumDev md = sc.media[lid & ~kMediumPrim]; lrgb = mk(md.r, md.g, md.b); }
+            else { const Mat lm = sc.mats[lmat]; lrgb = mk(lm.r, lm.g, lm.b); }
+            const D3 lf = l_med ? lrgb / (4 * kPi) : lrgb / kPi;                       // BSDF value of the light vertex
+            const bool media = EX && sc.n_media != 0;
             if (have_cam) {
                 const D3 dir = lp - cp;
                 const double dist2 = len2(dir);
                 if (dist2 > 0) {
                     const D3 du = unit(dir);
-                    const double cosCamera = dot(cn, du), cosLight = dot(ln, -du);
+                    const double cosCamera = c_med ? 1.0 : dot(cn, du), cosLight = l_med ? 1.0 : dot(ln, -du);
                     if (cosCamera > 0 && cosLight > 0) {
+                        dirc = du; distc = len(dir);
+                        const double tr = media ? segment_transmittance(sc, cp, dirc, distc) : 1.0;
+                        const double c_dir = c_med ? 1 / (4 * kPi) : cosCamera / kPi;       // pdf of the camera vertex scattering this way
+                        const double c_rev = c_med ? 1 / (4 * kPi) : cm.cos_in / kPi;       // ... and back towards its predecessor
                         if (lprim & kLightFlag) {   // s = 1: the emitter point (ctf = T * f of the camera vertex)
                             if (cm.len + 1u <= uint32_t(f.depth)) {
                                 const double directPdfW = pdfA * dist2 / cosLight, emissionPdfW = pdfA * cosLight / kPi;
-                                const double wLight = (cosCamera / kPi) / directPdfW;
-                                const double wCamera = (emissionPdfW * cosCamera / (directPdfW * cosLight)) * (cm.dVCM + cm.dVC * (cm.cos_in / kPi));
+                                const double wLight = (c_dir * tr) / directPdfW;
+                                const double wCamera = (emissionPdfW * cosCamera * tr / (directPdfW * cosLight)) * (cm.dVCM + cm.dVC * c_rev);
                                 const double wgt = 1.0 / (wLight + 1.0 + wCamera);
-                                contrib = (wgt * cosCamera / directPdfW) * (ctf * lrgb);
+                                contrib = (wgt * cosCamera * tr / directPdfW) * (ctf * lrgb);
                                 emit = true;
                             }
                         } else {
                             const VertMis vm = w.lvm[size_t(b) * size_t(w.depth) + size_t(m)];
                             if (cm.len + vm.len <= uint32_t(f.depth)) {
-                                const double camDirPdfA = (cosCamera / kPi) * cosLight / dist2, lightDirPdfA = (cosLight / kPi) * cosCamera / dist2;
-                                const double wLight = camDirPdfA * (vm.dVCM + vm.dVC * (vm.cos_in / kPi));
-                                const double wCamera = lightDirPdfA * (cm.dVCM + cm.dVC * (cm.cos_in / kPi));
+                                const double l_dir = l_med ? 1 / (4 * kPi) : cosLight / kPi, l_rev = l_med ? 1 / (4 * kPi) : vm.cos_in / kPi;
+                                const double camDirPdfA = c_dir * cosLight * tr / dist2, lightDirPdfA = l_dir * cosCamera * tr / dist2;
+                                const double wLight = camDirPdfA * (vm.dVCM + vm.dVC * l_rev);
+                                const double wCamera = lightDirPdfA * (cm.dVCM + cm.dVC * c_rev);
                                 const double wgt = 1.0 / (wLight + 1.0 + wCamera);
-                                contrib = (wgt * cosLight * cosCamera / dist2) * (ctf * lT * (lrgb / kPi));
+                                contrib = (wgt * cosLight * cosCamera * tr / dist2) * (ctf * lT * lf);
                                 emit = true;
                             }
                         }
-                        dirc = du; distc = len(dir);
                     }
                 }
             }
@@ -1270,7 +1337,7 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                 const double dist2 = len2(dir);
                 if (dist2 > 0) {
                     const D3 du = unit(dir);
-                    const double cosToCamera = dot(ln, du), cosAtCamera = dot(f.fwd, -du);
+                    const double cosToCamera = l_med ? 1.0 : dot(ln, du), cosAtCamera = dot(f.fwd, -du);
                     if (cosToCamera > 0 && cosAtCamera > 0) {
                         const D3 P = f.center + (f.focus / cosAtCamera) * (-du);
                         const D3 rel = P - f.ul;
@@ -1278,12 +1345,13 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                         if (xc >= 0 && yc >= 0 && xc < f.W && yc < f.H) {
                             const VertMis vm = w.lvm[size_t(b) * size_t(w.depth) + size_t(m)];
                             const double ipcd = f.plane_px / cosAtCamera;
-                            const double imageToSurface = (ipcd * ipcd / cosAtCamera) * cosToCamera / dist2;
-                            const double wLight = (imageToSurface / f.n_light) * (vm.dVCM + vm.dVC * (vm.cos_in / kPi));
-                            const double wgt = 1.0 / (wLight + 1.0);
-                            contrib_s = (wgt * imageToSurface / f.n_light) * (lT * (lrgb / kPi));
-                            spix = uint32_t(int(yc)) * uint32_t(f.W) + uint32_t(int(xc));
                             dirs = du; dists = len(dir);
+                            const double tr = media ? segment_transmittance(sc, lp, dirs, dists) : 1.0;
+                            const double imageToSurface = (ipcd * ipcd / cosAtCamera) * cosToCamera * tr / dist2;
+                            const double wLight = (imageToSurface / f.n_light) * (vm.dVCM + vm.dVC * (l_med ? 1 / (4 * kPi) : vm.cos_in / kPi));
+                            const double wgt = 1.0 / (wLight + 1.0);
+                            contrib_s = (wgt * imageToSurface / f.n_light) * (lT * lf);
+                            spix = uint32_t(int(yc)) * uint32_t(f.W) + uint32_t(int(xc));
                             emit_splat = true;
                         }
                     }
@@ -1960,7 +2028,6 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (o.weighting != BDPT_WEIGHT_REF_SUM && o.weighting != BDPT_WEIGHT_MIS) { ctx->err = "unknown weighting"; return BDPT_ERR_ARG; }
     const bool mis = o.weighting == BDPT_WEIGHT_MIS;
     const bool textured = ctx->view.n_tex > 0;
-    if (mis && ctx->view.n_media > 0) { ctx->err = "BDPT_WEIGHT_MIS does not support participating media (bdpt_scene_set_media)"; return BDPT_ERR_ARG; }
     if (ctx->view.n_spheres > 0 && ctx->spheres_max_mat >= ctx->view.n_mats) { ctx->err = "a sphere names a material outside the scene's table"; return BDPT_ERR_ARG; }
     int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
     H = H < 1 ? 1 : H;

@@ -217,6 +217,7 @@ void camera::render(const hittable& world, const hittable& lights) {
             bdpt_render_opts o{};
             o.seed = options.seed; o.stratum_begin = g; o.stratum_step = G; o.bvh = options.bvh;
             o.flags = options.stats ? BDPT_RENDER_STATS : 0;
+            o.weighting = options.weighting;
             check(bdpt_render(ctx, &c, &o), ctx, "bdpt_render");
             bdpt_stats(ctx, &stats[g]);
             bdpt_last_device_ms(ctx, &ms[g]);

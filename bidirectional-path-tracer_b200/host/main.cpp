@@ -7,7 +7,7 @@
 
 int main(int argc, char** argv) {
     if (argc < 2) {
-        std::cerr << "usage: bdpt scene.yaml [--res WxH] [--spp N] [--depth N] [--gpus N] [--bvh ref|fast] [--seed S] [--out name.png] [--cache file.bdptimg] [--stats] [--quiet]\n";
+        std::cerr << "usage: bdpt scene.yaml [--res WxH] [--spp N] [--depth N] [--gpus N] [--bvh ref|fast] [--mis] [--seed S] [--out name.png] [--cache file.bdptimg] [--stats] [--quiet]\n";
         return 2;
     }
     // --cache FILE: keep the scene image (flattened soup + both BVHs) beside the scene; a later run whose YAML and
@@ -45,6 +45,7 @@ int main(int argc, char** argv) {
             else if (!std::strcmp(argv[i], "--cache")) next("--cache");
             else if (!std::strcmp(argv[i], "--stats")) scene.cam.options.stats = true;     // count the reference's BvhStats (slower)
             else if (!std::strcmp(argv[i], "--quiet")) scene.cam.options.quiet = true;
+            else if (!std::strcmp(argv[i], "--mis")) scene.cam.options.weighting = BDPT_WEIGHT_MIS;   // the unbiased estimator; default: the reference's sum
             else if (!std::strcmp(argv[i], "--bvh")) scene.cam.options.bvh = std::strcmp(next("--bvh"), "ref") ? BDPT_BVH_FAST : BDPT_BVH_REFERENCE;
             else throw std::runtime_error(std::string("unknown flag ") + argv[i]);
         }

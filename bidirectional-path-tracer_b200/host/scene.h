@@ -206,6 +206,7 @@ class bvh_node : public hittable {
 struct render_options {         // overrides the CLI adds on top of the YAML
     int gpus = 1;               // strata are sharded over this many devices
     int bvh = BDPT_BVH_FAST;    // both give the reference's hits; REFERENCE also walks its topology
+    int weighting = BDPT_WEIGHT_REF_SUM;   // REF_SUM: the reference's estimator (camera.h:294-323); BDPT_WEIGHT_MIS: balance-heuristic weights + light-tracing splats
     uint64_t seed = 0;
     bool quiet = false;
     bool stats = false;         // count the reference's BvhStats (stats.h:8-16) during the render (BDPT_RENDER_STATS: slower)

@@ -184,8 +184,9 @@ int bdpt_scene_set_textures(bdpt_ctx* ctx, const bdpt_texture* tex, uint32_t n_t
  * every medium is asked with the interval [tmin, nearest hit so far] (constant_medium.h:22-58: two boundary hits, clamp,
  * ONE random draw, scatter distance -1/density * log(xi)); a scatter point is a path vertex with the isotropic material
  * (uniform sphere scatter, f = albedo / 4 pi, the reference's arbitrary normal (1,0,0)); visible() lets a medium
- * between two vertices scatter the shadow ray with the same probability.  BDPT_WEIGHT_REF_SUM only (BDPT_WEIGHT_MIS with
- * media is refused); bdpt_trace / bdpt_visible stay triangle queries.  Limits: 16 media, 4096 boundary triangles each.
+ * between two vertices scatter the shadow ray with the same probability.  BDPT_WEIGHT_MIS: a scatter point is a
+ * connectable vertex (no cosine, 1 / (4 pi) both ways) and every pdf and contribution holds the analytic transmittance of its
+ * segment.  bdpt_trace / bdpt_visible stay deterministic queries (media draw random numbers).  Limits: 16 media, 4096 boundary triangles each.
  * Belongs to the context like the texture table: before or after the scene upload, again to replace, n_media = 0 to drop. */
 typedef struct {
     double   density;        /* > 0 */
@@ -201,8 +202,7 @@ int bdpt_scene_set_media(bdpt_ctx* ctx, const bdpt_medium* media, uint32_t n_med
  * triangles: lights are sampled by area over triangles, triangle.h:199-224), kept in a side list of at most 256 that every
  * world.hit asks after the triangle walk, in list order, with the bound found so far (closest hit), and that every visible()
  * query asks for any hit.  Intersection: the quadratic in fp64, nearer root first, inclusive interval like triangle.h:68, outward
- * normal (p - c) / r face-forwarded like hittable.h:20-26.  Either weighting (under BDPT_WEIGHT_MIS together with media: refused, as
- * media are).  bdpt_trace / bdpt_visible ask the sphere list too while one is set (world queries: a hit on sphere k reports
+ * normal (p - c) / r face-forwarded like hittable.h:20-26.  Either weighting.  bdpt_trace / bdpt_visible ask the sphere list too while one is set (world queries: a hit on sphere k reports
  * prim = 0x10000000 | k, u = v = 0); media draw random numbers and stay out of the batch queries.  Belongs to the context like textures and media; mat_id is checked against the uploaded scene when rendering. */
 typedef struct { double center[3]; double radius; uint32_t mat_id; uint32_t pad; } bdpt_sphere;
 int bdpt_scene_set_spheres(bdpt_ctx* ctx, const bdpt_sphere* spheres, uint32_t n_spheres);

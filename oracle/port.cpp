@@ -477,6 +477,25 @@ struct Scene {
         t_out = t1 + hit_distance / ray_length;
         return true;
     }
+    // The part of [tmin, tmax] a ray spends inside medium m, as constant_medium::hit measures it (the same two boundary
+    // hits and clamps as medium_hit above, without the draw): exp(-density * this) is the probability that medium_hit
+    // does NOT scatter the ray before tmax -- the transmittance the MIS estimator weighs with.
+    static double medium_overlap(const Medium& m, V3 o, V3 d, double tmin, double tmax) {
+        double t1, t2;
+        if (!boundary_hit(m, o, d, -kInf, kInf, t1)) return 0.0;
+        if (!boundary_hit(m, o, d, t1 + 0.0001, kInf, t2)) return 0.0;
+        if (t1 < tmin) t1 = tmin;
+        if (t2 > tmax) t2 = tmax;
+        if (t1 >= t2) return 0.0;
+        if (t1 < 0) t1 = 0;
+        return (t2 - t1) * len(d);
+    }
+    // transmittance of all media along o + t d, t in [tmin, tmax]
+    double transmittance(V3 o, V3 d, double tmin, double tmax) const {
+        double tau = 0.0;
+        for (const Medium& m : media) tau += medium_overlap(m, o, d, tmin, tmax) / -m.neg_inv_density;
+        return tau > 0.0 ? std::exp(-tau) : 1.0;
+    }
     // world.hit with media in the world list.  The reference reaches a medium whenever its BVH walk gets to it, with the
     // bound found so far; here the triangles go first and every medium then sees [tmin, best]: one draw per medium either
     // way, and the same event decides (scatter before the nearer of exit and best), so the outcome has the same
@@ -779,7 +798,22 @@ struct Integrator {
         V3 p, n, T, albedo;        // position, normal facing the arriving path, throughput up to here
         double dVCM, dVC, cos_in;
         int len;                   // surface vertices of the subpath up to and including this one
+        bool medium = false;       // a scatter point inside a medium: isotropic phase function, no cosine
+        // pdf per solid angle of scattering back towards the previous vertex, the BSDF value, and the cosine of a direction
+        double rev_pdf() const { return medium ? 1 / (4 * kPi) : cos_in / kPi; }
+        V3 f() const { return medium ? albedo / (4 * kPi) : albedo / kPi; }
+        double cosine(V3 du) const { return medium ? 1.0 : dot(n, du); }
+        double dir_pdf(double c) const { return medium ? 1 / (4 * kPi) : c / kPi; }
     };
+    // transmittance of the media along the segment visible_mis tests (1 without media)
+    double tr_mis(V3 a, V3 b) const {
+        if (sc.media.empty()) return 1.0;
+        V3 dir = b - a;
+        double dist = len(dir);
+        V3 du = dir / dist;
+        double max_t = dist - 0.001 - 1e-6 * (1.0 + dist);
+        return sc.transmittance(a + (0.001 * du), du, 0.001, max_t);
+    }
 
     bool visible_mis(V3 a, V3 b) const {
         V3 dir = b - a;
@@ -806,15 +840,33 @@ struct Integrator {
         int length = len0;   // surface vertices already on the subpath (light subpath: the emitter = 1)
         for (int bounce = 0; bounce < depth; ++bounce) {
             Hit rec;
-            if (!sc.hit_prims(o, d, 0.001, kInf, rec)) {
+            if (!(sc.media.empty() ? sc.hit_prims(o, d, 0.001, kInf, rec) : sc.hit_world(o, d, 0.001, kInf, rec, rng))) {
                 if (camera) *result = *result + T * cam.background;
                 break;
             }
             ++length;
-            const orc_material& m = sc.mats[sc.mat_of(rec.prim)];
             const double dist2 = rec.t * rec.t * len2(d);
+            // media: the pdf of getting this far holds the transmittance of the segment (and, for a scatter point, the density,
+            // which every strategy that makes this vertex shares): the segment's 1/dist^2 becomes Tr/dist^2 in every pdf
+            const double tr = sc.media.empty() ? 1.0 : sc.transmittance(o, d, 0.001, rec.t);
+            if (rec.prim & kMediumPrim) {   // isotropic scatter point: connectable, no cosine, 1/(4 pi) both ways
+                const Medium& md = sc.media[rec.prim & ~kMediumPrim];
+                dVCM *= dist2 / tr;
+                MisVertex v;
+                v.p = rec.p; v.n = rec.normal; v.T = T; v.albedo = md.albedo; v.dVCM = dVCM; v.dVC = dVC; v.cos_in = 1.0; v.len = length;
+                v.medium = true;
+                verts.push_back(v);
+                V3 sd = random_unit_vector(rng);
+                const double dirPdfW = 1 / (4 * kPi), revPdfW = 1 / (4 * kPi);
+                T = T * md.albedo * revPdfW / dirPdfW;   // attenuation * scattering_pdf / pdf, as trace_path writes it
+                dVC = (1.0 / dirPdfW) * (dVC * revPdfW + dVCM);
+                dVCM = 1.0 / dirPdfW;
+                o = rec.p; d = sd;
+                continue;
+            }
+            const orc_material& m = sc.mats[sc.mat_of(rec.prim)];
             const double cos_in = std::fabs(dot(rec.normal, unit(-d)));
-            dVCM *= dist2;
+            dVCM *= sc.media.empty() ? dist2 : dist2 / tr;
             dVCM /= cos_in; dVC /= cos_in;
             if (m.type == ORC_MAT_LIGHT) {           // absorbs; a camera path that arrives on the emitting side sees it
                 if (camera && rec.front) {
@@ -910,20 +962,21 @@ struct Integrator {
             }
         }
         for (const MisVertex& c : cp) {
-            const V3 fc = c.albedo / kPi;
+            const V3 fc = c.f();
             // s = 1: the emitter point itself
             if (c.len + 1 <= depth) {
                 V3 dir = y0 - c.p;
                 double dist2 = len2(dir);
                 if (dist2 > 0) {
                     V3 du = unit(dir);
-                    const double cosToLight = dot(c.n, du), cosAtLight = dot(n0, -du);
+                    const double cosToLight = c.cosine(du), cosAtLight = dot(n0, -du);
                     if (cosToLight > 0 && cosAtLight > 0 && visible_mis(c.p, y0)) {
+                        const double tr = tr_mis(c.p, y0);
                         const double directPdfW = pdfA * dist2 / cosAtLight, emissionPdfW = pdfA * cosAtLight / kPi;
-                        const double wLight = (cosToLight / kPi) / directPdfW;
-                        const double wCamera = (emissionPdfW * cosToLight / (directPdfW * cosAtLight)) * (c.dVCM + c.dVC * (c.cos_in / kPi));
+                        const double wLight = (c.dir_pdf(cosToLight) * tr) / directPdfW;
+                        const double wCamera = (emissionPdfW * cosToLight * tr / (directPdfW * cosAtLight)) * (c.dVCM + c.dVC * c.rev_pdf());
                         const double w = pick_w(1.0 / (wLight + 1.0 + wCamera), 1);
-                        result = result + (w * cosToLight / directPdfW) * (c.T * fc * Le);
+                        result = result + (w * cosToLight * tr / directPdfW) * (c.T * fc * Le);
                     }
                 }
             }
@@ -934,14 +987,15 @@ struct Integrator {
                 double dist2 = len2(dir);
                 if (dist2 <= 0) continue;
                 V3 du = unit(dir);
-                const double cosCamera = dot(c.n, du), cosLight = dot(l.n, -du);
+                const double cosCamera = c.cosine(du), cosLight = l.cosine(-du);
                 if (cosCamera <= 0 || cosLight <= 0) continue;
                 if (!visible_mis(c.p, l.p)) continue;
-                const double camDirPdfA = (cosCamera / kPi) * cosLight / dist2, lightDirPdfA = (cosLight / kPi) * cosCamera / dist2;
-                const double wLight = camDirPdfA * (l.dVCM + l.dVC * (l.cos_in / kPi));
-                const double wCamera = lightDirPdfA * (c.dVCM + c.dVC * (c.cos_in / kPi));
+                const double tr = tr_mis(c.p, l.p);
+                const double camDirPdfA = c.dir_pdf(cosCamera) * cosLight * tr / dist2, lightDirPdfA = l.dir_pdf(cosLight) * cosCamera * tr / dist2;
+                const double wLight = camDirPdfA * (l.dVCM + l.dVC * l.rev_pdf());
+                const double wCamera = lightDirPdfA * (c.dVCM + c.dVC * c.rev_pdf());
                 const double w = pick_w(1.0 / (wLight + 1.0 + wCamera), 2);
-                result = result + (w * cosLight * cosCamera / dist2) * (c.T * fc * l.T * (l.albedo / kPi));
+                result = result + (w * cosLight * cosCamera * tr / dist2) * (c.T * fc * l.T * l.f());
             }
         }
         // t = 1: every light-subpath vertex seen from the camera lands on the film, wherever that is
@@ -950,7 +1004,7 @@ struct Integrator {
             double dist2 = len2(dir);
             if (dist2 <= 0) continue;
             V3 du = unit(dir);
-            const double cosToCamera = dot(l.n, du), cosAtCamera = dot(cam.fwd, -du);
+            const double cosToCamera = l.cosine(du), cosAtCamera = dot(cam.fwd, -du);
             if (cosToCamera <= 0 || cosAtCamera <= 0) continue;
             // where the line camera -> vertex crosses the viewport, in pixel coordinates from its upper-left corner
             V3 P = cam.center + (cam.c.focus_dist / cosAtCamera) * (-du);
@@ -959,10 +1013,10 @@ struct Integrator {
             if (!(xc >= 0 && yc >= 0 && xc < W && yc < H)) continue;
             if (!visible_mis(l.p, cam.center)) continue;
             const double ipcd = cam.plane_dist_px / cosAtCamera;
-            const double imageToSurface = (ipcd * ipcd / cosAtCamera) * cosToCamera / dist2;
-            const double wLight = (imageToSurface / n_light) * (l.dVCM + l.dVC * (l.cos_in / kPi));
+            const double imageToSurface = (ipcd * ipcd / cosAtCamera) * cosToCamera * tr_mis(l.p, cam.center) / dist2;
+            const double wLight = (imageToSurface / n_light) * (l.dVCM + l.dVC * l.rev_pdf());
             const double w = pick_w(1.0 / (wLight + 1.0), 3);
-            splat(int(yc) * W + int(xc), (w * imageToSurface / n_light) * (l.T * (l.albedo / kPi)));
+            splat(int(yc) * W + int(xc), (w * imageToSurface / n_light) * (l.T * l.f()));
         }
         return result;
     }

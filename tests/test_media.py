@@ -6,7 +6,10 @@ materials/material.h:149-171) -- bdpt_scene_set_media.
        statistical -- image means within Monte-Carlo error, and far from the medium-free image.
   GPU: film equal to the port's sample for sample on the counter-based stream (tolerance 1e-9 of the peak: fp64 atomics
        reorder the adds), both tree flavours; the draw inside constant_medium::hit goes through a deterministic log shared
-       bit for bit by the kernels and the port."""
+       bit for bit by the kernels and the port.
+  BDPT_WEIGHT_MIS with media (volume vertices in the recursive balance-heuristic weights, transmittance in every pdf and
+  contribution): the port's estimator against the reference's OWN path tracer (camera::path_trace_color) run over the same
+  constant_medium objects -- equal means, an unbiased estimator; GPU film = port film sample for sample."""
 import numpy as np
 import pytest
 
@@ -60,8 +63,6 @@ def test_media_film_equals_the_port_sample_for_sample(name, bvh, bdpt, scenes):
         ctx.upload(v, m, mats)
         ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H)
         assert rel_err(ctx.film(), ref) < 1e-9
-        with pytest.raises(bdpt.BdptError, match="media"):
-            ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
         ctx.set_media([])                                           # dropped: the plain scene again
         ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H)
         assert rel_err(ctx.film(), clear) < 1e-9
@@ -158,3 +159,57 @@ def test_cli_renders_a_yaml_scene_with_media(bdpt, tmp_path):
     ref_png = tmp_path / "ctypes.png"
     bdpt.write_png(str(ref_png), rgb)
     assert (tmp_path / "output" / "smoke.png").read_bytes() == ref_png.read_bytes()
+    # --mis: render_options.weighting = BDPT_WEIGHT_MIS through the same front end (media under MIS: volume vertices)
+    r = subprocess.run([exe, str(path), "--seed", "9", "--quiet", "--mis", "--out", "smoke_mis.png"], cwd=tmp_path, capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stderr
+    with bdpt.Context(0) as ctx:
+        ctx.set_media(s.media)
+        ctx.upload(s.verts, s.mat_id, s.materials)
+        ctx.render(s.camera, seed=9, bvh=bdpt.BVH_FAST, weighting=bdpt.WEIGHT_MIS)
+        mis_rgb = ctx.film_rgb8(4)
+    assert (mis_rgb != rgb).mean() > 0.05
+    mis_png = tmp_path / "ctypes_mis.png"
+    bdpt.write_png(str(mis_png), mis_rgb)   # (fp64 atomics reorder the adds by ~1e-16: far from an 8-bit step)
+    assert (tmp_path / "output" / "smoke_mis.png").read_bytes() == mis_png.read_bytes()
+
+
+@pytest.mark.skipif(not available("ref"), reason="oracle/_ref not shipped")
+def test_port_mis_with_media_agrees_with_the_references_path_tracer():
+    """The MIS estimator with volume vertices is unbiased: same image mean as camera::path_trace_color (camera.h:255-292) over the
+    reference's own constant_medium objects, overall and per 4 x 4-pixel block; the medium-free MIS image is 12 % brighter."""
+    from oracle.oracle import WEIGHT_MIS
+    v, m, mats, cam = ts.cornell(False)
+    media = ts.cornell_media()
+    W = H = 16
+    c = ocam(W, H, 900, 6, **cam)
+    mis = Oracle("port").load(v, m, mats).set_media(media).render(c, rng_mode=RNG_PHILOX, seed=3, nthreads=8, height=H, weighting=WEIGHT_MIS)
+    pt = Oracle("ref").load(v, m, mats).set_media(media).render_pt(c, seed=5, height=H)
+    clear = Oracle("port").load(v, m, mats).render(c, rng_mode=RNG_PHILOX, seed=3, nthreads=8, height=H, weighting=WEIGHT_MIS)
+    assert abs(mis.mean() / pt.mean() - 1.0) < 0.02, (mis.mean(), pt.mean())
+    assert clear.mean() / pt.mean() > 1.08
+    blk = lambda f: f.reshape(4, 4, 4, 4, 3).mean(axis=(1, 3, 4))
+    assert np.abs(blk(mis) / blk(pt) - 1.0).max() < 0.12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bvh", [0, 1])
+@pytest.mark.parametrize("name", ["cornell_box", "cornell_spheres"])
+def test_mis_media_film_equals_the_port_sample_for_sample(name, bvh, bdpt, scenes):
+    from oracle.oracle import WEIGHT_MIS
+    v, m, mats, cam = scenes[name]()
+    media = ts.cornell_media()
+    W, H, spp, depth = 36, 28, 4, 7
+    ref = Oracle("port").load(v, m, mats).set_media(media).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=42,
+                                                                  nthreads=8, height=H, weighting=WEIGHT_MIS)
+    clear = Oracle("port").load(v, m, mats).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=42, nthreads=8, height=H,
+                                                   weighting=WEIGHT_MIS)
+    assert np.mean(np.abs(clear - ref) > 1e-6 * ref.max()) > 0.5     # the media change the image (nearly every pixel)
+    with bdpt.Context(0) as ctx:
+        ctx.set_media(media)
+        ctx.upload(v, m, mats)
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
+        assert rel_err(ctx.film(), ref) < 1e-9          # fp64 atomics reorder the adds; exp() of the transmittance: an ulp
+        ctx.set_media([])
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
+        assert rel_err(ctx.film(), clear) < 1e-9

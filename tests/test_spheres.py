@@ -118,9 +118,7 @@ def test_sphere_argument_checks(bdpt):
         with pytest.raises(bdpt.BdptError, match="material"):
             ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8)
         ctx.set_spheres(spheres)
-        ctx.set_media(ts.cornell_media())
-        with pytest.raises(bdpt.BdptError, match="media"):   # spheres alone are fine under MIS (below); media are not
-            ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8, weighting=bdpt.WEIGHT_MIS)
+        ctx.render(bdpt.make_camera(8, 8, 1, 3, **cam), height=8, weighting=bdpt.WEIGHT_MIS)   # spheres (and media) render under MIS too
 
 
 def test_port_mis_with_analytic_spheres_agrees_with_the_reference_sum_free_estimate():
@@ -163,7 +161,15 @@ def test_mis_sphere_film_equals_the_port_sample_for_sample(bvh, bdpt):
         ctx.set_spheres(spheres)
         ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=13, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
         assert rel_err(ctx.film(), ref) < 1e-9          # fp64 atomics: only the order of the adds differs
-        ctx.set_spheres([])
+        # together with media
+        media = ts.cornell_media()
+        both = Oracle("port").load(v, m, mats).set_spheres(spheres).set_media(media).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX,
+                                                                                             seed=13, nthreads=8, height=H, weighting=WEIGHT_MIS)
+        assert rel_err(both, ref) > 0.02
+        ctx.set_media(media)
+        ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=13, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
+        assert rel_err(ctx.film(), both) < 1e-9
+        ctx.set_media([]); ctx.set_spheres([])
         ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=13, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
         assert rel_err(ctx.film(), bare) < 1e-9
 
