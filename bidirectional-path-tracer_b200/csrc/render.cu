@@ -355,8 +355,10 @@ __device__ __forceinline__ bool boundary_hit(const TriGeom* __restrict__ med_tri
     t_out = closest;
     return any;
 }
-// false: the ray's LINE certainly misses the (padded) bounds of the boundary mesh, so neither boundary hit exists
-__device__ __forceinline__ bool line_meets_bounds(const MediumDev& m, const D3& o, const D3& d) {
+// false: the part [tmin, tmax] of the ray certainly has nothing in common with the (padded) bounds of the boundary mesh.  Both boundary
+// hits of constant_medium::hit, if they exist, lie inside the line's slab interval [tn, tf]; after its clamps to [tmin, tmax] the medium
+// then sees t1 >= t2 and answers "no hit" WITHOUT a draw -- so skipping the boundary loops here changes nothing.
+__device__ __forceinline__ bool line_meets_bounds(const MediumDev& m, const D3& o, const D3& d, double tmin, double tmax) {
     const double oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
     double tn = -__longlong_as_double(0x7FF0000000000000LL), tf = __longlong_as_double(0x7FF0000000000000LL);
 #pragma unroll
@@ -367,13 +369,13 @@ __device__ __forceinline__ bool line_meets_bounds(const MediumDev& m, const D3& 
             tn = fmax(tn, fmin(a, b)); tf = fmin(tf, fmax(a, b));
         }
     }
-    return !(tn > tf);
+    return !(tn > tf) && !(tf < tmin) && !(tn > tmax);
 }
 // constant_medium::hit, constant_medium.h:22-58 (oracle/port.cpp: medium_hit).  ONE draw, only when the part of the ray inside
 // the boundary overlaps [tmin, tmax].
 __device__ __forceinline__ bool medium_hit(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double tmin,
                                            double tmax, Rng& rng, double& t_out) {
-    if (!line_meets_bounds(m, o, d)) return false;
+    if (!line_meets_bounds(m, o, d, tmin, tmax)) return false;
     const double inf = __longlong_as_double(0x7FF0000000000000LL);
     double t1, t2;
     if (!boundary_hit(med_tris, m, o, d, -inf, inf, t1)) return false;
@@ -394,7 +396,7 @@ __device__ __forceinline__ bool medium_hit(const TriGeom* __restrict__ med_tris,
 // oracle/port.cpp: medium_overlap.
 __device__ __forceinline__ double medium_overlap(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double tmin,
                                                  double tmax) {
-    if (!line_meets_bounds(m, o, d)) return 0.0;
+    if (!line_meets_bounds(m, o, d, tmin, tmax)) return 0.0;
     const double inf = __longlong_as_double(0x7FF0000000000000LL);
     double t1, t2;
     if (!boundary_hit(med_tris, m, o, d, -inf, inf, t1)) return 0.0;
@@ -1170,6 +1172,13 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                             sd = vdu;
                             emit = true;
                             if (l_medium || l_sphere) far_prim = BDPT_MISS;   // no far-endpoint triangle to test first
+                            // the far vertex's own triangle settles ~80 % of the segments (k_shadow_pre does the same for the
+                            // survivors' queue): asked here first, before the side lists' loops over boundary triangles
+                            if (MEDIA && far_prim != BDPT_MISS) {
+                                RayD sr;
+                                sr.o = so; sr.d = sd; sr.tmin = 0.001; sr.tmax = max_t;
+                                if (far_endpoint_occludes(sc, sr, far_prim, nullptr)) emit = false;
+                            }
                             // the sphere prims of the side list occlude like any prim (oracle/port.cpp: spheres_occlude)
                             for (uint32_t sk = 0; MEDIA && sk < sc.n_spheres && emit; ++sk) {
                                 double ts;
