@@ -355,6 +355,34 @@ __device__ __forceinline__ bool boundary_hit(const TriGeom* __restrict__ med_tri
     t_out = closest;
     return any;
 }
+// The two boundary hits constant_medium::hit asks for (constant_medium.h:25-29): the nearest over the whole line, then the nearest from
+// 0.0001 behind it.  Small boundaries (a box is 12 triangles) are met ONCE: the candidates' t are kept and the second query reads them
+// back -- the same comparisons on the same numbers as two loops over the triangles.
+__device__ __forceinline__ bool boundary_pair(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double& t1, double& t2) {
+    const double inf = __longlong_as_double(0x7FF0000000000000LL);
+    constexpr uint32_t kKeep = 16;
+    if (m.count > kKeep) return boundary_hit(med_tris, m, o, d, -inf, inf, t1) && boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2);
+    double ts[kKeep];
+    uint32_t n = 0;
+    double c1 = inf;
+    bool any = false;
+    for (uint32_t i = 0; i < m.count; ++i) {
+        double t, u, v;
+        if (tri_candidate(med_tris + m.first + i, o, d, t, u, v) && t == t) {
+            ts[n++] = t;
+            if (t <= c1) { any = true; c1 = t; }
+        }
+    }
+    if (!any) return false;
+    t1 = c1;
+    const double from = t1 + 0.0001;
+    double c2 = inf;
+    any = false;
+    for (uint32_t i = 0; i < n; ++i)
+        if (from <= ts[i] && ts[i] <= c2) { any = true; c2 = ts[i]; }
+    t2 = c2;
+    return any;
+}
 // false: the part [tmin, tmax] of the ray certainly has nothing in common with the (padded) bounds of the boundary mesh.  Both boundary
 // hits of constant_medium::hit, if they exist, lie inside the line's slab interval [tn, tf]; after its clamps to [tmin, tmax] the medium
 // then sees t1 >= t2 and answers "no hit" WITHOUT a draw -- so skipping the boundary loops here changes nothing.
@@ -378,8 +406,7 @@ __device__ __forceinline__ bool medium_hit(const TriGeom* __restrict__ med_tris,
     if (!line_meets_bounds(m, o, d, tmin, tmax)) return false;
     const double inf = __longlong_as_double(0x7FF0000000000000LL);
     double t1, t2;
-    if (!boundary_hit(med_tris, m, o, d, -inf, inf, t1)) return false;
-    if (!boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2)) return false;
+    if (!boundary_pair(med_tris, m, o, d, t1, t2)) return false;
     if (t1 < tmin) t1 = tmin;
     if (t2 > tmax) t2 = tmax;
     if (t1 >= t2) return false;
@@ -399,8 +426,7 @@ __device__ __forceinline__ double medium_overlap(const TriGeom* __restrict__ med
     if (!line_meets_bounds(m, o, d, tmin, tmax)) return 0.0;
     const double inf = __longlong_as_double(0x7FF0000000000000LL);
     double t1, t2;
-    if (!boundary_hit(med_tris, m, o, d, -inf, inf, t1)) return 0.0;
-    if (!boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2)) return 0.0;
+    if (!boundary_pair(med_tris, m, o, d, t1, t2)) return 0.0;
     if (t1 < tmin) t1 = tmin;
     if (t2 > tmax) t2 = tmax;
     if (t1 >= t2) return 0.0;
