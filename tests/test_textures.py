@@ -60,6 +60,29 @@ def test_gpu_textured_film_equals_the_port(bvh, weighting, bdpt, gpu_ctx, golden
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("weighting", [0, 1])
+def test_gpu_film_with_textures_media_and_spheres_together_equals_the_port(weighting, bdpt, gpu_ctx, golden):
+    """Every extension of the scene surface at once (the TEX + MEDIA kernel flavours under either weighting): textured room, two media,
+    two analytic spheres of the scene's own materials."""
+    g, v, m, mats, cam, texs = textured_scene(golden)
+    tarr, blob = O.make_textures(texs)
+    media = ts.cornell_media()
+    lamb = next(i for i, mt in enumerate(mats) if mt[0] == 0)
+    spheres = [((190.0, 90.0, 190.0), 90.0, lamb), ((400.0, 300.0, 350.0), 70.0, 3)]   # the second one wears a texture (u = v = 0 on a sphere prim)
+    W, H, spp, depth = 36, 28, 4, 7
+    port = O.Oracle("port").load(v, m, mats, textures=(tarr, len(texs), blob)).set_media(media).set_spheres(spheres)
+    ref = port.render(O.make_camera(W, H, spp, depth, **cam), rng_mode=O.RNG_PHILOX, seed=17, nthreads=8, height=H, weighting=weighting)
+    try:
+        gpu_ctx.upload(v, m, mats)
+        gpu_ctx.set_textures(texs); gpu_ctx.set_media(media); gpu_ctx.set_spheres(spheres)
+        gpu_ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=17, bvh=1, height=H, weighting=weighting)
+        assert ref.max() > 0
+        assert np.abs(gpu_ctx.film() - ref).max() / np.abs(ref).max() < 1e-9
+    finally:
+        gpu_ctx.set_textures([]); gpu_ctx.set_media([]); gpu_ctx.set_spheres([])
+
+
+@pytest.mark.gpu
 def test_set_textures_rejects_bad_tables(bdpt, gpu_ctx):
     with pytest.raises(bdpt.BdptError):
         gpu_ctx.set_textures([dict(type=bdpt.TEX_IMAGE, width=100, height=100, data=np.zeros(12, np.uint8))])
