@@ -1,5 +1,6 @@
 // C-ABI of libbdpt (include/bdpt.h): context, scene upload, batch trace / visible, film access.
 // Compiled with -fmad=false: the trace kernels instantiate the reference-exact traversal.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -367,6 +368,7 @@ void bdpt_ctx_destroy(bdpt_ctx* ctx) {
     if (ctx->d_media) cudaFree(ctx->d_media);
     if (ctx->d_spheres) cudaFree(ctx->d_spheres);
     if (ctx->d_med_tris) cudaFree(ctx->d_med_tris);
+    if (ctx->d_med_nodes) cudaFree(ctx->d_med_nodes);
     if (ctx->d_stats) cudaFree(ctx->d_stats);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -536,6 +538,42 @@ int bdpt_scene_set_spheres(bdpt_ctx* ctx, const bdpt_sphere* spheres, uint32_t n
     return BDPT_OK;
 }
 
+// Median-split tree over the boundary triangles [first, first + count) of one medium (reordered in place; their order means nothing:
+// a boundary query returns the smallest t).  Leaves of <= 4 triangles; boxes padded well beyond any rounding of the triangle test.
+static int32_t build_med_tree(std::vector<TriGeom>& tris, size_t first, size_t lo_i, size_t hi_i, std::vector<MedNode>& nodes, double pad) {
+    const int32_t me = int32_t(nodes.size());
+    nodes.push_back(MedNode{});
+    MedNode n{};
+    double clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int c = 0; c < 3; ++c) { n.lo[c] = INFINITY; n.hi[c] = -INFINITY; }
+    auto vert = [](const TriGeom& g, int v, int c) {
+        const double v0[3] = {g.v0x, g.v0y, g.v0z}, e1[3] = {g.e1x, g.e1y, g.e1z}, e2[3] = {g.e2x, g.e2y, g.e2z};
+        return v == 0 ? v0[c] : (v == 1 ? v0[c] + e1[c] : v0[c] + e2[c]);
+    };
+    auto centroid = [&](const TriGeom& g, int c) { return (vert(g, 0, c) + vert(g, 1, c) + vert(g, 2, c)) / 3.0; };
+    for (size_t i = lo_i; i < hi_i; ++i)
+        for (int c = 0; c < 3; ++c) {
+            for (int v = 0; v < 3; ++v) { const double x = vert(tris[i], v, c); n.lo[c] = std::fmin(n.lo[c], x); n.hi[c] = std::fmax(n.hi[c], x); }
+            const double ce = centroid(tris[i], c);
+            clo[c] = std::fmin(clo[c], ce); chi[c] = std::fmax(chi[c], ce);
+        }
+    for (int c = 0; c < 3; ++c) { n.lo[c] -= pad; n.hi[c] += pad; }
+    if (hi_i - lo_i <= 4) {
+        n.a = int32_t(lo_i - first); n.b = -int32_t(hi_i - lo_i);
+    } else {
+        int axis = 0;
+        if (chi[1] - clo[1] > chi[axis] - clo[axis]) axis = 1;
+        if (chi[2] - clo[2] > chi[axis] - clo[axis]) axis = 2;
+        const size_t mid = lo_i + (hi_i - lo_i) / 2;
+        std::nth_element(tris.begin() + lo_i, tris.begin() + mid, tris.begin() + hi_i,
+                         [&](const TriGeom& x, const TriGeom& y) { return centroid(x, axis) < centroid(y, axis); });
+        n.a = build_med_tree(tris, first, lo_i, mid, nodes, pad);
+        n.b = build_med_tree(tris, first, mid, hi_i, nodes, pad);
+    }
+    nodes[size_t(me)] = n;
+    return me;
+}
+
 int bdpt_scene_set_media(bdpt_ctx* ctx, const bdpt_medium* media, uint32_t n_media, const double* boundary_verts, uint64_t n_boundary_tris) {
     if (!ctx || (n_media && (!media || !boundary_verts))) return BDPT_ERR_ARG;
     if (n_media > 16) { ctx->err = "at most 16 media"; return BDPT_ERR_ARG; }
@@ -573,11 +611,36 @@ int bdpt_scene_set_media(bdpt_ctx* ctx, const bdpt_medium* media, uint32_t n_med
             d.lo[c] -= pad; d.hi[c] += pad;
         }
         d.first = uint32_t(m.first_tri); d.count = uint32_t(m.n_tris);
+        d.nodes = nullptr;
+    }
+    // large boundaries get a tree (two media may share triangles: then the second one keeps its loop)
+    std::vector<MedNode> nodes;
+    std::vector<size_t> root_of(n_media, SIZE_MAX);
+    std::vector<char> taken(n_boundary_tris, 0);
+    for (uint32_t k = 0; k < n_media; ++k) {
+        const MediumDev& d = h[k];
+        bool shared = false;
+        for (uint32_t i = 0; i < d.count; ++i) shared = shared || taken[d.first + i];
+        for (uint32_t i = 0; i < d.count; ++i) taken[d.first + i] = 1;
+        if (d.count <= kMedTreeMin || shared || std::getenv("BDPT_MEDIA_NO_TREE")) continue;
+        const double ext = std::fmax(d.hi[0] - d.lo[0], std::fmax(d.hi[1] - d.lo[1], d.hi[2] - d.lo[2]));
+        const double big = std::fmax(std::fmax(std::fabs(d.lo[0]) + std::fabs(d.hi[0]), std::fabs(d.lo[1]) + std::fabs(d.hi[1])), std::fabs(d.lo[2]) + std::fabs(d.hi[2]));
+        root_of[k] = nodes.size();
+        std::vector<MedNode> own;
+        build_med_tree(tris, d.first, d.first, size_t(d.first) + d.count, own, 1e-7 * (ext + big) + 1e-12);
+        // (child links are relative to the medium's own root: MediumDev.nodes points at it)
+        nodes.insert(nodes.end(), own.begin(), own.end());
     }
     if (ctx->d_media) { cudaFree(ctx->d_media); ctx->d_media = nullptr; }
     if (ctx->d_med_tris) { cudaFree(ctx->d_med_tris); ctx->d_med_tris = nullptr; }
+    if (ctx->d_med_nodes) { cudaFree(ctx->d_med_nodes); ctx->d_med_nodes = nullptr; }
     ctx->n_media = 0;
     if (n_media) {
+        if (!nodes.empty()) {
+            BDPT_CUDA(ctx, cudaMalloc(&ctx->d_med_nodes, nodes.size() * sizeof(MedNode)));
+            BDPT_CUDA(ctx, cudaMemcpy(ctx->d_med_nodes, nodes.data(), nodes.size() * sizeof(MedNode), cudaMemcpyHostToDevice));
+            for (uint32_t k = 0; k < n_media; ++k) if (root_of[k] != SIZE_MAX) h[k].nodes = ctx->d_med_nodes + root_of[k];
+        }
         BDPT_CUDA(ctx, cudaMalloc(&ctx->d_media, n_media * sizeof(MediumDev)));
         BDPT_CUDA(ctx, cudaMemcpy(ctx->d_media, h.data(), n_media * sizeof(MediumDev), cudaMemcpyHostToDevice));
         BDPT_CUDA(ctx, cudaMalloc(&ctx->d_med_tris, std::max<uint64_t>(tris.size(), 1) * sizeof(TriGeom)));

@@ -39,6 +39,7 @@ struct bdpt_ctx {
     // media of bdpt_scene_set_media: likewise
     bdpt::MediumDev* d_media = nullptr;
     bdpt::TriGeom* d_med_tris = nullptr;
+    bdpt::MedNode* d_med_nodes = nullptr;    // trees over the large boundary meshes, all media back to back
     uint32_t n_media = 0;
     bdpt::SphereDev* d_spheres = nullptr;   // bdpt_scene_set_spheres
     uint32_t n_spheres = 0;

@@ -355,12 +355,59 @@ __device__ __forceinline__ bool boundary_hit(const TriGeom* __restrict__ med_tri
     t_out = closest;
     return any;
 }
+// The same query through the tree over a large boundary (MedNode, built by bdpt_scene_set_media): the smallest candidate t inside
+// [tmin, tmax], found by visiting only the leaves whose padded boxes the line crosses before the best t so far -- the same number
+// the loop over all triangles returns.
+__device__ __noinline__ bool boundary_hit_tree(const TriGeom* __restrict__ tris, const MedNode* __restrict__ nodes, D3 o, D3 d, double tmin, double tmax,
+                                               double* t_out) {
+    const double oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+    double inv[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) inv[k] = 1.0 / dd[k];
+    int32_t stack[24];   // <= 4096 triangles, median splits, leaves of <= 4: depth <= 11
+    int sp = 0;
+    int32_t cur = 0;
+    bool any = false;
+    double closest = tmax;
+    for (;;) {
+        const MedNode* nd = nodes + cur;
+        double tn = tmin, tf = closest;
+        bool hit = true;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double lo = nd->lo[k], hi = nd->hi[k];
+            if (dd[k] == 0.0) { if (oo[k] < lo || oo[k] > hi) hit = false; }
+            else {
+                const double a = (lo - oo[k]) * inv[k], b = (hi - oo[k]) * inv[k];
+                tn = fmax(tn, fmin(a, b)); tf = fmin(tf, fmax(a, b));
+            }
+        }
+        if (hit && !(tn > tf)) {
+            const int32_t a = nd->a, b = nd->b;
+            if (b < 0) {
+                for (int32_t i = 0; i < -b; ++i) {
+                    double t, u, v;
+                    if (tri_candidate(tris + a + i, o, d, t, u, v) && tmin <= t && t <= closest) { any = true; closest = t; }
+                }
+            } else {
+                stack[sp++] = b;
+                cur = a;
+                continue;
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    *t_out = closest;
+    return any;
+}
 // The two boundary hits constant_medium::hit asks for (constant_medium.h:25-29): the nearest over the whole line, then the nearest from
 // 0.0001 behind it.  Small boundaries (a box is 12 triangles) are met ONCE: the candidates' t are kept and the second query reads them
 // back -- the same comparisons on the same numbers as two loops over the triangles.
 __device__ __forceinline__ bool boundary_pair(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double& t1, double& t2) {
     const double inf = __longlong_as_double(0x7FF0000000000000LL);
     constexpr uint32_t kKeep = 16;
+    if (m.nodes) return boundary_hit_tree(med_tris + m.first, m.nodes, o, d, -inf, inf, &t1) && boundary_hit_tree(med_tris + m.first, m.nodes, o, d, t1 + 0.0001, inf, &t2);
     if (m.count > kKeep) return boundary_hit(med_tris, m, o, d, -inf, inf, t1) && boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2);
     double ts[kKeep];
     uint32_t n = 0;

@@ -80,11 +80,17 @@ struct __align__(16) Tex {
 static_assert(sizeof(Tex) == 80, "Tex must be 80 bytes");
 
 // constant_medium (constant_medium.h:8-61) + isotropic (material.h:149-171): bdpt_scene_set_media
+// node of the small tree over a LARGE boundary mesh (more than kMedTreeMin triangles; a box's 12 are a plain loop): boxes in fp64, padded;
+// b >= 0: children a, b; b < 0: leaf of -b triangles from a (relative to the medium's first triangle)
+struct __align__(16) MedNode { double lo[3], hi[3]; int32_t a, b; int32_t pad[2]; };
+static_assert(sizeof(MedNode) == 64, "MedNode must be 64 bytes");
+constexpr uint32_t kMedTreeMin = 16;
 struct __align__(16) MediumDev {
     double neg_inv_density;          // constant_medium.h:12
     double r, g, b;                  // isotropic's colour
     double lo[3], hi[3];             // bounds of the boundary mesh: a ray that misses them has no boundary hit
     uint32_t first, count;           // boundary triangles in med_tris
+    const MedNode* nodes;            // tree over them (device pointer), null for small boundaries
 };
 static_assert(sizeof(MediumDev) == 96, "MediumDev must be 96 bytes");
 // analytic sphere of bdpt_scene_set_spheres: a world prim of a side list (the reference only tessellates)

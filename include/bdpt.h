@@ -186,7 +186,8 @@ int bdpt_scene_set_textures(bdpt_ctx* ctx, const bdpt_texture* tex, uint32_t n_t
  * (uniform sphere scatter, f = albedo / 4 pi, the reference's arbitrary normal (1,0,0)); visible() lets a medium
  * between two vertices scatter the shadow ray with the same probability.  BDPT_WEIGHT_MIS: a scatter point is a
  * connectable vertex (no cosine, 1 / (4 pi) both ways) and every pdf and contribution holds the analytic transmittance of its
- * segment.  bdpt_trace / bdpt_visible stay deterministic queries (media draw random numbers).  Limits: 16 media, 4096 boundary triangles each.
+ * segment.  bdpt_trace / bdpt_visible stay deterministic queries (media draw random numbers).  Limits: 16 media, 4096 boundary triangles each
+ * (a boundary of more than 16 gets a small tree of its own; a box's 12 are a loop).
  * Belongs to the context like the texture table: before or after the scene upload, again to replace, n_media = 0 to drop. */
 typedef struct {
     double   density;        /* > 0 */

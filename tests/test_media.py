@@ -213,3 +213,26 @@ def test_mis_media_film_equals_the_port_sample_for_sample(name, bvh, bdpt, scene
         ctx.set_media([])
         ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=42, bvh=bvh, height=H, weighting=bdpt.WEIGHT_MIS)
         assert rel_err(ctx.film(), clear) < 1e-9
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("weighting", [0, 1])
+def test_large_boundary_goes_through_its_tree_and_gives_the_port_film(weighting, bdpt):
+    """A medium bounded by a tessellated sphere (528 triangles) beside a box-shaped one: bdpt_scene_set_media builds a tree over the
+    large boundary (more than 16 triangles); the port loops over all of them.  Same film, sample for sample."""
+    v, m, mats, cam = ts.cornell(False)
+    ball = ts.uv_sphere((278.0, 200.0, 278.0), 120.0, 12, 24).reshape(-1, 9)
+    assert len(ball) > 400
+    media = [(0.012, (0.8, 0.85, 0.9), ball), (0.004, (0.2, 0.4, 0.9), ts.box_mesh((250, 150, 50), (500, 400, 250)))]
+    W, H, spp, depth = 32, 24, 4, 6
+    ref = Oracle("port").load(v, m, mats).set_media(media).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=23, nthreads=8,
+                                                                  height=H, weighting=weighting)
+    clear = Oracle("port").load(v, m, mats).render(ocam(W, H, spp, depth, **cam), rng_mode=RNG_PHILOX, seed=23, nthreads=8, height=H,
+                                                   weighting=weighting)
+    assert np.mean(np.abs(clear - ref) > 1e-6 * ref.max()) > 0.5
+    for bvh in (0, 1):
+        with bdpt.Context(0) as ctx:
+            ctx.upload(v, m, mats)
+            ctx.set_media(media)
+            ctx.render(bdpt.make_camera(W, H, spp, depth, **cam), seed=23, bvh=bvh, height=H, weighting=weighting)
+            assert rel_err(ctx.film(), ref) < 1e-9

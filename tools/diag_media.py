@@ -20,13 +20,15 @@ r = 0.08 * ext.max()
 lamb = next(i for i, m in enumerate(sf.materials) if m.type == 0)
 spheres = [(tuple(c + np.array([0.3, 0.2, 0.0]) * ext), r, lamb), (tuple(c + np.array([-0.3, 0.25, 0.1]) * ext), r, lamb),
            (tuple(c + np.array([0.0, 0.35, -0.3]) * ext), r, lamb)]
+ball = [(4.0 / ext.max(), (0.9, 0.9, 0.9), ts.uv_sphere(tuple(c), 0.3 * ext.max(), 16, 32).reshape(-1, 9))]   # a large boundary: goes through its tree
 out = {}
 STREAMS = int(os.environ.get("STREAMS", "0"))        # 1: one worker, kernel classes' times add up to the step
 ONLY = os.environ.get("ONLY", "")
 with b.Context(0) as ctx:
     ctx.upload(sf.verts, sf.mat_id, sf.materials)
-    for name, md, sp in (("plain", [], []), ("two_media", media, []), ("three_spheres", [], spheres), ("media_and_spheres", media, spheres)):
-        if ONLY and name not in ONLY.split(","): continue
+    for name, md, sp in (("plain", [], []), ("two_media", media, []), ("three_spheres", [], spheres), ("media_and_spheres", media, spheres),
+                         ("ball_medium_%d_triangles" % len(ball[0][2]), ball, [])):
+        if ONLY and not any(name.startswith(x) for x in ONLY.split(",")): continue
         ctx.set_media(md); ctx.set_spheres(sp)
         for tag, w in (("ref_sum", b.WEIGHT_REF_SUM), ("mis", b.WEIGHT_MIS)):
             ctx.film_clear(bench.WIDTH, bench.HEIGHT)
