@@ -105,7 +105,11 @@ struct SQ {
     uint32_t *pix, *far;             // pixel; prim of the far (light-side) vertex
     uint32_t* live;                  // segments the far-endpoint test did not settle (indices into this queue)
     uint32_t* cnt;                   // SQ_*
+    // participating media only (null otherwise): what k_media_segments needs to settle the media's share of a segment
+    unsigned long long* mkey;        // REF_SUM: (sample id << 20) | (camera vertex index * 128 + light vertex index): the draws' key
+    double* msum;                    // MIS: wLight + wCamera of the segment's weight with the transmittance taken out
 };
+constexpr uint32_t kDeadSeg = 0xFFFFFFFEu;   // SQ.far of a segment a medium scattered: the shadow stage skips it
 enum { SQ_N = 0, SQ_LIVE = 1, SQ_OVERFLOW = 2, SQ_CURSOR = 3 /* dynamic-fetch cursor of stage 2 */, SQ_COUNT = 8 };
 
 struct WF {              // wavefront workspace, all device pointers
@@ -130,6 +134,7 @@ struct WF {              // wavefront workspace, all device pointers
                                      // stream while the main stream already traces the next
     int textured;                    // the scene has textures: lcol exists
     D3* lcol;                        // beside lv: the light vertex's colour as connect_vertices needs it (emission / albedo at that point)
+    int media;                       // the scene has participating media: the shadow queues carry mkey / msum
     int mis;                         // BDPT_WEIGHT_MIS: the three arrays below exist
     PathMis* pmis;                   // per path id
     VertMis *cvm, *lvm;              // beside cv / lv
@@ -1206,6 +1211,7 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
         D3 so = mk(0, 0, 0), sd = mk(0, 0, 0), contrib = mk(0, 0, 0);
         double max_t = 0;
         uint32_t far_prim = 0;
+        unsigned long long mkey = 0;
         if (m < nl) {
             D3 lp, lT;
             uint32_t lprim, lindex;
@@ -1258,13 +1264,9 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                                 if (sphere_hit_t(sc.spheres[sk], so, sd, 0.001, max_t, ts)) emit = false;
                             }
                             // media between the two vertices scatter the shadow ray (world.hit inside visible(), camera.h:437): one draw
-                            // of the sample's shadow stream per (pair, medium) -- oracle/port.cpp: visible_media
-                            for (uint32_t mk_ = 0; MEDIA && mk_ < sc.n_media && emit; ++mk_) {
-                                Rng srng;
-                                srng.init(f.seed, 2u, sid, (cindex * 128u + lindex) * 16u + mk_);
-                                double tm;
-                                if (medium_hit(sc.med_tris, sc.media[mk_], so, sd, 0.001, max_t, srng, tm)) emit = false;
-                            }
+                            // of the sample's shadow stream per (pair, medium) -- oracle/port.cpp: visible_media.  Asked by
+                            // k_media_segments over the queued segments, where every lane has one (here ~3 of 32 lanes would).
+                            if (MEDIA && q.mkey) mkey = ((unsigned long long)sid << 20) | (unsigned long long)(cindex * 128u + lindex);
                         }
                     }
                 }
@@ -1279,6 +1281,7 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
                 q.cx[slot] = contrib.x; q.cy[slot] = contrib.y; q.cz[slot] = contrib.z;
                 q.pix[slot] = pix;
                 q.far[slot] = far_prim;
+                if (MEDIA && q.mkey) q.mkey[slot] = mkey;
             } else {
                 q.cnt[SQ_OVERFLOW] = 1;
             }
@@ -1295,7 +1298,8 @@ __global__ void __launch_bounds__(kBlock) k_connect(SceneView sc, Frame f, WF w,
 // the shadow queue (the segment stops short of the far surface: SURVEY F4 is a property of the reference's estimator,
 // not of this one) and reaches the film as atomic adds.
 template <bool EX>
-__device__ __forceinline__ void push_segment(const SceneView& sc, const WF& w, const SQ& q, bool emit, D3 from, D3 to_dir_unit, double dist, D3 contrib, uint32_t pix) {
+__device__ __forceinline__ void push_segment(const SceneView& sc, const WF& w, const SQ& q, bool emit, D3 from, D3 to_dir_unit, double dist, D3 contrib, uint32_t pix,
+                                             double msum = 0.0) {
     const double max_t = dist - 0.001 - 1e-6 * (1.0 + dist);
     emit = emit && max_t > 0.001;
     if (EX && emit) {   // the sphere prims of the side list occlude like any prim (oracle/port.cpp: visible_mis)
@@ -1315,16 +1319,11 @@ __device__ __forceinline__ void push_segment(const SceneView& sc, const WF& w, c
             q.cx[slot] = contrib.x; q.cy[slot] = contrib.y; q.cz[slot] = contrib.z;
             q.pix[slot] = pix;
             q.far[slot] = BDPT_MISS;   // no far-endpoint shortcut: the far surface is outside the segment by construction
+            if (EX && q.msum) q.msum[slot] = msum;
         } else {
             q.cnt[SQ_OVERFLOW] = 1;
         }
     }
-}
-
-// transmittance of the media along the segment push_segment queues (oracle/port.cpp: tr_mis)
-__device__ __forceinline__ double segment_transmittance(const SceneView& sc, D3 from, D3 to_dir_unit, double dist) {
-    const double max_t = dist - 0.001 - 1e-6 * (1.0 + dist);
-    return media_transmittance(sc.media, sc.med_tris, sc.n_media, from + (0.001 * to_dir_unit), to_dir_unit, 0.001, max_t);
 }
 
 template <bool EX>
@@ -1360,6 +1359,9 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
         bool emit = false, emit_splat = false;
         D3 dirc = mk(0, 0, 0), dirs = mk(0, 0, 0), contrib = mk(0, 0, 0), contrib_s = mk(0, 0, 0), lp = mk(0, 0, 0);
         double distc = 0, dists = 0;
+        // media: the segment's transmittance Tr is found by k_media_segments over the queue (all lanes busy there); every weight is
+        // 1 / (S Tr + 1) and every contribution C Tr / (S Tr + 1) with S and C free of Tr -- S travels in q.msum, C as the contribution
+        double msum = 0, msum_s = 0;
         uint32_t spix = 0;
         if (m < nl && (have_cam || splatter)) {
             D3 lT;
@@ -1387,7 +1389,7 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                     const double cosCamera = c_med ? 1.0 : dot(cn, du), cosLight = l_med ? 1.0 : dot(ln, -du);
                     if (cosCamera > 0 && cosLight > 0) {
                         dirc = du; distc = len(dir);
-                        const double tr = media ? segment_transmittance(sc, cp, dirc, distc) : 1.0;
+                        const double tr = 1.0;
                         const double c_dir = c_med ? 1 / (4 * kPi) : cosCamera / kPi;       // pdf of the camera vertex scattering this way
                         const double c_rev = c_med ? 1 / (4 * kPi) : cm.cos_in / kPi;       // ... and back towards its predecessor
                         if (lprim & kLightFlag) {   // s = 1: the emitter point (ctf = T * f of the camera vertex)
@@ -1395,7 +1397,8 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                                 const double directPdfW = pdfA * dist2 / cosLight, emissionPdfW = pdfA * cosLight / kPi;
                                 const double wLight = (c_dir * tr) / directPdfW;
                                 const double wCamera = (emissionPdfW * cosCamera * tr / (directPdfW * cosLight)) * (cm.dVCM + cm.dVC * c_rev);
-                                const double wgt = 1.0 / (wLight + 1.0 + wCamera);
+                                const double wgt = media ? 1.0 : 1.0 / (wLight + 1.0 + wCamera);
+                                msum = wLight + wCamera;
                                 contrib = (wgt * cosCamera * tr / directPdfW) * (ctf * lrgb);
                                 emit = true;
                             }
@@ -1406,7 +1409,8 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                                 const double camDirPdfA = c_dir * cosLight * tr / dist2, lightDirPdfA = l_dir * cosCamera * tr / dist2;
                                 const double wLight = camDirPdfA * (vm.dVCM + vm.dVC * l_rev);
                                 const double wCamera = lightDirPdfA * (cm.dVCM + cm.dVC * c_rev);
-                                const double wgt = 1.0 / (wLight + 1.0 + wCamera);
+                                const double wgt = media ? 1.0 : 1.0 / (wLight + 1.0 + wCamera);
+                                msum = wLight + wCamera;
                                 contrib = (wgt * cosLight * cosCamera * tr / dist2) * (ctf * lT * lf);
                                 emit = true;
                             }
@@ -1428,10 +1432,11 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                             const VertMis vm = w.lvm[size_t(b) * size_t(w.depth) + size_t(m)];
                             const double ipcd = f.plane_px / cosAtCamera;
                             dirs = du; dists = len(dir);
-                            const double tr = media ? segment_transmittance(sc, lp, dirs, dists) : 1.0;
+                            const double tr = 1.0;
                             const double imageToSurface = (ipcd * ipcd / cosAtCamera) * cosToCamera * tr / dist2;
                             const double wLight = (imageToSurface / f.n_light) * (vm.dVCM + vm.dVC * (l_med ? 1 / (4 * kPi) : vm.cos_in / kPi));
-                            const double wgt = 1.0 / (wLight + 1.0);
+                            const double wgt = media ? 1.0 : 1.0 / (wLight + 1.0);
+                            msum_s = wLight;
                             contrib_s = (wgt * imageToSurface / f.n_light) * (lT * lf);
                             spix = uint32_t(int(yc)) * uint32_t(f.W) + uint32_t(int(xc));
                             emit_splat = true;
@@ -1440,8 +1445,37 @@ __global__ void __launch_bounds__(kBlock) k_connect_mis(SceneView sc, Frame f, W
                 }
             }
         }
-        push_segment<EX>(sc, w, q, emit, cp, dirc, distc, contrib, pix);
-        push_segment<EX>(sc, w, q, emit_splat, lp, dirs, dists, contrib_s, spix);
+        push_segment<EX>(sc, w, q, emit, cp, dirc, distc, contrib, pix, msum);
+        push_segment<EX>(sc, w, q, emit_splat, lp, dirs, dists, contrib_s, spix, msum_s);
+    }
+}
+
+// ------------------------------------------------------------------ K3b, participating media only
+// The media's share of every queued segment, one segment per thread (in the connect kernels a handful of lanes per warp hold a
+// segment at any one time: ncu showed 3 of 32 busy in the boundary loops).  REF_SUM: a medium between the two vertices scatters the
+// shadow ray with the probability constant_medium::hit gives it, one draw of the sample's shadow stream per (pair, medium)
+// (oracle/port.cpp: visible_media); a scattered segment is marked dead.  MIS: the analytic transmittance finishes weight and
+// contribution (oracle/port.cpp: tr_mis).
+template <bool MIS>
+__global__ void __launch_bounds__(kBlock) k_media_segments(SceneView sc, Frame f, WF w, SQ q) {
+    const uint32_t idx = blockIdx.x * kBlock + threadIdx.x;
+    if (idx >= q.cnt[SQ_N] || idx >= uint32_t(w.scap)) return;
+    const D3 so = mk(q.ox[idx], q.oy[idx], q.oz[idx]), sd = mk(q.dx[idx], q.dy[idx], q.dz[idx]);
+    const double max_t = q.tmax[idx];
+    if (MIS) {
+        const double tr = media_transmittance(sc.media, sc.med_tris, sc.n_media, so, sd, 0.001, max_t);
+        const double wt = tr / (q.msum[idx] * tr + 1.0);
+        q.cx[idx] *= wt; q.cy[idx] *= wt; q.cz[idx] *= wt;
+    } else {
+        const unsigned long long key = q.mkey[idx];
+        const uint64_t sid = uint64_t(key >> 20);
+        const uint32_t pair = uint32_t(key & 0xFFFFFu);
+        for (uint32_t k = 0; k < sc.n_media; ++k) {
+            Rng srng;
+            srng.init(f.seed, 2u, sid, pair * 16u + k);
+            double tm;
+            if (medium_hit(sc.med_tris, sc.media[k], so, sd, 0.001, max_t, srng, tm)) { q.far[idx] = kDeadSeg; return; }
+        }
     }
 }
 
@@ -1469,7 +1503,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow_pre(SceneView sc, WF w, SQ q,
         const RayD r = load_shadow_ray(q, idx);
         TravStats ts{0, 0};
         const uint32_t far = q.far[idx];   // BDPT_MISS (MIS segments): there is no far surface inside the segment to test first
-        live = far == BDPT_MISS || !far_endpoint_occludes(sc, r, far, STATS ? &ts : nullptr);
+        live = far != kDeadSeg && (far == BDPT_MISS || !far_endpoint_occludes(sc, r, far, STATS ? &ts : nullptr));
         if (STATS) add_trav<1, false>(stats, ts);
     }
     const uint32_t slot = warp_append(q.cnt + SQ_LIVE, live);
@@ -1487,7 +1521,7 @@ __global__ void __launch_bounds__(kBlock, kTravBlocksPerSM) k_shadow(SceneView s
     if (BVH == BDPT_BVH_REFERENCE) {
         const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
         if (i == 0) atomicAdd(reinterpret_cast<unsigned long long*>(w.counters + C_SHADOW_TOTAL), (unsigned long long)q.cnt[SQ_N]);
-        if (i < q.cnt[SQ_N]) {
+        if (i < q.cnt[SQ_N] && q.far[i] != kDeadSeg) {
             const RayD r = load_shadow_ray(q, i);
             HitD h;
             TravStats ts{0, 0};
@@ -1769,6 +1803,8 @@ void carve(WF& w, char* base) {
         for (double** d : sq) *d = c.take<double>(S);
         q.pix = c.take<uint32_t>(S); q.far = c.take<uint32_t>(S); q.live = c.take<uint32_t>(S);
         q.cnt = c.take<uint32_t>(SQ_COUNT);
+        q.mkey = (w.media && !w.mis) ? c.take<unsigned long long>(S) : nullptr;
+        q.msum = (w.media && w.mis) ? c.take<double>(S) : nullptr;
     }
     w.bytes = c.off + 256;
 }
@@ -1925,6 +1961,13 @@ void run_worker(const Job& J, Worker& wk, int /*id*/) {
     // the shadow stage of one connect round, on the side stream: front blocks drain what earlier launches
     // parked, the rest walk this round's live segments
     auto launch_shadow = [&](const SQ& q, uint32_t ns_bound) {
+        if (wf.media && ns_bound) {   // the media's share of the queued segments first (REF_SUM: kills, MIS: weighs)
+            tm.begin(KT_CONNECT, st2);
+            if (J.mis) k_media_segments<true><<<grid_for(ns_bound, kBlock), kBlock, 0, st2>>>(sc, f, wf, q);
+            else k_media_segments<false><<<grid_for(ns_bound, kBlock), kBlock, 0, st2>>>(sc, f, wf, q);
+            tm.end(KT_CONNECT, st2);
+            wk.launches += 1;
+        }
         tm.begin(KT_SHADOW, st2);
         if (o.bvh == BDPT_BVH_REFERENCE) {
             if (want_stats) k_shadow<BDPT_BVH_REFERENCE, true><<<grid_for(ns_bound, kBlock), kBlock, smem, st2>>>(sc, wf, q, sx, 0u, 0u, J.film, J.d_stats);
@@ -2110,6 +2153,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
     if (o.weighting != BDPT_WEIGHT_REF_SUM && o.weighting != BDPT_WEIGHT_MIS) { ctx->err = "unknown weighting"; return BDPT_ERR_ARG; }
     const bool mis = o.weighting == BDPT_WEIGHT_MIS;
     const bool textured = ctx->view.n_tex > 0;
+    const bool has_media = ctx->view.n_media > 0;   // the shadow queues then carry what k_media_segments needs
     if (ctx->view.n_spheres > 0 && ctx->spheres_max_mat >= ctx->view.n_mats) { ctx->err = "a sphere names a material outside the scene's table"; return BDPT_ERR_ARG; }
     int H = int(cam->image_width / cam->aspect_ratio);   // camera.h:161-162
     H = H < 1 ? 1 : H;
@@ -2146,7 +2190,7 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
         // the default takes at most half of the free device memory: a slot costs ~5 KB at depth 16 and ~25 KB at
         // depth 80 (vertex pools and shadow queues grow with the depth)
         WF probe{};
-        probe.B = 65536; probe.depth = f.depth; probe.mis = mis ? 1 : 0; probe.textured = textured ? 1 : 0;
+        probe.B = 65536; probe.depth = f.depth; probe.mis = mis ? 1 : 0; probe.textured = textured ? 1 : 0; probe.media = has_media ? 1 : 0;
         probe.scap = std::max<int64_t>(probe.B * 8, int64_t(f.depth) * probe.B * (mis ? 2 : 1));
         probe.sscap = std::max<int64_t>(4096, probe.scap / 8);
         carve(probe, nullptr);
@@ -2172,10 +2216,11 @@ int render_impl(bdpt_ctx* ctx, const bdpt_camera* cam, const bdpt_render_opts* o
             for (auto& e : wk.ev_shadow) BDPT_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             BDPT_CUDA(ctx, cudaMallocHost(&wk.hc, (C_COUNT + SQ_COUNT) * sizeof(uint32_t)));
         }
-        if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth || wk.wf.mis != (mis ? 1 : 0) || wk.wf.textured != (textured ? 1 : 0)) {
+        if (!wk.wf.base || wk.wf.B < B || wk.wf.depth < f.depth || wk.wf.mis != (mis ? 1 : 0) || wk.wf.textured != (textured ? 1 : 0) ||
+            wk.wf.media != (has_media ? 1 : 0)) {
             if (wk.wf.base) { BDPT_CUDA(ctx, cudaStreamSynchronize(wk.stream)); cudaFree(wk.wf.base); }
             std::memset(&wk.wf, 0, sizeof(WF));
-            wk.wf.B = B; wk.wf.depth = f.depth; wk.wf.mis = mis ? 1 : 0; wk.wf.textured = textured ? 1 : 0;
+            wk.wf.B = B; wk.wf.depth = f.depth; wk.wf.mis = mis ? 1 : 0; wk.wf.textured = textured ? 1 : 0; wk.wf.media = has_media ? 1 : 0;
             wk.wf.scap = std::max<int64_t>(B * 8, int64_t(f.depth) * B * (mis ? 2 : 1));   // >= one camera slot against every light vertex (MIS: + the splats)
             wk.wf.scap = std::min<int64_t>(wk.wf.scap, int64_t(0xFFFFFFF0u));
             wk.wf.sscap = std::max<int64_t>(4096, wk.wf.scap / 8);
