@@ -406,25 +406,76 @@ __device__ __noinline__ bool boundary_hit_tree(const TriGeom* __restrict__ tris,
     *t_out = closest;
     return any;
 }
+// Both boundary hits from ONE walk of a large boundary's tree: every candidate t along the whole line is kept (a closed mesh gives a
+// handful), then the two queries are answered from them as for a small boundary.  false: more than `cap` candidates -- ask twice.
+__device__ __noinline__ bool boundary_candidates_tree(const TriGeom* __restrict__ tris, const MedNode* __restrict__ nodes, D3 o, D3 d, double* ts, uint32_t cap,
+                                                      uint32_t* n_out) {
+    const double oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+    double inv[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) inv[k] = 1.0 / dd[k];
+    int32_t stack[24];
+    int sp = 0;
+    int32_t cur = 0;
+    uint32_t n = 0;
+    for (;;) {
+        const MedNode* nd = nodes + cur;
+        double tn = -__longlong_as_double(0x7FF0000000000000LL), tf = __longlong_as_double(0x7FF0000000000000LL);
+        bool hit = true;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double lo = nd->lo[k], hi = nd->hi[k];
+            if (dd[k] == 0.0) { if (oo[k] < lo || oo[k] > hi) hit = false; }
+            else {
+                const double a = (lo - oo[k]) * inv[k], b = (hi - oo[k]) * inv[k];
+                tn = fmax(tn, fmin(a, b)); tf = fmin(tf, fmax(a, b));
+            }
+        }
+        if (hit && !(tn > tf)) {
+            const int32_t a = nd->a, b = nd->b;
+            if (b < 0) {
+                for (int32_t i = 0; i < -b; ++i) {
+                    double t, u, v;
+                    if (tri_candidate(tris + a + i, o, d, t, u, v) && t == t) {
+                        if (n == cap) return false;
+                        ts[n++] = t;
+                    }
+                }
+            } else {
+                stack[sp++] = b;
+                cur = a;
+                continue;
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    *n_out = n;
+    return true;
+}
 // The two boundary hits constant_medium::hit asks for (constant_medium.h:25-29): the nearest over the whole line, then the nearest from
 // 0.0001 behind it.  Small boundaries (a box is 12 triangles) are met ONCE: the candidates' t are kept and the second query reads them
 // back -- the same comparisons on the same numbers as two loops over the triangles.
 __device__ __forceinline__ bool boundary_pair(const TriGeom* __restrict__ med_tris, const MediumDev& m, const D3& o, const D3& d, double& t1, double& t2) {
     const double inf = __longlong_as_double(0x7FF0000000000000LL);
     constexpr uint32_t kKeep = 16;
-    if (m.nodes) return boundary_hit_tree(med_tris + m.first, m.nodes, o, d, -inf, inf, &t1) && boundary_hit_tree(med_tris + m.first, m.nodes, o, d, t1 + 0.0001, inf, &t2);
-    if (m.count > kKeep) return boundary_hit(med_tris, m, o, d, -inf, inf, t1) && boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2);
     double ts[kKeep];
     uint32_t n = 0;
-    double c1 = inf;
-    bool any = false;
-    for (uint32_t i = 0; i < m.count; ++i) {
-        double t, u, v;
-        if (tri_candidate(med_tris + m.first + i, o, d, t, u, v) && t == t) {
-            ts[n++] = t;
-            if (t <= c1) { any = true; c1 = t; }
+    if (m.nodes) {
+        if (!boundary_candidates_tree(med_tris + m.first, m.nodes, o, d, ts, kKeep, &n))
+            return boundary_hit_tree(med_tris + m.first, m.nodes, o, d, -inf, inf, &t1) && boundary_hit_tree(med_tris + m.first, m.nodes, o, d, t1 + 0.0001, inf, &t2);
+    } else if (m.count > kKeep) {
+        return boundary_hit(med_tris, m, o, d, -inf, inf, t1) && boundary_hit(med_tris, m, o, d, t1 + 0.0001, inf, t2);
+    } else {
+        for (uint32_t i = 0; i < m.count; ++i) {
+            double t, u, v;
+            if (tri_candidate(med_tris + m.first + i, o, d, t, u, v) && t == t) ts[n++] = t;
         }
     }
+    double c1 = inf;
+    bool any = false;
+    for (uint32_t i = 0; i < n; ++i)
+        if (ts[i] <= c1) { any = true; c1 = ts[i]; }
     if (!any) return false;
     t1 = c1;
     const double from = t1 + 0.0001;
