@@ -561,8 +561,17 @@ __device__ __forceinline__ uint32_t prim_mat(const SceneView& sc, uint32_t prim)
 // world.hit's media for one path ray.  Out of line on purpose: inlined into finish_trace its fp64 triangle loops raise the
 // register pressure of every traversal kernel (k_trace_fast: 150 -> 538 bytes of spills), scenes without media included.
 struct MediaOut { double t; uint32_t prim, found; };
+__device__ __noinline__ void spheres_after_triangles(const SphereDev* __restrict__ spheres, uint32_t n_spheres, const PathRec* path, MediaOut* io) {
+    const double2* q = reinterpret_cast<const double2*>(path);
+    const double2 q0 = q[0], q1 = q[1], q2 = q[2];
+    const D3 o = mk(q0.x, q0.y, q1.x), d = mk(q1.y, q2.x, q2.y);
+    double best = io->found ? io->t : __longlong_as_double(0x7FF0000000000000LL);
+    for (uint32_t k = 0; k < n_spheres; ++k) {   // in list order, against the bound so far
+        double ts;
+        if (sphere_hit_t(spheres[k], o, d, 0.001, best, ts)) { io->found = 1u; best = ts; io->t = ts; io->prim = kSpherePrim | k; }
+    }
+}
 __device__ __noinline__ void media_after_triangles(const MediumDev* __restrict__ media, const TriGeom* __restrict__ med_tris, uint32_t n_media,
-                                                   const SphereDev* __restrict__ spheres, uint32_t n_spheres,
                                                    PathRec* path, uint64_t seed, uint32_t stream, uint64_t sid, MediaOut* io) {
     const double2* q = reinterpret_cast<const double2*>(path);
     const double2 q0 = q[0], q1 = q[1], q2 = q[2];
@@ -571,10 +580,6 @@ __device__ __noinline__ void media_after_triangles(const MediumDev* __restrict__
     rng.init(seed, stream, sid, path->draws);
     const uint32_t d0 = rng.draws;
     double best = io->found ? io->t : __longlong_as_double(0x7FF0000000000000LL);
-    for (uint32_t k = 0; k < n_spheres; ++k) {   // the sphere prims of the side list, in order, against the bound so far
-        double ts;
-        if (sphere_hit_t(spheres[k], o, d, 0.001, best, ts)) { io->found = 1u; best = ts; io->t = ts; io->prim = kSpherePrim | k; }
-    }
     for (uint32_t k = 0; k < n_media; ++k) {
         double tm;
         if (medium_hit(med_tris, media[k], o, d, 0.001, best, rng, tm)) { io->found = 1u; best = tm; io->t = tm; io->prim = kMediumPrim | k; }
@@ -582,6 +587,16 @@ __device__ __noinline__ void media_after_triangles(const MediumDev* __restrict__
     if (rng.draws != d0) path->draws = rng.draws;
 }
 
+__device__ __forceinline__ RayD load_path_ray(const WF& w, uint32_t pid) {
+    RayD r;
+    const double2* q = reinterpret_cast<const double2*>(w.path + pid);
+    const double2 q0 = q[0], q1 = q[1], q2 = q[2];
+    r.o = mk(q0.x, q0.y, q1.x);
+    r.d = mk(q1.y, q2.x, q2.y);
+    r.tmin = 0.001;
+    r.tmax = __longlong_as_double(0x7FF0000000000000LL);
+    return r;
+}
 template <bool MEDIA = false>
 __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f, const WF& w, uint32_t pid, bool found,
                                             const HitD& h, double* film) {
@@ -592,8 +607,12 @@ __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f,
         const uint32_t b = is_cam ? pid : pid - uint32_t(w.B);
         MediaOut mo;
         mo.found = found ? 1u : 0u; mo.prim = prim; mo.t = t;
-        media_after_triangles(sc.media, sc.med_tris, sc.n_media, sc.spheres, sc.n_spheres, w.path + pid, f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, &mo);
-        found = mo.found != 0; prim = mo.prim; t = mo.t;
+        // the sphere prims of the side list first (their own small call: a scene of spheres only never pays the media's big one)
+        if (sc.n_spheres) { spheres_after_triangles(sc.spheres, sc.n_spheres, w.path + pid, &mo); found = mo.found != 0; prim = mo.prim; t = mo.t; }
+        if (sc.n_media) {
+            media_after_triangles(sc.media, sc.med_tris, sc.n_media, w.path + pid, f.seed, is_cam ? 0u : 1u, decode_sample(f, w.sample[b]).sid, &mo);
+            found = mo.found != 0; prim = mo.prim; t = mo.t;
+        }
     }
     if (found) {
         w.path[pid].hit_prim = prim;
@@ -609,16 +628,6 @@ __device__ __forceinline__ int finish_trace(const SceneView& sc, const Frame& f,
         if (c.x != 0.0 || c.y != 0.0 || c.z != 0.0) film_add(film, decode_sample(f, w.sample[pid]).pix, c);
     }
     return -1;
-}
-__device__ __forceinline__ RayD load_path_ray(const WF& w, uint32_t pid) {
-    RayD r;
-    const double2* q = reinterpret_cast<const double2*>(w.path + pid);
-    const double2 q0 = q[0], q1 = q[1], q2 = q[2];
-    r.o = mk(q0.x, q0.y, q1.x);
-    r.d = mk(q1.y, q2.x, q2.y);
-    r.tmin = 0.001;
-    r.tmax = __longlong_as_double(0x7FF0000000000000LL);
-    return r;
 }
 template <bool MEDIA = false>
 __device__ __forceinline__ void bin_by_material(const WF& w, int cls, uint32_t pid) {
